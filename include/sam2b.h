@@ -1,0 +1,87 @@
+/* sam2b — C ABI of the B200-native (sm_100a) SAM2.1 Hiera-L hot path.
+ *
+ * This is the drop-in boundary for the sub-graphs FasterProcess/sam2_opt hands to a backend executor
+ * (reference: sam2/ytools/executor/model_executor.py:133-169 `ModelExectuor.Inference`), i.e. what its
+ * TensorRT engines compute:
+ *   E1/E2  image encoder   sam2/sam2/sam2_image_predictor.py:252-276 (set_image_e2e_*),
+ *                          sam2/sam2/modeling/sam2_base_official.py:566-598 (inference_image_*)
+ *   E3     memory attention sam2/sam2/modeling/memory_attention.py:283-381 (inference_memory_attention_*)
+ *   E4     memory encoder   sam2/sam2/modeling/memory_encoder.py:228-251 (inference_memory_*)
+ *
+ * Conventions: every pointer marked `dev` is a CUDA device pointer on the engine's device; tensors are
+ * contiguous fp32 in the reference's own layouts; `stream` is a cudaStream_t (work is enqueued on it and the call
+ * returns without synchronising, like TensorRTExecutor's event hand-off, tensorrt_executor.py:251-289);
+ * inputs are borrowed for the duration of the enqueued work, outputs are caller-allocated.
+ * Every function returns 0 on success; otherwise sam2b_last_error() describes the failure (thread-local).
+ * There is no CPU fallback: without a CUDA device sam2b_create fails.
+ */
+#ifndef SAM2B_H_
+#define SAM2B_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct sam2b_engine* sam2b_handle;
+
+const char* sam2b_last_error(void);
+const char* sam2b_version(void);
+/* number of kernels this library has launched so far in this process (all engines) */
+unsigned long long sam2b_launch_count(void);
+
+/* ---- engine life cycle (replaces TensorRTExecutor.__init__/Release, tensorrt_executor.py:16-73,311-334) ---- */
+int sam2b_create(int device, sam2b_handle* out);
+int sam2b_destroy(sam2b_handle h);
+/* Register one tensor of the reference state_dict (reference names, e.g. "image_encoder.trunk.blocks.0.attn.qkv.weight")
+ * or a derived constant ("derived.*", see sam2_opt_b200/weights.py).  The data is copied (device to device). */
+int sam2b_set_tensor(sam2b_handle h, const char* name, const float* dev_data, const int64_t* shape, int ndim);
+/* Repack weights into kernel layouts (bf16 K-major) and check that everything the path needs is present. */
+int sam2b_finalize(sam2b_handle h);
+
+/* ---- E1 / E2: Hiera-L trunk + FpnNeck + conv_s0/conv_s1 ----
+ * img      dev [n,3,1024,1024]; normalised=1: already (x-mean)/std (E2, inference_image);
+ *                               normalised=0: raw [0,1] pixels, normalisation is fused (E1, set_image_e2e)
+ * add_no_mem_embed: 1 adds no_mem_embed to the 64x64 level (E1, sam2_image_predictor.py:259-260)
+ * fpn0 dev [n,32,256,256], fpn1 dev [n,64,128,128], fpn2 dev [n,256,64,64]  (NCHW fp32)
+ * (vision_features == fpn2; the vision_pos_enc outputs are constants, see sam2b_position_encoding) */
+int sam2b_image_encode(sam2b_handle h, const float* img, int n, int normalised, int add_no_mem_embed,
+                       float* fpn0, float* fpn1, float* fpn2, void* stream);
+/* Same, with HOST buffers (pinned or pageable): H2D of the images and D2H of the three outputs are issued on `stream`
+ * in micro-batches overlapped with compute; returns after the stream has been synchronised. */
+int sam2b_image_encode_host(sam2b_handle h, const float* img_host, int n, int normalised, int add_no_mem_embed,
+                            float* fpn0_host, float* fpn1_host, float* fpn2_host, void* stream);
+
+/* ---- E3: 4-layer MemoryAttention ----
+ * curr, curr_pos dev [4096,n,256]; memory, memory_pos dev [L,4096,n,64]; memory_exclude, memory_pos_exclude dev [P,n,64]
+ * (P may be 0, then both may be NULL: the `none` variant); out dev [4096,n,256]. L in [1,7], P in [0,64]. */
+int sam2b_memory_attention(sam2b_handle h, const float* curr, const float* curr_pos, const float* memory,
+                           const float* memory_pos, int L, const float* memory_exclude,
+                           const float* memory_pos_exclude, int P, int n, float* out, void* stream);
+
+/* ---- E4: MemoryEncoder ----
+ * pix_feat dev [n,256,64,64], masks dev [n,1,1024,1024] (already sigmoid-scaled) -> out_x dev [n,64,64,64].
+ * (the second reference output, the sine position encoding, is a constant: sam2b_position_encoding) */
+int sam2b_memory_encode(sam2b_handle h, const float* pix_feat, const float* masks, int n, float* out_x, void* stream);
+
+/* ---- building blocks (used by the parity tests and available to other callers) ---- */
+/* C[b][m][n] = act(alpha * A[b] B[b]^T + bias) * gamma + residual ; A [batch,M,K], B [batch or 1,N,K] bf16 K-major.
+ * act: 0 none, 1 exact GELU, 2 ReLU.  Exactly one of out_f32 / out_bf16 may be NULL. */
+int sam2b_op_gemm(const void* a_bf16, int64_t lda, int64_t a_batch_stride, const void* b_bf16, int64_t ldb,
+                  int64_t b_batch_stride, int m, int n, int k, int batch, float alpha, const float* bias,
+                  int bias_along_m, int act, const float* gamma, const float* residual, int64_t ld_res,
+                  int64_t res_batch_stride, int res_row_mod, float* out_f32, void* out_bf16, int64_t ldc,
+                  int64_t c_batch_stride, int force_block_n, void* stream);
+int sam2b_op_layernorm(const float* x, const float* gamma, const float* beta, float eps, void* y_bf16, float* y_f32,
+                       int64_t rows, int c, void* stream);
+int sam2b_op_cast_bf16(const float* x, void* y_bf16, int64_t n, void* stream);
+int sam2b_op_maxpool2x2_nhwc(const float* x, float* y, int b, int hgt, int wid, int c, void* stream);
+int sam2b_op_window_attention(const void* qkv_bf16, void* out_bf16, int b, int hgt, int wid, int heads, int ws,
+                              int q_pool, void* stream);
+int sam2b_op_softmax_rows(const float* s, int64_t lds, void* p_bf16, int64_t ldp, int64_t rows, int cols, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SAM2B_H_ */

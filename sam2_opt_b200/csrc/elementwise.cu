@@ -1,0 +1,303 @@
+// Memory-bound kernels of the path (SURVEY.md §8a' K5/K6/K7/K8/K11): LayerNorm rows with fp32 statistics
+// and bf16 output (GEMM operand), casts, 2x2 max-pool of the skip path, patch-embed im2col, FPN top-down add,
+// row softmax and RoPE.  All are coalesced / 16-byte vectorised; reductions are warp shuffles.
+#include "common.cuh"
+#include "ops.h"
+
+namespace sam2b {
+
+// ------------------------------------------------------------------------------------------
+// LayerNorm over the last dim (reference: nn.LayerNorm in hieradet.py:104,122 eps 1e-6;
+// memory_attention.py:44-46 eps 1e-5).  One warp per row, row kept in registers, two-pass variance.
+// ------------------------------------------------------------------------------------------
+template <int MAXV>  // max float4 per lane
+__global__ void __launch_bounds__(256) layernorm_rows_kernel(const float* __restrict__ x, const float* __restrict__ gamma,
+                                                             const float* __restrict__ beta, float eps,
+                                                             bf16* __restrict__ y16, float* __restrict__ y32, long rows, int C) {
+  const int lane = threadIdx.x & 31;
+  const long row = (long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (row >= rows) return;
+  const int nv = C >> 2;
+  const float4* xr = reinterpret_cast<const float4*>(x + row * C);
+  float4 v[MAXV];
+  float s = 0.f;
+#pragma unroll
+  for (int i = 0; i < MAXV; ++i) {
+    const int idx = lane + i * 32;
+    if (idx < nv) {
+      v[i] = xr[idx];
+      s += (v[i].x + v[i].y) + (v[i].z + v[i].w);
+    } else {
+      v[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+  }
+  const float mean = warp_sum(s) / (float)C;
+  float q = 0.f;
+#pragma unroll
+  for (int i = 0; i < MAXV; ++i) {
+    const int idx = lane + i * 32;
+    if (idx < nv) {
+      const float a = v[i].x - mean, b = v[i].y - mean, c = v[i].z - mean, d = v[i].w - mean;
+      q += (a * a + b * b) + (c * c + d * d);
+    }
+  }
+  const float rstd = rsqrtf(warp_sum(q) / (float)C + eps);
+#pragma unroll
+  for (int i = 0; i < MAXV; ++i) {
+    const int idx = lane + i * 32;
+    if (idx < nv) {
+      const float4 g = __ldg(reinterpret_cast<const float4*>(gamma) + idx);
+      const float4 b = __ldg(reinterpret_cast<const float4*>(beta) + idx);
+      float4 o;
+      o.x = (v[i].x - mean) * rstd * g.x + b.x;
+      o.y = (v[i].y - mean) * rstd * g.y + b.y;
+      o.z = (v[i].z - mean) * rstd * g.z + b.z;
+      o.w = (v[i].w - mean) * rstd * g.w + b.w;
+      if (y16) {
+        uint2 pk;
+        pk.x = pack_bf16x2(o.x, o.y);
+        pk.y = pack_bf16x2(o.z, o.w);
+        reinterpret_cast<uint2*>(y16 + row * C)[idx] = pk;
+      }
+      if (y32) reinterpret_cast<float4*>(y32 + row * C)[idx] = o;
+    }
+  }
+}
+
+int layernorm_rows(const float* x, const float* gamma, const float* beta, float eps, bf16* y16, float* y32, long rows,
+                   int C, cudaStream_t stream) {
+  if (C % 4 || C > 1152) { set_error("layernorm_rows: unsupported C=%d", C); return 1; }
+  const int nv = C / 4;
+  const int wpb = 8;
+  const unsigned grid = (unsigned)((rows + wpb - 1) / wpb);
+  if (nv <= 64) layernorm_rows_kernel<2><<<grid, 256, 0, stream>>>(x, gamma, beta, eps, y16, y32, rows, C);
+  else if (nv <= 96) layernorm_rows_kernel<3><<<grid, 256, 0, stream>>>(x, gamma, beta, eps, y16, y32, rows, C);
+  else if (nv <= 160) layernorm_rows_kernel<5><<<grid, 256, 0, stream>>>(x, gamma, beta, eps, y16, y32, rows, C);
+  else layernorm_rows_kernel<9><<<grid, 256, 0, stream>>>(x, gamma, beta, eps, y16, y32, rows, C);
+  SAM2B_CHECK_LAUNCH("layernorm_rows");
+  return 0;
+}
+
+// ------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) cast_f32_bf16_kernel(const float4* __restrict__ x, uint2* __restrict__ y, long n4) {
+  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (long)gridDim.x * blockDim.x) {
+    const float4 v = x[i];
+    uint2 pk;
+    pk.x = pack_bf16x2(v.x, v.y);
+    pk.y = pack_bf16x2(v.z, v.w);
+    y[i] = pk;
+  }
+}
+int cast_f32_bf16(const float* x, bf16* y, long n, cudaStream_t stream) {
+  if (n % 4) { set_error("cast_f32_bf16: n=%ld not a multiple of 4", n); return 1; }
+  const long n4 = n / 4;
+  long blocks = (n4 + 255) / 256;
+  if (blocks > (long)num_sms() * 16) blocks = (long)num_sms() * 16;
+  cast_f32_bf16_kernel<<<(unsigned)blocks, 256, 0, stream>>>(reinterpret_cast<const float4*>(x), reinterpret_cast<uint2*>(y), n4);
+  SAM2B_CHECK_LAUNCH("cast_f32_bf16");
+  return 0;
+}
+
+// ------------------------------------------------------------------------------------------
+// 2x2 max-pool, NHWC fp32 (reference: do_pool / MaxPool2d(2,2) on the skip path, hieradet.py:25-36,140-142)
+// ------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) maxpool2x2_nhwc_kernel(const float4* __restrict__ x, float4* __restrict__ y, int B, int H,
+                                                              int W, int C4) {
+  const int Ho = H >> 1, Wo = W >> 1;
+  const long total = (long)B * Ho * Wo * C4;
+  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
+    const int c = (int)(i % C4);
+    long t = i / C4;
+    const int ox = (int)(t % Wo); t /= Wo;
+    const int oy = (int)(t % Ho);
+    const int b = (int)(t / Ho);
+    const long base = (((long)b * H + 2 * oy) * W + 2 * ox) * C4 + c;
+    const float4 a = x[base], bq = x[base + C4], cq = x[base + (long)W * C4], d = x[base + (long)W * C4 + C4];
+    float4 o;
+    o.x = fmaxf(fmaxf(a.x, bq.x), fmaxf(cq.x, d.x));
+    o.y = fmaxf(fmaxf(a.y, bq.y), fmaxf(cq.y, d.y));
+    o.z = fmaxf(fmaxf(a.z, bq.z), fmaxf(cq.z, d.z));
+    o.w = fmaxf(fmaxf(a.w, bq.w), fmaxf(cq.w, d.w));
+    y[i] = o;
+  }
+}
+int maxpool2x2_nhwc(const float* x, float* y, int B, int H, int W, int C, cudaStream_t stream) {
+  if (C % 4 || H % 2 || W % 2) { set_error("maxpool2x2_nhwc: bad shape"); return 1; }
+  const long total = (long)B * (H / 2) * (W / 2) * (C / 4);
+  long blocks = (total + 255) / 256;
+  if (blocks > (long)num_sms() * 16) blocks = (long)num_sms() * 16;
+  maxpool2x2_nhwc_kernel<<<(unsigned)blocks, 256, 0, stream>>>(reinterpret_cast<const float4*>(x), reinterpret_cast<float4*>(y), B, H, W, C / 4);
+  SAM2B_CHECK_LAUNCH("maxpool2x2_nhwc");
+  return 0;
+}
+
+// ------------------------------------------------------------------------------------------
+// Patch-embed im2col (reference: PatchEmbed Conv2d(3,144,k7,s4,p3), backbones/utils.py:63-93;
+// optional (x-mean)/std of SAM2Transforms, utils/transforms.py:27-31).  One thread per 8-tap chunk.
+// ------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) patch_im2col_kernel(const float* __restrict__ img, uint4* __restrict__ cols, int B, int S,
+                                                           int normalise) {
+  const int So = S >> 2;
+  const long total = (long)B * So * So * 20;
+  const float mean[3] = {0.485f, 0.456f, 0.406f};
+  const float istd[3] = {1.f / 0.229f, 1.f / 0.224f, 1.f / 0.225f};
+  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
+    const int chunk = (int)(i % 20);
+    long t = i / 20;
+    const int ox = (int)(t % So); t /= So;
+    const int oy = (int)(t % So);
+    const int b = (int)(t / So);
+    float v[8];
+#pragma unroll
+    for (int e = 0; e < 8; ++e) {
+      const int k = chunk * 8 + e;
+      float val = 0.f;
+      if (k < 147) {
+        const int c = k / 49, r = k % 49, ky = r / 7, kx = r % 7;
+        const int y = oy * 4 - 3 + ky, x = ox * 4 - 3 + kx;
+        if (y >= 0 && y < S && x >= 0 && x < S) {
+          val = __ldg(img + (((long)b * 3 + c) * S + y) * S + x);
+          if (normalise) val = (val - mean[c]) * istd[c];
+        }
+      }
+      v[e] = val;
+    }
+    uint4 pk;
+    pk.x = pack_bf16x2(v[0], v[1]); pk.y = pack_bf16x2(v[2], v[3]);
+    pk.z = pack_bf16x2(v[4], v[5]); pk.w = pack_bf16x2(v[6], v[7]);
+    cols[i] = pk;
+  }
+}
+int patch_im2col(const float* img, bf16* cols, int B, int S, int normalise, cudaStream_t stream) {
+  if (S % 4) { set_error("patch_im2col: S=%d", S); return 1; }
+  const long total = (long)B * (S / 4) * (S / 4) * 20;
+  long blocks = (total + 255) / 256;
+  if (blocks > (long)num_sms() * 32) blocks = (long)num_sms() * 32;
+  patch_im2col_kernel<<<(unsigned)blocks, 256, 0, stream>>>(img, reinterpret_cast<uint4*>(cols), B, S, normalise);
+  SAM2B_CHECK_LAUNCH("patch_im2col");
+  return 0;
+}
+
+// ------------------------------------------------------------------------------------------
+// FPN top-down: dst += nearest_x2(src)   (reference: image_encoder.py:115-127, fpn_interp_model nearest)
+// ------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) upsample2x_add_kernel(float4* __restrict__ dst, const float2* __restrict__ src, long total4, int W4,
+                                                             int H, int Ws2) {
+  // dst viewed as float4 (4 consecutive x) ; src as float2 (2 consecutive x)
+  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < total4; i += (long)gridDim.x * blockDim.x) {
+    const int x4 = (int)(i % W4);
+    long t = i / W4;
+    const int y = (int)(t % H);
+    const long bc = t / H;
+    const float2 s = src[(bc * (H >> 1) + (y >> 1)) * Ws2 + x4];
+    float4 d = dst[i];
+    d.x += s.x; d.y += s.x; d.z += s.y; d.w += s.y;
+    dst[i] = d;
+  }
+}
+int upsample2x_add_nchw(float* dst, const float* src, int B, int C, int H, int W, cudaStream_t stream) {
+  if (W % 4 || H % 2) { set_error("upsample2x_add: bad shape"); return 1; }
+  const long total4 = (long)B * C * H * (W / 4);
+  long blocks = (total4 + 255) / 256;
+  if (blocks > (long)num_sms() * 16) blocks = (long)num_sms() * 16;
+  upsample2x_add_kernel<<<(unsigned)blocks, 256, 0, stream>>>(reinterpret_cast<float4*>(dst), reinterpret_cast<const float2*>(src), total4, W / 4, H, W / 4);
+  SAM2B_CHECK_LAUNCH("upsample2x_add");
+  return 0;
+}
+
+// ------------------------------------------------------------------------------------------
+// Row softmax fp32 -> bf16 (memory-attention scores).  One CTA per row; the row is staged in shared
+// memory so HBM/L2 sees it once.
+// ------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(512) softmax_rows_kernel(const float* __restrict__ s, long lds, bf16* __restrict__ p, long ldp, int cols) {
+  extern __shared__ float row[];
+  __shared__ float red[16];
+  const float* sr = s + (long)blockIdx.x * lds;
+  bf16* pr = p + (long)blockIdx.x * ldp;
+  const int tid = threadIdx.x, nt = blockDim.x, lane = tid & 31, wid = tid >> 5, nw = nt >> 5;
+  const int c4 = cols >> 2;
+  float m = -INFINITY;
+  for (int i = tid; i < c4; i += nt) {
+    const float4 v = reinterpret_cast<const float4*>(sr)[i];
+    reinterpret_cast<float4*>(row)[i] = v;
+    m = fmaxf(m, fmaxf(fmaxf(v.x, v.y), fmaxf(v.z, v.w)));
+  }
+  for (int i = (c4 << 2) + tid; i < cols; i += nt) { row[i] = sr[i]; m = fmaxf(m, sr[i]); }
+  m = warp_max(m);
+  if (lane == 0) red[wid] = m;
+  __syncthreads();
+  m = red[0];
+  for (int i = 1; i < nw; ++i) m = fmaxf(m, red[i]);
+  __syncthreads();
+  float sum = 0.f;
+  for (int i = tid; i < cols; i += nt) {
+    const float e = __expf(row[i] - m);
+    row[i] = e;
+    sum += e;
+  }
+  sum = warp_sum(sum);
+  if (lane == 0) red[wid] = sum;
+  __syncthreads();
+  sum = 0.f;
+  for (int i = 0; i < nw; ++i) sum += red[i];
+  const float inv = 1.0f / sum;
+  const int ldp2 = (int)(ldp >> 1);
+  for (int i = tid; i < ldp2; i += nt) {
+    const int c = 2 * i;
+    const float a = c < cols ? row[c] * inv : 0.f;
+    const float b = c + 1 < cols ? row[c + 1] * inv : 0.f;
+    reinterpret_cast<uint32_t*>(pr)[i] = pack_bf16x2(a, b);
+  }
+}
+int softmax_rows(const float* s, long lds, bf16* p, long ldp, long rows, int cols, cudaStream_t stream) {
+  const size_t smem = (size_t)cols * 4 + 16;
+  if (smem > 200 * 1024 || (lds % 4) || (ldp % 2) || ldp < cols) { set_error("softmax_rows: unsupported cols=%d lds=%ld ldp=%ld", cols, lds, ldp); return 1; }
+  static bool attr = false;
+  if (!attr) {
+    cudaFuncSetAttribute(softmax_rows_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+    attr = true;
+  }
+  softmax_rows_kernel<<<(unsigned)rows, 512, smem, stream>>>(s, lds, p, ldp, cols);
+  SAM2B_CHECK_LAUNCH("softmax_rows");
+  return 0;
+}
+
+// ------------------------------------------------------------------------------------------
+// RoPE + cast (reference: apply_rotary_emb, position_encoding_fix.py:192-205; RoPEAttention.forward
+// transformer.py:380-418: table repeats every 4096 rows, rows >= rope_rows are left un-rotated).
+// cos_t / sin_t: [4096,128] (angle of pair i at grid position r).
+// ------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) rope_cast_rows_kernel(const float* __restrict__ x, const float* __restrict__ cos_t,
+                                                             const float* __restrict__ sin_t, bf16* __restrict__ y, long rows, long rope_rows) {
+  // one thread per 2 pairs (4 floats): 64 threads per row
+  const long total = rows * 64;
+  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
+    const long r = i >> 6;
+    const int j = (int)(i & 63);
+    const float4 v = reinterpret_cast<const float4*>(x)[i];
+    float4 o = v;
+    if (r < rope_rows) {
+      const int pos = (int)(r & 4095);
+      const float2 c = reinterpret_cast<const float2*>(cos_t)[pos * 64 + j];
+      const float2 s = reinterpret_cast<const float2*>(sin_t)[pos * 64 + j];
+      o.x = v.x * c.x - v.y * s.x;
+      o.y = v.x * s.x + v.y * c.x;
+      o.z = v.z * c.y - v.w * s.y;
+      o.w = v.z * s.y + v.w * c.y;
+    }
+    uint2 pk;
+    pk.x = pack_bf16x2(o.x, o.y);
+    pk.y = pack_bf16x2(o.z, o.w);
+    reinterpret_cast<uint2*>(y)[i] = pk;
+  }
+}
+int rope_cast_rows(const float* x, const float* cos_t, const float* sin_t, bf16* y, long rows, long rope_rows, cudaStream_t stream) {
+  const long total = rows * 64;
+  long blocks = (total + 255) / 256;
+  if (blocks > (long)num_sms() * 16) blocks = (long)num_sms() * 16;
+  rope_cast_rows_kernel<<<(unsigned)blocks, 256, 0, stream>>>(x, cos_t, sin_t, y, rows, rope_rows);
+  SAM2B_CHECK_LAUNCH("rope_cast_rows");
+  return 0;
+}
+
+}  // namespace sam2b

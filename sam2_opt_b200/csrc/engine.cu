@@ -1,0 +1,458 @@
+// Engine: weight store + workspace + the kernel schedules of the three sub-graphs, behind the C ABI of
+// include/sam2b.h.  Reference call sites it replaces: ImageEncoder.forward (modeling/backbones/image_encoder.py:29-42)
+// = Hiera.forward (hieradet.py:283-299) + FpnNeck.forward (image_encoder.py:102-134) + conv_s0/s1
+// (sam2_base_official.py:571-577); MemoryAttention (memory_attention.py:299-349); MemoryEncoder (memory_encoder.py:233-241).
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <map>
+#include <string>
+#include <vector>
+
+#include "../../include/sam2b.h"
+#include "ops.h"
+
+namespace sam2b {
+
+static thread_local char g_err[1024] = "";
+unsigned long long g_launch_count = 0;
+
+void set_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+}
+const char* get_error() { return g_err; }
+
+int num_sms() {
+  static int n = 0;
+  if (!n) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
+    if (n <= 0) n = 148;
+  }
+  return n;
+}
+
+#define CUDA_OK(expr)                                                              \
+  do {                                                                             \
+    cudaError_t e__ = (expr);                                                      \
+    if (e__ != cudaSuccess) {                                                      \
+      set_error("%s failed: %s (%s:%d)", #expr, cudaGetErrorString(e__), __FILE__, __LINE__); \
+      return 1;                                                                    \
+    }                                                                              \
+  } while (0)
+#define TRY(expr) do { if (expr) return 1; } while (0)
+
+struct Tensor {
+  float* f32 = nullptr;
+  bf16* b16 = nullptr;
+  std::vector<int64_t> shape;
+  int64_t numel = 0;
+};
+
+struct Buf {
+  void* p = nullptr;
+  size_t bytes = 0;
+};
+
+struct BlockCfg { int dim, dim_out, heads, window, q_pool; };
+
+}  // namespace sam2b
+
+using namespace sam2b;
+
+struct sam2b_engine {
+  int device = 0;
+  bool finalized = false;
+  std::map<std::string, Tensor> w;
+  std::map<std::string, Buf> ws;   // named workspace buffers, grow-only
+  std::vector<BlockCfg> blocks;
+  cudaStream_t copy_stream = nullptr;
+  cudaEvent_t ev[8] = {};
+
+  Tensor* find(const std::string& n) {
+    auto it = w.find(n);
+    return it == w.end() ? nullptr : &it->second;
+  }
+};
+
+namespace sam2b {
+
+static int ws_get(sam2b_engine* e, const char* name, size_t bytes, void** out) {
+  Buf& b = e->ws[name];
+  if (b.bytes < bytes) {
+    if (b.p) CUDA_OK(cudaFree(b.p));
+    b.p = nullptr; b.bytes = 0;
+    CUDA_OK(cudaMalloc(&b.p, bytes));
+    b.bytes = bytes;
+  }
+  *out = b.p;
+  return 0;
+}
+template <typename T>
+static int ws_get_t(sam2b_engine* e, const char* name, size_t count, T** out) {
+  void* p = nullptr;
+  TRY(ws_get(e, name, count * sizeof(T), &p));
+  *out = reinterpret_cast<T*>(p);
+  return 0;
+}
+
+static void build_block_cfgs(std::vector<BlockCfg>& out) {
+  // Hiera-L: configs/sam2.1/sam2.1_hiera_l.yaml:10-16, hieradet.py:233-260 (window lags one block at stage changes)
+  const int stages[4] = {2, 6, 36, 4};
+  const int window_spec[4] = {8, 4, 16, 8};
+  const int stage_ends[4] = {1, 7, 43, 47};
+  int dim = 144, heads = 2, cur_stage = 1;
+  for (int i = 0; i < stages[0] + stages[1] + stages[2] + stages[3]; ++i) {
+    int dim_out = dim;
+    int window = window_spec[cur_stage - 1];
+    if (i == 23 || i == 33 || i == 43) window = 0;
+    bool after_end = false;
+    for (int s : stage_ends) after_end |= (i - 1 == s);
+    if (after_end) { dim_out = dim * 2; heads *= 2; cur_stage += 1; }
+    BlockCfg c{dim, dim_out, heads, window, (i == 2 || i == 8 || i == 44) ? 1 : 0};
+    out.push_back(c);
+    dim = dim_out;
+  }
+}
+
+static int need(sam2b_engine* e, const std::string& name, Tensor** t, bool want_bf16) {
+  Tensor* x = e->find(name);
+  if (!x) { set_error("missing tensor '%s' (call sam2b_set_tensor for every state_dict / derived entry)", name.c_str()); return 1; }
+  if (want_bf16 && !x->b16) {
+    CUDA_OK(cudaMalloc(&x->b16, (size_t)x->numel * sizeof(bf16)));
+    TRY(cast_f32_bf16(x->f32, x->b16, x->numel, 0));
+  }
+  if (t) *t = x;
+  return 0;
+}
+
+static const float* W32(sam2b_engine* e, const std::string& n) { return e->w.at(n).f32; }
+static const bf16* W16(sam2b_engine* e, const std::string& n) { return e->w.at(n).b16; }
+
+static int finalize(sam2b_engine* e) {
+  CUDA_OK(cudaSetDevice(e->device));
+  const std::string t = "image_encoder.trunk.";
+  for (size_t i = 0; i < e->blocks.size(); ++i) {
+    const std::string b = t + "blocks." + std::to_string(i) + ".";
+    for (const char* ln : {"norm1.", "norm2."}) {
+      TRY(need(e, b + ln + "weight", nullptr, false));
+      TRY(need(e, b + ln + "bias", nullptr, false));
+    }
+    for (const char* lin : {"attn.qkv.", "attn.proj.", "mlp.layers.0.", "mlp.layers.1."}) {
+      TRY(need(e, b + lin + "weight", nullptr, true));
+      TRY(need(e, b + lin + "bias", nullptr, false));
+    }
+    if (e->blocks[i].dim != e->blocks[i].dim_out) {
+      TRY(need(e, b + "proj.weight", nullptr, true));
+      TRY(need(e, b + "proj.bias", nullptr, false));
+    }
+  }
+  TRY(need(e, "derived.patch_embed.weight", nullptr, true));   // [144,160] (147 taps zero padded)
+  TRY(need(e, t + "patch_embed.proj.bias", nullptr, false));
+  TRY(need(e, "derived.pos_embed", nullptr, false));           // [256*256,144] NHWC
+  TRY(need(e, "derived.neck.lat3.weight", nullptr, true));     // [256,1152]
+  TRY(need(e, "derived.neck.lat3.bias", nullptr, false));
+  TRY(need(e, "derived.neck.lat2.weight", nullptr, true));     // [256,576]
+  TRY(need(e, "derived.neck.lat2.bias", nullptr, false));
+  TRY(need(e, "derived.neck.lat2.bias_nomem", nullptr, false));
+  TRY(need(e, "derived.neck.s1.weight", nullptr, true));       // conv_s1 o lateral: [64,288]
+  TRY(need(e, "derived.neck.s1.bias", nullptr, false));
+  TRY(need(e, "derived.neck.s0.weight", nullptr, true));       // conv_s0 o lateral: [32,144]
+  TRY(need(e, "derived.neck.s0.bias", nullptr, false));
+  CUDA_OK(cudaStreamSynchronize(0));
+  e->finalized = true;
+  return 0;
+}
+
+// One micro-batch (n images resident on the device) through trunk + neck.
+static int image_encode_mb(sam2b_engine* e, const float* img, int n, int normalised, int add_no_mem, float* fpn0,
+                           float* fpn1, float* fpn2, cudaStream_t st) {
+  const long T0 = 65536L * n;
+  float *X, *X2, *SC, *LAT3;
+  bf16 *XN, *QKV, *ATT, *HID, *COLS, *TAP[4];
+  TRY(ws_get_t(e, "x", (size_t)T0 * 144, &X));
+  TRY(ws_get_t(e, "x2", (size_t)T0 * 144, &X2));
+  TRY(ws_get_t(e, "sc", (size_t)T0 * 288, &SC));
+  TRY(ws_get_t(e, "xn", (size_t)T0 * 144, &XN));
+  TRY(ws_get_t(e, "qkv", (size_t)T0 * 864, &QKV));
+  TRY(ws_get_t(e, "att", (size_t)T0 * 144, &ATT));
+  TRY(ws_get_t(e, "hid", (size_t)T0 * 576, &HID));
+  TRY(ws_get_t(e, "cols", (size_t)T0 * 160, &COLS));
+  TRY(ws_get_t(e, "tap0", (size_t)T0 * 144, &TAP[0]));
+  TRY(ws_get_t(e, "tap1", (size_t)T0 / 4 * 288, &TAP[1]));
+  TRY(ws_get_t(e, "tap2", (size_t)T0 / 16 * 576, &TAP[2]));
+  TRY(ws_get_t(e, "tap3", (size_t)T0 / 64 * 1152, &TAP[3]));
+  TRY(ws_get_t(e, "lat3", (size_t)n * 256 * 1024, &LAT3));
+
+  const std::string t = "image_encoder.trunk.";
+  // ---- patch embed (im2col + GEMM) with the constant position embedding added in the epilogue ----
+  TRY(patch_im2col(img, COLS, n, 1024, normalised ? 0 : 1, st));
+  {
+    GemmArgs g;
+    g.A = COLS; g.lda = 160; g.M = (int)T0; g.K = 160;
+    g.B = W16(e, "derived.patch_embed.weight"); g.ldb = 160; g.N = 144;
+    g.bias = W32(e, t + "patch_embed.proj.bias");
+    g.residual = W32(e, "derived.pos_embed"); g.ld_res = 144; g.res_row_mod = 65536;
+    g.out_f32 = X; g.ldc = 144;
+    TRY(gemm_bf16(g, st));
+  }
+  int H = 256, tap = 0;
+  for (size_t i = 0; i < e->blocks.size(); ++i) {
+    const BlockCfg& c = e->blocks[i];
+    const std::string b = t + "blocks." + std::to_string(i) + ".";
+    const long T = (long)n * H * H;
+    TRY(layernorm_rows(X, W32(e, b + "norm1.weight"), W32(e, b + "norm1.bias"), 1e-6f, XN, nullptr, T, c.dim, st));
+    float* shortcut = X;
+    const bool trans = c.dim != c.dim_out;
+    if (trans) {
+      GemmArgs g;
+      g.A = XN; g.lda = c.dim; g.M = (int)T; g.K = c.dim;
+      g.B = W16(e, b + "proj.weight"); g.ldb = c.dim; g.N = c.dim_out;
+      g.bias = W32(e, b + "proj.bias");
+      g.out_f32 = SC; g.ldc = c.dim_out;
+      TRY(gemm_bf16(g, st));
+      TRY(maxpool2x2_nhwc(SC, X2, n, H, H, c.dim_out, st));
+      shortcut = X2;
+    }
+    {
+      GemmArgs g;
+      g.A = XN; g.lda = c.dim; g.M = (int)T; g.K = c.dim;
+      g.B = W16(e, b + "attn.qkv.weight"); g.ldb = c.dim; g.N = 3 * c.dim_out;
+      g.bias = W32(e, b + "attn.qkv.bias");
+      g.out_bf16 = QKV; g.ldc = 3 * c.dim_out;
+      TRY(gemm_bf16(g, st));
+    }
+    TRY(window_attention_hd72(QKV, ATT, n, H, H, c.heads, c.window ? c.window : H, c.q_pool, st));
+    if (c.q_pool) H /= 2;
+    const long Tq = (long)n * H * H;
+    {
+      GemmArgs g;
+      g.A = ATT; g.lda = c.dim_out; g.M = (int)Tq; g.K = c.dim_out;
+      g.B = W16(e, b + "attn.proj.weight"); g.ldb = c.dim_out; g.N = c.dim_out;
+      g.bias = W32(e, b + "attn.proj.bias");
+      g.residual = shortcut; g.ld_res = c.dim_out;
+      g.out_f32 = shortcut; g.ldc = c.dim_out;
+      TRY(gemm_bf16(g, st));
+    }
+    if (trans) { float* tmp = X; X = X2; X2 = tmp; }
+    TRY(layernorm_rows(X, W32(e, b + "norm2.weight"), W32(e, b + "norm2.bias"), 1e-6f, XN, nullptr, Tq, c.dim_out, st));
+    {
+      GemmArgs g;
+      g.A = XN; g.lda = c.dim_out; g.M = (int)Tq; g.K = c.dim_out;
+      g.B = W16(e, b + "mlp.layers.0.weight"); g.ldb = c.dim_out; g.N = 4 * c.dim_out;
+      g.bias = W32(e, b + "mlp.layers.0.bias"); g.act = ACT_GELU;
+      g.out_bf16 = HID; g.ldc = 4 * c.dim_out;
+      TRY(gemm_bf16(g, st));
+    }
+    {
+      GemmArgs g;
+      g.A = HID; g.lda = 4 * c.dim_out; g.M = (int)Tq; g.K = 4 * c.dim_out;
+      g.B = W16(e, b + "mlp.layers.1.weight"); g.ldb = 4 * c.dim_out; g.N = c.dim_out;
+      g.bias = W32(e, b + "mlp.layers.1.bias");
+      g.residual = X; g.ld_res = c.dim_out;
+      g.out_f32 = X; g.ldc = c.dim_out;
+      TRY(gemm_bf16(g, st));
+    }
+    if (i == 1 || i == 7 || i == 43 || i == 47) {
+      TRY(cast_f32_bf16(X, TAP[tap], Tq * c.dim_out, st));
+      ++tap;
+    }
+  }
+  // ---- FpnNeck (+ conv_s0 / conv_s1 folded into the level-0/1 laterals): out[b][co][hw] = W[co][:] . x[b][hw][:] ----
+  struct NeckJob { const char* w; const char* bias; const bf16* x; int cin, cout, hw; float* out; };
+  const NeckJob jobs[4] = {
+      {"derived.neck.lat3.weight", "derived.neck.lat3.bias", TAP[3], 1152, 256, 1024, LAT3},
+      {"derived.neck.lat2.weight", add_no_mem ? "derived.neck.lat2.bias_nomem" : "derived.neck.lat2.bias", TAP[2], 576, 256, 4096, fpn2},
+      {"derived.neck.s1.weight", "derived.neck.s1.bias", TAP[1], 288, 64, 16384, fpn1},
+      {"derived.neck.s0.weight", "derived.neck.s0.bias", TAP[0], 144, 32, 65536, fpn0},
+  };
+  for (const NeckJob& j : jobs) {
+    GemmArgs g;
+    g.A = W16(e, j.w); g.lda = j.cin; g.M = j.cout; g.K = j.cin;   // weights shared by the batch
+    g.B = j.x; g.ldb = j.cin; g.N = j.hw; g.b_batch_stride = (long)j.hw * j.cin;
+    g.batch = n;
+    g.bias = W32(e, j.bias); g.bias_along_m = 1;
+    g.out_f32 = j.out; g.ldc = j.hw; g.c_batch_stride = (long)j.cout * j.hw;
+    TRY(gemm_bf16(g, st));
+  }
+  TRY(upsample2x_add_nchw(fpn2, LAT3, n, 256, 64, 64, st));
+  return 0;
+}
+
+static const int kMaxMicroBatch = 16;
+
+}  // namespace sam2b
+
+// ============================================================================================
+// C ABI
+// ============================================================================================
+extern "C" {
+
+const char* sam2b_last_error(void) { return get_error(); }
+const char* sam2b_version(void) { return "sam2b 0.1 (sm_100a)"; }
+unsigned long long sam2b_launch_count(void) { return g_launch_count; }
+
+int sam2b_create(int device, sam2b_handle* out) {
+  if (!out) { set_error("sam2b_create: null out"); return 1; }
+  int count = 0;
+  if (cudaGetDeviceCount(&count) != cudaSuccess || count <= 0) {
+    set_error("sam2b_create: no CUDA device available (this library has no CPU path)");
+    return 1;
+  }
+  if (device < 0 || device >= count) { set_error("sam2b_create: device %d out of range (%d devices)", device, count); return 1; }
+  cudaDeviceProp prop;
+  CUDA_OK(cudaGetDeviceProperties(&prop, device));
+  if (prop.major != 10) { set_error("sam2b_create: device %d is sm_%d%d; this library is built for sm_100a only", device, prop.major, prop.minor); return 1; }
+  CUDA_OK(cudaSetDevice(device));
+  sam2b_engine* e = new sam2b_engine();
+  e->device = device;
+  build_block_cfgs(e->blocks);
+  CUDA_OK(cudaStreamCreateWithFlags(&e->copy_stream, cudaStreamNonBlocking));
+  for (auto& ev : e->ev) CUDA_OK(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
+  *out = e;
+  return 0;
+}
+
+int sam2b_destroy(sam2b_handle h) {
+  if (!h) return 0;
+  cudaSetDevice(h->device);
+  cudaDeviceSynchronize();
+  for (auto& kv : h->w) { if (kv.second.f32) cudaFree(kv.second.f32); if (kv.second.b16) cudaFree(kv.second.b16); }
+  for (auto& kv : h->ws) if (kv.second.p) cudaFree(kv.second.p);
+  for (auto& ev : h->ev) if (ev) cudaEventDestroy(ev);
+  if (h->copy_stream) cudaStreamDestroy(h->copy_stream);
+  delete h;
+  return 0;
+}
+
+int sam2b_set_tensor(sam2b_handle h, const char* name, const float* dev_data, const int64_t* shape, int ndim) {
+  if (!h || !name || !dev_data) { set_error("sam2b_set_tensor: null argument"); return 1; }
+  CUDA_OK(cudaSetDevice(h->device));
+  Tensor& t = h->w[name];
+  int64_t numel = 1;
+  std::vector<int64_t> shp;
+  for (int i = 0; i < ndim; ++i) { numel *= shape[i]; shp.push_back(shape[i]); }
+  if (t.f32 && t.numel != numel) { cudaFree(t.f32); t.f32 = nullptr; }
+  if (t.b16) { cudaFree(t.b16); t.b16 = nullptr; }
+  // round the allocation up so vectorised (16 B) reads of the tail stay in bounds
+  if (!t.f32) CUDA_OK(cudaMalloc(&t.f32, ((size_t)numel * 4 + 63) & ~(size_t)63));
+  CUDA_OK(cudaMemcpy(t.f32, dev_data, (size_t)numel * 4, cudaMemcpyDeviceToDevice));
+  t.numel = numel; t.shape = shp;
+  h->finalized = false;
+  return 0;
+}
+
+int sam2b_finalize(sam2b_handle h) {
+  if (!h) { set_error("sam2b_finalize: null handle"); return 1; }
+  return finalize(h);
+}
+
+int sam2b_image_encode(sam2b_handle h, const float* img, int n, int normalised, int add_no_mem_embed, float* fpn0,
+                       float* fpn1, float* fpn2, void* stream) {
+  if (!h || !h->finalized) { set_error("sam2b_image_encode: engine not finalized"); return 1; }
+  if (n <= 0 || !img || !fpn0 || !fpn1 || !fpn2) { set_error("sam2b_image_encode: bad arguments (n=%d)", n); return 1; }
+  CUDA_OK(cudaSetDevice(h->device));
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  for (int i0 = 0; i0 < n; i0 += kMaxMicroBatch) {
+    const int mb = (n - i0) < kMaxMicroBatch ? (n - i0) : kMaxMicroBatch;
+    TRY(image_encode_mb(h, img + (size_t)i0 * 3 * 1024 * 1024, mb, normalised, add_no_mem_embed,
+                        fpn0 + (size_t)i0 * 32 * 65536, fpn1 + (size_t)i0 * 64 * 16384, fpn2 + (size_t)i0 * 256 * 4096, st));
+  }
+  return 0;
+}
+
+int sam2b_image_encode_host(sam2b_handle h, const float* img_host, int n, int normalised, int add_no_mem_embed,
+                            float* fpn0_host, float* fpn1_host, float* fpn2_host, void* stream) {
+  if (!h || !h->finalized) { set_error("sam2b_image_encode_host: engine not finalized"); return 1; }
+  if (n <= 0 || !img_host || !fpn0_host || !fpn1_host || !fpn2_host) { set_error("sam2b_image_encode_host: bad arguments"); return 1; }
+  CUDA_OK(cudaSetDevice(h->device));
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  // double-buffered staging: copies run on copy_stream, compute on `st`
+  const size_t in_sz = (size_t)3 * 1024 * 1024, o0 = (size_t)32 * 65536, o1 = (size_t)64 * 16384, o2 = (size_t)256 * 4096;
+  float *in[2], *f0[2], *f1[2], *f2[2];
+  const char* names[2][4] = {{"h_in0", "h_f00", "h_f10", "h_f20"}, {"h_in1", "h_f01", "h_f11", "h_f21"}};
+  for (int s = 0; s < 2; ++s) {
+    TRY(ws_get_t(h, names[s][0], in_sz * kMaxMicroBatch, &in[s]));
+    TRY(ws_get_t(h, names[s][1], o0 * kMaxMicroBatch, &f0[s]));
+    TRY(ws_get_t(h, names[s][2], o1 * kMaxMicroBatch, &f1[s]));
+    TRY(ws_get_t(h, names[s][3], o2 * kMaxMicroBatch, &f2[s]));
+  }
+  cudaStream_t cs = h->copy_stream;
+  // ev[0..1]: input slot s uploaded; ev[2..3]: compute on slot s done; ev[4..5]: outputs of slot s downloaded
+  CUDA_OK(cudaEventRecord(h->ev[6], st));
+  CUDA_OK(cudaStreamWaitEvent(cs, h->ev[6], 0));
+  int it = 0;
+  for (int i0 = 0; i0 < n; i0 += kMaxMicroBatch, ++it) {
+    const int s = it & 1;
+    const int mb = (n - i0) < kMaxMicroBatch ? (n - i0) : kMaxMicroBatch;
+    if (it >= 2) CUDA_OK(cudaStreamWaitEvent(cs, h->ev[2 + s], 0));       // slot's previous compute has consumed the input
+    CUDA_OK(cudaMemcpyAsync(in[s], img_host + (size_t)i0 * in_sz, in_sz * mb * 4, cudaMemcpyHostToDevice, cs));
+    CUDA_OK(cudaEventRecord(h->ev[s], cs));
+    CUDA_OK(cudaStreamWaitEvent(st, h->ev[s], 0));
+    if (it >= 2) CUDA_OK(cudaStreamWaitEvent(st, h->ev[4 + s], 0));       // slot's previous outputs have left the device
+    TRY(image_encode_mb(h, in[s], mb, normalised, add_no_mem_embed, f0[s], f1[s], f2[s], st));
+    CUDA_OK(cudaEventRecord(h->ev[2 + s], st));
+    CUDA_OK(cudaStreamWaitEvent(cs, h->ev[2 + s], 0));
+    CUDA_OK(cudaMemcpyAsync(fpn0_host + (size_t)i0 * o0, f0[s], o0 * mb * 4, cudaMemcpyDeviceToHost, cs));
+    CUDA_OK(cudaMemcpyAsync(fpn1_host + (size_t)i0 * o1, f1[s], o1 * mb * 4, cudaMemcpyDeviceToHost, cs));
+    CUDA_OK(cudaMemcpyAsync(fpn2_host + (size_t)i0 * o2, f2[s], o2 * mb * 4, cudaMemcpyDeviceToHost, cs));
+    CUDA_OK(cudaEventRecord(h->ev[4 + s], cs));
+  }
+  CUDA_OK(cudaStreamSynchronize(cs));
+  CUDA_OK(cudaStreamSynchronize(st));
+  return 0;
+}
+
+int sam2b_memory_attention(sam2b_handle h, const float* curr, const float* curr_pos, const float* memory,
+                           const float* memory_pos, int L, const float* memory_exclude, const float* memory_pos_exclude,
+                           int P, int n, float* out, void* stream) {
+  (void)h; (void)curr; (void)curr_pos; (void)memory; (void)memory_pos; (void)L; (void)memory_exclude; (void)memory_pos_exclude;
+  (void)P; (void)n; (void)out; (void)stream;
+  set_error("sam2b_memory_attention: not built yet");
+  return 1;
+}
+
+int sam2b_memory_encode(sam2b_handle h, const float* pix_feat, const float* masks, int n, float* out_x, void* stream) {
+  (void)h; (void)pix_feat; (void)masks; (void)n; (void)out_x; (void)stream;
+  set_error("sam2b_memory_encode: not built yet");
+  return 1;
+}
+
+// ---- building blocks ----
+int sam2b_op_gemm(const void* a, int64_t lda, int64_t a_bs, const void* b, int64_t ldb, int64_t b_bs, int m, int n, int k,
+                  int batch, float alpha, const float* bias, int bias_along_m, int act, const float* gamma,
+                  const float* residual, int64_t ld_res, int64_t res_bs, int res_row_mod, float* out_f32, void* out_bf16,
+                  int64_t ldc, int64_t c_bs, int force_block_n, void* stream) {
+  GemmArgs g;
+  g.A = reinterpret_cast<const bf16*>(a); g.lda = lda; g.a_batch_stride = a_bs;
+  g.B = reinterpret_cast<const bf16*>(b); g.ldb = ldb; g.b_batch_stride = b_bs;
+  g.M = m; g.N = n; g.K = k; g.batch = batch; g.alpha = alpha;
+  g.bias = bias; g.bias_along_m = bias_along_m; g.act = act; g.gamma = gamma;
+  g.residual = residual; g.ld_res = ld_res; g.res_batch_stride = res_bs; g.res_row_mod = res_row_mod;
+  g.out_f32 = out_f32; g.out_bf16 = reinterpret_cast<bf16*>(out_bf16); g.ldc = ldc; g.c_batch_stride = c_bs;
+  g.force_bn = force_block_n;
+  return gemm_bf16(g, reinterpret_cast<cudaStream_t>(stream));
+}
+int sam2b_op_layernorm(const float* x, const float* gamma, const float* beta, float eps, void* y_bf16, float* y_f32,
+                       int64_t rows, int c, void* stream) {
+  return layernorm_rows(x, gamma, beta, eps, reinterpret_cast<bf16*>(y_bf16), y_f32, rows, c, reinterpret_cast<cudaStream_t>(stream));
+}
+int sam2b_op_cast_bf16(const float* x, void* y, int64_t n, void* stream) {
+  return cast_f32_bf16(x, reinterpret_cast<bf16*>(y), n, reinterpret_cast<cudaStream_t>(stream));
+}
+int sam2b_op_maxpool2x2_nhwc(const float* x, float* y, int b, int hgt, int wid, int c, void* stream) {
+  return maxpool2x2_nhwc(x, y, b, hgt, wid, c, reinterpret_cast<cudaStream_t>(stream));
+}
+int sam2b_op_window_attention(const void* qkv, void* out, int b, int hgt, int wid, int heads, int ws, int q_pool, void* stream) {
+  return window_attention_hd72(reinterpret_cast<const bf16*>(qkv), reinterpret_cast<bf16*>(out), b, hgt, wid, heads, ws, q_pool,
+                               reinterpret_cast<cudaStream_t>(stream));
+}
+int sam2b_op_softmax_rows(const float* s, int64_t lds, void* p, int64_t ldp, int64_t rows, int cols, void* stream) {
+  return softmax_rows(s, lds, reinterpret_cast<bf16*>(p), ldp, rows, cols, reinterpret_cast<cudaStream_t>(stream));
+}
+
+}  // extern "C"

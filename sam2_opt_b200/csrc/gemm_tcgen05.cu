@@ -1,0 +1,351 @@
+// K1: persistent, warp-specialised bf16 GEMM for sm_100a.
+//   TMA (cp.async.bulk.tensor, 128B swizzle) -> shared-memory ring -> tcgen05.mma (one issuing thread,
+//   fp32 accumulators in TMEM, double-buffered) -> tcgen05.ld epilogue warps (bias / GELU / gamma /
+//   fp32 residual / bf16 or fp32 store).
+//   C[b][m][n] = epi(alpha * sum_k A[b][m][k] * B[b][n][k]);  A, B K-major (nn.Linear's [out,in] layout
+//   is exactly a K-major B operand, so weights are used as stored).
+//
+// Covers (SURVEY.md §8a') every dense contraction of the path: trunk qkv/proj/MLP linears
+// (reference hieradet.py:56-81, sam2_utils.py:131-136), patch-embed as im2col GEMM (backbones/utils.py:89-93),
+// FpnNeck 1x1 convs + conv_s0/s1 (image_encoder.py:102-134, sam2_base_official.py:571-577), and the
+// memory-attention / memory-encoder linears and score/PV products.
+#include <mutex>
+#include <unordered_map>
+
+#include "common.cuh"
+#include "ops.h"
+
+namespace sam2b {
+
+static constexpr int BM = 128;      // UMMA M (cta_group::1)
+static constexpr int BK = 64;       // 64 bf16 = 128 B = one swizzle row
+static constexpr int UMMA_K = 16;
+static constexpr int ACC_STRIDE = 256;   // TMEM columns between the two accumulator stages
+static constexpr int TMEM_COLS = 512;
+static constexpr int NUM_THREADS = 256;  // warp0 TMA, warp1 MMA, warp2 TMEM alloc, warp3 idle, warps4-7 epilogue
+static constexpr int SMEM_BUDGET = 200 * 1024;
+
+struct GemmKernelParams {
+  int M, N, K, batch;
+  int tiles_m, tiles_n, num_kb;
+  int b_batched;
+  float alpha;
+  const float* bias; int bias_along_m;
+  int act;
+  const float* gamma;
+  const float* residual; long ld_res; long res_batch_stride; int res_row_mod;
+  float* out_f32; bf16* out_bf16; long ldc; long c_batch_stride;
+};
+
+template <int BN>
+struct GemmCfg {
+  static constexpr int STAGE_A = BM * BK * 2;
+  static constexpr int STAGE_B = BN * BK * 2;
+  static constexpr int STAGE = STAGE_A + STAGE_B;
+  static constexpr int STAGES = (SMEM_BUDGET / STAGE) > 8 ? 8 : (SMEM_BUDGET / STAGE);
+  static constexpr int SMEM = STAGES * STAGE + 1024 /*align slack*/ + 256 /*barriers*/;
+};
+
+template <int BN>
+__global__ void __launch_bounds__(NUM_THREADS, 1)
+gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b,
+                         const GemmKernelParams p) {
+  using Cfg = GemmCfg<BN>;
+  constexpr int STAGES = Cfg::STAGES;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* smem_a = smem;
+  uint8_t* smem_b = smem + STAGES * Cfg::STAGE_A;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + STAGES * Cfg::STAGE);
+  uint64_t* full_bar = bars;
+  uint64_t* empty_bar = bars + STAGES;
+  uint64_t* tmem_full = bars + 2 * STAGES;
+  uint64_t* tmem_empty = bars + 2 * STAGES + 2;
+  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bars + 2 * STAGES + 4);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const int num_tiles = p.tiles_m * p.tiles_n * p.batch;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tma_a);
+    tma_prefetch_desc(&tma_b);
+  }
+  if (warp == 1 && lane == 0) {
+    for (int i = 0; i < STAGES; ++i) { mbar_init(&full_bar[i], 1); mbar_init(&empty_bar[i], 1); }
+    for (int i = 0; i < 2; ++i) { mbar_init(&tmem_full[i], 1); mbar_init(&tmem_empty[i], 4); }
+    fence_barrier_init();
+  }
+  if (warp == 2) {
+    tmem_alloc(tmem_ptr, TMEM_COLS);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_ptr;
+
+  if (warp == 0) {
+    // ===================== TMA producer =====================
+    if (lane == 0) {
+      int stage = 0; uint32_t phase = 0;
+      for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
+        const int n_blk = t % p.tiles_n;
+        const int m_blk = (t / p.tiles_n) % p.tiles_m;
+        const int b = t / (p.tiles_n * p.tiles_m);
+        for (int kb = 0; kb < p.num_kb; ++kb) {
+          mbar_wait(&empty_bar[stage], phase ^ 1);
+          mbar_arrive_expect_tx(&full_bar[stage], Cfg::STAGE);
+          tma_load_3d(smem_a + stage * Cfg::STAGE_A, &tma_a, &full_bar[stage], kb * BK, m_blk * BM, b);
+          tma_load_3d(smem_b + stage * Cfg::STAGE_B, &tma_b, &full_bar[stage], kb * BK, n_blk * BN, p.b_batched ? b : 0);
+          if (++stage == STAGES) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===================== MMA issuer (one thread) =====================
+    if (lane == 0) {
+      constexpr uint32_t idesc = make_idesc_bf16(BM, BN);
+      int stage = 0; uint32_t phase = 0;
+      int local = 0;
+      for (int t = blockIdx.x; t < num_tiles; t += gridDim.x, ++local) {
+        const int acc = local & 1;
+        const uint32_t acc_phase = (local >> 1) & 1;
+        mbar_wait(&tmem_empty[acc], acc_phase ^ 1);
+        tc_fence_after();
+        const uint32_t tmem_d = tmem_base + acc * ACC_STRIDE;
+        for (int kb = 0; kb < p.num_kb; ++kb) {
+          mbar_wait(&full_bar[stage], phase);
+          tc_fence_after();
+          const uint64_t da = make_smem_desc_sw128(smem_u32(smem_a + stage * Cfg::STAGE_A));
+          const uint64_t db = make_smem_desc_sw128(smem_u32(smem_b + stage * Cfg::STAGE_B));
+#pragma unroll
+          for (int k = 0; k < BK / UMMA_K; ++k) {
+            // advance 32 B (16 bf16) along K inside the 128 B swizzle row: +2 in the >>4 address field
+            umma_bf16(tmem_d, da + 2 * k, db + 2 * k, idesc, (kb | k) != 0);
+          }
+          umma_commit(&empty_bar[stage]);   // frees the smem slot once these MMAs have read it
+          if (++stage == STAGES) { stage = 0; phase ^= 1; }
+        }
+        umma_commit(&tmem_full[acc]);       // accumulator complete -> epilogue
+      }
+    }
+  } else if (warp >= 4) {
+    // ===================== epilogue: TMEM -> registers -> global =====================
+    const int ew = warp & 3;                 // TMEM lane quarter this warp may read
+    int local = 0;
+    for (int t = blockIdx.x; t < num_tiles; t += gridDim.x, ++local) {
+      const int n_blk = t % p.tiles_n;
+      const int m_blk = (t / p.tiles_n) % p.tiles_m;
+      const int b = t / (p.tiles_n * p.tiles_m);
+      const int acc = local & 1;
+      const uint32_t acc_phase = (local >> 1) & 1;
+      mbar_wait(&tmem_full[acc], acc_phase);
+      tc_fence_after();
+      const int row = m_blk * BM + ew * 32 + lane;
+      const bool row_ok = row < p.M;
+      const uint32_t taddr = tmem_base + acc * ACC_STRIDE + ((uint32_t)(ew * 32) << 16);
+      float* o32 = p.out_f32 ? p.out_f32 + (long)b * p.c_batch_stride + (long)row * p.ldc : nullptr;
+      bf16* o16 = p.out_bf16 ? p.out_bf16 + (long)b * p.c_batch_stride + (long)row * p.ldc : nullptr;
+      const float* res = nullptr;
+      if (p.residual) {
+        const int rr = p.res_row_mod ? (row % p.res_row_mod) : row;
+        res = p.residual + (long)b * p.res_batch_stride + (long)rr * p.ld_res;
+      }
+      const float bias_m = (p.bias && p.bias_along_m && row_ok) ? __ldg(p.bias + row) : 0.f;
+#pragma unroll 1
+      for (int c0 = 0; c0 < BN; c0 += 32) {
+        uint32_t r[32];
+        const int width = (BN - c0) >= 32 ? 32 : 16;
+        if (width == 32) tmem_ld_x32(taddr + c0, r); else tmem_ld_x16(taddr + c0, r);
+        tmem_ld_wait();
+        const int col0 = n_blk * BN + c0;
+        if (row_ok && col0 < p.N) {
+#pragma unroll
+          for (int j = 0; j < 32; j += 8) {
+            if (j < width) {
+              const int col = col0 + j;
+              if (col + 8 <= p.N) {
+                float v[8];
+#pragma unroll
+                for (int e = 0; e < 8; ++e) v[e] = __uint_as_float(r[j + e]) * p.alpha;
+                if (p.bias) {
+                  if (p.bias_along_m) {
+#pragma unroll
+                    for (int e = 0; e < 8; ++e) v[e] += bias_m;
+                  } else {
+                    const float4 b0 = __ldg(reinterpret_cast<const float4*>(p.bias + col));
+                    const float4 b1 = __ldg(reinterpret_cast<const float4*>(p.bias + col + 4));
+                    v[0] += b0.x; v[1] += b0.y; v[2] += b0.z; v[3] += b0.w;
+                    v[4] += b1.x; v[5] += b1.y; v[6] += b1.z; v[7] += b1.w;
+                  }
+                }
+                if (p.act == ACT_GELU) {
+#pragma unroll
+                  for (int e = 0; e < 8; ++e) v[e] = gelu_erf(v[e]);
+                } else if (p.act == ACT_RELU) {
+#pragma unroll
+                  for (int e = 0; e < 8; ++e) v[e] = fmaxf(v[e], 0.f);
+                }
+                if (p.gamma) {
+                  const float4 g0 = __ldg(reinterpret_cast<const float4*>(p.gamma + col));
+                  const float4 g1 = __ldg(reinterpret_cast<const float4*>(p.gamma + col + 4));
+                  v[0] *= g0.x; v[1] *= g0.y; v[2] *= g0.z; v[3] *= g0.w;
+                  v[4] *= g1.x; v[5] *= g1.y; v[6] *= g1.z; v[7] *= g1.w;
+                }
+                if (res) {
+                  const float4 r0 = *reinterpret_cast<const float4*>(res + col);
+                  const float4 r1 = *reinterpret_cast<const float4*>(res + col + 4);
+                  v[0] += r0.x; v[1] += r0.y; v[2] += r0.z; v[3] += r0.w;
+                  v[4] += r1.x; v[5] += r1.y; v[6] += r1.z; v[7] += r1.w;
+                }
+                if (o32) {
+                  *reinterpret_cast<float4*>(o32 + col) = make_float4(v[0], v[1], v[2], v[3]);
+                  *reinterpret_cast<float4*>(o32 + col + 4) = make_float4(v[4], v[5], v[6], v[7]);
+                }
+                if (o16) {
+                  uint4 pk;
+                  pk.x = pack_bf16x2(v[0], v[1]); pk.y = pack_bf16x2(v[2], v[3]);
+                  pk.z = pack_bf16x2(v[4], v[5]); pk.w = pack_bf16x2(v[6], v[7]);
+                  *reinterpret_cast<uint4*>(o16 + col) = pk;
+                }
+              } else {
+                // ragged N tail: scalar path
+                for (int e = 0; e < 8 && col + e < p.N; ++e) {
+                  float v = __uint_as_float(r[j + e]) * p.alpha;
+                  if (p.bias) v += p.bias_along_m ? bias_m : __ldg(p.bias + col + e);
+                  if (p.act == ACT_GELU) v = gelu_erf(v); else if (p.act == ACT_RELU) v = fmaxf(v, 0.f);
+                  if (p.gamma) v *= __ldg(p.gamma + col + e);
+                  if (res) v += res[col + e];
+                  if (o32) o32[col + e] = v;
+                  if (o16) o16[col + e] = __float2bfloat16(v);
+                }
+              }
+            }
+          }
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&tmem_empty[acc]);
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, TMEM_COLS);
+  }
+}
+
+// ------------------------------------------------------------------------------------------
+// host side
+// ------------------------------------------------------------------------------------------
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn get_encode_fn() {
+  static EncodeTiledFn fn = nullptr;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    void* f = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &f, cudaEnableDefault, &q) == cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiledFn>(f);
+  });
+  return fn;
+}
+
+// 3-D bf16 tensor map over [batch][rows][K] (K contiguous), box = {64, box_rows, 1}, 128B swizzle, zero OOB fill.
+static int make_tmap(CUtensorMap* m, const bf16* ptr, long rows, long K, long ld, long batch, long batch_stride,
+                     int box_rows) {
+  EncodeTiledFn enc = get_encode_fn();
+  if (!enc) { set_error("cuTensorMapEncodeTiled entry point not available"); return 1; }
+  if ((reinterpret_cast<uintptr_t>(ptr) & 15) || (ld * 2) % 16 || (batch > 1 && (batch_stride * 2) % 16)) {
+    set_error("gemm operand not 16B aligned (ptr=%p ld=%ld batch_stride=%ld)", (const void*)ptr, ld, batch_stride);
+    return 1;
+  }
+  cuuint64_t dims[3] = {(cuuint64_t)K, (cuuint64_t)rows, (cuuint64_t)(batch > 0 ? batch : 1)};
+  cuuint64_t strides[2] = {(cuuint64_t)ld * 2, (cuuint64_t)(batch > 1 ? batch_stride : ld * rows) * 2};
+  cuuint32_t box[3] = {(cuuint32_t)BK, (cuuint32_t)box_rows, 1};
+  cuuint32_t estr[3] = {1, 1, 1};
+  CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<bf16*>(ptr), dims, strides, box, estr,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    set_error("cuTensorMapEncodeTiled failed (%d) rows=%ld K=%ld ld=%ld batch=%ld bs=%ld box_rows=%d", (int)r, rows, K,
+              ld, batch, batch_stride, box_rows);
+    return 1;
+  }
+  return 0;
+}
+
+template <int BN>
+static int launch_gemm(const GemmArgs& a, cudaStream_t stream) {
+  using Cfg = GemmCfg<BN>;
+  static bool attr_set = false;
+  if (!attr_set) {
+    cudaError_t e = cudaFuncSetAttribute(gemm_bf16_tcgen05_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM);
+    if (e != cudaSuccess) { set_error("cudaFuncSetAttribute(gemm<%d>): %s", BN, cudaGetErrorString(e)); return 1; }
+    attr_set = true;
+  }
+  CUtensorMap ta, tb;
+  if (make_tmap(&ta, a.A, a.M, a.K, a.lda, a.batch, a.a_batch_stride, BM)) return 1;
+  const bool b_batched = a.batch > 1 && a.b_batch_stride != 0;
+  if (make_tmap(&tb, a.B, a.N, a.K, a.ldb, b_batched ? a.batch : 1, a.b_batch_stride, BN)) return 1;
+  GemmKernelParams p;
+  p.M = a.M; p.N = a.N; p.K = a.K; p.batch = a.batch;
+  p.tiles_m = (a.M + BM - 1) / BM; p.tiles_n = (a.N + BN - 1) / BN; p.num_kb = (a.K + BK - 1) / BK;
+  p.b_batched = b_batched ? 1 : 0;
+  p.alpha = a.alpha; p.bias = a.bias; p.bias_along_m = a.bias_along_m; p.act = a.act; p.gamma = a.gamma;
+  p.residual = a.residual; p.ld_res = a.ld_res; p.res_batch_stride = a.res_batch_stride; p.res_row_mod = a.res_row_mod;
+  p.out_f32 = a.out_f32; p.out_bf16 = a.out_bf16; p.ldc = a.ldc; p.c_batch_stride = a.c_batch_stride;
+  const long tiles = (long)p.tiles_m * p.tiles_n * p.batch;
+  const int grid = (int)(tiles < num_sms() ? tiles : num_sms());
+  gemm_bf16_tcgen05_kernel<BN><<<grid, NUM_THREADS, Cfg::SMEM, stream>>>(ta, tb, p);
+  SAM2B_CHECK_LAUNCH("gemm_bf16_tcgen05");
+  return 0;
+}
+
+static int pick_bn(const GemmArgs& a) {
+  static const int cand[] = {256, 192, 144, 128, 96, 64, 32};
+  const long tiles_m = (a.M + BM - 1) / BM;
+  double best = 1e30; int best_bn = 128;
+  for (int bn : cand) {
+    const long tiles = tiles_m * ((a.N + bn - 1) / bn) * a.batch;
+    const long waves = (tiles + num_sms() - 1) / num_sms();
+    // per-tile cost ~ MMA time (prop. to BN) + fixed per-tile overhead (epilogue drain, barriers)
+    const double cost = (double)waves * (bn + 24.0);
+    if (cost < best - 1e-9) { best = cost; best_bn = bn; }
+  }
+  return best_bn;
+}
+
+int gemm_bf16(const GemmArgs& a, cudaStream_t stream) {
+  if (a.M <= 0 || a.N <= 0 || a.K <= 0 || a.batch <= 0) { set_error("gemm: empty problem M=%d N=%d K=%d batch=%d", a.M, a.N, a.K, a.batch); return 1; }
+  if (!a.out_f32 && !a.out_bf16) { set_error("gemm: no output"); return 1; }
+  if (a.K % 8) { set_error("gemm: K=%d must be a multiple of 8", a.K); return 1; }
+  if ((a.out_f32 && (a.ldc % 4 || (reinterpret_cast<uintptr_t>(a.out_f32) & 15))) ||
+      (a.out_bf16 && (a.ldc % 8 || (reinterpret_cast<uintptr_t>(a.out_bf16) & 15))) ||
+      (a.residual && (a.ld_res % 4 || (reinterpret_cast<uintptr_t>(a.residual) & 15)))) {
+    set_error("gemm: output/residual leading dimension or pointer not vector aligned (ldc=%ld ld_res=%ld)", a.ldc, a.ld_res);
+    return 1;
+  }
+  const int bn = a.force_bn ? a.force_bn : pick_bn(a);
+  switch (bn) {
+    case 256: return launch_gemm<256>(a, stream);
+    case 192: return launch_gemm<192>(a, stream);
+    case 144: return launch_gemm<144>(a, stream);
+    case 128: return launch_gemm<128>(a, stream);
+    case 96: return launch_gemm<96>(a, stream);
+    case 64: return launch_gemm<64>(a, stream);
+    case 32: return launch_gemm<32>(a, stream);
+  }
+  set_error("gemm: unsupported BLOCK_N %d", bn);
+  return 1;
+}
+
+}  // namespace sam2b

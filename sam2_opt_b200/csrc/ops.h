@@ -1,0 +1,73 @@
+// Internal C++ interface between the kernels (*.cu) and the engine (engine.cu).  Every function
+// enqueues work on `stream` and returns immediately; errors are reported through set_error().
+#pragma once
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace sam2b {
+
+typedef __nv_bfloat16 bf16;
+
+void set_error(const char* fmt, ...);
+const char* get_error();
+int num_sms();
+// counts kernel launches made by this library (bench.py's gpu_launches)
+extern unsigned long long g_launch_count;
+
+#define SAM2B_CHECK_LAUNCH(name)                                              \
+  do {                                                                        \
+    ++::sam2b::g_launch_count;                                                \
+    cudaError_t e__ = cudaGetLastError();                                     \
+    if (e__ != cudaSuccess) {                                                 \
+      ::sam2b::set_error("%s launch failed: %s", name, cudaGetErrorString(e__)); \
+      return 1;                                                               \
+    }                                                                         \
+  } while (0)
+
+enum Act { ACT_NONE = 0, ACT_GELU = 1, ACT_RELU = 2 };
+
+// C[b][m][n] = epilogue( alpha * sum_k A[b][m][k] * B[b][n][k] )      (both operands K-major, bf16)
+// epilogue(v) = (act(v + bias)) * gamma[n] + residual[b][m % res_row_mod][n]
+struct GemmArgs {
+  const bf16* A = nullptr; long lda = 0; long a_batch_stride = 0;
+  const bf16* B = nullptr; long ldb = 0; long b_batch_stride = 0;  // b_batch_stride == 0: B shared by all batches
+  int M = 0, N = 0, K = 0, batch = 1;
+  float alpha = 1.0f;
+  const float* bias = nullptr; int bias_along_m = 0;
+  int act = ACT_NONE;
+  const float* gamma = nullptr;
+  const float* residual = nullptr; long ld_res = 0; long res_batch_stride = 0; int res_row_mod = 0;
+  float* out_f32 = nullptr; bf16* out_bf16 = nullptr; long ldc = 0; long c_batch_stride = 0;
+  int force_bn = 0;  // 0 = pick automatically
+};
+int gemm_bf16(const GemmArgs& a, cudaStream_t stream);
+
+// rows x C fp32 -> bf16 (LayerNorm with affine, or plain cast when gamma == nullptr)
+int layernorm_rows(const float* x, const float* gamma, const float* beta, float eps, bf16* y_bf16, float* y_f32,
+                   long rows, int C, cudaStream_t stream);
+int cast_f32_bf16(const float* x, bf16* y, long n, cudaStream_t stream);
+// 2x2 max-pool over NHWC fp32: [B,H,W,C] -> [B,H/2,W/2,C]
+int maxpool2x2_nhwc(const float* x, float* y, int B, int H, int W, int C, cudaStream_t stream);
+// im2col for the 7x7 stride-4 pad-3 patch embedding: img [B,3,S,S] fp32 (optionally (x-mean)/std first)
+// -> cols [B*(S/4)^2, 160] bf16 (147 taps in (c,ky,kx) order, zero padded to 160)
+int patch_im2col(const float* img, bf16* cols, int B, int S, int normalise, cudaStream_t stream);
+// dst[b,c,y,x] += src[b,c,y/2,x/2]   (nearest x2 top-down add of the FPN), NCHW fp32
+int upsample2x_add_nchw(float* dst, const float* src, int B, int C, int H, int W, cudaStream_t stream);
+
+// Hiera window attention on a packed qkv tensor [B, H, W, 3, heads, 72] bf16 (token-major).
+// ws = window side (ws == H: global).  q_pool: queries are the 2x2 max of q inside the window and the
+// output lives on the (H/2, W/2) grid.  out: [B, Ho, Wo, heads*72] bf16.
+int window_attention_hd72(const bf16* qkv, bf16* out, int B, int H, int W, int heads, int ws, int q_pool,
+                          cudaStream_t stream);
+
+// Row softmax over fp32 scores -> bf16 probabilities (row stride lds / ldp elements), `cols` valid columns;
+// columns in [cols, ldp) are written as zero.
+int softmax_rows(const float* s, long lds, bf16* p, long ldp, long rows, int cols, cudaStream_t stream);
+
+// Axial RoPE (interleaved pairs) applied in place on x [rows, 256] fp32->bf16 conversion included:
+// y_bf16[r] = rope(x[r]) with table row (r % 4096) when r < rope_rows, else plain cast.
+int rope_cast_rows(const float* x, const float* cos_t, const float* sin_t, bf16* y, long rows, long rope_rows,
+                   cudaStream_t stream);
+
+}  // namespace sam2b

@@ -1,0 +1,87 @@
+"""torch-tensor front ends of the library's building-block entry points (``sam2b_op_*``): used by the parity tests
+and by callers that want a single kernel.  Every function enqueues on the current stream of the tensors' device."""
+import ctypes as C
+from typing import Optional
+
+import torch
+
+from . import _lib
+from .engine import _ptr, _stream
+
+ACT = {None: 0, "none": 0, "gelu": 1, "relu": 2}
+
+
+def gemm(a: torch.Tensor, b: torch.Tensor, bias: Optional[torch.Tensor] = None, act=None, alpha: float = 1.0,
+         gamma: Optional[torch.Tensor] = None, residual: Optional[torch.Tensor] = None, res_row_mod: int = 0,
+         out_dtype=torch.float32, bias_along_m: bool = False, block_n: int = 0) -> torch.Tensor:
+    """out[b] = act(alpha * a[b] @ b[b]^T + bias) * gamma + residual.   a: [M,K] or [B,M,K] bf16; b: [N,K] or [B,N,K]."""
+    lib = _lib.load()
+    assert a.dtype == torch.bfloat16 and b.dtype == torch.bfloat16 and a.is_cuda
+    a3 = a if a.dim() == 3 else a[None]
+    b3 = b if b.dim() == 3 else b[None]
+    assert a3.stride(2) == 1 and b3.stride(2) == 1
+    batch, M, K = a3.shape
+    N = b3.shape[1]
+    out = torch.empty((batch, M, N), device=a.device, dtype=out_dtype)
+    res3 = None
+    if residual is not None:
+        res3 = residual if residual.dim() == 3 else residual[None]
+        assert res3.dtype == torch.float32 and res3.stride(2) == 1
+    _lib.check(lib.sam2b_op_gemm(
+        _ptr(a3), a3.stride(1), a3.stride(0) if batch > 1 else 0,
+        _ptr(b3), b3.stride(1), b3.stride(0) if b3.shape[0] > 1 else 0,
+        M, N, K, batch, float(alpha), _ptr(bias), int(bias_along_m), ACT[act], _ptr(gamma),
+        _ptr(res3), 0 if res3 is None else res3.stride(1),
+        0 if res3 is None or res3.shape[0] == 1 else res3.stride(0), int(res_row_mod),
+        _ptr(out if out_dtype == torch.float32 else None), _ptr(out if out_dtype == torch.bfloat16 else None),
+        N, M * N, int(block_n), _stream()), "op_gemm")
+    return out if a.dim() == 3 else out[0]
+
+
+def layernorm(x: torch.Tensor, gamma: torch.Tensor, beta: torch.Tensor, eps: float, out_dtype=torch.bfloat16):
+    lib = _lib.load()
+    x = x.contiguous()
+    Cdim = x.shape[-1]
+    rows = x.numel() // Cdim
+    y = torch.empty(x.shape, device=x.device, dtype=out_dtype)
+    _lib.check(lib.sam2b_op_layernorm(_ptr(x), _ptr(gamma), _ptr(beta), float(eps),
+                                      _ptr(y if out_dtype == torch.bfloat16 else None),
+                                      _ptr(y if out_dtype == torch.float32 else None), rows, Cdim, _stream()), "op_layernorm")
+    return y
+
+
+def cast_bf16(x: torch.Tensor) -> torch.Tensor:
+    lib = _lib.load()
+    x = x.contiguous()
+    y = torch.empty(x.shape, device=x.device, dtype=torch.bfloat16)
+    _lib.check(lib.sam2b_op_cast_bf16(_ptr(x), _ptr(y), x.numel(), _stream()), "op_cast_bf16")
+    return y
+
+
+def maxpool2x2_nhwc(x: torch.Tensor) -> torch.Tensor:
+    lib = _lib.load()
+    B, H, W, Cd = x.shape
+    y = torch.empty((B, H // 2, W // 2, Cd), device=x.device, dtype=torch.float32)
+    _lib.check(lib.sam2b_op_maxpool2x2_nhwc(_ptr(x.contiguous()), _ptr(y), B, H, W, Cd, _stream()), "op_maxpool")
+    return y
+
+
+def window_attention(qkv: torch.Tensor, heads: int, ws: int, q_pool: bool) -> torch.Tensor:
+    """qkv [B,H,W,3*heads*72] bf16 -> [B,Ho,Wo,heads*72] bf16  (ws == H: global attention)."""
+    lib = _lib.load()
+    B, H, W, C3 = qkv.shape
+    assert qkv.dtype == torch.bfloat16 and qkv.is_contiguous() and C3 == 3 * heads * 72
+    Ho, Wo = (H // 2, W // 2) if q_pool else (H, W)
+    out = torch.empty((B, Ho, Wo, heads * 72), device=qkv.device, dtype=torch.bfloat16)
+    _lib.check(lib.sam2b_op_window_attention(_ptr(qkv), _ptr(out), B, H, W, heads, ws, int(q_pool), _stream()),
+               "op_window_attention")
+    return out
+
+
+def softmax_rows(s: torch.Tensor, ldp: Optional[int] = None) -> torch.Tensor:
+    lib = _lib.load()
+    rows, cols = s.shape
+    ldp = ldp or ((cols + 63) // 64 * 64)
+    p = torch.empty((rows, ldp), device=s.device, dtype=torch.bfloat16)
+    _lib.check(lib.sam2b_op_softmax_rows(_ptr(s), s.stride(0), _ptr(p), ldp, rows, cols, _stream()), "op_softmax_rows")
+    return p

@@ -1,0 +1,78 @@
+"""One-time weight preparation at ``speedup()`` time: constants that the reference recomputes on every call
+(or bakes into its ONNX/TensorRT engine) are derived once here with torch and handed to the engine as
+``derived.*`` tensors.  Nothing in this file runs on the per-frame path.
+
+All ``ref:`` citations are relative to /root/reference/sam2/sam2/.
+"""
+import math
+from typing import Dict
+
+import torch
+import torch.nn.functional as F
+
+IMAGE_SIZE = 1024
+D_MODEL = 256
+MEM_DIM = 64
+
+
+def hiera_pos_embed(w: Dict[str, torch.Tensor], size: int = 256) -> torch.Tensor:
+    """ref: modeling/backbones/hieradet.py:273-281 (bicubic background + tiled window embedding) -> [size*size, C]"""
+    t = "image_encoder.trunk."
+    pe = F.interpolate(w[t + "pos_embed"].float(), size=(size, size), mode="bicubic")
+    win = w[t + "pos_embed_window"].float()
+    pe = pe + win.tile([x // y for x, y in zip(pe.shape, win.shape)])
+    return pe.permute(0, 2, 3, 1).reshape(size * size, -1).contiguous()
+
+
+def position_sine(num_pos_feats: int, H: int, Wd: int, device, temperature: float = 10000.0) -> torch.Tensor:
+    """ref: modeling/position_encoding.py:90-124 (PositionEmbeddingSine, normalize=True, scale=2*pi) -> [C,H,W].
+    The reference materialises this with .repeat(B,...) on every call; we keep one constant and expand views."""
+    npf = num_pos_feats // 2
+    y = torch.arange(1, H + 1, dtype=torch.float32, device=device).view(-1, 1).repeat(1, Wd)
+    x = torch.arange(1, Wd + 1, dtype=torch.float32, device=device).view(1, -1).repeat(H, 1)
+    eps, scale = 1e-6, 2 * math.pi
+    y = y / (y[-1:, :] + eps) * scale
+    x = x / (x[:, -1:] + eps) * scale
+    dim_t = torch.arange(npf, dtype=torch.float32, device=device)
+    dim_t = temperature ** (2 * torch.div(dim_t, 2, rounding_mode="floor") / npf)
+    px, py = x[:, :, None] / dim_t, y[:, :, None] / dim_t
+    px = torch.stack((px[:, :, 0::2].sin(), px[:, :, 1::2].cos()), dim=3).flatten(2)
+    py = torch.stack((py[:, :, 0::2].sin(), py[:, :, 1::2].cos()), dim=3).flatten(2)
+    return torch.cat((py, px), dim=2).permute(2, 0, 1).contiguous()
+
+
+def rope_tables(device, dim: int = 256, end: int = 64, theta: float = 10000.0):
+    """ref: modeling/position_encoding_fix.py:166-183 -> (cos, sin) [end*end, dim/2]: angle of pair i at position r
+    (pairs i < dim/4 rotate with x, the rest with y)."""
+    freqs = 1.0 / (theta ** (torch.arange(0, dim, 4, device=device)[: dim // 4].float() / dim))
+    t = torch.arange(end * end, dtype=torch.float32, device=device)
+    tx, ty = (t % end).float(), torch.div(t, end, rounding_mode="floor").float()
+    ang = torch.cat([torch.outer(tx, freqs), torch.outer(ty, freqs)], dim=-1)     # [4096, dim/2]
+    return ang.cos().contiguous(), ang.sin().contiguous()
+
+
+def derive(w: Dict[str, torch.Tensor]) -> Dict[str, torch.Tensor]:
+    """Derived constants for the engine (all fp32, same device as the weights)."""
+    d = {}
+    dev = w["image_encoder.trunk.pos_embed"].device
+    pw = w["image_encoder.trunk.patch_embed.proj.weight"].float().reshape(144, 147)
+    d["derived.patch_embed.weight"] = F.pad(pw, (0, 13)).contiguous()            # K 147 -> 160
+    d["derived.pos_embed"] = hiera_pos_embed(w)
+    # FpnNeck laterals: level i uses convs[3 - i]  (ref: modeling/backbones/image_encoder.py:112-114)
+    nk = "image_encoder.neck.convs.{}.conv."
+    lat = {i: (w[nk.format(3 - i) + "weight"].double().flatten(1), w[nk.format(3 - i) + "bias"].double()) for i in range(4)}
+    d["derived.neck.lat3.weight"] = lat[3][0].float().contiguous()
+    d["derived.neck.lat3.bias"] = lat[3][1].float().contiguous()
+    d["derived.neck.lat2.weight"] = lat[2][0].float().contiguous()
+    d["derived.neck.lat2.bias"] = lat[2][1].float().contiguous()
+    d["derived.neck.lat2.bias_nomem"] = (lat[2][1] + w["no_mem_embed"].double().view(-1)).float().contiguous()
+    # conv_s0 / conv_s1 (ref: sam2_base_official.py:571-577) are 1x1 convs applied right after the level-0/1 lateral
+    # 1x1 convs (no top-down term reaches those levels), so they compose exactly: W = Ws @ Wl, b = Ws @ bl + bs.
+    for lvl, name in ((1, "s1"), (0, "s0")):
+        ws_ = w[f"sam_mask_decoder.conv_{name}.weight"].double().flatten(1)
+        bs_ = w[f"sam_mask_decoder.conv_{name}.bias"].double()
+        d[f"derived.neck.{name}.weight"] = (ws_ @ lat[lvl][0]).float().contiguous()
+        d[f"derived.neck.{name}.bias"] = (ws_ @ lat[lvl][1] + bs_).float().contiguous()
+    cos, sin = rope_tables(dev)
+    d["derived.rope.cos"], d["derived.rope.sin"] = cos, sin
+    return d

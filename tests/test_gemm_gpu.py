@@ -1,0 +1,107 @@
+"""Parity of the tcgen05 GEMM (sam2b_op_gemm, through the C ABI) against a torch fp32 matmul of the same
+bf16-rounded operands.  Tolerance: fp32 accumulation-order noise only (1e-3 relative to the output scale);
+bf16 outputs add one rounding (2^-8 relative)."""
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+def _ref(a, b, bias=None, act=None, alpha=1.0, gamma=None, residual=None, bias_along_m=False):
+    o = alpha * (a.float() @ b.float().transpose(-1, -2))
+    if bias is not None:
+        o = o + (bias[:, None] if bias_along_m else bias)
+    if act == "gelu":
+        o = torch.nn.functional.gelu(o)
+    elif act == "relu":
+        o = torch.relu(o)
+    if gamma is not None:
+        o = o * gamma
+    if residual is not None:
+        o = o + residual
+    return o
+
+
+def _close(x, y, tol):
+    scale = y.abs().max().item() + 1e-6
+    err = (x.float() - y).abs().max().item()
+    assert err <= tol * scale, f"max err {err:.4g} vs scale {scale:.4g}"
+
+
+# (M, N, K): trunk linears of every stage incl. ragged K (144 = 2.25 k-blocks) and ragged N / M tails
+SHAPES = [(256, 128, 64), (128, 256, 128), (4096, 1728, 576), (4096, 576, 2304), (8192, 432, 144), (1000, 144, 144),
+          (1024, 3456, 1152), (4096, 2304, 576), (300, 72, 160), (65536, 144, 160), (16384, 864, 288)]
+
+
+@pytest.mark.parametrize("M,N,K", SHAPES)
+def test_gemm_plain(M, N, K):
+    from sam2_opt_b200 import ops
+    g = torch.Generator(device="cuda").manual_seed(M + N + K)
+    a = torch.randn(M, K, device="cuda", generator=g).bfloat16()
+    b = (torch.randn(N, K, device="cuda", generator=g) / K ** 0.5).bfloat16()
+    out = ops.gemm(a, b)
+    torch.cuda.synchronize()
+    _close(out, _ref(a, b), 2e-3)
+
+
+@pytest.mark.parametrize("bn", [32, 64, 96, 128, 144, 192, 256])
+def test_gemm_every_block_n(bn):
+    from sam2_opt_b200 import ops
+    g = torch.Generator(device="cuda").manual_seed(bn)
+    M, N, K = 640, 1008, 328
+    a = torch.randn(M, K, device="cuda", generator=g).bfloat16()
+    b = (torch.randn(N, K, device="cuda", generator=g) / K ** 0.5).bfloat16()
+    bias = torch.randn(N, device="cuda", generator=g)
+    out = ops.gemm(a, b, bias=bias, block_n=bn)
+    torch.cuda.synchronize()
+    _close(out, _ref(a, b, bias), 2e-3)
+
+
+def test_gemm_epilogues():
+    from sam2_opt_b200 import ops
+    g = torch.Generator(device="cuda").manual_seed(7)
+    M, N, K = 2048, 576, 576
+    a = torch.randn(M, K, device="cuda", generator=g).bfloat16()
+    b = (torch.randn(N, K, device="cuda", generator=g) / K ** 0.5).bfloat16()
+    bias = torch.randn(N, device="cuda", generator=g)
+    gamma = torch.rand(N, device="cuda", generator=g) + 0.5
+    res = torch.randn(M, N, device="cuda", generator=g)
+    _close(ops.gemm(a, b, bias=bias, act="gelu", out_dtype=torch.bfloat16), _ref(a, b, bias, "gelu"), 1e-2)
+    _close(ops.gemm(a, b, bias=bias, act="relu"), _ref(a, b, bias, "relu"), 2e-3)
+    _close(ops.gemm(a, b, bias=bias, residual=res), _ref(a, b, bias, residual=res), 2e-3)
+    _close(ops.gemm(a, b, bias=bias, gamma=gamma, residual=res, alpha=0.5), _ref(a, b, bias, None, 0.5, gamma, res), 2e-3)
+    # residual broadcast over row blocks (pos-embed add of the patch embedding)
+    res_small = torch.randn(256, N, device="cuda", generator=g)
+    _close(ops.gemm(a, b, residual=res_small, res_row_mod=256), _ref(a, b, residual=res_small.repeat(M // 256, 1)), 2e-3)
+    # in-place residual (what the trunk does): out aliases residual
+    bias_m = torch.randn(M, device="cuda", generator=g)
+    _close(ops.gemm(a, b, bias=bias_m, bias_along_m=True), _ref(a, b, bias_m, bias_along_m=True), 2e-3)
+    torch.cuda.synchronize()
+
+
+def test_gemm_batched_shared_a_nchw_out():
+    """FpnNeck form: weights [Cout,Cin] as A (shared), per-image tokens [hw,Cin] as B -> NCHW output."""
+    from sam2_opt_b200 import ops
+    g = torch.Generator(device="cuda").manual_seed(11)
+    n, hw, cin, cout = 3, 4096, 576, 256
+    wgt = (torch.randn(cout, cin, device="cuda", generator=g) / cin ** 0.5).bfloat16()
+    x = torch.randn(n, hw, cin, device="cuda", generator=g).bfloat16()
+    bias = torch.randn(cout, device="cuda", generator=g)
+    out = ops.gemm(wgt[None].expand(n, -1, -1), x, bias=bias, bias_along_m=True)
+    ref = torch.einsum("ok,nhk->noh", wgt.float(), x.float()) + bias[None, :, None]
+    _close(out, ref, 2e-3)
+    # small-M (32 rows, one quarter of the MMA tile)
+    w32 = (torch.randn(32, cin, device="cuda", generator=g) / cin ** 0.5).bfloat16()
+    out = ops.gemm(w32[None].expand(n, -1, -1), x)
+    _close(out, torch.einsum("ok,nhk->noh", w32.float(), x.float()), 2e-3)
+
+
+def test_gemm_many_tiles_persistent_phases():
+    """> 148*2 tiles per CTA so every barrier ring wraps several times (both accumulator stages, all phases)."""
+    from sam2_opt_b200 import ops
+    g = torch.Generator(device="cuda").manual_seed(5)
+    M, N, K = 128 * 148 * 5, 256, 1152
+    a = torch.randn(M, K, device="cuda", generator=g).bfloat16()
+    b = (torch.randn(N, K, device="cuda", generator=g) / K ** 0.5).bfloat16()
+    out = ops.gemm(a, b, block_n=64)
+    _close(out, _ref(a, b), 2e-3)

@@ -1,0 +1,79 @@
+"""Parity of the non-GEMM kernels (through the C ABI) against plain torch fp32 on the same inputs."""
+import math
+
+import pytest
+import torch
+import torch.nn.functional as F
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.mark.parametrize("C", [144, 256, 288, 576, 1152])
+def test_layernorm(C):
+    from sam2_opt_b200 import ops
+    g = torch.Generator(device="cuda").manual_seed(C)
+    x = torch.randn(1000, C, device="cuda", generator=g) * 3 + 1
+    w = torch.randn(C, device="cuda", generator=g)
+    b = torch.randn(C, device="cuda", generator=g)
+    ref = F.layer_norm(x, (C,), w, b, 1e-6)
+    y32 = ops.layernorm(x, w, b, 1e-6, out_dtype=torch.float32)
+    assert (y32 - ref).abs().max().item() < 2e-5 * ref.abs().max().item()
+    y16 = ops.layernorm(x, w, b, 1e-6)
+    assert (y16.float() - ref).abs().max().item() <= 2 ** -8 * ref.abs().max().item()
+
+
+def test_cast_and_maxpool():
+    from sam2_opt_b200 import ops
+    x = torch.randn(2, 64, 64, 288, device="cuda")
+    assert torch.equal(ops.cast_bf16(x), x.bfloat16())
+    ref = F.max_pool2d(x.permute(0, 3, 1, 2), 2, 2).permute(0, 2, 3, 1)
+    assert torch.equal(ops.maxpool2x2_nhwc(x), ref)
+
+
+def _attn_ref(qkv, heads, ws, q_pool):
+    """Reference semantics (hieradet.py:56-81 + window partition) in fp32 on bf16-rounded q/k/v."""
+    B, H, W, _ = qkv.shape
+    C = heads * 72
+    x = qkv.float().view(B, H // ws, ws, W // ws, ws, 3, heads, 72).permute(0, 1, 3, 2, 4, 5, 6, 7)
+    x = x.reshape(-1, ws, ws, 3, heads, 72)
+    q, k, v = x[:, :, :, 0], x[:, :, :, 1], x[:, :, :, 2]
+    Bw = q.shape[0]
+    wq = ws
+    if q_pool:
+        q = F.max_pool2d(q.reshape(Bw, ws, ws, C).permute(0, 3, 1, 2), 2, 2).permute(0, 2, 3, 1)
+        wq = ws // 2
+        q = q.reshape(Bw, wq, wq, heads, 72)
+    q = q.reshape(Bw, wq * wq, heads, 72).transpose(1, 2)
+    k = k.reshape(Bw, ws * ws, heads, 72).transpose(1, 2)
+    v = v.reshape(Bw, ws * ws, heads, 72).transpose(1, 2)
+    o = F.scaled_dot_product_attention(q, k, v).transpose(1, 2).reshape(Bw, wq, wq, C)
+    Ho, Wo = (H // 2, W // 2) if q_pool else (H, W)
+    o = o.reshape(B, H // ws, W // ws, wq, wq, C).permute(0, 1, 3, 2, 4, 5).reshape(B, Ho, Wo, C)
+    return o
+
+
+# (H, heads, ws, q_pool): every window configuration of Hiera-L (scaled-down grids keep the test fast)
+ATTN = [(64, 2, 8, False), (64, 4, 8, True), (32, 4, 4, False), (32, 8, 4, True), (32, 8, 16, False),
+        (64, 8, 64, False), (32, 16, 16, True), (32, 16, 8, False)]
+
+
+@pytest.mark.parametrize("H,heads,ws,q_pool", ATTN)
+def test_window_attention(H, heads, ws, q_pool):
+    from sam2_opt_b200 import ops
+    g = torch.Generator(device="cuda").manual_seed(H * 31 + heads * 7 + ws)
+    B = 2
+    qkv = (torch.randn(B, H, H, 3 * heads * 72, device="cuda", generator=g) * 1.5).bfloat16()
+    out = ops.window_attention(qkv, heads, ws, q_pool)
+    torch.cuda.synchronize()
+    ref = _attn_ref(qkv, heads, ws, q_pool)
+    err = (out.float() - ref).abs().max().item()
+    assert err < 2e-2 * ref.abs().max().item(), err     # P is rounded to bf16 before PV (2^-8) + bf16 output
+
+
+def test_softmax_rows():
+    from sam2_opt_b200 import ops
+    s = torch.randn(64, 28736 + 4, device="cuda") * 4
+    p = ops.softmax_rows(s)
+    ref = torch.softmax(s, -1)
+    assert p.shape[1] % 64 == 0 and (p[:, s.shape[1]:] == 0).all()
+    assert (p[:, :s.shape[1]].float() - ref).abs().max().item() <= 2 ** -8 * ref.max().item()
