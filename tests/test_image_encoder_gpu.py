@@ -1,0 +1,83 @@
+"""GPU parity of the image-encoder sub-graph (boundaries E1 / E2) through the C ABI against
+(a) the committed golden fixtures produced by the unmodified reference and (b) the fp32 oracle run on the host CPU.
+Tolerance (BASELINE.json north_star): relative error <= 2e-2 for embeddings and high-res features."""
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+TOL = 2e-2
+
+
+def rel_l2(a, b):
+    a, b = torch.as_tensor(a).double().cpu(), torch.as_tensor(b).double().cpu()
+    return ((a - b).norm() / b.norm()).item()
+
+
+@pytest.fixture(scope="module")
+def weights():
+    from oracle import sam2_oracle as O
+    return O.make_weights(0)
+
+
+@pytest.fixture(scope="module")
+def engine(weights):
+    from sam2_opt_b200.engine import Engine
+    e = Engine(weights)
+    yield e
+    e.release()
+
+
+def _sl16(a):
+    s = a.shape[-1] // 16
+    return a[0, :16, ::s, ::s]
+
+
+def test_e2_forward_image_vs_reference_golden(engine, golden):
+    from oracle.synth import synth_image_norm
+    img = synth_image_norm(1, 1).cuda()
+    f0, f1, f2 = engine.image_encode(img, normalised=True, add_no_mem_embed=False)
+    torch.cuda.synchronize()
+    for name, got, key in (("fpn0", f0, "e2_out4"), ("fpn1", f1, "e2_out5"), ("fpn2", f2, "e2_out6")):
+        r = rel_l2(_sl16(got), golden[key])
+        print(f"E2 {name}: rel-L2 vs reference golden slice = {r:.4%}")
+        assert r <= TOL, (name, r)
+        ref_norm = golden[key + "_stats"][3]
+        assert abs(got.double().norm().item() - ref_norm) <= TOL * ref_norm
+
+
+def test_e1_set_image_vs_reference_golden(engine, golden):
+    from oracle.synth import synth_image_u8
+    img = (torch.as_tensor(synth_image_u8(0)).permute(2, 0, 1)[None].float() / 255.0).cuda()
+    outs = engine.image_encode(img, normalised=False, add_no_mem_embed=True)
+    torch.cuda.synchronize()
+    for i, got in enumerate(outs):
+        r = rel_l2(_sl16(got), golden[f"e1_out{i}"])
+        print(f"E1 feat{i}: rel-L2 vs reference golden slice = {r:.4%}")
+        assert r <= TOL, (i, r)
+
+
+def test_e2_full_tensors_vs_oracle_and_batch_invariance(engine, weights):
+    """Whole-tensor comparison against the CPU oracle on a fresh seed, inside a batch of 3 (different images), plus:
+    each image's result must not depend on its batch neighbours."""
+    from oracle import sam2_oracle as O
+    from oracle.synth import synth_image_norm
+    imgs = synth_image_norm(3, seed=5)
+    with torch.no_grad():
+        ref = O.forward_image(weights, imgs[1:2])
+    f0, f1, f2 = engine.image_encode(imgs.cuda(), normalised=True, add_no_mem_embed=False)
+    s0, s1, s2 = engine.image_encode(imgs[1:2].cuda(), normalised=True, add_no_mem_embed=False)
+    torch.cuda.synchronize()
+    for name, got, single, want in (("fpn0", f0, s0, ref[4]), ("fpn1", f1, s1, ref[5]), ("fpn2", f2, s2, ref[6])):
+        r = rel_l2(got[1:2], want)
+        mx = (got[1:2].cpu() - want).abs().max().item()
+        print(f"E2 {name}: rel-L2 vs oracle = {r:.4%}, max-abs = {mx:.4g}")
+        assert r <= TOL, (name, r)
+        assert rel_l2(got[1:2], single) < 1e-3
+
+
+def test_rejects_bad_inputs(engine):
+    with pytest.raises(ValueError):
+        engine.image_encode(torch.zeros(1, 3, 512, 512, device="cuda"), True, False)
+    with pytest.raises(RuntimeError, match="CUDA tensor"):
+        engine.image_encode(torch.zeros(1, 3, 1024, 1024), True, False)
