@@ -65,6 +65,12 @@ int sam2b_memory_attention(sam2b_handle h, const float* curr, const float* curr_
  * (the second reference output, the sine position encoding, is a constant: sam2b_position_encoding) */
 int sam2b_memory_encode(sam2b_handle h, const float* pix_feat, const float* masks, int n, float* out_x, void* stream);
 
+/* ---- per-launch profiling (CUDA event pair around every kernel this library launches, on the launching stream) ----
+ * begin: clear + enable.  end: disable, synchronise the device and write a CSV "name,ms,flops,bytes" (one line per
+ * launch; flops/bytes are the ALGORITHMIC work of that launch) into buf; *needed receives the full length. */
+int sam2b_profile_begin(void);
+int sam2b_profile_end(char* buf, int64_t buflen, int64_t* needed);
+
 /* ---- building blocks (used by the parity tests and available to other callers) ---- */
 /* C[b][m][n] = act(alpha * A[b] B[b]^T + bias) * gamma + residual ; A [batch,M,K], B [batch or 1,N,K] bf16 K-major.
  * act: 0 none, 1 exact GELU, 2 ReLU.  Exactly one of out_f32 / out_bf16 may be NULL. */

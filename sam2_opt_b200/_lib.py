@@ -21,6 +21,8 @@ SIGNATURES = {
     "sam2b_image_encode_host": (_i, [_vp, _vp, _i, _i, _i, _vp, _vp, _vp, _vp]),
     "sam2b_memory_attention": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _vp, _vp, _i, _i, _vp, _vp]),
     "sam2b_memory_encode": (_i, [_vp, _vp, _vp, _i, _vp, _vp]),
+    "sam2b_profile_begin": (_i, []),
+    "sam2b_profile_end": (_i, [C.c_char_p, _i64, C.POINTER(_i64)]),
     "sam2b_op_gemm": (_i, [_vp, _i64, _i64, _vp, _i64, _i64, _i, _i, _i, _i, _f, _vp, _i, _i, _vp, _vp, _i64, _i64, _i,
                            _vp, _vp, _i64, _i64, _i, _vp]),
     "sam2b_op_layernorm": (_i, [_vp, _vp, _vp, _f, _vp, _vp, _i64, _i, _vp]),

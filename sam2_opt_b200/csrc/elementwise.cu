@@ -1,6 +1,8 @@
 // Memory-bound kernels of the path (SURVEY.md §8a' K5/K6/K7/K8/K11): LayerNorm rows with fp32 statistics
 // and bf16 output (GEMM operand), casts, 2x2 max-pool of the skip path, patch-embed im2col, FPN top-down add,
 // row softmax and RoPE.  All are coalesced / 16-byte vectorised; reductions are warp shuffles.
+#include <cstdio>
+
 #include "common.cuh"
 #include "ops.h"
 
@@ -70,6 +72,9 @@ int layernorm_rows(const float* x, const float* gamma, const float* beta, float 
   const int nv = C / 4;
   const int wpb = 8;
   const unsigned grid = (unsigned)((rows + wpb - 1) / wpb);
+  char nm[64];
+  if (g_prof_on) snprintf(nm, sizeof(nm), "layernorm c%d", C);
+  ProfRange pr(stream, nm, 0, (double)rows * C * (4.0 + (y16 ? 2.0 : 0.0) + (y32 ? 4.0 : 0.0)));
   if (nv <= 64) layernorm_rows_kernel<2><<<grid, 256, 0, stream>>>(x, gamma, beta, eps, y16, y32, rows, C);
   else if (nv <= 96) layernorm_rows_kernel<3><<<grid, 256, 0, stream>>>(x, gamma, beta, eps, y16, y32, rows, C);
   else if (nv <= 160) layernorm_rows_kernel<5><<<grid, 256, 0, stream>>>(x, gamma, beta, eps, y16, y32, rows, C);
@@ -93,6 +98,7 @@ int cast_f32_bf16(const float* x, bf16* y, long n, cudaStream_t stream) {
   const long n4 = n / 4;
   long blocks = (n4 + 255) / 256;
   if (blocks > (long)num_sms() * 16) blocks = (long)num_sms() * 16;
+  ProfRange pr(stream, "cast_bf16", 0, (double)n * 6.0);
   cast_f32_bf16_kernel<<<(unsigned)blocks, 256, 0, stream>>>(reinterpret_cast<const float4*>(x), reinterpret_cast<uint2*>(y), n4);
   SAM2B_CHECK_LAUNCH("cast_f32_bf16");
   return 0;
@@ -126,6 +132,7 @@ int maxpool2x2_nhwc(const float* x, float* y, int B, int H, int W, int C, cudaSt
   const long total = (long)B * (H / 2) * (W / 2) * (C / 4);
   long blocks = (total + 255) / 256;
   if (blocks > (long)num_sms() * 16) blocks = (long)num_sms() * 16;
+  ProfRange pr(stream, "maxpool2x2", 0, (double)B * H * W * C * 5.0);
   maxpool2x2_nhwc_kernel<<<(unsigned)blocks, 256, 0, stream>>>(reinterpret_cast<const float4*>(x), reinterpret_cast<float4*>(y), B, H, W, C / 4);
   SAM2B_CHECK_LAUNCH("maxpool2x2_nhwc");
   return 0;
@@ -173,6 +180,7 @@ int patch_im2col(const float* img, bf16* cols, int B, int S, int normalise, cuda
   const long total = (long)B * (S / 4) * (S / 4) * 20;
   long blocks = (total + 255) / 256;
   if (blocks > (long)num_sms() * 32) blocks = (long)num_sms() * 32;
+  ProfRange pr(stream, "patch_im2col", 0, (double)B * S * S * 3 * 4.0 + (double)total * 16.0);
   patch_im2col_kernel<<<(unsigned)blocks, 256, 0, stream>>>(img, reinterpret_cast<uint4*>(cols), B, S, normalise);
   SAM2B_CHECK_LAUNCH("patch_im2col");
   return 0;
@@ -200,6 +208,7 @@ int upsample2x_add_nchw(float* dst, const float* src, int B, int C, int H, int W
   const long total4 = (long)B * C * H * (W / 4);
   long blocks = (total4 + 255) / 256;
   if (blocks > (long)num_sms() * 16) blocks = (long)num_sms() * 16;
+  ProfRange pr(stream, "upsample2x_add", 0, (double)total4 * 16.0 * 2.25);
   upsample2x_add_kernel<<<(unsigned)blocks, 256, 0, stream>>>(reinterpret_cast<float4*>(dst), reinterpret_cast<const float2*>(src), total4, W / 4, H, W / 4);
   SAM2B_CHECK_LAUNCH("upsample2x_add");
   return 0;
@@ -257,6 +266,7 @@ int softmax_rows(const float* s, long lds, bf16* p, long ldp, long rows, int col
     cudaFuncSetAttribute(softmax_rows_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
     attr = true;
   }
+  ProfRange pr(stream, "softmax_rows", 0, (double)rows * cols * 6.0);
   softmax_rows_kernel<<<(unsigned)rows, 512, smem, stream>>>(s, lds, p, ldp, cols);
   SAM2B_CHECK_LAUNCH("softmax_rows");
   return 0;
@@ -295,6 +305,7 @@ int rope_cast_rows(const float* x, const float* cos_t, const float* sin_t, bf16*
   const long total = rows * 64;
   long blocks = (total + 255) / 256;
   if (blocks > (long)num_sms() * 16) blocks = (long)num_sms() * 16;
+  ProfRange pr(stream, "rope_cast", 0, (double)rows * 256 * 6.0);
   rope_cast_rows_kernel<<<(unsigned)blocks, 256, 0, stream>>>(x, cos_t, sin_t, y, rows, rope_rows);
   SAM2B_CHECK_LAUNCH("rope_cast_rows");
   return 0;

@@ -25,6 +25,20 @@ void set_error(const char* fmt, ...) {
 }
 const char* get_error() { return g_err; }
 
+// ---- profiling ----
+bool g_prof_on = false;
+struct ProfRec { char name[96]; double flops, bytes; cudaEvent_t a, b; };
+static std::vector<ProfRec> g_prof;
+void prof_push(const char* name, double flops, double bytes, cudaStream_t st) {
+  ProfRec r;
+  snprintf(r.name, sizeof(r.name), "%s", name);
+  r.flops = flops; r.bytes = bytes;
+  cudaEventCreate(&r.a); cudaEventCreate(&r.b);
+  cudaEventRecord(r.a, st);
+  g_prof.push_back(r);
+}
+void prof_pop(cudaStream_t st) { cudaEventRecord(g_prof.back().b, st); }
+
 int num_sms() {
   static int n = 0;
   if (!n) {
@@ -420,6 +434,31 @@ int sam2b_memory_encode(sam2b_handle h, const float* pix_feat, const float* mask
   (void)h; (void)pix_feat; (void)masks; (void)n; (void)out_x; (void)stream;
   set_error("sam2b_memory_encode: not built yet");
   return 1;
+}
+
+// ---- profiling ----
+int sam2b_profile_begin(void) {
+  for (auto& r : g_prof) { cudaEventDestroy(r.a); cudaEventDestroy(r.b); }
+  g_prof.clear();
+  g_prof_on = true;
+  return 0;
+}
+int sam2b_profile_end(char* buf, int64_t buflen, int64_t* needed) {
+  g_prof_on = false;
+  cudaDeviceSynchronize();
+  std::string out = "name,ms,flops,bytes\n";
+  char line[256];
+  for (auto& r : g_prof) {
+    float ms = 0.f;
+    cudaEventElapsedTime(&ms, r.a, r.b);
+    snprintf(line, sizeof(line), "%s,%.6f,%.6g,%.6g\n", r.name, ms, r.flops, r.bytes);
+    out += line;
+    cudaEventDestroy(r.a); cudaEventDestroy(r.b);
+  }
+  g_prof.clear();
+  if (needed) *needed = (int64_t)out.size() + 1;
+  if (buf && buflen > 0) { snprintf(buf, (size_t)buflen, "%s", out.c_str()); }
+  return 0;
 }
 
 // ---- building blocks ----

@@ -9,6 +9,7 @@
 // (reference hieradet.py:56-81, sam2_utils.py:131-136), patch-embed as im2col GEMM (backbones/utils.py:89-93),
 // FpnNeck 1x1 convs + conv_s0/s1 (image_encoder.py:102-134, sam2_base_official.py:571-577), and the
 // memory-attention / memory-encoder linears and score/PV products.
+#include <cstdio>
 #include <mutex>
 #include <unordered_map>
 
@@ -305,6 +306,11 @@ static int launch_gemm(const GemmArgs& a, cudaStream_t stream) {
   p.out_f32 = a.out_f32; p.out_bf16 = a.out_bf16; p.ldc = a.ldc; p.c_batch_stride = a.c_batch_stride;
   const long tiles = (long)p.tiles_m * p.tiles_n * p.batch;
   const int grid = (int)(tiles < num_sms() ? tiles : num_sms());
+  char nm[96];
+  if (g_prof_on) snprintf(nm, sizeof(nm), "gemm m%d n%d k%d b%d bn%d act%d%s%s", a.M, a.N, a.K, a.batch, BN, a.act, a.residual ? " res" : "", a.out_bf16 ? " o16" : " o32");
+  const double esz = a.out_bf16 ? 2.0 : 4.0;
+  ProfRange pr(stream, nm, 2.0 * a.M * a.N * (double)a.K * a.batch,
+               ((double)a.M * a.K * 2 + (b_batched ? 1.0 : 1.0 / a.batch) * (double)a.N * a.K * 2 + (double)a.M * a.N * (esz + (a.residual ? 4.0 : 0.0))) * a.batch);
   gemm_bf16_tcgen05_kernel<BN><<<grid, NUM_THREADS, Cfg::SMEM, stream>>>(ta, tb, p);
   SAM2B_CHECK_LAUNCH("gemm_bf16_tcgen05");
   return 0;

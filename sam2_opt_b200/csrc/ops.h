@@ -25,6 +25,17 @@ extern unsigned long long g_launch_count;
     }                                                                         \
   } while (0)
 
+// ---- optional per-launch CUDA-event profiling (bench.py's roofline leg; off by default) ----
+// A ProfRange placed around a launch records an event pair on the launching stream when profiling is enabled.
+void prof_push(const char* name, double flops, double bytes, cudaStream_t st);
+void prof_pop(cudaStream_t st);
+extern bool g_prof_on;
+struct ProfRange {
+  cudaStream_t st; bool on;
+  ProfRange(cudaStream_t s, const char* name, double flops, double bytes) : st(s), on(g_prof_on) { if (on) prof_push(name, flops, bytes, st); }
+  ~ProfRange() { if (on) prof_pop(st); }
+};
+
 enum Act { ACT_NONE = 0, ACT_GELU = 1, ACT_RELU = 2 };
 
 // C[b][m][n] = epilogue( alpha * sum_k A[b][m][k] * B[b][n][k] )      (both operands K-major, bf16)

@@ -10,6 +10,8 @@
 //
 // This legacy-tensor-path kernel carries ~11 % of the encoder's FLOPs; the tcgen05 flash kernel for the three
 // global blocks is the planned replacement.
+#include <cstdio>
+
 #include "common.cuh"
 #include "ops.h"
 
@@ -265,6 +267,10 @@ int window_attention_hd72(const bf16* qkv, bf16* out, int B, int H, int W, int h
     cudaFuncSetAttribute(window_attn_hd72_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     attr = true;
   }
+  char nm[96];
+  if (g_prof_on) snprintf(nm, sizeof(nm), "attn h%d heads%d ws%d pool%d b%d", H, heads, ws, q_pool, B);
+  const double nq = (double)B * nwin * p.QW * heads;
+  ProfRange pr(stream, nm, 4.0 * nq * p.KW * HD, ((double)B * H * W * 3 + (double)B * nwin * p.QW) * heads * HD * 2.0);
   if (p.QW >= 64) {
     if (p.QW % 64 || p.KW % 64) { set_error("window_attention: QW=%d KW=%d not multiples of 64", p.QW, p.KW); return 1; }
     dim3 grid(nwin * (p.QW / 64), heads, B);

@@ -135,3 +135,20 @@ class Engine:
 
 def launch_count() -> int:
     return int(_lib.load().sam2b_launch_count())
+
+
+def profile_begin():
+    _lib.check(_lib.load().sam2b_profile_begin(), "profile_begin")
+
+
+def profile_end():
+    """-> list of (name, ms, flops, bytes), one per kernel launch since profile_begin()."""
+    lib = _lib.load()
+    need = C.c_int64(0)
+    buf = C.create_string_buffer(1 << 24)
+    _lib.check(lib.sam2b_profile_end(buf, len(buf), C.byref(need)), "profile_end")
+    rows = []
+    for line in buf.value.decode().splitlines()[1:]:
+        name, ms, fl, by = line.rsplit(",", 3)
+        rows.append((name, float(ms), float(fl), float(by)))
+    return rows
