@@ -177,6 +177,26 @@ static int finalize(sam2b_engine* e) {
   TRY(need(e, "derived.neck.s1.bias", nullptr, false));
   TRY(need(e, "derived.neck.s0.weight", nullptr, true));       // conv_s0 o lateral: [32,144]
   TRY(need(e, "derived.neck.s0.bias", nullptr, false));
+  // ---- memory attention (memory_attention.py:18-109, transformer.py:297-424) ----
+  for (int l = 0; l < 4; ++l) {
+    const std::string p = "memory_attention.layers." + std::to_string(l) + ".";
+    const std::string d = "derived.memattn." + std::to_string(l) + ".";
+    TRY(need(e, d + "sa_qk.weight", nullptr, true));          // [512,256] = cat(q_proj, k_proj)
+    TRY(need(e, d + "sa_qk.bias", nullptr, false));
+    for (const char* lin : {"self_attn.v_proj.", "self_attn.out_proj.", "cross_attn_image.q_proj.", "cross_attn_image.k_proj.",
+                            "cross_attn_image.v_proj.", "cross_attn_image.out_proj.", "linear1.", "linear2."}) {
+      TRY(need(e, p + lin + "weight", nullptr, true));
+      TRY(need(e, p + lin + "bias", nullptr, false));
+    }
+    for (const char* ln : {"norm1.", "norm2.", "norm3."}) {
+      TRY(need(e, p + ln + "weight", nullptr, false));
+      TRY(need(e, p + ln + "bias", nullptr, false));
+    }
+  }
+  TRY(need(e, "memory_attention.norm.weight", nullptr, false));
+  TRY(need(e, "memory_attention.norm.bias", nullptr, false));
+  TRY(need(e, "derived.rope.cos", nullptr, false));            // [4096,128]
+  TRY(need(e, "derived.rope.sin", nullptr, false));
   CUDA_OK(cudaStreamSynchronize(0));
   e->finalized = true;
   return 0;
@@ -294,6 +314,129 @@ static int image_encode_mb(sam2b_engine* e, const float* img, int n, int normali
     TRY(gemm_bf16(g, st));
   }
   TRY(upsample2x_add_nchw(fpn2, LAT3, n, 256, 64, 64, st));
+  return 0;
+}
+
+// ------------------------------------------------------------------------------------------------------------
+// MemoryAttention (boundary E3) for a micro-batch of n objects.  All contractions run on the tcgen05 GEMM:
+//   S = q k^T / 16 (fp32) -> row softmax (bf16 P) -> O = P V with V^T produced directly by a swapped-operand GEMM.
+// ------------------------------------------------------------------------------------------------------------
+static int memory_attention_mb(sam2b_engine* e, const float* curr, const float* curr_pos, const float* memory,
+                               const float* memory_pos, int L, const float* excl, const float* pos_excl, int P, int n,
+                               int n_total, float* out, cudaStream_t st) {
+  // curr/memory pointers address object 0 of this micro-batch inside tensors whose batch dimension is n_total
+  const int T = 4096, C = 256;
+  const long Lk = (long)L * 4096 + P;
+  const long Lkp = (Lk + 63) / 64 * 64;
+  const long TT = (long)n * T;
+  float *X, *QK, *S, *KC32, *OUT;
+  bf16 *XN, *Qb, *Kb, *VT, *Pm, *KIN, *VIN, *Kc, *VcT, *O, *HID;
+  TRY(ws_get_t(e, "ma_x", (size_t)TT * C, &X));
+  TRY(ws_get_t(e, "ma_qk", (size_t)TT * 512, &QK));
+  TRY(ws_get_t(e, "ma_s", (size_t)n * T * Lkp, &S));
+  TRY(ws_get_t(e, "ma_kc32", (size_t)n * Lk * C, &KC32));
+  TRY(ws_get_t(e, "ma_out", (size_t)TT * C, &OUT));
+  TRY(ws_get_t(e, "ma_xn", (size_t)TT * C, &XN));
+  TRY(ws_get_t(e, "ma_qb", (size_t)TT * C, &Qb));
+  TRY(ws_get_t(e, "ma_kb", (size_t)TT * C, &Kb));
+  TRY(ws_get_t(e, "ma_vt", (size_t)TT * C, &VT));
+  TRY(ws_get_t(e, "ma_p", (size_t)n * T * Lkp, &Pm));
+  TRY(ws_get_t(e, "ma_kin", (size_t)n * Lkp * 64, &KIN));
+  TRY(ws_get_t(e, "ma_vin", (size_t)n * Lkp * 64, &VIN));
+  TRY(ws_get_t(e, "ma_kc", (size_t)n * Lkp * C, &Kc));
+  TRY(ws_get_t(e, "ma_vct", (size_t)n * C * Lkp, &VcT));
+  TRY(ws_get_t(e, "ma_o", (size_t)TT * C, &O));
+  TRY(ws_get_t(e, "ma_hid", (size_t)TT * 2048, &HID));
+  const float* cos_t = W32(e, "derived.rope.cos");
+  const float* sin_t = W32(e, "derived.rope.sin");
+
+  if (n == n_total) {
+    TRY(memattn_prep_x(curr, curr_pos, X, T, n, C, st));
+    TRY(memattn_prep_memory(memory, memory_pos, L, excl, pos_excl, P, n, KIN, VIN, Lkp, st));
+  } else {
+    set_error("memory_attention: object micro-batching of a strided batch is not supported (n=%d of %d)", n, n_total);
+    return 1;
+  }
+
+  auto linear = [&](const bf16* A, long lda, int M, const std::string& wname, int N, int K, int act, const float* residual,
+                    float* o32, bf16* o16, long ldc) -> int {
+    GemmArgs g;
+    g.A = A; g.lda = lda; g.M = M; g.K = K;
+    g.B = W16(e, wname + "weight"); g.ldb = K; g.N = N;
+    g.bias = W32(e, wname + "bias"); g.act = act;
+    g.residual = residual; g.ld_res = ldc;
+    g.out_f32 = o32; g.out_bf16 = o16; g.ldc = ldc;
+    return gemm_bf16(g, st);
+  };
+  // attention core on prepared operands: q [n][T][256], k [n][keys][256] (row stride 256), vT [n][256][ldv]
+  auto attend = [&](const bf16* q, const bf16* k, long k_rows_alloc, const bf16* vT, long keys, long ldv) -> int {
+    const long lds = (keys + 63) / 64 * 64;
+    {
+      GemmArgs g;
+      g.A = q; g.lda = C; g.a_batch_stride = (long)T * C; g.M = T; g.K = C;
+      g.B = k; g.ldb = C; g.b_batch_stride = k_rows_alloc * C; g.N = (int)keys;
+      g.batch = n; g.alpha = 1.0f / 16.0f;                 // 1/sqrt(256)
+      g.out_f32 = S; g.ldc = lds; g.c_batch_stride = (long)T * lds;
+      TRY(gemm_bf16(g, st));
+    }
+    TRY(softmax_rows(S, lds, Pm, lds, (long)n * T, (int)keys, st));
+    {
+      GemmArgs g;
+      g.A = Pm; g.lda = lds; g.a_batch_stride = (long)T * lds; g.M = T; g.K = (int)keys;
+      g.B = vT; g.ldb = ldv; g.b_batch_stride = (long)C * ldv; g.N = C;
+      g.batch = n;
+      g.out_bf16 = O; g.ldc = C; g.c_batch_stride = (long)T * C;
+      TRY(gemm_bf16(g, st));
+    }
+    return 0;
+  };
+  // V^T[b][c][j] = sum_k Wv[c][k] * in[b][j][k] + bv[c]
+  auto v_transposed = [&](const std::string& wname, const bf16* in, long in_rows_alloc, int K, long keys, long ldv, bf16* vt) -> int {
+    GemmArgs g;
+    g.A = W16(e, wname + "weight"); g.lda = K; g.M = C; g.K = K;
+    g.B = in; g.ldb = K; g.b_batch_stride = in_rows_alloc * K; g.N = (int)keys;
+    g.batch = n;
+    g.bias = W32(e, wname + "bias"); g.bias_along_m = 1;
+    g.out_bf16 = vt; g.ldc = ldv; g.c_batch_stride = (long)C * ldv;
+    return gemm_bf16(g, st);
+  };
+
+  for (int l = 0; l < 4; ++l) {
+    const std::string p = "memory_attention.layers." + std::to_string(l) + ".";
+    const std::string d = "derived.memattn." + std::to_string(l) + ".";
+    // ---- self attention (RoPE on q and k) ----
+    TRY(layernorm_rows(X, W32(e, p + "norm1.weight"), W32(e, p + "norm1.bias"), 1e-5f, XN, nullptr, TT, C, st));
+    TRY(linear(XN, C, (int)TT, d + "sa_qk.", 512, C, ACT_NONE, nullptr, QK, nullptr, 512));
+    TRY(rope_cast_batched(QK, 512, cos_t, sin_t, Qb, n, T, T, T, st));
+    TRY(rope_cast_batched(QK + 256, 512, cos_t, sin_t, Kb, n, T, T, T, st));
+    TRY(v_transposed(p + "self_attn.v_proj.", XN, T, C, T, T, VT));
+    TRY(attend(Qb, Kb, T, VT, T, T));
+    TRY(linear(O, C, (int)TT, p + "self_attn.out_proj.", C, C, ACT_NONE, X, X, nullptr, C));
+    // ---- cross attention over the memory bank (RoPE on q and on the L*4096 spatial keys only) ----
+    TRY(layernorm_rows(X, W32(e, p + "norm2.weight"), W32(e, p + "norm2.bias"), 1e-5f, XN, nullptr, TT, C, st));
+    TRY(linear(XN, C, (int)TT, p + "cross_attn_image.q_proj.", C, C, ACT_NONE, nullptr, QK, nullptr, C));
+    TRY(rope_cast_batched(QK, C, cos_t, sin_t, Qb, n, T, T, T, st));
+    {
+      GemmArgs g;   // k = k_proj(memory + pos): [n][Lk][256] fp32
+      g.A = KIN; g.lda = 64; g.a_batch_stride = Lkp * 64; g.M = (int)Lk; g.K = 64;
+      g.B = W16(e, p + "cross_attn_image.k_proj.weight"); g.ldb = 64; g.N = C;
+      g.batch = n;
+      g.bias = W32(e, p + "cross_attn_image.k_proj.bias");
+      g.out_f32 = KC32; g.ldc = C; g.c_batch_stride = Lk * C;
+      TRY(gemm_bf16(g, st));
+    }
+    TRY(rope_cast_batched(KC32, C, cos_t, sin_t, Kc, n, Lk, (long)L * 4096, Lkp, st));
+    TRY(v_transposed(p + "cross_attn_image.v_proj.", VIN, Lkp, 64, Lk, Lkp, VcT));
+    TRY(attend(Qb, Kc, Lkp, VcT, Lk, Lkp));
+    TRY(linear(O, C, (int)TT, p + "cross_attn_image.out_proj.", C, C, ACT_NONE, X, X, nullptr, C));
+    // ---- FFN ----
+    TRY(layernorm_rows(X, W32(e, p + "norm3.weight"), W32(e, p + "norm3.bias"), 1e-5f, XN, nullptr, TT, C, st));
+    TRY(linear(XN, C, (int)TT, p + "linear1.", 2048, C, ACT_RELU, nullptr, nullptr, HID, 2048));
+    TRY(linear(HID, 2048, (int)TT, p + "linear2.", C, 2048, ACT_NONE, X, X, nullptr, C));
+  }
+  TRY(layernorm_rows(X, W32(e, "memory_attention.norm.weight"), W32(e, "memory_attention.norm.bias"), 1e-5f, nullptr,
+                     n == 1 ? out : OUT, TT, C, st));
+  if (n > 1) TRY(batch_to_seq(OUT, out, T, n, C, st));
   return 0;
 }
 
@@ -424,10 +567,13 @@ int sam2b_image_encode_host(sam2b_handle h, const float* img_host, int n, int no
 int sam2b_memory_attention(sam2b_handle h, const float* curr, const float* curr_pos, const float* memory,
                            const float* memory_pos, int L, const float* memory_exclude, const float* memory_pos_exclude,
                            int P, int n, float* out, void* stream) {
-  (void)h; (void)curr; (void)curr_pos; (void)memory; (void)memory_pos; (void)L; (void)memory_exclude; (void)memory_pos_exclude;
-  (void)P; (void)n; (void)out; (void)stream;
-  set_error("sam2b_memory_attention: not built yet");
-  return 1;
+  if (!h || !h->finalized) { set_error("sam2b_memory_attention: engine not finalized"); return 1; }
+  if (!curr || !curr_pos || !memory || !memory_pos || !out || n <= 0) { set_error("sam2b_memory_attention: null/empty argument"); return 1; }
+  if (L < 1 || L > 7 || P < 0 || P > 64 || (P % 4)) { set_error("sam2b_memory_attention: L=%d must be in [1,7], P=%d in [0,64] and a multiple of 4", L, P); return 1; }
+  if (P > 0 && (!memory_exclude || !memory_pos_exclude)) { set_error("sam2b_memory_attention: P=%d but memory_exclude is NULL", P); return 1; }
+  CUDA_OK(cudaSetDevice(h->device));
+  return memory_attention_mb(h, curr, curr_pos, memory, memory_pos, L, memory_exclude, memory_pos_exclude, P, n, n, out,
+                             reinterpret_cast<cudaStream_t>(stream));
 }
 
 int sam2b_memory_encode(sam2b_handle h, const float* pix_feat, const float* masks, int n, float* out_x, void* stream) {

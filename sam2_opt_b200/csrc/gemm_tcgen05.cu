@@ -333,7 +333,6 @@ static int pick_bn(const GemmArgs& a) {
 int gemm_bf16(const GemmArgs& a, cudaStream_t stream) {
   if (a.M <= 0 || a.N <= 0 || a.K <= 0 || a.batch <= 0) { set_error("gemm: empty problem M=%d N=%d K=%d batch=%d", a.M, a.N, a.K, a.batch); return 1; }
   if (!a.out_f32 && !a.out_bf16) { set_error("gemm: no output"); return 1; }
-  if (a.K % 8) { set_error("gemm: K=%d must be a multiple of 8", a.K); return 1; }
   if ((a.out_f32 && (a.ldc % 4 || (reinterpret_cast<uintptr_t>(a.out_f32) & 15))) ||
       (a.out_bf16 && (a.ldc % 8 || (reinterpret_cast<uintptr_t>(a.out_bf16) & 15))) ||
       (a.residual && (a.ld_res % 4 || (reinterpret_cast<uintptr_t>(a.residual) & 15)))) {

@@ -82,3 +82,41 @@ int rope_cast_rows(const float* x, const float* cos_t, const float* sin_t, bf16*
                    cudaStream_t stream);
 
 }  // namespace sam2b
+
+namespace sam2b {
+// ---- memory attention helpers (memory_attention.cu) ----
+// x[b][t][c] = curr[t][b][c] + 0.1 * curr_pos[t][b][c]      (seq-first [T,n,C] -> batch-major [n,T,C], fp32)
+int memattn_prep_x(const float* curr, const float* curr_pos, float* x, int T, int n, int C, cudaStream_t stream);
+// out[t][b][c] = x[b][t][c]
+int batch_to_seq(const float* x, float* out, int T, int n, int C, cudaStream_t stream);
+// kin[b][j] = bf16(mem + pos), vin[b][j] = bf16(mem);  j = l*4096+t for the L spatial frames then L*4096+p for the P
+// pointer tokens; rows [Lk, ldk) of each batch are zero-filled.
+int memattn_prep_memory(const float* memory, const float* memory_pos, int L, const float* excl, const float* pos_excl,
+                        int P, int n, bf16* kin, bf16* vin, long ldk, cudaStream_t stream);
+// Batch-aware RoPE + cast: x fp32 [batch][rows_per_batch][ldx] (first 256 columns of each row) -> y bf16
+// [batch][rows_out_per_batch][256]; rows r < rope_rows of each batch are rotated with table row (r % 4096).
+int rope_cast_batched(const float* x, long ldx, const float* cos_t, const float* sin_t, bf16* y, int batch,
+                      long rows_per_batch, long rope_rows, long rows_out_per_batch, cudaStream_t stream);
+}  // namespace sam2b
+
+namespace sam2b {
+// ---- memory encoder helpers (memory_encoder.cu); reference modeling/memory_encoder.py:19-137 ----
+// LayerNorm rows followed by exact GELU, bf16 out (LayerNorm2d + GELU of the mask down-sampler in channels-last form)
+int layernorm_gelu_rows(const float* x, const float* gamma, const float* beta, float eps, bf16* y, long rows, int C,
+                        cudaStream_t stream);
+// MaskDownSampler stages 1-3: conv3x3 s2 p1 + LayerNorm2d(eps 1e-6) + GELU, fp32, channels-last outputs.
+//   stage 1: mask [n,1,S,S]        -> [n,S/2,S/2,4]
+//   stage 2: [n,H,H,4]  NHWC       -> [n,H/2,H/2,16]
+//   stage 3: [n,H,H,16] NHWC       -> [n,H/2,H/2,64]
+// w: conv weight in the reference layout [Cout,Cin,3,3]; b, ln_w, ln_b: [Cout]
+int mask_ds_stage(int stage, const float* in, float* out, int n, int H_in, const float* w, const float* b,
+                  const float* ln_w, const float* ln_b, cudaStream_t stream);
+// im2col for conv3x3 s2 p1 on NHWC fp32 [n,H,H,C] -> bf16 [n*(H/2)^2, 9*C], k = (ky*3+kx)*C + c
+int im2col3x3s2_nhwc(const float* in, bf16* cols, int n, int H, int C, cudaStream_t stream);
+// [n,C,HW] fp32 -> [n,HW,C] bf16
+int nchw_to_nhwc_bf16(const float* in, bf16* out, int n, int C, int HW, cudaStream_t stream);
+// CXBlock front half: depthwise 7x7 (pad 3) + LayerNorm2d(eps 1e-6) on NHWC fp32 [n,H,H,256] -> bf16 [n*H*H,256].
+// dw_w: [49][256] (tap-major), dw_b/ln_w/ln_b: [256]
+int dwconv7_ln_nhwc(const float* x, bf16* y, int n, int H, const float* dw_w, const float* dw_b, const float* ln_w,
+                    const float* ln_b, cudaStream_t stream);
+}  // namespace sam2b

@@ -73,6 +73,12 @@ def derive(w: Dict[str, torch.Tensor]) -> Dict[str, torch.Tensor]:
         bs_ = w[f"sam_mask_decoder.conv_{name}.bias"].double()
         d[f"derived.neck.{name}.weight"] = (ws_ @ lat[lvl][0]).float().contiguous()
         d[f"derived.neck.{name}.bias"] = (ws_ @ lat[lvl][1] + bs_).float().contiguous()
+    # memory attention: self-attention q and k projections share their input -> one GEMM
+    for l in range(4):
+        sa = f"memory_attention.layers.{l}.self_attn."
+        if sa + "q_proj.weight" in w:
+            d[f"derived.memattn.{l}.sa_qk.weight"] = torch.cat([w[sa + "q_proj.weight"], w[sa + "k_proj.weight"]], 0).float().contiguous()
+            d[f"derived.memattn.{l}.sa_qk.bias"] = torch.cat([w[sa + "q_proj.bias"], w[sa + "k_proj.bias"]], 0).float().contiguous()
     cos, sin = rope_tables(dev)
     d["derived.rope.cos"], d["derived.rope.sin"] = cos, sin
     return d
