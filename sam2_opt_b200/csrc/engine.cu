@@ -195,6 +195,33 @@ static int finalize(sam2b_engine* e) {
   }
   TRY(need(e, "memory_attention.norm.weight", nullptr, false));
   TRY(need(e, "memory_attention.norm.bias", nullptr, false));
+  // ---- memory encoder (memory_encoder.py) ----
+  {
+    const std::string m = "memory_encoder.", en = m + "mask_downsampler.encoder.";
+    for (int j = 0; j < 4; ++j) {
+      if (j < 3) TRY(need(e, en + std::to_string(3 * j) + ".weight", nullptr, false));
+      TRY(need(e, en + std::to_string(3 * j) + ".bias", nullptr, false));
+      TRY(need(e, en + std::to_string(3 * j + 1) + ".weight", nullptr, false));
+      TRY(need(e, en + std::to_string(3 * j + 1) + ".bias", nullptr, false));
+    }
+    TRY(need(e, "derived.memenc.ds4.weight", nullptr, true));   // [256, (ky,kx,cin)=576]
+    for (const char* c : {"mask_downsampler.encoder.12.", "pix_feat_proj.", "out_proj."}) {
+      TRY(need(e, m + c + "weight", nullptr, true));
+      TRY(need(e, m + c + "bias", nullptr, false));
+    }
+    for (int l = 0; l < 2; ++l) {
+      const std::string f = m + "fuser.layers." + std::to_string(l) + ".";
+      TRY(need(e, "derived.memenc.fuser." + std::to_string(l) + ".dw.weight", nullptr, false));   // [49,256]
+      TRY(need(e, f + "dwconv.bias", nullptr, false));
+      TRY(need(e, f + "norm.weight", nullptr, false));
+      TRY(need(e, f + "norm.bias", nullptr, false));
+      TRY(need(e, f + "gamma", nullptr, false));
+      for (const char* c : {"pwconv1.", "pwconv2."}) {
+        TRY(need(e, f + c + "weight", nullptr, true));
+        TRY(need(e, f + c + "bias", nullptr, false));
+      }
+    }
+  }
   TRY(need(e, "derived.rope.cos", nullptr, false));            // [4096,128]
   TRY(need(e, "derived.rope.sin", nullptr, false));
   CUDA_OK(cudaStreamSynchronize(0));
@@ -440,6 +467,72 @@ static int memory_attention_mb(sam2b_engine* e, const float* curr, const float* 
   return 0;
 }
 
+// ------------------------------------------------------------------------------------------------------------
+// MemoryEncoder (boundary E4): MaskDownSampler -> + pix_feat_proj -> 2 x CXBlock -> out_proj, channels-last inside.
+// ------------------------------------------------------------------------------------------------------------
+static int memory_encode_mb(sam2b_engine* e, const float* pix_feat, const float* masks, int n, float* out_x, cudaStream_t st) {
+  const long T = 4096L * n;
+  float *D1, *D2, *D3, *D4, *MDS, *X;
+  bf16 *COLS, *D4N, *PIXT, *XN, *HID, *XB;
+  TRY(ws_get_t(e, "me_d1", (size_t)n * 512 * 512 * 4, &D1));
+  TRY(ws_get_t(e, "me_d2", (size_t)n * 256 * 256 * 16, &D2));
+  TRY(ws_get_t(e, "me_d3", (size_t)n * 128 * 128 * 64, &D3));
+  TRY(ws_get_t(e, "me_d4", (size_t)T * 256, &D4));
+  TRY(ws_get_t(e, "me_mds", (size_t)T * 256, &MDS));
+  TRY(ws_get_t(e, "me_x", (size_t)T * 256, &X));
+  TRY(ws_get_t(e, "me_cols", (size_t)T * 576, &COLS));
+  TRY(ws_get_t(e, "me_d4n", (size_t)T * 256, &D4N));
+  TRY(ws_get_t(e, "me_pixt", (size_t)T * 256, &PIXT));
+  TRY(ws_get_t(e, "me_xn", (size_t)T * 256, &XN));
+  TRY(ws_get_t(e, "me_hid", (size_t)T * 1024, &HID));
+  TRY(ws_get_t(e, "me_xb", (size_t)T * 256, &XB));
+  const std::string m = "memory_encoder.", en = m + "mask_downsampler.encoder.";
+  auto P = [&](const std::string& name) { return W32(e, name); };
+  float* stage_out[3] = {D1, D2, D3};
+  const float* stage_in = masks;
+  int H = 1024;
+  for (int j = 0; j < 3; ++j) {
+    const std::string c = en + std::to_string(3 * j) + ".", l = en + std::to_string(3 * j + 1) + ".";
+    TRY(mask_ds_stage(j + 1, stage_in, stage_out[j], n, H, P(c + "weight"), P(c + "bias"), P(l + "weight"), P(l + "bias"), st));
+    stage_in = stage_out[j];
+    H /= 2;
+  }
+  TRY(im2col3x3s2_nhwc(D3, COLS, n, 128, 64, st));
+  auto linear = [&](const bf16* A, int K, const bf16* Wt, const float* bias, int N, int act, const float* gamma,
+                    const float* residual, float* o32, bf16* o16) -> int {
+    GemmArgs g;
+    g.A = A; g.lda = K; g.M = (int)T; g.K = K;
+    g.B = Wt; g.ldb = K; g.N = N;
+    g.bias = bias; g.act = act; g.gamma = gamma;
+    g.residual = residual; g.ld_res = N;
+    g.out_f32 = o32; g.out_bf16 = o16; g.ldc = N;
+    return gemm_bf16(g, st);
+  };
+  TRY(linear(COLS, 576, W16(e, "derived.memenc.ds4.weight"), P(en + "9.bias"), 256, ACT_NONE, nullptr, nullptr, D4, nullptr));
+  TRY(layernorm_gelu_rows(D4, P(en + "10.weight"), P(en + "10.bias"), 1e-6f, D4N, T, 256, st));
+  TRY(linear(D4N, 256, W16(e, en + "12.weight"), P(en + "12.bias"), 256, ACT_NONE, nullptr, nullptr, MDS, nullptr));
+  TRY(nchw_to_nhwc_bf16(pix_feat, PIXT, n, 256, 4096, st));
+  TRY(linear(PIXT, 256, W16(e, m + "pix_feat_proj.weight"), P(m + "pix_feat_proj.bias"), 256, ACT_NONE, nullptr, MDS, X, nullptr));
+  for (int l = 0; l < 2; ++l) {
+    const std::string f = m + "fuser.layers." + std::to_string(l) + ".";
+    TRY(dwconv7_ln_nhwc(X, XN, n, 64, P("derived.memenc.fuser." + std::to_string(l) + ".dw.weight"), P(f + "dwconv.bias"),
+                        P(f + "norm.weight"), P(f + "norm.bias"), st));
+    TRY(linear(XN, 256, W16(e, f + "pwconv1.weight"), P(f + "pwconv1.bias"), 1024, ACT_GELU, nullptr, nullptr, nullptr, HID));
+    TRY(linear(HID, 1024, W16(e, f + "pwconv2.weight"), P(f + "pwconv2.bias"), 256, ACT_NONE, P(f + "gamma"), X, X, nullptr));
+  }
+  TRY(cast_f32_bf16(X, XB, T * 256, st));
+  {
+    GemmArgs g;   // out_proj with swapped operands -> NCHW [n][64][4096]
+    g.A = W16(e, m + "out_proj.weight"); g.lda = 256; g.M = 64; g.K = 256;
+    g.B = XB; g.ldb = 256; g.b_batch_stride = 4096L * 256; g.N = 4096;
+    g.batch = n;
+    g.bias = P(m + "out_proj.bias"); g.bias_along_m = 1;
+    g.out_f32 = out_x; g.ldc = 4096; g.c_batch_stride = 64L * 4096;
+    TRY(gemm_bf16(g, st));
+  }
+  return 0;
+}
+
 static const int kMaxMicroBatch = 16;
 
 }  // namespace sam2b
@@ -577,9 +670,15 @@ int sam2b_memory_attention(sam2b_handle h, const float* curr, const float* curr_
 }
 
 int sam2b_memory_encode(sam2b_handle h, const float* pix_feat, const float* masks, int n, float* out_x, void* stream) {
-  (void)h; (void)pix_feat; (void)masks; (void)n; (void)out_x; (void)stream;
-  set_error("sam2b_memory_encode: not built yet");
-  return 1;
+  if (!h || !h->finalized) { set_error("sam2b_memory_encode: engine not finalized"); return 1; }
+  if (!pix_feat || !masks || !out_x || n <= 0) { set_error("sam2b_memory_encode: null/empty argument"); return 1; }
+  CUDA_OK(cudaSetDevice(h->device));
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  for (int i0 = 0; i0 < n; i0 += kMaxMicroBatch) {
+    const int mb = (n - i0) < kMaxMicroBatch ? (n - i0) : kMaxMicroBatch;
+    TRY(memory_encode_mb(h, pix_feat + (size_t)i0 * 256 * 4096, masks + (size_t)i0 * 1024 * 1024, mb, out_x + (size_t)i0 * 64 * 4096, st));
+  }
+  return 0;
 }
 
 // ---- profiling ----

@@ -79,6 +79,13 @@ def derive(w: Dict[str, torch.Tensor]) -> Dict[str, torch.Tensor]:
         if sa + "q_proj.weight" in w:
             d[f"derived.memattn.{l}.sa_qk.weight"] = torch.cat([w[sa + "q_proj.weight"], w[sa + "k_proj.weight"]], 0).float().contiguous()
             d[f"derived.memattn.{l}.sa_qk.bias"] = torch.cat([w[sa + "q_proj.bias"], w[sa + "k_proj.bias"]], 0).float().contiguous()
+    # memory encoder: last down-sampler conv as an im2col GEMM with k = (ky,kx,cin); depthwise weights tap-major
+    k9 = "memory_encoder.mask_downsampler.encoder.9.weight"
+    if k9 in w:
+        d["derived.memenc.ds4.weight"] = w[k9].float().permute(0, 2, 3, 1).reshape(256, 576).contiguous()
+        for l in range(2):
+            dw = w[f"memory_encoder.fuser.layers.{l}.dwconv.weight"].float()
+            d[f"derived.memenc.fuser.{l}.dw.weight"] = dw.reshape(256, 49).t().contiguous()
     cos, sin = rope_tables(dev)
     d["derived.rope.cos"], d["derived.rope.sin"] = cos, sin
     return d
