@@ -1,0 +1,300 @@
+"""Standalone predictors with the reference's public API, running the hot path on the sm_100a engine.
+
+``SAM2ImagePredictor`` / ``SAM2VideoPredictor`` mirror the reference classes' user-facing calls
+(ref: sam2/sam2/sam2_image_predictor.py:141-202,388-589; sam2/sam2/sam2_video_predictor_official.py:148-205,267-399,
+586-736,843-945) over a plain ``state_dict`` with the reference's tensor names, so a user without the reference package
+installed (e.g. the GPU box) still has ``set_image`` / ``predict`` / ``init_state`` / ``add_new_points_or_box`` /
+``propagate_in_video`` and the ``speedup()`` / ``release()`` switch.  The image encoder, memory attention and memory
+encoder run inside libsam2b.so; prompt encoder / mask decoder / memory-bank assembly are fp32 torch (``sam_heads.py``).
+
+Differences from the reference that are deliberate: all objects of a video are batched through the engine in one call
+per frame (the reference loops objects with batch 1, sam2_video_predictor_official.py:689-725), and frame embeddings are
+produced a few frames ahead in one batched encoder call.
+"""
+from collections import OrderedDict
+from typing import Dict, List, Optional
+
+import numpy as np
+import torch
+import torch.nn.functional as F
+
+from . import sam_heads as H
+from .executor import B200Executor
+
+IMG_MEAN = (0.485, 0.456, 0.406)
+IMG_STD = (0.229, 0.224, 0.225)
+
+
+class _Base:
+    def __init__(self, state_dict: Dict[str, torch.Tensor], device="cuda", backend="b200"):
+        self.device = torch.device(device)
+        if self.device.type != "cuda":
+            raise RuntimeError("sam2_opt_b200 predictors need a CUDA device (no CPU fallback)")
+        self.w = {k: v.detach().to(self.device, torch.float32).contiguous() for k, v in state_dict.items() if torch.is_tensor(v)}
+        self.engine = None
+        self.backend_contexts: List[B200Executor] = []
+        self._dense_pe = H.dense_pe(self.w)
+        self.speedup(backend)
+
+    def speedup(self, backend="b200", use_cache=True, model_root_path=None):
+        """Same switch as the reference (ref: sam2_image_predictor.py:94-138).  "b200" builds the engine from the
+        current weights (re-snapshotting them if called again).  This package ships no torch implementation of the hot
+        path, so "torch" / "tensorrt" / "onnxruntime" raise instead of silently running something else."""
+        for ctx in self.backend_contexts:
+            ctx.Release()
+        self.backend_contexts = []
+        if self.engine is not None:
+            self.engine.release()
+            self.engine = None
+        if backend is None:
+            return
+        if backend.lower() not in ("b200", "sm100", "sm_100a", "cuda"):
+            raise Exception(f"unsupported runtime backend={backend} (the reference torch/TensorRT paths live in the reference package)")
+        from .engine import Engine
+        self.engine = Engine(self.w, self.device)
+        self.backend_contexts = [B200Executor(self.engine, k) for k in
+                                 ("set_image_e2e", "inference_image", "memory_attention_none", "memory_attention_exclude", "memory_encoder")]
+        self._ex = {c.kind: c for c in self.backend_contexts}
+
+    def release(self):
+        self.speedup(None)
+
+    def _prep_image(self, image) -> torch.Tensor:
+        """uint8 HWC numpy -> [1,3,1024,1024] fp32 in [0,1] (ref: sam2_image_predictor.py:173-196: /255 then resize)."""
+        img = torch.as_tensor(np.ascontiguousarray(image)).to(self.device)
+        img = img.permute(2, 0, 1)[None].float() / 255.0
+        if img.shape[-2:] != (1024, 1024):
+            img = F.interpolate(img, size=(1024, 1024), mode="bilinear", align_corners=False, antialias=True)
+        return img
+
+
+class SAM2ImagePredictor(_Base):
+    def __init__(self, state_dict, device="cuda", mask_threshold=0.0, backend="b200"):
+        super().__init__(state_dict, device, backend)
+        self.mask_threshold = mask_threshold
+        self.reset_predictor()
+
+    def reset_predictor(self):
+        self._is_image_set, self._features, self._orig_hw, self._is_batch = False, None, None, False
+
+    @torch.no_grad()
+    def set_image(self, image: np.ndarray):
+        self.reset_predictor()
+        self._orig_hw = [image.shape[:2]]
+        f0, f1, f2 = self._ex["set_image_e2e"].Inference([self._prep_image(image)], output_type="torch")
+        self._features = {"image_embed": f2, "high_res_feats": [f0, f1]}
+        self._is_image_set = True
+
+    @torch.no_grad()
+    def set_image_batch(self, image_list: List[np.ndarray]):
+        self.reset_predictor()
+        assert isinstance(image_list, list)
+        self._orig_hw = [im.shape[:2] for im in image_list]
+        batch = torch.cat([self._prep_image(im) for im in image_list], 0)
+        f0, f1, f2 = self._ex["set_image_e2e"].Inference([batch], output_type="torch")
+        self._features = {"image_embed": f2, "high_res_feats": [f0, f1]}
+        self._is_image_set, self._is_batch = True, True
+
+    def get_image_embedding(self) -> torch.Tensor:
+        if not self._is_image_set:
+            raise RuntimeError("An image must be set with .set_image(...) to generate an embedding.")
+        return self._features["image_embed"]
+
+    @torch.no_grad()
+    def predict(self, point_coords=None, point_labels=None, box=None, mask_input=None, multimask_output=True,
+                return_logits=False, normalize_coords=True, img_idx=0):
+        """ref: sam2_image_predictor.py:388-589.  Returns (masks [C,H,W], iou_predictions [C], low_res_masks [C,256,256])."""
+        if not self._is_image_set:
+            raise RuntimeError("An image must be set with .set_image(...) before mask prediction.")
+        oh, ow = self._orig_hw[img_idx]
+        coords = labels = None
+        if point_coords is not None:
+            assert point_labels is not None, "point_labels must be supplied if point_coords is supplied."
+            coords = torch.as_tensor(np.asarray(point_coords), dtype=torch.float32, device=self.device).clone().reshape(-1, 2)
+            if normalize_coords:
+                coords[:, 0] = coords[:, 0] / ow * 1024
+                coords[:, 1] = coords[:, 1] / oh * 1024
+            coords = coords[None]
+            labels = torch.as_tensor(np.asarray(point_labels), dtype=torch.int32, device=self.device).reshape(1, -1)
+        if box is not None:
+            b = torch.as_tensor(np.asarray(box), dtype=torch.float32, device=self.device).clone().reshape(-1, 2, 2)
+            if normalize_coords:
+                b[..., 0] = b[..., 0] / ow * 1024
+                b[..., 1] = b[..., 1] / oh * 1024
+            bl = torch.tensor([[2, 3]], dtype=torch.int32, device=self.device).repeat(b.shape[0], 1)
+            coords = b if coords is None else torch.cat([b, coords], 1)
+            labels = bl if labels is None else torch.cat([bl, labels], 1)
+        mask_t = None
+        if mask_input is not None:
+            mask_t = torch.as_tensor(mask_input, dtype=torch.float32, device=self.device)
+            if mask_t.dim() == 3:
+                mask_t = mask_t[None]
+        sparse, dense = H.prompt_encoder(self.w, coords, labels, mask_t)
+        batched = coords is not None and coords.shape[0] > 1
+        hr = [f[img_idx:img_idx + 1] for f in self._features["high_res_feats"]]
+        low, iou, _, _ = H.mask_decoder(self.w, self._features["image_embed"][img_idx:img_idx + 1], sparse, dense,
+                                        multimask_output, hr, repeat_image=batched, pe=self._dense_pe)
+        masks = F.interpolate(low.float(), (oh, ow), mode="bilinear", align_corners=False)
+        low = torch.clamp(low, -32.0, 32.0)
+        if not return_logits:
+            masks = masks > self.mask_threshold
+        return masks[0].float().cpu().numpy(), iou[0].float().cpu().numpy(), low[0].float().cpu().numpy()
+
+
+class SAM2VideoPredictor(_Base):
+    """Forward video propagation with click / box prompts (BASELINE.json configs 3 and 4)."""
+
+    def __init__(self, state_dict, device="cuda", backend="b200", encode_ahead=4):
+        super().__init__(state_dict, device, backend)
+        self.encode_ahead = max(1, int(encode_ahead))
+
+    @torch.no_grad()
+    def init_state(self, frames=None, video_height=None, video_width=None, offload_video_to_cpu=True):
+        """frames: float tensor [T,3,1024,1024] already normalised (what the reference's loader returns,
+        utils/misc.py:213-277) or a list of uint8 HWC numpy frames."""
+        if isinstance(frames, (list, tuple)):
+            video_height, video_width = frames[0].shape[:2]
+            mean = torch.tensor(IMG_MEAN, device=self.device)[None, :, None, None]
+            std = torch.tensor(IMG_STD, device=self.device)[None, :, None, None]
+            frames = torch.cat([((self._prep_image(f) - mean) / std).cpu() for f in frames], 0)
+        assert frames.dim() == 4 and tuple(frames.shape[1:]) == (3, 1024, 1024)
+        st = {"images": frames if offload_video_to_cpu else frames.to(self.device), "num_frames": frames.shape[0],
+              "video_height": video_height or 1024, "video_width": video_width or 1024,
+              "obj_ids": [], "prompts": OrderedDict(), "cond": OrderedDict(), "non_cond": OrderedDict(),
+              "feat_cache": {}, "frames_tracked": {}}
+        return st
+
+    def reset_state(self, st):
+        for k in ("prompts", "cond", "non_cond"):
+            st[k].clear()
+        st["obj_ids"], st["feat_cache"], st["frames_tracked"] = [], {}, {}
+
+    # -- per-frame image features, produced `encode_ahead` frames at a time --------------------------------------
+    def _features(self, st, t):
+        if t not in st["feat_cache"]:
+            t1 = min(st["num_frames"], t + self.encode_ahead)
+            imgs = st["images"][t:t1].to(self.device, non_blocking=True)
+            outs = self._ex["inference_image"].Inference([imgs], output_type="torch")
+            st["feat_cache"] = {t + i: (outs[6][i:i + 1], outs[3][i:i + 1], [outs[4][i:i + 1], outs[5][i:i + 1]]) for i in range(t1 - t)}
+        return st["feat_cache"][t]      # fpn2 [1,256,64,64], pos2 [1,256,64,64], [fpn0, fpn1]
+
+    def _encode_memory(self, f2, high_res_masks, obj_logits, from_points):
+        """ref: sam2_base_official.py:978-1026 + bf16 storage (sam2_video_predictor_official.py:887,939)"""
+        n = high_res_masks.shape[0]
+        m = (high_res_masks > 0).float() if from_points else torch.sigmoid(high_res_masks)
+        x, pos = self._ex["memory_encoder"].Inference([f2.expand(n, -1, -1, -1), m * 20.0 - 10.0], output_type="torch")
+        is_obj = (obj_logits > 0).float()
+        x = x + (1 - is_obj[..., None, None]) * self.w["no_obj_embed_spatial"][..., None, None].expand(*x.shape)
+        return x.to(torch.bfloat16), pos
+
+    def _video_res(self, st, low):
+        hw = (st["video_height"], st["video_width"])
+        return F.interpolate(low, size=hw, mode="bilinear", align_corners=False)
+
+    @torch.no_grad()
+    def add_new_points_or_box(self, st, frame_idx, obj_id, points=None, labels=None, clear_old_points=True,
+                              normalize_coords=True, box=None):
+        """ref: sam2_video_predictor_official.py:267-399.  Returns (frame_idx, obj_ids, video_res_masks)."""
+        if obj_id not in st["obj_ids"]:
+            if st["frames_tracked"]:
+                raise RuntimeError(f"Cannot add new object id {obj_id} after tracking starts; call reset_state first.")
+            st["obj_ids"].append(obj_id)
+        pts = torch.zeros(0, 2) if points is None else torch.as_tensor(np.asarray(points), dtype=torch.float32).reshape(-1, 2)
+        lab = torch.zeros(0, dtype=torch.int32) if labels is None else torch.as_tensor(np.asarray(labels), dtype=torch.int32).reshape(-1)
+        if box is not None:
+            if not clear_old_points:
+                raise ValueError("cannot add box without clearing old points")
+            pts = torch.cat([torch.as_tensor(np.asarray(box), dtype=torch.float32).reshape(2, 2), pts], 0)
+            lab = torch.cat([torch.tensor([2, 3], dtype=torch.int32), lab], 0)
+        pts = pts.clone()
+        if normalize_coords:
+            pts[:, 0] = pts[:, 0] / st["video_width"] * 1024
+            pts[:, 1] = pts[:, 1] / st["video_height"] * 1024
+        key = (frame_idx, obj_id)
+        if not clear_old_points and key in st["prompts"]:
+            pts = torch.cat([st["prompts"][key][0].cpu(), pts], 0)
+            lab = torch.cat([st["prompts"][key][1].cpu(), lab], 0)
+        st["prompts"][key] = (pts.to(self.device), lab.to(self.device))
+        out = self._run_cond_frame(st, frame_idx, [obj_id])
+        st["cond"].setdefault(frame_idx, {})[obj_id] = out
+        low = torch.cat([st["cond"][frame_idx][o]["pred_masks"] if o in st["cond"][frame_idx] else
+                         torch.full((1, 1, 256, 256), H.NO_OBJ_SCORE, device=self.device) for o in st["obj_ids"]], 0)
+        return frame_idx, list(st["obj_ids"]), self._video_res(st, low)
+
+    def _run_cond_frame(self, st, t, obj_ids):
+        f2, _, hr = self._features(st, t)
+        o = obj_ids[0]
+        pts, lab = st["prompts"][(t, o)]
+        pin = {"point_coords": pts[None], "point_labels": lab[None]}
+        pix = f2 + self.w["no_mem_embed"].view(1, -1, 1, 1)
+        multimask = 0 < pts.shape[0] <= 1      # ref: _use_multimask, sam2_base_official.py:1181-1189 (min 0, max 1 point)
+        _, _, _, low, high, ptr, obj = H.forward_sam_heads(self.w, pix, point_inputs=pin, high_res_features=hr,
+                                                           multimask_output=multimask, pe=self._dense_pe)
+        return {"pred_masks": low, "obj_ptr": ptr, "object_score_logits": obj, "maskmem_features": None, "maskmem_pos": None}
+
+    @torch.no_grad()
+    def propagate_in_video_preflight(self, st):
+        """Encode the memory of every prompted frame (ref: sam2_video_predictor_official.py:586-649)."""
+        for t, per_obj in st["cond"].items():
+            todo = [o for o, out in per_obj.items() if out["maskmem_features"] is None]
+            if not todo:
+                continue
+            f2 = self._features(st, t)[0]
+            low = torch.cat([per_obj[o]["pred_masks"] for o in todo], 0)
+            high = F.interpolate(low, size=(1024, 1024), mode="bilinear", align_corners=False)
+            obj = torch.cat([per_obj[o]["object_score_logits"] for o in todo], 0)
+            mf, mp = self._encode_memory(f2, high, obj, from_points=True)
+            for i, o in enumerate(todo):
+                per_obj[o]["maskmem_features"], per_obj[o]["maskmem_pos"] = mf[i:i + 1], mp[i:i + 1]
+
+    @torch.no_grad()
+    def propagate_in_video(self, st, start_frame_idx=None, max_frame_num_to_track=None):
+        """Generator of (frame_idx, obj_ids, video_res_masks [n,1,H,W]) — ref: sam2_video_predictor_official.py:652-736."""
+        self.propagate_in_video_preflight(st)
+        if not st["cond"]:
+            raise RuntimeError("No input points or masks are provided for any object; please add inputs first.")
+        T, objs = st["num_frames"], list(st["obj_ids"])
+        t0 = min(st["cond"]) if start_frame_idx is None else start_frame_idx
+        t1 = T - 1 if max_frame_num_to_track is None else min(T - 1, t0 + max_frame_num_to_track)
+        for t in range(t0, t1 + 1):
+            per_obj_low = {}
+            tracked = [o for o in objs if not (t in st["cond"] and o in st["cond"][t])]
+            for o in objs:
+                if o not in tracked:
+                    per_obj_low[o] = st["cond"][t][o]["pred_masks"]
+            if tracked:
+                outs = self._track_frame(st, t, tracked)
+                for o, out in zip(tracked, outs):
+                    st["non_cond"].setdefault(o, {})[t] = out
+                    per_obj_low[o] = out["pred_masks"]
+            st["frames_tracked"][t] = True
+            low = torch.cat([per_obj_low[o] for o in objs], 0)
+            yield t, objs, self._video_res(st, low)
+
+    def _track_frame(self, st, t, objs):
+        """One non-prompted frame for a list of objects, batched through the engine (ref: track_step,
+        sam2_base_official.py:1028-1179)."""
+        f2, pos2, hr = self._features(st, t)
+        groups = OrderedDict()
+        for o in objs:
+            cond = {tt: per[o] for tt, per in st["cond"].items() if o in per and per[o]["maskmem_features"] is not None}
+            mem = H.assemble_memory(self.w, t, cond, st["non_cond"].get(o, {}), st["num_frames"])
+            groups.setdefault((mem[0].shape[0], mem[2].shape[0]), []).append((o, mem))
+        results = {}
+        for (L, P), items in groups.items():
+            n = len(items)
+            cat = lambda i: torch.cat([m[i] for _, m in items], dim=2 if i < 2 else 1)
+            curr = f2.flatten(2).permute(2, 0, 1).expand(-1, n, -1)
+            curr_pos = pos2.flatten(2).permute(2, 0, 1).expand(-1, n, -1)
+            if P:
+                pix = self._ex["memory_attention_exclude"].Inference([curr, cat(0), curr_pos, cat(1), cat(2), cat(3)], output_type="torch")[0]
+            else:
+                pix = self._ex["memory_attention_none"].Inference([curr, cat(0), curr_pos, cat(1)], output_type="torch")[0]
+            pix = pix.permute(1, 2, 0).reshape(n, H.D_MODEL, 64, 64)
+            hr_n = [h.expand(n, -1, -1, -1) for h in hr]
+            _, _, _, low, high, ptr, obj = H.forward_sam_heads(self.w, pix, high_res_features=hr_n, multimask_output=True, pe=self._dense_pe)
+            mf, mp = self._encode_memory(f2, high, obj, from_points=False)
+            for i, (o, _) in enumerate(items):
+                results[o] = {"pred_masks": low[i:i + 1], "obj_ptr": ptr[i:i + 1], "object_score_logits": obj[i:i + 1],
+                              "maskmem_features": mf[i:i + 1], "maskmem_pos": mp[i:i + 1]}
+        return [results[o] for o in objs]

@@ -1,0 +1,107 @@
+"""``predictor.speedup("b200")`` for the REFERENCE's own predictor objects (drop-in).
+
+The reference switches backends by rebinding method pointers and storing executors in ``backend_contexts``
+(ref: sam2/sam2/sam2_image_predictor.py:94-138,204-250; sam2/sam2/sam2_video_predictor_official.py:45-145;
+sam2/sam2/modeling/sam2_base_official.py:230-276; modeling/memory_attention.py:134-261; modeling/memory_encoder.py:160-215).
+``speedup(predictor, "b200")`` does exactly that with ``B200Executor`` objects over one shared engine, so
+``SAM2ImagePredictor`` / ``SAM2VideoPredictor`` keep their API.  ``install()`` additionally teaches the reference classes'
+own ``speedup`` method the new backend name, making ``predictor.speedup("b200")`` work verbatim.
+
+The reference tree is read-only, so this is duck-typed: anything with the same attributes works (the CPU tests drive the
+real reference predictors with a stub engine; on a GPU box the standalone predictors of ``predictor.py`` are used).
+"""
+import torch
+
+from .executor import B200Executor
+
+B200_NAMES = ("b200", "sm100", "sm_100a", "cuda")
+
+
+def _release_contexts(obj):
+    for ctx in (getattr(obj, "backend_contexts", None) or []):
+        ctx.Release()
+    obj.backend_contexts = []
+
+
+def _make_engine(model, device, engine_factory):
+    if engine_factory is None:
+        from .engine import Engine
+        engine_factory = Engine
+    return engine_factory(model.state_dict(), device)
+
+
+def speedup(predictor, backend="b200", engine=None, engine_factory=None, warmup=True):
+    """Engage (``backend="b200"``) or disengage (``"torch"``) the sm_100a engine on a reference predictor.
+
+    Image predictor (has ``set_image_e2e``): rebinds E1.  Video predictor / SAM2Base (has ``inference_image``): rebinds
+    E2, E3 (both ``none`` and ``exclude`` variants) and E4.  Returns the engine in use (None for "torch")."""
+    b = backend.lower()
+    is_image = hasattr(predictor, "set_image_e2e") and hasattr(predictor, "model")
+    model = predictor.model if is_image else predictor
+    if b == "torch":
+        predictor.set_runtime_backend(backend="torch")
+        if not is_image:
+            model.memory_attention.set_runtime_backend(backend="torch")
+            model.memory_encoder.set_runtime_backend(backend="torch")
+        return None
+    if b not in B200_NAMES:
+        raise Exception(f"unsupported runtime backend={backend}")
+    device = next(model.parameters()).device if hasattr(model, "parameters") else torch.device("cuda")
+    if engine is None:
+        engine = _make_engine(model, device, engine_factory)
+
+    if is_image:
+        _release_contexts(predictor)
+        ex = B200Executor(engine, "set_image_e2e")
+        predictor.backend_contexts.append(ex)
+        predictor.set_image_e2e = lambda img, _ex=ex: tuple(o.to(img.device) for o in _ex.Inference([img], output_type="torch"))
+        if warmup:
+            ex.warmup([torch.randn(1, 3, 1024, 1024)])
+        return engine
+
+    # ---- SAM2Base / SAM2VideoPredictor ----
+    _release_contexts(model)
+    ex_img = B200Executor(engine, "inference_image")
+    model.backend_contexts.append(ex_img)
+    model.inference_image = lambda img, _ex=ex_img: tuple(o.to(img.device) for o in _ex.Inference([img], output_type="torch"))
+    ma = model.memory_attention
+    _release_contexts(ma)
+    ma.backend_contexts = [B200Executor(engine, "memory_attention_none"), B200Executor(engine, "memory_attention_exclude")]
+    ma.inference_memory_attention_none = ma.inference_memory_attention_speedup_none
+    ma.inference_memory_attention_exclude = ma.inference_memory_attention_speedup_exclude
+    me = model.memory_encoder
+    _release_contexts(me)
+    ex_me = B200Executor(engine, "memory_encoder")
+    me.backend_contexts = [ex_me]
+
+    def inference_memory(pix_feat, masks, _ex=ex_me):
+        x, pos = _ex.Inference([pix_feat, masks], output_type="torch")
+        return x.to(pix_feat.device), pos.to(pix_feat.device)
+
+    me.inference_memory = inference_memory
+    if warmup:
+        ex_img.warmup([torch.randn(1, 3, 1024, 1024)])
+        for L in (1, 7):
+            base = [torch.randn(4096, 1, 256), torch.randn(L, 4096, 1, 64), torch.randn(4096, 1, 256), torch.randn(L, 4096, 1, 64)]
+            ma.backend_contexts[0].warmup(base)
+            ma.backend_contexts[1].warmup(base + [torch.randn(64, 1, 64), torch.randn(64, 1, 64)])
+        ex_me.warmup([torch.randn(1, 256, 64, 64), torch.rand(1, 1, 1024, 1024)])
+    return engine
+
+
+def install(*classes):
+    """Patch reference predictor classes so that ``obj.speedup("b200")`` routes here and every other backend name keeps
+    the reference behaviour.  Call as ``install(SAM2ImagePredictor, SAM2VideoPredictor)``."""
+    for cls in classes:
+        orig = cls.speedup
+        if getattr(orig, "_sam2b_patched", False):
+            continue
+
+        def patched(self, backend="b200", *a, _orig=orig, **k):
+            if isinstance(backend, str) and backend.lower() in B200_NAMES:
+                self._sam2b_engine = speedup(self, backend, **{x: k[x] for x in ("engine", "engine_factory", "warmup") if x in k})
+                return None
+            return _orig(self, backend, *a, **k)
+
+        patched._sam2b_patched = True
+        cls.speedup = patched

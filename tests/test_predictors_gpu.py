@@ -1,0 +1,84 @@
+"""GPU: the standalone predictors (reference API, engine underneath) against the reference's own predictor outputs
+(golden fixtures made by the unmodified reference) and the fp32 oracle.  Gate (BASELINE.json north_star): mask IoU >= 0.99."""
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+def iou_bits(a_bool, b_bool):
+    u = (a_bool | b_bool).sum()
+    return 1.0 if u == 0 else float((a_bool & b_bool).sum()) / float(u)
+
+
+@pytest.fixture(scope="module")
+def weights():
+    from oracle import sam2_oracle as O
+    return O.make_weights(0)
+
+
+def test_config1_set_image_predict_iou(weights, golden):
+    from oracle.synth import synth_image_u8
+    from sam2_opt_b200.predictor import SAM2ImagePredictor
+    p = SAM2ImagePredictor(weights)
+    p.set_image(synth_image_u8(0))
+    masks, iou, low = p.predict(point_coords=np.array([[512, 512]]), point_labels=np.array([1]), multimask_output=True, return_logits=True)
+    ref_bits = np.unpackbits(golden["c1_low_res_bits"]).reshape(3, 256, 256).astype(bool)
+    ious = [iou_bits(low[i] > 0, ref_bits[i]) for i in range(3)]
+    print("config1 low-res mask IoU vs reference:", [f"{v:.4f}" for v in ious], "iou_pred", iou, "ref", golden["c1_iou"])
+    assert min(ious) >= 0.99
+    assert np.abs(iou - golden["c1_iou"]).max() < 2e-2
+    area = (masks > 0).sum(axis=(1, 2))
+    assert np.all(np.abs(area - golden["c1_mask_area"][0]) <= 0.02 * golden["c1_mask_area"][0] + 50)
+    with pytest.raises(Exception, match="unsupported runtime backend"):
+        p.speedup("tensorrt")
+    p.speedup("b200")          # re-snapshot works
+    p.release(); p.release()   # idempotent
+
+
+def test_config3_video_vs_reference_golden(weights, golden):
+    from oracle.synth import synth_video
+    from sam2_opt_b200.predictor import SAM2VideoPredictor
+    vp = SAM2VideoPredictor(weights)
+    st = vp.init_state(synth_video(4, seed=1))
+    vp.add_new_points_or_box(st, 0, 1, points=np.array([[512, 512]], dtype=np.float32), labels=np.array([1], np.int32))
+    ious = []
+    for t, ids, m in vp.propagate_in_video(st):
+        low = (st["cond"][t][1] if t in st["cond"] else st["non_cond"][1][t])["pred_masks"][0, 0]
+        ref = np.unpackbits(golden["c3_low_res_bits"][t]).reshape(256, 256).astype(bool)
+        ious.append(iou_bits((low > 0).cpu().numpy(), ref))
+        assert m.shape == (1, 1, 1024, 1024) and ids == [1]
+    print("config3 per-frame IoU vs reference:", [f"{v:.4f}" for v in ious])
+    assert min(ious) >= 0.99
+    vp.release()
+
+
+def test_video_full_bank_vs_oracle_and_object_batching(weights):
+    """9 frames (the 7-frame bank fills), two objects batched in one engine call per frame; object 1 must match the fp32
+    oracle's single-object run frame by frame, and batching must not change an object's result."""
+    from oracle import sam2_oracle as O
+    from oracle.synth import synth_video
+    from sam2_opt_b200.predictor import SAM2VideoPredictor
+    T = 9
+    frames = synth_video(T, seed=2)
+    vp = SAM2VideoPredictor(weights)
+    st = vp.init_state(frames)
+    vp.add_new_points_or_box(st, 0, 1, points=np.array([[512, 512]], dtype=np.float32), labels=np.array([1], np.int32))
+    vp.add_new_points_or_box(st, 0, 2, points=np.array([[300, 700]], dtype=np.float32), labels=np.array([1], np.int32))
+    got = {t: m for t, _, m in vp.propagate_in_video(st)}
+    st1 = vp.init_state(frames)
+    vp.add_new_points_or_box(st1, 0, 2, points=np.array([[300, 700]], dtype=np.float32), labels=np.array([1], np.int32))
+    alone = {t: m for t, _, m in vp.propagate_in_video(st1)}
+    with torch.no_grad():
+        ref = {t: low for t, low in O.video_propagate(weights, frames)}
+    ious, ious_b = [], []
+    for t in range(T):
+        low = (st["cond"][t][1] if t in st["cond"] else st["non_cond"][1][t])["pred_masks"][0, 0].cpu()
+        ious.append(O.mask_iou(low, ref[t][0, 0]))
+        ious_b.append(iou_bits((got[t][1, 0] > 0).cpu().numpy(), (alone[t][0, 0] > 0).cpu().numpy()))
+    print("9-frame IoU vs oracle:", [f"{v:.4f}" for v in ious])
+    print("batched-vs-alone IoU:", [f"{v:.4f}" for v in ious_b])
+    assert min(ious) >= 0.99
+    assert min(ious_b) >= 0.995
+    vp.release()
