@@ -23,8 +23,11 @@ static constexpr int BK = 64;       // 64 bf16 = 128 B = one swizzle row
 static constexpr int UMMA_K = 16;
 static constexpr int ACC_STRIDE = 256;   // TMEM columns between the two accumulator stages
 static constexpr int TMEM_COLS = 512;
-static constexpr int NUM_THREADS = 256;  // warp0 TMA, warp1 MMA, warp2 TMEM alloc, warp3 idle, warps4-7 epilogue
-static constexpr int SMEM_BUDGET = 200 * 1024;
+static constexpr int NUM_EPI_WARPS = 8;  // two warps per TMEM lane quarter, interleaved over 32-column chunks
+static constexpr int NUM_THREADS = 128 + 32 * NUM_EPI_WARPS;  // warp0 TMA, warp1 MMA, warp2 TMEM alloc, warp3 idle, warps4-11 epilogue
+static constexpr int EPI_STAGE_BYTES = 32 * 32 * 4;           // one 32x32 fp32 transpose buffer per epilogue warp (XOR swizzled)
+static constexpr int EPI_SMEM = NUM_EPI_WARPS * EPI_STAGE_BYTES;
+static constexpr int SMEM_TOTAL = 227 * 1024;
 
 struct GemmKernelParams {
   int M, N, K, batch;
@@ -43,9 +46,26 @@ struct GemmCfg {
   static constexpr int STAGE_A = BM * BK * 2;
   static constexpr int STAGE_B = BN * BK * 2;
   static constexpr int STAGE = STAGE_A + STAGE_B;
-  static constexpr int STAGES = (SMEM_BUDGET / STAGE) > 8 ? 8 : (SMEM_BUDGET / STAGE);
-  static constexpr int SMEM = STAGES * STAGE + 1024 /*align slack*/ + 256 /*barriers*/;
+  static constexpr int AVAIL = SMEM_TOTAL - EPI_SMEM - 1024 /*align slack*/ - 256 /*barriers*/;
+  static constexpr int STAGES = (AVAIL / STAGE) > 8 ? 8 : (AVAIL / STAGE);
+  static constexpr int SMEM = STAGES * STAGE + EPI_SMEM + 1024 + 256;
 };
+
+// Exact-erf GELU, x * Phi(x), evaluated as relu(x) - |x| * h(|x|) with h(t) = Phi(-t) = 2^p(t); p is a degree-6
+// fit of log2(0.5 erfc(t/sqrt 2)) on [0,6] (max |error| of the GELU value 2e-7 in fp32) -> 6 FMA + 1 MUFU.EX2.
+SAM2B_DEVINL float gelu_fast(float x) {
+  const float t = fminf(fabsf(x), 6.0f);
+  float p = 3.242628146753161e-05f;
+  p = fmaf(p, t, -0.0007628580443300231f);
+  p = fmaf(p, t, 0.008056423025940528f);
+  p = fmaf(p, t, -0.05336353987295394f);
+  p = fmaf(p, t, -0.4588251982307528f);
+  p = fmaf(p, t, -1.1511703007880216f);
+  p = fmaf(p, t, -1.0f);
+  float h;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(h) : "f"(p));
+  return fmaf(-fabsf(x), h, fmaxf(x, 0.0f));
+}
 
 template <int BN>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
@@ -57,7 +77,8 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* smem_a = smem;
   uint8_t* smem_b = smem + STAGES * Cfg::STAGE_A;
-  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + STAGES * Cfg::STAGE);
+  uint8_t* smem_epi = smem + STAGES * Cfg::STAGE;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem_epi + EPI_SMEM);
   uint64_t* full_bar = bars;
   uint64_t* empty_bar = bars + STAGES;
   uint64_t* tmem_full = bars + 2 * STAGES;
@@ -74,7 +95,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid
   }
   if (warp == 1 && lane == 0) {
     for (int i = 0; i < STAGES; ++i) { mbar_init(&full_bar[i], 1); mbar_init(&empty_bar[i], 1); }
-    for (int i = 0; i < 2; ++i) { mbar_init(&tmem_full[i], 1); mbar_init(&tmem_empty[i], 4); }
+    for (int i = 0; i < 2; ++i) { mbar_init(&tmem_full[i], 1); mbar_init(&tmem_empty[i], NUM_EPI_WARPS); }
     fence_barrier_init();
   }
   if (warp == 2) {
@@ -132,8 +153,19 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid
       }
     }
   } else if (warp >= 4) {
-    // ===================== epilogue: TMEM -> registers -> global =====================
-    const int ew = warp & 3;                 // TMEM lane quarter this warp may read
+    // ===================== epilogue: TMEM -> registers -> smem transpose -> coalesced global =====================
+    // Warp (4+we) may read TMEM lanes 32*(we&3)..+31 (hardware rule: warp id mod 4).  The two warps of a lane quarter
+    // take alternate 32-column chunks.  tcgen05.ld gives thread i row i of the chunk; the XOR-swizzled staging buffer
+    // turns that into "8 lanes x float4 = one 128 B row segment", so every global load/store instruction of the warp
+    // covers 4 full 128 B lines (fp32) instead of 32 scattered 16 B pieces.
+    const int we = warp - 4;
+    const int q = we & 3;
+    const int half = we >> 2;
+    float4* stg = reinterpret_cast<float4*>(smem_epi + we * EPI_STAGE_BYTES);
+    const int lr = lane >> 3;            // row inside a group of 4 rows (transposed layout)
+    const int lc = lane & 7;             // float4 column inside the 32-column chunk
+    constexpr int NCHUNK = (BN + 31) / 32;
+    const bool has_res = p.residual != nullptr;
     int local = 0;
     for (int t = blockIdx.x; t < num_tiles; t += gridDim.x, ++local) {
       const int n_blk = t % p.tiles_n;
@@ -141,89 +173,106 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid
       const int b = t / (p.tiles_n * p.tiles_m);
       const int acc = local & 1;
       const uint32_t acc_phase = (local >> 1) & 1;
+      const int row0 = m_blk * BM + q * 32 + lr;           // this lane's rows: row0 + 4k
+      const int ncol0 = n_blk * BN + lc * 4;               // this lane's columns in chunk c: ncol0 + 32c .. +3
+      const float* res_base = nullptr;
+      if (has_res) res_base = p.residual + (long)b * p.res_batch_stride;
+      float4 res[8];
+      auto load_res = [&](int c) {
+        const int col = ncol0 + c * 32;
+        const bool col_ok = (c * 32 + lc * 4 < BN) && (col + 4 <= p.N);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+          const int row = row0 + 4 * k;
+          res[k] = make_float4(0.f, 0.f, 0.f, 0.f);
+          if (col_ok && row < p.M) {
+            const int rr = p.res_row_mod ? (row % p.res_row_mod) : row;
+            res[k] = *reinterpret_cast<const float4*>(res_base + (long)rr * p.ld_res + col);
+          }
+        }
+      };
+      if (has_res && half < NCHUNK) load_res(half);       // overlaps the wait for the accumulator
+      float bias_m[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+      if (p.bias && p.bias_along_m) {
+#pragma unroll
+        for (int k = 0; k < 8; ++k) bias_m[k] = (row0 + 4 * k < p.M) ? __ldg(p.bias + row0 + 4 * k) : 0.f;
+      }
       mbar_wait(&tmem_full[acc], acc_phase);
       tc_fence_after();
-      const int row = m_blk * BM + ew * 32 + lane;
-      const bool row_ok = row < p.M;
-      const uint32_t taddr = tmem_base + acc * ACC_STRIDE + ((uint32_t)(ew * 32) << 16);
-      float* o32 = p.out_f32 ? p.out_f32 + (long)b * p.c_batch_stride + (long)row * p.ldc : nullptr;
-      bf16* o16 = p.out_bf16 ? p.out_bf16 + (long)b * p.c_batch_stride + (long)row * p.ldc : nullptr;
-      const float* res = nullptr;
-      if (p.residual) {
-        const int rr = p.res_row_mod ? (row % p.res_row_mod) : row;
-        res = p.residual + (long)b * p.res_batch_stride + (long)rr * p.ld_res;
-      }
-      const float bias_m = (p.bias && p.bias_along_m && row_ok) ? __ldg(p.bias + row) : 0.f;
+      const uint32_t taddr = tmem_base + acc * ACC_STRIDE + ((uint32_t)(q * 32) << 16);
 #pragma unroll 1
-      for (int c0 = 0; c0 < BN; c0 += 32) {
+      for (int c = half; c < NCHUNK; c += 2) {
         uint32_t r[32];
-        const int width = (BN - c0) >= 32 ? 32 : 16;
-        if (width == 32) tmem_ld_x32(taddr + c0, r); else tmem_ld_x16(taddr + c0, r);
+        tmem_ld_x32(taddr + c * 32, r);      // columns past BN (last chunk of BN=144) are never stored
         tmem_ld_wait();
-        const int col0 = n_blk * BN + c0;
-        if (row_ok && col0 < p.N) {
 #pragma unroll
-          for (int j = 0; j < 32; j += 8) {
-            if (j < width) {
-              const int col = col0 + j;
-              if (col + 8 <= p.N) {
-                float v[8];
+        for (int j = 0; j < 8; ++j)
+          stg[lane * 8 + (j ^ (lane & 7))] = make_float4(__uint_as_float(r[4 * j]), __uint_as_float(r[4 * j + 1]),
+                                                         __uint_as_float(r[4 * j + 2]), __uint_as_float(r[4 * j + 3]));
+        __syncwarp();
+        float4 v[8];
 #pragma unroll
-                for (int e = 0; e < 8; ++e) v[e] = __uint_as_float(r[j + e]) * p.alpha;
-                if (p.bias) {
-                  if (p.bias_along_m) {
+        for (int k = 0; k < 8; ++k) {
+          const int rl = 4 * k + lr;
+          v[k] = stg[rl * 8 + (lc ^ (rl & 7))];
+        }
+        __syncwarp();
+        const int col = ncol0 + c * 32;
+        const bool in_tile = c * 32 + lc * 4 < BN;
+        if (in_tile && col + 4 <= p.N) {
+          float4 bn = make_float4(0.f, 0.f, 0.f, 0.f), gm = make_float4(1.f, 1.f, 1.f, 1.f);
+          if (p.bias && !p.bias_along_m) bn = __ldg(reinterpret_cast<const float4*>(p.bias + col));
+          if (p.gamma) gm = __ldg(reinterpret_cast<const float4*>(p.gamma + col));
 #pragma unroll
-                    for (int e = 0; e < 8; ++e) v[e] += bias_m;
-                  } else {
-                    const float4 b0 = __ldg(reinterpret_cast<const float4*>(p.bias + col));
-                    const float4 b1 = __ldg(reinterpret_cast<const float4*>(p.bias + col + 4));
-                    v[0] += b0.x; v[1] += b0.y; v[2] += b0.z; v[3] += b0.w;
-                    v[4] += b1.x; v[5] += b1.y; v[6] += b1.z; v[7] += b1.w;
-                  }
-                }
-                if (p.act == ACT_GELU) {
+          for (int k = 0; k < 8; ++k) {
+            float4 o = v[k];
+            const float bm = (p.bias && p.bias_along_m) ? bias_m[k] : 0.f;
+            o.x = fmaf(o.x, p.alpha, bn.x + bm); o.y = fmaf(o.y, p.alpha, bn.y + bm);
+            o.z = fmaf(o.z, p.alpha, bn.z + bm); o.w = fmaf(o.w, p.alpha, bn.w + bm);
+            if (p.act == ACT_GELU) { o.x = gelu_fast(o.x); o.y = gelu_fast(o.y); o.z = gelu_fast(o.z); o.w = gelu_fast(o.w); }
+            else if (p.act == ACT_RELU) { o.x = fmaxf(o.x, 0.f); o.y = fmaxf(o.y, 0.f); o.z = fmaxf(o.z, 0.f); o.w = fmaxf(o.w, 0.f); }
+            if (p.gamma) { o.x *= gm.x; o.y *= gm.y; o.z *= gm.z; o.w *= gm.w; }
+            if (has_res) { o.x += res[k].x; o.y += res[k].y; o.z += res[k].z; o.w += res[k].w; }
+            v[k] = o;
+          }
+          if (has_res && c + 2 < NCHUNK) load_res(c + 2);   // next chunk's residual in flight during the stores
 #pragma unroll
-                  for (int e = 0; e < 8; ++e) v[e] = gelu_erf(v[e]);
-                } else if (p.act == ACT_RELU) {
-#pragma unroll
-                  for (int e = 0; e < 8; ++e) v[e] = fmaxf(v[e], 0.f);
-                }
-                if (p.gamma) {
-                  const float4 g0 = __ldg(reinterpret_cast<const float4*>(p.gamma + col));
-                  const float4 g1 = __ldg(reinterpret_cast<const float4*>(p.gamma + col + 4));
-                  v[0] *= g0.x; v[1] *= g0.y; v[2] *= g0.z; v[3] *= g0.w;
-                  v[4] *= g1.x; v[5] *= g1.y; v[6] *= g1.z; v[7] *= g1.w;
-                }
-                if (res) {
-                  const float4 r0 = *reinterpret_cast<const float4*>(res + col);
-                  const float4 r1 = *reinterpret_cast<const float4*>(res + col + 4);
-                  v[0] += r0.x; v[1] += r0.y; v[2] += r0.z; v[3] += r0.w;
-                  v[4] += r1.x; v[5] += r1.y; v[6] += r1.z; v[7] += r1.w;
-                }
-                if (o32) {
-                  *reinterpret_cast<float4*>(o32 + col) = make_float4(v[0], v[1], v[2], v[3]);
-                  *reinterpret_cast<float4*>(o32 + col + 4) = make_float4(v[4], v[5], v[6], v[7]);
-                }
-                if (o16) {
-                  uint4 pk;
-                  pk.x = pack_bf16x2(v[0], v[1]); pk.y = pack_bf16x2(v[2], v[3]);
-                  pk.z = pack_bf16x2(v[4], v[5]); pk.w = pack_bf16x2(v[6], v[7]);
-                  *reinterpret_cast<uint4*>(o16 + col) = pk;
-                }
-              } else {
-                // ragged N tail: scalar path
-                for (int e = 0; e < 8 && col + e < p.N; ++e) {
-                  float v = __uint_as_float(r[j + e]) * p.alpha;
-                  if (p.bias) v += p.bias_along_m ? bias_m : __ldg(p.bias + col + e);
-                  if (p.act == ACT_GELU) v = gelu_erf(v); else if (p.act == ACT_RELU) v = fmaxf(v, 0.f);
-                  if (p.gamma) v *= __ldg(p.gamma + col + e);
-                  if (res) v += res[col + e];
-                  if (o32) o32[col + e] = v;
-                  if (o16) o16[col + e] = __float2bfloat16(v);
-                }
+          for (int k = 0; k < 8; ++k) {
+            const int row = row0 + 4 * k;
+            if (row < p.M) {
+              const long off = (long)b * p.c_batch_stride + (long)row * p.ldc + col;
+              if (p.out_f32) *reinterpret_cast<float4*>(p.out_f32 + off) = v[k];
+              if (p.out_bf16) {
+                uint2 pk;
+                pk.x = pack_bf16x2(v[k].x, v[k].y); pk.y = pack_bf16x2(v[k].z, v[k].w);
+                *reinterpret_cast<uint2*>(p.out_bf16 + off) = pk;
               }
             }
           }
+        } else {
+          if (in_tile && col < p.N) {
+            // ragged N tail (N % 4 != 0 or the tile edge cuts this float4): scalar path
+#pragma unroll
+            for (int k = 0; k < 8; ++k) {
+              const int row = row0 + 4 * k;
+              if (row >= p.M) continue;
+              const float vv[4] = {v[k].x, v[k].y, v[k].z, v[k].w};
+              for (int e = 0; e < 4 && col + e < p.N; ++e) {
+                float o = vv[e] * p.alpha;
+                if (p.bias) o += p.bias_along_m ? bias_m[k] : __ldg(p.bias + col + e);
+                if (p.act == ACT_GELU) o = gelu_fast(o); else if (p.act == ACT_RELU) o = fmaxf(o, 0.f);
+                if (p.gamma) o *= __ldg(p.gamma + col + e);
+                if (has_res) {
+                  const int rr = p.res_row_mod ? (row % p.res_row_mod) : row;
+                  o += res_base[(long)rr * p.ld_res + col + e];
+                }
+                const long off = (long)b * p.c_batch_stride + (long)row * p.ldc + col + e;
+                if (p.out_f32) p.out_f32[off] = o;
+                if (p.out_bf16) p.out_bf16[off] = __float2bfloat16(o);
+              }
+            }
+          }
+          if (has_res && c + 2 < NCHUNK) load_res(c + 2);
         }
       }
       tc_fence_before();
