@@ -157,15 +157,25 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid
     // Warp (4+we) may read TMEM lanes 32*(we&3)..+31 (hardware rule: warp id mod 4).  The two warps of a lane quarter
     // take alternate 32-column chunks.  tcgen05.ld gives thread i row i of the chunk; the XOR-swizzled staging buffer
     // turns that into "8 lanes x float4 = one 128 B row segment", so every global load/store instruction of the warp
-    // covers 4 full 128 B lines (fp32) instead of 32 scattered 16 B pieces.
+    // covers 4 full 128 B lines (fp32) instead of 32 scattered 16 B pieces.  Every epilogue option is a warp-uniform
+    // branch taken once per 32x32 chunk (not per element), and addresses advance by precomputed strides.
     const int we = warp - 4;
     const int q = we & 3;
     const int half = we >> 2;
-    float4* stg = reinterpret_cast<float4*>(smem_epi + we * EPI_STAGE_BYTES);
+    const uint32_t stg_base = smem_u32(smem_epi + we * EPI_STAGE_BYTES);
     const int lr = lane >> 3;            // row inside a group of 4 rows (transposed layout)
     const int lc = lane & 7;             // float4 column inside the 32-column chunk
+    const uint32_t sts_base = stg_base + lane * 128;                       // row `lane`, slot j ^ (lane & 7)
+    const uint32_t sts_xor = (uint32_t)(lane & 7) << 4;
+    // transposed read: row rl = 4k + lr, slot lc ^ (rl & 7); (4k + lr) & 7 = lr + 4 (k & 1)
+    const uint32_t lds_even = stg_base + lr * 128 + ((uint32_t)(lc ^ lr) << 4);          // k even
+    const uint32_t lds_odd = stg_base + (lr + 4) * 128 + ((uint32_t)(lc ^ (lr + 4)) << 4);  // k odd
     constexpr int NCHUNK = (BN + 31) / 32;
     const bool has_res = p.residual != nullptr;
+    const bool bias_n = p.bias != nullptr && !p.bias_along_m;
+    const bool bias_m_on = p.bias != nullptr && p.bias_along_m;
+    const long row_step_c = 4 * p.ldc;       // elements between this lane's consecutive rows
+    const long row_step_r = 4 * p.ld_res;
     int local = 0;
     for (int t = blockIdx.x; t < num_tiles; t += gridDim.x, ++local) {
       const int n_blk = t % p.tiles_n;
@@ -175,27 +185,32 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid
       const uint32_t acc_phase = (local >> 1) & 1;
       const int row0 = m_blk * BM + q * 32 + lr;           // this lane's rows: row0 + 4k
       const int ncol0 = n_blk * BN + lc * 4;               // this lane's columns in chunk c: ncol0 + 32c .. +3
-      const float* res_base = nullptr;
-      if (has_res) res_base = p.residual + (long)b * p.res_batch_stride;
+      uint32_t row_mask = 0;                               // bit k: row0 + 4k < M
+#pragma unroll
+      for (int k = 0; k < 8; ++k) row_mask |= (row0 + 4 * k < p.M) ? (1u << k) : 0u;
+      const long out_off0 = (long)b * p.c_batch_stride + (long)row0 * p.ldc + ncol0;
+      const float* res_ptr0 = nullptr;
+      if (has_res) {
+        // res_row_mod (broadcast of a [mod, N] table over row blocks) must be a multiple of BM: one modulo per tile
+        const int rbase = p.res_row_mod ? ((m_blk * BM) % p.res_row_mod) + q * 32 + lr : row0;
+        res_ptr0 = p.residual + (long)b * p.res_batch_stride + (long)rbase * p.ld_res + ncol0;
+      }
       float4 res[8];
       auto load_res = [&](int c) {
-        const int col = ncol0 + c * 32;
-        const bool col_ok = (c * 32 + lc * 4 < BN) && (col + 4 <= p.N);
+        const bool col_ok = (c * 32 + lc * 4 < BN) && (ncol0 + c * 32 + 4 <= p.N);
+        const float* rp = res_ptr0 + c * 32;
 #pragma unroll
         for (int k = 0; k < 8; ++k) {
-          const int row = row0 + 4 * k;
           res[k] = make_float4(0.f, 0.f, 0.f, 0.f);
-          if (col_ok && row < p.M) {
-            const int rr = p.res_row_mod ? (row % p.res_row_mod) : row;
-            res[k] = *reinterpret_cast<const float4*>(res_base + (long)rr * p.ld_res + col);
-          }
+          if (col_ok && ((row_mask >> k) & 1)) res[k] = ld_global_f4(rp);
+          rp += row_step_r;
         }
       };
       if (has_res && half < NCHUNK) load_res(half);       // overlaps the wait for the accumulator
       float bias_m[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-      if (p.bias && p.bias_along_m) {
+      if (bias_m_on) {
 #pragma unroll
-        for (int k = 0; k < 8; ++k) bias_m[k] = (row0 + 4 * k < p.M) ? __ldg(p.bias + row0 + 4 * k) : 0.f;
+        for (int k = 0; k < 8; ++k) bias_m[k] = ((row_mask >> k) & 1) ? __ldg(p.bias + row0 + 4 * k) : 0.f;
       }
       mbar_wait(&tmem_full[acc], acc_phase);
       tc_fence_after();
@@ -205,48 +220,68 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid
         uint32_t r[32];
         tmem_ld_x32(taddr + c * 32, r);      // columns past BN (last chunk of BN=144) are never stored
         tmem_ld_wait();
+        if (c + 2 >= NCHUNK) {
+          // last chunk of this warp is in registers: hand the accumulator stage back to the MMA warp now
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(&tmem_empty[acc]);
+        }
 #pragma unroll
         for (int j = 0; j < 8; ++j)
-          stg[lane * 8 + (j ^ (lane & 7))] = make_float4(__uint_as_float(r[4 * j]), __uint_as_float(r[4 * j + 1]),
-                                                         __uint_as_float(r[4 * j + 2]), __uint_as_float(r[4 * j + 3]));
+          st_shared_u4(sts_base + (((uint32_t)j << 4) ^ sts_xor), r[4 * j], r[4 * j + 1], r[4 * j + 2], r[4 * j + 3]);
         __syncwarp();
         float4 v[8];
 #pragma unroll
-        for (int k = 0; k < 8; ++k) {
-          const int rl = 4 * k + lr;
-          v[k] = stg[rl * 8 + (lc ^ (rl & 7))];
-        }
+        for (int k = 0; k < 8; ++k) v[k] = ld_shared_f4(((k & 1) ? lds_odd : lds_even) + (k >> 1) * 1024);
         __syncwarp();
         const int col = ncol0 + c * 32;
         const bool in_tile = c * 32 + lc * 4 < BN;
         if (in_tile && col + 4 <= p.N) {
-          float4 bn = make_float4(0.f, 0.f, 0.f, 0.f), gm = make_float4(1.f, 1.f, 1.f, 1.f);
-          if (p.bias && !p.bias_along_m) bn = __ldg(reinterpret_cast<const float4*>(p.bias + col));
-          if (p.gamma) gm = __ldg(reinterpret_cast<const float4*>(p.gamma + col));
+          {
+            float4 bn = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (bias_n) bn = __ldg(reinterpret_cast<const float4*>(p.bias + col));
+            const float al = p.alpha;
 #pragma unroll
-          for (int k = 0; k < 8; ++k) {
-            float4 o = v[k];
-            const float bm = (p.bias && p.bias_along_m) ? bias_m[k] : 0.f;
-            o.x = fmaf(o.x, p.alpha, bn.x + bm); o.y = fmaf(o.y, p.alpha, bn.y + bm);
-            o.z = fmaf(o.z, p.alpha, bn.z + bm); o.w = fmaf(o.w, p.alpha, bn.w + bm);
-            if (p.act == ACT_GELU) { o.x = gelu_fast(o.x); o.y = gelu_fast(o.y); o.z = gelu_fast(o.z); o.w = gelu_fast(o.w); }
-            else if (p.act == ACT_RELU) { o.x = fmaxf(o.x, 0.f); o.y = fmaxf(o.y, 0.f); o.z = fmaxf(o.z, 0.f); o.w = fmaxf(o.w, 0.f); }
-            if (p.gamma) { o.x *= gm.x; o.y *= gm.y; o.z *= gm.z; o.w *= gm.w; }
-            if (has_res) { o.x += res[k].x; o.y += res[k].y; o.z += res[k].z; o.w += res[k].w; }
-            v[k] = o;
+            for (int k = 0; k < 8; ++k) {
+              v[k].x = fmaf(v[k].x, al, bn.x + bias_m[k]); v[k].y = fmaf(v[k].y, al, bn.y + bias_m[k]);
+              v[k].z = fmaf(v[k].z, al, bn.z + bias_m[k]); v[k].w = fmaf(v[k].w, al, bn.w + bias_m[k]);
+            }
           }
-          if (has_res && c + 2 < NCHUNK) load_res(c + 2);   // next chunk's residual in flight during the stores
+          if (p.act == ACT_GELU) {
 #pragma unroll
-          for (int k = 0; k < 8; ++k) {
-            const int row = row0 + 4 * k;
-            if (row < p.M) {
-              const long off = (long)b * p.c_batch_stride + (long)row * p.ldc + col;
-              if (p.out_f32) *reinterpret_cast<float4*>(p.out_f32 + off) = v[k];
-              if (p.out_bf16) {
-                uint2 pk;
-                pk.x = pack_bf16x2(v[k].x, v[k].y); pk.y = pack_bf16x2(v[k].z, v[k].w);
-                *reinterpret_cast<uint2*>(p.out_bf16 + off) = pk;
-              }
+            for (int k = 0; k < 8; ++k) {
+              v[k].x = gelu_fast(v[k].x); v[k].y = gelu_fast(v[k].y); v[k].z = gelu_fast(v[k].z); v[k].w = gelu_fast(v[k].w);
+            }
+          } else if (p.act == ACT_RELU) {
+#pragma unroll
+            for (int k = 0; k < 8; ++k) {
+              v[k].x = fmaxf(v[k].x, 0.f); v[k].y = fmaxf(v[k].y, 0.f); v[k].z = fmaxf(v[k].z, 0.f); v[k].w = fmaxf(v[k].w, 0.f);
+            }
+          }
+          if (p.gamma) {
+            const float4 gm = __ldg(reinterpret_cast<const float4*>(p.gamma + col));
+#pragma unroll
+            for (int k = 0; k < 8; ++k) { v[k].x *= gm.x; v[k].y *= gm.y; v[k].z *= gm.z; v[k].w *= gm.w; }
+          }
+          if (has_res) {
+#pragma unroll
+            for (int k = 0; k < 8; ++k) { v[k].x += res[k].x; v[k].y += res[k].y; v[k].z += res[k].z; v[k].w += res[k].w; }
+            if (c + 2 < NCHUNK) load_res(c + 2);   // next chunk's residual in flight during the stores
+          }
+          if (p.out_f32) {
+            float* op = p.out_f32 + out_off0 + c * 32;
+#pragma unroll
+            for (int k = 0; k < 8; ++k) {
+              if ((row_mask >> k) & 1) st_global_f4(op, v[k]);
+              op += row_step_c;
+            }
+          }
+          if (p.out_bf16) {
+            bf16* op = p.out_bf16 + out_off0 + c * 32;
+#pragma unroll
+            for (int k = 0; k < 8; ++k) {
+              if ((row_mask >> k) & 1) st_global_u2(op, pack_bf16x2(v[k].x, v[k].y), pack_bf16x2(v[k].z, v[k].w));
+              op += row_step_c;
             }
           }
         } else {
@@ -255,29 +290,29 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid
 #pragma unroll
             for (int k = 0; k < 8; ++k) {
               const int row = row0 + 4 * k;
-              if (row >= p.M) continue;
-              const float vv[4] = {v[k].x, v[k].y, v[k].z, v[k].w};
-              for (int e = 0; e < 4 && col + e < p.N; ++e) {
-                float o = vv[e] * p.alpha;
-                if (p.bias) o += p.bias_along_m ? bias_m[k] : __ldg(p.bias + col + e);
-                if (p.act == ACT_GELU) o = gelu_fast(o); else if (p.act == ACT_RELU) o = fmaxf(o, 0.f);
-                if (p.gamma) o *= __ldg(p.gamma + col + e);
-                if (has_res) {
-                  const int rr = p.res_row_mod ? (row % p.res_row_mod) : row;
-                  o += res_base[(long)rr * p.ld_res + col + e];
+              if (row < p.M) {
+#pragma unroll
+                for (int e = 0; e < 4; ++e) {
+                  if (col + e < p.N) {
+                    float o = (e == 0 ? v[k].x : e == 1 ? v[k].y : e == 2 ? v[k].z : v[k].w) * p.alpha;
+                    if (p.bias) o += p.bias_along_m ? __ldg(p.bias + row) : __ldg(p.bias + col + e);
+                    if (p.act == ACT_GELU) o = gelu_fast(o); else if (p.act == ACT_RELU) o = fmaxf(o, 0.f);
+                    if (p.gamma) o *= __ldg(p.gamma + col + e);
+                    if (has_res) o += res_ptr0[c * 32 + (long)k * row_step_r + e];
+                    const long off = out_off0 + c * 32 + (long)k * row_step_c + e;
+                    if (p.out_f32) p.out_f32[off] = o;
+                    if (p.out_bf16) p.out_bf16[off] = __float2bfloat16(o);
+                  }
                 }
-                const long off = (long)b * p.c_batch_stride + (long)row * p.ldc + col + e;
-                if (p.out_f32) p.out_f32[off] = o;
-                if (p.out_bf16) p.out_bf16[off] = __float2bfloat16(o);
               }
             }
           }
           if (has_res && c + 2 < NCHUNK) load_res(c + 2);
         }
       }
-      tc_fence_before();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(&tmem_empty[acc]);
+      if (half >= NCHUNK) {   // BN = 32: the second warp of each quarter has no chunk but still owes its arrival
+        if (lane == 0) mbar_arrive(&tmem_empty[acc]);
+      }
     }
   }
 
@@ -373,7 +408,7 @@ static int pick_bn(const GemmArgs& a) {
     const long tiles = tiles_m * ((a.N + bn - 1) / bn) * a.batch;
     const long waves = (tiles + num_sms() - 1) / num_sms();
     // per-tile cost ~ MMA time (prop. to BN) + fixed per-tile overhead (epilogue drain, barriers)
-    const double cost = (double)waves * (bn + 24.0);
+    const double cost = (double)waves * (bn + 64.0);
     if (cost < best - 1e-9) { best = cost; best_bn = bn; }
   }
   return best_bn;
@@ -386,6 +421,10 @@ int gemm_bf16(const GemmArgs& a, cudaStream_t stream) {
       (a.out_bf16 && (a.ldc % 8 || (reinterpret_cast<uintptr_t>(a.out_bf16) & 15))) ||
       (a.residual && (a.ld_res % 4 || (reinterpret_cast<uintptr_t>(a.residual) & 15)))) {
     set_error("gemm: output/residual leading dimension or pointer not vector aligned (ldc=%ld ld_res=%ld)", a.ldc, a.ld_res);
+    return 1;
+  }
+  if (a.residual && a.res_row_mod && (a.res_row_mod % BM)) {
+    set_error("gemm: res_row_mod=%d must be a multiple of %d", a.res_row_mod, BM);
     return 1;
   }
   const int bn = a.force_bn ? a.force_bn : pick_bn(a);
