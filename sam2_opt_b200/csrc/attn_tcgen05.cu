@@ -1,0 +1,421 @@
+// K3: flash attention for Hiera's head_dim-72 MultiScaleAttention on the 5th-gen tensor cores (tcgen05 / TMEM / TMA).
+// Covers the blocks that carry almost all of the trunk's attention FLOPs: the 16x16-window blocks of stage 3
+// (256 queries x 256 keys per window) and the three global blocks 23/33/43 (4096 x 4096 per head).
+// Reference: MultiScaleAttention.forward (hieradet.py:56-81) + window_partition/unpartition
+// (backbones/utils.py:16-60), i.e. softmax(q k^T / sqrt(72)) v per (window, head).
+//
+// One persistent CTA works on units of 256 queries (one 16x16 window, or 4 rows of the 64x64 grid in global mode) of
+// one (image, head), as two 128-row Q tiles that ping-pong on the tensor core:
+//   warp 0      TMA producer: Q / K / V tiles are gathered straight out of the packed qkv tensor [B,H,W,3,heads,72]
+//               by 5-D tensor maps (d, section*heads+head, x, y, b); window partition = box coordinates.  head_dim 72
+//               is split 64 + 16: a 128 B-swizzled tile of d 0..63 and a 32 B-swizzled tile of d 64..79 whose last
+//               8 columns are out of bounds of the d axis and therefore zero-filled by TMA.
+//   warp 1      MMA issuer (one thread): S_t = Q_t K^T (M128 N128, 5 k-steps) into TMEM, then O_t = P_t V
+//               (V consumed as an MN-major B operand, N = 64 + 16) into TMEM.
+//   warps 4-7   softmax warpgroup of Q tile 0, warps 8-11 of Q tile 1: thread = query row (tcgen05.ld 32x32b),
+//               fp32 online softmax, P written as bf16 into a 128B-swizzled K-major smem tile (A operand of P V),
+//               per-tile O partials accumulated in registers with the running rescale (no TMEM correction pass).
+#include <cstdio>
+#include <mutex>
+
+#include "common.cuh"
+#include "ops.h"
+
+namespace sam2b {
+
+namespace fa {
+static constexpr int HD = 72;
+static constexpr int TQ = 128;          // rows per Q tile (UMMA M)
+static constexpr int TK = 128;          // keys per KV tile
+static constexpr int NSTAGE = 2;        // K and V ring depth
+static constexpr int LO_BYTES = 128 * 128;   // [128 rows][64 d] bf16, SW128
+static constexpr int HI_BYTES = 128 * 32;    // [128 rows][16 d] bf16, SW32
+static constexpr int TILE_BYTES = LO_BYTES + HI_BYTES;
+static constexpr int P_BYTES = 128 * 128 * 2;     // [128][128] bf16 as two SW128 sub-tiles
+static constexpr int OFF_Q = 0;                                   // 2 Q tiles
+static constexpr int OFF_K = OFF_Q + 2 * TILE_BYTES;
+static constexpr int OFF_V = OFF_K + NSTAGE * TILE_BYTES;
+static constexpr int OFF_P = OFF_V + NSTAGE * TILE_BYTES;         // 2 P tiles
+static constexpr int OFF_BAR = OFF_P + 2 * P_BYTES;
+static constexpr int SMEM = OFF_BAR + 256 + 1024;
+static constexpr int THREADS = 384;
+// TMEM columns
+static constexpr int COL_S = 0;         // S_t at COL_S + 128 t
+static constexpr int COL_O = 256;       // O_t at COL_O + 80 t
+static constexpr int TMEM_COLS = 512;
+}  // namespace fa
+
+struct FaParams {
+  bf16* out;
+  int B, H, W, heads, ws;
+  int n_kv;            // KV tiles per unit (2 for 16x16 windows, H*W/128 in global mode)
+  int blocks_per_img;  // 256-query blocks per image
+  int nwx;             // windows per grid row (window mode)
+  int rows_per_tile;   // grid rows covered by one 128-token tile = 128 / ws
+  int num_units;
+  float scale_log2;
+};
+
+SAM2B_DEVINL void tma_load_5d(void* smem_dst, const CUtensorMap* map, uint64_t* bar, int c0, int c1, int c2, int c3, int c4) {
+  asm volatile(
+      "cp.async.bulk.tensor.5d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6, %7}], [%2];"
+      ::"r"(smem_u32(smem_dst)), "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2), "r"(c3), "r"(c4)
+      : "memory");
+}
+
+// shared-memory matrix descriptor: start address, leading / stride byte offsets (>>4), version 1, layout type
+// (2 = SWIZZLE_128B, 6 = SWIZZLE_32B).
+SAM2B_DEVINL uint64_t make_desc(uint32_t smem_addr, uint32_t lbo_bytes, uint32_t sbo_bytes, uint32_t layout) {
+  uint64_t d = 0;
+  d |= (uint64_t)((smem_addr >> 4) & 0x3FFF);
+  d |= (uint64_t)((lbo_bytes >> 4) & 0x3FFF) << 16;
+  d |= (uint64_t)((sbo_bytes >> 4) & 0x3FFF) << 32;
+  d |= (uint64_t)1 << 46;
+  d |= (uint64_t)layout << 61;
+  return d;
+}
+// instruction descriptor: bf16 x bf16 -> fp32, A K-major, B K-major (b_mn = 0) or MN-major (b_mn = 1)
+SAM2B_DEVINL constexpr uint32_t make_idesc(int m, int n, int b_mn) {
+  return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)b_mn << 16) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(m >> 4) << 24);
+}
+
+struct UnitCoord { int b, head, x0, y0; };
+SAM2B_DEVINL UnitCoord unit_coord(const FaParams& p, int u) {
+  UnitCoord c;
+  const int blk = u % p.blocks_per_img;
+  const int bh = u / p.blocks_per_img;
+  c.head = bh % p.heads;
+  c.b = bh / p.heads;
+  if (p.ws == p.W) { c.x0 = 0; c.y0 = blk * 2 * p.rows_per_tile; }          // global: 256 consecutive tokens
+  else { c.x0 = (blk % p.nwx) * p.ws; c.y0 = (blk / p.nwx) * p.ws; }        // one window
+  return c;
+}
+
+__global__ void __launch_bounds__(fa::THREADS, 1)
+flash_attn_hd72_tcgen05_kernel(const __grid_constant__ CUtensorMap map_lo, const __grid_constant__ CUtensorMap map_hi,
+                               const FaParams p) {
+  using namespace fa;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + OFF_BAR);
+  uint64_t* q_full = bars + 0;
+  uint64_t* q_empty = bars + 1;
+  uint64_t* k_full = bars + 2;              // [NSTAGE]
+  uint64_t* k_empty = k_full + NSTAGE;
+  uint64_t* v_full = k_empty + NSTAGE;
+  uint64_t* v_empty = v_full + NSTAGE;
+  uint64_t* s_full = v_empty + NSTAGE;      // [2]
+  uint64_t* s_free = s_full + 2;
+  uint64_t* p_full = s_free + 2;
+  uint64_t* o_full = p_full + 2;
+  uint64_t* o_free = o_full + 2;
+  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(o_free + 2);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&map_lo);
+    tma_prefetch_desc(&map_hi);
+  }
+  if (warp == 1 && lane == 0) {
+    mbar_init(q_full, 1); mbar_init(q_empty, 1);
+    for (int i = 0; i < NSTAGE; ++i) { mbar_init(&k_full[i], 1); mbar_init(&k_empty[i], 1); mbar_init(&v_full[i], 1); mbar_init(&v_empty[i], 1); }
+    for (int t = 0; t < 2; ++t) {
+      mbar_init(&s_full[t], 1); mbar_init(&s_free[t], 4); mbar_init(&p_full[t], 4);
+      mbar_init(&o_full[t], 1); mbar_init(&o_free[t], 4);
+    }
+    fence_barrier_init();
+  }
+  if (warp == 2) {
+    tmem_alloc(tmem_ptr, TMEM_COLS);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_ptr;
+
+  if (warp == 0) {
+    // ===================== TMA producer =====================
+    if (lane == 0) {
+      int it = 0, nu = 0;
+      for (int u = blockIdx.x; u < p.num_units; u += gridDim.x, ++nu) {
+        const UnitCoord c = unit_coord(p, u);
+        mbar_wait(q_empty, (nu & 1) ^ 1);
+        mbar_arrive_expect_tx(q_full, 2 * TILE_BYTES);
+#pragma unroll
+        for (int t = 0; t < 2; ++t) {
+          uint8_t* q = smem + OFF_Q + t * TILE_BYTES;
+          tma_load_5d(q, &map_lo, q_full, 0, c.head, c.x0, c.y0 + t * p.rows_per_tile, c.b);
+          tma_load_5d(q + LO_BYTES, &map_hi, q_full, 64, c.head, c.x0, c.y0 + t * p.rows_per_tile, c.b);
+        }
+        const bool global = p.ws == p.W;
+        for (int j = 0; j < p.n_kv; ++j, ++it) {
+          const int st = it % NSTAGE;
+          const uint32_t ph = (it / NSTAGE) & 1;
+          const int ky = (global ? 0 : c.y0) + j * p.rows_per_tile;
+          uint8_t* k = smem + OFF_K + st * TILE_BYTES;
+          uint8_t* v = smem + OFF_V + st * TILE_BYTES;
+          mbar_wait(&k_empty[st], ph ^ 1);
+          mbar_arrive_expect_tx(&k_full[st], TILE_BYTES);
+          tma_load_5d(k, &map_lo, &k_full[st], 0, p.heads + c.head, c.x0, ky, c.b);
+          tma_load_5d(k + LO_BYTES, &map_hi, &k_full[st], 64, p.heads + c.head, c.x0, ky, c.b);
+          mbar_wait(&v_empty[st], ph ^ 1);
+          mbar_arrive_expect_tx(&v_full[st], TILE_BYTES);
+          tma_load_5d(v, &map_lo, &v_full[st], 0, 2 * p.heads + c.head, c.x0, ky, c.b);
+          tma_load_5d(v + LO_BYTES, &map_hi, &v_full[st], 64, 2 * p.heads + c.head, c.x0, ky, c.b);
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===================== MMA issuer (one thread) =====================
+    if (lane == 0) {
+      constexpr uint32_t idesc_qk = make_idesc(128, 128, 0);
+      constexpr uint32_t idesc_pv_lo = make_idesc(128, 64, 1);
+      constexpr uint32_t idesc_pv_hi = make_idesc(128, 16, 1);
+      const uint32_t sbase = smem_u32(smem);
+      uint32_t n_s[2] = {0, 0};     // QK^T products issued on S_t
+      uint32_t n_o[2] = {0, 0};     // P V products issued on O_t
+      int it = 0, nu = 0;
+      auto issue_qk = [&](int t, int st) {
+        mbar_wait(&s_free[t], (n_s[t] & 1) ^ 1);
+        tc_fence_after();
+        const uint32_t q = sbase + OFF_Q + t * TILE_BYTES, k = sbase + OFF_K + st * TILE_BYTES;
+        const uint32_t d = tmem_base + COL_S + 128 * t;
+#pragma unroll
+        for (int ks = 0; ks < 4; ++ks)
+          umma_bf16(d, make_desc(q + 32 * ks, 16, 1024, 2), make_desc(k + 32 * ks, 16, 1024, 2), idesc_qk, ks != 0);
+        umma_bf16(d, make_desc(q + LO_BYTES, 16, 256, 6), make_desc(k + LO_BYTES, 16, 256, 6), idesc_qk, 1);
+        umma_commit(&s_full[t]);
+        ++n_s[t];
+      };
+      auto issue_pv = [&](int t, int st) {
+        mbar_wait(&p_full[t], n_o[t] & 1);
+        mbar_wait(&o_free[t], (n_o[t] & 1) ^ 1);
+        tc_fence_after();
+        const uint32_t pa = sbase + OFF_P + t * P_BYTES, v = sbase + OFF_V + st * TILE_BYTES;
+        const uint32_t d = tmem_base + COL_O + 80 * t;
+#pragma unroll
+        for (int ks = 0; ks < 8; ++ks) {
+          // A: P[128][16 keys of k-step ks] (K-major, sub-tile ks/4); B: V rows 16ks..16ks+15 (MN-major: d contiguous)
+          const uint64_t da = make_desc(pa + (ks >> 2) * 16384 + (ks & 3) * 32, 16, 1024, 2);
+          umma_bf16(d, da, make_desc(v + ks * 2048, 1024, 1024, 2), idesc_pv_lo, ks != 0);
+          umma_bf16(d + 64, da, make_desc(v + LO_BYTES + ks * 512, 256, 256, 6), idesc_pv_hi, ks != 0);
+        }
+        umma_commit(&o_full[t]);
+        ++n_o[t];
+      };
+      for (int u = blockIdx.x; u < p.num_units; u += gridDim.x, ++nu) {
+        mbar_wait(q_full, nu & 1);
+        tc_fence_after();
+        {
+          const int st = it % NSTAGE;
+          mbar_wait(&k_full[st], (it / NSTAGE) & 1);
+          tc_fence_after();
+          issue_qk(0, st);
+          issue_qk(1, st);
+          umma_commit(&k_empty[st]);
+          if (p.n_kv == 1) umma_commit(q_empty);
+        }
+        for (int j = 0; j < p.n_kv; ++j, ++it) {
+          const int st = it % NSTAGE;
+          const int st1 = (it + 1) % NSTAGE;
+          mbar_wait(&v_full[st], (it / NSTAGE) & 1);
+          tc_fence_after();
+          const bool more = j + 1 < p.n_kv;
+          if (more) { mbar_wait(&k_full[st1], ((it + 1) / NSTAGE) & 1); tc_fence_after(); }
+#pragma unroll
+          for (int t = 0; t < 2; ++t) {
+            issue_pv(t, st);
+            if (t == 1) umma_commit(&v_empty[st]);
+            if (more) {
+              issue_qk(t, st1);
+              if (t == 1) {
+                umma_commit(&k_empty[st1]);
+                if (j + 2 == p.n_kv) umma_commit(q_empty);
+              }
+            }
+          }
+        }
+      }
+    }
+  } else if (warp >= 4) {
+    // ===================== softmax warpgroups (thread = query row) =====================
+    const int t = (warp - 4) >> 2;            // Q tile of this warpgroup
+    const int wq = warp & 3;                  // TMEM lane quarter
+    const int r = wq * 32 + lane;             // row inside the Q tile
+    const uint32_t lane_sel = (uint32_t)(wq * 32) << 16;
+    const uint32_t ts = tmem_base + COL_S + 128 * t + lane_sel;
+    const uint32_t to = tmem_base + COL_O + 80 * t + lane_sel;
+    const uint32_t p_row = smem_u32(smem + OFF_P + t * P_BYTES) + r * 128;
+    const uint32_t p_xor = (uint32_t)(r & 7) << 4;
+    const int C = p.heads * HD;
+    uint32_t n = 0;                           // KV tiles processed by this warpgroup (all units)
+    for (int u = blockIdx.x; u < p.num_units; u += gridDim.x) {
+      const UnitCoord c = unit_coord(p, u);
+      float m_run = -INFINITY, l_run = 0.f, corr_prev = 0.f;
+      float o_acc[HD];
+#pragma unroll
+      for (int i = 0; i < HD; ++i) o_acc[i] = 0.f;
+      auto accumulate_o = [&]() {
+        // O partial of the previous KV tile (relative to the running max after that tile)
+        mbar_wait(&o_full[t], (n - 1) & 1);
+        tc_fence_after();
+        uint32_t a[32], b[32], cc[32];
+        tmem_ld_x32(to, a);
+        tmem_ld_x32(to + 32, b);
+        tmem_ld_x16(to + 64, cc);
+        tmem_ld_wait();
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&o_free[t]);
+#pragma unroll
+        for (int i = 0; i < 32; ++i) o_acc[i] = fmaf(o_acc[i], corr_prev, __uint_as_float(a[i]));
+#pragma unroll
+        for (int i = 0; i < 32; ++i) o_acc[32 + i] = fmaf(o_acc[32 + i], corr_prev, __uint_as_float(b[i]));
+#pragma unroll
+        for (int i = 0; i < 8; ++i) o_acc[64 + i] = fmaf(o_acc[64 + i], corr_prev, __uint_as_float(cc[i]));
+      };
+      for (int j = 0; j < p.n_kv; ++j, ++n) {
+        mbar_wait(&s_full[t], n & 1);
+        tc_fence_after();
+        // pass 1: row max of the 128 scores
+        float mx = -INFINITY;
+#pragma unroll
+        for (int ch = 0; ch < 4; ++ch) {
+          uint32_t s[32];
+          tmem_ld_x32(ts + 32 * ch, s);
+          tmem_ld_wait();
+#pragma unroll
+          for (int i = 0; i < 32; ++i) mx = fmaxf(mx, __uint_as_float(s[i]));
+        }
+        const float m_new = fmaxf(m_run, mx * p.scale_log2);
+        const float corr = exp2f(m_run - m_new);
+        if (j > 0) accumulate_o();
+        // pass 2: P = exp2(S * scale - m) -> bf16 -> swizzled K-major smem tile; fp32 row sum
+        float rs = 0.f;
+#pragma unroll
+        for (int ch = 0; ch < 4; ++ch) {
+          uint32_t s[32];
+          tmem_ld_x32(ts + 32 * ch, s);
+          tmem_ld_wait();
+          if (ch == 3) {
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&s_free[t]);   // S_t is in registers: the next Q K^T may overwrite it
+          }
+          uint32_t pk[16];
+#pragma unroll
+          for (int i = 0; i < 16; ++i) {
+            const float e0 = exp2f(fmaf(__uint_as_float(s[2 * i]), p.scale_log2, -m_new));
+            const float e1 = exp2f(fmaf(__uint_as_float(s[2 * i + 1]), p.scale_log2, -m_new));
+            rs += e0 + e1;
+            pk[i] = pack_bf16x2(e0, e1);
+          }
+          // 32 keys = 64 B = 16 B chunks (ch & 1) * 4 + i of sub-tile ch >> 1, XOR-swizzled by (row & 7)
+          const uint32_t base = p_row + (ch >> 1) * 16384;
+#pragma unroll
+          for (int i = 0; i < 4; ++i)
+            st_shared_u4(base + (((uint32_t)((ch & 1) * 4 + i) << 4) ^ p_xor), pk[4 * i], pk[4 * i + 1], pk[4 * i + 2], pk[4 * i + 3]);
+        }
+        l_run = fmaf(l_run, corr, rs);
+        m_run = m_new;
+        corr_prev = corr;
+        fence_proxy_async_smem();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&p_full[t]);
+      }
+      accumulate_o();
+      // ---- O / l -> bf16 -> out[token][head*72 ..] ----
+      const float inv = 1.0f / l_run;
+      const int rr = t * TQ + r;
+      const int y = c.y0 + rr / p.ws, x = c.x0 + rr % p.ws;
+      bf16* op = p.out + (((long)c.b * p.H + y) * p.W + x) * C + c.head * HD;
+#pragma unroll
+      for (int i = 0; i < 9; ++i) {
+        uint4 v;
+        v.x = pack_bf16x2(o_acc[8 * i] * inv, o_acc[8 * i + 1] * inv);
+        v.y = pack_bf16x2(o_acc[8 * i + 2] * inv, o_acc[8 * i + 3] * inv);
+        v.z = pack_bf16x2(o_acc[8 * i + 4] * inv, o_acc[8 * i + 5] * inv);
+        v.w = pack_bf16x2(o_acc[8 * i + 6] * inv, o_acc[8 * i + 7] * inv);
+        *reinterpret_cast<uint4*>(op + 8 * i) = v;
+      }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, fa::TMEM_COLS);
+  }
+}
+
+// ------------------------------------------------------------------------------------------
+// host side
+// ------------------------------------------------------------------------------------------
+typedef CUresult (*EncodeTiledFn5)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                   const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                   CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static EncodeTiledFn5 fa_encode_fn() {
+  static EncodeTiledFn5 fn = nullptr;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    void* f = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &f, cudaEnableDefault, &q) == cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiledFn5>(f);
+  });
+  return fn;
+}
+
+bool flash_attention_hd72_supported(int H, int W, int ws, int q_pool) {
+  if (q_pool || H != W || (H * W) % 256) return false;
+  if (ws == W) return W <= 128 && 128 % W == 0 && H % (256 / W) == 0;   // global: a tile = 128 / W full grid rows
+  return ws == 16 && H % 16 == 0;
+}
+
+int flash_attention_hd72(const bf16* qkv, bf16* out, int B, int H, int W, int heads, int ws, cudaStream_t stream) {
+  using namespace fa;
+  if (!flash_attention_hd72_supported(H, W, ws, 0)) { set_error("flash_attention_hd72: unsupported H=%d W=%d ws=%d", H, W, ws); return 1; }
+  EncodeTiledFn5 enc = fa_encode_fn();
+  if (!enc) { set_error("cuTensorMapEncodeTiled entry point not available"); return 1; }
+  const long C = (long)heads * HD;
+  CUtensorMap maps[2];
+  const cuuint64_t dims[5] = {(cuuint64_t)HD, (cuuint64_t)(3 * heads), (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)B};
+  const cuuint64_t strides[4] = {(cuuint64_t)HD * 2, (cuuint64_t)(3 * C * 2), (cuuint64_t)W * 3 * C * 2, (cuuint64_t)H * W * 3 * C * 2};
+  const cuuint32_t estr[5] = {1, 1, 1, 1, 1};
+  for (int i = 0; i < 2; ++i) {
+    const cuuint32_t box[5] = {(cuuint32_t)(i == 0 ? 64 : 16), 1, (cuuint32_t)ws, (cuuint32_t)(128 / ws), 1};
+    CUresult r = enc(&maps[i], CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 5, const_cast<bf16*>(qkv), dims, strides, box, estr,
+                     CU_TENSOR_MAP_INTERLEAVE_NONE, i == 0 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_32B,
+                     CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) { set_error("flash_attention_hd72: cuTensorMapEncodeTiled failed (%d) map %d", (int)r, i); return 1; }
+  }
+  static bool attr = false;
+  if (!attr) {
+    cudaError_t e = cudaFuncSetAttribute(flash_attn_hd72_tcgen05_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM);
+    if (e != cudaSuccess) { set_error("cudaFuncSetAttribute(flash_attn): %s", cudaGetErrorString(e)); return 1; }
+    attr = true;
+  }
+  FaParams p;
+  p.out = out; p.B = B; p.H = H; p.W = W; p.heads = heads; p.ws = ws;
+  p.rows_per_tile = 128 / ws;
+  p.n_kv = ws == W ? H * W / 128 : 2;
+  p.blocks_per_img = H * W / 256;
+  p.nwx = W / ws;
+  p.num_units = B * heads * p.blocks_per_img;
+  p.scale_log2 = 1.4426950408889634f / sqrtf((float)HD);
+  const int grid = p.num_units < num_sms() ? p.num_units : num_sms();
+  char nm[96];
+  if (g_prof_on) snprintf(nm, sizeof(nm), "attn h%d heads%d ws%d pool0 b%d tc", H, heads, ws, B);
+  const double nq = (double)B * H * W * heads;
+  ProfRange pr(stream, nm, 4.0 * nq * (ws == W ? H * W : 256) * HD, (double)B * H * W * 4 * C * 2.0);
+  flash_attn_hd72_tcgen05_kernel<<<grid, THREADS, SMEM, stream>>>(maps[0], maps[1], p);
+  SAM2B_CHECK_LAUNCH("flash_attn_hd72_tcgen05");
+  return 0;
+}
+
+}  // namespace sam2b

@@ -72,6 +72,10 @@ int upsample2x_add_nchw(float* dst, const float* src, int B, int C, int H, int W
 int window_attention_hd72(const bf16* qkv, bf16* out, int B, int H, int W, int heads, int ws, int q_pool,
                           cudaStream_t stream);
 
+// tcgen05 flash kernel for the 16x16-window and global (ws == W) blocks; same tensor contract as above, no q-pool.
+bool flash_attention_hd72_supported(int H, int W, int ws, int q_pool);
+int flash_attention_hd72(const bf16* qkv, bf16* out, int B, int H, int W, int heads, int ws, cudaStream_t stream);
+
 // Row softmax over fp32 scores -> bf16 probabilities (row stride lds / ldp elements), `cols` valid columns;
 // columns in [cols, ldp) are written as zero.
 int softmax_rows(const float* s, long lds, bf16* p, long ldp, long rows, int cols, cudaStream_t stream);

@@ -11,6 +11,7 @@
 // This legacy-tensor-path kernel carries ~11 % of the encoder's FLOPs; the tcgen05 flash kernel for the three
 // global blocks is the planned replacement.
 #include <cstdio>
+#include <cstdlib>
 
 #include "common.cuh"
 #include "ops.h"
@@ -255,6 +256,8 @@ __global__ void __launch_bounds__(ATT_THREADS) window_attn_hd72_kernel(const Att
 
 int window_attention_hd72(const bf16* qkv, bf16* out, int B, int H, int W, int heads, int ws, int q_pool, cudaStream_t stream) {
   if (ws <= 0 || H % ws || W % ws || (q_pool && (ws & 1))) { set_error("window_attention: bad window %d for %dx%d", ws, H, W); return 1; }
+  // 16x16 windows and global attention run on the tcgen05 flash kernel (attn_tcgen05.cu)
+  if (flash_attention_hd72_supported(H, W, ws, q_pool) && !getenv("SAM2B_LEGACY_ATTN")) return flash_attention_hd72(qkv, out, B, H, W, heads, ws, stream);
   AttnParams p;
   p.qkv = qkv; p.out = out; p.B = B; p.H = H; p.W = W; p.heads = heads; p.ws = ws; p.q_pool = q_pool;
   p.KW = ws * ws; p.QW = q_pool ? p.KW / 4 : p.KW; p.nwx = W / ws;
