@@ -4,6 +4,7 @@
 // (sam2_base_official.py:571-577); MemoryAttention (memory_attention.py:299-349); MemoryEncoder (memory_encoder.py:233-241).
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <map>
 #include <string>
@@ -533,7 +534,18 @@ static int memory_encode_mb(sam2b_engine* e, const float* pix_feat, const float*
   return 0;
 }
 
-static const int kMaxMicroBatch = 16;
+static const int kMaxMicroBatchCap = 16;   // staging buffers of the host path are sized for this
+// images per pass through the trunk (SAM2B_MICROBATCH overrides; smaller keeps producer->consumer tensors in the 126 MB L2)
+static int max_micro_batch() {
+  static int v = 0;
+  if (!v) {
+    const char* e = getenv("SAM2B_MICROBATCH");
+    v = e ? atoi(e) : 16;
+    if (v < 1) v = 1;
+    if (v > kMaxMicroBatchCap) v = kMaxMicroBatchCap;
+  }
+  return v;
+}
 
 }  // namespace sam2b
 
@@ -607,6 +619,7 @@ int sam2b_image_encode(sam2b_handle h, const float* img, int n, int normalised, 
   if (n <= 0 || !img || !fpn0 || !fpn1 || !fpn2) { set_error("sam2b_image_encode: bad arguments (n=%d)", n); return 1; }
   CUDA_OK(cudaSetDevice(h->device));
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  const int kMaxMicroBatch = max_micro_batch();
   for (int i0 = 0; i0 < n; i0 += kMaxMicroBatch) {
     const int mb = (n - i0) < kMaxMicroBatch ? (n - i0) : kMaxMicroBatch;
     TRY(image_encode_mb(h, img + (size_t)i0 * 3 * 1024 * 1024, mb, normalised, add_no_mem_embed,
@@ -623,6 +636,7 @@ int sam2b_image_encode_host(sam2b_handle h, const float* img_host, int n, int no
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   // double-buffered staging: copies run on copy_stream, compute on `st`
   const size_t in_sz = (size_t)3 * 1024 * 1024, o0 = (size_t)32 * 65536, o1 = (size_t)64 * 16384, o2 = (size_t)256 * 4096;
+  const int kMaxMicroBatch = max_micro_batch();
   float *in[2], *f0[2], *f1[2], *f2[2];
   const char* names[2][4] = {{"h_in0", "h_f00", "h_f10", "h_f20"}, {"h_in1", "h_f01", "h_f11", "h_f21"}};
   for (int s = 0; s < 2; ++s) {
@@ -674,6 +688,7 @@ int sam2b_memory_encode(sam2b_handle h, const float* pix_feat, const float* mask
   if (!pix_feat || !masks || !out_x || n <= 0) { set_error("sam2b_memory_encode: null/empty argument"); return 1; }
   CUDA_OK(cudaSetDevice(h->device));
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  const int kMaxMicroBatch = kMaxMicroBatchCap;
   for (int i0 = 0; i0 < n; i0 += kMaxMicroBatch) {
     const int mb = (n - i0) < kMaxMicroBatch ? (n - i0) : kMaxMicroBatch;
     TRY(memory_encode_mb(h, pix_feat + (size_t)i0 * 256 * 4096, masks + (size_t)i0 * 1024 * 1024, mb, out_x + (size_t)i0 * 64 * 4096, st));

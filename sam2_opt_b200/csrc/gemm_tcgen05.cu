@@ -10,6 +10,7 @@
 // FpnNeck 1x1 convs + conv_s0/s1 (image_encoder.py:102-134, sam2_base_official.py:571-577), and the
 // memory-attention / memory-encoder linears and score/PV products.
 #include <cstdio>
+#include <cstdlib>
 #include <mutex>
 #include <unordered_map>
 
@@ -39,6 +40,7 @@ struct GemmKernelParams {
   const float* gamma;
   const float* residual; long ld_res; long res_batch_stride; int res_row_mod;
   float* out_f32; bf16* out_bf16; long ldc; long c_batch_stride;
+  int dbg;   // timing experiments only (SAM2B_GEMM_DBG): 1 = skip global stores, 2 = skip the smem transpose
 };
 
 template <int BN>
@@ -212,34 +214,55 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid
 #pragma unroll
         for (int k = 0; k < 8; ++k) bias_m[k] = ((row_mask >> k) & 1) ? __ldg(p.bias + row0 + 4 * k) : 0.f;
       }
+      // bias / gamma of this lane's 4 columns: fetched one chunk ahead so the load latency never sits on the critical path
+      auto load_vec = [&](const float* base, int c, float fill) {
+        const int col = ncol0 + c * 32;
+        float4 v = make_float4(fill, fill, fill, fill);
+        if (base && (c * 32 + lc * 4 < BN) && (col + 4 <= p.N)) v = __ldg(reinterpret_cast<const float4*>(base + col));
+        return v;
+      };
+      float4 bn_next = load_vec(bias_n ? p.bias : nullptr, half, 0.f);
+      float4 gm_next = load_vec(p.gamma, half, 1.f);
       mbar_wait(&tmem_full[acc], acc_phase);
       tc_fence_after();
       const uint32_t taddr = tmem_base + acc * ACC_STRIDE + ((uint32_t)(q * 32) << 16);
+      uint32_t r[32];
+      if (half < NCHUNK) tmem_ld_x32(taddr + half * 32, r);   // columns past BN (last chunk of BN=144) are never stored
 #pragma unroll 1
       for (int c = half; c < NCHUNK; c += 2) {
-        uint32_t r[32];
-        tmem_ld_x32(taddr + c * 32, r);      // columns past BN (last chunk of BN=144) are never stored
         tmem_ld_wait();
-        if (c + 2 >= NCHUNK) {
-          // last chunk of this warp is in registers: hand the accumulator stage back to the MMA warp now
-          tc_fence_before();
-          __syncwarp();
-          if (lane == 0) mbar_arrive(&tmem_empty[acc]);
-        }
+        if (!(p.dbg & 2)) {
 #pragma unroll
         for (int j = 0; j < 8; ++j)
           st_shared_u4(sts_base + (((uint32_t)j << 4) ^ sts_xor), r[4 * j], r[4 * j + 1], r[4 * j + 2], r[4 * j + 3]);
-        __syncwarp();
+        }
         float4 v[8];
+        if (p.dbg & 2) {
+#pragma unroll
+          for (int k = 0; k < 8; ++k) v[k] = make_float4(__uint_as_float(r[4 * k]), __uint_as_float(r[4 * k + 1]), __uint_as_float(r[4 * k + 2]), __uint_as_float(r[4 * k + 3]));
+        }
+        __syncwarp();
+        if (c + 2 < NCHUNK) {
+          tmem_ld_x32(taddr + (c + 2) * 32, r);     // next chunk streams out of TMEM while this one is processed
+        } else {
+          // last chunk of this warp has left TMEM: hand the accumulator stage back to the MMA warp now
+          tc_fence_before();
+          if (lane == 0) mbar_arrive(&tmem_empty[acc]);
+        }
+        const float4 bn = bn_next, gm = gm_next;
+        if (c + 2 < NCHUNK) {
+          bn_next = load_vec(bias_n ? p.bias : nullptr, c + 2, 0.f);
+          gm_next = load_vec(p.gamma, c + 2, 1.f);
+        }
+        if (!(p.dbg & 2)) {
 #pragma unroll
         for (int k = 0; k < 8; ++k) v[k] = ld_shared_f4(((k & 1) ? lds_odd : lds_even) + (k >> 1) * 1024);
+        }
         __syncwarp();
         const int col = ncol0 + c * 32;
         const bool in_tile = c * 32 + lc * 4 < BN;
         if (in_tile && col + 4 <= p.N) {
           {
-            float4 bn = make_float4(0.f, 0.f, 0.f, 0.f);
-            if (bias_n) bn = __ldg(reinterpret_cast<const float4*>(p.bias + col));
             const float al = p.alpha;
 #pragma unroll
             for (int k = 0; k < 8; ++k) {
@@ -259,7 +282,6 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid
             }
           }
           if (p.gamma) {
-            const float4 gm = __ldg(reinterpret_cast<const float4*>(p.gamma + col));
 #pragma unroll
             for (int k = 0; k < 8; ++k) { v[k].x *= gm.x; v[k].y *= gm.y; v[k].z *= gm.z; v[k].w *= gm.w; }
           }
@@ -268,7 +290,9 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid
             for (int k = 0; k < 8; ++k) { v[k].x += res[k].x; v[k].y += res[k].y; v[k].z += res[k].z; v[k].w += res[k].w; }
             if (c + 2 < NCHUNK) load_res(c + 2);   // next chunk's residual in flight during the stores
           }
-          if (p.out_f32) {
+          if (p.dbg & 1) {
+            if (v[0].x + v[1].y + v[2].z + v[3].w + v[4].x + v[5].y + v[6].z + v[7].w == 123.456f) p.out_f32[0] = 0.f;
+          } else if (p.out_f32) {
             float* op = p.out_f32 + out_off0 + c * 32;
 #pragma unroll
             for (int k = 0; k < 8; ++k) {
@@ -276,7 +300,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid
               op += row_step_c;
             }
           }
-          if (p.out_bf16) {
+          if (!(p.dbg & 1) && p.out_bf16) {
             bf16* op = p.out_bf16 + out_off0 + c * 32;
 #pragma unroll
             for (int k = 0; k < 8; ++k) {
@@ -388,6 +412,7 @@ static int launch_gemm(const GemmArgs& a, cudaStream_t stream) {
   p.alpha = a.alpha; p.bias = a.bias; p.bias_along_m = a.bias_along_m; p.act = a.act; p.gamma = a.gamma;
   p.residual = a.residual; p.ld_res = a.ld_res; p.res_batch_stride = a.res_batch_stride; p.res_row_mod = a.res_row_mod;
   p.out_f32 = a.out_f32; p.out_bf16 = a.out_bf16; p.ldc = a.ldc; p.c_batch_stride = a.c_batch_stride;
+  { static int dbg = -1; if (dbg < 0) { const char* e = getenv("SAM2B_GEMM_DBG"); dbg = e ? atoi(e) : 0; } p.dbg = dbg; }
   const long tiles = (long)p.tiles_m * p.tiles_n * p.batch;
   const int grid = (int)(tiles < num_sms() ? tiles : num_sms());
   char nm[96];
