@@ -26,9 +26,8 @@ static constexpr int ACC_STRIDE = 256;   // TMEM columns between the two accumul
 static constexpr int TMEM_COLS = 512;
 static constexpr int NUM_EPI_WARPS = 8;  // two warps per TMEM lane quarter, interleaved over 32-column chunks
 static constexpr int NUM_THREADS = 128 + 32 * NUM_EPI_WARPS;  // warp0 TMA, warp1 MMA, warp2 TMEM alloc, warp3 idle, warps4-11 epilogue
-static constexpr int EPI_STAGE_BYTES = 32 * 32 * 4;           // one 32x32 fp32 transpose buffer per epilogue warp (XOR swizzled)
-static constexpr int EPI_SMEM = NUM_EPI_WARPS * EPI_STAGE_BYTES;
 static constexpr int SMEM_TOTAL = 227 * 1024;
+static constexpr int BAR_BYTES = 512;
 
 struct GemmKernelParams {
   int M, N, K, batch;
@@ -38,9 +37,8 @@ struct GemmKernelParams {
   const float* bias; int bias_along_m;
   int act;
   const float* gamma;
-  const float* residual; long ld_res; long res_batch_stride; int res_row_mod;
-  float* out_f32; bf16* out_bf16; long ldc; long c_batch_stride;
-  int dbg;   // timing experiments only (SAM2B_GEMM_DBG): 1 = skip global stores, 2 = skip the smem transpose
+  int has_res; int res_batched; int res_row_mod;
+  int out_is_bf16;
 };
 
 template <int BN>
@@ -48,9 +46,14 @@ struct GemmCfg {
   static constexpr int STAGE_A = BM * BK * 2;
   static constexpr int STAGE_B = BN * BK * 2;
   static constexpr int STAGE = STAGE_A + STAGE_B;
-  static constexpr int AVAIL = SMEM_TOTAL - EPI_SMEM - 1024 /*align slack*/ - 256 /*barriers*/;
+  // Epilogue staging per warp: 32 rows x 128 B (32 fp32 or, for bf16, 32 rows x 64 B), the box of one TMA store.
+  // BN <= 192 leaves room for two 4 KB buffers per warp (store of chunk i overlaps chunk i+1, residual prefetch);
+  // BN > 192 gets one 4 KB buffer (two 2 KB buffers for bf16 outputs).
+  static constexpr int EPI_WARP_BYTES = BN > 192 ? 4096 : 8192;
+  static constexpr int EPI_SMEM = NUM_EPI_WARPS * EPI_WARP_BYTES;
+  static constexpr int AVAIL = SMEM_TOTAL - EPI_SMEM - 1024 /*align slack*/ - BAR_BYTES;
   static constexpr int STAGES = (AVAIL / STAGE) > 8 ? 8 : (AVAIL / STAGE);
-  static constexpr int SMEM = STAGES * STAGE + EPI_SMEM + 1024 + 256;
+  static constexpr int SMEM = STAGES * STAGE + EPI_SMEM + 1024 + BAR_BYTES;
 };
 
 // Exact-erf GELU, x * Phi(x), evaluated as relu(x) - |x| * h(|x|) with h(t) = Phi(-t) = 2^p(t); p is a degree-6
@@ -72,6 +75,7 @@ SAM2B_DEVINL float gelu_fast(float x) {
 template <int BN>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
 gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b,
+                         const __grid_constant__ CUtensorMap tma_c, const __grid_constant__ CUtensorMap tma_r,
                          const GemmKernelParams p) {
   using Cfg = GemmCfg<BN>;
   constexpr int STAGES = Cfg::STAGES;
@@ -80,12 +84,13 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid
   uint8_t* smem_a = smem;
   uint8_t* smem_b = smem + STAGES * Cfg::STAGE_A;
   uint8_t* smem_epi = smem + STAGES * Cfg::STAGE;
-  uint64_t* bars = reinterpret_cast<uint64_t*>(smem_epi + EPI_SMEM);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem_epi + Cfg::EPI_SMEM);
   uint64_t* full_bar = bars;
   uint64_t* empty_bar = bars + STAGES;
   uint64_t* tmem_full = bars + 2 * STAGES;
   uint64_t* tmem_empty = bars + 2 * STAGES + 2;
-  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bars + 2 * STAGES + 4);
+  uint64_t* res_bar = bars + 2 * STAGES + 4;          // [NUM_EPI_WARPS][2]: residual chunk landed in the staging buffer
+  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(res_bar + 2 * NUM_EPI_WARPS);
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -94,10 +99,13 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tma_a);
     tma_prefetch_desc(&tma_b);
+    tma_prefetch_desc(&tma_c);
+    if (p.has_res) tma_prefetch_desc(&tma_r);
   }
   if (warp == 1 && lane == 0) {
     for (int i = 0; i < STAGES; ++i) { mbar_init(&full_bar[i], 1); mbar_init(&empty_bar[i], 1); }
     for (int i = 0; i < 2; ++i) { mbar_init(&tmem_full[i], 1); mbar_init(&tmem_empty[i], NUM_EPI_WARPS); }
+    for (int i = 0; i < 2 * NUM_EPI_WARPS; ++i) mbar_init(&res_bar[i], 1);
     fence_barrier_init();
   }
   if (warp == 2) {
@@ -155,29 +163,27 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid
       }
     }
   } else if (warp >= 4) {
-    // ===================== epilogue: TMEM -> registers -> smem transpose -> coalesced global =====================
-    // Warp (4+we) may read TMEM lanes 32*(we&3)..+31 (hardware rule: warp id mod 4).  The two warps of a lane quarter
-    // take alternate 32-column chunks.  tcgen05.ld gives thread i row i of the chunk; the XOR-swizzled staging buffer
-    // turns that into "8 lanes x float4 = one 128 B row segment", so every global load/store instruction of the warp
-    // covers 4 full 128 B lines (fp32) instead of 32 scattered 16 B pieces.  Every epilogue option is a warp-uniform
-    // branch taken once per 32x32 chunk (not per element), and addresses advance by precomputed strides.
+    // ===================== epilogue: TMEM -> registers -> swizzled smem row -> TMA store =====================
+    // Warp (4+we) may read TMEM lanes 32*(we&3)..+31 (hardware rule: warp id mod 4); the two warps of a lane quarter
+    // take alternate 32-column chunks.  tcgen05.ld 32x32b gives thread i row i of the chunk, which it finishes in
+    // registers (alpha, bias, GELU/ReLU, gamma, + fp32 residual that TMA dropped into the same staging buffer) and
+    // writes as one swizzled row of the staging box; one lane then issues cp.async.bulk.tensor (smem -> global), which
+    // also clips ragged M / N edges.  No per-thread global loads/stores, no transposition pass.
     const int we = warp - 4;
     const int q = we & 3;
     const int half = we >> 2;
-    const uint32_t stg_base = smem_u32(smem_epi + we * EPI_STAGE_BYTES);
-    const int lr = lane >> 3;            // row inside a group of 4 rows (transposed layout)
-    const int lc = lane & 7;             // float4 column inside the 32-column chunk
-    const uint32_t sts_base = stg_base + lane * 128;                       // row `lane`, slot j ^ (lane & 7)
-    const uint32_t sts_xor = (uint32_t)(lane & 7) << 4;
-    // transposed read: row rl = 4k + lr, slot lc ^ (rl & 7); (4k + lr) & 7 = lr + 4 (k & 1)
-    const uint32_t lds_even = stg_base + lr * 128 + ((uint32_t)(lc ^ lr) << 4);          // k even
-    const uint32_t lds_odd = stg_base + (lr + 4) * 128 + ((uint32_t)(lc ^ (lr + 4)) << 4);  // k odd
-    constexpr int NCHUNK = (BN + 31) / 32;
-    const bool has_res = p.residual != nullptr;
+    constexpr int NCHUNK = BN / 32;
+    constexpr int WB = Cfg::EPI_WARP_BYTES;
+    const bool bf = p.out_is_bf16 != 0;
+    const bool has_res = p.has_res != 0;
     const bool bias_n = p.bias != nullptr && !p.bias_along_m;
-    const bool bias_m_on = p.bias != nullptr && p.bias_along_m;
-    const long row_step_c = 4 * p.ldc;       // elements between this lane's consecutive rows
-    const long row_step_r = 4 * p.ld_res;
+    const uint32_t buf_bytes = bf ? 2048u : 4096u;
+    const bool two_buf = bf || WB >= 8192;
+    const uint32_t buf_base = smem_u32(smem_epi + we * WB);
+    uint64_t* my_res_bar = res_bar + 2 * we;
+    const uint32_t row_f32 = (uint32_t)lane * 128, xor_f32 = (uint32_t)(lane & 7) << 4;
+    const uint32_t row_b16 = (uint32_t)lane * 64, xor_b16 = (uint32_t)((lane >> 1) & 3) << 4;
+    uint32_t i = 0;                       // live chunks processed by this warp: buffer = i & 1 (two_buf), res phase
     int local = 0;
     for (int t = blockIdx.x; t < num_tiles; t += gridDim.x, ++local) {
       const int n_blk = t % p.tiles_n;
@@ -185,159 +191,140 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid
       const int b = t / (p.tiles_n * p.tiles_m);
       const int acc = local & 1;
       const uint32_t acc_phase = (local >> 1) & 1;
-      const int row0 = m_blk * BM + q * 32 + lr;           // this lane's rows: row0 + 4k
-      const int ncol0 = n_blk * BN + lc * 4;               // this lane's columns in chunk c: ncol0 + 32c .. +3
-      uint32_t row_mask = 0;                               // bit k: row0 + 4k < M
+      const int row_g = m_blk * BM + q * 32;             // first row of this warp's 32-row slab
+      const int n0 = n_blk * BN;
+      const bool rows_live = row_g < p.M;
+      const int res_row = p.res_row_mod ? ((m_blk * BM) % p.res_row_mod) + q * 32 : row_g;
+      const int res_b = p.res_batched ? b : 0;
+      auto issue_res = [&](uint32_t ii, int c) {          // lane 0: residual chunk c -> staging buffer of chunk ii
+        const uint32_t bsel = two_buf ? (ii & 1) : 0;
+        mbar_arrive_expect_tx(&my_res_bar[bsel], 4096);
+        tma_load_3d_addr(buf_base + bsel * buf_bytes, &tma_r, &my_res_bar[bsel], n0 + c * 32, res_row, res_b);
+      };
+      auto load_vec8 = [&](const float* base, int c, float fill, float4 (&o)[8]) {
+        // 32 consecutive per-column values (bias / gamma), same addresses for every lane (L1 broadcast)
 #pragma unroll
-      for (int k = 0; k < 8; ++k) row_mask |= (row0 + 4 * k < p.M) ? (1u << k) : 0u;
-      const long out_off0 = (long)b * p.c_batch_stride + (long)row0 * p.ldc + ncol0;
-      const float* res_ptr0 = nullptr;
-      if (has_res) {
-        // res_row_mod (broadcast of a [mod, N] table over row blocks) must be a multiple of BM: one modulo per tile
-        const int rbase = p.res_row_mod ? ((m_blk * BM) % p.res_row_mod) + q * 32 + lr : row0;
-        res_ptr0 = p.residual + (long)b * p.res_batch_stride + (long)rbase * p.ld_res + ncol0;
-      }
-      float4 res[8];
-      auto load_res = [&](int c) {
-        const bool col_ok = (c * 32 + lc * 4 < BN) && (ncol0 + c * 32 + 4 <= p.N);
-        const float* rp = res_ptr0 + c * 32;
-#pragma unroll
-        for (int k = 0; k < 8; ++k) {
-          res[k] = make_float4(0.f, 0.f, 0.f, 0.f);
-          if (col_ok && ((row_mask >> k) & 1)) res[k] = ld_global_f4(rp);
-          rp += row_step_r;
+        for (int j = 0; j < 8; ++j) {
+          const int col = n0 + c * 32 + 4 * j;
+          o[j] = make_float4(fill, fill, fill, fill);
+          if (base) {
+            if (col + 4 <= p.N) o[j] = __ldg(reinterpret_cast<const float4*>(base + col));
+            else {
+              if (col < p.N) o[j].x = __ldg(base + col);
+              if (col + 1 < p.N) o[j].y = __ldg(base + col + 1);
+              if (col + 2 < p.N) o[j].z = __ldg(base + col + 2);
+            }
+          }
         }
       };
-      if (has_res && half < NCHUNK) load_res(half);       // overlaps the wait for the accumulator
-      float bias_m[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-      if (bias_m_on) {
-#pragma unroll
-        for (int k = 0; k < 8; ++k) bias_m[k] = ((row_mask >> k) & 1) ? __ldg(p.bias + row0 + 4 * k) : 0.f;
+      const bool first_live = rows_live && half < NCHUNK && (n0 + half * 32 < p.N);
+      if (has_res && first_live && lane == 0) {
+        if (two_buf) bulk_wait_read<1>(); else bulk_wait_read<0>();
+        issue_res(i, half);
       }
-      // bias / gamma of this lane's 4 columns: fetched one chunk ahead so the load latency never sits on the critical path
-      auto load_vec = [&](const float* base, int c, float fill) {
-        const int col = ncol0 + c * 32;
-        float4 v = make_float4(fill, fill, fill, fill);
-        if (base && (c * 32 + lc * 4 < BN) && (col + 4 <= p.N)) v = __ldg(reinterpret_cast<const float4*>(base + col));
-        return v;
-      };
-      float4 bn_next = load_vec(bias_n ? p.bias : nullptr, half, 0.f);
-      float4 gm_next = load_vec(p.gamma, half, 1.f);
+      float4 bn_next[8];
+      load_vec8(bias_n ? p.bias : nullptr, half, 0.f, bn_next);
+      const float bias_m = (p.bias && p.bias_along_m && row_g + lane < p.M) ? __ldg(p.bias + row_g + lane) : 0.f;
       mbar_wait(&tmem_full[acc], acc_phase);
       tc_fence_after();
       const uint32_t taddr = tmem_base + acc * ACC_STRIDE + ((uint32_t)(q * 32) << 16);
       uint32_t r[32];
-      if (half < NCHUNK) tmem_ld_x32(taddr + half * 32, r);   // columns past BN (last chunk of BN=144) are never stored
+      if (half < NCHUNK) tmem_ld_x32(taddr + half * 32, r);
 #pragma unroll 1
       for (int c = half; c < NCHUNK; c += 2) {
         tmem_ld_wait();
-        if (!(p.dbg & 2)) {
-#pragma unroll
-        for (int j = 0; j < 8; ++j)
-          st_shared_u4(sts_base + (((uint32_t)j << 4) ^ sts_xor), r[4 * j], r[4 * j + 1], r[4 * j + 2], r[4 * j + 3]);
-        }
-        float4 v[8];
-        if (p.dbg & 2) {
-#pragma unroll
-          for (int k = 0; k < 8; ++k) v[k] = make_float4(__uint_as_float(r[4 * k]), __uint_as_float(r[4 * k + 1]), __uint_as_float(r[4 * k + 2]), __uint_as_float(r[4 * k + 3]));
-        }
-        __syncwarp();
-        if (c + 2 < NCHUNK) {
-          tmem_ld_x32(taddr + (c + 2) * 32, r);     // next chunk streams out of TMEM while this one is processed
-        } else {
+        if (c + 2 >= NCHUNK) {
           // last chunk of this warp has left TMEM: hand the accumulator stage back to the MMA warp now
           tc_fence_before();
+          __syncwarp();
           if (lane == 0) mbar_arrive(&tmem_empty[acc]);
         }
-        const float4 bn = bn_next, gm = gm_next;
-        if (c + 2 < NCHUNK) {
-          bn_next = load_vec(bias_n ? p.bias : nullptr, c + 2, 0.f);
-          gm_next = load_vec(p.gamma, c + 2, 1.f);
-        }
-        if (!(p.dbg & 2)) {
+        const bool live = rows_live && (n0 + c * 32 < p.N);
+        const bool next_live = rows_live && (c + 2 < NCHUNK) && (n0 + (c + 2) * 32 < p.N);
+        if (live) {
+          const uint32_t bsel = two_buf ? (i & 1) : 0;
+          const uint32_t buf = buf_base + bsel * buf_bytes;
+          if (lane == 0) {
+            if (has_res) {
+              if (two_buf) { if (next_live) { bulk_wait_read<0>(); issue_res(i + 1, c + 2); } }
+              else if (c != half) { bulk_wait_read<0>(); issue_res(i, c); }
+            } else {
+              if (two_buf) bulk_wait_read<1>(); else bulk_wait_read<0>();     // staging buffer `bsel` is free again
+            }
+          }
+          __syncwarp();
+          float4 bn[8];
 #pragma unroll
-        for (int k = 0; k < 8; ++k) v[k] = ld_shared_f4(((k & 1) ? lds_odd : lds_even) + (k >> 1) * 1024);
-        }
-        __syncwarp();
-        const int col = ncol0 + c * 32;
-        const bool in_tile = c * 32 + lc * 4 < BN;
-        if (in_tile && col + 4 <= p.N) {
+          for (int j = 0; j < 8; ++j) bn[j] = bn_next[j];
+          if (c + 2 < NCHUNK) load_vec8(bias_n ? p.bias : nullptr, c + 2, 0.f, bn_next);
+          float4 v[8];
           {
             const float al = p.alpha;
 #pragma unroll
-            for (int k = 0; k < 8; ++k) {
-              v[k].x = fmaf(v[k].x, al, bn.x + bias_m[k]); v[k].y = fmaf(v[k].y, al, bn.y + bias_m[k]);
-              v[k].z = fmaf(v[k].z, al, bn.z + bias_m[k]); v[k].w = fmaf(v[k].w, al, bn.w + bias_m[k]);
+            for (int j = 0; j < 8; ++j) {
+              v[j].x = fmaf(__uint_as_float(r[4 * j]), al, bn[j].x + bias_m);
+              v[j].y = fmaf(__uint_as_float(r[4 * j + 1]), al, bn[j].y + bias_m);
+              v[j].z = fmaf(__uint_as_float(r[4 * j + 2]), al, bn[j].z + bias_m);
+              v[j].w = fmaf(__uint_as_float(r[4 * j + 3]), al, bn[j].w + bias_m);
             }
           }
+          if (c + 2 < NCHUNK) tmem_ld_x32(taddr + (c + 2) * 32, r);   // next chunk streams out of TMEM meanwhile
           if (p.act == ACT_GELU) {
 #pragma unroll
-            for (int k = 0; k < 8; ++k) {
-              v[k].x = gelu_fast(v[k].x); v[k].y = gelu_fast(v[k].y); v[k].z = gelu_fast(v[k].z); v[k].w = gelu_fast(v[k].w);
+            for (int j = 0; j < 8; ++j) {
+              v[j].x = gelu_fast(v[j].x); v[j].y = gelu_fast(v[j].y); v[j].z = gelu_fast(v[j].z); v[j].w = gelu_fast(v[j].w);
             }
           } else if (p.act == ACT_RELU) {
 #pragma unroll
-            for (int k = 0; k < 8; ++k) {
-              v[k].x = fmaxf(v[k].x, 0.f); v[k].y = fmaxf(v[k].y, 0.f); v[k].z = fmaxf(v[k].z, 0.f); v[k].w = fmaxf(v[k].w, 0.f);
+            for (int j = 0; j < 8; ++j) {
+              v[j].x = fmaxf(v[j].x, 0.f); v[j].y = fmaxf(v[j].y, 0.f); v[j].z = fmaxf(v[j].z, 0.f); v[j].w = fmaxf(v[j].w, 0.f);
             }
           }
           if (p.gamma) {
+            float4 gm[8];
+            load_vec8(p.gamma, c, 1.f, gm);
 #pragma unroll
-            for (int k = 0; k < 8; ++k) { v[k].x *= gm.x; v[k].y *= gm.y; v[k].z *= gm.z; v[k].w *= gm.w; }
+            for (int j = 0; j < 8; ++j) { v[j].x *= gm[j].x; v[j].y *= gm[j].y; v[j].z *= gm[j].z; v[j].w *= gm[j].w; }
           }
           if (has_res) {
+            mbar_wait(&my_res_bar[bsel], (two_buf ? (i >> 1) : i) & 1);
 #pragma unroll
-            for (int k = 0; k < 8; ++k) { v[k].x += res[k].x; v[k].y += res[k].y; v[k].z += res[k].z; v[k].w += res[k].w; }
-            if (c + 2 < NCHUNK) load_res(c + 2);   // next chunk's residual in flight during the stores
-          }
-          if (p.dbg & 1) {
-            if (v[0].x + v[1].y + v[2].z + v[3].w + v[4].x + v[5].y + v[6].z + v[7].w == 123.456f) p.out_f32[0] = 0.f;
-          } else if (p.out_f32) {
-            float* op = p.out_f32 + out_off0 + c * 32;
-#pragma unroll
-            for (int k = 0; k < 8; ++k) {
-              if ((row_mask >> k) & 1) st_global_f4(op, v[k]);
-              op += row_step_c;
+            for (int j = 0; j < 8; ++j) {
+              const float4 rv = ld_shared_f4(buf + row_f32 + (((uint32_t)j << 4) ^ xor_f32));
+              v[j].x += rv.x; v[j].y += rv.y; v[j].z += rv.z; v[j].w += rv.w;
             }
           }
-          if (!(p.dbg & 1) && p.out_bf16) {
-            bf16* op = p.out_bf16 + out_off0 + c * 32;
+          if (bf) {
 #pragma unroll
-            for (int k = 0; k < 8; ++k) {
-              if ((row_mask >> k) & 1) st_global_u2(op, pack_bf16x2(v[k].x, v[k].y), pack_bf16x2(v[k].z, v[k].w));
-              op += row_step_c;
-            }
+            for (int j = 0; j < 4; ++j)
+              st_shared_u4(buf + row_b16 + (((uint32_t)j << 4) ^ xor_b16), pack_bf16x2(v[2 * j].x, v[2 * j].y),
+                           pack_bf16x2(v[2 * j].z, v[2 * j].w), pack_bf16x2(v[2 * j + 1].x, v[2 * j + 1].y),
+                           pack_bf16x2(v[2 * j + 1].z, v[2 * j + 1].w));
+          } else {
+#pragma unroll
+            for (int j = 0; j < 8; ++j)
+              st_shared_u4(buf + row_f32 + (((uint32_t)j << 4) ^ xor_f32), __float_as_uint(v[j].x), __float_as_uint(v[j].y),
+                           __float_as_uint(v[j].z), __float_as_uint(v[j].w));
           }
+          fence_proxy_async_smem();
+          __syncwarp();
+          if (lane == 0) {
+            tma_store_3d(&tma_c, buf, n0 + c * 32, row_g, b);
+            bulk_commit();
+          }
+          ++i;
         } else {
-          if (in_tile && col < p.N) {
-            // ragged N tail (N % 4 != 0 or the tile edge cuts this float4): scalar path
-#pragma unroll
-            for (int k = 0; k < 8; ++k) {
-              const int row = row0 + 4 * k;
-              if (row < p.M) {
-#pragma unroll
-                for (int e = 0; e < 4; ++e) {
-                  if (col + e < p.N) {
-                    float o = (e == 0 ? v[k].x : e == 1 ? v[k].y : e == 2 ? v[k].z : v[k].w) * p.alpha;
-                    if (p.bias) o += p.bias_along_m ? __ldg(p.bias + row) : __ldg(p.bias + col + e);
-                    if (p.act == ACT_GELU) o = gelu_fast(o); else if (p.act == ACT_RELU) o = fmaxf(o, 0.f);
-                    if (p.gamma) o *= __ldg(p.gamma + col + e);
-                    if (has_res) o += res_ptr0[c * 32 + (long)k * row_step_r + e];
-                    const long off = out_off0 + c * 32 + (long)k * row_step_c + e;
-                    if (p.out_f32) p.out_f32[off] = o;
-                    if (p.out_bf16) p.out_bf16[off] = __float2bfloat16(o);
-                  }
-                }
-              }
-            }
+          if (c + 2 < NCHUNK) {
+            load_vec8(bias_n ? p.bias : nullptr, c + 2, 0.f, bn_next);
+            tmem_ld_x32(taddr + (c + 2) * 32, r);
           }
-          if (has_res && c + 2 < NCHUNK) load_res(c + 2);
         }
       }
       if (half >= NCHUNK) {   // BN = 32: the second warp of each quarter has no chunk but still owes its arrival
         if (lane == 0) mbar_arrive(&tmem_empty[acc]);
       }
     }
+    if (lane == 0) bulk_wait_read<0>();    // staging smem must outlive the last TMA store's read
   }
 
   tc_fence_before();
@@ -392,27 +379,64 @@ static int make_tmap(CUtensorMap* m, const bf16* ptr, long rows, long K, long ld
   return 0;
 }
 
+// 3-D tensor map over the output / residual [batch][rows][cols] (cols contiguous): box = 32 rows x 32 columns,
+// 64B swizzle for bf16 (64 B rows), 128B swizzle for fp32 (128 B rows) -- the layouts the epilogue warps write.
+static int make_tmap_out(CUtensorMap* m, const void* ptr, int is_bf16, long rows, long cols, long ld, long batch,
+                         long batch_stride) {
+  EncodeTiledFn enc = get_encode_fn();
+  if (!enc) { set_error("cuTensorMapEncodeTiled entry point not available"); return 1; }
+  const long es = is_bf16 ? 2 : 4;
+  if ((reinterpret_cast<uintptr_t>(ptr) & 15) || (ld * es) % 16 || (batch > 1 && (batch_stride * es) % 16)) {
+    set_error("gemm output/residual not 16B aligned (ptr=%p ld=%ld batch_stride=%ld)", ptr, ld, batch_stride);
+    return 1;
+  }
+  cuuint64_t dims[3] = {(cuuint64_t)cols, (cuuint64_t)rows, (cuuint64_t)(batch > 0 ? batch : 1)};
+  cuuint64_t strides[2] = {(cuuint64_t)(ld * es), (cuuint64_t)((batch > 1 ? batch_stride : ld * rows) * es)};
+  cuuint32_t box[3] = {32, 32, 1};
+  cuuint32_t estr[3] = {1, 1, 1};
+  CUresult r = enc(m, is_bf16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, const_cast<void*>(ptr),
+                   dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                   is_bf16 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    set_error("cuTensorMapEncodeTiled(out) failed (%d) rows=%ld cols=%ld ld=%ld batch=%ld bs=%ld", (int)r, rows, cols, ld, batch, batch_stride);
+    return 1;
+  }
+  return 0;
+}
+
 template <int BN>
 static int launch_gemm(const GemmArgs& a, cudaStream_t stream) {
   using Cfg = GemmCfg<BN>;
+  static_assert(BN % 32 == 0 && BN >= 32 && BN <= 256, "BLOCK_N must be a multiple of 32");
+  static_assert(Cfg::STAGES >= 3, "pipeline too shallow");
   static bool attr_set = false;
   if (!attr_set) {
     cudaError_t e = cudaFuncSetAttribute(gemm_bf16_tcgen05_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM);
     if (e != cudaSuccess) { set_error("cudaFuncSetAttribute(gemm<%d>): %s", BN, cudaGetErrorString(e)); return 1; }
     attr_set = true;
   }
-  CUtensorMap ta, tb;
+  CUtensorMap ta, tb, tc, tr;
   if (make_tmap(&ta, a.A, a.M, a.K, a.lda, a.batch, a.a_batch_stride, BM)) return 1;
   const bool b_batched = a.batch > 1 && a.b_batch_stride != 0;
   if (make_tmap(&tb, a.B, a.N, a.K, a.ldb, b_batched ? a.batch : 1, a.b_batch_stride, BN)) return 1;
+  const int out_bf16 = a.out_bf16 != nullptr;
+  if (make_tmap_out(&tc, out_bf16 ? (const void*)a.out_bf16 : (const void*)a.out_f32, out_bf16, a.M, a.N, a.ldc, a.batch,
+                    a.c_batch_stride)) return 1;
+  const bool res_batched = a.residual && a.batch > 1 && a.res_batch_stride != 0;
+  if (a.residual) {
+    const long res_rows = a.res_row_mod ? a.res_row_mod : a.M;
+    if (make_tmap_out(&tr, a.residual, 0, res_rows, a.N, a.ld_res, res_batched ? a.batch : 1, a.res_batch_stride)) return 1;
+  } else {
+    tr = tc;
+  }
   GemmKernelParams p;
   p.M = a.M; p.N = a.N; p.K = a.K; p.batch = a.batch;
   p.tiles_m = (a.M + BM - 1) / BM; p.tiles_n = (a.N + BN - 1) / BN; p.num_kb = (a.K + BK - 1) / BK;
   p.b_batched = b_batched ? 1 : 0;
   p.alpha = a.alpha; p.bias = a.bias; p.bias_along_m = a.bias_along_m; p.act = a.act; p.gamma = a.gamma;
-  p.residual = a.residual; p.ld_res = a.ld_res; p.res_batch_stride = a.res_batch_stride; p.res_row_mod = a.res_row_mod;
-  p.out_f32 = a.out_f32; p.out_bf16 = a.out_bf16; p.ldc = a.ldc; p.c_batch_stride = a.c_batch_stride;
-  { static int dbg = -1; if (dbg < 0) { const char* e = getenv("SAM2B_GEMM_DBG"); dbg = e ? atoi(e) : 0; } p.dbg = dbg; }
+  p.has_res = a.residual ? 1 : 0; p.res_batched = res_batched ? 1 : 0; p.res_row_mod = a.res_row_mod;
+  p.out_is_bf16 = out_bf16;
   const long tiles = (long)p.tiles_m * p.tiles_n * p.batch;
   const int grid = (int)(tiles < num_sms() ? tiles : num_sms());
   char nm[96];
@@ -420,13 +444,13 @@ static int launch_gemm(const GemmArgs& a, cudaStream_t stream) {
   const double esz = a.out_bf16 ? 2.0 : 4.0;
   ProfRange pr(stream, nm, 2.0 * a.M * a.N * (double)a.K * a.batch,
                ((double)a.M * a.K * 2 + (b_batched ? 1.0 : 1.0 / a.batch) * (double)a.N * a.K * 2 + (double)a.M * a.N * (esz + (a.residual ? 4.0 : 0.0))) * a.batch);
-  gemm_bf16_tcgen05_kernel<BN><<<grid, NUM_THREADS, Cfg::SMEM, stream>>>(ta, tb, p);
+  gemm_bf16_tcgen05_kernel<BN><<<grid, NUM_THREADS, Cfg::SMEM, stream>>>(ta, tb, tc, tr, p);
   SAM2B_CHECK_LAUNCH("gemm_bf16_tcgen05");
   return 0;
 }
 
 static int pick_bn(const GemmArgs& a) {
-  static const int cand[] = {256, 192, 144, 128, 96, 64, 32};
+  static const int cand[] = {256, 224, 192, 160, 128, 96, 64, 32};
   const long tiles_m = (a.M + BM - 1) / BM;
   double best = 1e30; int best_bn = 128;
   for (int bn : cand) {
@@ -441,13 +465,8 @@ static int pick_bn(const GemmArgs& a) {
 
 int gemm_bf16(const GemmArgs& a, cudaStream_t stream) {
   if (a.M <= 0 || a.N <= 0 || a.K <= 0 || a.batch <= 0) { set_error("gemm: empty problem M=%d N=%d K=%d batch=%d", a.M, a.N, a.K, a.batch); return 1; }
-  if (!a.out_f32 && !a.out_bf16) { set_error("gemm: no output"); return 1; }
-  if ((a.out_f32 && (a.ldc % 4 || (reinterpret_cast<uintptr_t>(a.out_f32) & 15))) ||
-      (a.out_bf16 && (a.ldc % 8 || (reinterpret_cast<uintptr_t>(a.out_bf16) & 15))) ||
-      (a.residual && (a.ld_res % 4 || (reinterpret_cast<uintptr_t>(a.residual) & 15)))) {
-    set_error("gemm: output/residual leading dimension or pointer not vector aligned (ldc=%ld ld_res=%ld)", a.ldc, a.ld_res);
-    return 1;
-  }
+  if (!a.out_f32 == !a.out_bf16) { set_error("gemm: exactly one of out_f32 / out_bf16 must be given"); return 1; }
+  if (a.residual && a.out_bf16) { set_error("gemm: a residual needs an fp32 output"); return 1; }
   if (a.residual && a.res_row_mod && (a.res_row_mod % BM)) {
     set_error("gemm: res_row_mod=%d must be a multiple of %d", a.res_row_mod, BM);
     return 1;
@@ -455,14 +474,15 @@ int gemm_bf16(const GemmArgs& a, cudaStream_t stream) {
   const int bn = a.force_bn ? a.force_bn : pick_bn(a);
   switch (bn) {
     case 256: return launch_gemm<256>(a, stream);
+    case 224: return launch_gemm<224>(a, stream);
     case 192: return launch_gemm<192>(a, stream);
-    case 144: return launch_gemm<144>(a, stream);
+    case 160: return launch_gemm<160>(a, stream);
     case 128: return launch_gemm<128>(a, stream);
     case 96: return launch_gemm<96>(a, stream);
     case 64: return launch_gemm<64>(a, stream);
     case 32: return launch_gemm<32>(a, stream);
   }
-  set_error("gemm: unsupported BLOCK_N %d", bn);
+  set_error("gemm: unsupported BLOCK_N %d (256, 224, 192, 160, 128, 96, 64, 32)", bn);
   return 1;
 }
 

@@ -44,7 +44,7 @@ def test_gemm_plain(M, N, K):
     _close(out, _ref(a, b), 2e-3)
 
 
-@pytest.mark.parametrize("bn", [32, 64, 96, 128, 144, 192, 256])
+@pytest.mark.parametrize("bn", [32, 64, 96, 128, 160, 192, 224, 256])
 def test_gemm_every_block_n(bn):
     from sam2_opt_b200 import ops
     g = torch.Generator(device="cuda").manual_seed(bn)
