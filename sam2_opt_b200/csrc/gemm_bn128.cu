@@ -1,0 +1,6 @@
+// tcgen05 GEMM instantiations for BLOCK_N = 128 (see gemm_kernel.cuh)
+#include "gemm_kernel.cuh"
+
+namespace sam2b {
+SAM2B_GEMM_INSTANTIATE_FULL(128)
+}  // namespace sam2b
