@@ -27,7 +27,7 @@ int make_tmap_out(CUtensorMap* m, const void* ptr, int is_bf16, long rows, long 
 static constexpr int BM = 128;      // UMMA M (cta_group::1)
 static constexpr int BK = 64;       // 64 bf16 = 128 B = one swizzle row
 static constexpr int UMMA_K = 16;
-static constexpr int ACC_STRIDE = 256;   // TMEM columns between the two accumulator stages
+// accumulator stages in TMEM: 2 x 256 columns, or 4 x 128 columns when BLOCK_N <= 128 (GemmCfg::NACC / ACC_STRIDE)
 static constexpr int TMEM_COLS = 512;
 static constexpr int NUM_EPI_WARPS = 8;  // two warps per TMEM lane quarter, interleaved over 32-column chunks
 static constexpr int NUM_THREADS = 128 + 32 * NUM_EPI_WARPS;  // warp0 TMA, warp1 MMA, warp2 TMEM alloc, warp3 idle, warps4-11 epilogue
@@ -44,10 +44,13 @@ struct GemmKernelParams {
   const float* gamma;
   int has_res; int res_batched; int res_row_mod;
   int out_is_bf16;
+  int dbg;   // timing experiments (SAM2B_GEMM_DBG): 1 = no TMA store, 2 = no proxy fence, 4 = no staging writes
 };
 
 template <int BN>
 struct GemmCfg {
+  static constexpr int NACC = BN <= 128 ? 4 : 2;
+  static constexpr int ACC_STRIDE = 512 / NACC;
   static constexpr int STAGE_A = BM * BK * 2;
   static constexpr int STAGE_B = BN * BK * 2;
   static constexpr int STAGE = STAGE_A + STAGE_B;
@@ -93,8 +96,8 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid
   uint64_t* full_bar = bars;
   uint64_t* empty_bar = bars + STAGES;
   uint64_t* tmem_full = bars + 2 * STAGES;
-  uint64_t* tmem_empty = bars + 2 * STAGES + 2;
-  uint64_t* res_bar = bars + 2 * STAGES + 4;          // [NUM_EPI_WARPS][2]: residual chunk landed in the staging buffer
+  uint64_t* tmem_empty = bars + 2 * STAGES + 4;
+  uint64_t* res_bar = bars + 2 * STAGES + 8;          // [NUM_EPI_WARPS][2]: residual chunk landed in the staging buffer
   uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(res_bar + 2 * NUM_EPI_WARPS);
 
   const int warp = threadIdx.x >> 5;
@@ -109,7 +112,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid
   }
   if (warp == 1 && lane == 0) {
     for (int i = 0; i < STAGES; ++i) { mbar_init(&full_bar[i], 1); mbar_init(&empty_bar[i], 1); }
-    for (int i = 0; i < 2; ++i) { mbar_init(&tmem_full[i], 1); mbar_init(&tmem_empty[i], NUM_EPI_WARPS); }
+    for (int i = 0; i < Cfg::NACC; ++i) { mbar_init(&tmem_full[i], 1); mbar_init(&tmem_empty[i], NUM_EPI_WARPS); }
     for (int i = 0; i < 2 * NUM_EPI_WARPS; ++i) mbar_init(&res_bar[i], 1);
     fence_barrier_init();
   }
@@ -146,11 +149,11 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid
       int stage = 0; uint32_t phase = 0;
       int local = 0;
       for (int t = blockIdx.x; t < num_tiles; t += gridDim.x, ++local) {
-        const int acc = local & 1;
-        const uint32_t acc_phase = (local >> 1) & 1;
+        const int acc = local % Cfg::NACC;
+        const uint32_t acc_phase = (local / Cfg::NACC) & 1;
         mbar_wait(&tmem_empty[acc], acc_phase ^ 1);
         tc_fence_after();
-        const uint32_t tmem_d = tmem_base + acc * ACC_STRIDE;
+        const uint32_t tmem_d = tmem_base + acc * Cfg::ACC_STRIDE;
         for (int kb = 0; kb < p.num_kb; ++kb) {
           mbar_wait(&full_bar[stage], phase);
           tc_fence_after();
@@ -196,8 +199,8 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid
       const int n_blk = t % p.tiles_n;
       const int m_blk = (t / p.tiles_n) % p.tiles_m;
       const int b = t / (p.tiles_n * p.tiles_m);
-      const int acc = local & 1;
-      const uint32_t acc_phase = (local >> 1) & 1;
+      const int acc = local % Cfg::NACC;
+      const uint32_t acc_phase = (local / Cfg::NACC) & 1;
       const int row_g = m_blk * BM + q * 32;             // first row of this warp's 32-row slab
       const int n0 = n_blk * BN;
       const bool rows_live = row_g < p.M;
@@ -211,16 +214,21 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid
       };
       auto load_vec8 = [&](const float* base, int c, float fill, float4 (&o)[8]) {
         // 32 consecutive per-column values (bias / gamma), same addresses for every lane (L1 broadcast)
+        const int col0 = n0 + c * 32;
+        if (base != nullptr && col0 + 32 <= p.N) {             // whole chunk inside N: 8 unguarded vector loads
+          const float4* src = reinterpret_cast<const float4*>(base + col0);
 #pragma unroll
-        for (int j = 0; j < 8; ++j) {
-          const int col = n0 + c * 32 + 4 * j;
-          o[j] = make_float4(fill, fill, fill, fill);
-          if (base) {
-            if (full_n || col + 4 <= p.N) o[j] = __ldg(reinterpret_cast<const float4*>(base + col));
-            else {
+          for (int j = 0; j < 8; ++j) o[j] = __ldg(src + j);
+        } else {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            const int col = col0 + 4 * j;
+            o[j] = make_float4(fill, fill, fill, fill);
+            if (base != nullptr) {
               if (col < p.N) o[j].x = __ldg(base + col);
               if (col + 1 < p.N) o[j].y = __ldg(base + col + 1);
               if (col + 2 < p.N) o[j].z = __ldg(base + col + 2);
+              if (col + 3 < p.N) o[j].w = __ldg(base + col + 3);
             }
           }
         }
@@ -230,13 +238,13 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid
         if (two_buf) bulk_wait_read<1>(); else bulk_wait_read<0>();
         issue_res(i, half);
       }
-      float4 bn_next[8];
-      load_vec8(bias_n ? p.bias : nullptr, half, 0.f, bn_next);
+      float4 bn[8];                                      // bias of the chunk in flight (reloaded right after use)
+      load_vec8(bias_n ? p.bias : nullptr, half, 0.f, bn);
       float bias_m = 0.f;
       if (GEN) bias_m = (p.bias && p.bias_along_m && row_g + lane < p.M) ? __ldg(p.bias + row_g + lane) : 0.f;
       mbar_wait(&tmem_full[acc], acc_phase);
       tc_fence_after();
-      const uint32_t taddr = tmem_base + acc * ACC_STRIDE + ((uint32_t)(q * 32) << 16);
+      const uint32_t taddr = tmem_base + acc * Cfg::ACC_STRIDE + ((uint32_t)(q * 32) << 16);
       uint32_t r[32];
       if (half < NCHUNK) tmem_ld_x32(taddr + half * 32, r);
 #pragma unroll 1
@@ -262,10 +270,6 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid
             }
           }
           __syncwarp();
-          float4 bn[8];
-#pragma unroll
-          for (int j = 0; j < 8; ++j) bn[j] = bn_next[j];
-          if (c + 2 < NCHUNK) load_vec8(bias_n ? p.bias : nullptr, c + 2, 0.f, bn_next);
           float4 v[8];
           if (GEN) {
             const float al = p.alpha;
@@ -285,7 +289,10 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid
               v[j].w = __uint_as_float(r[4 * j + 3]) + bn[j].w;
             }
           }
-          if (c + 2 < NCHUNK) tmem_ld_x32(taddr + (c + 2) * 32, r);   // next chunk streams out of TMEM meanwhile
+          if (c + 2 < NCHUNK) {
+            tmem_ld_x32(taddr + (c + 2) * 32, r);   // next chunk streams out of TMEM (and its bias out of L1) meanwhile
+            load_vec8(bias_n ? p.bias : nullptr, c + 2, 0.f, bn);
+          }
           if (act == ACT_GELU) {
 #pragma unroll
             for (int j = 0; j < 8; ++j) {
@@ -311,7 +318,9 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid
               v[j].x += rv.x; v[j].y += rv.y; v[j].z += rv.z; v[j].w += rv.w;
             }
           }
-          if (bf) {
+          if (p.dbg & 4) {
+            if (v[0].x + v[3].y + v[5].z + v[7].w == 123.456f) st_shared_u4(buf, 0, 0, 0, 0);
+          } else if (bf) {
 #pragma unroll
             for (int j = 0; j < 4; ++j)
               st_shared_u4(buf + row_b16 + (((uint32_t)j << 4) ^ xor_b16), pack_bf16x2(v[2 * j].x, v[2 * j].y),
@@ -323,16 +332,16 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid
               st_shared_u4(buf + row_f32 + (((uint32_t)j << 4) ^ xor_f32), __float_as_uint(v[j].x), __float_as_uint(v[j].y),
                            __float_as_uint(v[j].z), __float_as_uint(v[j].w));
           }
-          fence_proxy_async_smem();
+          if (!(p.dbg & 2)) fence_proxy_async_smem();
           __syncwarp();
-          if (lane == 0) {
+          if (lane == 0 && !(p.dbg & 1)) {
             tma_store_3d(&tma_c, buf, n0 + c * 32, row_g, b);
             bulk_commit();
           }
           ++i;
         } else {
           if (c + 2 < NCHUNK) {
-            load_vec8(bias_n ? p.bias : nullptr, c + 2, 0.f, bn_next);
+            load_vec8(bias_n ? p.bias : nullptr, c + 2, 0.f, bn);
             tmem_ld_x32(taddr + (c + 2) * 32, r);
           }
         }
@@ -387,6 +396,7 @@ static int launch_gemm(const GemmArgs& a, cudaStream_t stream) {
   p.alpha = a.alpha; p.bias = a.bias; p.bias_along_m = a.bias_along_m; p.act = a.act; p.gamma = a.gamma;
   p.has_res = a.residual ? 1 : 0; p.res_batched = res_batched ? 1 : 0; p.res_row_mod = a.res_row_mod;
   p.out_is_bf16 = out_bf16;
+  { static int dbg = -1; if (dbg < 0) { const char* e = getenv("SAM2B_GEMM_DBG"); dbg = e ? atoi(e) : 0; } p.dbg = dbg; }
   const long tiles = (long)p.tiles_m * p.tiles_n * p.batch;
   const int grid = (int)(tiles < num_sms() ? tiles : num_sms());
   char nm[96];
