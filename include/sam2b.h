@@ -86,6 +86,12 @@ int sam2b_op_maxpool2x2_nhwc(const float* x, float* y, int b, int hgt, int wid, 
 int sam2b_op_window_attention(const void* qkv_bf16, void* out_bf16, int b, int hgt, int wid, int heads, int ws,
                               int q_pool, void* stream);
 int sam2b_op_softmax_rows(const float* s, int64_t lds, void* p_bf16, int64_t ldp, int64_t rows, int cols, void* stream);
+/* Single-head flash attention, head_dim 256 (the MemoryAttention core; reference sam/transformer.py:265-296):
+ * out[b] = softmax(q[b] k[b]^T / 16) v[b];  q [n][tq][256], k, v [n][lk][256], out [n][tq][256], all bf16 device memory,
+ * tq a multiple of 128.  workspace: at least sam2b_op_attention_hd256_workspace(n, tq, lk) bytes of device memory. */
+int64_t sam2b_op_attention_hd256_workspace(int n, int tq, int64_t lk);
+int sam2b_op_attention_hd256(const void* q_bf16, const void* k_bf16, const void* v_bf16, int n, int tq, int64_t lk,
+                             void* out_bf16, void* workspace, void* stream);
 
 #ifdef __cplusplus
 }

@@ -56,29 +56,6 @@ struct FaParams {
   float scale_log2;
 };
 
-SAM2B_DEVINL void tma_load_5d(void* smem_dst, const CUtensorMap* map, uint64_t* bar, int c0, int c1, int c2, int c3, int c4) {
-  asm volatile(
-      "cp.async.bulk.tensor.5d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6, %7}], [%2];"
-      ::"r"(smem_u32(smem_dst)), "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2), "r"(c3), "r"(c4)
-      : "memory");
-}
-
-// shared-memory matrix descriptor: start address, leading / stride byte offsets (>>4), version 1, layout type
-// (2 = SWIZZLE_128B, 6 = SWIZZLE_32B).
-SAM2B_DEVINL uint64_t make_desc(uint32_t smem_addr, uint32_t lbo_bytes, uint32_t sbo_bytes, uint32_t layout) {
-  uint64_t d = 0;
-  d |= (uint64_t)((smem_addr >> 4) & 0x3FFF);
-  d |= (uint64_t)((lbo_bytes >> 4) & 0x3FFF) << 16;
-  d |= (uint64_t)((sbo_bytes >> 4) & 0x3FFF) << 32;
-  d |= (uint64_t)1 << 46;
-  d |= (uint64_t)layout << 61;
-  return d;
-}
-// instruction descriptor: bf16 x bf16 -> fp32, A K-major, B K-major (b_mn = 0) or MN-major (b_mn = 1)
-SAM2B_DEVINL constexpr uint32_t make_idesc(int m, int n, int b_mn) {
-  return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)b_mn << 16) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(m >> 4) << 24);
-}
-
 struct UnitCoord { int b, head, x0, y0; };
 SAM2B_DEVINL UnitCoord unit_coord(const FaParams& p, int u) {
   UnitCoord c;
@@ -171,9 +148,9 @@ flash_attn_hd72_tcgen05_kernel(const __grid_constant__ CUtensorMap map_lo, const
   } else if (warp == 1) {
     // ===================== MMA issuer (one thread) =====================
     if (lane == 0) {
-      constexpr uint32_t idesc_qk = make_idesc(128, 128, 0);
-      constexpr uint32_t idesc_pv_lo = make_idesc(128, 64, 1);
-      constexpr uint32_t idesc_pv_hi = make_idesc(128, 16, 1);
+      constexpr uint32_t idesc_qk = make_idesc_ex(128, 128, 0);
+      constexpr uint32_t idesc_pv_lo = make_idesc_ex(128, 64, 1);
+      constexpr uint32_t idesc_pv_hi = make_idesc_ex(128, 16, 1);
       const uint32_t sbase = smem_u32(smem);
       uint32_t n_s[2] = {0, 0};     // QK^T products issued on S_t
       uint32_t n_o[2] = {0, 0};     // P V products issued on O_t
@@ -185,8 +162,8 @@ flash_attn_hd72_tcgen05_kernel(const __grid_constant__ CUtensorMap map_lo, const
         const uint32_t d = tmem_base + COL_S + 128 * t;
 #pragma unroll
         for (int ks = 0; ks < 4; ++ks)
-          umma_bf16(d, make_desc(q + 32 * ks, 16, 1024, 2), make_desc(k + 32 * ks, 16, 1024, 2), idesc_qk, ks != 0);
-        umma_bf16(d, make_desc(q + LO_BYTES, 16, 256, 6), make_desc(k + LO_BYTES, 16, 256, 6), idesc_qk, 1);
+          umma_bf16(d, make_smem_desc(q + 32 * ks, 16, 1024, 2), make_smem_desc(k + 32 * ks, 16, 1024, 2), idesc_qk, ks != 0);
+        umma_bf16(d, make_smem_desc(q + LO_BYTES, 16, 256, 6), make_smem_desc(k + LO_BYTES, 16, 256, 6), idesc_qk, 1);
         umma_commit(&s_full[t]);
         ++n_s[t];
       };
@@ -199,9 +176,9 @@ flash_attn_hd72_tcgen05_kernel(const __grid_constant__ CUtensorMap map_lo, const
 #pragma unroll
         for (int ks = 0; ks < 8; ++ks) {
           // A: P[128][16 keys of k-step ks] (K-major, sub-tile ks/4); B: V rows 16ks..16ks+15 (MN-major: d contiguous)
-          const uint64_t da = make_desc(pa + (ks >> 2) * 16384 + (ks & 3) * 32, 16, 1024, 2);
-          umma_bf16(d, da, make_desc(v + ks * 2048, 1024, 1024, 2), idesc_pv_lo, ks != 0);
-          umma_bf16(d + 64, da, make_desc(v + LO_BYTES + ks * 512, 256, 256, 6), idesc_pv_hi, ks != 0);
+          const uint64_t da = make_smem_desc(pa + (ks >> 2) * 16384 + (ks & 3) * 32, 16, 1024, 2);
+          umma_bf16(d, da, make_smem_desc(v + ks * 2048, 1024, 1024, 2), idesc_pv_lo, ks != 0);
+          umma_bf16(d + 64, da, make_smem_desc(v + LO_BYTES + ks * 512, 256, 256, 6), idesc_pv_hi, ks != 0);
         }
         umma_commit(&o_full[t]);
         ++n_o[t];

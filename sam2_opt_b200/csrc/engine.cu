@@ -754,4 +754,19 @@ int sam2b_op_softmax_rows(const float* s, int64_t lds, void* p, int64_t ldp, int
   return softmax_rows(s, lds, reinterpret_cast<bf16*>(p), ldp, rows, cols, reinterpret_cast<cudaStream_t>(stream));
 }
 
+int64_t sam2b_op_attention_hd256_workspace(int n, int tq, int64_t lk) {
+  if (n <= 0 || tq <= 0 || lk <= 0) return 0;
+  return (int64_t)flash_attention_hd256_splits(n, tq, lk) * n * tq * (256 + 2) * 4;
+}
+int sam2b_op_attention_hd256(const void* q, const void* k, const void* v, int n, int tq, int64_t lk, void* out, void* workspace,
+                             void* stream) {
+  if (!q || !k || !v || !out || !workspace) { set_error("sam2b_op_attention_hd256: null argument"); return 1; }
+  const int splits = flash_attention_hd256_splits(n, tq, lk);
+  float* o_part = reinterpret_cast<float*>(workspace);
+  float* ml_part = o_part + (size_t)splits * n * tq * 256;
+  return flash_attention_hd256(reinterpret_cast<const bf16*>(q), (long)tq * 256, reinterpret_cast<const bf16*>(k), lk * 256,
+                               reinterpret_cast<const bf16*>(v), lk * 256, n, tq, lk, o_part, ml_part,
+                               reinterpret_cast<bf16*>(out), reinterpret_cast<cudaStream_t>(stream));
+}
+
 }  // extern "C"

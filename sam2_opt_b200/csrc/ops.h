@@ -76,6 +76,14 @@ int window_attention_hd72(const bf16* qkv, bf16* out, int B, int H, int W, int h
 bool flash_attention_hd72_supported(int H, int W, int ws, int q_pool);
 int flash_attention_hd72(const bf16* qkv, bf16* out, int B, int H, int W, int heads, int ws, cudaStream_t stream);
 
+// K4 (attn_hd256.cu): softmax(q k^T / 16) v, single head, head_dim 256.  q [n][Tq][256], k / v [n][Lk][256] bf16 (batch
+// strides in elements), out [n][Tq][256] bf16.  o_part / ml_part: workspaces of splits*n*Tq*256 and splits*n*Tq*2 floats
+// with splits = flash_attention_hd256_splits(n, Tq, Lk).
+int flash_attention_hd256_splits(int n, int Tq, long Lk);
+int flash_attention_hd256(const bf16* q, long q_batch_stride, const bf16* k, long k_batch_stride, const bf16* v,
+                          long v_batch_stride, int n, int Tq, long Lk, float* o_part, float* ml_part, bf16* out,
+                          cudaStream_t stream);
+
 // Row softmax over fp32 scores -> bf16 probabilities (row stride lds / ldp elements), `cols` valid columns;
 // columns in [cols, ldp) are written as zero.
 int softmax_rows(const float* s, long lds, bf16* p, long ldp, long rows, int cols, cudaStream_t stream);

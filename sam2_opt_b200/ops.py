@@ -85,3 +85,18 @@ def softmax_rows(s: torch.Tensor, ldp: Optional[int] = None) -> torch.Tensor:
     p = torch.empty((rows, ldp), device=s.device, dtype=torch.bfloat16)
     _lib.check(lib.sam2b_op_softmax_rows(_ptr(s), s.stride(0), _ptr(p), ldp, rows, cols, _stream()), "op_softmax_rows")
     return p
+
+
+def attention_hd256(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor) -> torch.Tensor:
+    """softmax(q k^T / 16) v for q [n,Tq,256], k / v [n,Lk,256] bf16 (single head; the MemoryAttention core)."""
+    lib = _lib.load()
+    assert q.dtype == k.dtype == v.dtype == torch.bfloat16 and q.is_cuda
+    q, k, v = q.contiguous(), k.contiguous(), v.contiguous()
+    n, tq, d = q.shape
+    lk = k.shape[1]
+    assert d == 256 and k.shape == v.shape == (n, lk, 256)
+    out = torch.empty_like(q)
+    ws = torch.empty(int(lib.sam2b_op_attention_hd256_workspace(n, tq, lk)), device=q.device, dtype=torch.uint8)
+    _lib.check(lib.sam2b_op_attention_hd256(_ptr(q), _ptr(k), _ptr(v), n, tq, lk, _ptr(out), _ptr(ws), _stream()),
+               "op_attention_hd256")
+    return out

@@ -77,3 +77,22 @@ def test_softmax_rows():
     ref = torch.softmax(s, -1)
     assert p.shape[1] % 64 == 0 and (p[:, s.shape[1]:] == 0).all()
     assert (p[:, :s.shape[1]].float() - ref).abs().max().item() <= 2 ** -8 * ref.max().item()
+
+
+# (n, Tq, Lk): self attention, the first propagated frame (L=1, P=4), the full bank (7*4096+64), ragged Lk, multi-object
+ATTN256 = [(1, 4096, 4096), (1, 4096, 4100), (1, 4096, 28736), (3, 256, 200), (4, 4096, 8256), (2, 128, 64)]
+
+
+@pytest.mark.parametrize("n,Tq,Lk", ATTN256)
+def test_attention_hd256(n, Tq, Lk):
+    """tcgen05 flash attention (K4) against torch SDPA in fp32 on the same bf16 operands."""
+    from sam2_opt_b200 import ops
+    g = torch.Generator(device="cuda").manual_seed(n * 7 + Lk)
+    q = (torch.randn(n, Tq, 256, device="cuda", generator=g) * 1.2).bfloat16()
+    k = (torch.randn(n, Lk, 256, device="cuda", generator=g) * 1.2).bfloat16()
+    v = torch.randn(n, Lk, 256, device="cuda", generator=g).bfloat16()
+    out = ops.attention_hd256(q, k, v)
+    torch.cuda.synchronize()
+    ref = F.scaled_dot_product_attention(q.float()[:, None], k.float()[:, None], v.float()[:, None])[:, 0]
+    err = (out.float() - ref).abs().max().item()
+    assert err < 2e-2 * ref.abs().max().item(), err     # P rounded to bf16 before PV (2^-8) + bf16 output
