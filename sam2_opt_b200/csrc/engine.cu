@@ -347,7 +347,8 @@ static int image_encode_mb(sam2b_engine* e, const float* img, int n, int normali
 
 // ------------------------------------------------------------------------------------------------------------
 // MemoryAttention (boundary E3) for a micro-batch of n objects.  All contractions run on the tcgen05 GEMM:
-//   S = q k^T / 16 (fp32) -> row softmax (bf16 P) -> O = P V with V^T produced directly by a swapped-operand GEMM.
+// projections and FFN run on the tcgen05 GEMM (K1), softmax(q k^T / 16) v on the hd-256 flash kernel (K4): the score and
+// probability matrices never reach HBM.
 // ------------------------------------------------------------------------------------------------------------
 static int memory_attention_mb(sam2b_engine* e, const float* curr, const float* curr_pos, const float* memory,
                                const float* memory_pos, int L, const float* excl, const float* pos_excl, int P, int n,
@@ -357,22 +358,20 @@ static int memory_attention_mb(sam2b_engine* e, const float* curr, const float* 
   const long Lk = (long)L * 4096 + P;
   const long Lkp = (Lk + 63) / 64 * 64;
   const long TT = (long)n * T;
-  float *X, *QK, *S, *KC32, *OUT;
-  bf16 *XN, *Qb, *Kb, *VT, *Pm, *KIN, *VIN, *Kc, *VcT, *O, *HID;
+  float *X, *QK, *KC32, *OUT;
+  bf16 *XN, *Qb, *Kb, *Vb, *KIN, *VIN, *Kc, *Vc, *O, *HID;
   TRY(ws_get_t(e, "ma_x", (size_t)TT * C, &X));
   TRY(ws_get_t(e, "ma_qk", (size_t)TT * 512, &QK));
-  TRY(ws_get_t(e, "ma_s", (size_t)n * T * Lkp, &S));
   TRY(ws_get_t(e, "ma_kc32", (size_t)n * Lk * C, &KC32));
   TRY(ws_get_t(e, "ma_out", (size_t)TT * C, &OUT));
   TRY(ws_get_t(e, "ma_xn", (size_t)TT * C, &XN));
   TRY(ws_get_t(e, "ma_qb", (size_t)TT * C, &Qb));
   TRY(ws_get_t(e, "ma_kb", (size_t)TT * C, &Kb));
-  TRY(ws_get_t(e, "ma_vt", (size_t)TT * C, &VT));
-  TRY(ws_get_t(e, "ma_p", (size_t)n * T * Lkp, &Pm));
+  TRY(ws_get_t(e, "ma_vb", (size_t)TT * C, &Vb));
   TRY(ws_get_t(e, "ma_kin", (size_t)n * Lkp * 64, &KIN));
   TRY(ws_get_t(e, "ma_vin", (size_t)n * Lkp * 64, &VIN));
   TRY(ws_get_t(e, "ma_kc", (size_t)n * Lkp * C, &Kc));
-  TRY(ws_get_t(e, "ma_vct", (size_t)n * C * Lkp, &VcT));
+  TRY(ws_get_t(e, "ma_vc", (size_t)n * Lkp * C, &Vc));
   TRY(ws_get_t(e, "ma_o", (size_t)TT * C, &O));
   TRY(ws_get_t(e, "ma_hid", (size_t)TT * 2048, &HID));
   const float* cos_t = W32(e, "derived.rope.cos");
@@ -396,39 +395,14 @@ static int memory_attention_mb(sam2b_engine* e, const float* curr, const float* 
     g.out_f32 = o32; g.out_bf16 = o16; g.ldc = ldc;
     return gemm_bf16(g, st);
   };
-  // attention core on prepared operands: q [n][T][256], k [n][keys][256] (row stride 256), vT [n][256][ldv]
-  auto attend = [&](const bf16* q, const bf16* k, long k_rows_alloc, const bf16* vT, long keys, long ldv) -> int {
-    const long lds = (keys + 63) / 64 * 64;
-    {
-      GemmArgs g;
-      g.A = q; g.lda = C; g.a_batch_stride = (long)T * C; g.M = T; g.K = C;
-      g.B = k; g.ldb = C; g.b_batch_stride = k_rows_alloc * C; g.N = (int)keys;
-      g.batch = n; g.alpha = 1.0f / 16.0f;                 // 1/sqrt(256)
-      g.out_f32 = S; g.ldc = lds; g.c_batch_stride = (long)T * lds;
-      TRY(gemm_bf16(g, st));
-    }
-    TRY(softmax_rows(S, lds, Pm, lds, (long)n * T, (int)keys, st));
-    {
-      GemmArgs g;
-      g.A = Pm; g.lda = lds; g.a_batch_stride = (long)T * lds; g.M = T; g.K = (int)keys;
-      g.B = vT; g.ldb = ldv; g.b_batch_stride = (long)C * ldv; g.N = C;
-      g.batch = n;
-      g.out_bf16 = O; g.ldc = C; g.c_batch_stride = (long)T * C;
-      TRY(gemm_bf16(g, st));
-    }
-    return 0;
+  // attention core (K4, attn_hd256.cu) on prepared operands: q [n][T][256], k / v [n][rows_alloc][256], `keys` valid rows
+  auto attend = [&](const bf16* q, const bf16* k, const bf16* v, long rows_alloc, long keys) -> int {
+    const int splits = flash_attention_hd256_splits(n, T, keys);
+    float* part = nullptr;
+    TRY(ws_get_t(e, "ma_part", (size_t)splits * n * T * (C + 2), &part));
+    return flash_attention_hd256(q, (long)T * C, k, rows_alloc * C, v, rows_alloc * C, n, T, keys, part,
+                                 part + (size_t)splits * n * T * C, O, st);
   };
-  // V^T[b][c][j] = sum_k Wv[c][k] * in[b][j][k] + bv[c]
-  auto v_transposed = [&](const std::string& wname, const bf16* in, long in_rows_alloc, int K, long keys, long ldv, bf16* vt) -> int {
-    GemmArgs g;
-    g.A = W16(e, wname + "weight"); g.lda = K; g.M = C; g.K = K;
-    g.B = in; g.ldb = K; g.b_batch_stride = in_rows_alloc * K; g.N = (int)keys;
-    g.batch = n;
-    g.bias = W32(e, wname + "bias"); g.bias_along_m = 1;
-    g.out_bf16 = vt; g.ldc = ldv; g.c_batch_stride = (long)C * ldv;
-    return gemm_bf16(g, st);
-  };
-
   for (int l = 0; l < 4; ++l) {
     const std::string p = "memory_attention.layers." + std::to_string(l) + ".";
     const std::string d = "derived.memattn." + std::to_string(l) + ".";
@@ -437,8 +411,8 @@ static int memory_attention_mb(sam2b_engine* e, const float* curr, const float* 
     TRY(linear(XN, C, (int)TT, d + "sa_qk.", 512, C, ACT_NONE, nullptr, QK, nullptr, 512));
     TRY(rope_cast_batched(QK, 512, cos_t, sin_t, Qb, n, T, T, T, st));
     TRY(rope_cast_batched(QK + 256, 512, cos_t, sin_t, Kb, n, T, T, T, st));
-    TRY(v_transposed(p + "self_attn.v_proj.", XN, T, C, T, T, VT));
-    TRY(attend(Qb, Kb, T, VT, T, T));
+    TRY(linear(XN, C, (int)TT, p + "self_attn.v_proj.", C, C, ACT_NONE, nullptr, nullptr, Vb, C));
+    TRY(attend(Qb, Kb, Vb, T, T));
     TRY(linear(O, C, (int)TT, p + "self_attn.out_proj.", C, C, ACT_NONE, X, X, nullptr, C));
     // ---- cross attention over the memory bank (RoPE on q and on the L*4096 spatial keys only) ----
     TRY(layernorm_rows(X, W32(e, p + "norm2.weight"), W32(e, p + "norm2.bias"), 1e-5f, XN, nullptr, TT, C, st));
@@ -454,8 +428,8 @@ static int memory_attention_mb(sam2b_engine* e, const float* curr, const float* 
       TRY(gemm_bf16(g, st));
     }
     TRY(rope_cast_batched(KC32, C, cos_t, sin_t, Kc, n, Lk, (long)L * 4096, Lkp, st));
-    TRY(v_transposed(p + "cross_attn_image.v_proj.", VIN, Lkp, 64, Lk, Lkp, VcT));
-    TRY(attend(Qb, Kc, Lkp, VcT, Lk, Lkp));
+    TRY(linear(VIN, 64, (int)(n * Lkp), p + "cross_attn_image.v_proj.", C, 64, ACT_NONE, nullptr, nullptr, Vc, C));
+    TRY(attend(Qb, Kc, Vc, Lkp, Lk));
     TRY(linear(O, C, (int)TT, p + "cross_attn_image.out_proj.", C, C, ACT_NONE, X, X, nullptr, C));
     // ---- FFN ----
     TRY(layernorm_rows(X, W32(e, p + "norm3.weight"), W32(e, p + "norm3.bias"), 1e-5f, XN, nullptr, TT, C, st));
