@@ -47,12 +47,16 @@ struct GemmKernelParams {
   int dbg;   // timing experiments (SAM2B_GEMM_DBG): 1 = no TMA store, 2 = no proxy fence, 4 = no staging writes
 };
 
-template <int BN>
+// NCTA = 2: a CTA pair (cluster of 2, `tcgen05.mma.cta_group::2`) works on a 256 x BN tile.  Each CTA holds 128 rows of A and
+// of the accumulator and HALF of the B tile (BN/2 rows) in its own shared memory, so a CTA moves (128 + BN/2) x 64 operands per
+// k-block instead of (128 + BN) x 64: one third less L2 -> SM traffic at BN = 256 and a deeper ring in the same smem.
+template <int BN, int NCTA = 1>
 struct GemmCfg {
   static constexpr int NACC = BN <= 128 ? 4 : 2;
   static constexpr int ACC_STRIDE = 512 / NACC;
   static constexpr int STAGE_A = BM * BK * 2;
-  static constexpr int STAGE_B = BN * BK * 2;
+  static constexpr int B_ROWS = BN / NCTA;            // rows of the B tile this CTA loads
+  static constexpr int STAGE_B = B_ROWS * BK * 2;
   static constexpr int STAGE = STAGE_A + STAGE_B;
   // Epilogue staging per warp: 32 rows x 128 B (32 fp32 or, for bf16, 32 rows x 64 B), the box of one TMA store.
   // BN <= 192 leaves room for two 4 KB buffers per warp (store of chunk i overlaps chunk i+1, residual prefetch);
@@ -80,13 +84,14 @@ SAM2B_DEVINL float gelu_fast(float x) {
   return fmaf(-fabsf(x), h, fmaxf(x, 0.0f));
 }
 
-template <int BN, int MODE>
+template <int BN, int MODE, int NCTA>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
 gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b,
                          const __grid_constant__ CUtensorMap tma_c, const __grid_constant__ CUtensorMap tma_r,
                          const GemmKernelParams p) {
-  using Cfg = GemmCfg<BN>;
+  using Cfg = GemmCfg<BN, NCTA>;
   constexpr int STAGES = Cfg::STAGES;
+  constexpr int TILE_M = BM * NCTA;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* smem_a = smem;
@@ -103,6 +108,9 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
   const int num_tiles = p.tiles_m * p.tiles_n * p.batch;
+  const int cta_rank = NCTA == 2 ? (int)cluster_ctarank() : 0;      // 0 = leader (issues the MMAs of the pair)
+  const int tile0 = NCTA == 2 ? (int)(blockIdx.x >> 1) : (int)blockIdx.x;
+  const int tile_step = NCTA == 2 ? (int)(gridDim.x >> 1) : (int)gridDim.x;
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tma_a);
@@ -112,16 +120,16 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid
   }
   if (warp == 1 && lane == 0) {
     for (int i = 0; i < STAGES; ++i) { mbar_init(&full_bar[i], 1); mbar_init(&empty_bar[i], 1); }
-    for (int i = 0; i < Cfg::NACC; ++i) { mbar_init(&tmem_full[i], 1); mbar_init(&tmem_empty[i], NUM_EPI_WARPS); }
+    for (int i = 0; i < Cfg::NACC; ++i) { mbar_init(&tmem_full[i], 1); mbar_init(&tmem_empty[i], NUM_EPI_WARPS * NCTA); }
     for (int i = 0; i < 2 * NUM_EPI_WARPS; ++i) mbar_init(&res_bar[i], 1);
     fence_barrier_init();
   }
   if (warp == 2) {
-    tmem_alloc(tmem_ptr, TMEM_COLS);
-    tmem_relinquish();
+    if (NCTA == 2) { tmem_alloc_2cta(tmem_ptr, TMEM_COLS); tmem_relinquish_2cta(); }
+    else { tmem_alloc(tmem_ptr, TMEM_COLS); tmem_relinquish(); }
   }
   tc_fence_before();
-  __syncthreads();
+  if (NCTA == 2) cluster_sync_all(); else __syncthreads();     // the pair's barriers are initialised before any remote arrive
   tc_fence_after();
   const uint32_t tmem_base = *tmem_ptr;
 
@@ -129,26 +137,34 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid
     // ===================== TMA producer =====================
     if (lane == 0) {
       int stage = 0; uint32_t phase = 0;
-      for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
+      for (int t = tile0; t < num_tiles; t += tile_step) {
         const int n_blk = t % p.tiles_n;
         const int m_blk = (t / p.tiles_n) % p.tiles_m;
         const int b = t / (p.tiles_n * p.tiles_m);
         for (int kb = 0; kb < p.num_kb; ++kb) {
           mbar_wait(&empty_bar[stage], phase ^ 1);
-          mbar_arrive_expect_tx(&full_bar[stage], Cfg::STAGE);
-          tma_load_3d(smem_a + stage * Cfg::STAGE_A, &tma_a, &full_bar[stage], kb * BK, m_blk * BM, b);
-          tma_load_3d(smem_b + stage * Cfg::STAGE_B, &tma_b, &full_bar[stage], kb * BK, n_blk * BN, p.b_batched ? b : 0);
+          if (NCTA == 2) {
+            // both CTAs' loads complete on the LEADER's full barrier, which expects the bytes of the pair
+            if (cta_rank == 0) mbar_arrive_expect_tx(&full_bar[stage], 2 * Cfg::STAGE);
+            tma_load_3d_2cta(smem_a + stage * Cfg::STAGE_A, &tma_a, &full_bar[stage], kb * BK, m_blk * TILE_M + cta_rank * BM, b);
+            tma_load_3d_2cta(smem_b + stage * Cfg::STAGE_B, &tma_b, &full_bar[stage], kb * BK, n_blk * BN + cta_rank * Cfg::B_ROWS,
+                             p.b_batched ? b : 0);
+          } else {
+            mbar_arrive_expect_tx(&full_bar[stage], Cfg::STAGE);
+            tma_load_3d(smem_a + stage * Cfg::STAGE_A, &tma_a, &full_bar[stage], kb * BK, m_blk * BM, b);
+            tma_load_3d(smem_b + stage * Cfg::STAGE_B, &tma_b, &full_bar[stage], kb * BK, n_blk * BN, p.b_batched ? b : 0);
+          }
           if (++stage == STAGES) { stage = 0; phase ^= 1; }
         }
       }
     }
   } else if (warp == 1) {
     // ===================== MMA issuer (one thread) =====================
-    if (lane == 0) {
-      constexpr uint32_t idesc = make_idesc_bf16(BM, BN);
+    if (lane == 0 && cta_rank == 0) {
+      constexpr uint32_t idesc = make_idesc_bf16(TILE_M, BN);
       int stage = 0; uint32_t phase = 0;
       int local = 0;
-      for (int t = blockIdx.x; t < num_tiles; t += gridDim.x, ++local) {
+      for (int t = tile0; t < num_tiles; t += tile_step, ++local) {
         const int acc = local % Cfg::NACC;
         const uint32_t acc_phase = (local / Cfg::NACC) & 1;
         mbar_wait(&tmem_empty[acc], acc_phase ^ 1);
@@ -162,12 +178,15 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid
 #pragma unroll
           for (int k = 0; k < BK / UMMA_K; ++k) {
             // advance 32 B (16 bf16) along K inside the 128 B swizzle row: +2 in the >>4 address field
-            umma_bf16(tmem_d, da + 2 * k, db + 2 * k, idesc, (kb | k) != 0);
+            if (NCTA == 2) umma_bf16_2cta(tmem_d, da + 2 * k, db + 2 * k, idesc, (kb | k) != 0);
+            else umma_bf16(tmem_d, da + 2 * k, db + 2 * k, idesc, (kb | k) != 0);
           }
-          umma_commit(&empty_bar[stage]);   // frees the smem slot once these MMAs have read it
+          // frees the smem slot (in both CTAs of a pair) once these MMAs have read it
+          if (NCTA == 2) umma_commit_2cta(&empty_bar[stage]); else umma_commit(&empty_bar[stage]);
           if (++stage == STAGES) { stage = 0; phase ^= 1; }
         }
-        umma_commit(&tmem_full[acc]);       // accumulator complete -> epilogue
+        // accumulator complete -> epilogue warps (of both CTAs)
+        if (NCTA == 2) umma_commit_2cta(&tmem_full[acc]); else umma_commit(&tmem_full[acc]);
       }
     }
   } else if (warp >= 4) {
@@ -195,17 +214,17 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid
     const uint32_t row_b16 = (uint32_t)lane * 64, xor_b16 = (uint32_t)((lane >> 1) & 3) << 4;
     uint32_t i = 0;                       // live chunks processed by this warp: buffer = i & 1 (two_buf), res phase
     int local = 0;
-    for (int t = blockIdx.x; t < num_tiles; t += gridDim.x, ++local) {
+    for (int t = tile0; t < num_tiles; t += tile_step, ++local) {
       const int n_blk = t % p.tiles_n;
       const int m_blk = (t / p.tiles_n) % p.tiles_m;
       const int b = t / (p.tiles_n * p.tiles_m);
       const int acc = local % Cfg::NACC;
       const uint32_t acc_phase = (local / Cfg::NACC) & 1;
-      const int row_g = m_blk * BM + q * 32;             // first row of this warp's 32-row slab
+      const int row_g = m_blk * TILE_M + cta_rank * BM + q * 32;   // first row of this warp's 32-row slab
       const int n0 = n_blk * BN;
       const bool rows_live = row_g < p.M;
       const bool full_n = n0 + BN <= p.N;                // no column guards needed anywhere in this tile
-      const int res_row = p.res_row_mod ? ((m_blk * BM) % p.res_row_mod) + q * 32 : row_g;
+      const int res_row = p.res_row_mod ? ((m_blk * TILE_M + cta_rank * BM) % p.res_row_mod) + q * 32 : row_g;
       const int res_b = p.res_batched ? b : 0;
       auto issue_res = [&](uint32_t ii, int c) {          // lane 0: residual chunk c -> staging buffer of chunk ii
         const uint32_t bsel = two_buf ? (ii & 1) : 0;
@@ -254,7 +273,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid
           // last chunk of this warp has left TMEM: hand the accumulator stage back to the MMA warp now
           tc_fence_before();
           __syncwarp();
-          if (lane == 0) mbar_arrive(&tmem_empty[acc]);
+          if (lane == 0) { if (NCTA == 2) mbar_arrive_cluster(&tmem_empty[acc], 0); else mbar_arrive(&tmem_empty[acc]); }
         }
         const bool live = rows_live && (n0 + c * 32 < p.N);
         const bool next_live = rows_live && (c + 2 < NCHUNK) && (n0 + (c + 2) * 32 < p.N);
@@ -347,38 +366,51 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid
         }
       }
       if (half >= NCHUNK) {   // BN = 32: the second warp of each quarter has no chunk but still owes its arrival
-        if (lane == 0) mbar_arrive(&tmem_empty[acc]);
+        if (lane == 0) { if (NCTA == 2) mbar_arrive_cluster(&tmem_empty[acc], 0); else mbar_arrive(&tmem_empty[acc]); }
       }
     }
     if (lane == 0) bulk_wait_read<0>();    // staging smem must outlive the last TMA store's read
   }
 
   tc_fence_before();
-  __syncthreads();
+  if (NCTA == 2) cluster_sync_all(); else __syncthreads();     // the peer's smem / TMEM / barriers stay alive until both are done
   if (warp == 2) {
     tc_fence_after();
-    tmem_dealloc(tmem_base, TMEM_COLS);
+    if (NCTA == 2) tmem_dealloc_2cta(tmem_base, TMEM_COLS); else tmem_dealloc(tmem_base, TMEM_COLS);
   }
 }
 
 // ------------------------------------------------------------------------------------------
 // host side: launch of one instantiation
 // ------------------------------------------------------------------------------------------
-template <int BN, int MODE>
+template <int BN, int MODE, int NCTA>
 static int launch_gemm(const GemmArgs& a, cudaStream_t stream) {
-  using Cfg = GemmCfg<BN>;
+  using Cfg = GemmCfg<BN, NCTA>;
   static_assert(BN % 32 == 0 && BN >= 32 && BN <= 256, "BLOCK_N must be a multiple of 32");
   static_assert(Cfg::STAGES >= 3, "pipeline too shallow");
-  static bool attr_set = false;
-  if (!attr_set) {
-    cudaError_t e = cudaFuncSetAttribute(gemm_bf16_tcgen05_kernel<BN, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM);
-    if (e != cudaSuccess) { set_error("cudaFuncSetAttribute(gemm<%d>): %s", BN, cudaGetErrorString(e)); return 1; }
-    attr_set = true;
+  static_assert(NCTA == 1 || (BN % 32 == 0 && (BN / 2) % 8 == 0), "a CTA pair splits the B tile in two halves of whole swizzle atoms");
+  static int max_pairs = 0;       // 0: attributes not set yet
+  auto kern = gemm_bf16_tcgen05_kernel<BN, MODE, NCTA>;
+  if (!max_pairs) {
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM);
+    if (e != cudaSuccess) { set_error("cudaFuncSetAttribute(gemm<%d,%d>): %s", BN, NCTA, cudaGetErrorString(e)); return 1; }
+    max_pairs = num_sms() / NCTA;
+    if (NCTA == 2) {
+      cudaLaunchConfig_t qc = {};
+      qc.gridDim = dim3(num_sms() / 2 * 2); qc.blockDim = dim3(NUM_THREADS); qc.dynamicSmemBytes = Cfg::SMEM;
+      cudaLaunchAttribute qa[1];
+      qa[0].id = cudaLaunchAttributeClusterDimension; qa[0].val.clusterDim.x = 2; qa[0].val.clusterDim.y = 1; qa[0].val.clusterDim.z = 1;
+      qc.attrs = qa; qc.numAttrs = 1;
+      int n_clusters = 0;
+      e = cudaOccupancyMaxActiveClusters(&n_clusters, kern, &qc);
+      if (e != cudaSuccess || n_clusters <= 0) { set_error("cudaOccupancyMaxActiveClusters(gemm<%d,2>): %s (%d)", BN, cudaGetErrorString(e), n_clusters); max_pairs = 0; return 1; }
+      if (n_clusters < max_pairs) max_pairs = n_clusters;
+    }
   }
   CUtensorMap ta, tb, tc, tr;
   if (make_tmap(&ta, a.A, a.M, a.K, a.lda, a.batch, a.a_batch_stride, BM)) return 1;
   const bool b_batched = a.batch > 1 && a.b_batch_stride != 0;
-  if (make_tmap(&tb, a.B, a.N, a.K, a.ldb, b_batched ? a.batch : 1, a.b_batch_stride, BN)) return 1;
+  if (make_tmap(&tb, a.B, a.N, a.K, a.ldb, b_batched ? a.batch : 1, a.b_batch_stride, Cfg::B_ROWS)) return 1;
   const int out_bf16 = a.out_bf16 != nullptr;
   if (make_tmap_out(&tc, out_bf16 ? (const void*)a.out_bf16 : (const void*)a.out_f32, out_bf16, a.M, a.N, a.ldc, a.batch,
                     a.c_batch_stride)) return 1;
@@ -391,45 +423,60 @@ static int launch_gemm(const GemmArgs& a, cudaStream_t stream) {
   }
   GemmKernelParams p;
   p.M = a.M; p.N = a.N; p.K = a.K; p.batch = a.batch;
-  p.tiles_m = (a.M + BM - 1) / BM; p.tiles_n = (a.N + BN - 1) / BN; p.num_kb = (a.K + BK - 1) / BK;
+  p.tiles_m = (a.M + BM * NCTA - 1) / (BM * NCTA); p.tiles_n = (a.N + BN - 1) / BN; p.num_kb = (a.K + BK - 1) / BK;
   p.b_batched = b_batched ? 1 : 0;
   p.alpha = a.alpha; p.bias = a.bias; p.bias_along_m = a.bias_along_m; p.act = a.act; p.gamma = a.gamma;
   p.has_res = a.residual ? 1 : 0; p.res_batched = res_batched ? 1 : 0; p.res_row_mod = a.res_row_mod;
   p.out_is_bf16 = out_bf16;
   { static int dbg = -1; if (dbg < 0) { const char* e = getenv("SAM2B_GEMM_DBG"); dbg = e ? atoi(e) : 0; } p.dbg = dbg; }
   const long tiles = (long)p.tiles_m * p.tiles_n * p.batch;
-  const int grid = (int)(tiles < num_sms() ? tiles : num_sms());
+  const int grid = (int)(tiles < max_pairs ? tiles : max_pairs) * NCTA;
   char nm[96];
-  if (g_prof_on) snprintf(nm, sizeof(nm), "gemm m%d n%d k%d b%d bn%d md%d act%d%s%s", a.M, a.N, a.K, a.batch, BN, MODE, a.act, a.residual ? " res" : "", a.out_bf16 ? " o16" : " o32");
+  if (g_prof_on) snprintf(nm, sizeof(nm), "gemm m%d n%d k%d b%d bn%d%s md%d act%d%s%s", a.M, a.N, a.K, a.batch, BN, NCTA == 2 ? "x2" : "", MODE, a.act, a.residual ? " res" : "", a.out_bf16 ? " o16" : " o32");
   const double esz = a.out_bf16 ? 2.0 : 4.0;
   ProfRange pr(stream, nm, 2.0 * a.M * a.N * (double)a.K * a.batch,
                ((double)a.M * a.K * 2 + (b_batched ? 1.0 : 1.0 / a.batch) * (double)a.N * a.K * 2 + (double)a.M * a.N * (esz + (a.residual ? 4.0 : 0.0))) * a.batch);
-  gemm_bf16_tcgen05_kernel<BN, MODE><<<grid, NUM_THREADS, Cfg::SMEM, stream>>>(ta, tb, tc, tr, p);
-  SAM2B_CHECK_LAUNCH("gemm_bf16_tcgen05");
+  if (NCTA == 2) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(grid); cfg.blockDim = dim3(NUM_THREADS); cfg.dynamicSmemBytes = Cfg::SMEM; cfg.stream = stream;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeClusterDimension; at[0].val.clusterDim.x = 2; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+    cfg.attrs = at; cfg.numAttrs = 1;
+    cudaError_t e = cudaLaunchKernelEx(&cfg, kern, ta, tb, tc, tr, p);
+    if (e != cudaSuccess) { set_error("cudaLaunchKernelEx(gemm<%d,2>): %s", BN, cudaGetErrorString(e)); return 1; }
+    ++g_launch_count;
+  } else {
+    kern<<<grid, NUM_THREADS, Cfg::SMEM, stream>>>(ta, tb, tc, tr, p);
+    SAM2B_CHECK_LAUNCH("gemm_bf16_tcgen05");
+  }
   return 0;
 }
 
 
 // One translation unit per BLOCK_N (parallel compilation): the specialised modes for the large tiles, generic otherwise.
-#define SAM2B_GEMM_INSTANTIATE_FULL(BN_)                                                     \
-  int launch_gemm_bn##BN_(const GemmArgs& a, int mode, cudaStream_t stream) {                 \
-    switch (mode) {                                                                          \
-      case MODE_BF16_BIAS: return launch_gemm<BN_, MODE_BF16_BIAS>(a, stream);               \
-      case MODE_BF16_BIAS_GELU: return launch_gemm<BN_, MODE_BF16_BIAS_GELU>(a, stream);     \
-      case MODE_F32_BIAS_RES: return launch_gemm<BN_, MODE_F32_BIAS_RES>(a, stream);         \
-      default: return launch_gemm<BN_, MODE_GENERIC>(a, stream);                             \
-    }                                                                                        \
+// `cta2`: run as CTA pairs (256 x BN tiles).
+#define SAM2B_GEMM_DISPATCH_MODES(BN_, NCTA_)                                                   \
+  switch (mode) {                                                                              \
+    case MODE_BF16_BIAS: return launch_gemm<BN_, MODE_BF16_BIAS, NCTA_>(a, stream);            \
+    case MODE_BF16_BIAS_GELU: return launch_gemm<BN_, MODE_BF16_BIAS_GELU, NCTA_>(a, stream);  \
+    case MODE_F32_BIAS_RES: return launch_gemm<BN_, MODE_F32_BIAS_RES, NCTA_>(a, stream);      \
+    default: return launch_gemm<BN_, MODE_GENERIC, NCTA_>(a, stream);                          \
   }
-#define SAM2B_GEMM_INSTANTIATE_GENERIC(BN_)                                                  \
-  int launch_gemm_bn##BN_(const GemmArgs& a, int, cudaStream_t stream) { return launch_gemm<BN_, MODE_GENERIC>(a, stream); }
+#define SAM2B_GEMM_INSTANTIATE_FULL(BN_)                                                       \
+  int launch_gemm_bn##BN_(const GemmArgs& a, int mode, int cta2, cudaStream_t stream) {         \
+    if (cta2) { SAM2B_GEMM_DISPATCH_MODES(BN_, 2) }                                            \
+    SAM2B_GEMM_DISPATCH_MODES(BN_, 1)                                                          \
+  }
+#define SAM2B_GEMM_INSTANTIATE_GENERIC(BN_)                                                    \
+  int launch_gemm_bn##BN_(const GemmArgs& a, int, int, cudaStream_t stream) { return launch_gemm<BN_, MODE_GENERIC, 1>(a, stream); }
 
-int launch_gemm_bn256(const GemmArgs& a, int mode, cudaStream_t stream);
-int launch_gemm_bn224(const GemmArgs& a, int mode, cudaStream_t stream);
-int launch_gemm_bn192(const GemmArgs& a, int mode, cudaStream_t stream);
-int launch_gemm_bn160(const GemmArgs& a, int mode, cudaStream_t stream);
-int launch_gemm_bn128(const GemmArgs& a, int mode, cudaStream_t stream);
-int launch_gemm_bn96(const GemmArgs& a, int mode, cudaStream_t stream);
-int launch_gemm_bn64(const GemmArgs& a, int mode, cudaStream_t stream);
-int launch_gemm_bn32(const GemmArgs& a, int mode, cudaStream_t stream);
+int launch_gemm_bn256(const GemmArgs& a, int mode, int cta2, cudaStream_t stream);
+int launch_gemm_bn224(const GemmArgs& a, int mode, int cta2, cudaStream_t stream);
+int launch_gemm_bn192(const GemmArgs& a, int mode, int cta2, cudaStream_t stream);
+int launch_gemm_bn160(const GemmArgs& a, int mode, int cta2, cudaStream_t stream);
+int launch_gemm_bn128(const GemmArgs& a, int mode, int cta2, cudaStream_t stream);
+int launch_gemm_bn96(const GemmArgs& a, int mode, int cta2, cudaStream_t stream);
+int launch_gemm_bn64(const GemmArgs& a, int mode, int cta2, cudaStream_t stream);
+int launch_gemm_bn32(const GemmArgs& a, int mode, int cta2, cudaStream_t stream);
 
 }  // namespace sam2b

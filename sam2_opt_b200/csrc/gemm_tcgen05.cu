@@ -76,18 +76,29 @@ int make_tmap_out(CUtensorMap* m, const void* ptr, int is_bf16, long rows, long 
   return 0;
 }
 
-static int pick_bn(const GemmArgs& a) {
+// Tile choice: BLOCK_N and whether CTA pairs (256-row tiles) are used.  Cost model per tile ~ MMA time (prop. to BN) plus a
+// fixed overhead (epilogue drain, barriers); a pair tile moves 1/3 less operand data per flop and has a deeper smem ring.
+static void pick_tile(const GemmArgs& a, int* bn_out, int* cta2_out) {
   static const int cand[] = {256, 224, 192, 160, 128, 96, 64, 32};
-  const long tiles_m = (a.M + BM - 1) / BM;
-  double best = 1e30; int best_bn = 128;
-  for (int bn : cand) {
-    const long tiles = tiles_m * ((a.N + bn - 1) / bn) * a.batch;
-    const long waves = (tiles + num_sms() - 1) / num_sms();
-    // per-tile cost ~ MMA time (prop. to BN) + fixed per-tile overhead (epilogue drain, barriers)
-    const double cost = (double)waves * (bn + 64.0);
-    if (cost < best - 1e-9) { best = cost; best_bn = bn; }
+  static int allow2 = -1;
+  if (allow2 < 0) { const char* e = getenv("SAM2B_GEMM_2CTA"); allow2 = e ? atoi(e) : 1; }
+  double best = 1e30; int best_bn = 128, best_c2 = 0;
+  for (int c2 = 0; c2 <= (allow2 ? 1 : 0); ++c2) {
+    const int tm = c2 ? 2 * BM : BM;
+    const long units = c2 ? num_sms() / 2 : num_sms();
+    const long tiles_m = (a.M + tm - 1) / tm;
+    for (int bn : cand) {
+      if (c2 && bn < 128) continue;                      // pair kernels are instantiated for the large tiles only
+      const long tiles = tiles_m * ((a.N + bn - 1) / bn) * a.batch;
+      // measured on B200 (tests/_gemm_bench.py): pairs win 3-7 % on the K >= 1152 stage-4 shapes (long main loop), and lose
+      // a few % on the K = 576 / 288 / 144 shapes whose time is set by the epilogue, not by operand traffic
+      if (c2 && (tiles < units || a.K < 1024 || (a.res_row_mod && a.res_row_mod % tm))) continue;
+      const long waves = (tiles + units - 1) / units;
+      const double cost = (double)waves * (c2 ? 0.93 * bn + 64.0 : bn + 64.0);
+      if (cost < best - 1e-9) { best = cost; best_bn = bn; best_c2 = c2; }
+    }
   }
-  return best_bn;
+  *bn_out = best_bn; *cta2_out = best_c2;
 }
 
 int gemm_bf16(const GemmArgs& a, cudaStream_t stream) {
@@ -98,7 +109,11 @@ int gemm_bf16(const GemmArgs& a, cudaStream_t stream) {
     set_error("gemm: res_row_mod=%d must be a multiple of %d", a.res_row_mod, BM);
     return 1;
   }
-  const int bn = a.force_bn ? a.force_bn : pick_bn(a);
+  int bn = 0, cta2 = 0;
+  if (a.force_bn >= 1000) { bn = a.force_bn - 1000; cta2 = 1; }          // 1000 + BLOCK_N: force CTA pairs (tests / tuning)
+  else if (a.force_bn) bn = a.force_bn;
+  else pick_tile(a, &bn, &cta2);
+  if (cta2 && (bn < 128 || (a.res_row_mod && a.res_row_mod % (2 * BM)))) { set_error("gemm: CTA pairs need BLOCK_N >= 128 and res_row_mod %% 256 == 0"); return 1; }
   // compile-time specialised epilogues for the trunk's three dominant GEMM forms (fewer instructions per element)
   int mode = MODE_GENERIC;
   const bool plain = a.alpha == 1.0f && a.bias && !a.bias_along_m && !a.gamma && (a.N % 4) == 0 && !getenv("SAM2B_GEMM_GENERIC");
@@ -106,14 +121,14 @@ int gemm_bf16(const GemmArgs& a, cudaStream_t stream) {
   else if (plain && a.out_bf16 && !a.residual && a.act == ACT_GELU) mode = MODE_BF16_BIAS_GELU;
   else if (plain && a.out_f32 && a.residual && a.act == ACT_NONE) mode = MODE_F32_BIAS_RES;
   switch (bn) {
-    case 256: return launch_gemm_bn256(a, mode, stream);
-    case 224: return launch_gemm_bn224(a, mode, stream);
-    case 192: return launch_gemm_bn192(a, mode, stream);
-    case 160: return launch_gemm_bn160(a, mode, stream);
-    case 128: return launch_gemm_bn128(a, mode, stream);
-    case 96: return launch_gemm_bn96(a, mode, stream);
-    case 64: return launch_gemm_bn64(a, mode, stream);
-    case 32: return launch_gemm_bn32(a, mode, stream);
+    case 256: return launch_gemm_bn256(a, mode, cta2, stream);
+    case 224: return launch_gemm_bn224(a, mode, cta2, stream);
+    case 192: return launch_gemm_bn192(a, mode, cta2, stream);
+    case 160: return launch_gemm_bn160(a, mode, cta2, stream);
+    case 128: return launch_gemm_bn128(a, mode, cta2, stream);
+    case 96: return launch_gemm_bn96(a, mode, cta2, stream);
+    case 64: return launch_gemm_bn64(a, mode, cta2, stream);
+    case 32: return launch_gemm_bn32(a, mode, cta2, stream);
   }
   set_error("gemm: unsupported BLOCK_N %d (256, 224, 192, 160, 128, 96, 64, 32)", bn);
   return 1;

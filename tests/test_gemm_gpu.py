@@ -105,3 +105,44 @@ def test_gemm_many_tiles_persistent_phases():
     b = (torch.randn(N, K, device="cuda", generator=g) / K ** 0.5).bfloat16()
     out = ops.gemm(a, b, block_n=64)
     _close(out, _ref(a, b), 2e-3)
+
+
+# ---- CTA pairs (cluster of 2, tcgen05 cta_group::2, 256 x BLOCK_N tiles): block_n = 1000 + BLOCK_N forces them ----
+@pytest.mark.parametrize("bn", [128, 160, 192, 224, 256])
+def test_gemm_cta_pairs_every_block_n(bn):
+    from sam2_opt_b200 import ops
+    g = torch.Generator(device="cuda").manual_seed(100 + bn)
+    M, N, K = 1000, 1008, 328            # ragged M (not a multiple of 256 or 128), ragged N and K
+    a = torch.randn(M, K, device="cuda", generator=g).bfloat16()
+    b = (torch.randn(N, K, device="cuda", generator=g) / K ** 0.5).bfloat16()
+    bias = torch.randn(N, device="cuda", generator=g)
+    out = ops.gemm(a, b, bias=bias, block_n=1000 + bn)
+    torch.cuda.synchronize()
+    _close(out, _ref(a, b, bias), 2e-3)
+
+
+@pytest.mark.parametrize("M,N,K,bn", [(65536, 1728, 576, 256), (65536, 576, 2304, 192), (16384, 2304, 576, 256), (128 * 148 * 3, 256, 1152, 128)])
+def test_gemm_cta_pairs_epilogues_persistent(M, N, K, bn):
+    """Trunk forms on pair tiles, with enough tiles per pair that every barrier ring wraps several times."""
+    from sam2_opt_b200 import ops
+    g = torch.Generator(device="cuda").manual_seed(M % 1000 + N + K)
+    a = torch.randn(M, K, device="cuda", generator=g).bfloat16()
+    b = (torch.randn(N, K, device="cuda", generator=g) / K ** 0.5).bfloat16()
+    bias = torch.randn(N, device="cuda", generator=g)
+    res = torch.randn(M, N, device="cuda", generator=g)
+    _close(ops.gemm(a, b, bias=bias, out_dtype=torch.bfloat16, block_n=1000 + bn), _ref(a, b, bias), 1e-2)
+    _close(ops.gemm(a, b, bias=bias, act="gelu", out_dtype=torch.bfloat16, block_n=1000 + bn), _ref(a, b, bias, "gelu"), 1e-2)
+    _close(ops.gemm(a, b, bias=bias, residual=res, block_n=1000 + bn), _ref(a, b, bias, residual=res), 2e-3)
+    res_small = torch.randn(512, N, device="cuda", generator=g)
+    _close(ops.gemm(a, b, residual=res_small, res_row_mod=512, block_n=1000 + bn), _ref(a, b, residual=res_small.repeat(M // 512, 1)), 2e-3)
+    torch.cuda.synchronize()
+
+
+def test_gemm_cta_pairs_batched():
+    from sam2_opt_b200 import ops
+    g = torch.Generator(device="cuda").manual_seed(13)
+    n, M, N, K = 3, 4096, 4100, 256
+    a = torch.randn(n, M, K, device="cuda", generator=g).bfloat16()
+    b = (torch.randn(n, N, K, device="cuda", generator=g) / K ** 0.5).bfloat16()
+    out = ops.gemm(a, b, alpha=0.0625, block_n=1256)
+    _close(out, 0.0625 * torch.einsum("bmk,bnk->bmn", a.float(), b.float()), 2e-3)
