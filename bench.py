@@ -124,6 +124,8 @@ def main():
     ap.add_argument("--batch", type=int, default=32, help="images per GPU per step (configs[1]: 32)")
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--video-frames", type=int, default=40, help="frames of the propagate_in_video leg (0 = skip it)")
+    ap.add_argument("--video-objects", type=int, default=1)
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference(args)
@@ -219,6 +221,42 @@ def main():
                 "flops_per_launch_avg": g_fl / max(1, len(g)),
                 "note": "algorithmic 2MNK flops of every GEMM launch of one step / sum of their CUDA-event durations on the launching stream"}
 
+    # ---- second headline metric (BASELINE.json: "video frames/sec propagated"): propagate_in_video through the public
+    # predictor API, one synthetic clip and one prompted object per rank (videos shard across GPUs, config 3/4 shapes)
+    video = None
+    if args.video_frames > 0:
+        from sam2_opt_b200.predictor import SAM2VideoPredictor
+        from sam2_opt_b200.synth import synth_video
+        eng.release()
+        vp = SAM2VideoPredictor(make_weights(0), device=dev)
+        clip = synth_video(args.video_frames, seed=1 + rank).pin_memory()
+        t_steady, n_steady, t_all = 0.0, 0, 0.0
+        for rep in range(2):                      # first pass warms allocator / workspaces
+            st = vp.init_state(clip)
+            for o in range(args.video_objects):
+                g = max(1, int(args.video_objects ** 0.5 + 0.999))
+                xy = [512.0, 512.0] if args.video_objects == 1 else [128 + 768.0 * (o % g) / max(1, g - 1), 128 + 768.0 * (o // g) / max(1, g - 1)]
+                vp.add_new_points_or_box(st, 0, o, points=[xy], labels=[1])
+            barrier()
+            stamps = [time.perf_counter()]
+            for t, ids, masks in vp.propagate_in_video(st):
+                (masks > 0).any().item()          # the caller consumes every frame's masks (D2H read per frame)
+                stamps.append(time.perf_counter())
+            if rep == 1:
+                t_all = stamps[-1] - stamps[0]
+                s0 = min(16, len(stamps) - 2)      # steady state: full 7-frame bank + 16 object pointers from frame 16 on
+                t_steady, n_steady = stamps[-1] - stamps[s0], len(stamps) - 1 - s0
+        vt = torch.tensor([t_all, t_steady], device=dev, dtype=torch.float64)
+        if world > 1:
+            dist.all_reduce(vt, op=dist.ReduceOp.MAX)
+        t_all, t_steady = vt.tolist()
+        video = {"metric": "video frames/sec propagated (SAM2VideoPredictor.propagate_in_video)", "unit": "frames/s",
+                 "value_steady": world * n_steady / t_steady, "value_overall": world * args.video_frames / t_all,
+                 "frames_per_video": args.video_frames, "objects_per_video": args.video_objects, "videos": world,
+                 "object_frames_per_s_steady": world * args.video_objects * n_steady / t_steady,
+                 "timing": "host wall clock around the generator incl. H2D of frames and a D2H read of every frame's masks, max over ranks; steady = frames >= 16 (7-frame memory bank, 16 pointers)"}
+        vp.release()
+
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         v, cores, times = cpu_reference_images_per_s(1, 2, 1)
@@ -238,7 +276,7 @@ def main():
             "clocks": clk.summary(), "gpu_launches": int(launches),
             "e2e": {"value": e2e_value, "unit": "images/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "api": "Engine.image_encode_host -> sam2b_image_encode_host (pinned host in/out)"},
-            "roofline": roof, "cpu_baseline": cpu,
+            "roofline": roof, "cpu_baseline": cpu, "video": video,
         }))
     if world > 1:
         dist.destroy_process_group()
