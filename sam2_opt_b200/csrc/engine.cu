@@ -710,6 +710,28 @@ int sam2b_op_gemm(const void* a, int64_t lda, int64_t a_bs, const void* b, int64
   g.force_bn = force_block_n;
   return gemm_bf16(g, reinterpret_cast<cudaStream_t>(stream));
 }
+int sam2b_op_gemm_ln_producer(const void* a, const void* b, int m, int n, int k, const float* bias, const float* residual,
+                              float* out_f32, void* out2_bf16, float* stats, int stats_capacity_parts, int* parts,
+                              int force_block_n, void* stream) {
+  GemmArgs g;
+  g.A = reinterpret_cast<const bf16*>(a); g.lda = k; g.B = reinterpret_cast<const bf16*>(b); g.ldb = k;
+  g.M = m; g.N = n; g.K = k; g.bias = bias; g.residual = residual; g.ld_res = n;
+  g.out_f32 = out_f32; g.ldc = n; g.out2_bf16 = reinterpret_cast<bf16*>(out2_bf16); g.ldc2 = n;
+  g.stats_out = stats; g.stats_capacity_parts = stats_capacity_parts; g.stats_parts_out = parts;
+  g.force_bn = force_block_n;
+  return gemm_bf16(g, reinterpret_cast<cudaStream_t>(stream));
+}
+int sam2b_op_gemm_ln_consumer(const void* a, const void* b, int m, int n, int k, const float* bias, const float* colsum,
+                              const float* stats, int parts, float eps, int act, float* out_f32, void* out_bf16,
+                              int force_block_n, void* stream) {
+  GemmArgs g;
+  g.A = reinterpret_cast<const bf16*>(a); g.lda = k; g.B = reinterpret_cast<const bf16*>(b); g.ldb = k;
+  g.M = m; g.N = n; g.K = k; g.bias = bias; g.act = act;
+  g.out_f32 = out_f32; g.out_bf16 = reinterpret_cast<bf16*>(out_bf16); g.ldc = n;
+  g.ln_stats = stats; g.ln_parts = parts; g.ln_eps = eps; g.ln_colsum = colsum;
+  g.force_bn = force_block_n;
+  return gemm_bf16(g, reinterpret_cast<cudaStream_t>(stream));
+}
 int sam2b_op_layernorm(const float* x, const float* gamma, const float* beta, float eps, void* y_bf16, float* y_f32,
                        int64_t rows, int c, void* stream) {
   return layernorm_rows(x, gamma, beta, eps, reinterpret_cast<bf16*>(y_bf16), y_f32, rows, c, reinterpret_cast<cudaStream_t>(stream));

@@ -19,7 +19,11 @@
 namespace sam2b {
 
 // epilogue specialisations (compile-time): everything not listed is off / alpha = 1 / bias along N
-enum GemmMode { MODE_GENERIC = 0, MODE_BF16_BIAS = 1, MODE_BF16_BIAS_GELU = 2, MODE_F32_BIAS_RES = 3 };
+// MODE_F32_BIAS_RES_LN: MODE_F32_BIAS_RES that also emits what the NEXT LayerNorm needs -- a bf16 copy of its fp32 output and
+// per-row partial sums (sum x, sum x^2 per 32-column-chunk parity of every N tile) -- so that LayerNorm never runs as a kernel:
+// the consuming GEMM multiplies the raw bf16 rows with gamma-scaled weights and finishes the normalisation in its epilogue
+// (LN(x) W^T = rstd (x W'^T) - rstd mu colsum(W') + (b + W beta), W' = W diag(gamma)).
+enum GemmMode { MODE_GENERIC = 0, MODE_BF16_BIAS = 1, MODE_BF16_BIAS_GELU = 2, MODE_F32_BIAS_RES = 3, MODE_F32_BIAS_RES_LN = 4 };
 
 int make_tmap(CUtensorMap* m, const bf16* ptr, long rows, long K, long ld, long batch, long batch_stride, int box_rows);
 int make_tmap_out(CUtensorMap* m, const void* ptr, int is_bf16, long rows, long cols, long ld, long batch, long batch_stride);
@@ -44,13 +48,17 @@ struct GemmKernelParams {
   const float* gamma;
   int has_res; int res_batched; int res_row_mod;
   int out_is_bf16;
+  // LayerNorm fold, consumer side: rows of A are raw (un-normalised); ln_stats [M][ln_parts][2] partial (sum, sum of squares)
+  const float* ln_stats; int ln_parts; float ln_inv_c; float ln_eps; const float* ln_colsum;
+  // producer side (MODE_F32_BIAS_RES_LN): partial sums of this GEMM's output rows, [M][2 * tiles_n][2]
+  float* stats_out;
   int dbg;   // timing experiments (SAM2B_GEMM_DBG): 1 = no TMA store, 2 = no proxy fence, 4 = no staging writes
 };
 
 // NCTA = 2: a CTA pair (cluster of 2, `tcgen05.mma.cta_group::2`) works on a 256 x BN tile.  Each CTA holds 128 rows of A and
 // of the accumulator and HALF of the B tile (BN/2 rows) in its own shared memory, so a CTA moves (128 + BN/2) x 64 operands per
 // k-block instead of (128 + BN) x 64: one third less L2 -> SM traffic at BN = 256 and a deeper ring in the same smem.
-template <int BN, int NCTA = 1>
+template <int BN, int NCTA = 1, int MODE = 0>
 struct GemmCfg {
   static constexpr int NACC = BN <= 128 ? 4 : 2;
   static constexpr int ACC_STRIDE = 512 / NACC;
@@ -61,7 +69,9 @@ struct GemmCfg {
   // Epilogue staging per warp: 32 rows x 128 B (32 fp32 or, for bf16, 32 rows x 64 B), the box of one TMA store.
   // BN <= 192 leaves room for two 4 KB buffers per warp (store of chunk i overlaps chunk i+1, residual prefetch);
   // BN > 192 gets one 4 KB buffer (two 2 KB buffers for bf16 outputs).
-  static constexpr int EPI_WARP_BYTES = BN > 192 ? 4096 : 8192;
+  // MODE_F32_BIAS_RES_LN adds a 2 KB bf16 staging box per warp behind the fp32 buffers.
+  static constexpr int EPI_F32_BYTES = BN > 192 ? 4096 : 8192;
+  static constexpr int EPI_WARP_BYTES = EPI_F32_BYTES + (MODE == MODE_F32_BIAS_RES_LN ? 2048 : 0);
   static constexpr int EPI_SMEM = NUM_EPI_WARPS * EPI_WARP_BYTES;
   static constexpr int AVAIL = SMEM_TOTAL - EPI_SMEM - 1024 /*align slack*/ - BAR_BYTES;
   static constexpr int STAGES = (AVAIL / STAGE) > 8 ? 8 : (AVAIL / STAGE);
@@ -88,8 +98,8 @@ template <int BN, int MODE, int NCTA>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
 gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b,
                          const __grid_constant__ CUtensorMap tma_c, const __grid_constant__ CUtensorMap tma_r,
-                         const GemmKernelParams p) {
-  using Cfg = GemmCfg<BN, NCTA>;
+                         const __grid_constant__ CUtensorMap tma_c2, const GemmKernelParams p) {
+  using Cfg = GemmCfg<BN, NCTA, MODE>;
   constexpr int STAGES = Cfg::STAGES;
   constexpr int TILE_M = BM * NCTA;
   extern __shared__ uint8_t smem_raw[];
@@ -117,6 +127,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid
     tma_prefetch_desc(&tma_b);
     tma_prefetch_desc(&tma_c);
     if (p.has_res) tma_prefetch_desc(&tma_r);
+    if (MODE == MODE_F32_BIAS_RES_LN) tma_prefetch_desc(&tma_c2);
   }
   if (warp == 1 && lane == 0) {
     for (int i = 0; i < STAGES; ++i) { mbar_init(&full_bar[i], 1); mbar_init(&empty_bar[i], 1); }
@@ -202,12 +213,15 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid
     constexpr int NCHUNK = BN / 32;
     constexpr int WB = Cfg::EPI_WARP_BYTES;
     constexpr bool GEN = MODE == MODE_GENERIC;
+    constexpr bool LNP = MODE == MODE_F32_BIAS_RES_LN;          // producer of LayerNorm inputs
     const bool bf = GEN ? (p.out_is_bf16 != 0) : (MODE == MODE_BF16_BIAS || MODE == MODE_BF16_BIAS_GELU);
-    const bool has_res = GEN ? (p.has_res != 0) : (MODE == MODE_F32_BIAS_RES);
+    const bool has_res = GEN ? (p.has_res != 0) : (MODE == MODE_F32_BIAS_RES || LNP);
+    const bool ln_fold = !LNP && MODE != MODE_F32_BIAS_RES && p.ln_stats != nullptr;   // consumer of LayerNorm inputs
     const bool bias_n = GEN ? (p.bias != nullptr && !p.bias_along_m) : true;
     const int act = GEN ? p.act : (MODE == MODE_BF16_BIAS_GELU ? (int)ACT_GELU : (int)ACT_NONE);
     const uint32_t buf_bytes = bf ? 2048u : 4096u;
-    const bool two_buf = bf || WB >= 8192;
+    const bool two_buf = bf || Cfg::EPI_F32_BYTES >= 8192;
+    const uint32_t buf16 = smem_u32(smem_epi + we * WB) + Cfg::EPI_F32_BYTES;     // LNP: bf16 copy staging
     const uint32_t buf_base = smem_u32(smem_epi + we * WB);
     uint64_t* my_res_bar = res_bar + 2 * we;
     const uint32_t row_f32 = (uint32_t)lane * 128, xor_f32 = (uint32_t)(lane & 7) << 4;
@@ -252,6 +266,27 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid
           }
         }
       };
+      // LayerNorm-fold consumer: o[n] += d * colsum[n] for the 32 columns of chunk c (one float4 in flight at a time)
+      auto fold_colsum = [&](int c, float d, float4 (&o)[8]) {
+        const int col0 = n0 + c * 32;
+        if (col0 + 32 <= p.N) {
+          const float4* src = reinterpret_cast<const float4*>(p.ln_colsum + col0);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            const float4 sv = __ldg(src + j);
+            o[j].x = fmaf(d, sv.x, o[j].x); o[j].y = fmaf(d, sv.y, o[j].y); o[j].z = fmaf(d, sv.z, o[j].z); o[j].w = fmaf(d, sv.w, o[j].w);
+          }
+        } else {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            const int col = col0 + 4 * j;
+            if (col < p.N) o[j].x = fmaf(d, __ldg(p.ln_colsum + col), o[j].x);
+            if (col + 1 < p.N) o[j].y = fmaf(d, __ldg(p.ln_colsum + col + 1), o[j].y);
+            if (col + 2 < p.N) o[j].z = fmaf(d, __ldg(p.ln_colsum + col + 2), o[j].z);
+            if (col + 3 < p.N) o[j].w = fmaf(d, __ldg(p.ln_colsum + col + 3), o[j].w);
+          }
+        }
+      };
       const bool first_live = rows_live && half < NCHUNK && (n0 + half * 32 < p.N);
       if (has_res && first_live && lane == 0) {
         if (two_buf) bulk_wait_read<1>(); else bulk_wait_read<0>();
@@ -261,6 +296,20 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid
       load_vec8(bias_n ? p.bias : nullptr, half, 0.f, bn);
       float bias_m = 0.f;
       if (GEN) bias_m = (p.bias && p.bias_along_m && row_g + lane < p.M) ? __ldg(p.bias + row_g + lane) : 0.f;
+      float ln_a = 1.f, ln_d = 0.f;                      // v = ln_a * acc + (ln_d * colsum[n] + bias[n])
+      if (ln_fold) {
+        float s1 = 0.f, s2 = 0.f;
+        if (row_g + lane < p.M) {
+          const float2* st = reinterpret_cast<const float2*>(p.ln_stats) + (long)(row_g + lane) * p.ln_parts;
+          for (int k = 0; k < p.ln_parts; ++k) { const float2 t = __ldg(st + k); s1 += t.x; s2 += t.y; }
+        }
+        const float mu = s1 * p.ln_inv_c;
+        const float var = fmaxf(fmaf(s2, p.ln_inv_c, -mu * mu), 0.f);
+        ln_a = rsqrtf(var + p.ln_eps);
+        ln_d = -ln_a * mu;
+        fold_colsum(half, ln_d, bn);
+      }
+      float st1 = 0.f, st2 = 0.f;                         // LNP: this warp's partial row sums over its chunks of the tile
       mbar_wait(&tmem_full[acc], acc_phase);
       tc_fence_after();
       const uint32_t taddr = tmem_base + acc * Cfg::ACC_STRIDE + ((uint32_t)(q * 32) << 16);
@@ -291,7 +340,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid
           __syncwarp();
           float4 v[8];
           if (GEN) {
-            const float al = p.alpha;
+            const float al = p.alpha * ln_a;
 #pragma unroll
             for (int j = 0; j < 8; ++j) {
               v[j].x = fmaf(__uint_as_float(r[4 * j]), al, bn[j].x + bias_m);
@@ -302,15 +351,18 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid
           } else {
 #pragma unroll
             for (int j = 0; j < 8; ++j) {
-              v[j].x = __uint_as_float(r[4 * j]) + bn[j].x;
-              v[j].y = __uint_as_float(r[4 * j + 1]) + bn[j].y;
-              v[j].z = __uint_as_float(r[4 * j + 2]) + bn[j].z;
-              v[j].w = __uint_as_float(r[4 * j + 3]) + bn[j].w;
+              v[j].x = fmaf(__uint_as_float(r[4 * j]), ln_a, bn[j].x);
+              v[j].y = fmaf(__uint_as_float(r[4 * j + 1]), ln_a, bn[j].y);
+              v[j].z = fmaf(__uint_as_float(r[4 * j + 2]), ln_a, bn[j].z);
+              v[j].w = fmaf(__uint_as_float(r[4 * j + 3]), ln_a, bn[j].w);
             }
           }
           if (c + 2 < NCHUNK) {
             tmem_ld_x32(taddr + (c + 2) * 32, r);   // next chunk streams out of TMEM (and its bias out of L1) meanwhile
             load_vec8(bias_n ? p.bias : nullptr, c + 2, 0.f, bn);
+            if (ln_fold) {
+              fold_colsum(c + 2, ln_d, bn);
+            }
           }
           if (act == ACT_GELU) {
 #pragma unroll
@@ -337,6 +389,21 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid
               v[j].x += rv.x; v[j].y += rv.y; v[j].z += rv.z; v[j].w += rv.w;
             }
           }
+          if (LNP) {
+            // columns >= N hold exact zeros here (zero-filled B rows, guarded bias, zero-filled residual box)
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+              st1 += (v[j].x + v[j].y) + (v[j].z + v[j].w);
+              st2 = fmaf(v[j].x, v[j].x, st2); st2 = fmaf(v[j].y, v[j].y, st2); st2 = fmaf(v[j].z, v[j].z, st2); st2 = fmaf(v[j].w, v[j].w, st2);
+            }
+            if (lane == 0) bulk_wait_read<0>();          // the previous chunk's stores have left the bf16 staging box
+            __syncwarp();
+#pragma unroll
+            for (int j = 0; j < 4; ++j)
+              st_shared_u4(buf16 + row_b16 + (((uint32_t)j << 4) ^ xor_b16), pack_bf16x2(v[2 * j].x, v[2 * j].y),
+                           pack_bf16x2(v[2 * j].z, v[2 * j].w), pack_bf16x2(v[2 * j + 1].x, v[2 * j + 1].y),
+                           pack_bf16x2(v[2 * j + 1].z, v[2 * j + 1].w));
+          }
           if (p.dbg & 4) {
             if (v[0].x + v[3].y + v[5].z + v[7].w == 123.456f) st_shared_u4(buf, 0, 0, 0, 0);
           } else if (bf) {
@@ -355,15 +422,20 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid
           __syncwarp();
           if (lane == 0 && !(p.dbg & 1)) {
             tma_store_3d(&tma_c, buf, n0 + c * 32, row_g, b);
+            if (LNP) tma_store_3d(&tma_c2, buf16, n0 + c * 32, row_g, b);     // same bulk group as the fp32 box
             bulk_commit();
           }
           ++i;
         } else {
           if (c + 2 < NCHUNK) {
-            load_vec8(bias_n ? p.bias : nullptr, c + 2, 0.f, bn);
+            load_vec8(bias_n ? p.bias : nullptr, c + 2, 0.f, bn);   // (dead chunks: values unused, LN fold not needed)
             tmem_ld_x32(taddr + (c + 2) * 32, r);
           }
         }
+      }
+      if (LNP && p.stats_out != nullptr && row_g + lane < p.M) {
+        float2* so = reinterpret_cast<float2*>(p.stats_out) + ((long)b * p.M + row_g + lane) * (2 * p.tiles_n) + 2 * n_blk + half;
+        *so = make_float2(st1, st2);
       }
       if (half >= NCHUNK) {   // BN = 32: the second warp of each quarter has no chunk but still owes its arrival
         if (lane == 0) { if (NCTA == 2) mbar_arrive_cluster(&tmem_empty[acc], 0); else mbar_arrive(&tmem_empty[acc]); }
@@ -385,7 +457,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid
 // ------------------------------------------------------------------------------------------
 template <int BN, int MODE, int NCTA>
 static int launch_gemm(const GemmArgs& a, cudaStream_t stream) {
-  using Cfg = GemmCfg<BN, NCTA>;
+  using Cfg = GemmCfg<BN, NCTA, MODE>;
   static_assert(BN % 32 == 0 && BN >= 32 && BN <= 256, "BLOCK_N must be a multiple of 32");
   static_assert(Cfg::STAGES >= 3, "pipeline too shallow");
   static_assert(NCTA == 1 || (BN % 32 == 0 && (BN / 2) % 8 == 0), "a CTA pair splits the B tile in two halves of whole swizzle atoms");
@@ -407,7 +479,7 @@ static int launch_gemm(const GemmArgs& a, cudaStream_t stream) {
       if (n_clusters < max_pairs) max_pairs = n_clusters;
     }
   }
-  CUtensorMap ta, tb, tc, tr;
+  CUtensorMap ta, tb, tc, tr, tc2;
   if (make_tmap(&ta, a.A, a.M, a.K, a.lda, a.batch, a.a_batch_stride, BM)) return 1;
   const bool b_batched = a.batch > 1 && a.b_batch_stride != 0;
   if (make_tmap(&tb, a.B, a.N, a.K, a.ldb, b_batched ? a.batch : 1, a.b_batch_stride, Cfg::B_ROWS)) return 1;
@@ -421,6 +493,11 @@ static int launch_gemm(const GemmArgs& a, cudaStream_t stream) {
   } else {
     tr = tc;
   }
+  if (MODE == MODE_F32_BIAS_RES_LN) {
+    if (make_tmap_out(&tc2, a.out2_bf16, 1, a.M, a.N, a.ldc2, a.batch, a.c2_batch_stride)) return 1;
+  } else {
+    tc2 = tc;
+  }
   GemmKernelParams p;
   p.M = a.M; p.N = a.N; p.K = a.K; p.batch = a.batch;
   p.tiles_m = (a.M + BM * NCTA - 1) / (BM * NCTA); p.tiles_n = (a.N + BN - 1) / BN; p.num_kb = (a.K + BK - 1) / BK;
@@ -428,11 +505,13 @@ static int launch_gemm(const GemmArgs& a, cudaStream_t stream) {
   p.alpha = a.alpha; p.bias = a.bias; p.bias_along_m = a.bias_along_m; p.act = a.act; p.gamma = a.gamma;
   p.has_res = a.residual ? 1 : 0; p.res_batched = res_batched ? 1 : 0; p.res_row_mod = a.res_row_mod;
   p.out_is_bf16 = out_bf16;
+  p.ln_stats = a.ln_stats; p.ln_parts = a.ln_parts; p.ln_inv_c = a.ln_stats ? 1.0f / (float)a.K : 0.f; p.ln_eps = a.ln_eps;
+  p.ln_colsum = a.ln_colsum; p.stats_out = a.stats_out;
   { static int dbg = -1; if (dbg < 0) { const char* e = getenv("SAM2B_GEMM_DBG"); dbg = e ? atoi(e) : 0; } p.dbg = dbg; }
   const long tiles = (long)p.tiles_m * p.tiles_n * p.batch;
   const int grid = (int)(tiles < max_pairs ? tiles : max_pairs) * NCTA;
   char nm[96];
-  if (g_prof_on) snprintf(nm, sizeof(nm), "gemm m%d n%d k%d b%d bn%d%s md%d act%d%s%s", a.M, a.N, a.K, a.batch, BN, NCTA == 2 ? "x2" : "", MODE, a.act, a.residual ? " res" : "", a.out_bf16 ? " o16" : " o32");
+  if (g_prof_on) snprintf(nm, sizeof(nm), "gemm m%d n%d k%d b%d bn%d%s md%d act%d%s%s%s", a.M, a.N, a.K, a.batch, BN, NCTA == 2 ? "x2" : "", MODE, a.act, a.residual ? " res" : "", a.out_bf16 ? " o16" : " o32", a.ln_stats ? " ln" : "");
   const double esz = a.out_bf16 ? 2.0 : 4.0;
   ProfRange pr(stream, nm, 2.0 * a.M * a.N * (double)a.K * a.batch,
                ((double)a.M * a.K * 2 + (b_batched ? 1.0 : 1.0 / a.batch) * (double)a.N * a.K * 2 + (double)a.M * a.N * (esz + (a.residual ? 4.0 : 0.0))) * a.batch);
@@ -442,11 +521,11 @@ static int launch_gemm(const GemmArgs& a, cudaStream_t stream) {
     cudaLaunchAttribute at[1];
     at[0].id = cudaLaunchAttributeClusterDimension; at[0].val.clusterDim.x = 2; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
     cfg.attrs = at; cfg.numAttrs = 1;
-    cudaError_t e = cudaLaunchKernelEx(&cfg, kern, ta, tb, tc, tr, p);
+    cudaError_t e = cudaLaunchKernelEx(&cfg, kern, ta, tb, tc, tr, tc2, p);
     if (e != cudaSuccess) { set_error("cudaLaunchKernelEx(gemm<%d,2>): %s", BN, cudaGetErrorString(e)); return 1; }
     ++g_launch_count;
   } else {
-    kern<<<grid, NUM_THREADS, Cfg::SMEM, stream>>>(ta, tb, tc, tr, p);
+    kern<<<grid, NUM_THREADS, Cfg::SMEM, stream>>>(ta, tb, tc, tr, tc2, p);
     SAM2B_CHECK_LAUNCH("gemm_bf16_tcgen05");
   }
   return 0;
@@ -460,6 +539,7 @@ static int launch_gemm(const GemmArgs& a, cudaStream_t stream) {
     case MODE_BF16_BIAS: return launch_gemm<BN_, MODE_BF16_BIAS, NCTA_>(a, stream);            \
     case MODE_BF16_BIAS_GELU: return launch_gemm<BN_, MODE_BF16_BIAS_GELU, NCTA_>(a, stream);  \
     case MODE_F32_BIAS_RES: return launch_gemm<BN_, MODE_F32_BIAS_RES, NCTA_>(a, stream);      \
+    case MODE_F32_BIAS_RES_LN: return launch_gemm<BN_, MODE_F32_BIAS_RES_LN, NCTA_>(a, stream); \
     default: return launch_gemm<BN_, MODE_GENERIC, NCTA_>(a, stream);                          \
   }
 #define SAM2B_GEMM_INSTANTIATE_FULL(BN_)                                                       \

@@ -89,6 +89,7 @@ static void pick_tile(const GemmArgs& a, int* bn_out, int* cta2_out) {
     const long tiles_m = (a.M + tm - 1) / tm;
     for (int bn : cand) {
       if (c2 && bn < 128) continue;                      // pair kernels are instantiated for the large tiles only
+      if (a.out2_bf16 && bn < 128) continue;             // so is the LayerNorm-producer epilogue
       const long tiles = tiles_m * ((a.N + bn - 1) / bn) * a.batch;
       // measured on B200 (tests/_gemm_bench.py): pairs win 3-7 % on the K >= 1152 stage-4 shapes (long main loop), and lose
       // a few % on the K = 576 / 288 / 144 shapes whose time is set by the epilogue, not by operand traffic
@@ -119,7 +120,14 @@ int gemm_bf16(const GemmArgs& a, cudaStream_t stream) {
   const bool plain = a.alpha == 1.0f && a.bias && !a.bias_along_m && !a.gamma && (a.N % 4) == 0 && !getenv("SAM2B_GEMM_GENERIC");
   if (plain && a.out_bf16 && !a.residual && a.act == ACT_NONE) mode = MODE_BF16_BIAS;
   else if (plain && a.out_bf16 && !a.residual && a.act == ACT_GELU) mode = MODE_BF16_BIAS_GELU;
-  else if (plain && a.out_f32 && a.residual && a.act == ACT_NONE) mode = MODE_F32_BIAS_RES;
+  else if (plain && a.out_f32 && a.residual && a.act == ACT_NONE) mode = a.out2_bf16 ? MODE_F32_BIAS_RES_LN : MODE_F32_BIAS_RES;
+  if (a.out2_bf16) {
+    if (mode != MODE_F32_BIAS_RES_LN || bn < 128) { set_error("gemm: the LayerNorm-producer epilogue needs bias + fp32 residual, no activation, BLOCK_N >= 128"); return 1; }
+    const int parts = 2 * ((a.N + bn - 1) / bn);
+    if (a.stats_out && parts > a.stats_capacity_parts) { set_error("gemm: stats buffer holds %d parts per row, %d needed", a.stats_capacity_parts, parts); return 1; }
+    if (a.stats_parts_out) *a.stats_parts_out = parts;
+  }
+  if (a.ln_stats && (a.residual || !a.ln_colsum || a.ln_parts <= 0 || !a.bias || a.bias_along_m)) { set_error("gemm: LayerNorm-fold consumer needs bias along N, colsum, parts > 0 and no residual"); return 1; }
   switch (bn) {
     case 256: return launch_gemm_bn256(a, mode, cta2, stream);
     case 224: return launch_gemm_bn224(a, mode, cta2, stream);

@@ -50,7 +50,15 @@ struct GemmArgs {
   const float* gamma = nullptr;
   const float* residual = nullptr; long ld_res = 0; long res_batch_stride = 0; int res_row_mod = 0;
   float* out_f32 = nullptr; bf16* out_bf16 = nullptr; long ldc = 0; long c_batch_stride = 0;
-  int force_bn = 0;  // 0 = pick automatically
+  int force_bn = 0;  // 0 = pick automatically; 1000 + BLOCK_N forces CTA pairs
+  // ---- LayerNorm fold (see GemmMode in gemm_kernel.cuh) ----
+  // producer: also write a bf16 copy of the fp32 output and per-row partial (sum, sum x^2) into stats_out
+  // [batch*M][stats_parts][2]; the number of parts (2 * N tiles) is returned through *stats_parts_out.
+  bf16* out2_bf16 = nullptr; long ldc2 = 0; long c2_batch_stride = 0;
+  float* stats_out = nullptr; int stats_capacity_parts = 0; int* stats_parts_out = nullptr;
+  // consumer: A holds raw rows x; B holds W diag(gamma); bias holds b + W beta; ln_colsum[n] = sum_k B[n][k];
+  // the epilogue computes rstd * (acc - mu * colsum) + bias with (mu, rstd) from ln_stats [M][ln_parts][2] over K columns.
+  const float* ln_stats = nullptr; int ln_parts = 0; float ln_eps = 0.f; const float* ln_colsum = nullptr;
 };
 int gemm_bf16(const GemmArgs& a, cudaStream_t stream);
 

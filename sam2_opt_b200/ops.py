@@ -100,3 +100,34 @@ def attention_hd256(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor) -> torch.
     _lib.check(lib.sam2b_op_attention_hd256(_ptr(q), _ptr(k), _ptr(v), n, tq, lk, _ptr(out), _ptr(ws), _stream()),
                "op_attention_hd256")
     return out
+
+
+def gemm_ln_producer(a: torch.Tensor, b: torch.Tensor, bias: torch.Tensor, residual: torch.Tensor, block_n: int = 0):
+    """x = a @ b^T + bias + residual (fp32) -> (x, bf16(x), stats [M, parts, 2] partial (sum, sum x^2) per row)."""
+    lib = _lib.load()
+    M, K = a.shape
+    N = b.shape[0]
+    x = torch.empty((M, N), device=a.device, dtype=torch.float32)
+    xb = torch.empty((M, N), device=a.device, dtype=torch.bfloat16)
+    cap = 2 * ((N + 31) // 32)
+    stats = torch.zeros((M, cap, 2), device=a.device, dtype=torch.float32)
+    parts = C.c_int(0)
+    _lib.check(lib.sam2b_op_gemm_ln_producer(_ptr(a), _ptr(b), M, N, K, _ptr(bias), _ptr(residual), _ptr(x), _ptr(xb),
+                                             _ptr(stats), cap, C.byref(parts), int(block_n), _stream()), "op_gemm_ln_producer")
+    # the kernel wrote a dense [M, parts, 2] array at the start of the buffer
+    return x, xb, stats.flatten()[: M * parts.value * 2].view(M, parts.value, 2)
+
+
+def gemm_ln_consumer(xb: torch.Tensor, w_scaled: torch.Tensor, bias: torch.Tensor, colsum: torch.Tensor, stats: torch.Tensor,
+                     eps: float, act=None, out_dtype=torch.bfloat16, block_n: int = 0) -> torch.Tensor:
+    lib = _lib.load()
+    M, K = xb.shape
+    N = w_scaled.shape[0]
+    assert stats.is_contiguous() and stats.shape[0] == M
+    out = torch.empty((M, N), device=xb.device, dtype=out_dtype)
+    _lib.check(lib.sam2b_op_gemm_ln_consumer(_ptr(xb), _ptr(w_scaled), M, N, K, _ptr(bias), _ptr(colsum), _ptr(stats),
+                                             stats.shape[1], float(eps), ACT[act],
+                                             _ptr(out if out_dtype == torch.float32 else None),
+                                             _ptr(out if out_dtype == torch.bfloat16 else None), int(block_n), _stream()),
+               "op_gemm_ln_consumer")
+    return out

@@ -146,3 +146,40 @@ def test_gemm_cta_pairs_batched():
     b = (torch.randn(n, N, K, device="cuda", generator=g) / K ** 0.5).bfloat16()
     out = ops.gemm(a, b, alpha=0.0625, block_n=1256)
     _close(out, 0.0625 * torch.einsum("bmk,bnk->bmn", a.float(), b.float()), 2e-3)
+
+
+# ---- LayerNorm fold: producer GEMM emits bf16 rows + row statistics, consumer GEMM finishes LN in its epilogue ----
+@pytest.mark.parametrize("C,N2,M,bn", [(576, 1728, 4096, 0), (144, 432, 8192, 0), (288, 1152, 3000, 0), (1152, 3456, 1024, 0),
+                                       (576, 2304, 4096, 1192)])
+def test_gemm_layernorm_fold(C, N2, M, bn):
+    """x = a Wp^T + bp + res;  y = act(LayerNorm(x; gamma, beta, eps 1e-6) W^T + b)  vs torch fp32 (reference
+    MultiScaleBlock: norm -> Linear, hieradet.py:134-166).  Tolerance: bf16 operand rounding (1e-2 of the output scale)."""
+    from sam2_opt_b200 import ops
+    g = torch.Generator(device="cuda").manual_seed(C + N2)
+    Kp = 256
+    a = torch.randn(M, Kp, device="cuda", generator=g).bfloat16()
+    wp = (torch.randn(C, Kp, device="cuda", generator=g) / Kp ** 0.5).bfloat16()
+    bp = torch.randn(C, device="cuda", generator=g)
+    res = torch.randn(M, C, device="cuda", generator=g) * 2 + 0.7          # non-zero row mean
+    x, xb, stats = ops.gemm_ln_producer(a, wp, bp, res, block_n=bn)
+    x_ref = a.float() @ wp.float().t() + bp + res
+    _close(x, x_ref, 2e-3)
+    _close(xb, x_ref, 1e-2)
+    s = stats.sum(1)
+    _close(s[:, 0], x_ref.sum(1), 1e-4)
+    _close(s[:, 1], (x_ref * x_ref).sum(1), 1e-4)
+    gamma = torch.rand(C, device="cuda", generator=g) + 0.5
+    beta = torch.randn(C, device="cuda", generator=g) * 0.3
+    W = torch.randn(N2, C, device="cuda", generator=g) / C ** 0.5
+    b = torch.randn(N2, device="cuda", generator=g)
+    w_scaled = (W * gamma[None, :]).bfloat16()
+    colsum = w_scaled.float().sum(1)
+    bias2 = b + W @ beta
+    for act in (None, "gelu"):
+        y = ops.gemm_ln_consumer(xb, w_scaled, bias2, colsum, stats.contiguous(), 1e-6, act=act)
+        y_ref = torch.nn.functional.layer_norm(x_ref, (C,), gamma, beta, 1e-6) @ W.t() + b
+        if act == "gelu":
+            y_ref = torch.nn.functional.gelu(y_ref)
+        _close(y, y_ref, 1.5e-2)
+    y32 = ops.gemm_ln_consumer(xb, w_scaled, bias2, colsum, stats.contiguous(), 1e-6, out_dtype=torch.float32)
+    _close(y32, torch.nn.functional.layer_norm(x_ref, (C,), gamma, beta, 1e-6) @ W.t() + b, 1.5e-2)
