@@ -82,14 +82,14 @@ int sam2b_op_gemm(const void* a_bf16, int64_t lda, int64_t a_batch_stride, const
 /* LayerNorm fold (replaces nn.LayerNorm + nn.Linear pairs of MultiScaleBlock, reference hieradet.py:134-166):
  * producer: out_f32 = A B^T + bias + residual, plus a bf16 copy (out2_bf16) and per-row partial sums
  *   stats [m][*parts][2] = (sum, sum of squares) of every output row, *parts <= stats_capacity_parts;
- * consumer: out = act(LN(x) W^T + b) computed from the RAW rows a_bf16 = bf16(x) as
- *   rstd * (a (W diag(gamma))^T - mu * colsum) + (b + W beta): b_bf16 = W diag(gamma), bias = b + W beta,
- *   colsum[n] = sum_k b_bf16[n][k], (mu, rstd) from stats over k columns and eps. */
+ * consumer: out = act(LN(x) W^T + b) computed from the RAW rows a_bf16 = bf16(x) as rstd * (a W''^T) + (b + W beta):
+ *   b_bf16 = W'' = W diag(gamma) with every row centred to zero mean (the mean subtraction of LN is absorbed by the
+ *   weights: sum_k x_k W''[n][k] = sum_k (x_k - mu) (W diag(gamma))[n][k]), bias = b + W beta, rstd from stats over k columns. */
 int sam2b_op_gemm_ln_producer(const void* a_bf16, const void* b_bf16, int m, int n, int k, const float* bias,
                               const float* residual, float* out_f32, void* out2_bf16, float* stats,
                               int stats_capacity_parts, int* parts, int force_block_n, void* stream);
 int sam2b_op_gemm_ln_consumer(const void* a_bf16, const void* b_bf16, int m, int n, int k, const float* bias,
-                              const float* colsum, const float* stats, int parts, float eps, int act, float* out_f32,
+                              const float* stats, int parts, float eps, int act, float* out_f32,
                               void* out_bf16, int force_block_n, void* stream);
 int sam2b_op_layernorm(const float* x, const float* gamma, const float* beta, float eps, void* y_bf16, float* y_f32,
                        int64_t rows, int c, void* stream);

@@ -26,7 +26,7 @@ SIGNATURES = {
     "sam2b_op_gemm": (_i, [_vp, _i64, _i64, _vp, _i64, _i64, _i, _i, _i, _i, _f, _vp, _i, _i, _vp, _vp, _i64, _i64, _i,
                            _vp, _vp, _i64, _i64, _i, _vp]),
     "sam2b_op_gemm_ln_producer": (_i, [_vp, _vp, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _i, C.POINTER(_i), _i, _vp]),
-    "sam2b_op_gemm_ln_consumer": (_i, [_vp, _vp, _i, _i, _i, _vp, _vp, _vp, _i, _f, _i, _vp, _vp, _i, _vp]),
+    "sam2b_op_gemm_ln_consumer": (_i, [_vp, _vp, _i, _i, _i, _vp, _vp, _i, _f, _i, _vp, _vp, _i, _vp]),
     "sam2b_op_layernorm": (_i, [_vp, _vp, _vp, _f, _vp, _vp, _i64, _i, _vp]),
     "sam2b_op_cast_bf16": (_i, [_vp, _vp, _i64, _vp]),
     "sam2b_op_maxpool2x2_nhwc": (_i, [_vp, _vp, _i, _i, _i, _i, _vp]),

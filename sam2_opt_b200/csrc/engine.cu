@@ -165,6 +165,13 @@ static int finalize(sam2b_engine* e) {
       TRY(need(e, b + "proj.weight", nullptr, true));
       TRY(need(e, b + "proj.bias", nullptr, false));
     }
+    // LayerNorm-folded forms of the norm -> Linear pairs (weights.py derive())
+    const std::string d = "derived.blocks." + std::to_string(i) + ".";
+    for (const char* lin : {"qkv.", "fc1.", "skip."}) {
+      if (std::string(lin) == "skip." && e->blocks[i].dim == e->blocks[i].dim_out) continue;
+      TRY(need(e, d + lin + "weight", nullptr, true));
+      TRY(need(e, d + lin + "bias", nullptr, false));
+    }
   }
   TRY(need(e, "derived.patch_embed.weight", nullptr, true));   // [144,160] (147 taps zero padded)
   TRY(need(e, t + "patch_embed.proj.bias", nullptr, false));
@@ -251,6 +258,89 @@ static int image_encode_mb(sam2b_engine* e, const float* img, int n, int normali
   TRY(ws_get_t(e, "lat3", (size_t)n * 256 * 1024, &LAT3));
 
   const std::string t = "image_encoder.trunk.";
+  static int ln_fold = -1;
+  if (ln_fold < 0) { const char* ev = getenv("SAM2B_LN_FOLD"); ln_fold = ev ? atoi(ev) : 1; }
+  if (ln_fold) {
+    // ============ LayerNorm never runs as a kernel: every GEMM that writes the fp32 residual stream also emits its bf16
+    // copy and per-row (sum, sum x^2) partials; the norm -> Linear consumers fold the normalisation into their epilogue.
+    bf16 *XB, *XB2;
+    float *ST1, *ST2;
+    // partial-sum slots: 2 per N tile of the producing GEMM (BLOCK_N >= 128): <= 4 / 6 / 10 / 18 per row in stages 1..4,
+    // whose row counts shrink 4x per stage -> T0 * 8 floats cover every stage
+    const size_t kStatFloats = (size_t)T0 * 8;
+    auto stat_cap = [&](long rows) { return (int)(kStatFloats / ((size_t)rows * 2)); };
+    TRY(ws_get_t(e, "xb", (size_t)T0 * 144, &XB));
+    TRY(ws_get_t(e, "xb2", (size_t)T0 * 144, &XB2));
+    TRY(ws_get_t(e, "st1", kStatFloats, &ST1));
+    TRY(ws_get_t(e, "st2", kStatFloats, &ST2));
+    TRY(patch_im2col(img, COLS, n, 1024, normalised ? 0 : 1, st));
+    int parts1 = 0, parts2 = 0;         // partial-sum slots per row in ST1 (block input) / ST2 (after attention)
+    {
+      GemmArgs g;
+      g.A = COLS; g.lda = 160; g.M = (int)T0; g.K = 160;
+      g.B = W16(e, "derived.patch_embed.weight"); g.ldb = 160; g.N = 144;
+      g.bias = W32(e, t + "patch_embed.proj.bias");
+      g.residual = W32(e, "derived.pos_embed"); g.ld_res = 144; g.res_row_mod = 65536;
+      g.out_f32 = X; g.ldc = 144;
+      g.out2_bf16 = XB; g.ldc2 = 144; g.stats_out = ST1; g.stats_capacity_parts = stat_cap(T0); g.stats_parts_out = &parts1;
+      TRY(gemm_bf16(g, st));
+    }
+    const bf16* xb_in = XB;            // bf16 copy of the current residual stream (block input)
+    int H = 256, tap = 0;
+    for (size_t i = 0; i < e->blocks.size(); ++i) {
+      const BlockCfg& c = e->blocks[i];
+      const std::string b = t + "blocks." + std::to_string(i) + ".";
+      const std::string d = "derived.blocks." + std::to_string(i) + ".";
+      const long T = (long)n * H * H;
+      auto ln_linear = [&](const bf16* A, int K, const std::string& w, int N, const float* stats, int parts, int act,
+                           float* o32, bf16* o16, long M) -> int {
+        GemmArgs g;
+        g.A = A; g.lda = K; g.M = (int)M; g.K = K;
+        g.B = W16(e, w + "weight"); g.ldb = K; g.N = N;
+        g.bias = W32(e, w + "bias"); g.act = act;
+        g.ln_stats = stats; g.ln_parts = parts; g.ln_eps = 1e-6f;
+        g.out_f32 = o32; g.out_bf16 = o16; g.ldc = N;
+        return gemm_bf16(g, st);
+      };
+      float* shortcut = X;
+      const bool trans = c.dim != c.dim_out;
+      if (trans) {
+        TRY(ln_linear(xb_in, c.dim, d + "skip.", c.dim_out, ST1, parts1, ACT_NONE, SC, nullptr, T));
+        TRY(maxpool2x2_nhwc(SC, X2, n, H, H, c.dim_out, st));
+        shortcut = X2;
+      }
+      TRY(ln_linear(xb_in, c.dim, d + "qkv.", 3 * c.dim_out, ST1, parts1, ACT_NONE, nullptr, QKV, T));
+      TRY(window_attention_hd72(QKV, ATT, n, H, H, c.heads, c.window ? c.window : H, c.q_pool, st));
+      if (c.q_pool) H /= 2;
+      const long Tq = (long)n * H * H;
+      {
+        GemmArgs g;
+        g.A = ATT; g.lda = c.dim_out; g.M = (int)Tq; g.K = c.dim_out;
+        g.B = W16(e, b + "attn.proj.weight"); g.ldb = c.dim_out; g.N = c.dim_out;
+        g.bias = W32(e, b + "attn.proj.bias");
+        g.residual = shortcut; g.ld_res = c.dim_out;
+        g.out_f32 = shortcut; g.ldc = c.dim_out;
+        g.out2_bf16 = XB2; g.ldc2 = c.dim_out; g.stats_out = ST2; g.stats_capacity_parts = stat_cap(Tq); g.stats_parts_out = &parts2;
+        TRY(gemm_bf16(g, st));
+      }
+      if (trans) { float* tmp = X; X = X2; X2 = tmp; }
+      TRY(ln_linear(XB2, c.dim_out, d + "fc1.", 4 * c.dim_out, ST2, parts2, ACT_GELU, nullptr, HID, Tq));
+      const bool is_tap = (i == 1 || i == 7 || i == 43 || i == 47);
+      bf16* xb_out = is_tap ? TAP[tap] : XB;      // stage taps ARE the bf16 copy of the stream (no cast kernel)
+      {
+        GemmArgs g;
+        g.A = HID; g.lda = 4 * c.dim_out; g.M = (int)Tq; g.K = 4 * c.dim_out;
+        g.B = W16(e, b + "mlp.layers.1.weight"); g.ldb = 4 * c.dim_out; g.N = c.dim_out;
+        g.bias = W32(e, b + "mlp.layers.1.bias");
+        g.residual = X; g.ld_res = c.dim_out;
+        g.out_f32 = X; g.ldc = c.dim_out;
+        g.out2_bf16 = xb_out; g.ldc2 = c.dim_out; g.stats_out = ST1; g.stats_capacity_parts = stat_cap(Tq); g.stats_parts_out = &parts1;
+        TRY(gemm_bf16(g, st));
+      }
+      xb_in = xb_out;
+      if (is_tap) ++tap;
+    }
+  } else {
   // ---- patch embed (im2col + GEMM) with the constant position embedding added in the epilogue ----
   TRY(patch_im2col(img, COLS, n, 1024, normalised ? 0 : 1, st));
   {
@@ -323,6 +413,7 @@ static int image_encode_mb(sam2b_engine* e, const float* img, int n, int normali
       TRY(cast_f32_bf16(X, TAP[tap], Tq * c.dim_out, st));
       ++tap;
     }
+  }
   }
   // ---- FpnNeck (+ conv_s0 / conv_s1 folded into the level-0/1 laterals): out[b][co][hw] = W[co][:] . x[b][hw][:] ----
   struct NeckJob { const char* w; const char* bias; const bf16* x; int cin, cout, hw; float* out; };
@@ -721,14 +812,14 @@ int sam2b_op_gemm_ln_producer(const void* a, const void* b, int m, int n, int k,
   g.force_bn = force_block_n;
   return gemm_bf16(g, reinterpret_cast<cudaStream_t>(stream));
 }
-int sam2b_op_gemm_ln_consumer(const void* a, const void* b, int m, int n, int k, const float* bias, const float* colsum,
+int sam2b_op_gemm_ln_consumer(const void* a, const void* b, int m, int n, int k, const float* bias,
                               const float* stats, int parts, float eps, int act, float* out_f32, void* out_bf16,
                               int force_block_n, void* stream) {
   GemmArgs g;
   g.A = reinterpret_cast<const bf16*>(a); g.lda = k; g.B = reinterpret_cast<const bf16*>(b); g.ldb = k;
   g.M = m; g.N = n; g.K = k; g.bias = bias; g.act = act;
   g.out_f32 = out_f32; g.out_bf16 = reinterpret_cast<bf16*>(out_bf16); g.ldc = n;
-  g.ln_stats = stats; g.ln_parts = parts; g.ln_eps = eps; g.ln_colsum = colsum;
+  g.ln_stats = stats; g.ln_parts = parts; g.ln_eps = eps;
   g.force_bn = force_block_n;
   return gemm_bf16(g, reinterpret_cast<cudaStream_t>(stream));
 }

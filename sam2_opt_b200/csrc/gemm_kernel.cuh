@@ -21,8 +21,9 @@ namespace sam2b {
 // epilogue specialisations (compile-time): everything not listed is off / alpha = 1 / bias along N
 // MODE_F32_BIAS_RES_LN: MODE_F32_BIAS_RES that also emits what the NEXT LayerNorm needs -- a bf16 copy of its fp32 output and
 // per-row partial sums (sum x, sum x^2 per 32-column-chunk parity of every N tile) -- so that LayerNorm never runs as a kernel:
-// the consuming GEMM multiplies the raw bf16 rows with gamma-scaled weights and finishes the normalisation in its epilogue
-// (LN(x) W^T = rstd (x W'^T) - rstd mu colsum(W') + (b + W beta), W' = W diag(gamma)).
+// the consuming GEMM multiplies the raw bf16 rows with gamma-scaled, row-centred weights and finishes the normalisation in
+// its epilogue: LN(x) W^T + b = rstd * (x W''^T) + (b + W beta) with W' = W diag(gamma), W''[n][k] = W'[n][k] - mean_k W'[n][:]
+// (sum_k x_k W''[n][k] = sum_k (x_k - mu) W'[n][k]: the mean subtraction lives in the weights, only rstd is per row).
 enum GemmMode { MODE_GENERIC = 0, MODE_BF16_BIAS = 1, MODE_BF16_BIAS_GELU = 2, MODE_F32_BIAS_RES = 3, MODE_F32_BIAS_RES_LN = 4 };
 
 int make_tmap(CUtensorMap* m, const bf16* ptr, long rows, long K, long ld, long batch, long batch_stride, int box_rows);
@@ -49,7 +50,7 @@ struct GemmKernelParams {
   int has_res; int res_batched; int res_row_mod;
   int out_is_bf16;
   // LayerNorm fold, consumer side: rows of A are raw (un-normalised); ln_stats [M][ln_parts][2] partial (sum, sum of squares)
-  const float* ln_stats; int ln_parts; float ln_inv_c; float ln_eps; const float* ln_colsum;
+  const float* ln_stats; int ln_parts; float ln_inv_c; float ln_eps;
   // producer side (MODE_F32_BIAS_RES_LN): partial sums of this GEMM's output rows, [M][2 * tiles_n][2]
   float* stats_out;
   int dbg;   // timing experiments (SAM2B_GEMM_DBG): 1 = no TMA store, 2 = no proxy fence, 4 = no staging writes
@@ -266,27 +267,6 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid
           }
         }
       };
-      // LayerNorm-fold consumer: o[n] += d * colsum[n] for the 32 columns of chunk c (one float4 in flight at a time)
-      auto fold_colsum = [&](int c, float d, float4 (&o)[8]) {
-        const int col0 = n0 + c * 32;
-        if (col0 + 32 <= p.N) {
-          const float4* src = reinterpret_cast<const float4*>(p.ln_colsum + col0);
-#pragma unroll
-          for (int j = 0; j < 8; ++j) {
-            const float4 sv = __ldg(src + j);
-            o[j].x = fmaf(d, sv.x, o[j].x); o[j].y = fmaf(d, sv.y, o[j].y); o[j].z = fmaf(d, sv.z, o[j].z); o[j].w = fmaf(d, sv.w, o[j].w);
-          }
-        } else {
-#pragma unroll
-          for (int j = 0; j < 8; ++j) {
-            const int col = col0 + 4 * j;
-            if (col < p.N) o[j].x = fmaf(d, __ldg(p.ln_colsum + col), o[j].x);
-            if (col + 1 < p.N) o[j].y = fmaf(d, __ldg(p.ln_colsum + col + 1), o[j].y);
-            if (col + 2 < p.N) o[j].z = fmaf(d, __ldg(p.ln_colsum + col + 2), o[j].z);
-            if (col + 3 < p.N) o[j].w = fmaf(d, __ldg(p.ln_colsum + col + 3), o[j].w);
-          }
-        }
-      };
       const bool first_live = rows_live && half < NCHUNK && (n0 + half * 32 < p.N);
       if (has_res && first_live && lane == 0) {
         if (two_buf) bulk_wait_read<1>(); else bulk_wait_read<0>();
@@ -296,7 +276,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid
       load_vec8(bias_n ? p.bias : nullptr, half, 0.f, bn);
       float bias_m = 0.f;
       if (GEN) bias_m = (p.bias && p.bias_along_m && row_g + lane < p.M) ? __ldg(p.bias + row_g + lane) : 0.f;
-      float ln_a = 1.f, ln_d = 0.f;                      // v = ln_a * acc + (ln_d * colsum[n] + bias[n])
+      float ln_a = 1.f;                                  // LayerNorm fold: v = rstd(row) * acc + bias[n]
       if (ln_fold) {
         float s1 = 0.f, s2 = 0.f;
         if (row_g + lane < p.M) {
@@ -306,8 +286,6 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid
         const float mu = s1 * p.ln_inv_c;
         const float var = fmaxf(fmaf(s2, p.ln_inv_c, -mu * mu), 0.f);
         ln_a = rsqrtf(var + p.ln_eps);
-        ln_d = -ln_a * mu;
-        fold_colsum(half, ln_d, bn);
       }
       float st1 = 0.f, st2 = 0.f;                         // LNP: this warp's partial row sums over its chunks of the tile
       mbar_wait(&tmem_full[acc], acc_phase);
@@ -360,9 +338,6 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid
           if (c + 2 < NCHUNK) {
             tmem_ld_x32(taddr + (c + 2) * 32, r);   // next chunk streams out of TMEM (and its bias out of L1) meanwhile
             load_vec8(bias_n ? p.bias : nullptr, c + 2, 0.f, bn);
-            if (ln_fold) {
-              fold_colsum(c + 2, ln_d, bn);
-            }
           }
           if (act == ACT_GELU) {
 #pragma unroll
@@ -506,7 +481,7 @@ static int launch_gemm(const GemmArgs& a, cudaStream_t stream) {
   p.has_res = a.residual ? 1 : 0; p.res_batched = res_batched ? 1 : 0; p.res_row_mod = a.res_row_mod;
   p.out_is_bf16 = out_bf16;
   p.ln_stats = a.ln_stats; p.ln_parts = a.ln_parts; p.ln_inv_c = a.ln_stats ? 1.0f / (float)a.K : 0.f; p.ln_eps = a.ln_eps;
-  p.ln_colsum = a.ln_colsum; p.stats_out = a.stats_out;
+  p.stats_out = a.stats_out;
   { static int dbg = -1; if (dbg < 0) { const char* e = getenv("SAM2B_GEMM_DBG"); dbg = e ? atoi(e) : 0; } p.dbg = dbg; }
   const long tiles = (long)p.tiles_m * p.tiles_n * p.batch;
   const int grid = (int)(tiles < max_pairs ? tiles : max_pairs) * NCTA;

@@ -83,13 +83,24 @@ static void pick_tile(const GemmArgs& a, int* bn_out, int* cta2_out) {
   static int allow2 = -1;
   if (allow2 < 0) { const char* e = getenv("SAM2B_GEMM_2CTA"); allow2 = e ? atoi(e) : 1; }
   double best = 1e30; int best_bn = 128, best_c2 = 0;
+  // A LayerNorm producer writes one partial (sum, sum x^2) per N tile and chunk parity; fixing BLOCK_N by N keeps that
+  // partition -- and with it every rounding of the statistics -- independent of M, so an image's result is bit-identical
+  // whatever batch it is encoded in.  Least padding wins, ties go to the larger tile: 144, 288 -> 160; 576, 1152 -> 192.
+  int ln_bn = 0;
+  if (a.out2_bf16) {
+    long waste_best = 1L << 40;
+    for (int bn : {128, 160, 192}) {
+      const long waste = (long)((a.N + bn - 1) / bn) * bn - a.N;
+      if (waste <= waste_best) { waste_best = waste; ln_bn = bn; }
+    }
+  }
   for (int c2 = 0; c2 <= (allow2 ? 1 : 0); ++c2) {
     const int tm = c2 ? 2 * BM : BM;
     const long units = c2 ? num_sms() / 2 : num_sms();
     const long tiles_m = (a.M + tm - 1) / tm;
     for (int bn : cand) {
       if (c2 && bn < 128) continue;                      // pair kernels are instantiated for the large tiles only
-      if (a.out2_bf16 && bn < 128) continue;             // so is the LayerNorm-producer epilogue
+      if (a.out2_bf16 && bn != ln_bn) continue;          // LayerNorm producer: BLOCK_N is a function of N alone (see above)
       const long tiles = tiles_m * ((a.N + bn - 1) / bn) * a.batch;
       // measured on B200 (tests/_gemm_bench.py): pairs win 3-7 % on the K >= 1152 stage-4 shapes (long main loop), and lose
       // a few % on the K = 576 / 288 / 144 shapes whose time is set by the epilogue, not by operand traffic
@@ -127,7 +138,7 @@ int gemm_bf16(const GemmArgs& a, cudaStream_t stream) {
     if (a.stats_out && parts > a.stats_capacity_parts) { set_error("gemm: stats buffer holds %d parts per row, %d needed", a.stats_capacity_parts, parts); return 1; }
     if (a.stats_parts_out) *a.stats_parts_out = parts;
   }
-  if (a.ln_stats && (a.residual || !a.ln_colsum || a.ln_parts <= 0 || !a.bias || a.bias_along_m)) { set_error("gemm: LayerNorm-fold consumer needs bias along N, colsum, parts > 0 and no residual"); return 1; }
+  if (a.ln_stats && (a.residual || a.ln_parts <= 0 || !a.bias || a.bias_along_m)) { set_error("gemm: LayerNorm-fold consumer needs bias along N, parts > 0 and no residual"); return 1; }
   switch (bn) {
     case 256: return launch_gemm_bn256(a, mode, cta2, stream);
     case 224: return launch_gemm_bn224(a, mode, cta2, stream);

@@ -56,9 +56,9 @@ struct GemmArgs {
   // [batch*M][stats_parts][2]; the number of parts (2 * N tiles) is returned through *stats_parts_out.
   bf16* out2_bf16 = nullptr; long ldc2 = 0; long c2_batch_stride = 0;
   float* stats_out = nullptr; int stats_capacity_parts = 0; int* stats_parts_out = nullptr;
-  // consumer: A holds raw rows x; B holds W diag(gamma); bias holds b + W beta; ln_colsum[n] = sum_k B[n][k];
-  // the epilogue computes rstd * (acc - mu * colsum) + bias with (mu, rstd) from ln_stats [M][ln_parts][2] over K columns.
-  const float* ln_stats = nullptr; int ln_parts = 0; float ln_eps = 0.f; const float* ln_colsum = nullptr;
+  // consumer: A holds raw rows x; B holds W'' = W diag(gamma) with every row centred to zero mean; bias holds b + W beta;
+  // the epilogue computes rstd * acc + bias with rstd from ln_stats [M][ln_parts][2] over the K columns of A.
+  const float* ln_stats = nullptr; int ln_parts = 0; float ln_eps = 0.f;
 };
 int gemm_bf16(const GemmArgs& a, cudaStream_t stream);
 

@@ -118,14 +118,15 @@ def gemm_ln_producer(a: torch.Tensor, b: torch.Tensor, bias: torch.Tensor, resid
     return x, xb, stats.flatten()[: M * parts.value * 2].view(M, parts.value, 2)
 
 
-def gemm_ln_consumer(xb: torch.Tensor, w_scaled: torch.Tensor, bias: torch.Tensor, colsum: torch.Tensor, stats: torch.Tensor,
+def gemm_ln_consumer(xb: torch.Tensor, w_scaled: torch.Tensor, bias: torch.Tensor, stats: torch.Tensor,
                      eps: float, act=None, out_dtype=torch.bfloat16, block_n: int = 0) -> torch.Tensor:
+    """act(LayerNorm(x) W^T + b) from raw bf16 rows xb: w_scaled = bf16(W diag(gamma) with zero-mean rows), bias = b + W beta."""
     lib = _lib.load()
     M, K = xb.shape
     N = w_scaled.shape[0]
     assert stats.is_contiguous() and stats.shape[0] == M
     out = torch.empty((M, N), device=xb.device, dtype=out_dtype)
-    _lib.check(lib.sam2b_op_gemm_ln_consumer(_ptr(xb), _ptr(w_scaled), M, N, K, _ptr(bias), _ptr(colsum), _ptr(stats),
+    _lib.check(lib.sam2b_op_gemm_ln_consumer(_ptr(xb), _ptr(w_scaled), M, N, K, _ptr(bias), _ptr(stats),
                                              stats.shape[1], float(eps), ACT[act],
                                              _ptr(out if out_dtype == torch.float32 else None),
                                              _ptr(out if out_dtype == torch.bfloat16 else None), int(block_n), _stream()),

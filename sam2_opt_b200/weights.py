@@ -86,6 +86,25 @@ def derive(w: Dict[str, torch.Tensor]) -> Dict[str, torch.Tensor]:
         for l in range(2):
             dw = w[f"memory_encoder.fuser.layers.{l}.dwconv.weight"].float()
             d[f"derived.memenc.fuser.{l}.dw.weight"] = dw.reshape(256, 49).t().contiguous()
+    # LayerNorm fold for the trunk (engine.cu image_encode_mb): every norm -> Linear pair of MultiScaleBlock
+    # (ref: modeling/backbones/hieradet.py:134-166; norm1 -> attn.qkv [and -> proj on dim-change blocks], norm2 -> mlp.layers.0)
+    # becomes one GEMM on the raw rows with W'' = row-centred W diag(gamma) and b' = b + W beta; rstd is applied per row in the
+    # epilogue from statistics the producing GEMM emitted.
+    t = "image_encoder.trunk.blocks."
+    i = 0
+    while f"{t}{i}.norm1.weight" in w:
+        b = f"{t}{i}."
+        pairs = [("norm1.", "attn.qkv.", "qkv"), ("norm2.", "mlp.layers.0.", "fc1")]
+        if b + "proj.weight" in w:
+            pairs.append(("norm1.", "proj.", "skip"))
+        for norm, lin, short in pairs:
+            gamma, beta = w[b + norm + "weight"].double(), w[b + norm + "bias"].double()
+            W, bias = w[b + lin + "weight"].double(), w[b + lin + "bias"].double()
+            ws = W * gamma[None, :]
+            ws = ws - ws.mean(1, keepdim=True)        # zero-mean rows: sum_k x_k ws[n][k] = sum_k (x_k - mean(x)) (W gamma)[n][k]
+            d[f"derived.blocks.{i}.{short}.weight"] = ws.float().contiguous()
+            d[f"derived.blocks.{i}.{short}.bias"] = (bias + W @ beta).float().contiguous()
+        i += 1
     cos, sin = rope_tables(dev)
     d["derived.rope.cos"], d["derived.rope.sin"] = cos, sin
     return d
