@@ -13,8 +13,9 @@
 //   warp 1      MMA issuer (one thread): S_t = Q_t K^T (M128 N128, 5 k-steps) into TMEM, then O_t = P_t V
 //               (V consumed as an MN-major B operand, N = 64 + 16) into TMEM.
 //   warps 4-7   softmax warpgroup of Q tile 0, warps 8-11 of Q tile 1: thread = query row (tcgen05.ld 32x32b),
-//               fp32 online softmax, P written as bf16 into a 128B-swizzled K-major smem tile (A operand of P V),
-//               per-tile O partials accumulated in registers with the running rescale (no TMEM correction pass).
+//               fp32 online softmax in ONE pass over S (128 scores per thread held in registers), P written as bf16
+//               into a 128B-swizzled K-major smem tile (A operand of P V); O_t accumulates in TMEM across the KV tiles
+//               and is rescaled there only when the running max moves by more than 2^8 (lazy rescale).
 #include <cstdio>
 #include <mutex>
 
@@ -43,6 +44,7 @@ static constexpr int THREADS = 384;
 static constexpr int COL_S = 0;         // S_t at COL_S + 128 t
 static constexpr int COL_O = 256;       // O_t at COL_O + 80 t
 static constexpr int TMEM_COLS = 512;
+static constexpr float RESCALE_THRESHOLD = 8.0f;   // log2 units
 }  // namespace fa
 
 struct FaParams {
@@ -167,9 +169,9 @@ flash_attn_hd72_tcgen05_kernel(const __grid_constant__ CUtensorMap map_lo, const
         umma_commit(&s_full[t]);
         ++n_s[t];
       };
-      auto issue_pv = [&](int t, int st) {
-        mbar_wait(&p_full[t], n_o[t] & 1);
-        mbar_wait(&o_free[t], (n_o[t] & 1) ^ 1);
+      auto issue_pv = [&](int t, int st, int j) {
+        mbar_wait(&p_full[t], n_o[t] & 1);                  // P_t(j) written; O_t rescaled if the running max moved
+        if (j == 0) mbar_wait(&o_free[t], (nu & 1) ^ 1);    // the previous unit's O_t has been read out of TMEM
         tc_fence_after();
         const uint32_t pa = sbase + OFF_P + t * P_BYTES, v = sbase + OFF_V + st * TILE_BYTES;
         const uint32_t d = tmem_base + COL_O + 80 * t;
@@ -177,8 +179,8 @@ flash_attn_hd72_tcgen05_kernel(const __grid_constant__ CUtensorMap map_lo, const
         for (int ks = 0; ks < 8; ++ks) {
           // A: P[128][16 keys of k-step ks] (K-major, sub-tile ks/4); B: V rows 16ks..16ks+15 (MN-major: d contiguous)
           const uint64_t da = make_smem_desc(pa + (ks >> 2) * 16384 + (ks & 3) * 32, 16, 1024, 2);
-          umma_bf16(d, da, make_smem_desc(v + ks * 2048, 1024, 1024, 2), idesc_pv_lo, ks != 0);
-          umma_bf16(d + 64, da, make_smem_desc(v + LO_BYTES + ks * 512, 256, 256, 6), idesc_pv_hi, ks != 0);
+          umma_bf16(d, da, make_smem_desc(v + ks * 2048, 1024, 1024, 2), idesc_pv_lo, (j | ks) != 0);
+          umma_bf16(d + 64, da, make_smem_desc(v + LO_BYTES + ks * 512, 256, 256, 6), idesc_pv_hi, (j | ks) != 0);
         }
         umma_commit(&o_full[t]);
         ++n_o[t];
@@ -204,7 +206,7 @@ flash_attn_hd72_tcgen05_kernel(const __grid_constant__ CUtensorMap map_lo, const
           if (more) { mbar_wait(&k_full[st1], ((it + 1) / NSTAGE) & 1); tc_fence_after(); }
 #pragma unroll
           for (int t = 0; t < 2; ++t) {
-            issue_pv(t, st);
+            issue_pv(t, st, j);
             if (t == 1) umma_commit(&v_empty[st]);
             if (more) {
               issue_qk(t, st1);
@@ -228,66 +230,78 @@ flash_attn_hd72_tcgen05_kernel(const __grid_constant__ CUtensorMap map_lo, const
     const uint32_t p_row = smem_u32(smem + OFF_P + t * P_BYTES) + r * 128;
     const uint32_t p_xor = (uint32_t)(r & 7) << 4;
     const int C = p.heads * HD;
-    uint32_t n = 0;                           // KV tiles processed by this warpgroup (all units)
+    uint32_t n = 0;                           // KV tiles processed by this warpgroup (all units): phase of s_full[t]
+    uint32_t n_pv = 0;                        // P V completions observed on o_full[t] (in order)
     for (int u = blockIdx.x; u < p.num_units; u += gridDim.x) {
       const UnitCoord c = unit_coord(p, u);
-      float m_run = -INFINITY, l_run = 0.f, corr_prev = 0.f;
-      float o_acc[HD];
-#pragma unroll
-      for (int i = 0; i < HD; ++i) o_acc[i] = 0.f;
-      auto accumulate_o = [&]() {
-        // O partial of the previous KV tile (relative to the running max after that tile)
-        mbar_wait(&o_full[t], (n - 1) & 1);
-        tc_fence_after();
-        uint32_t a[32], b[32], cc[32];
-        tmem_ld_x32(to, a);
-        tmem_ld_x32(to + 32, b);
-        tmem_ld_x16(to + 64, cc);
-        tmem_ld_wait();
-        tc_fence_before();
-        __syncwarp();
-        if (lane == 0) mbar_arrive(&o_free[t]);
-#pragma unroll
-        for (int i = 0; i < 32; ++i) o_acc[i] = fmaf(o_acc[i], corr_prev, __uint_as_float(a[i]));
-#pragma unroll
-        for (int i = 0; i < 32; ++i) o_acc[32 + i] = fmaf(o_acc[32 + i], corr_prev, __uint_as_float(b[i]));
-#pragma unroll
-        for (int i = 0; i < 8; ++i) o_acc[64 + i] = fmaf(o_acc[64 + i], corr_prev, __uint_as_float(cc[i]));
-      };
+      float m_run = -INFINITY, l_run = 0.f;
       for (int j = 0; j < p.n_kv; ++j, ++n) {
         mbar_wait(&s_full[t], n & 1);
         tc_fence_after();
-        // pass 1: row max of the 128 scores
-        float mx = -INFINITY;
-#pragma unroll
-        for (int ch = 0; ch < 4; ++ch) {
-          uint32_t s[32];
-          tmem_ld_x32(ts + 32 * ch, s);
+        // the 128 scores of this row: one pass through TMEM, held in registers for max and exp
+        uint32_t s[128];
+        {
+          uint32_t (&s0)[32] = *reinterpret_cast<uint32_t(*)[32]>(&s[0]);
+          uint32_t (&s1)[32] = *reinterpret_cast<uint32_t(*)[32]>(&s[32]);
+          uint32_t (&s2)[32] = *reinterpret_cast<uint32_t(*)[32]>(&s[64]);
+          uint32_t (&s3)[32] = *reinterpret_cast<uint32_t(*)[32]>(&s[96]);
+          tmem_ld_x32(ts, s0);
+          tmem_ld_x32(ts + 32, s1);
+          tmem_ld_x32(ts + 64, s2);
+          tmem_ld_x32(ts + 96, s3);
           tmem_ld_wait();
-#pragma unroll
-          for (int i = 0; i < 32; ++i) mx = fmaxf(mx, __uint_as_float(s[i]));
         }
-        const float m_new = fmaxf(m_run, mx * p.scale_log2);
-        const float corr = exp2f(m_run - m_new);
-        if (j > 0) accumulate_o();
-        // pass 2: P = exp2(S * scale - m) -> bf16 -> swizzled K-major smem tile; fp32 row sum
-        float rs = 0.f;
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&s_free[t]);       // S_t is in registers: the next Q K^T may overwrite it
+        float mx0 = -INFINITY, mx1 = -INFINITY, mx2 = -INFINITY, mx3 = -INFINITY;
+#pragma unroll
+        for (int i = 0; i < 32; ++i) {
+          mx0 = fmaxf(mx0, __uint_as_float(s[i]));
+          mx1 = fmaxf(mx1, __uint_as_float(s[32 + i]));
+          mx2 = fmaxf(mx2, __uint_as_float(s[64 + i]));
+          mx3 = fmaxf(mx3, __uint_as_float(s[96 + i]));
+        }
+        const float mx = fmaxf(fmaxf(mx0, mx1), fmaxf(mx2, mx3)) * p.scale_log2;
+        // lazy rescale: the reference max only moves when the new one exceeds it by more than 2^8 (exact: the factor
+        // cancels in O / l; P stays below 2^8 and the fp32 accumulators have the headroom)
+        float corr = 1.0f;
+        const bool grow = mx > m_run + RESCALE_THRESHOLD;
+        if (grow) { corr = ex2_approx(m_run - mx); m_run = mx; }      // first tile: m_run = -inf -> corr = 0
+        if (j > 0) {
+          // P V of the previous tile has completed (it was issued before this tile's Q K^T): P_t may be overwritten and
+          // the accumulator rescaled
+          mbar_wait(&o_full[t], n_pv & 1);
+          ++n_pv;
+          tc_fence_after();
+          if (__any_sync(0xffffffffu, grow)) {
+            uint32_t a[32];
+#pragma unroll 1
+            for (int ch = 0; ch < 2; ++ch) {
+              tmem_ld_x32(to + 32 * ch, a);
+              tmem_ld_wait();
+#pragma unroll
+              for (int i = 0; i < 32; ++i) a[i] = __float_as_uint(__uint_as_float(a[i]) * corr);
+              tmem_st_x32(to + 32 * ch, a);
+            }
+            tmem_ld_x16(to + 64, a);
+            tmem_ld_wait();
+#pragma unroll
+            for (int i = 0; i < 16; ++i) a[i] = __float_as_uint(__uint_as_float(a[i]) * corr);
+            tmem_st_x16(to + 64, a);
+            tmem_st_wait();
+          }
+        }
+        // P = exp2(S * scale - m) -> bf16 -> swizzled K-major smem tile; fp32 row sum
+        float rs0 = 0.f, rs1 = 0.f;
 #pragma unroll
         for (int ch = 0; ch < 4; ++ch) {
-          uint32_t s[32];
-          tmem_ld_x32(ts + 32 * ch, s);
-          tmem_ld_wait();
-          if (ch == 3) {
-            tc_fence_before();
-            __syncwarp();
-            if (lane == 0) mbar_arrive(&s_free[t]);   // S_t is in registers: the next Q K^T may overwrite it
-          }
           uint32_t pk[16];
 #pragma unroll
           for (int i = 0; i < 16; ++i) {
-            const float e0 = exp2f(fmaf(__uint_as_float(s[2 * i]), p.scale_log2, -m_new));
-            const float e1 = exp2f(fmaf(__uint_as_float(s[2 * i + 1]), p.scale_log2, -m_new));
-            rs += e0 + e1;
+            const float e0 = ex2_approx(fmaf(__uint_as_float(s[32 * ch + 2 * i]), p.scale_log2, -m_run));
+            const float e1 = ex2_approx(fmaf(__uint_as_float(s[32 * ch + 2 * i + 1]), p.scale_log2, -m_run));
+            rs0 += e0; rs1 += e1;
             pk[i] = pack_bf16x2(e0, e1);
           }
           // 32 keys = 64 B = 16 B chunks (ch & 1) * 4 + i of sub-tile ch >> 1, XOR-swizzled by (row & 7)
@@ -296,27 +310,53 @@ flash_attn_hd72_tcgen05_kernel(const __grid_constant__ CUtensorMap map_lo, const
           for (int i = 0; i < 4; ++i)
             st_shared_u4(base + (((uint32_t)((ch & 1) * 4 + i) << 4) ^ p_xor), pk[4 * i], pk[4 * i + 1], pk[4 * i + 2], pk[4 * i + 3]);
         }
-        l_run = fmaf(l_run, corr, rs);
-        m_run = m_new;
-        corr_prev = corr;
+        l_run = fmaf(l_run, corr, rs0 + rs1);
         fence_proxy_async_smem();
+        tc_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive(&p_full[t]);
       }
-      accumulate_o();
-      // ---- O / l -> bf16 -> out[token][head*72 ..] ----
+      // ---- unit done: O_t / l -> bf16 -> out[token][head*72 ..] ----
+      mbar_wait(&o_full[t], n_pv & 1);
+      ++n_pv;
+      tc_fence_after();
+      uint32_t oa[32], ob[32], oc[32];
+      tmem_ld_x32(to, oa);
+      tmem_ld_x32(to + 32, ob);
+      tmem_ld_x16(to + 64, oc);
+      tmem_ld_wait();
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&o_free[t]);
       const float inv = 1.0f / l_run;
       const int rr = t * TQ + r;
       const int y = c.y0 + rr / p.ws, x = c.x0 + rr % p.ws;
       bf16* op = p.out + (((long)c.b * p.H + y) * p.W + x) * C + c.head * HD;
 #pragma unroll
-      for (int i = 0; i < 9; ++i) {
+      for (int i = 0; i < 4; ++i) {
         uint4 v;
-        v.x = pack_bf16x2(o_acc[8 * i] * inv, o_acc[8 * i + 1] * inv);
-        v.y = pack_bf16x2(o_acc[8 * i + 2] * inv, o_acc[8 * i + 3] * inv);
-        v.z = pack_bf16x2(o_acc[8 * i + 4] * inv, o_acc[8 * i + 5] * inv);
-        v.w = pack_bf16x2(o_acc[8 * i + 6] * inv, o_acc[8 * i + 7] * inv);
+        v.x = pack_bf16x2(__uint_as_float(oa[8 * i]) * inv, __uint_as_float(oa[8 * i + 1]) * inv);
+        v.y = pack_bf16x2(__uint_as_float(oa[8 * i + 2]) * inv, __uint_as_float(oa[8 * i + 3]) * inv);
+        v.z = pack_bf16x2(__uint_as_float(oa[8 * i + 4]) * inv, __uint_as_float(oa[8 * i + 5]) * inv);
+        v.w = pack_bf16x2(__uint_as_float(oa[8 * i + 6]) * inv, __uint_as_float(oa[8 * i + 7]) * inv);
         *reinterpret_cast<uint4*>(op + 8 * i) = v;
+      }
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        uint4 v;
+        v.x = pack_bf16x2(__uint_as_float(ob[8 * i]) * inv, __uint_as_float(ob[8 * i + 1]) * inv);
+        v.y = pack_bf16x2(__uint_as_float(ob[8 * i + 2]) * inv, __uint_as_float(ob[8 * i + 3]) * inv);
+        v.z = pack_bf16x2(__uint_as_float(ob[8 * i + 4]) * inv, __uint_as_float(ob[8 * i + 5]) * inv);
+        v.w = pack_bf16x2(__uint_as_float(ob[8 * i + 6]) * inv, __uint_as_float(ob[8 * i + 7]) * inv);
+        *reinterpret_cast<uint4*>(op + 32 + 8 * i) = v;
+      }
+      {
+        uint4 v;
+        v.x = pack_bf16x2(__uint_as_float(oc[0]) * inv, __uint_as_float(oc[1]) * inv);
+        v.y = pack_bf16x2(__uint_as_float(oc[2]) * inv, __uint_as_float(oc[3]) * inv);
+        v.z = pack_bf16x2(__uint_as_float(oc[4]) * inv, __uint_as_float(oc[5]) * inv);
+        v.w = pack_bf16x2(__uint_as_float(oc[6]) * inv, __uint_as_float(oc[7]) * inv);
+        *reinterpret_cast<uint4*>(op + 64) = v;
       }
     }
   }

@@ -95,6 +95,20 @@ SAM2B_DEVINL float gelu_fast(float x) {
   return fmaf(-fabsf(x), h, fmaxf(x, 0.0f));
 }
 
+// Same form with a degree-4 exponent (max |error| of the GELU value 6.1e-6, 1/160 of a bf16 ulp at the function's scale):
+// used where the result is rounded to bf16 anyway (trunk MLP hidden layer) -> 4 FMA + 1 MUFU.EX2 + 2 FMNMX + 1 FMA.
+SAM2B_DEVINL float gelu_fast_bf16(float x) {
+  const float t = fminf(fabsf(x), 5.0f);
+  float p = 0.00386557744f;
+  p = fmaf(p, t, -0.0440761234f);
+  p = fmaf(p, t, -0.468019552f);
+  p = fmaf(p, t, -1.14736964f);
+  p = fmaf(p, t, -1.00048006f);
+  float h;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(h) : "f"(p));
+  return fmaf(-fabsf(x), h, fmaxf(x, 0.0f));
+}
+
 template <int BN, int MODE, int NCTA>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
 gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b,
@@ -293,7 +307,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid
       const uint32_t taddr = tmem_base + acc * Cfg::ACC_STRIDE + ((uint32_t)(q * 32) << 16);
       uint32_t r[32];
       if (half < NCHUNK) tmem_ld_x32(taddr + half * 32, r);
-#pragma unroll 1
+#pragma unroll
       for (int c = half; c < NCHUNK; c += 2) {
         tmem_ld_wait();
         if (c + 2 >= NCHUNK) {
@@ -340,9 +354,16 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid
             load_vec8(bias_n ? p.bias : nullptr, c + 2, 0.f, bn);
           }
           if (act == ACT_GELU) {
+            if (MODE == MODE_BF16_BIAS_GELU) {
 #pragma unroll
-            for (int j = 0; j < 8; ++j) {
-              v[j].x = gelu_fast(v[j].x); v[j].y = gelu_fast(v[j].y); v[j].z = gelu_fast(v[j].z); v[j].w = gelu_fast(v[j].w);
+              for (int j = 0; j < 8; ++j) {
+                v[j].x = gelu_fast_bf16(v[j].x); v[j].y = gelu_fast_bf16(v[j].y); v[j].z = gelu_fast_bf16(v[j].z); v[j].w = gelu_fast_bf16(v[j].w);
+              }
+            } else {
+#pragma unroll
+              for (int j = 0; j < 8; ++j) {
+                v[j].x = gelu_fast(v[j].x); v[j].y = gelu_fast(v[j].y); v[j].z = gelu_fast(v[j].z); v[j].w = gelu_fast(v[j].w);
+              }
             }
           } else if (act == ACT_RELU) {
 #pragma unroll
