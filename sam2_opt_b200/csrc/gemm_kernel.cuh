@@ -34,8 +34,10 @@ static constexpr int BK = 64;       // 64 bf16 = 128 B = one swizzle row
 static constexpr int UMMA_K = 16;
 // accumulator stages in TMEM: 2 x 256 columns, or 4 x 128 columns when BLOCK_N <= 128 (GemmCfg::NACC / ACC_STRIDE)
 static constexpr int TMEM_COLS = 512;
-static constexpr int NUM_EPI_WARPS = 8;  // two warps per TMEM lane quarter, interleaved over 32-column chunks
-static constexpr int NUM_THREADS = 128 + 32 * NUM_EPI_WARPS;  // warp0 TMA, warp1 MMA, warp2 TMEM alloc, warp3 idle, warps4-11 epilogue
+// Epilogue warps EW = 8 or 16: 2 or 4 warps per TMEM lane quarter, interleaved over the 32-column chunks of a tile.
+// warp0 TMA, warp1 MMA, warp2 TMEM alloc, warp3 idle, warps 4.. epilogue.  EW = 16 (640 threads) doubles the warps that
+// hide each other's latency in the epilogue-bound small-K / GELU GEMMs (no prefetch registers there: 94 per thread).
+static constexpr int gemm_threads(int ew) { return 128 + 32 * ew; }
 static constexpr int SMEM_TOTAL = 227 * 1024;
 static constexpr int BAR_BYTES = 512;
 
@@ -59,7 +61,7 @@ struct GemmKernelParams {
 // NCTA = 2: a CTA pair (cluster of 2, `tcgen05.mma.cta_group::2`) works on a 256 x BN tile.  Each CTA holds 128 rows of A and
 // of the accumulator and HALF of the B tile (BN/2 rows) in its own shared memory, so a CTA moves (128 + BN/2) x 64 operands per
 // k-block instead of (128 + BN) x 64: one third less L2 -> SM traffic at BN = 256 and a deeper ring in the same smem.
-template <int BN, int NCTA = 1, int MODE = 0>
+template <int BN, int NCTA = 1, int MODE = 0, int EW = 8>
 struct GemmCfg {
   static constexpr int NACC = BN <= 128 ? 4 : 2;
   static constexpr int ACC_STRIDE = 512 / NACC;
@@ -71,9 +73,9 @@ struct GemmCfg {
   // BN <= 192 leaves room for two 4 KB buffers per warp (store of chunk i overlaps chunk i+1, residual prefetch);
   // BN > 192 gets one 4 KB buffer (two 2 KB buffers for bf16 outputs).
   // MODE_F32_BIAS_RES_LN adds a 2 KB bf16 staging box per warp behind the fp32 buffers.
-  static constexpr int EPI_F32_BYTES = BN > 192 ? 4096 : 8192;
+  static constexpr int EPI_F32_BYTES = (BN > 192 || EW > 8) ? 4096 : 8192;
   static constexpr int EPI_WARP_BYTES = EPI_F32_BYTES + (MODE == MODE_F32_BIAS_RES_LN ? 2048 : 0);
-  static constexpr int EPI_SMEM = NUM_EPI_WARPS * EPI_WARP_BYTES;
+  static constexpr int EPI_SMEM = EW * EPI_WARP_BYTES;
   static constexpr int AVAIL = SMEM_TOTAL - EPI_SMEM - 1024 /*align slack*/ - BAR_BYTES;
   static constexpr int STAGES = (AVAIL / STAGE) > 8 ? 8 : (AVAIL / STAGE);
   static constexpr int SMEM = STAGES * STAGE + EPI_SMEM + 1024 + BAR_BYTES;
@@ -109,14 +111,15 @@ SAM2B_DEVINL float gelu_fast_bf16(float x) {
   return fmaf(-fabsf(x), h, fmaxf(x, 0.0f));
 }
 
-template <int BN, int MODE, int NCTA>
-__global__ void __launch_bounds__(NUM_THREADS, 1)
+template <int BN, int MODE, int NCTA, int EW>
+__global__ void __launch_bounds__(gemm_threads(EW), 1)
 gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b,
                          const __grid_constant__ CUtensorMap tma_c, const __grid_constant__ CUtensorMap tma_r,
                          const __grid_constant__ CUtensorMap tma_c2, const GemmKernelParams p) {
-  using Cfg = GemmCfg<BN, NCTA, MODE>;
+  using Cfg = GemmCfg<BN, NCTA, MODE, EW>;
   constexpr int STAGES = Cfg::STAGES;
   constexpr int TILE_M = BM * NCTA;
+  constexpr int NSUB = EW / 4;                        // epilogue warps per TMEM lane quarter
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* smem_a = smem;
@@ -127,8 +130,8 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid
   uint64_t* empty_bar = bars + STAGES;
   uint64_t* tmem_full = bars + 2 * STAGES;
   uint64_t* tmem_empty = bars + 2 * STAGES + 4;
-  uint64_t* res_bar = bars + 2 * STAGES + 8;          // [NUM_EPI_WARPS][2]: residual chunk landed in the staging buffer
-  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(res_bar + 2 * NUM_EPI_WARPS);
+  uint64_t* res_bar = bars + 2 * STAGES + 8;          // [EW][2]: residual chunk landed in the staging buffer
+  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(res_bar + 2 * EW);
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -146,8 +149,8 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid
   }
   if (warp == 1 && lane == 0) {
     for (int i = 0; i < STAGES; ++i) { mbar_init(&full_bar[i], 1); mbar_init(&empty_bar[i], 1); }
-    for (int i = 0; i < Cfg::NACC; ++i) { mbar_init(&tmem_full[i], 1); mbar_init(&tmem_empty[i], NUM_EPI_WARPS * NCTA); }
-    for (int i = 0; i < 2 * NUM_EPI_WARPS; ++i) mbar_init(&res_bar[i], 1);
+    for (int i = 0; i < Cfg::NACC; ++i) { mbar_init(&tmem_full[i], 1); mbar_init(&tmem_empty[i], EW * NCTA); }
+    for (int i = 0; i < 2 * EW; ++i) mbar_init(&res_bar[i], 1);
     fence_barrier_init();
   }
   if (warp == 2) {
@@ -158,7 +161,6 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid
   if (NCTA == 2) cluster_sync_all(); else __syncthreads();     // the pair's barriers are initialised before any remote arrive
   tc_fence_after();
   const uint32_t tmem_base = *tmem_ptr;
-
   if (warp == 0) {
     // ===================== TMA producer =====================
     if (lane == 0) {
@@ -224,7 +226,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid
     // also clips ragged M / N edges.  No per-thread global loads/stores, no transposition pass.
     const int we = warp - 4;
     const int q = we & 3;
-    const int half = we >> 2;
+    const int half = we >> 2;                 // which of the NSUB warps of this lane quarter: chunks half, half + NSUB, ...
     constexpr int NCHUNK = BN / 32;
     constexpr int WB = Cfg::EPI_WARP_BYTES;
     constexpr bool GEN = MODE == MODE_GENERIC;
@@ -286,8 +288,8 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid
         if (two_buf) bulk_wait_read<1>(); else bulk_wait_read<0>();
         issue_res(i, half);
       }
-      float4 bn[8];                                      // bias of the chunk in flight (reloaded right after use)
-      load_vec8(bias_n ? p.bias : nullptr, half, 0.f, bn);
+      float4 bn[8];                                      // bias of the chunk in flight (EW = 8: prefetched one chunk ahead)
+      if (EW != 16) load_vec8(bias_n ? p.bias : nullptr, half, 0.f, bn);
       float bias_m = 0.f;
       if (GEN) bias_m = (p.bias && p.bias_along_m && row_g + lane < p.M) ? __ldg(p.bias + row_g + lane) : 0.f;
       float ln_a = 1.f;                                  // LayerNorm fold: v = rstd(row) * acc + bias[n]
@@ -306,24 +308,28 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid
       tc_fence_after();
       const uint32_t taddr = tmem_base + acc * Cfg::ACC_STRIDE + ((uint32_t)(q * 32) << 16);
       uint32_t r[32];
-      if (half < NCHUNK) tmem_ld_x32(taddr + half * 32, r);
-#pragma unroll
-      for (int c = half; c < NCHUNK; c += 2) {
+      if (EW != 16 && half < NCHUNK) tmem_ld_x32(taddr + half * 32, r);     // EW = 8: TMEM chunks are prefetched one ahead
+#pragma unroll(EW == 16 ? 1 : 8)
+      for (int c = half; c < NCHUNK; c += NSUB) {
+        if (EW == 16) {     // 112 registers per thread: no prefetch, the other three warps of the SM sub-partition hide the latency
+          tmem_ld_x32(taddr + c * 32, r);
+          load_vec8(bias_n ? p.bias : nullptr, c, 0.f, bn);
+        }
         tmem_ld_wait();
-        if (c + 2 >= NCHUNK) {
+        if (c + NSUB >= NCHUNK) {
           // last chunk of this warp has left TMEM: hand the accumulator stage back to the MMA warp now
           tc_fence_before();
           __syncwarp();
           if (lane == 0) { if (NCTA == 2) mbar_arrive_cluster(&tmem_empty[acc], 0); else mbar_arrive(&tmem_empty[acc]); }
         }
         const bool live = rows_live && (n0 + c * 32 < p.N);
-        const bool next_live = rows_live && (c + 2 < NCHUNK) && (n0 + (c + 2) * 32 < p.N);
+        const bool next_live = rows_live && (c + NSUB < NCHUNK) && (n0 + (c + NSUB) * 32 < p.N);
         if (live) {
           const uint32_t bsel = two_buf ? (i & 1) : 0;
           const uint32_t buf = buf_base + bsel * buf_bytes;
           if (lane == 0) {
             if (has_res) {
-              if (two_buf) { if (next_live) { bulk_wait_read<0>(); issue_res(i + 1, c + 2); } }
+              if (two_buf) { if (next_live) { bulk_wait_read<0>(); issue_res(i + 1, c + NSUB); } }
               else if (c != half) { bulk_wait_read<0>(); issue_res(i, c); }
             } else {
               if (two_buf) bulk_wait_read<1>(); else bulk_wait_read<0>();     // staging buffer `bsel` is free again
@@ -349,9 +355,9 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid
               v[j].w = fmaf(__uint_as_float(r[4 * j + 3]), ln_a, bn[j].w);
             }
           }
-          if (c + 2 < NCHUNK) {
-            tmem_ld_x32(taddr + (c + 2) * 32, r);   // next chunk streams out of TMEM (and its bias out of L1) meanwhile
-            load_vec8(bias_n ? p.bias : nullptr, c + 2, 0.f, bn);
+          if (EW != 16 && c + NSUB < NCHUNK) {
+            tmem_ld_x32(taddr + (c + NSUB) * 32, r);   // next chunk streams out of TMEM (and its bias out of L1) meanwhile
+            load_vec8(bias_n ? p.bias : nullptr, c + NSUB, 0.f, bn);
           }
           if (act == ACT_GELU) {
             if (MODE == MODE_BF16_BIAS_GELU) {
@@ -423,17 +429,17 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid
           }
           ++i;
         } else {
-          if (c + 2 < NCHUNK) {
-            load_vec8(bias_n ? p.bias : nullptr, c + 2, 0.f, bn);   // (dead chunks: values unused, LN fold not needed)
-            tmem_ld_x32(taddr + (c + 2) * 32, r);
+          if (EW != 16 && c + NSUB < NCHUNK) {
+            load_vec8(bias_n ? p.bias : nullptr, c + NSUB, 0.f, bn);   // (dead chunks: values unused)
+            tmem_ld_x32(taddr + (c + NSUB) * 32, r);
           }
         }
       }
       if (LNP && p.stats_out != nullptr && row_g + lane < p.M) {
-        float2* so = reinterpret_cast<float2*>(p.stats_out) + ((long)b * p.M + row_g + lane) * (2 * p.tiles_n) + 2 * n_blk + half;
+        float2* so = reinterpret_cast<float2*>(p.stats_out) + ((long)b * p.M + row_g + lane) * (NSUB * p.tiles_n) + NSUB * n_blk + half;
         *so = make_float2(st1, st2);
       }
-      if (half >= NCHUNK) {   // BN = 32: the second warp of each quarter has no chunk but still owes its arrival
+      if (half >= NCHUNK) {   // more warps per quarter than chunks: a warp without a chunk still owes its arrival
         if (lane == 0) { if (NCTA == 2) mbar_arrive_cluster(&tmem_empty[acc], 0); else mbar_arrive(&tmem_empty[acc]); }
       }
     }
@@ -451,14 +457,16 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid
 // ------------------------------------------------------------------------------------------
 // host side: launch of one instantiation
 // ------------------------------------------------------------------------------------------
-template <int BN, int MODE, int NCTA>
+template <int BN, int MODE, int NCTA, int EW>
 static int launch_gemm(const GemmArgs& a, cudaStream_t stream) {
-  using Cfg = GemmCfg<BN, NCTA, MODE>;
+  using Cfg = GemmCfg<BN, NCTA, MODE, EW>;
+  constexpr int NUM_THREADS = gemm_threads(EW);
   static_assert(BN % 32 == 0 && BN >= 32 && BN <= 256, "BLOCK_N must be a multiple of 32");
-  static_assert(Cfg::STAGES >= 3, "pipeline too shallow");
+  static_assert(Cfg::STAGES >= 2, "pipeline too shallow");
+  if (Cfg::STAGES < 3) { set_error("gemm<%d,%d,%d,%d>: only %d smem stages fit; not a supported combination", BN, MODE, NCTA, EW, Cfg::STAGES); return 1; }
   static_assert(NCTA == 1 || (BN % 32 == 0 && (BN / 2) % 8 == 0), "a CTA pair splits the B tile in two halves of whole swizzle atoms");
   static int max_pairs = 0;       // 0: attributes not set yet
-  auto kern = gemm_bf16_tcgen05_kernel<BN, MODE, NCTA>;
+  auto kern = gemm_bf16_tcgen05_kernel<BN, MODE, NCTA, EW>;
   if (!max_pairs) {
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM);
     if (e != cudaSuccess) { set_error("cudaFuncSetAttribute(gemm<%d,%d>): %s", BN, NCTA, cudaGetErrorString(e)); return 1; }
@@ -507,7 +515,7 @@ static int launch_gemm(const GemmArgs& a, cudaStream_t stream) {
   const long tiles = (long)p.tiles_m * p.tiles_n * p.batch;
   const int grid = (int)(tiles < max_pairs ? tiles : max_pairs) * NCTA;
   char nm[96];
-  if (g_prof_on) snprintf(nm, sizeof(nm), "gemm m%d n%d k%d b%d bn%d%s md%d act%d%s%s%s", a.M, a.N, a.K, a.batch, BN, NCTA == 2 ? "x2" : "", MODE, a.act, a.residual ? " res" : "", a.out_bf16 ? " o16" : " o32", a.ln_stats ? " ln" : "");
+  if (g_prof_on) snprintf(nm, sizeof(nm), "gemm m%d n%d k%d b%d bn%d%s%s md%d act%d%s%s%s", a.M, a.N, a.K, a.batch, BN, NCTA == 2 ? "x2" : "", EW == 16 ? "w16" : "", MODE, a.act, a.residual ? " res" : "", a.out_bf16 ? " o16" : " o32", a.ln_stats ? " ln" : "");
   const double esz = a.out_bf16 ? 2.0 : 4.0;
   ProfRange pr(stream, nm, 2.0 * a.M * a.N * (double)a.K * a.batch,
                ((double)a.M * a.K * 2 + (b_batched ? 1.0 : 1.0 / a.batch) * (double)a.N * a.K * 2 + (double)a.M * a.N * (esz + (a.residual ? 4.0 : 0.0))) * a.batch);
@@ -529,30 +537,32 @@ static int launch_gemm(const GemmArgs& a, cudaStream_t stream) {
 
 
 // One translation unit per BLOCK_N (parallel compilation): the specialised modes for the large tiles, generic otherwise.
-// `cta2`: run as CTA pairs (256 x BN tiles).
-#define SAM2B_GEMM_DISPATCH_MODES(BN_, NCTA_)                                                   \
-  switch (mode) {                                                                              \
-    case MODE_BF16_BIAS: return launch_gemm<BN_, MODE_BF16_BIAS, NCTA_>(a, stream);            \
-    case MODE_BF16_BIAS_GELU: return launch_gemm<BN_, MODE_BF16_BIAS_GELU, NCTA_>(a, stream);  \
-    case MODE_F32_BIAS_RES: return launch_gemm<BN_, MODE_F32_BIAS_RES, NCTA_>(a, stream);      \
-    case MODE_F32_BIAS_RES_LN: return launch_gemm<BN_, MODE_F32_BIAS_RES_LN, NCTA_>(a, stream); \
-    default: return launch_gemm<BN_, MODE_GENERIC, NCTA_>(a, stream);                          \
+// `cta2`: run as CTA pairs (256 x BN tiles); `ew16`: 16 epilogue warps instead of 8.
+#define SAM2B_GEMM_DISPATCH_MODES(BN_, NCTA_, EW_)                                                   \
+  switch (mode) {                                                                                   \
+    case MODE_BF16_BIAS: return launch_gemm<BN_, MODE_BF16_BIAS, NCTA_, EW_>(a, stream);            \
+    case MODE_BF16_BIAS_GELU: return launch_gemm<BN_, MODE_BF16_BIAS_GELU, NCTA_, EW_>(a, stream);  \
+    case MODE_F32_BIAS_RES: return launch_gemm<BN_, MODE_F32_BIAS_RES, NCTA_, EW_>(a, stream);      \
+    case MODE_F32_BIAS_RES_LN: return launch_gemm<BN_, MODE_F32_BIAS_RES_LN, NCTA_, EW_>(a, stream); \
+    default: return launch_gemm<BN_, MODE_GENERIC, NCTA_, EW_>(a, stream);                          \
   }
-#define SAM2B_GEMM_INSTANTIATE_FULL(BN_)                                                       \
-  int launch_gemm_bn##BN_(const GemmArgs& a, int mode, int cta2, cudaStream_t stream) {         \
-    if (cta2) { SAM2B_GEMM_DISPATCH_MODES(BN_, 2) }                                            \
-    SAM2B_GEMM_DISPATCH_MODES(BN_, 1)                                                          \
+#define SAM2B_GEMM_INSTANTIATE_FULL(BN_)                                                            \
+  int launch_gemm_bn##BN_(const GemmArgs& a, int mode, int cta2, int ew16, cudaStream_t stream) {    \
+    if (cta2 && ew16) { SAM2B_GEMM_DISPATCH_MODES(BN_, 2, 16) }                                     \
+    if (cta2) { SAM2B_GEMM_DISPATCH_MODES(BN_, 2, 8) }                                              \
+    if (ew16) { SAM2B_GEMM_DISPATCH_MODES(BN_, 1, 16) }                                             \
+    SAM2B_GEMM_DISPATCH_MODES(BN_, 1, 8)                                                            \
   }
-#define SAM2B_GEMM_INSTANTIATE_GENERIC(BN_)                                                    \
-  int launch_gemm_bn##BN_(const GemmArgs& a, int, int, cudaStream_t stream) { return launch_gemm<BN_, MODE_GENERIC, 1>(a, stream); }
+#define SAM2B_GEMM_INSTANTIATE_GENERIC(BN_)                                                         \
+  int launch_gemm_bn##BN_(const GemmArgs& a, int, int, int, cudaStream_t stream) { return launch_gemm<BN_, MODE_GENERIC, 1, 8>(a, stream); }
 
-int launch_gemm_bn256(const GemmArgs& a, int mode, int cta2, cudaStream_t stream);
-int launch_gemm_bn224(const GemmArgs& a, int mode, int cta2, cudaStream_t stream);
-int launch_gemm_bn192(const GemmArgs& a, int mode, int cta2, cudaStream_t stream);
-int launch_gemm_bn160(const GemmArgs& a, int mode, int cta2, cudaStream_t stream);
-int launch_gemm_bn128(const GemmArgs& a, int mode, int cta2, cudaStream_t stream);
-int launch_gemm_bn96(const GemmArgs& a, int mode, int cta2, cudaStream_t stream);
-int launch_gemm_bn64(const GemmArgs& a, int mode, int cta2, cudaStream_t stream);
-int launch_gemm_bn32(const GemmArgs& a, int mode, int cta2, cudaStream_t stream);
+int launch_gemm_bn256(const GemmArgs& a, int mode, int cta2, int ew16, cudaStream_t stream);
+int launch_gemm_bn224(const GemmArgs& a, int mode, int cta2, int ew16, cudaStream_t stream);
+int launch_gemm_bn192(const GemmArgs& a, int mode, int cta2, int ew16, cudaStream_t stream);
+int launch_gemm_bn160(const GemmArgs& a, int mode, int cta2, int ew16, cudaStream_t stream);
+int launch_gemm_bn128(const GemmArgs& a, int mode, int cta2, int ew16, cudaStream_t stream);
+int launch_gemm_bn96(const GemmArgs& a, int mode, int cta2, int ew16, cudaStream_t stream);
+int launch_gemm_bn64(const GemmArgs& a, int mode, int cta2, int ew16, cudaStream_t stream);
+int launch_gemm_bn32(const GemmArgs& a, int mode, int cta2, int ew16, cudaStream_t stream);
 
 }  // namespace sam2b

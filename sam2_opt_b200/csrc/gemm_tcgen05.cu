@@ -104,13 +104,27 @@ static void pick_tile(const GemmArgs& a, int* bn_out, int* cta2_out) {
       const long tiles = tiles_m * ((a.N + bn - 1) / bn) * a.batch;
       // measured on B200 (tests/_gemm_bench.py): pairs win 3-7 % on the K >= 1152 stage-4 shapes (long main loop), and lose
       // a few % on the K = 576 / 288 / 144 shapes whose time is set by the epilogue, not by operand traffic
-      if (c2 && (tiles < units || a.K < 1024 || (a.res_row_mod && a.res_row_mod % tm))) continue;
+      // and, combined with 16 epilogue warps, 7-11 % on the bf16-output forms from K = 576 up
+      const bool pair_ok = a.K >= 1024 || (a.out_bf16 && a.K >= 512);
+      if (c2 && (tiles < units || !pair_ok || (a.res_row_mod && a.res_row_mod % tm))) continue;
       const long waves = (tiles + units - 1) / units;
-      const double cost = (double)waves * (c2 ? 0.93 * bn + 64.0 : bn + 64.0);
+      const double cost = (double)waves * (c2 ? 0.90 * bn + 64.0 : bn + 64.0);
       if (cost < best - 1e-9) { best = cost; best_bn = bn; best_c2 = c2; }
     }
   }
   *bn_out = best_bn; *cta2_out = best_c2;
+}
+
+// 16 epilogue warps pay off where the epilogue, not the tensor pipe, sets the tile time.  The choice depends on (N, K, form)
+// only -- never on M -- so that the statistics partition of a LayerNorm producer stays batch-independent.
+static int pick_ew16(const GemmArgs& a, int bn) {
+  static int mode = -1;     // SAM2B_GEMM_EW16: 0 never, 1 heuristic (default), 2 always
+  if (mode < 0) { const char* e = getenv("SAM2B_GEMM_EW16"); mode = e ? atoi(e) : 1; }
+  if (bn < 128 || mode == 0) return 0;
+  if (mode == 2) return 1;
+  // measured (tests/_gemm_bench.py): +14..42 % on the K <= 288 bf16-output GEMMs (GELU most), +7..11 % with CTA pairs on the
+  // K >= 576 ones; nothing on the fp32 + residual forms, which are HBM-bound -- those keep 8 warps and double-buffered staging
+  return a.out_bf16 != nullptr && !a.residual;
 }
 
 int gemm_bf16(const GemmArgs& a, cudaStream_t stream) {
@@ -121,10 +135,14 @@ int gemm_bf16(const GemmArgs& a, cudaStream_t stream) {
     set_error("gemm: res_row_mod=%d must be a multiple of %d", a.res_row_mod, BM);
     return 1;
   }
-  int bn = 0, cta2 = 0;
-  if (a.force_bn >= 1000) { bn = a.force_bn - 1000; cta2 = 1; }          // 1000 + BLOCK_N: force CTA pairs (tests / tuning)
-  else if (a.force_bn) bn = a.force_bn;
-  else pick_tile(a, &bn, &cta2);
+  int bn = 0, cta2 = 0, ew16 = 0;
+  if (a.force_bn) {     // tests / tuning: BLOCK_N + 1000 (CTA pairs) + 2000 (16 epilogue warps)
+    bn = a.force_bn % 1000; cta2 = (a.force_bn / 1000) & 1; ew16 = (a.force_bn / 2000) & 1;
+  } else {
+    pick_tile(a, &bn, &cta2);
+    ew16 = pick_ew16(a, bn);
+  }
+  if (ew16 && bn < 128) ew16 = 0;
   if (cta2 && (bn < 128 || (a.res_row_mod && a.res_row_mod % (2 * BM)))) { set_error("gemm: CTA pairs need BLOCK_N >= 128 and res_row_mod %% 256 == 0"); return 1; }
   // compile-time specialised epilogues for the trunk's three dominant GEMM forms (fewer instructions per element)
   int mode = MODE_GENERIC;
@@ -134,20 +152,20 @@ int gemm_bf16(const GemmArgs& a, cudaStream_t stream) {
   else if (plain && a.out_f32 && a.residual && a.act == ACT_NONE) mode = a.out2_bf16 ? MODE_F32_BIAS_RES_LN : MODE_F32_BIAS_RES;
   if (a.out2_bf16) {
     if (mode != MODE_F32_BIAS_RES_LN || bn < 128) { set_error("gemm: the LayerNorm-producer epilogue needs bias + fp32 residual, no activation, BLOCK_N >= 128"); return 1; }
-    const int parts = 2 * ((a.N + bn - 1) / bn);
+    const int parts = (ew16 ? 4 : 2) * ((a.N + bn - 1) / bn);
     if (a.stats_out && parts > a.stats_capacity_parts) { set_error("gemm: stats buffer holds %d parts per row, %d needed", a.stats_capacity_parts, parts); return 1; }
     if (a.stats_parts_out) *a.stats_parts_out = parts;
   }
   if (a.ln_stats && (a.residual || a.ln_parts <= 0 || !a.bias || a.bias_along_m)) { set_error("gemm: LayerNorm-fold consumer needs bias along N, parts > 0 and no residual"); return 1; }
   switch (bn) {
-    case 256: return launch_gemm_bn256(a, mode, cta2, stream);
-    case 224: return launch_gemm_bn224(a, mode, cta2, stream);
-    case 192: return launch_gemm_bn192(a, mode, cta2, stream);
-    case 160: return launch_gemm_bn160(a, mode, cta2, stream);
-    case 128: return launch_gemm_bn128(a, mode, cta2, stream);
-    case 96: return launch_gemm_bn96(a, mode, cta2, stream);
-    case 64: return launch_gemm_bn64(a, mode, cta2, stream);
-    case 32: return launch_gemm_bn32(a, mode, cta2, stream);
+    case 256: return launch_gemm_bn256(a, mode, cta2, ew16, stream);
+    case 224: return launch_gemm_bn224(a, mode, cta2, ew16, stream);
+    case 192: return launch_gemm_bn192(a, mode, cta2, ew16, stream);
+    case 160: return launch_gemm_bn160(a, mode, cta2, ew16, stream);
+    case 128: return launch_gemm_bn128(a, mode, cta2, ew16, stream);
+    case 96: return launch_gemm_bn96(a, mode, cta2, ew16, stream);
+    case 64: return launch_gemm_bn64(a, mode, cta2, ew16, stream);
+    case 32: return launch_gemm_bn32(a, mode, cta2, ew16, stream);
   }
   set_error("gemm: unsupported BLOCK_N %d (256, 224, 192, 160, 128, 96, 64, 32)", bn);
   return 1;

@@ -109,7 +109,7 @@ def gemm_ln_producer(a: torch.Tensor, b: torch.Tensor, bias: torch.Tensor, resid
     N = b.shape[0]
     x = torch.empty((M, N), device=a.device, dtype=torch.float32)
     xb = torch.empty((M, N), device=a.device, dtype=torch.bfloat16)
-    cap = 2 * ((N + 31) // 32)
+    cap = 4 * ((N + 31) // 32)
     stats = torch.zeros((M, cap, 2), device=a.device, dtype=torch.float32)
     parts = C.c_int(0)
     _lib.check(lib.sam2b_op_gemm_ln_producer(_ptr(a), _ptr(b), M, N, K, _ptr(bias), _ptr(residual), _ptr(x), _ptr(xb),

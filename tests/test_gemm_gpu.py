@@ -183,3 +183,46 @@ def test_gemm_layernorm_fold(C, N2, M, bn):
         _close(y, y_ref, 1.5e-2)
     y32 = ops.gemm_ln_consumer(xb, w_scaled, bias2, stats.contiguous(), 1e-6, out_dtype=torch.float32)
     _close(y32, torch.nn.functional.layer_norm(x_ref, (C,), gamma, beta, 1e-6) @ W.t() + b, 1.5e-2)
+
+
+# ---- 16 epilogue warps (block_n + 2000), alone and with CTA pairs (+ 1000) ----
+@pytest.mark.parametrize("code", [2128, 2160, 2192, 2224, 2256, 3192, 3256])
+def test_gemm_sixteen_epilogue_warps(code):
+    from sam2_opt_b200 import ops
+    g = torch.Generator(device="cuda").manual_seed(code)
+    M, N, K = 128 * 148 * 2 + 72, 1008, 328
+    a = torch.randn(M, K, device="cuda", generator=g).bfloat16()
+    b = (torch.randn(N, K, device="cuda", generator=g) / K ** 0.5).bfloat16()
+    bias = torch.randn(N, device="cuda", generator=g)
+    res = torch.randn(M, N, device="cuda", generator=g)
+    _close(ops.gemm(a, b, bias=bias, block_n=code), _ref(a, b, bias), 2e-3)
+    _close(ops.gemm(a, b, bias=bias, out_dtype=torch.bfloat16, block_n=code), _ref(a, b, bias), 1e-2)
+    _close(ops.gemm(a, b, bias=bias, act="gelu", out_dtype=torch.bfloat16, block_n=code), _ref(a, b, bias, "gelu"), 1e-2)
+    _close(ops.gemm(a, b, bias=bias, residual=res, block_n=code), _ref(a, b, bias, residual=res), 2e-3)
+    torch.cuda.synchronize()
+
+
+@pytest.mark.parametrize("code", [2160, 2192, 3192])
+def test_gemm_layernorm_fold_sixteen_warps(code):
+    from sam2_opt_b200 import ops
+    g = torch.Generator(device="cuda").manual_seed(code)
+    M, C, Kp, N2 = 5000, 576, 320, 1152
+    a = torch.randn(M, Kp, device="cuda", generator=g).bfloat16()
+    wp = (torch.randn(C, Kp, device="cuda", generator=g) / Kp ** 0.5).bfloat16()
+    bp = torch.randn(C, device="cuda", generator=g)
+    res = torch.randn(M, C, device="cuda", generator=g) + 0.5
+    x, xb, stats = ops.gemm_ln_producer(a, wp, bp, res, block_n=code)
+    x_ref = a.float() @ wp.float().t() + bp + res
+    _close(x, x_ref, 2e-3)
+    _close(xb, x_ref, 1e-2)
+    s = stats.sum(1)
+    _close(s[:, 0], x_ref.sum(1), 1e-4)
+    _close(s[:, 1], (x_ref * x_ref).sum(1), 1e-4)
+    gamma = torch.rand(C, device="cuda", generator=g) + 0.5
+    beta = torch.randn(C, device="cuda", generator=g) * 0.3
+    W = torch.randn(N2, C, device="cuda", generator=g) / C ** 0.5
+    b = torch.randn(N2, device="cuda", generator=g)
+    ws = W * gamma[None, :]
+    ws = (ws - ws.mean(1, keepdim=True)).bfloat16()
+    y = ops.gemm_ln_consumer(xb, ws, b + W @ beta, stats.contiguous(), 1e-6, act="gelu", block_n=2256)
+    _close(y, torch.nn.functional.gelu(torch.nn.functional.layer_norm(x_ref, (C,), gamma, beta, 1e-6) @ W.t() + b), 1.5e-2)
