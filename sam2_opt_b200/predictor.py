@@ -144,7 +144,7 @@ class SAM2ImagePredictor(_Base):
 class SAM2VideoPredictor(_Base):
     """Forward video propagation with click / box prompts (BASELINE.json configs 3 and 4)."""
 
-    def __init__(self, state_dict, device="cuda", backend="b200", encode_ahead=4):
+    def __init__(self, state_dict, device="cuda", backend="b200", encode_ahead=8):
         super().__init__(state_dict, device, backend)
         self.encode_ahead = max(1, int(encode_ahead))
 
@@ -256,6 +256,9 @@ class SAM2VideoPredictor(_Base):
         T, objs = st["num_frames"], list(st["obj_ids"])
         t0 = min(st["cond"]) if start_frame_idx is None else start_frame_idx
         t1 = T - 1 if max_frame_num_to_track is None else min(T - 1, t0 + max_frame_num_to_track)
+        # One frame of look-ahead: frame t + 1 is enqueued on the GPU before frame t is handed to the caller, so the device
+        # keeps working while the caller synchronises on / copies out frame t's masks (results and order are unchanged).
+        pending = None
         for t in range(t0, t1 + 1):
             per_obj_low = {}
             tracked = [o for o in objs if not (t in st["cond"] and o in st["cond"][t])]
@@ -269,7 +272,12 @@ class SAM2VideoPredictor(_Base):
                     per_obj_low[o] = out["pred_masks"]
             st["frames_tracked"][t] = True
             low = torch.cat([per_obj_low[o] for o in objs], 0)
-            yield t, objs, self._video_res(st, low)
+            cur = (t, objs, self._video_res(st, low))
+            if pending is not None:
+                yield pending
+            pending = cur
+        if pending is not None:
+            yield pending
 
     def _track_frame(self, st, t, objs):
         """One non-prompted frame for a list of objects, batched through the engine (ref: track_step,
