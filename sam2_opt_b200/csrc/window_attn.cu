@@ -254,6 +254,151 @@ __global__ void __launch_bounds__(ATT_THREADS) window_attn_hd72_kernel(const Att
   }
 }
 
+// ------------------------------------------------------------------------------------------------------------
+// Persistent variant for the single-chunk cases (8x8 windows: 64 keys shared by 64 queries; 4x4 windows: four windows of
+// 16 tokens per tile), no q-pooling.  These launches are pure HBM traffic (read qkv once, write out once), so what
+// matters is bytes in flight: every CTA loops over work items and prefetches the Q / K / V rows of its NEXT item with
+// cp.async into the other half of a double buffer while the tensor cores work on the current one.
+// ------------------------------------------------------------------------------------------------------------
+template <bool PRIVATE>
+__global__ void __launch_bounds__(ATT_THREADS) window_attn_hd72_stream_kernel(const AttnParams p, int tiles_per_img, long n_items) {
+  extern __shared__ __align__(16) uint8_t smem_raw[];
+  bf16* sbuf = reinterpret_cast<bf16*>(smem_raw);           // [2][3][64][LDS]: Q, K, V of two items
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int C = p.heads * HD;
+  const long row_stride = 3L * C;
+  for (int i = tid; i < 6 * 64; i += ATT_THREADS) {          // pad columns [72,88) of every row stay zero
+    uint4* z = reinterpret_cast<uint4*>(sbuf + i * LDS + HD);
+    z[0] = make_uint4(0, 0, 0, 0);
+    z[1] = make_uint4(0, 0, 0, 0);
+  }
+  auto decode = [&](long it, int& tile, int& head, int& b) {
+    tile = (int)(it % tiles_per_img);
+    const long r = it / tiles_per_img;
+    head = (int)(r % p.heads);
+    b = (int)(r / p.heads);
+  };
+  auto row_token = [&](int tile, int b, int r) {            // token index of row r (query row == key row in these cases)
+    const int win = PRIVATE ? tile * 4 + (r >> 4) : tile;
+    const int j = PRIVATE ? (r & 15) : r;
+    return key_token(p, b, win, j);
+  };
+  auto prefetch = [&](long it, int buf) {
+    int tile, head, b;
+    decode(it, tile, head, b);
+    bf16* dst = sbuf + buf * 3 * 64 * LDS;
+    const bf16* src = p.qkv + head * HD;
+    for (int i = tid; i < 64 * 9; i += ATT_THREADS) {
+      const int r = i / 9, c = i - r * 9;
+      const bf16* g = src + row_token(tile, b, r) * row_stride + c * 8;
+      cp_async16(dst + r * LDS + c * 8, g);
+      cp_async16(dst + (64 + r) * LDS + c * 8, g + C);
+      cp_async16(dst + (128 + r) * LDS + c * 8, g + 2 * C);
+    }
+    cp_async_commit();
+  };
+  long it = blockIdx.x;
+  if (it < n_items) prefetch(it, 0);
+  int buf = 0;
+  for (; it < n_items; it += gridDim.x, buf ^= 1) {
+    const long nxt = it + gridDim.x;
+    if (nxt < n_items) { prefetch(nxt, buf ^ 1); cp_async_wait<1>(); } else { cp_async_wait<0>(); }
+    __syncthreads();
+    int tile, head, b;
+    decode(it, tile, head, b);
+    bf16* sQ = sbuf + buf * 3 * 64 * LDS;
+    const bf16* sK = sQ + 64 * LDS;
+    const bf16* sV = sQ + 128 * LDS;
+    uint32_t qa[5][4];
+    {
+      const uint32_t base = smem_u32(sQ + (warp * 16 + (lane & 15)) * LDS + (lane >> 4) * 8);
+#pragma unroll
+      for (int ks = 0; ks < 5; ++ks) ldsm_x4(base + ks * 32, qa[ks][0], qa[ks][1], qa[ks][2], qa[ks][3]);
+    }
+    constexpr int NT = PRIVATE ? 2 : 8;
+    const int key_lo = PRIVATE ? warp * 16 : 0;
+    float s[NT][4];
+#pragma unroll
+    for (int n = 0; n < NT; ++n) { s[n][0] = s[n][1] = s[n][2] = s[n][3] = 0.f; }
+    const bf16* kb = sK + key_lo * LDS;
+#pragma unroll
+    for (int ks = 0; ks < 5; ++ks) {
+#pragma unroll
+      for (int n = 0; n < NT; n += 2) {
+        uint32_t b0, b1, b2, b3;
+        ldsm_x4(smem_u32(kb + (8 * (n + (lane >> 4)) + (lane & 7)) * LDS + ks * 16 + ((lane >> 3) & 1) * 8), b0, b1, b2, b3);
+        mma_bf16_16816(s[n], qa[ks], b0, b1);
+        mma_bf16_16816(s[n + 1], qa[ks], b2, b3);
+      }
+    }
+    float mx[2] = {-INFINITY, -INFINITY};
+#pragma unroll
+    for (int n = 0; n < NT; ++n) {
+      mx[0] = fmaxf(mx[0], fmaxf(s[n][0], s[n][1]));
+      mx[1] = fmaxf(mx[1], fmaxf(s[n][2], s[n][3]));
+    }
+    float rs[2] = {0.f, 0.f};
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+      mx[h] = fmaxf(mx[h], __shfl_xor_sync(0xffffffffu, mx[h], 1));
+      mx[h] = fmaxf(mx[h], __shfl_xor_sync(0xffffffffu, mx[h], 2));
+      mx[h] *= p.scale_log2;
+    }
+#pragma unroll
+    for (int n = 0; n < NT; ++n) {
+      s[n][0] = ex2_approx(fmaf(s[n][0], p.scale_log2, -mx[0]));
+      s[n][1] = ex2_approx(fmaf(s[n][1], p.scale_log2, -mx[0]));
+      s[n][2] = ex2_approx(fmaf(s[n][2], p.scale_log2, -mx[1]));
+      s[n][3] = ex2_approx(fmaf(s[n][3], p.scale_log2, -mx[1]));
+      rs[0] += s[n][0] + s[n][1];
+      rs[1] += s[n][2] + s[n][3];
+    }
+    float o_acc[10][4];
+#pragma unroll
+    for (int i = 0; i < 10; ++i) { o_acc[i][0] = o_acc[i][1] = o_acc[i][2] = o_acc[i][3] = 0.f; }
+    const bf16* vb = sV + key_lo * LDS;
+#pragma unroll
+    for (int kk = 0; kk < NT / 2; ++kk) {
+      uint32_t pa[4];
+      pa[0] = pack_bf16x2(s[2 * kk][0], s[2 * kk][1]);
+      pa[1] = pack_bf16x2(s[2 * kk][2], s[2 * kk][3]);
+      pa[2] = pack_bf16x2(s[2 * kk + 1][0], s[2 * kk + 1][1]);
+      pa[3] = pack_bf16x2(s[2 * kk + 1][2], s[2 * kk + 1][3]);
+#pragma unroll
+      for (int dt = 0; dt < 10; dt += 2) {
+        uint32_t b0, b1, b2, b3;
+        ldsm_x4_t(smem_u32(vb + (16 * kk + (lane & 7) + ((lane >> 3) & 1) * 8) * LDS + 8 * (dt + (lane >> 4))), b0, b1, b2, b3);
+        mma_bf16_16816(o_acc[dt], pa, b0, b1);
+        mma_bf16_16816(o_acc[dt + 1], pa, b2, b3);
+      }
+    }
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+      rs[h] += __shfl_xor_sync(0xffffffffu, rs[h], 1);
+      rs[h] += __shfl_xor_sync(0xffffffffu, rs[h], 2);
+    }
+    const float inv0 = 1.f / rs[0], inv1 = 1.f / rs[1];
+    __syncwarp();        // every lane of this warp has read its Q fragments: rows 16w..16w+15 of sQ become the output staging
+    {
+      const int g = lane >> 2, tq = lane & 3;
+      bf16* r0 = sQ + (warp * 16 + g) * LDS;
+      bf16* r1 = sQ + (warp * 16 + g + 8) * LDS;
+#pragma unroll
+      for (int dt = 0; dt < 9; ++dt) {
+        *reinterpret_cast<uint32_t*>(r0 + dt * 8 + tq * 2) = pack_bf16x2(o_acc[dt][0] * inv0, o_acc[dt][1] * inv0);
+        *reinterpret_cast<uint32_t*>(r1 + dt * 8 + tq * 2) = pack_bf16x2(o_acc[dt][2] * inv1, o_acc[dt][3] * inv1);
+      }
+    }
+    __syncwarp();
+    for (int i = lane; i < 16 * 9; i += 32) {
+      const int rr = i / 9, c = i - rr * 9;
+      const int r = warp * 16 + rr;
+      *reinterpret_cast<uint4*>(p.out + row_token(tile, b, r) * C + head * HD + c * 8) = *reinterpret_cast<const uint4*>(sQ + r * LDS + c * 8);
+    }
+    __syncthreads();     // this buffer is refilled by the prefetch issued at the top of the next iteration
+  }
+}
+
 int window_attention_hd72(const bf16* qkv, bf16* out, int B, int H, int W, int heads, int ws, int q_pool, cudaStream_t stream) {
   if (ws <= 0 || H % ws || W % ws || (q_pool && (ws & 1))) { set_error("window_attention: bad window %d for %dx%d", ws, H, W); return 1; }
   // 16x16 windows and global attention run on the tcgen05 flash kernel (attn_tcgen05.cu)
@@ -274,7 +419,23 @@ int window_attention_hd72(const bf16* qkv, bf16* out, int B, int H, int W, int h
   if (g_prof_on) snprintf(nm, sizeof(nm), "attn h%d heads%d ws%d pool%d b%d", H, heads, ws, q_pool, B);
   const double nq = (double)B * nwin * p.QW * heads;
   ProfRange pr(stream, nm, 4.0 * nq * p.KW * HD, ((double)B * H * W * 3 + (double)B * nwin * p.QW) * heads * HD * 2.0);
-  if (p.QW >= 64) {
+  if (!q_pool && ((p.KW == 64) || (p.KW == 16 && nwin % 4 == 0)) && !getenv("SAM2B_LEGACY_WINDOW")) {
+    // single-chunk windows: persistent streaming kernel (3 CTAs per SM, next item prefetched while this one computes)
+    const bool priv = p.KW == 16;
+    const int tiles_per_img = priv ? nwin / 4 : nwin;
+    const long n_items = (long)tiles_per_img * heads * B;
+    const size_t smem2 = 6 * 64 * LDS * sizeof(bf16);
+    static bool attr2 = false;
+    if (!attr2) {
+      cudaFuncSetAttribute(window_attn_hd72_stream_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2);
+      cudaFuncSetAttribute(window_attn_hd72_stream_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2);
+      attr2 = true;
+    }
+    const long max_ctas = (long)num_sms() * 3;
+    const int grid = (int)(n_items < max_ctas ? n_items : max_ctas);
+    if (priv) window_attn_hd72_stream_kernel<true><<<grid, ATT_THREADS, smem2, stream>>>(p, tiles_per_img, n_items);
+    else window_attn_hd72_stream_kernel<false><<<grid, ATT_THREADS, smem2, stream>>>(p, tiles_per_img, n_items);
+  } else if (p.QW >= 64) {
     if (p.QW % 64 || p.KW % 64) { set_error("window_attention: QW=%d KW=%d not multiples of 64", p.QW, p.KW); return 1; }
     dim3 grid(nwin * (p.QW / 64), heads, B);
     window_attn_hd72_kernel<false><<<grid, ATT_THREADS, smem, stream>>>(p);
