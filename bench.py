@@ -215,7 +215,15 @@ def main():
         g_ms, g_fl = sum(x[0] for x in g), sum(x[1] for x in g)
         peak, hbm, how = _peaks()
         ach = g_fl / (g_ms * 1e-3) / 1e12
-        roof = {"bound": "tensor", "achieved": ach, "peak": peak, "unit": "TFLOP/s", "frac": ach / peak, "traffic": None,
+        traffic, traffic_note = None, None
+        tp = os.path.join(ROOT, "profiles", "r1e_traffic.json")
+        if os.path.exists(tp):
+            tj = json.load(open(tp))
+            traffic = tj["dram_bytes_per_launch_avg"]
+            traffic_note = ("bytes per launch (dram__bytes_read.sum + dram__bytes_write.sum), mean of the four stage-3 GEMM forms "
+                            "at batch 16 from one ncu --set full capture: " + tj["source"])
+        roof = {"bound": "tensor", "achieved": ach, "peak": peak, "unit": "TFLOP/s", "frac": ach / peak, "traffic": traffic,
+                "traffic_note": traffic_note,
                 "kernel": "gemm_bf16_tcgen05_kernel", "launches_per_step": len(g), "avg_launch_ms": g_ms / max(1, len(g)),
                 "share_of_step_kernel_time": g_ms / all_ms, "peak_source": how,
                 "flops_per_launch_avg": g_fl / max(1, len(g)),
