@@ -44,6 +44,7 @@ static constexpr int BAR_BYTES = 512;
 struct GemmKernelParams {
   int M, N, K, batch;
   int tiles_m, tiles_n, num_kb;
+  uint32_t div_n_mul, div_n_shr, div_m_mul, div_m_shr;   // exact division of the tile index by tiles_n / tiles_m (mulhi + shift)
   int b_batched;
   float alpha;
   const float* bias; int bias_along_m;
@@ -111,6 +112,16 @@ SAM2B_DEVINL float gelu_fast_bf16(float x) {
   return fmaf(-fabsf(x), h, fmaxf(x, 0.0f));
 }
 
+// q = t / d for 0 <= t < 2^31 with (mul, shr) from fast_div_setup(d): q = umulhi(t, mul) >> shr
+SAM2B_DEVINL uint32_t fast_div(uint32_t t, uint32_t mul, uint32_t shr) { return mul ? (__umulhi(t, mul) >> shr) : t; }
+// tile index -> (n block, m block, batch), n fastest
+SAM2B_DEVINL void decode_tile(const GemmKernelParams& p, int t, int& n_blk, int& m_blk, int& b) {
+  const uint32_t r = fast_div((uint32_t)t, p.div_n_mul, p.div_n_shr);
+  n_blk = t - (int)r * p.tiles_n;
+  b = (int)fast_div(r, p.div_m_mul, p.div_m_shr);
+  m_blk = (int)r - b * p.tiles_m;
+}
+
 template <int BN, int MODE, int NCTA, int EW>
 __global__ void __launch_bounds__(gemm_threads(EW), 1)
 gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b,
@@ -166,9 +177,8 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid
     if (lane == 0) {
       int stage = 0; uint32_t phase = 0;
       for (int t = tile0; t < num_tiles; t += tile_step) {
-        const int n_blk = t % p.tiles_n;
-        const int m_blk = (t / p.tiles_n) % p.tiles_m;
-        const int b = t / (p.tiles_n * p.tiles_m);
+        int n_blk, m_blk, b;
+        decode_tile(p, t, n_blk, m_blk, b);
         for (int kb = 0; kb < p.num_kb; ++kb) {
           mbar_wait(&empty_bar[stage], phase ^ 1);
           if (NCTA == 2) {
@@ -246,9 +256,8 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid
     uint32_t i = 0;                       // live chunks processed by this warp: buffer = i & 1 (two_buf), res phase
     int local = 0;
     for (int t = tile0; t < num_tiles; t += tile_step, ++local) {
-      const int n_blk = t % p.tiles_n;
-      const int m_blk = (t / p.tiles_n) % p.tiles_m;
-      const int b = t / (p.tiles_n * p.tiles_m);
+      int n_blk, m_blk, b;
+      decode_tile(p, t, n_blk, m_blk, b);
       const int acc = local % Cfg::NACC;
       const uint32_t acc_phase = (local / Cfg::NACC) & 1;
       const int row_g = m_blk * TILE_M + cta_rank * BM + q * 32;   // first row of this warp's 32-row slab
@@ -457,6 +466,15 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid
 // ------------------------------------------------------------------------------------------
 // host side: launch of one instantiation
 // ------------------------------------------------------------------------------------------
+// (mul, shr) with umulhi(t, mul) >> shr == t / d for every 0 <= t < 2^31 (round-up method); d == 1 -> mul = 0 (identity)
+static inline void fast_div_setup(uint32_t d, uint32_t* mul, uint32_t* shr) {
+  if (d <= 1) { *mul = 0; *shr = 0; return; }
+  uint32_t l = 0;
+  while ((1ull << l) < d) ++l;                     // l = ceil(log2 d)
+  const unsigned long long m = ((1ull << (31 + l)) + d - 1) / d;   // < 2^32 because 2^(l-1) < d
+  *mul = (uint32_t)m; *shr = l - 1;
+}
+
 template <int BN, int MODE, int NCTA, int EW>
 static int launch_gemm(const GemmArgs& a, cudaStream_t stream) {
   using Cfg = GemmCfg<BN, NCTA, MODE, EW>;
@@ -505,6 +523,8 @@ static int launch_gemm(const GemmArgs& a, cudaStream_t stream) {
   GemmKernelParams p;
   p.M = a.M; p.N = a.N; p.K = a.K; p.batch = a.batch;
   p.tiles_m = (a.M + BM * NCTA - 1) / (BM * NCTA); p.tiles_n = (a.N + BN - 1) / BN; p.num_kb = (a.K + BK - 1) / BK;
+  fast_div_setup((uint32_t)p.tiles_n, &p.div_n_mul, &p.div_n_shr);
+  fast_div_setup((uint32_t)p.tiles_m, &p.div_m_mul, &p.div_m_shr);
   p.b_batched = b_batched ? 1 : 0;
   p.alpha = a.alpha; p.bias = a.bias; p.bias_along_m = a.bias_along_m; p.act = a.act; p.gamma = a.gamma;
   p.has_res = a.residual ? 1 : 0; p.res_batched = res_batched ? 1 : 0; p.res_row_mod = a.res_row_mod;
