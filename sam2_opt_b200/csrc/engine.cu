@@ -85,8 +85,9 @@ struct sam2b_engine {
   std::map<std::string, Tensor> w;
   std::map<std::string, Buf> ws;   // named workspace buffers, grow-only
   std::vector<BlockCfg> blocks;
-  cudaStream_t copy_stream = nullptr;
-  cudaEvent_t ev[8] = {};
+  cudaStream_t copy_stream = nullptr;      // host -> device
+  cudaStream_t copy_stream2 = nullptr;     // device -> host (PCIe is full duplex: the two directions overlap)
+  cudaEvent_t ev[12] = {};
 
   Tensor* find(const std::string& n) {
     auto it = w.find(n);
@@ -238,8 +239,11 @@ static int finalize(sam2b_engine* e) {
 }
 
 // One micro-batch (n images resident on the device) through trunk + neck.
+// early_ev (optional, 2 events): recorded on `st` as soon as fpn0 / fpn1 are complete -- the level-0/1 neck outputs depend
+// only on the stage-1/2 taps, so they are produced right after blocks 1 and 7 and can leave the device while the rest of
+// the trunk is still running.
 static int image_encode_mb(sam2b_engine* e, const float* img, int n, int normalised, int add_no_mem, float* fpn0,
-                           float* fpn1, float* fpn2, cudaStream_t st) {
+                           float* fpn1, float* fpn2, cudaStream_t st, cudaEvent_t* early_ev = nullptr) {
   const long T0 = 65536L * n;
   float *X, *X2, *SC, *LAT3;
   bf16 *XN, *QKV, *ATT, *HID, *COLS, *TAP[4];
@@ -257,6 +261,25 @@ static int image_encode_mb(sam2b_engine* e, const float* img, int n, int normali
   TRY(ws_get_t(e, "tap3", (size_t)T0 / 64 * 1152, &TAP[3]));
   TRY(ws_get_t(e, "lat3", (size_t)n * 256 * 1024, &LAT3));
 
+  // ---- FpnNeck (+ conv_s0 / conv_s1 folded into the level-0/1 laterals): out[b][co][hw] = W[co][:] . x[b][hw][:] ----
+  struct NeckJob { const char* w; const char* bias; const bf16* x; int cin, cout, hw; float* out; };
+  const NeckJob jobs[4] = {
+      {"derived.neck.lat3.weight", "derived.neck.lat3.bias", TAP[3], 1152, 256, 1024, LAT3},
+      {"derived.neck.lat2.weight", add_no_mem ? "derived.neck.lat2.bias_nomem" : "derived.neck.lat2.bias", TAP[2], 576, 256, 4096, fpn2},
+      {"derived.neck.s1.weight", "derived.neck.s1.bias", TAP[1], 288, 64, 16384, fpn1},
+      {"derived.neck.s0.weight", "derived.neck.s0.bias", TAP[0], 144, 32, 65536, fpn0},
+  };
+  auto neck = [&](int k) -> int {
+    const NeckJob& j = jobs[k];
+    GemmArgs g;
+    g.A = W16(e, j.w); g.lda = j.cin; g.M = j.cout; g.K = j.cin;   // weights shared by the batch
+    g.B = j.x; g.ldb = j.cin; g.N = j.hw; g.b_batch_stride = (long)j.hw * j.cin;
+    g.batch = n;
+    g.bias = W32(e, j.bias); g.bias_along_m = 1;
+    g.out_f32 = j.out; g.ldc = j.hw; g.c_batch_stride = (long)j.cout * j.hw;
+    return gemm_bf16(g, st);
+  };
+  bool early_done = false;
   const std::string t = "image_encoder.trunk.";
   static int ln_fold = -1;
   if (ln_fold < 0) { const char* ev = getenv("SAM2B_LN_FOLD"); ln_fold = ev ? atoi(ev) : 1; }
@@ -339,6 +362,14 @@ static int image_encode_mb(sam2b_engine* e, const float* img, int n, int normali
       }
       xb_in = xb_out;
       if (is_tap) ++tap;
+      if (i == 1) {          // level 0 (conv_s0 o lateral) straight from the stage-1 tap
+        TRY(neck(3));
+        if (early_ev) CUDA_OK(cudaEventRecord(early_ev[0], st));
+      } else if (i == 7) {   // level 1 from the stage-2 tap
+        TRY(neck(2));
+        if (early_ev) CUDA_OK(cudaEventRecord(early_ev[1], st));
+        early_done = true;
+      }
     }
   } else {
   // ---- patch embed (im2col + GEMM) with the constant position embedding added in the epilogue ----
@@ -415,22 +446,12 @@ static int image_encode_mb(sam2b_engine* e, const float* img, int n, int normali
     }
   }
   }
-  // ---- FpnNeck (+ conv_s0 / conv_s1 folded into the level-0/1 laterals): out[b][co][hw] = W[co][:] . x[b][hw][:] ----
-  struct NeckJob { const char* w; const char* bias; const bf16* x; int cin, cout, hw; float* out; };
-  const NeckJob jobs[4] = {
-      {"derived.neck.lat3.weight", "derived.neck.lat3.bias", TAP[3], 1152, 256, 1024, LAT3},
-      {"derived.neck.lat2.weight", add_no_mem ? "derived.neck.lat2.bias_nomem" : "derived.neck.lat2.bias", TAP[2], 576, 256, 4096, fpn2},
-      {"derived.neck.s1.weight", "derived.neck.s1.bias", TAP[1], 288, 64, 16384, fpn1},
-      {"derived.neck.s0.weight", "derived.neck.s0.bias", TAP[0], 144, 32, 65536, fpn0},
-  };
-  for (const NeckJob& j : jobs) {
-    GemmArgs g;
-    g.A = W16(e, j.w); g.lda = j.cin; g.M = j.cout; g.K = j.cin;   // weights shared by the batch
-    g.B = j.x; g.ldb = j.cin; g.N = j.hw; g.b_batch_stride = (long)j.hw * j.cin;
-    g.batch = n;
-    g.bias = W32(e, j.bias); g.bias_along_m = 1;
-    g.out_f32 = j.out; g.ldc = j.hw; g.c_batch_stride = (long)j.cout * j.hw;
-    TRY(gemm_bf16(g, st));
+  TRY(neck(0));
+  TRY(neck(1));
+  if (!early_done) {
+    TRY(neck(2));
+    TRY(neck(3));
+    if (early_ev) { CUDA_OK(cudaEventRecord(early_ev[0], st)); CUDA_OK(cudaEventRecord(early_ev[1], st)); }
   }
   TRY(upsample2x_add_nchw(fpn2, LAT3, n, 256, 64, 64, st));
   return 0;
@@ -639,6 +660,7 @@ int sam2b_create(int device, sam2b_handle* out) {
   e->device = device;
   build_block_cfgs(e->blocks);
   CUDA_OK(cudaStreamCreateWithFlags(&e->copy_stream, cudaStreamNonBlocking));
+  CUDA_OK(cudaStreamCreateWithFlags(&e->copy_stream2, cudaStreamNonBlocking));
   for (auto& ev : e->ev) CUDA_OK(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
   *out = e;
   return 0;
@@ -652,6 +674,7 @@ int sam2b_destroy(sam2b_handle h) {
   for (auto& kv : h->ws) if (kv.second.p) cudaFree(kv.second.p);
   for (auto& ev : h->ev) if (ev) cudaEventDestroy(ev);
   if (h->copy_stream) cudaStreamDestroy(h->copy_stream);
+  if (h->copy_stream2) cudaStreamDestroy(h->copy_stream2);
   delete h;
   return 0;
 }
@@ -699,7 +722,7 @@ int sam2b_image_encode_host(sam2b_handle h, const float* img_host, int n, int no
   if (n <= 0 || !img_host || !fpn0_host || !fpn1_host || !fpn2_host) { set_error("sam2b_image_encode_host: bad arguments"); return 1; }
   CUDA_OK(cudaSetDevice(h->device));
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
-  // double-buffered staging: copies run on copy_stream, compute on `st`
+  // double-buffered staging: uploads run on copy_stream, downloads on copy_stream2, compute on `st`
   const size_t in_sz = (size_t)3 * 1024 * 1024, o0 = (size_t)32 * 65536, o1 = (size_t)64 * 16384, o2 = (size_t)256 * 4096;
   const int kMaxMicroBatch = max_micro_batch();
   float *in[2], *f0[2], *f1[2], *f2[2];
@@ -710,10 +733,12 @@ int sam2b_image_encode_host(sam2b_handle h, const float* img_host, int n, int no
     TRY(ws_get_t(h, names[s][2], o1 * kMaxMicroBatch, &f1[s]));
     TRY(ws_get_t(h, names[s][3], o2 * kMaxMicroBatch, &f2[s]));
   }
-  cudaStream_t cs = h->copy_stream;
-  // ev[0..1]: input slot s uploaded; ev[2..3]: compute on slot s done; ev[4..5]: outputs of slot s downloaded
+  cudaStream_t cs = h->copy_stream, ds = h->copy_stream2;
+  // ev[0..1]: input slot s uploaded; ev[2..3]: compute on slot s done; ev[4..5]: outputs of slot s downloaded;
+  // ev[8..9], ev[10..11]: fpn0 / fpn1 of slot s complete (early, see image_encode_mb)
   CUDA_OK(cudaEventRecord(h->ev[6], st));
   CUDA_OK(cudaStreamWaitEvent(cs, h->ev[6], 0));
+  CUDA_OK(cudaStreamWaitEvent(ds, h->ev[6], 0));
   int it = 0;
   for (int i0 = 0; i0 < n; i0 += kMaxMicroBatch, ++it) {
     const int s = it & 1;
@@ -723,14 +748,18 @@ int sam2b_image_encode_host(sam2b_handle h, const float* img_host, int n, int no
     CUDA_OK(cudaEventRecord(h->ev[s], cs));
     CUDA_OK(cudaStreamWaitEvent(st, h->ev[s], 0));
     if (it >= 2) CUDA_OK(cudaStreamWaitEvent(st, h->ev[4 + s], 0));       // slot's previous outputs have left the device
-    TRY(image_encode_mb(h, in[s], mb, normalised, add_no_mem_embed, f0[s], f1[s], f2[s], st));
+    cudaEvent_t early[2] = {h->ev[8 + s], h->ev[10 + s]};
+    TRY(image_encode_mb(h, in[s], mb, normalised, add_no_mem_embed, f0[s], f1[s], f2[s], st, early));
     CUDA_OK(cudaEventRecord(h->ev[2 + s], st));
-    CUDA_OK(cudaStreamWaitEvent(cs, h->ev[2 + s], 0));
-    CUDA_OK(cudaMemcpyAsync(fpn0_host + (size_t)i0 * o0, f0[s], o0 * mb * 4, cudaMemcpyDeviceToHost, cs));
-    CUDA_OK(cudaMemcpyAsync(fpn1_host + (size_t)i0 * o1, f1[s], o1 * mb * 4, cudaMemcpyDeviceToHost, cs));
-    CUDA_OK(cudaMemcpyAsync(fpn2_host + (size_t)i0 * o2, f2[s], o2 * mb * 4, cudaMemcpyDeviceToHost, cs));
-    CUDA_OK(cudaEventRecord(h->ev[4 + s], cs));
+    CUDA_OK(cudaStreamWaitEvent(ds, early[0], 0));
+    CUDA_OK(cudaMemcpyAsync(fpn0_host + (size_t)i0 * o0, f0[s], o0 * mb * 4, cudaMemcpyDeviceToHost, ds));
+    CUDA_OK(cudaStreamWaitEvent(ds, early[1], 0));
+    CUDA_OK(cudaMemcpyAsync(fpn1_host + (size_t)i0 * o1, f1[s], o1 * mb * 4, cudaMemcpyDeviceToHost, ds));
+    CUDA_OK(cudaStreamWaitEvent(ds, h->ev[2 + s], 0));
+    CUDA_OK(cudaMemcpyAsync(fpn2_host + (size_t)i0 * o2, f2[s], o2 * mb * 4, cudaMemcpyDeviceToHost, ds));
+    CUDA_OK(cudaEventRecord(h->ev[4 + s], ds));
   }
+  CUDA_OK(cudaStreamSynchronize(ds));
   CUDA_OK(cudaStreamSynchronize(cs));
   CUDA_OK(cudaStreamSynchronize(st));
   return 0;

@@ -81,3 +81,18 @@ def test_rejects_bad_inputs(engine):
         engine.image_encode(torch.zeros(1, 3, 512, 512, device="cuda"), True, False)
     with pytest.raises(RuntimeError, match="CUDA tensor"):
         engine.image_encode(torch.zeros(1, 3, 1024, 1024), True, False)
+
+
+def test_host_buffer_entry_point_matches_device_path(engine):
+    """sam2b_image_encode_host (pinned host in / out, uploads, compute and downloads overlapped over two micro-batch slots,
+    level-0/1 outputs leaving the device early) must return exactly what sam2b_image_encode returns: 18 images = one full
+    micro-batch of 16 plus a ragged one, called twice so that both staging slots are reused."""
+    from oracle.synth import synth_image_norm
+    imgs = synth_image_norm(18, seed=9)
+    dev = engine.image_encode(imgs.cuda(), normalised=True, add_no_mem_embed=False)
+    torch.cuda.synchronize()
+    host = None
+    for _ in range(2):
+        host = engine.image_encode_host(imgs.pin_memory(), True, False, host)
+    for d, h in zip(dev, host):
+        assert torch.equal(d.cpu(), h)
