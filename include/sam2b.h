@@ -97,6 +97,11 @@ int sam2b_op_cast_bf16(const float* x, void* y_bf16, int64_t n, void* stream);
 int sam2b_op_maxpool2x2_nhwc(const float* x, float* y, int b, int hgt, int wid, int c, void* stream);
 int sam2b_op_window_attention(const void* qkv_bf16, void* out_bf16, int b, int hgt, int wid, int heads, int ws,
                               int q_pool, void* stream);
+/* Connected components with areas, batched (replaces the reference's only native kernel, sam2/csrc/connected_components.cu:
+ * get_connected_componnets, called by fill_holes_in_mask_scores, sam2/utils/misc.py:311-338).  mask_u8 dev [n][h][w]
+ * (non-zero = foreground), labels / counts dev int32 [n][h][w]: label 0 and count 0 for background, otherwise a positive
+ * label shared by the 8-connected component and the component's area in pixels. */
+int sam2b_op_connected_components(const void* mask_u8, int32_t* labels, int32_t* counts, int n, int h, int w, void* stream);
 int sam2b_op_softmax_rows(const float* s, int64_t lds, void* p_bf16, int64_t ldp, int64_t rows, int cols, void* stream);
 /* Single-head flash attention, head_dim 256 (the MemoryAttention core; reference sam/transformer.py:265-296):
  * out[b] = softmax(q[b] k[b]^T / 16) v[b];  q [n][tq][256], k, v [n][lk][256], out [n][tq][256], all bf16 device memory,

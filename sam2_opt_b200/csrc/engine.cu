@@ -866,6 +866,10 @@ int sam2b_op_window_attention(const void* qkv, void* out, int b, int hgt, int wi
   return window_attention_hd72(reinterpret_cast<const bf16*>(qkv), reinterpret_cast<bf16*>(out), b, hgt, wid, heads, ws, q_pool,
                                reinterpret_cast<cudaStream_t>(stream));
 }
+int sam2b_op_connected_components(const void* mask_u8, int32_t* labels, int32_t* counts, int n, int h, int w, void* stream) {
+  if (!mask_u8 || !labels || !counts) { set_error("sam2b_op_connected_components: null argument"); return 1; }
+  return connected_components(reinterpret_cast<const uint8_t*>(mask_u8), labels, counts, n, h, w, reinterpret_cast<cudaStream_t>(stream));
+}
 int sam2b_op_softmax_rows(const float* s, int64_t lds, void* p, int64_t ldp, int64_t rows, int cols, void* stream) {
   return softmax_rows(s, lds, reinterpret_cast<bf16*>(p), ldp, rows, cols, reinterpret_cast<cudaStream_t>(stream));
 }

@@ -94,6 +94,9 @@ int flash_attention_hd256(const bf16* q, long q_batch_stride, const bf16* k, lon
 
 // Row softmax over fp32 scores -> bf16 probabilities (row stride lds / ldp elements), `cols` valid columns;
 // columns in [cols, ldp) are written as zero.
+// Connected components of `mask != 0` under 8-connectivity (connected_components.cu): labels int32 [n][H][W] (0 = background,
+// otherwise 1 + smallest pixel index of the component), counts = area of the pixel's component (0 for background).
+int connected_components(const uint8_t* mask, int* labels, int* counts, int n, int H, int W, cudaStream_t stream);
 int softmax_rows(const float* s, long lds, bf16* p, long ldp, long rows, int cols, cudaStream_t stream);
 
 // Axial RoPE (interleaved pairs) applied in place on x [rows, 256] fp32->bf16 conversion included:

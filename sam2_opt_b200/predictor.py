@@ -144,9 +144,14 @@ class SAM2ImagePredictor(_Base):
 class SAM2VideoPredictor(_Base):
     """Forward video propagation with click / box prompts (BASELINE.json configs 3 and 4)."""
 
-    def __init__(self, state_dict, device="cuda", backend="b200", encode_ahead=8):
+    def __init__(self, state_dict, device="cuda", backend="b200", encode_ahead=8, fill_hole_area=0):
+        """fill_hole_area: as the reference's constructor argument (sam2_video_predictor_official.py:25,889-894; the
+        reference's builder sets 8 when its native extension is available, build_sam.py:128-129): holes of at most that
+        many pixels in the low-res mask scores are filled before the masks are stored / returned.  0 = off, which is what
+        the reference does without `sam2._C` and what the golden fixtures use."""
         super().__init__(state_dict, device, backend)
         self.encode_ahead = max(1, int(encode_ahead))
+        self.fill_hole_area = int(fill_hole_area)
 
     @torch.no_grad()
     def init_state(self, frames=None, video_height=None, video_width=None, offload_video_to_cpu=True):
@@ -230,7 +235,14 @@ class SAM2VideoPredictor(_Base):
         multimask = 0 < pts.shape[0] <= 1      # ref: _use_multimask, sam2_base_official.py:1181-1189 (min 0, max 1 point)
         _, _, _, low, high, ptr, obj = H.forward_sam_heads(self.w, pix, point_inputs=pin, high_res_features=hr,
                                                            multimask_output=multimask, pe=self._dense_pe)
-        return {"pred_masks": low, "obj_ptr": ptr, "object_score_logits": obj, "maskmem_features": None, "maskmem_pos": None}
+        return {"pred_masks": self._fill_holes(low), "obj_ptr": ptr, "object_score_logits": obj, "maskmem_features": None,
+                "maskmem_pos": None}
+
+    def _fill_holes(self, low):
+        if self.fill_hole_area > 0:
+            from .postprocess import fill_holes_in_mask_scores
+            low = fill_holes_in_mask_scores(low, self.fill_hole_area)
+        return low
 
     @torch.no_grad()
     def propagate_in_video_preflight(self, st):
@@ -302,6 +314,7 @@ class SAM2VideoPredictor(_Base):
             hr_n = [h.expand(n, -1, -1, -1) for h in hr]
             _, _, _, low, high, ptr, obj = H.forward_sam_heads(self.w, pix, high_res_features=hr_n, multimask_output=True, pe=self._dense_pe)
             mf, mp = self._encode_memory(f2, high, obj, from_points=False)
+            low = self._fill_holes(low)            # after the memory is encoded from the unfilled masks, as in the reference
             for i, (o, _) in enumerate(items):
                 results[o] = {"pred_masks": low[i:i + 1], "obj_ptr": ptr[i:i + 1], "object_score_logits": obj[i:i + 1],
                               "maskmem_features": mf[i:i + 1], "maskmem_pos": mp[i:i + 1]}

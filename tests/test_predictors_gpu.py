@@ -82,3 +82,31 @@ def test_video_full_bank_vs_oracle_and_object_batching(weights):
     assert min(ious) >= 0.99
     assert min(ious_b) >= 0.995
     vp.release()
+
+
+def test_video_fill_hole_area():
+    """fill_hole_area post-processes the stored / returned low-res scores (reference
+    sam2_video_predictor_official.py:889-894).  The prompted frame, which depends on nothing else, must equal the plain
+    run's frame passed through the oracle's hole filling bit for bit; every later frame (whose memory was encoded from
+    the filled prompted frame, as in the reference's preflight) must be hole-free up to that area."""
+    import numpy as np
+    from oracle import postprocess_oracle as PO
+    from sam2_opt_b200.predictor import SAM2VideoPredictor
+    from sam2_opt_b200.synth import synth_video
+    from sam2_opt_b200.synth_weights import make_weights
+    w = make_weights(0)
+    frames = synth_video(4, seed=2)
+    outs = {}
+    for area in (0, 8):
+        vp = SAM2VideoPredictor(w, fill_hole_area=area)
+        st = vp.init_state(frames)
+        vp.add_new_points_or_box(st, 0, 1, points=[[512, 512]], labels=[1])
+        list(vp.propagate_in_video(st))
+        lows = [st["cond"][0][1]["pred_masks"]] + [st["non_cond"][1][t]["pred_masks"] for t in (1, 2, 3)]
+        outs[area] = [x.cpu().numpy() for x in lows]
+        vp.release()
+    want0 = PO.fill_holes_in_mask_scores(outs[0][0], 8)
+    assert np.array_equal(outs[8][0], want0)
+    print("pixels changed by hole filling on the prompted frame:", int((want0 != outs[0][0]).sum()))
+    for filled in outs[8]:
+        assert np.array_equal(PO.fill_holes_in_mask_scores(filled, 8), filled)
