@@ -105,3 +105,13 @@ def install(*classes):
 
         patched._sam2b_patched = True
         cls.speedup = patched
+
+
+def install_postprocess(misc_module):
+    """Give the reference's hole filling its labelling kernel back: ``sam2.utils.misc.get_connected_components`` imports
+    the native extension ``sam2._C`` (misc.py:47-63) and ``fill_holes_in_mask_scores`` silently skips the step when it is
+    missing (misc.py:325-336).  After ``install_postprocess(sam2.utils.misc)`` the reference predictors' ``fill_hole_area``
+    works on the B200 box through ``sam2b_op_connected_components`` (same (labels, counts) contract)."""
+    from . import postprocess
+    misc_module.get_connected_components = postprocess.get_connected_components
+    return misc_module

@@ -103,3 +103,22 @@ def test_video_predictor_speedup_dropin(weights, golden):
     assert [c[1:] for c in eng.calls if c[0] == "memory_attention"] == [(1, 4), (2, 8)]
     S.speedup(m, "torch")
     assert m.inference_image == m.inference_image_torch and m.memory_attention.backend_contexts == []
+
+
+def test_install_postprocess_rebinds_reference_labelling():
+    """The reference's fill_holes_in_mask_scores looks `get_connected_components` up in its own module at call time
+    (misc.py:320), so rebinding the module attribute is enough; on this CPU-only box our function then raises (no CPU
+    path) and the reference falls back to returning the mask unchanged with a warning (misc.py:325-336)."""
+    import warnings
+    import torch
+    rl.build_reference("image")            # puts the reference package (with its stubs) on sys.path
+    import sam2.utils.misc as misc
+    from sam2_opt_b200 import postprocess
+    from sam2_opt_b200.speedup import install_postprocess
+    install_postprocess(misc)
+    assert misc.get_connected_components is postprocess.get_connected_components
+    m = torch.randn(1, 1, 16, 16)
+    with warnings.catch_warnings(record=True) as w:
+        warnings.simplefilter("always")
+        out = misc.fill_holes_in_mask_scores(m, 8)
+    assert torch.equal(out, m) and any("CUDA tensor" in str(x.message) for x in w)
