@@ -140,7 +140,7 @@ flash_attn_hd256_tcgen05_kernel(const __grid_constant__ CUtensorMap map_q, const
     // ===================== MMA issuer (one thread) =====================
     if (lane == 0) {
       constexpr uint32_t idesc_qk = make_idesc_ex(128, 64, 0);
-      constexpr uint32_t idesc_pv = make_idesc_ex(128, 64, 1);
+      constexpr uint32_t idesc_pv = make_idesc_ex(128, 256, 1);
       const uint32_t sbase = smem_u32(smem);
       uint32_t n_s = 0;       // Q K^T products issued (S buffer = n_s & 1)
       uint32_t n_o = 0;       // P V products issued
@@ -181,14 +181,12 @@ flash_attn_hd256_tcgen05_kernel(const __grid_constant__ CUtensorMap map_q, const
           mbar_wait(p_full, n_o & 1);
           tc_fence_after();
           const uint32_t pa = sbase + OFF_P, v = sbase + OFF_V + st * KV_BYTES;
+          // one N = 256 instruction per 16 keys: V is MN-major, its four 64-dim sub-tiles are 8 KB apart (LBO); a wide N keeps
+          // the shared-memory operand traffic (P slice re-read per instruction) under the 128 B/clk the SM can deliver
 #pragma unroll
-          for (int ks = 0; ks < 4; ++ks) {
-            const uint64_t da = make_smem_desc(pa + ks * 32, 16, 1024, 2);
-#pragma unroll
-            for (int s = 0; s < 4; ++s)
-              umma_bf16(tmem_base + COL_O + 64 * s, da, make_smem_desc(v + s * 8192 + ks * 2048, 1024, 1024, 2), idesc_pv,
-                        (j | ks) != 0);
-          }
+          for (int ks = 0; ks < 4; ++ks)
+            umma_bf16(tmem_base + COL_O, make_smem_desc(pa + ks * 32, 16, 1024, 2), make_smem_desc(v + ks * 2048, 8192, 1024, 2),
+                      idesc_pv, (j | ks) != 0);
           umma_commit(o_done);
           umma_commit(&v_empty[st]);
           ++n_o;
