@@ -28,16 +28,15 @@ static constexpr int TK = 64;
 static constexpr int NSTAGE = 2;
 static constexpr int Q_BYTES = TQ * D * 2;          // 64 KB: 4 sub-tiles of 16 KB
 static constexpr int KV_BYTES = TK * D * 2;         // 32 KB: 4 sub-tiles of 8 KB
-static constexpr int P_BYTES = TQ * TK * 2;         // 16 KB
 static constexpr int OFF_Q = 0;
 static constexpr int OFF_K = OFF_Q + Q_BYTES;
 static constexpr int OFF_V = OFF_K + NSTAGE * KV_BYTES;
-static constexpr int OFF_P = OFF_V + NSTAGE * KV_BYTES;
-static constexpr int OFF_BAR = OFF_P + P_BYTES;
+static constexpr int OFF_BAR = OFF_V + NSTAGE * KV_BYTES;
 static constexpr int SMEM = OFF_BAR + 256 + 1024;
 static constexpr int THREADS = 256;                 // warp0 TMA, warp1 MMA, warp2 TMEM alloc, warp3 idle, warps4-7 softmax
 static constexpr int COL_S = 0;                     // S buffer b at COL_S + 64 b
 static constexpr int COL_O = 128;                   // O: 256 columns
+static constexpr int COL_Q = 384;                   // Q as the A operand of Q K^T: 128 rows x 256 bf16 = 128 columns
 static constexpr int TMEM_COLS = 512;
 static constexpr float RESCALE_THRESHOLD = 8.0f;    // log2 units
 }  // namespace fa256
@@ -84,7 +83,8 @@ flash_attn_hd256_tcgen05_kernel(const __grid_constant__ CUtensorMap map_q, const
   uint64_t* p_full = s_free + 2;
   uint64_t* o_done = p_full + 1;            // one completion per P V product
   uint64_t* o_free = o_done + 1;            // softmax has read the final O of a unit
-  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(o_free + 1);
+  uint64_t* qt_full = o_free + 1;           // the unit's Q tile has been copied shared -> tensor memory
+  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(qt_full + 1);
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -95,7 +95,7 @@ flash_attn_hd256_tcgen05_kernel(const __grid_constant__ CUtensorMap map_q, const
     tma_prefetch_desc(&map_v);
   }
   if (warp == 1 && lane == 0) {
-    mbar_init(q_full, 1); mbar_init(q_empty, 1);
+    mbar_init(q_full, 1); mbar_init(q_empty, 4); mbar_init(qt_full, 4);
     for (int i = 0; i < NSTAGE; ++i) { mbar_init(&k_full[i], 1); mbar_init(&k_empty[i], 1); mbar_init(&v_full[i], 1); mbar_init(&v_empty[i], 1); }
     for (int i = 0; i < 2; ++i) { mbar_init(&s_full[i], 1); mbar_init(&s_free[i], 4); }
     mbar_init(p_full, 4); mbar_init(o_done, 1); mbar_init(o_free, 4);
@@ -149,24 +149,24 @@ flash_attn_hd256_tcgen05_kernel(const __grid_constant__ CUtensorMap map_q, const
         const uint32_t bsel = n_s & 1;
         mbar_wait(&s_free[bsel], ((n_s >> 1) & 1) ^ 1);
         tc_fence_after();
-        const uint32_t q = sbase + OFF_Q, k = sbase + OFF_K + st * KV_BYTES;
+        // A = Q from tensor memory: with N = 64 a shared-memory A operand (4 KB re-read per instruction) would need 192 B/clk
+        const uint32_t k = sbase + OFF_K + st * KV_BYTES;
         const uint32_t d = tmem_base + COL_S + 64 * bsel;
 #pragma unroll
         for (int ks = 0; ks < 16; ++ks)
-          umma_bf16(d, make_smem_desc(q + (ks >> 2) * 16384 + (ks & 3) * 32, 16, 1024, 2),
-                    make_smem_desc(k + (ks >> 2) * 8192 + (ks & 3) * 32, 16, 1024, 2), idesc_qk, ks != 0);
+          umma_bf16_ts(d, tmem_base + COL_Q + 8 * ks, make_smem_desc(k + (ks >> 2) * 8192 + (ks & 3) * 32, 16, 1024, 2), idesc_qk,
+                       ks != 0);
         umma_commit(&s_full[bsel]);
         ++n_s;
       };
       for (int u = blockIdx.x; u < p.num_units; u += gridDim.x, ++nu) {
         const Unit256 c = unit256(p, u);
         const int n_kv = c.kv1 - c.kv0;
-        mbar_wait(q_full, nu & 1);
+        mbar_wait(qt_full, nu & 1);
         mbar_wait(&k_full[it % NSTAGE], (it / NSTAGE) & 1);
         tc_fence_after();
         issue_qk(it % NSTAGE);
         umma_commit(&k_empty[it % NSTAGE]);
-        if (n_kv == 1) umma_commit(q_empty);
         mbar_wait(o_free, (nu & 1) ^ 1);          // previous unit's accumulator has been read out
         for (int j = 0; j < n_kv; ++j, ++it) {
           const int st = it % NSTAGE, st1 = (it + 1) % NSTAGE;
@@ -175,18 +175,17 @@ flash_attn_hd256_tcgen05_kernel(const __grid_constant__ CUtensorMap map_q, const
             tc_fence_after();
             issue_qk(st1);                         // S(j+1) is computed while the softmax warps work on S(j)
             umma_commit(&k_empty[st1]);
-            if (j + 2 == n_kv) umma_commit(q_empty);
           }
           mbar_wait(&v_full[st], (it / NSTAGE) & 1);
           mbar_wait(p_full, n_o & 1);
           tc_fence_after();
-          const uint32_t pa = sbase + OFF_P, v = sbase + OFF_V + st * KV_BYTES;
-          // one N = 256 instruction per 16 keys: V is MN-major, its four 64-dim sub-tiles are 8 KB apart (LBO); a wide N keeps
-          // the shared-memory operand traffic (P slice re-read per instruction) under the 128 B/clk the SM can deliver
+          const uint32_t v = sbase + OFF_V + st * KV_BYTES;
+          const uint32_t pa = tmem_base + COL_S + 64 * (n_o & 1);      // P(j) lives in the first 32 columns of S(j)'s buffer
+          // one N = 256 instruction per 16 keys: V is MN-major, its four 64-dim sub-tiles are 8 KB apart (LBO); P is read from
+          // tensor memory, so the only shared-memory operand traffic is V (64 B/clk)
 #pragma unroll
           for (int ks = 0; ks < 4; ++ks)
-            umma_bf16(tmem_base + COL_O, make_smem_desc(pa + ks * 32, 16, 1024, 2), make_smem_desc(v + ks * 2048, 8192, 1024, 2),
-                      idesc_pv, (j | ks) != 0);
+            umma_bf16_ts(tmem_base + COL_O, pa + 8 * ks, make_smem_desc(v + ks * 2048, 8192, 1024, 2), idesc_pv, (j | ks) != 0);
           umma_commit(o_done);
           umma_commit(&v_empty[st]);
           ++n_o;
@@ -199,11 +198,33 @@ flash_attn_hd256_tcgen05_kernel(const __grid_constant__ CUtensorMap map_q, const
     const int r = wq * 32 + lane;
     const uint32_t lane_sel = (uint32_t)(wq * 32) << 16;
     const uint32_t to = tmem_base + COL_O + lane_sel;
-    const uint32_t p_row = smem_u32(smem + OFF_P) + r * 128;
-    const uint32_t p_xor = (uint32_t)(r & 7) << 4;
     uint32_t n = 0;          // KV tiles seen (S buffer = n & 1)
     uint32_t n_pv = 0;       // P V completions observed (always in order, never more than one behind)
-    for (int u = blockIdx.x; u < p.num_units; u += gridDim.x) {
+    // Q tile: shared (TMA, 128B swizzle) -> registers -> tensor memory, row r -> lane r, two bf16 per column.  Called when no
+    // Q K^T product that reads the previous Q is in flight (start of the kernel / after the unit's last P V has completed).
+    const uint32_t q_row = smem_u32(smem + OFF_Q) + r * 128;
+    const uint32_t q_xor = (uint32_t)(r & 7) << 4;
+    auto stage_q = [&](uint32_t parity) {
+      mbar_wait(q_full, parity);
+#pragma unroll 1
+      for (int sub = 0; sub < 4; ++sub) {
+        uint32_t qv[32];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          const float4 f = ld_shared_f4(q_row + sub * 16384 + (((uint32_t)i << 4) ^ q_xor));
+          qv[4 * i] = __float_as_uint(f.x); qv[4 * i + 1] = __float_as_uint(f.y);
+          qv[4 * i + 2] = __float_as_uint(f.z); qv[4 * i + 3] = __float_as_uint(f.w);
+        }
+        tmem_st_x32(tmem_base + COL_Q + 32 * sub + lane_sel, qv);
+      }
+      tmem_st_wait();
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) { mbar_arrive(q_empty); mbar_arrive(qt_full); }
+    };
+    uint32_t nu = 0;
+    if ((int)blockIdx.x < p.num_units) stage_q(0);
+    for (int u = blockIdx.x; u < p.num_units; u += gridDim.x, ++nu) {
       const Unit256 c = unit256(p, u);
       const int n_kv = c.kv1 - c.kv0;
       float m_run = -INFINITY, l_run = 0.f;
@@ -224,30 +245,35 @@ flash_attn_hd256_tcgen05_kernel(const __grid_constant__ CUtensorMap map_q, const
         __syncwarp();
         if (lane == 0) mbar_arrive(&s_free[bsel]);      // S is in registers: the MMA warp may overwrite this buffer
         const int valid = p.Lk - (c.kv0 + j) * TK;       // keys of this tile that exist (>= 64 except on the last tile)
+        if (valid < TK) {                                // ragged last tile only
+#pragma unroll
+          for (int i = 0; i < 64; ++i)
+            if (i >= valid) s[i] = __float_as_uint(-INFINITY);
+        }
         float mx = -INFINITY;
 #pragma unroll
-        for (int i = 0; i < 64; ++i) {
-          if (i >= valid) s[i] = __float_as_uint(-INFINITY);
-          mx = fmaxf(mx, __uint_as_float(s[i]));
-        }
+        for (int i = 0; i < 64; ++i) mx = fmaxf(mx, __uint_as_float(s[i]));
         mx *= p.scale_log2;
         // lazy rescale: keep the old reference max unless the new one exceeds it by more than 2^8
         float corr = 1.0f;
         const bool grow = mx > m_run + RESCALE_THRESHOLD;
         if (grow) { corr = exp2f(m_run - mx); m_run = mx; }     // first tile: m_run = -inf -> corr = 0 (nothing accumulated yet)
-        float rs = 0.f;
+        // packed fp32 pairs: one FFMA2 (scale, minus max) and one FADD2 (row sum) per two keys
+        const uint64_t sc2 = f2_pack(p.scale_log2, p.scale_log2), nm2 = f2_pack(-m_run, -m_run);
+        uint64_t rs2a = f2_pack(0.f, 0.f), rs2b = rs2a;
         uint32_t pk[32];
 #pragma unroll
         for (int i = 0; i < 32; ++i) {
-          float e0, e1;
-          const float a0 = fmaf(__uint_as_float(s[2 * i]), p.scale_log2, -m_run);
-          const float a1 = fmaf(__uint_as_float(s[2 * i + 1]), p.scale_log2, -m_run);
+          float a0, a1, e0, e1;
+          f2_unpack(f2_fma(f2_pack(__uint_as_float(s[2 * i]), __uint_as_float(s[2 * i + 1])), sc2, nm2), a0, a1);
           asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e0) : "f"(a0));
           asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e1) : "f"(a1));
-          rs += e0 + e1;
+          if (i & 1) rs2b = f2_add(rs2b, f2_pack(e0, e1)); else rs2a = f2_add(rs2a, f2_pack(e0, e1));
           pk[i] = pack_bf16x2(e0, e1);
         }
-        l_run = fmaf(l_run, corr, rs);
+        float rs0, rs1;
+        f2_unpack(f2_add(rs2a, rs2b), rs0, rs1);
+        l_run = fmaf(l_run, corr, rs0 + rs1);
         if (j > 0) {
           // P V of the previous tile must be complete before P is overwritten / the accumulator is rescaled
           mbar_wait(o_done, n_pv & 1);
@@ -266,10 +292,8 @@ flash_attn_hd256_tcgen05_kernel(const __grid_constant__ CUtensorMap map_q, const
             tmem_st_wait();
           }
         }
-#pragma unroll
-        for (int i = 0; i < 8; ++i)
-          st_shared_u4(p_row + (((uint32_t)i << 4) ^ p_xor), pk[4 * i], pk[4 * i + 1], pk[4 * i + 2], pk[4 * i + 3]);
-        fence_proxy_async_smem();
+        tmem_st_x32(tmem_base + COL_S + 64 * bsel + lane_sel, pk);     // P(j) as the A operand of P V, over S(j)'s columns
+        tmem_st_wait();
         tc_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive(p_full);
@@ -278,6 +302,7 @@ flash_attn_hd256_tcgen05_kernel(const __grid_constant__ CUtensorMap map_q, const
       mbar_wait(o_done, n_pv & 1);
       ++n_pv;
       tc_fence_after();
+      if (u + (int)gridDim.x < p.num_units) stage_q((nu + 1) & 1);   // next unit's first Q K^T overlaps this unit's read-out
       const long row_g = ((long)c.sp * p.n + c.b) * p.Tq + (long)c.qt * TQ + r;
       float* op = p.o_part + row_g * D;
 #pragma unroll 1
@@ -367,14 +392,22 @@ static int fa256_map(CUtensorMap* m, const bf16* ptr, long rows, long batch, lon
 }
 
 int flash_attention_hd256_splits(int n, int Tq, long Lk) {
+  // units = q tiles x splits are dealt round-robin to one CTA per SM: pick the split count that minimises the longest CTA's
+  // work, waves x (tiles per unit + per-unit prologue / read-out) plus the combine pass that grows with the split count
   const long q_units = (long)n * (Tq / fa256::TQ);
   const long kv_tiles = (Lk + fa256::TK - 1) / fa256::TK;
-  long splits = (2L * num_sms() + q_units - 1) / q_units;      // aim at >= 2 units per SM
-  if (splits > 8) splits = 8;
-  if (splits > kv_tiles) splits = kv_tiles;
-  if (splits < 1) splits = 1;
-  const long per = (kv_tiles + splits - 1) / splits;
-  return (int)((kv_tiles + per - 1) / per);                     // every split owns at least one tile
+  const long sms = num_sms();
+  long best = 1;
+  double best_cost = 1e30;
+  for (long s = 1; s <= 16 && s <= kv_tiles; ++s) {
+    const long per = (kv_tiles + s - 1) / s;
+    const long eff = (kv_tiles + per - 1) / per;                // every split owns at least one tile
+    if (eff != s) continue;
+    const long waves = (q_units * s + sms - 1) / sms;
+    const double cost = (double)waves * (per + 4.0) + 0.5 * s * (double)q_units / sms;
+    if (cost < best_cost - 1e-9) { best_cost = cost; best = s; }
+  }
+  return (int)best;
 }
 
 int flash_attention_hd256(const bf16* q, long q_batch_stride, const bf16* k, long k_batch_stride, const bf16* v,
