@@ -397,6 +397,13 @@ int flash_attention_hd256_splits(int n, int Tq, long Lk) {
   const long q_units = (long)n * (Tq / fa256::TQ);
   const long kv_tiles = (Lk + fa256::TK - 1) / fa256::TK;
   const long sms = num_sms();
+  if (const char* ev = getenv("SAM2B_FA256_SPLITS")) {          // experiments only
+    long s = atol(ev);
+    if (s >= 1 && s <= kv_tiles) {
+      const long per = (kv_tiles + s - 1) / s;
+      return (int)((kv_tiles + per - 1) / per);
+    }
+  }
   long best = 1;
   double best_cost = 1e30;
   for (long s = 1; s <= 16 && s <= kv_tiles; ++s) {
@@ -404,7 +411,7 @@ int flash_attention_hd256_splits(int n, int Tq, long Lk) {
     const long eff = (kv_tiles + per - 1) / per;                // every split owns at least one tile
     if (eff != s) continue;
     const long waves = (q_units * s + sms - 1) / sms;
-    const double cost = (double)waves * (per + 4.0) + 0.5 * s * (double)q_units / sms;
+    const double cost = (double)waves * (per + 4.0) + 0.03 * s * (double)q_units;   // partials: 256 KB written + read per unit
     if (cost < best_cost - 1e-9) { best_cost = cost; best = s; }
   }
   return (int)best;

@@ -32,11 +32,15 @@ static constexpr int NSTAGE = 2;        // K and V ring depth
 static constexpr int LO_BYTES = 128 * 128;   // [128 rows][64 d] bf16, SW128
 static constexpr int HI_BYTES = 128 * 32;    // [128 rows][16 d] bf16, SW32
 static constexpr int TILE_BYTES = LO_BYTES + HI_BYTES;
+// V tiles are the MN-major B operand of P V.  A tcgen05.mma costs max(N / 2, ~50) clocks (tools/umma_rate.cu), so the 64 + 16
+// split used for Q and K would pay 100 clocks per 16 keys; instead V is two 128B-swizzle atoms (d 0-63, d 64-127 with 72+ zero
+// filled by TMA) 16 KB apart, which one N = 80 instruction walks through the descriptor's leading-dimension offset.
+static constexpr int V_BYTES = 2 * LO_BYTES;
 static constexpr int P_BYTES = 128 * 128 * 2;     // [128][128] bf16 as two SW128 sub-tiles
 static constexpr int OFF_Q = 0;                                   // 2 Q tiles
 static constexpr int OFF_K = OFF_Q + 2 * TILE_BYTES;
 static constexpr int OFF_V = OFF_K + NSTAGE * TILE_BYTES;
-static constexpr int OFF_P = OFF_V + NSTAGE * TILE_BYTES;         // 2 P tiles
+static constexpr int OFF_P = OFF_V + NSTAGE * V_BYTES;            // 2 P tiles
 static constexpr int OFF_BAR = OFF_P + 2 * P_BYTES;
 static constexpr int SMEM = OFF_BAR + 256 + 1024;
 static constexpr int THREADS = 384;
@@ -135,15 +139,15 @@ flash_attn_hd72_tcgen05_kernel(const __grid_constant__ CUtensorMap map_lo, const
           const uint32_t ph = (it / NSTAGE) & 1;
           const int ky = (global ? 0 : c.y0) + j * p.rows_per_tile;
           uint8_t* k = smem + OFF_K + st * TILE_BYTES;
-          uint8_t* v = smem + OFF_V + st * TILE_BYTES;
+          uint8_t* v = smem + OFF_V + st * V_BYTES;
           mbar_wait(&k_empty[st], ph ^ 1);
           mbar_arrive_expect_tx(&k_full[st], TILE_BYTES);
           tma_load_5d(k, &map_lo, &k_full[st], 0, p.heads + c.head, c.x0, ky, c.b);
           tma_load_5d(k + LO_BYTES, &map_hi, &k_full[st], 64, p.heads + c.head, c.x0, ky, c.b);
           mbar_wait(&v_empty[st], ph ^ 1);
-          mbar_arrive_expect_tx(&v_full[st], TILE_BYTES);
+          mbar_arrive_expect_tx(&v_full[st], V_BYTES);
           tma_load_5d(v, &map_lo, &v_full[st], 0, 2 * p.heads + c.head, c.x0, ky, c.b);
-          tma_load_5d(v + LO_BYTES, &map_hi, &v_full[st], 64, 2 * p.heads + c.head, c.x0, ky, c.b);
+          tma_load_5d(v + LO_BYTES, &map_lo, &v_full[st], 64, 2 * p.heads + c.head, c.x0, ky, c.b);
         }
       }
     }
@@ -151,8 +155,7 @@ flash_attn_hd72_tcgen05_kernel(const __grid_constant__ CUtensorMap map_lo, const
     // ===================== MMA issuer (one thread) =====================
     if (lane == 0) {
       constexpr uint32_t idesc_qk = make_idesc_ex(128, 128, 0);
-      constexpr uint32_t idesc_pv_lo = make_idesc_ex(128, 64, 1);
-      constexpr uint32_t idesc_pv_hi = make_idesc_ex(128, 16, 1);
+      constexpr uint32_t idesc_pv = make_idesc_ex(128, 80, 1);
       const uint32_t sbase = smem_u32(smem);
       uint32_t n_s[2] = {0, 0};     // QK^T products issued on S_t
       uint32_t n_o[2] = {0, 0};     // P V products issued on O_t
@@ -173,14 +176,13 @@ flash_attn_hd72_tcgen05_kernel(const __grid_constant__ CUtensorMap map_lo, const
         mbar_wait(&p_full[t], n_o[t] & 1);                  // P_t(j) written; O_t rescaled if the running max moved
         if (j == 0) mbar_wait(&o_free[t], (nu & 1) ^ 1);    // the previous unit's O_t has been read out of TMEM
         tc_fence_after();
-        const uint32_t pa = sbase + OFF_P + t * P_BYTES, v = sbase + OFF_V + st * TILE_BYTES;
+        const uint32_t pa = sbase + OFF_P + t * P_BYTES, v = sbase + OFF_V + st * V_BYTES;
         const uint32_t d = tmem_base + COL_O + 80 * t;
 #pragma unroll
         for (int ks = 0; ks < 8; ++ks) {
           // A: P[128][16 keys of k-step ks] (K-major, sub-tile ks/4); B: V rows 16ks..16ks+15 (MN-major: d contiguous)
           const uint64_t da = make_smem_desc(pa + (ks >> 2) * 16384 + (ks & 3) * 32, 16, 1024, 2);
-          umma_bf16(d, da, make_smem_desc(v + ks * 2048, 1024, 1024, 2), idesc_pv_lo, (j | ks) != 0);
-          umma_bf16(d + 64, da, make_smem_desc(v + LO_BYTES + ks * 512, 256, 256, 6), idesc_pv_hi, (j | ks) != 0);
+          umma_bf16(d, da, make_smem_desc(v + ks * 2048, LO_BYTES, 1024, 2), idesc_pv, (j | ks) != 0);
         }
         umma_commit(&o_full[t]);
         ++n_o[t];

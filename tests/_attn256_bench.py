@@ -21,9 +21,10 @@ def timeit(f, it=10):
 
 
 quick = "--quick" in sys.argv
+ns = [int(x) for x in sys.argv[1].split(",")] if len(sys.argv) > 1 and sys.argv[1][0].isdigit() else ((2,) if quick else (1, 4, 16))
 g = torch.Generator(device="cuda").manual_seed(0)
 for lk in (4096, 28736):
-    for n in ((2,) if quick else (1, 4, 16)):
+    for n in ns:
         q = torch.randn(n, 4096, 256, device="cuda", generator=g).bfloat16()
         k = torch.randn(n, lk, 256, device="cuda", generator=g).bfloat16()
         v = torch.randn(n, lk, 256, device="cuda", generator=g).bfloat16()
