@@ -43,6 +43,7 @@ class _Base:
         for ctx in self.backend_contexts:
             ctx.Release()
         self.backend_contexts = []
+        getattr(self, "_heads_graphs", {}).clear()      # captured SAM-heads graphs (video predictor)
         if self.engine is not None:
             self.engine.release()
             self.engine = None
@@ -141,10 +142,42 @@ class SAM2ImagePredictor(_Base):
         return masks[0].float().cpu().numpy(), iou[0].float().cpu().numpy(), low[0].float().cpu().numpy()
 
 
+class _GraphedHeads:
+    """the SAM heads of a tracked (un-prompted) frame — prompt encoder with the padding point, two-way
+    transformer, upscaling, hyper-network MLPs, best-IoU select, x4 bilinear, obj_ptr_proj (sam_heads.forward_sam_heads) — are
+    ~130 small fp32 kernels whose launch cost, not their arithmetic, bounds a frame with many objects.  The shapes depend on
+    the number of objects only, so the whole sequence is captured once per object count into a CUDA graph and replayed:
+    identical kernels and arithmetic, one launch.  Inputs are copied into the graph's static buffers; the outputs that
+    outlive the frame (low-res masks, object pointers, object scores) are cloned out."""
+
+    def __init__(self, w, n, pe, device):
+        self.pix = torch.zeros(n, H.D_MODEL, 64, 64, device=device)
+        self.hr = [torch.zeros(1, 32, 256, 256, device=device), torch.zeros(1, 64, 128, 128, device=device)]
+        run = lambda: H.forward_sam_heads(w, self.pix, high_res_features=[h.expand(n, -1, -1, -1) for h in self.hr],
+                                          multimask_output=True, pe=pe)
+        side = torch.cuda.Stream(device=device)
+        side.wait_stream(torch.cuda.current_stream(device))
+        with torch.cuda.stream(side):
+            for _ in range(2):
+                run()                       # warm-up outside capture (cuBLAS workspaces, lazy module loads)
+        torch.cuda.current_stream(device).wait_stream(side)
+        self.graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(self.graph):
+            self.out = run()
+
+    def __call__(self, pix, hr):
+        self.pix.copy_(pix)
+        self.hr[0].copy_(hr[0])
+        self.hr[1].copy_(hr[1])
+        self.graph.replay()
+        _, _, _, low, high, ptr, obj = self.out
+        return low.clone(), high, ptr.clone(), obj.clone()      # `high` is consumed (memory encoder) before the next replay
+
+
 class SAM2VideoPredictor(_Base):
     """Forward video propagation with click / box prompts (BASELINE.json configs 3 and 4)."""
 
-    def __init__(self, state_dict, device="cuda", backend="b200", encode_ahead=8, fill_hole_area=0):
+    def __init__(self, state_dict, device="cuda", backend="b200", encode_ahead=8, fill_hole_area=0, graph_heads=True):
         """fill_hole_area: as the reference's constructor argument (sam2_video_predictor_official.py:25,889-894; the
         reference's builder sets 8 when its native extension is available, build_sam.py:128-129): holes of at most that
         many pixels in the low-res mask scores are filled before the masks are stored / returned.  0 = off, which is what
@@ -152,6 +185,9 @@ class SAM2VideoPredictor(_Base):
         super().__init__(state_dict, device, backend)
         self.encode_ahead = max(1, int(encode_ahead))
         self.fill_hole_area = int(fill_hole_area)
+        self.graph_heads = bool(graph_heads)
+        self._heads_graphs = {}            # object count -> _GraphedHeads
+        self._tpos_cache = {}              # (num_frames, max_ptrs) -> projected temporal encodings of the object pointers
 
     @torch.no_grad()
     def init_state(self, frames=None, video_height=None, video_width=None, offload_video_to_cpu=True):
@@ -298,7 +334,7 @@ class SAM2VideoPredictor(_Base):
         groups = OrderedDict()
         for o in objs:
             cond = {tt: per[o] for tt, per in st["cond"].items() if o in per and per[o]["maskmem_features"] is not None}
-            mem = H.assemble_memory(self.w, t, cond, st["non_cond"].get(o, {}), st["num_frames"])
+            mem = H.assemble_memory(self.w, t, cond, st["non_cond"].get(o, {}), st["num_frames"], cache=self._tpos_cache)
             groups.setdefault((mem[0].shape[0], mem[2].shape[0]), []).append((o, mem))
         results = {}
         for (L, P), items in groups.items():
@@ -311,8 +347,13 @@ class SAM2VideoPredictor(_Base):
             else:
                 pix = self._ex["memory_attention_none"].Inference([curr, cat(0), curr_pos, cat(1)], output_type="torch")[0]
             pix = pix.permute(1, 2, 0).reshape(n, H.D_MODEL, 64, 64)
-            hr_n = [h.expand(n, -1, -1, -1) for h in hr]
-            _, _, _, low, high, ptr, obj = H.forward_sam_heads(self.w, pix, high_res_features=hr_n, multimask_output=True, pe=self._dense_pe)
+            if self.graph_heads:
+                if n not in self._heads_graphs:
+                    self._heads_graphs[n] = _GraphedHeads(self.w, n, self._dense_pe, self.device)
+                low, high, ptr, obj = self._heads_graphs[n](pix, hr)
+            else:
+                hr_n = [h.expand(n, -1, -1, -1) for h in hr]
+                _, _, _, low, high, ptr, obj = H.forward_sam_heads(self.w, pix, high_res_features=hr_n, multimask_output=True, pe=self._dense_pe)
             mf, mp = self._encode_memory(f2, high, obj, from_points=False)
             low = self._fill_holes(low)            # after the memory is encoded from the unfilled masks, as in the reference
             for i, (o, _) in enumerate(items):

@@ -203,7 +203,19 @@ def get_1d_sine_pe(pos, dim, temperature=10000.0):
     return torch.cat([e.sin(), e.cos()], dim=-1)
 
 
-def assemble_memory(w: W, frame_idx: int, cond_outputs: dict, non_cond_outputs: dict, num_frames: int):
+def _ptr_tpos_table(w: W, num_frames: int, max_ptrs: int, cache: dict):
+    """Projected temporal encodings of every integer frame distance 0..num_frames, [num_frames + 1, 64], built once per
+    video length: the per-call `torch.tensor(pos_list, device=...)` of the reference (sam2_base_official.py:930-937) is a
+    pageable host-to-device copy, i.e. a stream synchronisation per object per frame."""
+    key = (num_frames, max_ptrs)
+    if key not in cache:
+        d = torch.arange(num_frames + 1, dtype=torch.float32, device=w["obj_ptr_tpos_proj.weight"].device)
+        pe = get_1d_sine_pe(d / (max_ptrs - 1), D_MODEL)
+        cache[key] = F.linear(pe, w["obj_ptr_tpos_proj.weight"], w["obj_ptr_tpos_proj.bias"])
+    return cache[key]
+
+
+def assemble_memory(w: W, frame_idx: int, cond_outputs: dict, non_cond_outputs: dict, num_frames: int, cache: dict = None):
     """Memory bank + object-pointer tokens of one object for `frame_idx` (forward tracking, stride 1).
     ref: modeling/sam2_base_official.py:825-950.  Stored outputs hold 'maskmem_features' [1,64,64,64] (bf16, as the
     reference stores them, sam2_video_predictor_official.py:887), 'maskmem_pos' [1,64,64,64], 'obj_ptr' [1,256].
@@ -229,8 +241,12 @@ def assemble_memory(w: W, frame_idx: int, cond_outputs: dict, non_cond_outputs: 
     pos_list, ptrs = zip(*pos_ptrs)
     ptrs = torch.stack(ptrs, 0)                                                   # [np,1,256]
     dev = ptrs.device
-    opos = get_1d_sine_pe(torch.tensor(pos_list, dtype=torch.float32, device=dev) / (max_ptrs - 1), D_MODEL)
-    opos = F.linear(opos, w["obj_ptr_tpos_proj.weight"], w["obj_ptr_tpos_proj.bias"])
+    if cache is not None and max_ptrs > 1:
+        table = _ptr_tpos_table(w, num_frames, max_ptrs, cache)
+        opos = torch.stack([table[d] for d in pos_list], 0)
+    else:
+        opos = get_1d_sine_pe(torch.tensor(pos_list, dtype=torch.float32, device=dev) / (max_ptrs - 1), D_MODEL)
+        opos = F.linear(opos, w["obj_ptr_tpos_proj.weight"], w["obj_ptr_tpos_proj.bias"])
     opos = opos.unsqueeze(1).expand(-1, 1, MEM_DIM)
     ptrs = ptrs.reshape(-1, 1, D_MODEL // MEM_DIM, MEM_DIM).permute(0, 2, 1, 3).flatten(0, 1)
     opos = opos.repeat_interleave(D_MODEL // MEM_DIM, dim=0)

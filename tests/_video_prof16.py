@@ -19,3 +19,4 @@ run()
 with profile(activities=[ProfilerActivity.CPU, ProfilerActivity.CUDA]) as p:
     run()
 print(p.key_averages().table(sort_by="self_cuda_time_total", row_limit=32, max_name_column_width=70))
+print(p.key_averages().table(sort_by="self_cpu_time_total", row_limit=18, max_name_column_width=60))
