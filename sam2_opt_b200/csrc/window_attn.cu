@@ -63,7 +63,7 @@ __global__ void __launch_bounds__(ATT_THREADS) window_attn_hd72_kernel(const Att
   bf16* sK = sQ + 64 * LDS;                                 // [2][64][LDS]
   bf16* sV = sK + 2 * 64 * LDS;                             // [2][64][LDS]
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  const int tile = blockIdx.x, head = blockIdx.y, b = blockIdx.z;
+  const int head = blockIdx.x, tile = blockIdx.y, b = blockIdx.z;      // head fastest: co-scheduled CTAs share sectors / DRAM pages
   const int C = p.heads * HD;
   const long row_stride = 3L * C;                           // elements between consecutive tokens in qkv
   const bf16* qbase = p.qkv + head * HD;
@@ -273,10 +273,12 @@ __global__ void __launch_bounds__(ATT_THREADS) window_attn_hd72_stream_kernel(co
     z[1] = make_uint4(0, 0, 0, 0);
   }
   auto decode = [&](long it, int& tile, int& head, int& b) {
-    tile = (int)(it % tiles_per_img);
-    const long r = it / tiles_per_img;
-    head = (int)(r % p.heads);
-    b = (int)(r / p.heads);
+    // head fastest: the heads of one window are adjacent 144 B segments of the same rows, so CTAs that run at the same
+    // time share the 32 B sectors straddling two heads and the DRAM pages
+    head = (int)(it % p.heads);
+    const long r = it / p.heads;
+    tile = (int)(r % tiles_per_img);
+    b = (int)(r / tiles_per_img);
   };
   auto row_token = [&](int tile, int b, int r) {            // token index of row r (query row == key row in these cases)
     const int win = PRIVATE ? tile * 4 + (r >> 4) : tile;
@@ -437,11 +439,11 @@ int window_attention_hd72(const bf16* qkv, bf16* out, int B, int H, int W, int h
     else window_attn_hd72_stream_kernel<false><<<grid, ATT_THREADS, smem2, stream>>>(p, tiles_per_img, n_items);
   } else if (p.QW >= 64) {
     if (p.QW % 64 || p.KW % 64) { set_error("window_attention: QW=%d KW=%d not multiples of 64", p.QW, p.KW); return 1; }
-    dim3 grid(nwin * (p.QW / 64), heads, B);
+    dim3 grid(heads, nwin * (p.QW / 64), B);
     window_attn_hd72_kernel<false><<<grid, ATT_THREADS, smem, stream>>>(p);
   } else {
     if (p.QW > 16 || p.KW % 16 || nwin % 4) { set_error("window_attention: unsupported small window QW=%d KW=%d nwin=%d", p.QW, p.KW, nwin); return 1; }
-    dim3 grid(nwin / 4, heads, B);
+    dim3 grid(heads, nwin / 4, B);
     window_attn_hd72_kernel<true><<<grid, ATT_THREADS, smem, stream>>>(p);
   }
   SAM2B_CHECK_LAUNCH("window_attn_hd72");
