@@ -205,19 +205,19 @@ flash_attn_hd72_tcgen05_kernel(const __grid_constant__ CUtensorMap map_lo, const
           mbar_wait(&v_full[st], (it / NSTAGE) & 1);
           tc_fence_after();
           const bool more = j + 1 < p.n_kv;
-          if (more) { mbar_wait(&k_full[st1], ((it + 1) / NSTAGE) & 1); tc_fence_after(); }
-#pragma unroll
-          for (int t = 0; t < 2; ++t) {
-            issue_pv(t, st, j);
-            if (t == 1) umma_commit(&v_empty[st]);
-            if (more) {
-              issue_qk(t, st1);
-              if (t == 1) {
-                umma_commit(&k_empty[st1]);
-                if (j + 2 == p.n_kv) umma_commit(q_empty);
-              }
-            }
+          if (more) {
+            // Q K^T of the NEXT tile first: S_t is free as soon as the softmax warps hold tile j's scores in registers (early
+            // in their pass), so S_t(j+1) is being computed while they exponentiate tile j; P V of tile j follows.
+            mbar_wait(&k_full[st1], ((it + 1) / NSTAGE) & 1);
+            tc_fence_after();
+            issue_qk(0, st1);
+            issue_qk(1, st1);
+            umma_commit(&k_empty[st1]);
+            if (j + 2 == p.n_kv) umma_commit(q_empty);
           }
+          issue_pv(0, st, j);
+          issue_pv(1, st, j);
+          umma_commit(&v_empty[st]);
         }
       }
     }
