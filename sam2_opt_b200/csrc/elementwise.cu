@@ -140,48 +140,73 @@ int maxpool2x2_nhwc(const float* x, float* y, int B, int H, int W, int C, cudaSt
 
 // ------------------------------------------------------------------------------------------
 // Patch-embed im2col (reference: PatchEmbed Conv2d(3,144,k7,s4,p3), backbones/utils.py:63-93;
-// optional (x-mean)/std of SAM2Transforms, utils/transforms.py:27-31).  One thread per 8-tap chunk.
+// optional (x-mean)/std of SAM2Transforms, utils/transforms.py:27-31) -> bf16 rows [B*256*256][160] (K 147 padded to 160).
 // ------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) patch_im2col_kernel(const float* __restrict__ img, uint4* __restrict__ cols, int B, int S,
+// One CTA per 64 consecutive output pixels of one output row.  Work item = (pixel, channel, ky): the 7 taps of that row
+// of the 7x7 window are x = 4 ox - 3 .. 4 ox + 3, i.e. lanes 1-3 of the aligned float4 at 4 ox - 4 and the float4 at 4 ox:
+// two coalesced 16 B loads per item (consecutive pixels -> consecutive float4s).  The bf16 row tile [64][160] is staged in
+// shared memory (row pitch 81 words: conflict-free 2-byte stores) and written out with coalesced 4-byte stores.
+static constexpr int PI_PIX = 64;
+static constexpr int PI_PITCH = 162;      // bf16 elements per staged row
+__global__ void __launch_bounds__(256) patch_im2col_kernel(const float* __restrict__ img, uint32_t* __restrict__ cols, int B, int S,
                                                            int normalise) {
+  __shared__ __align__(16) bf16 tile[PI_PIX * PI_PITCH];
   const int So = S >> 2;
-  const long total = (long)B * So * So * 20;
+  const int tiles_x = So / PI_PIX;
   const float mean[3] = {0.485f, 0.456f, 0.406f};
   const float istd[3] = {1.f / 0.229f, 1.f / 0.224f, 1.f / 0.225f};
-  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
-    const int chunk = (int)(i % 20);
-    long t = i / 20;
-    const int ox = (int)(t % So); t /= So;
-    const int oy = (int)(t % So);
-    const int b = (int)(t / So);
-    float v[8];
+  const long n_tiles = (long)B * So * tiles_x;
+  for (long t = blockIdx.x; t < n_tiles; t += gridDim.x) {
+    const int tx = (int)(t % tiles_x);
+    const long r = t / tiles_x;
+    const int oy = (int)(r % So), b = (int)(r / So);
+    const int ox0 = tx * PI_PIX;
+    for (int i = threadIdx.x; i < 21 * PI_PIX; i += 256) {
+      const int px = i & (PI_PIX - 1), q = i >> 6;          // q = c * 7 + ky
+      const int c = q / 7, ky = q - c * 7;
+      const int y = oy * 4 - 3 + ky, ox = ox0 + px;
+      float4 lo = make_float4(0.f, 0.f, 0.f, 0.f), hi = lo;
+      bool ok_lo = false, ok_hi = false;
+      if (y >= 0 && y < S) {
+        const float* row = img + (((long)b * 3 + c) * S + y) * S + 4 * ox;
+        ok_hi = true;
+        hi = __ldg(reinterpret_cast<const float4*>(row));
+        if (ox > 0) { ok_lo = true; lo = __ldg(reinterpret_cast<const float4*>(row - 4)); }
+      }
+      float v[7] = {lo.y, lo.z, lo.w, hi.x, hi.y, hi.z, hi.w};
+      if (normalise) {
 #pragma unroll
-    for (int e = 0; e < 8; ++e) {
-      const int k = chunk * 8 + e;
-      float val = 0.f;
-      if (k < 147) {
-        const int c = k / 49, r = k % 49, ky = r / 7, kx = r % 7;
-        const int y = oy * 4 - 3 + ky, x = ox * 4 - 3 + kx;
-        if (y >= 0 && y < S && x >= 0 && x < S) {
-          val = __ldg(img + (((long)b * 3 + c) * S + y) * S + x);
-          if (normalise) val = (val - mean[c]) * istd[c];
+        for (int e = 0; e < 7; ++e) {
+          const bool ok = e < 3 ? ok_lo : ok_hi;            // zero padding stays zero (it pads the NORMALISED image)
+          v[e] = ok ? (v[e] - mean[c]) * istd[c] : 0.f;
         }
       }
-      v[e] = val;
+      bf16* dst = tile + px * PI_PITCH + q * 7;
+#pragma unroll
+      for (int e = 0; e < 7; ++e) dst[e] = __float2bfloat16(v[e]);
     }
-    uint4 pk;
-    pk.x = pack_bf16x2(v[0], v[1]); pk.y = pack_bf16x2(v[2], v[3]);
-    pk.z = pack_bf16x2(v[4], v[5]); pk.w = pack_bf16x2(v[6], v[7]);
-    cols[i] = pk;
+    for (int i = threadIdx.x; i < 13 * PI_PIX; i += 256) {   // K padding 147 -> 160
+      const int px = i & (PI_PIX - 1), e = i >> 6;
+      tile[px * PI_PITCH + 147 + e] = __float2bfloat16(0.f);
+    }
+    __syncthreads();
+    const uint32_t* tw = reinterpret_cast<const uint32_t*>(tile);
+    uint32_t* out = cols + (((long)b * So + oy) * So + ox0) * 80;
+    for (int i = threadIdx.x; i < PI_PIX * 80; i += 256) {
+      const int px = i / 80, w = i - px * 80;
+      out[i] = tw[px * (PI_PITCH / 2) + w];
+    }
+    __syncthreads();
   }
 }
 int patch_im2col(const float* img, bf16* cols, int B, int S, int normalise, cudaStream_t stream) {
-  if (S % 4) { set_error("patch_im2col: S=%d", S); return 1; }
+  if (S % (4 * PI_PIX) || (reinterpret_cast<uintptr_t>(img) & 15)) { set_error("patch_im2col: S=%d must be a multiple of %d, image 16 B aligned", S, 4 * PI_PIX); return 1; }
   const long total = (long)B * (S / 4) * (S / 4) * 20;
-  long blocks = (total + 255) / 256;
-  if (blocks > (long)num_sms() * 32) blocks = (long)num_sms() * 32;
+  const long n_tiles = (long)B * (S / 4) * (S / 4 / PI_PIX);
+  long blocks = n_tiles;
+  if (blocks > (long)num_sms() * 8) blocks = (long)num_sms() * 8;
   ProfRange pr(stream, "patch_im2col", 0, (double)B * S * S * 3 * 4.0 + (double)total * 16.0);
-  patch_im2col_kernel<<<(unsigned)blocks, 256, 0, stream>>>(img, reinterpret_cast<uint4*>(cols), B, S, normalise);
+  patch_im2col_kernel<<<(unsigned)blocks, 256, 0, stream>>>(img, reinterpret_cast<uint32_t*>(cols), B, S, normalise);
   SAM2B_CHECK_LAUNCH("patch_im2col");
   return 0;
 }
