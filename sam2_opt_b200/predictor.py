@@ -205,11 +205,11 @@ class SAM2VideoPredictor(_Base):
         st = {"images": frames if offload_video_to_cpu else frames.to(self.device), "num_frames": frames.shape[0],
               "video_height": video_height or 1024, "video_width": video_width or 1024,
               "obj_ids": [], "prompts": OrderedDict(), "cond": OrderedDict(), "non_cond": OrderedDict(),
-              "feat_cache": {}, "frames_tracked": {}}
+              "feat_cache": {}, "frames_tracked": {}, "non_cond_b": {}, "cond_b": {}}
         return st
 
     def reset_state(self, st):
-        for k in ("prompts", "cond", "non_cond"):
+        for k in ("prompts", "cond", "non_cond", "non_cond_b", "cond_b"):
             st[k].clear()
         st["obj_ids"], st["feat_cache"], st["frames_tracked"] = [], {}, {}
 
@@ -261,6 +261,7 @@ class SAM2VideoPredictor(_Base):
         st["prompts"][key] = (pts.to(self.device), lab.to(self.device))
         out = self._run_cond_frame(st, frame_idx, [obj_id])
         st["cond"].setdefault(frame_idx, {})[obj_id] = out
+        st["cond_b"].pop(frame_idx, None)          # stacked copies of this frame's conditioning outputs are stale
         low = torch.cat([st["cond"][frame_idx][o]["pred_masks"] if o in st["cond"][frame_idx] else
                          torch.full((1, 1, 256, 256), H.NO_OBJ_SCORE, device=self.device) for o in st["obj_ids"]], 0)
         return frame_idx, list(st["obj_ids"]), self._video_res(st, low)
@@ -287,6 +288,10 @@ class SAM2VideoPredictor(_Base):
     def propagate_in_video_preflight(self, st):
         """Encode the memory of every prompted frame (ref: sam2_video_predictor_official.py:586-649)."""
         for t, per_obj in st["cond"].items():
+            # a frame that became a conditioning frame is no longer a tracked one (ref: :640-643)
+            for o in per_obj:
+                if st["non_cond"].get(o, {}).pop(t, None) is not None:
+                    st["non_cond_b"].pop(t, None)
             todo = [o for o, out in per_obj.items() if out["maskmem_features"] is None]
             if not todo:
                 continue
@@ -297,6 +302,7 @@ class SAM2VideoPredictor(_Base):
             mf, mp = self._encode_memory(f2, high, obj, from_points=True)
             for i, o in enumerate(todo):
                 per_obj[o]["maskmem_features"], per_obj[o]["maskmem_pos"] = mf[i:i + 1], mp[i:i + 1]
+            st["cond_b"].pop(t, None)
 
     @torch.no_grad()
     def propagate_in_video(self, st, start_frame_idx=None, max_frame_num_to_track=None):
@@ -334,15 +340,30 @@ class SAM2VideoPredictor(_Base):
         """One non-prompted frame for a list of objects, batched through the engine (ref: track_step,
         sam2_base_official.py:1028-1179)."""
         f2, pos2, hr = self._features(st, t)
+        # Objects that share their conditioning frames and their tracked history (the usual case: everything prompted on
+        # the same frame) form one group whose memory bank is assembled once from the per-frame BATCHED outputs
+        # (SURVEY section 8 f-2): no per-object float / add / stack / cat kernels.  Anything else takes the per-object path.
         groups = OrderedDict()
         for o in objs:
-            cond = {tt: per[o] for tt, per in st["cond"].items() if o in per and per[o]["maskmem_features"] is not None}
-            mem = H.assemble_memory(self.w, t, cond, st["non_cond"].get(o, {}), st["num_frames"], cache=self._tpos_cache)
-            groups.setdefault((mem[0].shape[0], mem[2].shape[0]), []).append((o, mem))
+            cond_keys = tuple(tt for tt, per in st["cond"].items() if o in per and per[o]["maskmem_features"] is not None)
+            nc = st["non_cond"].get(o, {})
+            hist = tuple(tt for tt in range(max(0, t - 16), t) if tt in nc)
+            groups.setdefault((cond_keys, hist), []).append(o)
         results = {}
-        for (L, P), items in groups.items():
-            n = len(items)
-            cat = lambda i: torch.cat([m[i] for _, m in items], dim=2 if i < 2 else 1)
+        for (cond_keys, hist), g_objs in groups.items():
+            n, key = len(g_objs), tuple(g_objs)
+            batched = {tt: st["non_cond_b"].get(tt, {}).get(key) for tt in hist}
+            if all(v is not None for v in batched.values()):
+                cond_b = {tt: self._stacked_cond(st, tt, key) for tt in cond_keys}
+                mem = H.assemble_memory(self.w, t, cond_b, batched, st["num_frames"], cache=self._tpos_cache)
+            else:
+                per = []
+                for o in g_objs:
+                    cond = {tt: st["cond"][tt][o] for tt in cond_keys}
+                    per.append(H.assemble_memory(self.w, t, cond, st["non_cond"].get(o, {}), st["num_frames"], cache=self._tpos_cache))
+                mem = [torch.cat([m[i] for m in per], dim=2 if i < 2 else 1) for i in range(4)]
+            L, P = mem[0].shape[0], mem[2].shape[0]
+            cat = lambda i: mem[i]
             curr = f2.flatten(2).permute(2, 0, 1).expand(-1, n, -1)
             curr_pos = pos2.flatten(2).permute(2, 0, 1).expand(-1, n, -1)
             if P:
@@ -359,7 +380,16 @@ class SAM2VideoPredictor(_Base):
                 _, _, _, low, high, ptr, obj = H.forward_sam_heads(self.w, pix, high_res_features=hr_n, multimask_output=True, pe=self._dense_pe)
             mf, mp = self._encode_memory(f2, high, obj, from_points=False)
             low = self._fill_holes(low)            # after the memory is encoded from the unfilled masks, as in the reference
-            for i, (o, _) in enumerate(items):
+            st["non_cond_b"].setdefault(t, {})[key] = {"maskmem_features": mf, "maskmem_pos": mp, "obj_ptr": ptr}
+            for i, o in enumerate(g_objs):
                 results[o] = {"pred_masks": low[i:i + 1], "obj_ptr": ptr[i:i + 1], "object_score_logits": obj[i:i + 1],
                               "maskmem_features": mf[i:i + 1], "maskmem_pos": mp[i:i + 1]}
         return [results[o] for o in objs]
+
+    def _stacked_cond(self, st, t, key):
+        """Conditioning-frame outputs of the objects `key`, stacked once along the batch dimension."""
+        c = st["cond_b"].setdefault(t, {})
+        if key not in c:
+            per = st["cond"][t]
+            c[key] = {k: torch.cat([per[o][k] for o in key], 0) for k in ("maskmem_features", "maskmem_pos", "obj_ptr")}
+        return c[key]

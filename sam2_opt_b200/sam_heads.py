@@ -216,10 +216,11 @@ def _ptr_tpos_table(w: W, num_frames: int, max_ptrs: int, cache: dict):
 
 
 def assemble_memory(w: W, frame_idx: int, cond_outputs: dict, non_cond_outputs: dict, num_frames: int, cache: dict = None):
-    """Memory bank + object-pointer tokens of one object for `frame_idx` (forward tracking, stride 1).
-    ref: modeling/sam2_base_official.py:825-950.  Stored outputs hold 'maskmem_features' [1,64,64,64] (bf16, as the
-    reference stores them, sam2_video_predictor_official.py:887), 'maskmem_pos' [1,64,64,64], 'obj_ptr' [1,256].
-    -> memory [L,4096,1,64], memory_pos [L,4096,1,64], ptr tokens [P,1,64], ptr pos [P,1,64]"""
+    """Memory bank + object-pointer tokens for `frame_idx` (forward tracking, stride 1) of one object or of n objects that
+    share the same conditioning / tracked frames.  ref: modeling/sam2_base_official.py:825-950.  Stored outputs hold
+    'maskmem_features' [n,64,64,64] (bf16, as the reference stores them, sam2_video_predictor_official.py:887),
+    'maskmem_pos' [n,64,64,64], 'obj_ptr' [n,256].
+    -> memory [L,4096,n,64], memory_pos [L,4096,n,64], ptr tokens [P,n,64], ptr pos [P,n,64]"""
     t_pos_prev = [(0, o) for o in cond_outputs.values()]
     for t_pos in range(1, NUM_MASKMEM):
         t_pos_prev.append((t_pos, non_cond_outputs.get(frame_idx - (NUM_MASKMEM - t_pos))))
@@ -239,15 +240,15 @@ def assemble_memory(w: W, frame_idx: int, cond_outputs: dict, non_cond_outputs: 
         if o is not None:
             pos_ptrs.append((t_diff, o["obj_ptr"]))
     pos_list, ptrs = zip(*pos_ptrs)
-    ptrs = torch.stack(ptrs, 0)                                                   # [np,1,256]
-    dev = ptrs.device
+    ptrs = torch.stack(ptrs, 0)                                                   # [np,n,256]
+    dev, n = ptrs.device, ptrs.shape[1]
     if cache is not None and max_ptrs > 1:
         table = _ptr_tpos_table(w, num_frames, max_ptrs, cache)
         opos = torch.stack([table[d] for d in pos_list], 0)
     else:
         opos = get_1d_sine_pe(torch.tensor(pos_list, dtype=torch.float32, device=dev) / (max_ptrs - 1), D_MODEL)
         opos = F.linear(opos, w["obj_ptr_tpos_proj.weight"], w["obj_ptr_tpos_proj.bias"])
-    opos = opos.unsqueeze(1).expand(-1, 1, MEM_DIM)
-    ptrs = ptrs.reshape(-1, 1, D_MODEL // MEM_DIM, MEM_DIM).permute(0, 2, 1, 3).flatten(0, 1)
+    opos = opos.unsqueeze(1).expand(-1, n, MEM_DIM)
+    ptrs = ptrs.reshape(-1, n, D_MODEL // MEM_DIM, MEM_DIM).permute(0, 2, 1, 3).flatten(0, 1)
     opos = opos.repeat_interleave(D_MODEL // MEM_DIM, dim=0)
     return torch.stack(mem, 0), torch.stack(mpos, 0), ptrs, opos

@@ -110,3 +110,56 @@ def test_video_fill_hole_area():
     print("pixels changed by hole filling on the prompted frame:", int((want0 != outs[0][0]).sum()))
     for filled in outs[8]:
         assert np.array_equal(PO.fill_holes_in_mask_scores(filled, 8), filled)
+
+
+def test_video_batched_bank_and_graphed_heads_equal_the_plain_path(weights):
+    """The per-frame batched memory-bank assembly (one group of objects sharing their history) and the CUDA-graph replay
+    of the SAM heads are pure scheduling changes: three objects must give bit-identical low-res masks with both switched
+    off (per-object assembly + eager heads).  Also covers the fallback when objects do NOT share their history (one
+    object is added after the first propagation, so the groups differ) - it must run and track every object."""
+    from oracle.synth import synth_video
+    from sam2_opt_b200.predictor import SAM2VideoPredictor
+    T = 10
+    frames = synth_video(T, seed=4)
+    pts = {1: [[512, 512]], 2: [[300, 700]], 3: [[700, 300]]}
+
+    def run(plain):
+        vp = SAM2VideoPredictor(weights, graph_heads=not plain)
+        st = vp.init_state(frames)
+        for o, p in pts.items():
+            vp.add_new_points_or_box(st, 0, o, points=np.array(p, dtype=np.float32), labels=np.array([1], np.int32))
+        if plain:
+            class _Never(dict):                      # never remembers a batched frame -> always the per-object path
+                def setdefault(self, k, d=None):
+                    return {}
+                def get(self, k, d=None):
+                    return {}
+            st["non_cond_b"] = _Never()
+        out = {t: m.clone() for t, _, m in vp.propagate_in_video(st)}
+        return vp, st, out
+
+    vp_a, st_a, a = run(plain=False)
+    vp_b, st_b, b = run(plain=True)
+    for t in range(T):
+        assert torch.equal(a[t], b[t]), f"frame {t}: batched/graphed path differs from the plain path"
+    assert len(st_a["non_cond_b"]) == T - 1 and all(tuple(k) == (1, 2, 3) for d in st_a["non_cond_b"].values() for k in d)
+    vp_a.release(); vp_b.release()
+    # mixed history (7 frames, so that two conditioning frames + recent frames stay within the 7-slot bank of the E3
+    # boundary): object 3 gets a second prompt on frame 3 -> its conditioning frames differ from objects 1-2, the frame
+    # groups split ((1, 2) and (3,)) and no batched record matches: the per-object fallback runs.  Objects 1-2 keep their
+    # history, so their masks stay the same up to the summation order of a batch of 2 instead of 3.
+    T2 = 7
+    vp_a = SAM2VideoPredictor(weights)
+    st_a = vp_a.init_state(frames[:T2])
+    for o, p in pts.items():
+        vp_a.add_new_points_or_box(st_a, 0, o, points=np.array(p, dtype=np.float32), labels=np.array([1], np.int32))
+    first = {t: m.clone() for t, _, m in vp_a.propagate_in_video(st_a)}
+    vp_a.add_new_points_or_box(st_a, 3, 3, points=np.array([[705, 305]], dtype=np.float32), labels=np.array([1], np.int32))
+    again = {t: m for t, _, m in vp_a.propagate_in_video(st_a, start_frame_idx=3)}
+    assert sorted(again) == list(range(3, T2)) and all(m.shape[0] == 3 for m in again.values())
+    for t in range(4, T2):
+        for i in range(2):
+            v = iou_bits((again[t][i, 0] > 0).cpu().numpy(), (first[t][i, 0] > 0).cpu().numpy())
+            assert v >= 0.995, f"frame {t} object {i + 1}: IoU {v:.4f} after re-prompting object 3"
+    assert all({(1, 2), (3,)} <= set(d) for t, d in st_a["non_cond_b"].items() if t >= 4)
+    vp_a.release()
