@@ -162,7 +162,9 @@ class _GraphedHeads:
                 run()                       # warm-up outside capture (cuBLAS workspaces, lazy module loads)
         torch.cuda.current_stream(device).wait_stream(side)
         self.graph = torch.cuda.CUDAGraph()
-        with torch.cuda.graph(self.graph):
+        # thread_local: other host threads (the reference's video_multi_thread.py drives one predictor from two) may keep
+        # issuing CUDA work while this thread captures
+        with torch.cuda.graph(self.graph, capture_error_mode="thread_local"):
             self.out = run()
 
     def __call__(self, pix, hr):
