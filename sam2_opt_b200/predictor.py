@@ -11,6 +11,7 @@ Differences from the reference that are deliberate: all objects of a video are b
 per frame (the reference loops objects with batch 1, sam2_video_predictor_official.py:689-725), and frame embeddings are
 produced a few frames ahead in one batched encoder call.
 """
+import threading
 from collections import OrderedDict
 from typing import Dict, List, Optional
 
@@ -191,7 +192,7 @@ class SAM2VideoPredictor(_Base):
         self.encode_ahead = max(1, int(encode_ahead))
         self.fill_hole_area = int(fill_hole_area)
         self.graph_heads = bool(graph_heads)
-        self._heads_graphs = {}            # object count -> _GraphedHeads
+        self._heads_graphs = {}            # (object count, host thread) -> _GraphedHeads
         self._tpos_cache = {}              # (num_frames, max_ptrs) -> projected temporal encodings of the object pointers
 
     @torch.no_grad()
@@ -374,9 +375,10 @@ class SAM2VideoPredictor(_Base):
                 pix = self._ex["memory_attention_none"].Inference([curr, cat(0), curr_pos, cat(1)], output_type="torch")[0]
             pix = pix.permute(1, 2, 0).reshape(n, H.D_MODEL, 64, 64)
             if self.graph_heads:
-                if n not in self._heads_graphs:
-                    self._heads_graphs[n] = _GraphedHeads(self.w, n, self._dense_pe, self.device)
-                low, high, ptr, obj = self._heads_graphs[n](pix, hr)
+                gk = (n, threading.get_ident())    # static buffers are per graph: one graph per host thread
+                if gk not in self._heads_graphs:
+                    self._heads_graphs[gk] = _GraphedHeads(self.w, n, self._dense_pe, self.device)
+                low, high, ptr, obj = self._heads_graphs[gk](pix, hr)
             else:
                 hr_n = [h.expand(n, -1, -1, -1) for h in hr]
                 _, _, _, low, high, ptr, obj = H.forward_sam_heads(self.w, pix, high_res_features=hr_n, multimask_output=True, pe=self._dense_pe)
