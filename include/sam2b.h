@@ -55,7 +55,8 @@ int sam2b_image_encode_host(sam2b_handle h, const float* img_host, int n, int no
 
 /* ---- E3: 4-layer MemoryAttention ----
  * curr, curr_pos dev [4096,n,256]; memory, memory_pos dev [L,4096,n,64]; memory_exclude, memory_pos_exclude dev [P,n,64]
- * (P may be 0, then both may be NULL: the `none` variant); out dev [4096,n,256]. L in [1,7], P in [0,64]. */
+ * (P may be 0, then both may be NULL: the `none` variant); out dev [4096,n,256]. L in [1,16] (the reference's
+ * engines: [1,7]; more than one conditioning frame needs more), P in [0,64]. */
 int sam2b_memory_attention(sam2b_handle h, const float* curr, const float* curr_pos, const float* memory,
                            const float* memory_pos, int L, const float* memory_exclude,
                            const float* memory_pos_exclude, int P, int n, float* out, void* stream);

@@ -773,7 +773,9 @@ int sam2b_memory_attention(sam2b_handle h, const float* curr, const float* curr_
                            int P, int n, float* out, void* stream) {
   if (!h || !h->finalized) { set_error("sam2b_memory_attention: engine not finalized"); return 1; }
   if (!curr || !curr_pos || !memory || !memory_pos || !out || n <= 0) { set_error("sam2b_memory_attention: null/empty argument"); return 1; }
-  if (L < 1 || L > 7 || P < 0 || P > 64 || (P % 4)) { set_error("sam2b_memory_attention: L=%d must be in [1,7], P=%d in [0,64] and a multiple of 4", L, P); return 1; }
+  // the reference's exported engines carry L in [1,7] (one conditioning frame + 6 recent ones); every kernel here is general
+  // in L, so several conditioning frames (L up to 16) are accepted as the reference's torch path accepts them
+  if (L < 1 || L > 16 || P < 0 || P > 64 || (P % 4)) { set_error("sam2b_memory_attention: L=%d must be in [1,16], P=%d in [0,64] and a multiple of 4", L, P); return 1; }
   if (P > 0 && (!memory_exclude || !memory_pos_exclude)) { set_error("sam2b_memory_attention: P=%d but memory_exclude is NULL", P); return 1; }
   CUDA_OK(cudaSetDevice(h->device));
   return memory_attention_mb(h, curr, curr_pos, memory, memory_pos, L, memory_exclude, memory_pos_exclude, P, n, n, out,

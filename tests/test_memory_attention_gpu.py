@@ -53,9 +53,24 @@ def test_e3_full_vs_oracle_steady_state_shape(engine, weights):
     assert r <= TOL
 
 
+def test_e3_more_than_seven_memory_frames(engine, weights):
+    """Several conditioning frames make the bank longer than the 7 slots of the reference's exported engines (its torch
+    path has no such limit, sam2_base_official.py:839-872): L = 9, P = 16 against the CPU oracle."""
+    from oracle import sam2_oracle as O
+    from oracle.synth import synth_memattn_inputs
+    ins = synth_memattn_inputs(9, 16, 1, seed=12)
+    with torch.no_grad():
+        ref = O.memory_attention(weights, *ins)
+    out = engine.memory_attention(*[t.cuda() for t in ins])
+    torch.cuda.synchronize()
+    r = rel_l2(out, ref)
+    print(f"E3 L=9 P=16: rel-L2 vs oracle = {r:.4%}")
+    assert r <= TOL
+
+
 def test_e3_argument_errors(engine):
     from oracle.synth import synth_memattn_inputs
     ins = [t.cuda() for t in synth_memattn_inputs(1, 4, 1, seed=1)]
     with pytest.raises(RuntimeError, match="L="):
-        engine.memory_attention(ins[0], torch.zeros(8, 4096, 1, 64, device="cuda"), ins[2],
-                                torch.zeros(8, 4096, 1, 64, device="cuda"), ins[4], ins[5])
+        engine.memory_attention(ins[0], torch.zeros(17, 4096, 1, 64, device="cuda"), ins[2],
+                                torch.zeros(17, 4096, 1, 64, device="cuda"), ins[4], ins[5])
