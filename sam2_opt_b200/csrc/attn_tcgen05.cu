@@ -295,15 +295,18 @@ flash_attn_hd72_tcgen05_kernel(const __grid_constant__ CUtensorMap map_lo, const
           }
         }
         // P = exp2(S * scale - m) -> bf16 -> swizzled K-major smem tile; fp32 row sum
-        float rs0 = 0.f, rs1 = 0.f;
+        // packed fp32 pairs: one FFMA2 (scale, minus max) and one FADD2 (row sum) per two keys
+        const uint64_t sc2 = f2_pack(p.scale_log2, p.scale_log2), nm2 = f2_pack(-m_run, -m_run);
+        uint64_t rs2a = f2_pack(0.f, 0.f), rs2b = rs2a;
 #pragma unroll
         for (int ch = 0; ch < 4; ++ch) {
           uint32_t pk[16];
 #pragma unroll
           for (int i = 0; i < 16; ++i) {
-            const float e0 = ex2_approx(fmaf(__uint_as_float(s[32 * ch + 2 * i]), p.scale_log2, -m_run));
-            const float e1 = ex2_approx(fmaf(__uint_as_float(s[32 * ch + 2 * i + 1]), p.scale_log2, -m_run));
-            rs0 += e0; rs1 += e1;
+            float a0, a1;
+            f2_unpack(f2_fma(f2_pack(__uint_as_float(s[32 * ch + 2 * i]), __uint_as_float(s[32 * ch + 2 * i + 1])), sc2, nm2), a0, a1);
+            const float e0 = ex2_approx(a0), e1 = ex2_approx(a1);
+            if (i & 1) rs2b = f2_add(rs2b, f2_pack(e0, e1)); else rs2a = f2_add(rs2a, f2_pack(e0, e1));
             pk[i] = pack_bf16x2(e0, e1);
           }
           // 32 keys = 64 B = 16 B chunks (ch & 1) * 4 + i of sub-tile ch >> 1, XOR-swizzled by (row & 7)
@@ -312,6 +315,8 @@ flash_attn_hd72_tcgen05_kernel(const __grid_constant__ CUtensorMap map_lo, const
           for (int i = 0; i < 4; ++i)
             st_shared_u4(base + (((uint32_t)((ch & 1) * 4 + i) << 4) ^ p_xor), pk[4 * i], pk[4 * i + 1], pk[4 * i + 2], pk[4 * i + 3]);
         }
+        float rs0, rs1;
+        f2_unpack(f2_add(rs2a, rs2b), rs0, rs1);
         l_run = fmaf(l_run, corr, rs0 + rs1);
         fence_proxy_async_smem();
         tc_fence_before();
