@@ -298,6 +298,7 @@ static int image_encode_mb(sam2b_engine* e, const float* img, int n, int normali
     TRY(ws_get_t(e, "st2", kStatFloats, &ST2));
     TRY(patch_im2col(img, COLS, n, 1024, normalised ? 0 : 1, st));
     int parts1 = 0, parts2 = 0;         // partial-sum slots per row in ST1 (block input) / ST2 (after attention)
+    static const bool fused_mlp = []() { const char* v = getenv("SAM2B_FUSED_MLP"); return v ? atoi(v) != 0 : false; }();
     {
       GemmArgs g;
       g.A = COLS; g.lda = 160; g.M = (int)T0; g.K = 160;
@@ -347,9 +348,15 @@ static int image_encode_mb(sam2b_engine* e, const float* img, int n, int normali
         TRY(gemm_bf16(g, st));
       }
       if (trans) { float* tmp = X; X = X2; X2 = tmp; }
-      TRY(ln_linear(XB2, c.dim_out, d + "fc1.", 4 * c.dim_out, ST2, parts2, ACT_GELU, nullptr, HID, Tq));
       const bool is_tap = (i == 1 || i == 7 || i == 43 || i == 47);
       bf16* xb_out = is_tap ? TAP[tap] : XB;      // stage taps ARE the bf16 copy of the stream (no cast kernel)
+      if (fused_mlp && mlp_fused_supported(c.dim_out)) {
+        // stages 1 and 2: fc1 -> GELU -> fc2 in one kernel, the hidden layer stays in tensor memory
+        TRY(mlp_fused(XB2, ST2, parts2, 1e-6f, W16(e, d + "fc1.weight"), W32(e, d + "fc1.bias"), W16(e, b + "mlp.layers.1.weight"),
+                      W32(e, b + "mlp.layers.1.bias"), X, xb_out, ST1, Tq, c.dim_out, st));
+        parts1 = 2;
+      } else {
+      TRY(ln_linear(XB2, c.dim_out, d + "fc1.", 4 * c.dim_out, ST2, parts2, ACT_GELU, nullptr, HID, Tq));
       {
         GemmArgs g;
         g.A = HID; g.lda = 4 * c.dim_out; g.M = (int)Tq; g.K = 4 * c.dim_out;
@@ -359,6 +366,7 @@ static int image_encode_mb(sam2b_engine* e, const float* img, int n, int normali
         g.out_f32 = X; g.ldc = c.dim_out;
         g.out2_bf16 = xb_out; g.ldc2 = c.dim_out; g.stats_out = ST1; g.stats_capacity_parts = stat_cap(Tq); g.stats_parts_out = &parts1;
         TRY(gemm_bf16(g, st));
+      }
       }
       xb_in = xb_out;
       if (is_tap) ++tap;

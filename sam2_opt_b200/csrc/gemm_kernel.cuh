@@ -82,36 +82,6 @@ struct GemmCfg {
   static constexpr int SMEM = STAGES * STAGE + EPI_SMEM + 1024 + BAR_BYTES;
 };
 
-// Exact-erf GELU, x * Phi(x), evaluated as relu(x) - |x| * h(|x|) with h(t) = Phi(-t) = 2^p(t); p is a degree-6
-// fit of log2(0.5 erfc(t/sqrt 2)) on [0,6] (max |error| of the GELU value 2e-7 in fp32) -> 6 FMA + 1 MUFU.EX2.
-SAM2B_DEVINL float gelu_fast(float x) {
-  const float t = fminf(fabsf(x), 6.0f);
-  float p = 3.242628146753161e-05f;
-  p = fmaf(p, t, -0.0007628580443300231f);
-  p = fmaf(p, t, 0.008056423025940528f);
-  p = fmaf(p, t, -0.05336353987295394f);
-  p = fmaf(p, t, -0.4588251982307528f);
-  p = fmaf(p, t, -1.1511703007880216f);
-  p = fmaf(p, t, -1.0f);
-  float h;
-  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(h) : "f"(p));
-  return fmaf(-fabsf(x), h, fmaxf(x, 0.0f));
-}
-
-// Same form with a degree-4 exponent (max |error| of the GELU value 6.1e-6, 1/160 of a bf16 ulp at the function's scale):
-// used where the result is rounded to bf16 anyway (trunk MLP hidden layer) -> 4 FMA + 1 MUFU.EX2 + 2 FMNMX + 1 FMA.
-SAM2B_DEVINL float gelu_fast_bf16(float x) {
-  const float t = fminf(fabsf(x), 5.0f);
-  float p = 0.00386557744f;
-  p = fmaf(p, t, -0.0440761234f);
-  p = fmaf(p, t, -0.468019552f);
-  p = fmaf(p, t, -1.14736964f);
-  p = fmaf(p, t, -1.00048006f);
-  float h;
-  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(h) : "f"(p));
-  return fmaf(-fabsf(x), h, fmaxf(x, 0.0f));
-}
-
 // q = t / d for 0 <= t < 2^31 with (mul, shr) from fast_div_setup(d): q = umulhi(t, mul) >> shr
 SAM2B_DEVINL uint32_t fast_div(uint32_t t, uint32_t mul, uint32_t shr) { return mul ? (__umulhi(t, mul) >> shr) : t; }
 // tile index -> (n block, m block, batch), n fastest
