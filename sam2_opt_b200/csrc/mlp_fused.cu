@@ -5,13 +5,15 @@
 // Why: in stages 1 and 2 (K = 144 / 288) the two MLP GEMMs are not tensor bound - fc1's GELU epilogue is issue bound and
 // the 4C-wide hidden tensor is written to and read back from HBM (1.2 GB / 0.6 GB per block per 16 images).  Here the
 // hidden activations never leave the SM:
-//   for every 192-wide chunk h of the hidden layer
-//     S[128 x 192]  = A[128 x C] W1[h]^T                  tcgen05.mma, A tile resident in shared memory, W1 streamed by TMA
-//     P             = bf16(GELU(rstd * S + b1[h]))         epilogue warps, written back over S's columns as packed pairs
+//   for every 96-wide chunk h of the hidden layer
+//     S_b[128 x 96] = A[128 x C] W1[h]^T                  tcgen05.mma, A tile resident in shared memory, W1 streamed by TMA;
+//                                                         b = h & 1: two S buffers, chunk h + 1 is computed while
+//     P             = bf16(GELU(rstd * S_b + b1[h]))       the epilogue warps work on chunk h; P is written back over S_b's
+//                                                         columns as packed pairs
 //     O[128 x C]   += P W2[:, h]^T                         tcgen05.mma with the A operand (P) read from TENSOR MEMORY
 //   x_out = O + b2 + x; bf16 copy and per-row (sum, sum of squares) for the next block's folded LayerNorm
-// TMEM: S 192 columns + O C columns (<= 480).  Warps: 0 TMA producer, 1 MMA issuer, 2 TMEM allocation, 4-11 epilogue
-// (lane quarter = warp & 3, column half = (warp - 4) >> 2).
+// TMEM: S 2 x 96 columns + O C columns (<= 480).  Warps: 0 TMA producer, 1 MMA issuer, 2 TMEM allocation, 4-11 epilogue:
+// lane quarter = warp & 3; group (warp - 4) >> 2 takes the even / odd hidden chunks and one half of O's columns.
 #include <cuda.h>
 #include <cuda_runtime.h>
 
@@ -25,11 +27,11 @@ namespace sam2b {
 
 namespace fm {
 static constexpr int BM = 128;
-static constexpr int BH = 192;                       // hidden chunk
+static constexpr int BH = 96;                        // hidden chunk
 static constexpr int THREADS = 384;
 static constexpr int A_KB_BYTES = BM * 128;          // [128 rows][64 k] bf16, 128B swizzle
-static constexpr int W1_BYTES = BH * 128;            // [192 hidden][64 k]
-static constexpr int COL_S = 0;
+static constexpr int W1_BYTES = BH * 128;            // [96 hidden][64 k]
+static constexpr int COL_S = 0;                      // S buffer b at COL_S + 96 b; P over its first 48 columns
 static constexpr int COL_O = 192;
 template <int C>
 struct Cfg {
@@ -37,14 +39,15 @@ struct Cfg {
   static constexpr int NH = 4 * C / BH;              // hidden chunks
   static constexpr int NSPLIT = C / 144;             // fc2 instructions per k-step (N = 144 each; tcgen05.mma N <= 256)
   static constexpr int W2_BYTES = C * 128;           // [C rows][64 hidden]
-  static constexpr int NS1 = C == 144 ? 3 : 2;       // W1 ring depth
+  static constexpr int NB2 = 4 * C / 64;             // 64-wide W2 blocks per tile (a block may straddle two hidden chunks)
+  static constexpr int NS1 = 4;                      // W1 ring depth
   static constexpr int NS2 = C == 144 ? 3 : 2;       // W2 ring depth
   static constexpr int OFF_A = 0;
   static constexpr int OFF_W1 = OFF_A + KB * A_KB_BYTES;
   static constexpr int OFF_W2 = OFF_W1 + NS1 * W1_BYTES;
   static constexpr int OFF_BAR = OFF_W2 + NS2 * W2_BYTES;
   static constexpr int SMEM = OFF_BAR + 256 + 1024;
-  static_assert(4 * C % BH == 0 && C % 144 == 0, "C must be 144 or 288");
+  static_assert(4 * C % BH == 0 && C % 144 == 0 && NH % 2 == 0, "C must be 144 or 288");
   static_assert(COL_O + C <= 512, "TMEM columns");
 };
 }  // namespace fm
@@ -76,9 +79,9 @@ mlp_fused_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
   uint64_t* w1_empty = w1_full + K::NS1;
   uint64_t* w2_full = w1_empty + K::NS1;        // [NS2]
   uint64_t* w2_empty = w2_full + K::NS2;
-  uint64_t* s_full = w2_empty + K::NS2;
-  uint64_t* p_full = s_full + 1;
-  uint64_t* o_full = p_full + 1;
+  uint64_t* s_full = w2_empty + K::NS2;         // [2]
+  uint64_t* p_full = s_full + 2;                // [2]
+  uint64_t* o_full = p_full + 2;
   uint64_t* o_free = o_full + 1;
   uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(o_free + 1);
 
@@ -92,7 +95,8 @@ mlp_fused_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
     mbar_init(a_full, 1); mbar_init(a_empty, 1);
     for (int i = 0; i < K::NS1; ++i) { mbar_init(&w1_full[i], 1); mbar_init(&w1_empty[i], 1); }
     for (int i = 0; i < K::NS2; ++i) { mbar_init(&w2_full[i], 1); mbar_init(&w2_empty[i], 1); }
-    mbar_init(s_full, 1); mbar_init(p_full, 8); mbar_init(o_full, 1); mbar_init(o_free, 8);
+    for (int i = 0; i < 2; ++i) { mbar_init(&s_full[i], 1); mbar_init(&p_full[i], 4); }
+    mbar_init(o_full, 1); mbar_init(o_free, 8);
     fence_barrier_init();
   }
   if (warp == 2) { tmem_alloc(tmem_ptr, 512); tmem_relinquish(); }
@@ -110,20 +114,28 @@ mlp_fused_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
         mbar_arrive_expect_tx(a_full, K::KB * A_KB_BYTES);
 #pragma unroll
         for (int kb = 0; kb < K::KB; ++kb) tma_load_3d(smem + K::OFF_A + kb * A_KB_BYTES, &map_a, a_full, kb * 64, t * BM, 0);
-        for (int h = 0; h < K::NH; ++h) {
+        // same order as the MMA warp consumes: W1 of chunk 0, then for every chunk h: W1 of chunk h + 1, W2 blocks up to the
+        // last one chunk h touches
+        auto load_w1 = [&](int h) {
           for (int kb = 0; kb < K::KB; ++kb, ++i1) {
             const int s = i1 % K::NS1;
             mbar_wait(&w1_empty[s], ((i1 / K::NS1) & 1) ^ 1);
             mbar_arrive_expect_tx(&w1_full[s], W1_BYTES);
             tma_load_3d(smem + K::OFF_W1 + s * W1_BYTES, &map_w1, &w1_full[s], kb * 64, h * BH, 0);
           }
-          for (int kb = 0; kb < BH / 64; ++kb, ++i2) {
+        };
+        load_w1(0);
+        int blk = 0;
+        for (int h = 0; h < K::NH; ++h) {
+          if (h + 1 < K::NH) load_w1(h + 1);
+          const int last = (BH * h + BH - 1) / 64;
+          for (; blk <= last; ++blk, ++i2) {
             const int s = i2 % K::NS2;
             mbar_wait(&w2_empty[s], ((i2 / K::NS2) & 1) ^ 1);
             mbar_arrive_expect_tx(&w2_full[s], K::W2_BYTES);
 #pragma unroll
             for (int j = 0; j < K::NSPLIT; ++j)
-              tma_load_3d(smem + K::OFF_W2 + s * K::W2_BYTES + j * 144 * 128, &map_w2, &w2_full[s], h * BH + kb * 64, j * 144, 0);
+              tma_load_3d(smem + K::OFF_W2 + s * K::W2_BYTES + j * 144 * 128, &map_w2, &w2_full[s], blk * 64, j * 144, 0);
           }
         }
       }
@@ -135,55 +147,67 @@ mlp_fused_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
       constexpr uint32_t idesc_fc2 = make_idesc_ex(128, 144, 0);
       const uint32_t sbase = smem_u32(smem);
       int i1 = 0, i2 = 0, nt = 0;
-      uint32_t n_p = 0;                 // hidden chunks handed over by the epilogue warps (phase of p_full)
+      uint32_t n_s[2] = {0, 0};         // fc1 products issued on S buffer b
+      uint32_t n_p[2] = {0, 0};         // hidden chunks handed over through buffer b (phase of p_full[b])
+      auto issue_fc1 = [&](int h) {
+        const int b = h & 1;
+        for (int kb = 0; kb < K::KB; ++kb, ++i1) {
+          const int s = i1 % K::NS1;
+          mbar_wait(&w1_full[s], (i1 / K::NS1) & 1);
+          tc_fence_after();
+          const uint32_t a = sbase + K::OFF_A + kb * A_KB_BYTES, w = sbase + K::OFF_W1 + s * W1_BYTES;
+          const int ksteps = (C - kb * 64) >= 64 ? 4 : (C - kb * 64) / 16;
+          for (int k = 0; k < ksteps; ++k)
+            umma_bf16(tmem_base + COL_S + BH * b, make_smem_desc(a + k * 32, 16, 1024, 2), make_smem_desc(w + k * 32, 16, 1024, 2),
+                      idesc_fc1, (kb | k) != 0);
+          umma_commit(&w1_empty[s]);
+        }
+        umma_commit(&s_full[b]);
+        ++n_s[b];
+      };
       for (int t = blockIdx.x; t < p.num_tiles; t += gridDim.x, ++nt) {
         mbar_wait(a_full, nt & 1);
         tc_fence_after();
+        // S_b is reused by chunk h + 2: in order behind fc2 of chunk h, which read P(h) out of it after the epilogue warps had
+        // read S(h) - no extra barrier needed
+        issue_fc1(0);
         for (int h = 0; h < K::NH; ++h) {
-          // ---- S = A W1[h]^T (the tensor pipe is in order: this follows fc2 of chunk h - 1, which read P out of S's columns) ----
-          for (int kb = 0; kb < K::KB; ++kb, ++i1) {
-            const int s = i1 % K::NS1;
-            mbar_wait(&w1_full[s], (i1 / K::NS1) & 1);
-            tc_fence_after();
-            const uint32_t a = sbase + K::OFF_A + kb * A_KB_BYTES, w = sbase + K::OFF_W1 + s * W1_BYTES;
-            const int ksteps = (C - kb * 64) >= 64 ? 4 : (C - kb * 64) / 16;
-            for (int k = 0; k < ksteps; ++k)
-              umma_bf16(tmem_base + COL_S, make_smem_desc(a + k * 32, 16, 1024, 2), make_smem_desc(w + k * 32, 16, 1024, 2), idesc_fc1,
-                        (kb | k) != 0);
-            umma_commit(&w1_empty[s]);
-          }
-          umma_commit(s_full);
-          if (h == K::NH - 1) umma_commit(a_empty);          // the A tile has been read for the last time
-          // ---- O += P W2[:, h]^T, P from tensor memory ----
-          mbar_wait(p_full, n_p & 1);
-          ++n_p;
-          if (h == 0) mbar_wait(o_free, (nt & 1) ^ 1);       // the previous tile's O has been read out
+          if (h + 1 < K::NH) issue_fc1(h + 1);                 // overlaps the GELU pass over chunk h
+          if (h + 1 >= K::NH - 1 && h + 1 <= K::NH - 1) umma_commit(a_empty);   // last fc1 of the tile has been issued
+          const int b = h & 1;
+          mbar_wait(&p_full[b], n_p[b] & 1);
+          ++n_p[b];
+          if (h == 0) mbar_wait(o_free, (nt & 1) ^ 1);          // the previous tile's O has been read out
           tc_fence_after();
-          for (int kb = 0; kb < BH / 64; ++kb, ++i2) {
-            const int s = i2 % K::NS2;
-            mbar_wait(&w2_full[s], (i2 / K::NS2) & 1);
-            tc_fence_after();
-            const uint32_t w = sbase + K::OFF_W2 + s * K::W2_BYTES;
-#pragma unroll
-            for (int k = 0; k < 4; ++k) {
-              const uint32_t pa = tmem_base + COL_S + kb * 32 + k * 8;       // 16 hidden units = 8 columns of bf16 pairs
-#pragma unroll
-              for (int j = 0; j < K::NSPLIT; ++j)
-                umma_bf16_ts(tmem_base + COL_O + j * 144, pa, make_smem_desc(w + j * 144 * 128 + k * 32, 16, 1024, 2), idesc_fc2,
-                             (h | kb | k) != 0);
+#pragma unroll 1
+          for (int k = 0; k < BH / 16; ++k) {
+            const int g = h * (BH / 16) + k;                    // k-step of this tile's fc2: 64-wide W2 block g / 4, step g % 4
+            const int st = g & 3;
+            const int s = (i2 + (g >> 2)) % K::NS2;
+            if (st == 0 || k == 0) {
+              if (st == 0) {                                      // first use of the block
+                mbar_wait(&w2_full[s], ((i2 + (g >> 2)) / K::NS2) & 1);
+                tc_fence_after();
+              }
             }
-            umma_commit(&w2_empty[s]);
+            const uint32_t w = sbase + K::OFF_W2 + s * K::W2_BYTES;
+            const uint32_t pa = tmem_base + COL_S + BH * b + k * 8;            // 16 hidden units = 8 columns of bf16 pairs
+#pragma unroll
+            for (int j = 0; j < K::NSPLIT; ++j)
+              umma_bf16_ts(tmem_base + COL_O + j * 144, pa, make_smem_desc(w + j * 144 * 128 + st * 32, 16, 1024, 2), idesc_fc2,
+                           (h | k) != 0);
+            if (st == 3) umma_commit(&w2_empty[s]);
           }
         }
+        i2 += K::NB2;
         umma_commit(o_full);
       }
     }
   } else if (warp >= 4) {
     // ===================== epilogue warps =====================
-    const int q = warp & 3, half = (warp - 4) >> 2;
+    const int q = warp & 3, half = (warp - 4) >> 2;          // half: hidden chunks of this parity, and this half of O's columns
     const uint32_t lane_sel = (uint32_t)(q * 32) << 16;
-    auto pair_sync = [&]() { asm volatile("bar.sync %0, 64;" ::"r"(1 + q) : "memory"); };
-    uint32_t n_s = 0;
+    uint32_t n_s = 0;                                         // chunks this group has taken (phase of s_full[half])
     int nt = 0;
     for (int t = blockIdx.x; t < p.num_tiles; t += gridDim.x, ++nt) {
       const long row = (long)t * BM + q * 32 + lane;
@@ -196,16 +220,17 @@ mlp_fused_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
         const float mu = s1 * p.inv_c;
         rstd = rsqrtf(fmaxf(fmaf(s2, p.inv_c, -mu * mu), 0.f) + p.eps);
       }
-      for (int h = 0; h < K::NH; ++h, ++n_s) {
-        mbar_wait(s_full, n_s & 1);
+      const uint32_t ts = tmem_base + COL_S + BH * half + lane_sel;
+      for (int h = half; h < K::NH; h += 2, ++n_s) {
+        mbar_wait(&s_full[half], n_s & 1);
         tc_fence_after();
-        uint32_t pk[64];                                  // this thread's 96 hidden units of the chunk as 48 bf16 pairs (+ slack)
+        uint32_t pk[64];                                  // this row's 96 hidden units of the chunk as 48 bf16 pairs (+ slack)
 #pragma unroll
         for (int c = 0; c < 3; ++c) {
           uint32_t r[32];
-          tmem_ld_x32(tmem_base + COL_S + half * 96 + c * 32 + lane_sel, r);
+          tmem_ld_x32(ts + c * 32, r);
           tmem_ld_wait();
-          const float4* bsrc = reinterpret_cast<const float4*>(p.b1 + h * BH + half * 96 + c * 32);
+          const float4* bsrc = reinterpret_cast<const float4*>(p.b1 + h * BH + c * 32);
 #pragma unroll
           for (int j = 0; j < 8; ++j) {
             const float4 b = __ldg(bsrc + j);
@@ -217,16 +242,13 @@ mlp_fused_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
             pk[c * 16 + 2 * j + 1] = pack_bf16x2(v2, v3);
           }
         }
-        // P overwrites S's first 96 columns: both warps of this lane quarter must hold their scores in registers first
-        tc_fence_before();
-        pair_sync();
-        tc_fence_after();
-        tmem_st_x32(tmem_base + COL_S + half * 48 + lane_sel, *reinterpret_cast<uint32_t(*)[32]>(&pk[0]));
-        tmem_st_x16(tmem_base + COL_S + half * 48 + 32 + lane_sel, *reinterpret_cast<uint32_t(*)[32]>(&pk[32]));
+        // P over the first 48 columns of the buffer this warp has just read (same lanes, same warp: no cross-warp hazard)
+        tmem_st_x32(ts, *reinterpret_cast<uint32_t(*)[32]>(&pk[0]));
+        tmem_st_x16(ts + 32, *reinterpret_cast<uint32_t(*)[32]>(&pk[32]));
         tmem_st_wait();
         tc_fence_before();
         __syncwarp();
-        if (lane == 0) mbar_arrive(p_full);
+        if (lane == 0) mbar_arrive(&p_full[half]);
       }
       // ---- tile done: x = O + b2 + x, bf16 copy, row statistics ----
       mbar_wait(o_full, nt & 1);

@@ -96,3 +96,22 @@ def test_host_buffer_entry_point_matches_device_path(engine):
         host = engine.image_encode_host(imgs.pin_memory(), True, False, host)
     for d, h in zip(dev, host):
         assert torch.equal(d.cpu(), h)
+
+
+def test_fused_mlp_path_matches_the_two_gemm_path(monkeypatch):
+    """mlp_fused.cu (fc1 -> GELU -> fc2 in one kernel for the C = 144 / 288 blocks, hidden layer in tensor memory; off by
+    default) against the default schedule on the same engine: same arithmetic up to the order of the fp32 sums."""
+    from oracle import sam2_oracle as O
+    from sam2_opt_b200.engine import Engine
+    e = Engine(O.make_weights(0))
+    g = torch.Generator(device="cuda").manual_seed(5)
+    img = torch.randn(2, 3, 1024, 1024, device="cuda", generator=g)
+    monkeypatch.delenv("SAM2B_FUSED_MLP", raising=False)
+    ref = [o.clone() for o in e.image_encode(img, True, False)]
+    monkeypatch.setenv("SAM2B_FUSED_MLP", "1")
+    got = e.image_encode(img, True, False)
+    for a, b in zip(got, ref):
+        r = float((a - b).norm() / b.norm())
+        print(f"fused-MLP vs default: rel-L2 {r:.3e}")
+        assert r < 5e-3
+    e.release()
