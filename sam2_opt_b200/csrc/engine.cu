@@ -298,8 +298,8 @@ static int image_encode_mb(sam2b_engine* e, const float* img, int n, int normali
     TRY(ws_get_t(e, "st2", kStatFloats, &ST2));
     TRY(patch_im2col(img, COLS, n, 1024, normalised ? 0 : 1, st));
     int parts1 = 0, parts2 = 0;         // partial-sum slots per row in ST1 (block input) / ST2 (after attention)
-    // experimental (mlp_fused.cu): parity green but, at 0.9-1.4 ms per block, not yet faster than the two GEMMs it replaces
-    // (0.55-0.97 ms); read per call so that a test can switch it
+    // experimental (mlp_fused.cu): parity green but, at 1.05 / 1.4 ms per stage-2 / stage-1 block, not yet faster than the two
+    // GEMMs it replaces (0.55 / 0.97 ms) - see DESIGN.md section 7; read per call so that a test can switch it
     const char* fused_env = getenv("SAM2B_FUSED_MLP");
     const bool fused_mlp = fused_env && atoi(fused_env) != 0;
     {

@@ -12,7 +12,7 @@
 //                                                         columns as packed pairs
 //     O[128 x C]   += P W2[:, h]^T                         tcgen05.mma with the A operand (P) read from TENSOR MEMORY
 //   x_out = O + b2 + x; bf16 copy and per-row (sum, sum of squares) for the next block's folded LayerNorm
-// TMEM: S 2 x 96 columns + O C columns (<= 480).  Warps: 0 TMA producer, 1 MMA issuer, 2 TMEM allocation, 4-11 epilogue:
+// TMEM: S 2 x 96 columns + O C columns (<= 480).  Warps: 0 and 3 TMA producers (A + W1 / W2), 1 MMA issuer, 2 TMEM allocation, 4-11 epilogue:
 // lane quarter = warp & 3; group (warp - 4) >> 2 takes the even / odd hidden chunks and one half of O's columns.
 #include <cuda.h>
 #include <cuda_runtime.h>
@@ -40,8 +40,8 @@ struct Cfg {
   static constexpr int NSPLIT = C / 144;             // fc2 instructions per k-step (N = 144 each; tcgen05.mma N <= 256)
   static constexpr int W2_BYTES = C * 128;           // [C rows][64 hidden]
   static constexpr int NB2 = 4 * C / 64;             // 64-wide W2 blocks per tile (a block may straddle two hidden chunks)
-  static constexpr int NS1 = 4;                      // W1 ring depth
-  static constexpr int NS2 = C == 144 ? 3 : 2;       // W2 ring depth
+  static constexpr int NS1 = C == 144 ? 4 : 3;       // W1 ring depth
+  static constexpr int NS2 = 3;                      // W2 ring depth
   static constexpr int OFF_A = 0;
   static constexpr int OFF_W1 = OFF_A + KB * A_KB_BYTES;
   static constexpr int OFF_W2 = OFF_W1 + NS1 * W1_BYTES;
@@ -106,37 +106,36 @@ mlp_fused_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
   const uint32_t tmem_base = *tmem_ptr;
 
   if (warp == 0) {
-    // ===================== TMA producer =====================
+    // ===================== TMA producer 1: the A tile and the W1 ring =====================
     if (lane == 0) {
-      int i1 = 0, i2 = 0, nt = 0;
+      int i1 = 0, nt = 0;
       for (int t = blockIdx.x; t < p.num_tiles; t += gridDim.x, ++nt) {
         mbar_wait(a_empty, (nt & 1) ^ 1);
         mbar_arrive_expect_tx(a_full, K::KB * A_KB_BYTES);
 #pragma unroll
         for (int kb = 0; kb < K::KB; ++kb) tma_load_3d(smem + K::OFF_A + kb * A_KB_BYTES, &map_a, a_full, kb * 64, t * BM, 0);
-        // same order as the MMA warp consumes: W1 of chunk 0, then for every chunk h: W1 of chunk h + 1, W2 blocks up to the
-        // last one chunk h touches
-        auto load_w1 = [&](int h) {
+        for (int h = 0; h < K::NH; ++h) {
           for (int kb = 0; kb < K::KB; ++kb, ++i1) {
             const int s = i1 % K::NS1;
             mbar_wait(&w1_empty[s], ((i1 / K::NS1) & 1) ^ 1);
             mbar_arrive_expect_tx(&w1_full[s], W1_BYTES);
             tma_load_3d(smem + K::OFF_W1 + s * W1_BYTES, &map_w1, &w1_full[s], kb * 64, h * BH, 0);
           }
-        };
-        load_w1(0);
-        int blk = 0;
-        for (int h = 0; h < K::NH; ++h) {
-          if (h + 1 < K::NH) load_w1(h + 1);
-          const int last = (BH * h + BH - 1) / 64;
-          for (; blk <= last; ++blk, ++i2) {
-            const int s = i2 % K::NS2;
-            mbar_wait(&w2_empty[s], ((i2 / K::NS2) & 1) ^ 1);
-            mbar_arrive_expect_tx(&w2_full[s], K::W2_BYTES);
+        }
+      }
+    }
+  } else if (warp == 3) {
+    // ===================== TMA producer 2: the W2 ring (its own thread: a full W2 ring must not hold back W1) =====================
+    if (lane == 0) {
+      int i2 = 0;
+      for (int t = blockIdx.x; t < p.num_tiles; t += gridDim.x) {
+        for (int blk = 0; blk < K::NB2; ++blk, ++i2) {
+          const int s = i2 % K::NS2;
+          mbar_wait(&w2_empty[s], ((i2 / K::NS2) & 1) ^ 1);
+          mbar_arrive_expect_tx(&w2_full[s], K::W2_BYTES);
 #pragma unroll
-            for (int j = 0; j < K::NSPLIT; ++j)
-              tma_load_3d(smem + K::OFF_W2 + s * K::W2_BYTES + j * 144 * 128, &map_w2, &w2_full[s], blk * 64, j * 144, 0);
-          }
+          for (int j = 0; j < K::NSPLIT; ++j)
+            tma_load_3d(smem + K::OFF_W2 + s * K::W2_BYTES + j * 144 * 128, &map_w2, &w2_full[s], blk * 64, j * 144, 0);
         }
       }
     }
@@ -258,7 +257,7 @@ mlp_fused_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
       float* xr = p.x + row * C;
       bf16* xbr = p.xb_out + row * C;
       float s1 = 0.f, s2 = 0.f;
-#pragma unroll 1
+#pragma unroll 3
       for (int c = c0; c < c1; ++c) {
         uint32_t r[32];
         tmem_ld_x16(tmem_base + COL_O + c * 16 + lane_sel, r);
