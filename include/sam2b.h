@@ -103,6 +103,11 @@ int sam2b_op_window_attention(const void* qkv_bf16, void* out_bf16, int b, int h
  * (non-zero = foreground), labels / counts dev int32 [n][h][w]: label 0 and count 0 for background, otherwise a positive
  * label shared by the 8-connected component and the component's area in pixels. */
 int sam2b_op_connected_components(const void* mask_u8, int32_t* labels, int32_t* counts, int n, int h, int w, void* stream);
+/* Pre-processing of camera / video frames (replaces SAM2Transforms.__call__, sam2/utils/transforms.py:38-46, at the model
+ * resolution where its Resize is the identity): hwc_u8 dev uint8 [n][h][w][3] -> out_nchw dev fp32 [n][3][h][w] = x / 255 and,
+ * with normalise != 0, (x / 255 - mean) / std with the ImageNet constants of transforms.py:27-28.  Same IEEE operations in
+ * the same order as the reference: bit-exact.  w must be a multiple of 4. */
+int sam2b_op_preprocess_u8(const void* hwc_u8, float* out_nchw, int n, int h, int w, int normalise, void* stream);
 int sam2b_op_softmax_rows(const float* s, int64_t lds, void* p_bf16, int64_t ldp, int64_t rows, int cols, void* stream);
 /* Single-head flash attention, head_dim 256 (the MemoryAttention core; reference sam/transformer.py:265-296):
  * out[b] = softmax(q[b] k[b]^T / 16) v[b];  q [n][tq][256], k, v [n][lk][256], out [n][tq][256], all bf16 device memory,

@@ -212,6 +212,49 @@ int patch_im2col(const float* img, bf16* cols, int B, int S, int normalise, cuda
 }
 
 // ------------------------------------------------------------------------------------------
+// Pre-processing: uint8 HWC frames -> fp32 NCHW in [0,1], optionally (x - mean) / std.
+// Reference: SAM2Transforms.__call__ (sam2/utils/transforms.py:38-46: ToTensor = /255, Resize is the identity at the
+// model resolution, Normalize = sub(mean).div(std)); same IEEE operations in the same order -> bit-exact.
+// One thread per 4 pixels of a row: 12 input bytes (three aligned 32-bit loads), one float4 store per colour plane.
+// ------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) preprocess_u8_kernel(const uint32_t* __restrict__ in, float4* __restrict__ out, long quads,
+                                                            long quads_per_img, int normalise) {
+  const float mean[3] = {0.485f, 0.456f, 0.406f};
+  const float stdv[3] = {0.229f, 0.224f, 0.225f};
+  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < quads; i += (long)gridDim.x * blockDim.x) {
+    const uint32_t w0 = __ldg(in + 3 * i), w1 = __ldg(in + 3 * i + 1), w2 = __ldg(in + 3 * i + 2);
+    const uint8_t b[12] = {(uint8_t)w0, (uint8_t)(w0 >> 8), (uint8_t)(w0 >> 16), (uint8_t)(w0 >> 24),
+                           (uint8_t)w1, (uint8_t)(w1 >> 8), (uint8_t)(w1 >> 16), (uint8_t)(w1 >> 24),
+                           (uint8_t)w2, (uint8_t)(w2 >> 8), (uint8_t)(w2 >> 16), (uint8_t)(w2 >> 24)};
+    const long img = i / quads_per_img, q = i - img * quads_per_img;
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+      float v[4];
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        v[e] = __fdiv_rn((float)b[3 * e + c], 255.0f);
+        if (normalise) v[e] = __fdiv_rn(__fsub_rn(v[e], mean[c]), stdv[c]);
+      }
+      out[(img * 3 + c) * quads_per_img + q] = make_float4(v[0], v[1], v[2], v[3]);
+    }
+  }
+}
+int preprocess_u8_hwc(const uint8_t* in, float* out, int n, int H, int W, int normalise, cudaStream_t stream) {
+  if (n <= 0 || H <= 0 || W <= 0 || W % 4 || (reinterpret_cast<uintptr_t>(in) & 3) || (reinterpret_cast<uintptr_t>(out) & 15)) {
+    set_error("preprocess_u8_hwc: n=%d H=%d W=%d (W must be a multiple of 4, input 4 B / output 16 B aligned)", n, H, W);
+    return 1;
+  }
+  const long qpi = (long)H * W / 4, quads = qpi * n;
+  long blocks = (quads + 255) / 256;
+  if (blocks > (long)num_sms() * 16) blocks = (long)num_sms() * 16;
+  ProfRange pr(stream, "preprocess_u8", 0, (double)quads * (12.0 + 48.0));
+  preprocess_u8_kernel<<<(unsigned)blocks, 256, 0, stream>>>(reinterpret_cast<const uint32_t*>(in), reinterpret_cast<float4*>(out), quads, qpi,
+                                                             normalise);
+  SAM2B_CHECK_LAUNCH("preprocess_u8");
+  return 0;
+}
+
+// ------------------------------------------------------------------------------------------
 // FPN top-down: dst += nearest_x2(src)   (reference: image_encoder.py:115-127, fpn_interp_model nearest)
 // ------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256) upsample2x_add_kernel(float4* __restrict__ dst, const float2* __restrict__ src, long total4, int W4,

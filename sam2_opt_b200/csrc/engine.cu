@@ -886,6 +886,10 @@ int sam2b_op_connected_components(const void* mask_u8, int32_t* labels, int32_t*
   if (!mask_u8 || !labels || !counts) { set_error("sam2b_op_connected_components: null argument"); return 1; }
   return connected_components(reinterpret_cast<const uint8_t*>(mask_u8), labels, counts, n, h, w, reinterpret_cast<cudaStream_t>(stream));
 }
+int sam2b_op_preprocess_u8(const void* hwc_u8, float* out_nchw, int n, int h, int w, int normalise, void* stream) {
+  if (!hwc_u8 || !out_nchw) { set_error("sam2b_op_preprocess_u8: null argument"); return 1; }
+  return preprocess_u8_hwc(reinterpret_cast<const uint8_t*>(hwc_u8), out_nchw, n, h, w, normalise, reinterpret_cast<cudaStream_t>(stream));
+}
 int sam2b_op_softmax_rows(const float* s, int64_t lds, void* p, int64_t ldp, int64_t rows, int cols, void* stream) {
   return softmax_rows(s, lds, reinterpret_cast<bf16*>(p), ldp, rows, cols, reinterpret_cast<cudaStream_t>(stream));
 }

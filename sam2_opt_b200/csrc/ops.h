@@ -94,15 +94,17 @@ int flash_attention_hd256(const bf16* q, long q_batch_stride, const bf16* k, lon
 
 // Row softmax over fp32 scores -> bf16 probabilities (row stride lds / ldp elements), `cols` valid columns;
 // columns in [cols, ldp) are written as zero.
+int softmax_rows(const float* s, long lds, bf16* p, long ldp, long rows, int cols, cudaStream_t stream);
 // Connected components of `mask != 0` under 8-connectivity (connected_components.cu): labels int32 [n][H][W] (0 = background,
 // otherwise 1 + smallest pixel index of the component), counts = area of the pixel's component (0 for background).
+int connected_components(const uint8_t* mask, int* labels, int* counts, int n, int H, int W, cudaStream_t stream);
+// uint8 HWC [n][H][W][3] -> fp32 NCHW [n][3][H][W] = x / 255, optionally (x - mean) / std (SAM2Transforms, bit-exact)
+int preprocess_u8_hwc(const uint8_t* in, float* out, int n, int H, int W, int normalise, cudaStream_t stream);
 // Fused trunk MLP for C = 144 / 288 (mlp_fused.cu): x += fc2(GELU(rstd * (xb W1''^T) + b1)) + b2 in place, bf16 copy and
 // per-row (sum, sum of squares) in two parts for the next folded LayerNorm; the hidden layer never reaches HBM.
 bool mlp_fused_supported(int C);
 int mlp_fused(const bf16* xb, const float* stats_in, int parts_in, float eps, const bf16* w1, const float* b1, const bf16* w2,
               const float* b2, float* x, bf16* xb_out, float* stats_out, long M, int C, cudaStream_t stream);
-int connected_components(const uint8_t* mask, int* labels, int* counts, int n, int H, int W, cudaStream_t stream);
-int softmax_rows(const float* s, long lds, bf16* p, long ldp, long rows, int cols, cudaStream_t stream);
 
 // Axial RoPE (interleaved pairs) applied in place on x [rows, 256] fp32->bf16 conversion included:
 // y_bf16[r] = rope(x[r]) with table row (r % 4096) when r < rope_rows, else plain cast.

@@ -58,6 +58,21 @@ def cast_bf16(x: torch.Tensor) -> torch.Tensor:
     return y
 
 
+def preprocess_u8(hwc: torch.Tensor, normalise: bool = False) -> torch.Tensor:
+    """uint8 [N,H,W,3] (or [H,W,3]) on the device -> fp32 [N,3,H,W]: /255 and, if `normalise`, (x - mean) / std with the
+    ImageNet constants, bit-identical to the reference's ToTensor -> Normalize (sam2/utils/transforms.py:27-46)."""
+    lib = _lib.load()
+    if hwc.dim() == 3:
+        hwc = hwc[None]
+    if hwc.dtype != torch.uint8 or hwc.dim() != 4 or hwc.shape[-1] != 3 or not hwc.is_cuda:
+        raise ValueError(f"preprocess_u8: expected a CUDA uint8 [N,H,W,3] tensor, got {hwc.dtype} {tuple(hwc.shape)} on {hwc.device}")
+    hwc = hwc.contiguous()
+    n, h, w, _ = hwc.shape
+    y = torch.empty((n, 3, h, w), device=hwc.device, dtype=torch.float32)
+    _lib.check(lib.sam2b_op_preprocess_u8(_ptr(hwc), _ptr(y), n, h, w, int(bool(normalise)), _stream()), "op_preprocess_u8")
+    return y
+
+
 def maxpool2x2_nhwc(x: torch.Tensor) -> torch.Tensor:
     lib = _lib.load()
     B, H, W, Cd = x.shape

@@ -19,6 +19,7 @@ import numpy as np
 import torch
 import torch.nn.functional as F
 
+from . import ops
 from . import sam_heads as H
 from .executor import B200Executor
 
@@ -64,6 +65,8 @@ class _Base:
     def _prep_image(self, image) -> torch.Tensor:
         """uint8 HWC numpy -> [1,3,1024,1024] fp32 in [0,1] (ref: sam2_image_predictor.py:173-196: /255 then resize)."""
         img = torch.as_tensor(np.ascontiguousarray(image)).to(self.device)
+        if img.dtype == torch.uint8 and tuple(img.shape) == (1024, 1024, 3):
+            return ops.preprocess_u8(img)         # one pass: bytes in, fp32 planes out
         img = img.permute(2, 0, 1)[None].float() / 255.0
         if img.shape[-2:] != (1024, 1024):
             img = F.interpolate(img, size=(1024, 1024), mode="bilinear", align_corners=False, antialias=True)
@@ -203,7 +206,7 @@ class SAM2VideoPredictor(_Base):
             video_height, video_width = frames[0].shape[:2]
             mean = torch.tensor(IMG_MEAN, device=self.device)[None, :, None, None]
             std = torch.tensor(IMG_STD, device=self.device)[None, :, None, None]
-            frames = torch.cat([((self._prep_image(f) - mean) / std).cpu() for f in frames], 0)
+            frames = torch.cat([self._prep_frame(f, mean, std).cpu() for f in frames], 0)
         assert frames.dim() == 4 and tuple(frames.shape[1:]) == (3, 1024, 1024)
         st = {"images": frames if offload_video_to_cpu else frames.to(self.device), "num_frames": frames.shape[0],
               "video_height": video_height or 1024, "video_width": video_width or 1024,
@@ -215,6 +218,12 @@ class SAM2VideoPredictor(_Base):
         for k in ("prompts", "cond", "non_cond", "non_cond_b", "cond_b"):
             st[k].clear()
         st["obj_ids"], st["feat_cache"], st["frames_tracked"] = [], {}, {}
+
+    def _prep_frame(self, f, mean, std):
+        """one uint8 HWC frame -> normalised [1,3,1024,1024] fp32 (ref: utils/misc.py:96,161-162)"""
+        if isinstance(f, np.ndarray) and f.dtype == np.uint8 and f.shape == (1024, 1024, 3):
+            return ops.preprocess_u8(torch.as_tensor(np.ascontiguousarray(f)).to(self.device), normalise=True)
+        return (self._prep_image(f) - mean) / std
 
     # -- per-frame image features, produced `encode_ahead` frames at a time --------------------------------------
     def _features(self, st, t):

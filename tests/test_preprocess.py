@@ -1,0 +1,90 @@
+"""uint8 -> fp32 image preprocessing: the oracle is pinned on CPU against the operators the reference
+calls (torch `div`/`sub`, sam2/utils/transforms.py:27-46; numpy float64 route of utils/misc.py:96), the CUDA op is
+compared with the oracle bit for bit through the C ABI."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import preprocess_oracle as O
+
+
+def _frames(n, h, w, seed=0):
+    rng = np.random.default_rng(seed)
+    x = rng.integers(0, 256, size=(n, h, w, 3), dtype=np.uint8)
+    x[0, 0, :min(w, 256), 0] = np.arange(min(w, 256), dtype=np.uint8)     # every byte value at least once
+    return x
+
+
+def _bits(a):
+    return np.ascontiguousarray(a, dtype=np.float32).view(np.uint32)
+
+
+# ---- CPU: pin the oracle --------------------------------------------------------------------------------------------
+def test_oracle_equals_torch_totensor_and_normalize():
+    x = _frames(2, 8, 256)
+    t = torch.from_numpy(x).permute(0, 3, 1, 2).to(torch.float32).div(255)            # ToTensor
+    assert np.array_equal(_bits(O.to_tensor(x)), _bits(t.numpy()))
+    mean = torch.tensor(O.IMG_MEAN, dtype=torch.float32)[None, :, None, None]
+    std = torch.tensor(O.IMG_STD, dtype=torch.float32)[None, :, None, None]
+    t = t.clone().sub_(mean).div_(std)                                                 # Normalize
+    assert np.array_equal(_bits(O.preprocess_u8(x, True)), _bits(t.numpy()))
+
+
+def test_oracle_float64_loader_route_rounds_to_the_same_fp32():
+    x = np.zeros((1, 1, 256, 3), np.uint8)
+    x[0, 0, :, :] = np.arange(256, dtype=np.uint8)[:, None]
+    assert np.array_equal(_bits(O.video_loader_route(x)), _bits(O.preprocess_u8(x, True)))
+
+
+def test_oracle_known_answers():
+    x = np.array([[[[0, 255, 51]]]], np.uint8)
+    y = O.preprocess_u8(x, False)
+    assert y.shape == (1, 3, 1, 1)
+    assert y[0, 0, 0, 0] == 0.0 and y[0, 1, 0, 0] == 1.0 and y[0, 2, 0, 0] == np.float32(0.2)
+    z = O.preprocess_u8(x, True)
+    assert z[0, 0, 0, 0] == np.float32(np.float32(0.0 - np.float32(0.485)) / np.float32(0.229))
+    assert z[0, 1, 0, 0] == np.float32(np.float32(np.float32(1.0) - np.float32(0.456)) / np.float32(0.224))
+
+
+def test_wrapper_rejects_bad_inputs_without_a_gpu():
+    from sam2_opt_b200 import ops
+    with pytest.raises(ValueError):
+        ops.preprocess_u8(torch.zeros(4, 4, 3, dtype=torch.uint8))          # host tensor
+    with pytest.raises(ValueError):
+        ops.preprocess_u8(torch.zeros(1, 4, 4, 3, dtype=torch.float32))
+
+
+# ---- GPU: parity through the C ABI --------------------------------------------------------------------------------
+@pytest.mark.gpu
+@pytest.mark.parametrize("n,h,w", [(1, 1024, 1024), (3, 64, 260), (2, 5, 4), (1, 1, 4)])
+@pytest.mark.parametrize("normalise", [False, True])
+def test_preprocess_u8_bit_exact(n, h, w, normalise):
+    from sam2_opt_b200 import ops
+    x = _frames(n, h, w, seed=n * 7 + h)
+    y = ops.preprocess_u8(torch.from_numpy(x).cuda(), normalise)
+    assert y.shape == (n, 3, h, w) and y.dtype == torch.float32
+    assert np.array_equal(_bits(y.cpu().numpy()), _bits(O.preprocess_u8(x, normalise)))
+
+
+@pytest.mark.gpu
+def test_preprocess_u8_single_frame_and_width_error():
+    from sam2_opt_b200 import ops
+    x = _frames(1, 16, 16, seed=3)
+    y = ops.preprocess_u8(torch.from_numpy(x[0]).cuda())
+    assert np.array_equal(_bits(y.cpu().numpy()), _bits(O.preprocess_u8(x, False)))
+    with pytest.raises(RuntimeError, match="multiple of 4"):
+        ops.preprocess_u8(torch.zeros(1, 8, 6, 3, dtype=torch.uint8, device="cuda"))
+
+
+@pytest.mark.gpu
+def test_predictor_prep_paths_use_the_op_and_match_the_oracle():
+    """_prep_image / init_state on 1024x1024 uint8 frames == oracle (un-normalised for the image predictor, which
+    normalises inside the engine; normalised for the video loader route)."""
+    from sam2_opt_b200.predictor import SAM2VideoPredictor
+    from oracle import sam2_oracle
+    vp = SAM2VideoPredictor(sam2_oracle.make_weights(0))
+    x = _frames(2, 1024, 1024, seed=11)
+    a = vp._prep_image(x[0])
+    assert np.array_equal(_bits(a.cpu().numpy()), _bits(O.preprocess_u8(x[:1], False)))
+    st = vp.init_state([x[0], x[1]])
+    assert np.array_equal(_bits(st["images"].cpu().numpy()), _bits(O.video_loader_route(x)))
