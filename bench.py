@@ -204,6 +204,20 @@ def main():
     h2d = img_host.numel() * 4
     d2h = sum(o.numel() * 4 for o in outs_host)
 
+    # ---- the same from raw uint8 frames (what set_image_batch receives): bytes over PCIe, ToTensor/Normalize on the device
+    raw_host = torch.randint(0, 256, (B, 1024, 1024, 3), dtype=torch.uint8, generator=torch.Generator().manual_seed(7 + rank)).pin_memory()
+    for _ in range(2):
+        outs_host = eng.image_encode_host_u8(raw_host, False, outs_host)
+    barrier()
+    u0 = time.perf_counter()
+    for _ in range(args.steps):
+        outs_host = eng.image_encode_host_u8(raw_host, False, outs_host)
+    barrier()
+    u_ms = torch.tensor([(time.perf_counter() - u0) * 1e3], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(u_ms, op=dist.ReduceOp.MAX)
+    e2e_u8_value = world * B * args.steps / (u_ms.item() / 1e3)
+
     # ---- roofline of the dominant kernel (tcgen05 GEMM): live CUDA-event pairs around every launch of one more step
     roof = None
     if rank == 0:
@@ -284,6 +298,8 @@ def main():
             "clocks": clk.summary(), "gpu_launches": int(launches),
             "e2e": {"value": e2e_value, "unit": "images/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "api": "Engine.image_encode_host -> sam2b_image_encode_host (pinned host in/out)"},
+            "e2e_u8_frames": {"value": e2e_u8_value, "unit": "images/s", "h2d_bytes_per_step": raw_host.numel(), "d2h_bytes_per_step": d2h,
+                              "api": "Engine.image_encode_host_u8 -> sam2b_image_encode_host_u8 (raw uint8 HWC frames, pinned; host wall clock)"},
             "roofline": roof, "cpu_baseline": cpu, "video": video,
         }))
     if world > 1:

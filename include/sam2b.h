@@ -52,6 +52,12 @@ int sam2b_image_encode(sam2b_handle h, const float* img, int n, int normalised, 
  * in micro-batches overlapped with compute; returns after the stream has been synchronised. */
 int sam2b_image_encode_host(sam2b_handle h, const float* img_host, int n, int normalised, int add_no_mem_embed,
                             float* fpn0_host, float* fpn1_host, float* fpn2_host, void* stream);
+/* Same, from raw frames: hwc_u8_host is HOST uint8 [n][1024][1024][3] (what set_image / set_image_batch receive,
+ * sam2_image_predictor.py:173-196, already at the model resolution).  The frames cross PCIe as bytes (a quarter of the fp32
+ * traffic) and ToTensor -> Normalize (sam2/utils/transforms.py:27-46) runs on the device, bit-identical to the reference;
+ * the outputs equal sam2b_image_encode_host(normalised=1) on the reference-preprocessed frames bit for bit. */
+int sam2b_image_encode_host_u8(sam2b_handle h, const void* hwc_u8_host, int n, int add_no_mem_embed,
+                               float* fpn0_host, float* fpn1_host, float* fpn2_host, void* stream);
 
 /* ---- E3: 4-layer MemoryAttention ----
  * curr, curr_pos dev [4096,n,256]; memory, memory_pos dev [L,4096,n,64]; memory_exclude, memory_pos_exclude dev [P,n,64]

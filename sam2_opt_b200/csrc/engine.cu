@@ -730,11 +730,15 @@ int sam2b_image_encode(sam2b_handle h, const float* img, int n, int normalised, 
   return 0;
 }
 
-int sam2b_image_encode_host(sam2b_handle h, const float* img_host, int n, int normalised, int add_no_mem_embed,
-                            float* fpn0_host, float* fpn1_host, float* fpn2_host, void* stream) {
+// Host-buffer encode.  `u8` = 0: img_host is fp32 [n][3][1024][1024]; `u8` = 1: img_host is uint8 [n][1024][1024][3] (raw frames),
+// uploaded as bytes (a quarter of the PCIe traffic) and converted on the device by preprocess_u8_hwc (/255, then mean/std).
+static int image_encode_host_impl(sam2b_handle h, const void* img_host_v, int u8, int n, int normalised, int add_no_mem_embed,
+                                  float* fpn0_host, float* fpn1_host, float* fpn2_host, void* stream) {
   if (!h || !h->finalized) { set_error("sam2b_image_encode_host: engine not finalized"); return 1; }
-  if (n <= 0 || !img_host || !fpn0_host || !fpn1_host || !fpn2_host) { set_error("sam2b_image_encode_host: bad arguments"); return 1; }
+  if (n <= 0 || !img_host_v || !fpn0_host || !fpn1_host || !fpn2_host) { set_error("sam2b_image_encode_host: bad arguments"); return 1; }
   CUDA_OK(cudaSetDevice(h->device));
+  const float* img_host = reinterpret_cast<const float*>(img_host_v);
+  const uint8_t* img_host_u8 = reinterpret_cast<const uint8_t*>(img_host_v);
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   // double-buffered staging: uploads run on copy_stream, downloads on copy_stream2, compute on `st`
   const size_t in_sz = (size_t)3 * 1024 * 1024, o0 = (size_t)32 * 65536, o1 = (size_t)64 * 16384, o2 = (size_t)256 * 4096;
@@ -747,6 +751,11 @@ int sam2b_image_encode_host(sam2b_handle h, const float* img_host, int n, int no
     TRY(ws_get_t(h, names[s][2], o1 * kMaxMicroBatch, &f1[s]));
     TRY(ws_get_t(h, names[s][3], o2 * kMaxMicroBatch, &f2[s]));
   }
+  uint8_t* raw[2] = {nullptr, nullptr};
+  if (u8) {
+    TRY(ws_get_t(h, "h_raw0", in_sz * kMaxMicroBatch, &raw[0]));
+    TRY(ws_get_t(h, "h_raw1", in_sz * kMaxMicroBatch, &raw[1]));
+  }
   cudaStream_t cs = h->copy_stream, ds = h->copy_stream2;
   // ev[0..1]: input slot s uploaded; ev[2..3]: compute on slot s done; ev[4..5]: outputs of slot s downloaded;
   // ev[8..9], ev[10..11]: fpn0 / fpn1 of slot s complete (early, see image_encode_mb)
@@ -758,9 +767,11 @@ int sam2b_image_encode_host(sam2b_handle h, const float* img_host, int n, int no
     const int s = it & 1;
     const int mb = (n - i0) < kMaxMicroBatch ? (n - i0) : kMaxMicroBatch;
     if (it >= 2) CUDA_OK(cudaStreamWaitEvent(cs, h->ev[2 + s], 0));       // slot's previous compute has consumed the input
-    CUDA_OK(cudaMemcpyAsync(in[s], img_host + (size_t)i0 * in_sz, in_sz * mb * 4, cudaMemcpyHostToDevice, cs));
+    if (u8) CUDA_OK(cudaMemcpyAsync(raw[s], img_host_u8 + (size_t)i0 * in_sz, in_sz * mb, cudaMemcpyHostToDevice, cs));
+    else CUDA_OK(cudaMemcpyAsync(in[s], img_host + (size_t)i0 * in_sz, in_sz * mb * 4, cudaMemcpyHostToDevice, cs));
     CUDA_OK(cudaEventRecord(h->ev[s], cs));
     CUDA_OK(cudaStreamWaitEvent(st, h->ev[s], 0));
+    if (u8) TRY(preprocess_u8_hwc(raw[s], in[s], mb, 1024, 1024, 1, st));
     if (it >= 2) CUDA_OK(cudaStreamWaitEvent(st, h->ev[4 + s], 0));       // slot's previous outputs have left the device
     cudaEvent_t early[2] = {h->ev[8 + s], h->ev[10 + s]};
     TRY(image_encode_mb(h, in[s], mb, normalised, add_no_mem_embed, f0[s], f1[s], f2[s], st, early));
@@ -777,6 +788,16 @@ int sam2b_image_encode_host(sam2b_handle h, const float* img_host, int n, int no
   CUDA_OK(cudaStreamSynchronize(cs));
   CUDA_OK(cudaStreamSynchronize(st));
   return 0;
+}
+
+int sam2b_image_encode_host(sam2b_handle h, const float* img_host, int n, int normalised, int add_no_mem_embed,
+                            float* fpn0_host, float* fpn1_host, float* fpn2_host, void* stream) {
+  return image_encode_host_impl(h, img_host, 0, n, normalised, add_no_mem_embed, fpn0_host, fpn1_host, fpn2_host, stream);
+}
+
+int sam2b_image_encode_host_u8(sam2b_handle h, const void* hwc_u8_host, int n, int add_no_mem_embed,
+                               float* fpn0_host, float* fpn1_host, float* fpn2_host, void* stream) {
+  return image_encode_host_impl(h, hwc_u8_host, 1, n, 1, add_no_mem_embed, fpn0_host, fpn1_host, fpn2_host, stream);
 }
 
 int sam2b_memory_attention(sam2b_handle h, const float* curr, const float* curr_pos, const float* memory,

@@ -93,6 +93,23 @@ class Engine:
                        "image_encode_host")
         return out
 
+    def image_encode_host_u8(self, frames: torch.Tensor, add_no_mem_embed: bool, out=None):
+        """Raw HOST frames uint8 [n,1024,1024,3] (pinned recommended) -> the three HOST feature levels.  The frames are
+        uploaded as bytes and ToTensor -> Normalize (ref: sam2/utils/transforms.py:27-46) runs on the device."""
+        if frames.is_cuda or frames.dtype != torch.uint8 or not frames.is_contiguous() or frames.dim() != 4 \
+                or tuple(frames.shape[1:]) != (1024, 1024, 3):
+            raise ValueError(f"image_encode_host_u8 expects a contiguous host uint8 [n,1024,1024,3] tensor, got {frames.dtype} {tuple(frames.shape)}")
+        n = frames.shape[0]
+        if out is None:
+            out = (torch.empty((n, 32, 256, 256), dtype=torch.float32).pin_memory(),
+                   torch.empty((n, 64, 128, 128), dtype=torch.float32).pin_memory(),
+                   torch.empty((n, 256, 64, 64), dtype=torch.float32).pin_memory())
+        with self._lock:
+            _lib.check(self.lib.sam2b_image_encode_host_u8(self._h, _ptr(frames), n, int(add_no_mem_embed),
+                                                           _ptr(out[0]), _ptr(out[1]), _ptr(out[2]), _stream()),
+                       "image_encode_host_u8")
+        return out
+
     # -- E3 --------------------------------------------------------------------------------------------------
     def memory_attention(self, curr, memory, curr_pos, memory_pos, memory_exclude=None, memory_pos_exclude=None):
         curr, curr_pos = _f32c(curr, "curr"), _f32c(curr_pos, "curr_pos")

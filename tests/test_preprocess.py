@@ -88,3 +88,26 @@ def test_predictor_prep_paths_use_the_op_and_match_the_oracle():
     assert np.array_equal(_bits(a.cpu().numpy()), _bits(O.preprocess_u8(x[:1], False)))
     st = vp.init_state([x[0], x[1]])
     assert np.array_equal(_bits(st["images"].cpu().numpy()), _bits(O.video_loader_route(x)))
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("n", [1, 18])
+def test_image_encode_host_u8_equals_the_fp32_host_entry_bit_for_bit(n):
+    """sam2b_image_encode_host_u8 (raw frames over PCIe, ToTensor -> Normalize on the device) == sam2b_image_encode_host on
+    the frames the oracle preprocessed (n = 18: two micro-batch slots, the second ragged)."""
+    from oracle import sam2_oracle
+    from sam2_opt_b200.engine import Engine
+    e = Engine(sam2_oracle.make_weights(0))
+    try:
+        rng = np.random.default_rng(21)
+        base = rng.integers(0, 256, size=(2, 64, 64, 3), dtype=np.uint8)
+        x = np.stack([np.kron(base[i % 2], np.ones((16, 16, 1), np.uint8)) + np.uint8(i) for i in range(n)])   # blocky 1024^2 frames
+        ref = e.image_encode_host(torch.from_numpy(O.preprocess_u8(x, True)).pin_memory(), True, False)
+        ref = [t.clone() for t in ref]
+        got = e.image_encode_host_u8(torch.from_numpy(x).pin_memory(), False)
+        for a, b in zip(got, ref):
+            assert torch.equal(a, b)
+        with pytest.raises(ValueError):
+            e.image_encode_host_u8(torch.zeros(1, 512, 512, 3, dtype=torch.uint8), False)
+    finally:
+        e.release()
