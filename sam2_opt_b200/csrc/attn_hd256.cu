@@ -425,11 +425,11 @@ int flash_attention_hd256(const bf16* q, long q_batch_stride, const bf16* k, lon
   CUtensorMap mq, mk, mv;
   if (fa256_map(&mq, q, Tq, n, q_batch_stride, TQ) || fa256_map(&mk, k, Lk, n, k_batch_stride, TK) ||
       fa256_map(&mv, v, Lk, n, v_batch_stride, TK)) return 1;
-  static bool attr = false;
-  if (!attr) {
+  static PerDeviceFlag attr;
+  if (!attr.is_set()) {
     cudaError_t e = cudaFuncSetAttribute(flash_attn_hd256_tcgen05_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM);
     if (e != cudaSuccess) { set_error("cudaFuncSetAttribute(flash_attn_hd256): %s", cudaGetErrorString(e)); return 1; }
-    attr = true;
+    attr.set();
   }
   Fa256Params p;
   p.o_part = o_part; p.ml_part = ml_part; p.n = n; p.Tq = Tq; p.Lk = (int)Lk;

@@ -418,11 +418,11 @@ int flash_attention_hd72(const bf16* qkv, bf16* out, int B, int H, int W, int he
                      CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) { set_error("flash_attention_hd72: cuTensorMapEncodeTiled failed (%d) map %d", (int)r, i); return 1; }
   }
-  static bool attr = false;
-  if (!attr) {
+  static PerDeviceFlag attr;
+  if (!attr.is_set()) {
     cudaError_t e = cudaFuncSetAttribute(flash_attn_hd72_tcgen05_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM);
     if (e != cudaSuccess) { set_error("cudaFuncSetAttribute(flash_attn): %s", cudaGetErrorString(e)); return 1; }
-    attr = true;
+    attr.set();
   }
   FaParams p;
   p.out = out; p.B = B; p.H = H; p.W = W; p.heads = heads; p.ws = ws;

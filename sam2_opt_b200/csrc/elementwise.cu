@@ -329,10 +329,10 @@ __global__ void __launch_bounds__(512) softmax_rows_kernel(const float* __restri
 int softmax_rows(const float* s, long lds, bf16* p, long ldp, long rows, int cols, cudaStream_t stream) {
   const size_t smem = (size_t)cols * 4 + 16;
   if (smem > 200 * 1024 || (lds % 4) || (ldp % 2) || ldp < cols) { set_error("softmax_rows: unsupported cols=%d lds=%ld ldp=%ld", cols, lds, ldp); return 1; }
-  static bool attr = false;
-  if (!attr) {
+  static PerDeviceFlag attr;
+  if (!attr.is_set()) {
     cudaFuncSetAttribute(softmax_rows_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
-    attr = true;
+    attr.set();
   }
   ProfRange pr(stream, "softmax_rows", 0, (double)rows * cols * 6.0);
   softmax_rows_kernel<<<(unsigned)rows, 512, smem, stream>>>(s, lds, p, ldp, cols);

@@ -61,6 +61,24 @@ int num_sms() {
   } while (0)
 #define TRY(expr) do { if (expr) return 1; } while (0)
 
+// Makes `dev` the calling thread's current device for the lifetime of the guard and restores the previous one afterwards,
+// so that a call on an engine of another GPU does not silently change the caller's (and torch's) current device.
+struct DeviceGuard {
+  int prev = -1;
+  bool switched = false;
+  cudaError_t err = cudaSuccess;
+  explicit DeviceGuard(int dev) {
+    err = cudaGetDevice(&prev);
+    if (err == cudaSuccess && prev != dev) { err = cudaSetDevice(dev); switched = (err == cudaSuccess); }
+  }
+  ~DeviceGuard() { if (switched) cudaSetDevice(prev); }
+  DeviceGuard(const DeviceGuard&) = delete;
+  DeviceGuard& operator=(const DeviceGuard&) = delete;
+};
+#define ENTER_DEVICE(dev)          \
+  DeviceGuard device_guard__(dev); \
+  CUDA_OK(device_guard__.err)
+
 struct Tensor {
   float* f32 = nullptr;
   bf16* b16 = nullptr;
@@ -150,7 +168,7 @@ static const float* W32(sam2b_engine* e, const std::string& n) { return e->w.at(
 static const bf16* W16(sam2b_engine* e, const std::string& n) { return e->w.at(n).b16; }
 
 static int finalize(sam2b_engine* e) {
-  CUDA_OK(cudaSetDevice(e->device));
+  ENTER_DEVICE(e->device);
   const std::string t = "image_encoder.trunk.";
   for (size_t i = 0; i < e->blocks.size(); ++i) {
     const std::string b = t + "blocks." + std::to_string(i) + ".";
@@ -669,7 +687,7 @@ int sam2b_create(int device, sam2b_handle* out) {
   cudaDeviceProp prop;
   CUDA_OK(cudaGetDeviceProperties(&prop, device));
   if (prop.major != 10) { set_error("sam2b_create: device %d is sm_%d%d; this library is built for sm_100a only", device, prop.major, prop.minor); return 1; }
-  CUDA_OK(cudaSetDevice(device));
+  ENTER_DEVICE(device);
   sam2b_engine* e = new sam2b_engine();
   e->device = device;
   build_block_cfgs(e->blocks);
@@ -682,7 +700,7 @@ int sam2b_create(int device, sam2b_handle* out) {
 
 int sam2b_destroy(sam2b_handle h) {
   if (!h) return 0;
-  cudaSetDevice(h->device);
+  DeviceGuard guard(h->device);
   cudaDeviceSynchronize();
   for (auto& kv : h->w) { if (kv.second.f32) cudaFree(kv.second.f32); if (kv.second.b16) cudaFree(kv.second.b16); }
   for (auto& kv : h->ws) if (kv.second.p) cudaFree(kv.second.p);
@@ -695,7 +713,7 @@ int sam2b_destroy(sam2b_handle h) {
 
 int sam2b_set_tensor(sam2b_handle h, const char* name, const float* dev_data, const int64_t* shape, int ndim) {
   if (!h || !name || !dev_data) { set_error("sam2b_set_tensor: null argument"); return 1; }
-  CUDA_OK(cudaSetDevice(h->device));
+  ENTER_DEVICE(h->device);
   Tensor& t = h->w[name];
   int64_t numel = 1;
   std::vector<int64_t> shp;
@@ -719,7 +737,7 @@ int sam2b_image_encode(sam2b_handle h, const float* img, int n, int normalised, 
                        float* fpn1, float* fpn2, void* stream) {
   if (!h || !h->finalized) { set_error("sam2b_image_encode: engine not finalized"); return 1; }
   if (n <= 0 || !img || !fpn0 || !fpn1 || !fpn2) { set_error("sam2b_image_encode: bad arguments (n=%d)", n); return 1; }
-  CUDA_OK(cudaSetDevice(h->device));
+  ENTER_DEVICE(h->device);
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   const int kMaxMicroBatch = max_micro_batch();
   for (int i0 = 0; i0 < n; i0 += kMaxMicroBatch) {
@@ -736,7 +754,7 @@ static int image_encode_host_impl(sam2b_handle h, const void* img_host_v, int u8
                                   float* fpn0_host, float* fpn1_host, float* fpn2_host, void* stream) {
   if (!h || !h->finalized) { set_error("sam2b_image_encode_host: engine not finalized"); return 1; }
   if (n <= 0 || !img_host_v || !fpn0_host || !fpn1_host || !fpn2_host) { set_error("sam2b_image_encode_host: bad arguments"); return 1; }
-  CUDA_OK(cudaSetDevice(h->device));
+  ENTER_DEVICE(h->device);
   const float* img_host = reinterpret_cast<const float*>(img_host_v);
   const uint8_t* img_host_u8 = reinterpret_cast<const uint8_t*>(img_host_v);
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
@@ -809,7 +827,7 @@ int sam2b_memory_attention(sam2b_handle h, const float* curr, const float* curr_
   // in L, so several conditioning frames (L up to 16) are accepted as the reference's torch path accepts them
   if (L < 1 || L > 16 || P < 0 || P > 64 || (P % 4)) { set_error("sam2b_memory_attention: L=%d must be in [1,16], P=%d in [0,64] and a multiple of 4", L, P); return 1; }
   if (P > 0 && (!memory_exclude || !memory_pos_exclude)) { set_error("sam2b_memory_attention: P=%d but memory_exclude is NULL", P); return 1; }
-  CUDA_OK(cudaSetDevice(h->device));
+  ENTER_DEVICE(h->device);
   return memory_attention_mb(h, curr, curr_pos, memory, memory_pos, L, memory_exclude, memory_pos_exclude, P, n, n, out,
                              reinterpret_cast<cudaStream_t>(stream));
 }
@@ -817,7 +835,7 @@ int sam2b_memory_attention(sam2b_handle h, const float* curr, const float* curr_
 int sam2b_memory_encode(sam2b_handle h, const float* pix_feat, const float* masks, int n, float* out_x, void* stream) {
   if (!h || !h->finalized) { set_error("sam2b_memory_encode: engine not finalized"); return 1; }
   if (!pix_feat || !masks || !out_x || n <= 0) { set_error("sam2b_memory_encode: null/empty argument"); return 1; }
-  CUDA_OK(cudaSetDevice(h->device));
+  ENTER_DEVICE(h->device);
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   const int kMaxMicroBatch = 16;
   for (int i0 = 0; i0 < n; i0 += kMaxMicroBatch) {

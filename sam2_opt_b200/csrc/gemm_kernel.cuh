@@ -453,12 +453,13 @@ static int launch_gemm(const GemmArgs& a, cudaStream_t stream) {
   static_assert(Cfg::STAGES >= 2, "pipeline too shallow");
   if (Cfg::STAGES < 3) { set_error("gemm<%d,%d,%d,%d>: only %d smem stages fit; not a supported combination", BN, MODE, NCTA, EW, Cfg::STAGES); return 1; }
   static_assert(NCTA == 1 || (BN % 32 == 0 && (BN / 2) % 8 == 0), "a CTA pair splits the B tile in two halves of whole swizzle atoms");
-  static int max_pairs = 0;       // 0: attributes not set yet
+  static int max_pairs = 0;       // resident CTAs / CTA pairs of this instantiation (identical GPUs assumed within a process)
+  static PerDeviceFlag attr;      // attributes set on the current device
   auto kern = gemm_bf16_tcgen05_kernel<BN, MODE, NCTA, EW>;
-  if (!max_pairs) {
+  if (!attr.is_set()) {
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM);
     if (e != cudaSuccess) { set_error("cudaFuncSetAttribute(gemm<%d,%d>): %s", BN, NCTA, cudaGetErrorString(e)); return 1; }
-    max_pairs = num_sms() / NCTA;
+    int mp = num_sms() / NCTA;
     if (NCTA == 2) {
       cudaLaunchConfig_t qc = {};
       qc.gridDim = dim3(num_sms() / 2 * 2); qc.blockDim = dim3(NUM_THREADS); qc.dynamicSmemBytes = Cfg::SMEM;
@@ -467,9 +468,11 @@ static int launch_gemm(const GemmArgs& a, cudaStream_t stream) {
       qc.attrs = qa; qc.numAttrs = 1;
       int n_clusters = 0;
       e = cudaOccupancyMaxActiveClusters(&n_clusters, kern, &qc);
-      if (e != cudaSuccess || n_clusters <= 0) { set_error("cudaOccupancyMaxActiveClusters(gemm<%d,2>): %s (%d)", BN, cudaGetErrorString(e), n_clusters); max_pairs = 0; return 1; }
-      if (n_clusters < max_pairs) max_pairs = n_clusters;
+      if (e != cudaSuccess || n_clusters <= 0) { set_error("cudaOccupancyMaxActiveClusters(gemm<%d,2>): %s (%d)", BN, cudaGetErrorString(e), n_clusters); return 1; }
+      if (n_clusters < mp) mp = n_clusters;
     }
+    max_pairs = mp;
+    attr.set();
   }
   CUtensorMap ta, tb, tc, tr, tc2;
   if (make_tmap(&ta, a.A, a.M, a.K, a.lda, a.batch, a.a_batch_stride, BM)) return 1;

@@ -243,8 +243,8 @@ int mask_ds_stage(int stage, const float* in, float* out, int n, int H_in, const
   } else if (stage == 3) {
     ProfRange pr(stream, nm, 2.0 * pix * 9216, (double)pix * (256.0 + 256.0));
     const size_t smem = (9216 + 192) * sizeof(float);
-    static bool attr = false;
-    if (!attr) { cudaFuncSetAttribute(mask_ds3_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); attr = true; }
+    static PerDeviceFlag attr;
+    if (!attr.is_set()) { cudaFuncSetAttribute(mask_ds3_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); attr.set(); }
     long blocks = (pix * 4 + 255) / 256; if (blocks > (long)num_sms() * 4) blocks = (long)num_sms() * 4;
     mask_ds3_kernel<<<(unsigned)blocks, 256, smem, stream>>>(reinterpret_cast<const float4*>(in), reinterpret_cast<float4*>(out), n, H_in, w, b, ln_w, ln_b);
   } else {

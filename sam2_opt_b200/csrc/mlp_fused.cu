@@ -338,11 +338,11 @@ static int fm_map(CUtensorMap* m, const bf16* ptr, long rows, long cols, long ld
 template <int C>
 static int launch_mlp_fused(const CUtensorMap& ma, const CUtensorMap& m1, const CUtensorMap& m2, const FusedMlpParams& p, cudaStream_t stream) {
   using K = fm::Cfg<C>;
-  static bool attr = false;
-  if (!attr) {
+  static PerDeviceFlag attr;
+  if (!attr.is_set()) {
     cudaError_t e = cudaFuncSetAttribute(mlp_fused_kernel<C>, cudaFuncAttributeMaxDynamicSharedMemorySize, K::SMEM);
     if (e != cudaSuccess) { set_error("cudaFuncSetAttribute(mlp_fused<%d>): %s", C, cudaGetErrorString(e)); return 1; }
-    attr = true;
+    attr.set();
   }
   const int grid = p.num_tiles < num_sms() ? p.num_tiles : num_sms();
   mlp_fused_kernel<C><<<grid, fm::THREADS, K::SMEM, stream>>>(ma, m1, m2, p);

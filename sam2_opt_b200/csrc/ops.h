@@ -5,6 +5,8 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include <atomic>
+
 namespace sam2b {
 
 typedef __nv_bfloat16 bf16;
@@ -12,6 +14,18 @@ typedef __nv_bfloat16 bf16;
 void set_error(const char* fmt, ...);
 const char* get_error();
 int num_sms();
+// "This kernel's launch attributes have been set on the current device."  cudaFuncSetAttribute applies to the current device
+// only, so a process-wide `static bool` would leave the second GPU of a multi-device process without its opt-in shared
+// memory.  Two host threads may both find the flag clear and both set the (idempotent) attribute; neither launches before
+// its own call has returned.
+class PerDeviceFlag {
+ public:
+  bool is_set() const { return (bits_.load(std::memory_order_acquire) >> cur()) & 1ull; }
+  void set() { bits_.fetch_or(1ull << cur(), std::memory_order_release); }
+ private:
+  static int cur() { int d = 0; cudaGetDevice(&d); return d & 63; }
+  std::atomic<unsigned long long> bits_{0};
+};
 // counts kernel launches made by this library (bench.py's gpu_launches)
 extern unsigned long long g_launch_count;
 

@@ -411,11 +411,11 @@ int window_attention_hd72(const bf16* qkv, bf16* out, int B, int H, int W, int h
   p.scale_log2 = 1.4426950408889634f / sqrtf((float)HD);
   const int nwin = (H / ws) * (W / ws);
   const size_t smem = 5 * 64 * LDS * sizeof(bf16);
-  static bool attr = false;
-  if (!attr) {
+  static PerDeviceFlag attr;
+  if (!attr.is_set()) {
     cudaFuncSetAttribute(window_attn_hd72_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     cudaFuncSetAttribute(window_attn_hd72_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    attr = true;
+    attr.set();
   }
   char nm[96];
   if (g_prof_on) snprintf(nm, sizeof(nm), "attn h%d heads%d ws%d pool%d b%d", H, heads, ws, q_pool, B);
@@ -427,11 +427,11 @@ int window_attention_hd72(const bf16* qkv, bf16* out, int B, int H, int W, int h
     const int tiles_per_img = priv ? nwin / 4 : nwin;
     const long n_items = (long)tiles_per_img * heads * B;
     const size_t smem2 = 6 * 64 * LDS * sizeof(bf16);
-    static bool attr2 = false;
-    if (!attr2) {
+    static PerDeviceFlag attr2;
+    if (!attr2.is_set()) {
       cudaFuncSetAttribute(window_attn_hd72_stream_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2);
       cudaFuncSetAttribute(window_attn_hd72_stream_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2);
-      attr2 = true;
+      attr2.set();
     }
     const long max_ctas = (long)num_sms() * 3;
     const int grid = (int)(n_items < max_ctas ? n_items : max_ctas);

@@ -42,6 +42,10 @@ class Engine:
         self._upload(state_dict)
         self._pos_cache = {}
 
+    def _stream(self):
+        """the caller's current stream ON THE ENGINE'S DEVICE (which need not be the calling thread's current device)"""
+        return C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
+
     # -- weights ---------------------------------------------------------------------------------------------
     def _upload(self, sd: Dict[str, torch.Tensor]):
         with torch.no_grad():
@@ -76,7 +80,7 @@ class Engine:
         f2 = torch.empty((n, 256, 64, 64), device=self.device, dtype=torch.float32)
         with self._lock:
             _lib.check(self.lib.sam2b_image_encode(self._h, _ptr(img), n, int(normalised), int(add_no_mem_embed),
-                                                   _ptr(f0), _ptr(f1), _ptr(f2), _stream()), "image_encode")
+                                                   _ptr(f0), _ptr(f1), _ptr(f2), self._stream()), "image_encode")
         return f0, f1, f2
 
     def image_encode_host(self, img: torch.Tensor, normalised: bool, add_no_mem_embed: bool, out=None):
@@ -89,7 +93,7 @@ class Engine:
                    torch.empty((n, 256, 64, 64), dtype=torch.float32).pin_memory())
         with self._lock:
             _lib.check(self.lib.sam2b_image_encode_host(self._h, _ptr(img), n, int(normalised), int(add_no_mem_embed),
-                                                        _ptr(out[0]), _ptr(out[1]), _ptr(out[2]), _stream()),
+                                                        _ptr(out[0]), _ptr(out[1]), _ptr(out[2]), self._stream()),
                        "image_encode_host")
         return out
 
@@ -106,7 +110,7 @@ class Engine:
                    torch.empty((n, 256, 64, 64), dtype=torch.float32).pin_memory())
         with self._lock:
             _lib.check(self.lib.sam2b_image_encode_host_u8(self._h, _ptr(frames), n, int(add_no_mem_embed),
-                                                           _ptr(out[0]), _ptr(out[1]), _ptr(out[2]), _stream()),
+                                                           _ptr(out[0]), _ptr(out[1]), _ptr(out[2]), self._stream()),
                        "image_encode_host_u8")
         return out
 
@@ -122,7 +126,7 @@ class Engine:
         with self._lock:
             _lib.check(self.lib.sam2b_memory_attention(
                 self._h, _ptr(curr), _ptr(curr_pos), _ptr(memory), _ptr(memory_pos), L,
-                _ptr(memory_exclude if P else None), _ptr(memory_pos_exclude if P else None), P, n, _ptr(out), _stream()),
+                _ptr(memory_exclude if P else None), _ptr(memory_pos_exclude if P else None), P, n, _ptr(out), self._stream()),
                 "memory_attention")
         return out
 
@@ -132,7 +136,7 @@ class Engine:
         n = pix_feat.shape[0]
         x = torch.empty((n, 64, 64, 64), device=self.device, dtype=torch.float32)
         with self._lock:
-            _lib.check(self.lib.sam2b_memory_encode(self._h, _ptr(pix_feat), _ptr(masks), n, _ptr(x), _stream()),
+            _lib.check(self.lib.sam2b_memory_encode(self._h, _ptr(pix_feat), _ptr(masks), n, _ptr(x), self._stream()),
                        "memory_encode")
         return x, self.position_encoding(64, 64, n)
 
