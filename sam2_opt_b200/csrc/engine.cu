@@ -16,7 +16,7 @@
 namespace sam2b {
 
 static thread_local char g_err[1024] = "";
-unsigned long long g_launch_count = 0;
+std::atomic<unsigned long long> g_launch_count{0};
 
 void set_error(const char* fmt, ...) {
   va_list ap;
@@ -674,7 +674,7 @@ extern "C" {
 
 const char* sam2b_last_error(void) { return get_error(); }
 const char* sam2b_version(void) { return "sam2b 0.1 (sm_100a)"; }
-unsigned long long sam2b_launch_count(void) { return g_launch_count; }
+unsigned long long sam2b_launch_count(void) { return g_launch_count.load(std::memory_order_relaxed); }
 
 int sam2b_create(int device, sam2b_handle* out) {
   if (!out) { set_error("sam2b_create: null out"); return 1; }

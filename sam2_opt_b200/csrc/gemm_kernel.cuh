@@ -520,7 +520,7 @@ static int launch_gemm(const GemmArgs& a, cudaStream_t stream) {
     cfg.attrs = at; cfg.numAttrs = 1;
     cudaError_t e = cudaLaunchKernelEx(&cfg, kern, ta, tb, tc, tr, tc2, p);
     if (e != cudaSuccess) { set_error("cudaLaunchKernelEx(gemm<%d,2>): %s", BN, cudaGetErrorString(e)); return 1; }
-    ++g_launch_count;
+    g_launch_count.fetch_add(1, std::memory_order_relaxed);
   } else {
     kern<<<grid, NUM_THREADS, Cfg::SMEM, stream>>>(ta, tb, tc, tr, tc2, p);
     SAM2B_CHECK_LAUNCH("gemm_bf16_tcgen05");

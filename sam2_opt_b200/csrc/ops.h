@@ -27,11 +27,11 @@ class PerDeviceFlag {
   std::atomic<unsigned long long> bits_{0};
 };
 // counts kernel launches made by this library (bench.py's gpu_launches)
-extern unsigned long long g_launch_count;
+extern std::atomic<unsigned long long> g_launch_count;   // several host threads may drive one library (video_multi_thread.py)
 
 #define SAM2B_CHECK_LAUNCH(name)                                              \
   do {                                                                        \
-    ++::sam2b::g_launch_count;                                                \
+    ::sam2b::g_launch_count.fetch_add(1, std::memory_order_relaxed);         \
     cudaError_t e__ = cudaGetLastError();                                     \
     if (e__ != cudaSuccess) {                                                 \
       ::sam2b::set_error("%s launch failed: %s", name, cudaGetErrorString(e__)); \
