@@ -114,6 +114,13 @@ int sam2b_op_connected_components(const void* mask_u8, int32_t* labels, int32_t*
  * with normalise != 0, (x / 255 - mean) / std with the ImageNet constants of transforms.py:27-28.  Same IEEE operations in
  * the same order as the reference: bit-exact.  w must be a multiple of 4. */
 int sam2b_op_preprocess_u8(const void* hwc_u8, float* out_nchw, int n, int h, int w, int normalise, void* stream);
+/* Post-processing of predicted masks (replaces the F.interpolate of SAM2Transforms.postprocess_masks, sam2/utils/transforms.py:119,
+ * and the `masks > mask_threshold` that follows it, sam2_image_predictor.py:300-302 / the video predictor's `video_res_masks > 0`):
+ * low dev fp32 [n][h][w] mask logits -> out dev fp32 [n][out_h][out_w] (bilinear, align_corners = False; may be NULL) and
+ * mask_u8 dev uint8 [n][out_h][out_w] = (out > threshold) (may be NULL; at least one of the two).  fp32 arithmetic of the reference framework's
+ * bilinear up-sampling operator (coordinate = one fma, blend = separately rounded operations): bit-exact against oracle/postprocess_oracle.py:upsample_bilinear. */
+int sam2b_op_upsample_masks(const float* low, float* out, void* mask_u8, int64_t n, int h, int w, int out_h, int out_w,
+                            float threshold, void* stream);
 int sam2b_op_softmax_rows(const float* s, int64_t lds, void* p_bf16, int64_t ldp, int64_t rows, int cols, void* stream);
 /* Single-head flash attention, head_dim 256 (the MemoryAttention core; reference sam/transformer.py:265-296):
  * out[b] = softmax(q[b] k[b]^T / 16) v[b];  q [n][tq][256], k, v [n][lk][256], out [n][tq][256], all bf16 device memory,

@@ -34,6 +34,7 @@ SIGNATURES = {
     "sam2b_op_window_attention": (_i, [_vp, _vp, _i, _i, _i, _i, _i, _i, _vp]),
     "sam2b_op_connected_components": (_i, [_vp, _vp, _vp, _i, _i, _i, _vp]),
     "sam2b_op_preprocess_u8": (_i, [_vp, _vp, _i, _i, _i, _i, _vp]),
+    "sam2b_op_upsample_masks": (_i, [_vp, _vp, _vp, _i64, _i, _i, _i, _i, _f, _vp]),
     "sam2b_op_softmax_rows": (_i, [_vp, _i64, _vp, _i64, _i64, _i, _vp]),
     "sam2b_op_attention_hd256_workspace": (_i64, [_i, _i, _i64]),
     "sam2b_op_attention_hd256": (_i, [_vp, _vp, _vp, _i, _i, _i64, _vp, _vp, _vp]),

@@ -255,6 +255,79 @@ int preprocess_u8_hwc(const uint8_t* in, float* out, int n, int H, int W, int no
 }
 
 // ------------------------------------------------------------------------------------------
+// Post-processing: low-resolution mask logits -> output resolution, bilinear, align_corners = False,
+// optionally thresholded in the same pass.  Reference: SAM2Transforms.postprocess_masks (sam2/utils/transforms.py:119,
+// F.interpolate(masks, orig_hw, mode="bilinear", align_corners=False)), then `masks > mask_threshold`
+// (sam2_image_predictor.py:300-302; sam2_video_predictor_official.py `video_res_masks > 0`).
+// Arithmetic = torch's upsample_bilinear2d; the source coordinate is one fma (as torch's builds contract it), the blend is
+// separately rounded fp32 operations:
+//   src = max(fma(scale, dst + 0.5, -0.5), 0), scale = (float)in / out;  i0 = (int)src;  i1 = i0 + (i0 < in - 1);
+//   l1 = src - i0, l0 = 1 - l1;  out = hl0 * (wl0 * v00 + wl1 * v01) + hl1 * (wl0 * v10 + wl1 * v11).
+// HBM-bound on the store: 4 B (+ 1 B mask) per output pixel; the low-resolution source (256 KB per mask) stays in L1/L2.
+// One thread per VEC consecutive output pixels of a row (VEC = 4: one 16-byte store + one 4-byte mask store).
+// ------------------------------------------------------------------------------------------
+__device__ __forceinline__ void bilinear_coord(int dst, float scale, int in_size, int& i0, int& i1, float& l0, float& l1) {
+  float src = __fmaf_rn(scale, __fadd_rn((float)dst, 0.5f), -0.5f);
+  src = src < 0.f ? 0.f : src;
+  i0 = (int)src;
+  if (i0 > in_size - 1) i0 = in_size - 1;
+  i1 = i0 + (i0 < in_size - 1 ? 1 : 0);
+  l1 = __fsub_rn(src, (float)i0);
+  l1 = l1 < 0.f ? 0.f : (l1 > 1.f ? 1.f : l1);
+  l0 = __fsub_rn(1.f, l1);
+}
+template <int VEC>
+__global__ void __launch_bounds__(256) upsample_bilinear_mask_kernel(const float* __restrict__ low, float* __restrict__ out,
+                                                                     uint8_t* __restrict__ mask, long groups, int h, int w, int H, int W,
+                                                                     float sh, float sw, float threshold) {
+  const int gpr = W / VEC;                       // groups per output row
+  for (long g = (long)blockIdx.x * blockDim.x + threadIdx.x; g < groups; g += (long)gridDim.x * blockDim.x) {
+    const long row = g / gpr;
+    const int x0 = (int)(g - row * gpr) * VEC;
+    const long img = row / H;
+    const int y = (int)(row - img * H);
+    int y0, y1; float hl0, hl1;
+    bilinear_coord(y, sh, h, y0, y1, hl0, hl1);
+    const float* r0 = low + (img * h + y0) * (long)w;
+    const float* r1 = low + (img * h + y1) * (long)w;
+    float v[VEC];
+#pragma unroll
+    for (int e = 0; e < VEC; ++e) {
+      int c0, c1; float wl0, wl1;
+      bilinear_coord(x0 + e, sw, w, c0, c1, wl0, wl1);
+      const float top = __fadd_rn(__fmul_rn(wl0, __ldg(r0 + c0)), __fmul_rn(wl1, __ldg(r0 + c1)));
+      const float bot = __fadd_rn(__fmul_rn(wl0, __ldg(r1 + c0)), __fmul_rn(wl1, __ldg(r1 + c1)));
+      v[e] = __fadd_rn(__fmul_rn(hl0, top), __fmul_rn(hl1, bot));
+    }
+    const long o = row * W + x0;
+    if constexpr (VEC == 4) {
+      if (out) *reinterpret_cast<float4*>(out + o) = make_float4(v[0], v[1], v[2], v[3]);
+      if (mask) *reinterpret_cast<uint32_t*>(mask + o) = (v[0] > threshold ? 1u : 0u) | (v[1] > threshold ? 0x100u : 0u) |
+                                                         (v[2] > threshold ? 0x10000u : 0u) | (v[3] > threshold ? 0x1000000u : 0u);
+    } else {
+      if (out) out[o] = v[0];
+      if (mask) mask[o] = v[0] > threshold ? 1 : 0;
+    }
+  }
+}
+int upsample_bilinear_mask(const float* low, float* out, uint8_t* mask, long n, int h, int w, int H, int W, float threshold, cudaStream_t stream) {
+  if (n <= 0 || h <= 0 || w <= 0 || H <= 0 || W <= 0 || !low || (!out && !mask)) {
+    set_error("upsample_bilinear_mask: n=%ld h=%d w=%d H=%d W=%d (needs a source and at least one of out / mask)", n, h, w, H, W);
+    return 1;
+  }
+  const float sh = (float)h / (float)H, sw = (float)w / (float)W;
+  const bool vec = W % 4 == 0 && !(reinterpret_cast<uintptr_t>(out) & 15) && !(reinterpret_cast<uintptr_t>(mask) & 3);
+  const long groups = n * H * (vec ? W / 4 : W);
+  long blocks = (groups + 255) / 256;
+  if (blocks > (long)num_sms() * 16) blocks = (long)num_sms() * 16;
+  ProfRange pr(stream, "upsample_bilinear_mask", 0, (double)n * H * W * ((out ? 4.0 : 0.0) + (mask ? 1.0 : 0.0)) + (double)n * h * w * 4.0);
+  if (vec) upsample_bilinear_mask_kernel<4><<<(unsigned)blocks, 256, 0, stream>>>(low, out, mask, groups, h, w, H, W, sh, sw, threshold);
+  else upsample_bilinear_mask_kernel<1><<<(unsigned)blocks, 256, 0, stream>>>(low, out, mask, groups, h, w, H, W, sh, sw, threshold);
+  SAM2B_CHECK_LAUNCH("upsample_bilinear_mask");
+  return 0;
+}
+
+// ------------------------------------------------------------------------------------------
 // FPN top-down: dst += nearest_x2(src)   (reference: image_encoder.py:115-127, fpn_interp_model nearest)
 // ------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256) upsample2x_add_kernel(float4* __restrict__ dst, const float2* __restrict__ src, long total4, int W4,

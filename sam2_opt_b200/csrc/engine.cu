@@ -929,6 +929,12 @@ int sam2b_op_preprocess_u8(const void* hwc_u8, float* out_nchw, int n, int h, in
   if (!hwc_u8 || !out_nchw) { set_error("sam2b_op_preprocess_u8: null argument"); return 1; }
   return preprocess_u8_hwc(reinterpret_cast<const uint8_t*>(hwc_u8), out_nchw, n, h, w, normalise, reinterpret_cast<cudaStream_t>(stream));
 }
+int sam2b_op_upsample_masks(const float* low, float* out, void* mask_u8, int64_t n, int h, int w, int out_h, int out_w, float threshold,
+                            void* stream) {
+  if (!low || (!out && !mask_u8)) { set_error("sam2b_op_upsample_masks: null argument"); return 1; }
+  return upsample_bilinear_mask(low, out, reinterpret_cast<uint8_t*>(mask_u8), (long)n, h, w, out_h, out_w, threshold,
+                                reinterpret_cast<cudaStream_t>(stream));
+}
 int sam2b_op_softmax_rows(const float* s, int64_t lds, void* p, int64_t ldp, int64_t rows, int cols, void* stream) {
   return softmax_rows(s, lds, reinterpret_cast<bf16*>(p), ldp, rows, cols, reinterpret_cast<cudaStream_t>(stream));
 }

@@ -114,6 +114,8 @@ int softmax_rows(const float* s, long lds, bf16* p, long ldp, long rows, int col
 int connected_components(const uint8_t* mask, int* labels, int* counts, int n, int H, int W, cudaStream_t stream);
 // uint8 HWC [n][H][W][3] -> fp32 NCHW [n][3][H][W] = x / 255, optionally (x - mean) / std (SAM2Transforms, bit-exact)
 int preprocess_u8_hwc(const uint8_t* in, float* out, int n, int H, int W, int normalise, cudaStream_t stream);
+// low fp32 [n][h][w] -> out fp32 [n][H][W] (nullable) and mask uint8 [n][H][W] = out > threshold (nullable); bilinear, align_corners = False
+int upsample_bilinear_mask(const float* low, float* out, uint8_t* mask, long n, int h, int w, int H, int W, float threshold, cudaStream_t stream);
 // Fused trunk MLP for C = 144 / 288 (mlp_fused.cu): x += fc2(GELU(rstd * (xb W1''^T) + b1)) + b2 in place, bf16 copy and
 // per-row (sum, sum of squares) in two parts for the next folded LayerNorm; the hidden layer never reaches HBM.
 bool mlp_fused_supported(int C);

@@ -21,6 +21,7 @@ import torch.nn.functional as F
 
 from . import ops
 from . import sam_heads as H
+from .postprocess import upsample_masks
 from .executor import B200Executor
 
 IMG_MEAN = (0.485, 0.456, 0.406)
@@ -139,10 +140,12 @@ class SAM2ImagePredictor(_Base):
         hr = [f[img_idx:img_idx + 1] for f in self._features["high_res_feats"]]
         low, iou, _, _ = H.mask_decoder(self.w, self._features["image_embed"][img_idx:img_idx + 1], sparse, dense,
                                         multimask_output, hr, repeat_image=batched, pe=self._dense_pe)
-        masks = F.interpolate(low.float(), (oh, ow), mode="bilinear", align_corners=False)
+        # postprocess_masks (ref: utils/transforms.py:119) and the threshold in one pass: sam2b_op_upsample_masks
+        if return_logits:
+            masks = upsample_masks(low.float(), (oh, ow))
+        else:
+            masks = upsample_masks(low.float(), (oh, ow), threshold=self.mask_threshold, return_logits=False)
         low = torch.clamp(low, -32.0, 32.0)
-        if not return_logits:
-            masks = masks > self.mask_threshold
         return masks[0].float().cpu().numpy(), iou[0].float().cpu().numpy(), low[0].float().cpu().numpy()
 
 
@@ -245,7 +248,7 @@ class SAM2VideoPredictor(_Base):
 
     def _video_res(self, st, low):
         hw = (st["video_height"], st["video_width"])
-        return F.interpolate(low, size=hw, mode="bilinear", align_corners=False)
+        return upsample_masks(low, hw)         # ref: _get_orig_video_res_output (sam2_video_predictor_official.py:843-862)
 
     @torch.no_grad()
     def add_new_points_or_box(self, st, frame_idx, obj_id, points=None, labels=None, clear_old_points=True,

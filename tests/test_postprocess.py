@@ -91,3 +91,81 @@ def test_rejects_cpu_tensor():
     from sam2_opt_b200 import postprocess as PP
     with pytest.raises(RuntimeError, match="CUDA tensor"):
         PP.get_connected_components(torch.zeros(1, 1, 8, 8, dtype=torch.bool))
+
+
+# ---- mask up-sampling (+ threshold): sam2b_op_upsample_masks vs oracle/postprocess_oracle.py:upsample_bilinear ----
+def _bits(a):
+    return np.ascontiguousarray(a, dtype=np.float32).view(np.uint32)
+
+
+def _logits(n, c, h, w, seed):
+    rng = np.random.default_rng(seed)
+    return (rng.standard_normal((n, c, h, w)) * 8).astype(np.float32)
+
+
+UPSAMPLE_CASES = [  # (n, c, h, w, H, W): SAM2's 256 -> 1024, video resolutions (W % 4 != 0 takes the scalar route), down-sampling, identity
+    (2, 3, 256, 256, 1024, 1024), (1, 1, 256, 256, 480, 854), (3, 1, 256, 256, 720, 1280), (1, 2, 64, 64, 37, 53),
+    (1, 1, 256, 256, 256, 256), (1, 1, 256, 256, 100, 100), (2, 1, 1, 1, 8, 8), (1, 1, 5, 7, 1, 1)]
+
+
+@pytest.mark.parametrize("case", UPSAMPLE_CASES[:5] + UPSAMPLE_CASES[6:], ids=str)
+def test_upsample_oracle_pinned_against_torch_interpolate(case):
+    """The operator the reference calls (transforms.py:119) on CPU; torch's CPU kernel may contract multiply-adds, so the
+    pin is 2e-6 relative to the logit scale, and the thresholded masks may differ only where |logit| is below that."""
+    n, c, h, w, H, W = case
+    x = _logits(n, c, h, w, 1)
+    want = torch.nn.functional.interpolate(torch.from_numpy(x), (H, W), mode="bilinear", align_corners=False).numpy()
+    got = PO.upsample_bilinear(x, (H, W))
+    assert got.shape == want.shape and got.dtype == np.float32
+    tol = 2e-6 * float(np.abs(x).max())
+    assert float(np.abs(got - want).max()) <= tol
+    diff = (got > 0) != (want > 0)
+    assert not diff.any() or float(np.abs(want[diff]).max()) <= tol
+
+
+def test_upsample_oracle_known_answers():
+    x = np.array([[[[0.0, 4.0], [8.0, 12.0]]]], np.float32)
+    y = PO.upsample_bilinear(x, (4, 4))
+    assert np.array_equal(y[0, 0, 0], np.array([0.0, 1.0, 3.0, 4.0], np.float32))        # corners clamp, 1/4-3/4 weights inside
+    assert np.array_equal(y[0, 0, :, 0], np.array([0.0, 2.0, 6.0, 8.0], np.float32))
+    assert np.array_equal(PO.upsample_bilinear(x, (2, 2)), x)                            # identity at the same size
+    assert np.array_equal(PO.upsample_bilinear(np.full((1, 1, 3, 3), 2.5, np.float32), (7, 5)), np.full((1, 1, 7, 5), 2.5, np.float32))
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("case", UPSAMPLE_CASES, ids=str)
+def test_upsample_masks_bit_exact_vs_oracle(case):
+    from sam2_opt_b200 import postprocess as PP
+    n, c, h, w, H, W = case
+    x = _logits(n, c, h, w, 2)
+    want = PO.upsample_bilinear(x, (H, W))
+    xd = torch.from_numpy(x).cuda()
+    out, mask = PP.upsample_masks(xd, (H, W), threshold=0.0)
+    assert out.shape == (n, c, H, W) and mask.dtype == torch.bool
+    assert np.array_equal(_bits(out.cpu().numpy()), _bits(want))
+    assert np.array_equal(mask.cpu().numpy(), want > 0)
+    only = PP.upsample_masks(xd, (H, W), threshold=1.5, return_logits=False)
+    assert np.array_equal(only.cpu().numpy(), want > 1.5)
+    assert np.array_equal(_bits(PP.upsample_masks(xd, (H, W)).cpu().numpy()), _bits(want))
+
+
+@pytest.mark.gpu
+def test_upsample_masks_full_size_properties():
+    """64 object masks 256^2 -> 1024^2 (the video predictor's per-frame load): constants are preserved, the result is bounded
+    by the source's range, and it matches torch's CUDA operator within fp32 rounding."""
+    from sam2_opt_b200 import postprocess as PP
+    g = torch.Generator(device="cuda").manual_seed(0)
+    x = torch.randn(64, 1, 256, 256, device="cuda", generator=g) * 8
+    y, m = PP.upsample_masks(x, (1024, 1024), threshold=0.0)
+    assert float(y.max()) <= float(x.max()) and float(y.min()) >= float(x.min())
+    assert torch.equal(m, y > 0)
+    ref = torch.nn.functional.interpolate(x, (1024, 1024), mode="bilinear", align_corners=False)
+    assert float((y - ref).abs().max()) <= 2e-6 * float(x.abs().max())
+    c = torch.full((2, 1, 256, 256), -3.25, device="cuda")
+    assert torch.equal(PP.upsample_masks(c, (480, 854)), torch.full((2, 1, 480, 854), -3.25, device="cuda"))
+
+
+def test_upsample_masks_rejects_cpu_tensor_and_bad_arguments():
+    from sam2_opt_b200 import postprocess as PP
+    with pytest.raises(RuntimeError, match="CUDA tensor"):
+        PP.upsample_masks(torch.zeros(1, 1, 8, 8), (16, 16))
