@@ -264,7 +264,7 @@ int preprocess_u8_hwc(const uint8_t* in, float* out, int n, int H, int W, int no
 //   src = max(fma(scale, dst + 0.5, -0.5), 0), scale = (float)in / out;  i0 = (int)src;  i1 = i0 + (i0 < in - 1);
 //   l1 = src - i0, l0 = 1 - l1;  out = hl0 * (wl0 * v00 + wl1 * v01) + hl1 * (wl0 * v10 + wl1 * v11).
 // HBM-bound on the store: 4 B (+ 1 B mask) per output pixel; the low-resolution source (256 KB per mask) stays in L1/L2.
-// One thread per VEC consecutive output pixels of a row (VEC = 4: one 16-byte store + one 4-byte mask store).
+// VEC = 4 output columns per thread: one 16-byte store + one 4-byte mask store per row (VEC = 1 when W % 4 != 0).
 // ------------------------------------------------------------------------------------------
 __device__ __forceinline__ void bilinear_coord(int dst, float scale, int in_size, int& i0, int& i1, float& l0, float& l1) {
   float src = __fmaf_rn(scale, __fadd_rn((float)dst, 0.5f), -0.5f);
@@ -276,53 +276,82 @@ __device__ __forceinline__ void bilinear_coord(int dst, float scale, int in_size
   l1 = l1 < 0.f ? 0.f : (l1 > 1.f ? 1.f : l1);
   l0 = __fsub_rn(1.f, l1);
 }
+// Each thread owns VEC output columns (their source columns and weights are computed once) and walks UP_ROWS output rows;
+// the horizontally blended source rows `top` / `bot` are recomputed only when the source row pair changes (every 4th output
+// row at 256 -> 1024), which leaves ~1 fma-class operation per output pixel per row and makes the kernel store-bound.
+constexpr int UP_ROWS = 8;
 template <int VEC>
 __global__ void __launch_bounds__(256) upsample_bilinear_mask_kernel(const float* __restrict__ low, float* __restrict__ out,
-                                                                     uint8_t* __restrict__ mask, long groups, int h, int w, int H, int W,
+                                                                     uint8_t* __restrict__ mask, int n, int h, int w, int H, int W,
                                                                      float sh, float sw, float threshold) {
-  const int gpr = W / VEC;                       // groups per output row
-  for (long g = (long)blockIdx.x * blockDim.x + threadIdx.x; g < groups; g += (long)gridDim.x * blockDim.x) {
-    const long row = g / gpr;
-    const int x0 = (int)(g - row * gpr) * VEC;
-    const long img = row / H;
-    const int y = (int)(row - img * H);
-    int y0, y1; float hl0, hl1;
-    bilinear_coord(y, sh, h, y0, y1, hl0, hl1);
-    const float* r0 = low + (img * h + y0) * (long)w;
-    const float* r1 = low + (img * h + y1) * (long)w;
-    float v[VEC];
+  const unsigned gpr = (unsigned)(W / VEC);                     // column groups per output row
+  const unsigned tiles = (unsigned)((H + UP_ROWS - 1) / UP_ROWS);
+  const unsigned t = blockIdx.x * blockDim.x + threadIdx.x;     // (row tile, column group) of one image
+  if (t >= gpr * tiles) return;
+  const unsigned tile = t / gpr;
+  const int x0 = (int)(t - tile * gpr) * VEC;
+  int c0[VEC], c1[VEC];
+  float wl0[VEC], wl1[VEC];
 #pragma unroll
-    for (int e = 0; e < VEC; ++e) {
-      int c0, c1; float wl0, wl1;
-      bilinear_coord(x0 + e, sw, w, c0, c1, wl0, wl1);
-      const float top = __fadd_rn(__fmul_rn(wl0, __ldg(r0 + c0)), __fmul_rn(wl1, __ldg(r0 + c1)));
-      const float bot = __fadd_rn(__fmul_rn(wl0, __ldg(r1 + c0)), __fmul_rn(wl1, __ldg(r1 + c1)));
-      v[e] = __fadd_rn(__fmul_rn(hl0, top), __fmul_rn(hl1, bot));
-    }
-    const long o = row * W + x0;
-    if constexpr (VEC == 4) {
-      if (out) *reinterpret_cast<float4*>(out + o) = make_float4(v[0], v[1], v[2], v[3]);
-      if (mask) *reinterpret_cast<uint32_t*>(mask + o) = (v[0] > threshold ? 1u : 0u) | (v[1] > threshold ? 0x100u : 0u) |
-                                                         (v[2] > threshold ? 0x10000u : 0u) | (v[3] > threshold ? 0x1000000u : 0u);
-    } else {
-      if (out) out[o] = v[0];
-      if (mask) mask[o] = v[0] > threshold ? 1 : 0;
+  for (int e = 0; e < VEC; ++e) bilinear_coord(x0 + e, sw, w, c0[e], c1[e], wl0[e], wl1[e]);
+  const int y_begin = (int)tile * UP_ROWS, y_end = y_begin + UP_ROWS < H ? y_begin + UP_ROWS : H;
+  for (int img = blockIdx.y; img < n; img += gridDim.y) {
+    const float* src = low + (long)img * h * w;
+    float top[VEC], bot[VEC];
+    int py0 = -1, py1 = -1;
+    for (int y = y_begin; y < y_end; ++y) {
+      int y0, y1; float hl0, hl1;
+      bilinear_coord(y, sh, h, y0, y1, hl0, hl1);
+      if (y0 != py0) {
+        if (y0 == py1) {
+#pragma unroll
+          for (int e = 0; e < VEC; ++e) top[e] = bot[e];
+        } else {
+          const float* r0 = src + (long)y0 * w;
+#pragma unroll
+          for (int e = 0; e < VEC; ++e) top[e] = __fadd_rn(__fmul_rn(wl0[e], __ldg(r0 + c0[e])), __fmul_rn(wl1[e], __ldg(r0 + c1[e])));
+        }
+      }
+      if (y1 != py1) {
+        if (y1 == y0) {
+#pragma unroll
+          for (int e = 0; e < VEC; ++e) bot[e] = top[e];
+        } else {
+          const float* r1 = src + (long)y1 * w;
+#pragma unroll
+          for (int e = 0; e < VEC; ++e) bot[e] = __fadd_rn(__fmul_rn(wl0[e], __ldg(r1 + c0[e])), __fmul_rn(wl1[e], __ldg(r1 + c1[e])));
+        }
+      }
+      py0 = y0; py1 = y1;
+      float v[VEC];
+#pragma unroll
+      for (int e = 0; e < VEC; ++e) v[e] = __fadd_rn(__fmul_rn(hl0, top[e]), __fmul_rn(hl1, bot[e]));
+      const long o = ((long)img * H + y) * W + x0;
+      if constexpr (VEC == 4) {
+        if (out) __stcs(reinterpret_cast<float4*>(out + o), make_float4(v[0], v[1], v[2], v[3]));
+        if (mask) __stcs(reinterpret_cast<uint32_t*>(mask + o), (v[0] > threshold ? 1u : 0u) | (v[1] > threshold ? 0x100u : 0u) |
+                                                                  (v[2] > threshold ? 0x10000u : 0u) | (v[3] > threshold ? 0x1000000u : 0u));
+      } else {
+        if (out) __stcs(out + o, v[0]);
+        if (mask) mask[o] = v[0] > threshold ? 1 : 0;
+      }
     }
   }
 }
 int upsample_bilinear_mask(const float* low, float* out, uint8_t* mask, long n, int h, int w, int H, int W, float threshold, cudaStream_t stream) {
-  if (n <= 0 || h <= 0 || w <= 0 || H <= 0 || W <= 0 || !low || (!out && !mask)) {
+  if (n <= 0 || n > 0x7fffffffL || h <= 0 || w <= 0 || H <= 0 || W <= 0 || !low || (!out && !mask)) {
     set_error("upsample_bilinear_mask: n=%ld h=%d w=%d H=%d W=%d (needs a source and at least one of out / mask)", n, h, w, H, W);
     return 1;
   }
   const float sh = (float)h / (float)H, sw = (float)w / (float)W;
   const bool vec = W % 4 == 0 && !(reinterpret_cast<uintptr_t>(out) & 15) && !(reinterpret_cast<uintptr_t>(mask) & 3);
-  const long groups = n * H * (vec ? W / 4 : W);
-  long blocks = (groups + 255) / 256;
-  if (blocks > (long)num_sms() * 16) blocks = (long)num_sms() * 16;
+  const long tiles = (H + UP_ROWS - 1) / UP_ROWS;
+  const long per_img = tiles * (vec ? W / 4 : W);
+  if (per_img > 0x7fffffffL) { set_error("upsample_bilinear_mask: output %d x %d too large", H, W); return 1; }
+  dim3 grid((unsigned)((per_img + 255) / 256), (unsigned)(n < 65535 ? n : 65535));
   ProfRange pr(stream, "upsample_bilinear_mask", 0, (double)n * H * W * ((out ? 4.0 : 0.0) + (mask ? 1.0 : 0.0)) + (double)n * h * w * 4.0);
-  if (vec) upsample_bilinear_mask_kernel<4><<<(unsigned)blocks, 256, 0, stream>>>(low, out, mask, groups, h, w, H, W, sh, sw, threshold);
-  else upsample_bilinear_mask_kernel<1><<<(unsigned)blocks, 256, 0, stream>>>(low, out, mask, groups, h, w, H, W, sh, sw, threshold);
+  if (vec) upsample_bilinear_mask_kernel<4><<<grid, 256, 0, stream>>>(low, out, mask, (int)n, h, w, H, W, sh, sw, threshold);
+  else upsample_bilinear_mask_kernel<1><<<grid, 256, 0, stream>>>(low, out, mask, (int)n, h, w, H, W, sh, sw, threshold);
   SAM2B_CHECK_LAUNCH("upsample_bilinear_mask");
   return 0;
 }
