@@ -276,10 +276,10 @@ __device__ __forceinline__ void bilinear_coord(int dst, float scale, int in_size
   l1 = l1 < 0.f ? 0.f : (l1 > 1.f ? 1.f : l1);
   l0 = __fsub_rn(1.f, l1);
 }
-// Each thread owns VEC output columns (their source columns and weights are computed once) and walks UP_ROWS output rows;
+// Each thread owns VEC output columns (their source columns and weights are computed once) and walks UP_ROWS output rows (16: 0.074 -> 0.066 ms against 8 for 64 masks -> 1024^2);
 // the horizontally blended source rows `top` / `bot` are recomputed only when the source row pair changes (every 4th output
 // row at 256 -> 1024), which leaves ~1 fma-class operation per output pixel per row and makes the kernel store-bound.
-constexpr int UP_ROWS = 8;
+constexpr int UP_ROWS = 16;
 template <int VEC>
 __global__ void __launch_bounds__(256) upsample_bilinear_mask_kernel(const float* __restrict__ low, float* __restrict__ out,
                                                                      uint8_t* __restrict__ mask, int n, int h, int w, int H, int W,
