@@ -59,6 +59,13 @@ int sam2b_image_encode_host(sam2b_handle h, const float* img_host, int n, int no
 int sam2b_image_encode_host_u8(sam2b_handle h, const void* hwc_u8_host, int n, int add_no_mem_embed,
                                float* fpn0_host, float* fpn1_host, float* fpn2_host, void* stream);
 
+/* ---- constant outputs of E2 / E4: the sine position encodings ----
+ * E2's vision_pos_enc0..2 ([n,256,256,256], [n,256,128,128], [n,256,64,64]) and E4's mask_memory_pos_enc ([n,64,64,64]) do
+ * not depend on the input (PositionEmbeddingSine, sam2/sam2/modeling/position_encoding.py:90-124, which the reference
+ * re-materialises with .repeat(n, ...) on every call).  out_chw dev [channels][h][w] fp32: one level, computed on `stream`;
+ * the caller broadcasts it over the batch.  channels must be a multiple of 4 (the reference uses 256 and 64). */
+int sam2b_position_encoding(int channels, int h, int w, float* out_chw, void* stream);
+
 /* ---- E3: 4-layer MemoryAttention ----
  * curr, curr_pos dev [4096,n,256]; memory, memory_pos dev [L,4096,n,64]; memory_exclude, memory_pos_exclude dev [P,n,64]
  * (P may be 0, then both may be NULL: the `none` variant); out dev [4096,n,256]. L in [1,16] (the reference's

@@ -1,8 +1,10 @@
 """Import and build the UNMODIFIED reference model (FasterProcess/sam2_opt) in this container.
 
-TEST INFRASTRUCTURE ONLY.  Used by ``oracle/make_golden.py`` and by the CPU tests that
-pin the oracle against the real reference when ``/root/reference`` is present (it is not
-present on the GPU box; nothing under ``-m gpu``, ``smoke()`` or ``bench.py`` imports this).
+TEST INFRASTRUCTURE ONLY.  Used by ``oracle/make_golden.py``, by the CPU tests that pin the
+oracle against the real reference, by the GPU tests that drive the reference's own predictors
+through ``speedup("b200")`` and by ``bench.py``'s reference / baseline legs.  The sources are
+``/root/reference`` in the build container and the byte-identical copy under ``oracle/_ref``
+(made by ``oracle/build_ref.py``, git-ignored) on the GPU box.  No product module imports this.
 
 The reference needs ``hydra``/``omegaconf``/``iopath`` only for its builders
 (reference ``sam2/sam2/build_sam.py:11-13``, ``sam2/sam2/__init__.py:7-11``,
@@ -17,12 +19,30 @@ import re
 import sys
 import types
 
-REF_ROOT = os.environ.get("SAM2_REFERENCE_ROOT", "/root/reference")
 _CFG = "sam2/sam2/configs/sam2.1/sam2.1_hiera_l.yaml"
+_VENDORED = os.path.join(os.path.dirname(os.path.abspath(__file__)), "_ref")
+
+
+def _pick_root() -> str:
+    """/root/reference in the build container; on the GPU box the byte-identical copy that `oracle/build_ref.py` made
+    under the git-ignored `oracle/_ref/` (it travels with the working tree)."""
+    env = os.environ.get("SAM2_REFERENCE_ROOT")
+    for cand in ([env] if env else []) + ["/root/reference", _VENDORED]:
+        if cand and os.path.isfile(os.path.join(cand, _CFG)):
+            return cand
+    return env or "/root/reference"
+
+
+REF_ROOT = _pick_root()
 
 
 def available() -> bool:
     return os.path.isfile(os.path.join(REF_ROOT, _CFG))
+
+
+def kind() -> str:
+    """'reference' = the unmodified reference sources (in place or the oracle/_ref copy), 'absent' otherwise."""
+    return "reference" if available() else "absent"
 
 
 def _install_stubs():

@@ -385,6 +385,38 @@ int upsample2x_add_nchw(float* dst, const float* src, int B, int C, int H, int W
 }
 
 // ------------------------------------------------------------------------------------------
+// Sine position encoding of one feature level (PositionEmbeddingSine, reference modeling/position_encoding.py:90-124 with
+// normalize = True, scale = 2 pi, temperature 10000): out [C][H][W]; channels [0, C/2) encode the row, [C/2, C) the column;
+// inside a half, channel j holds sin (j even) / cos (j odd) of pos / 10000^(2 floor(j / 2) / (C / 2)),
+// pos = (index + 1) / (extent + 1e-6) * 2 pi.  A constant of the model: computed once per (C, H, W) and cached by the caller.
+// ------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) position_sine_kernel(float* __restrict__ out, int C, int H, int W) {
+  const long total = (long)C * H * W;
+  const int npf = C / 2;
+  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
+    const int x = (int)(i % W);
+    const int y = (int)((i / W) % H);
+    const int c = (int)(i / ((long)W * H));
+    const int j = c < npf ? c : c - npf;
+    const float pos = c < npf ? (float)(y + 1) / ((float)H + 1e-6f) * 6.283185307179586f
+                              : (float)(x + 1) / ((float)W + 1e-6f) * 6.283185307179586f;
+    const float dim_t = powf(10000.0f, (float)(2 * (j / 2)) / (float)npf);
+    const float a = pos / dim_t;
+    out[i] = (j & 1) ? cosf(a) : sinf(a);
+  }
+}
+int position_sine(float* out, int C, int H, int W, cudaStream_t stream) {
+  if (!out || C <= 0 || (C & 3) || H <= 0 || W <= 0) { set_error("position_sine: bad arguments (C=%d must be a positive multiple of 4, H=%d, W=%d)", C, H, W); return 1; }
+  const long total = (long)C * H * W;
+  long blocks = (total + 255) / 256;
+  if (blocks > (long)num_sms() * 16) blocks = (long)num_sms() * 16;
+  ProfRange pr(stream, "position_sine", 0, (double)total * 4.0);
+  position_sine_kernel<<<(unsigned)blocks, 256, 0, stream>>>(out, C, H, W);
+  SAM2B_CHECK_LAUNCH("position_sine");
+  return 0;
+}
+
+// ------------------------------------------------------------------------------------------
 // Row softmax fp32 -> bf16 (memory-attention scores).  One CTA per row; the row is staged in shared
 // memory so HBM/L2 sees it once.
 // ------------------------------------------------------------------------------------------

@@ -7,6 +7,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <map>
+#include <mutex>
 #include <string>
 #include <vector>
 
@@ -106,6 +107,13 @@ struct sam2b_engine {
   cudaStream_t copy_stream = nullptr;      // host -> device
   cudaStream_t copy_stream2 = nullptr;     // device -> host (PCIe is full duplex: the two directions overlap)
   cudaEvent_t ev[12] = {};
+  // Calls on one engine share the named workspaces, so they must not overlap on the DEVICE either (two host threads with
+  // private streams drive one predictor in the reference's video_multi_thread.py:36-60).  `mu` serialises the host enqueue;
+  // `done` is recorded on the caller's stream at the end of every call and the next call's stream waits for it first: the
+  // same hand-off the reference executor gets from its private work stream (tensorrt_executor.py:248-252,288-291).
+  std::mutex mu;
+  cudaEvent_t done = nullptr;
+  bool done_valid = false;
 
   Tensor* find(const std::string& n) {
     auto it = w.find(n);
@@ -114,6 +122,25 @@ struct sam2b_engine {
 };
 
 namespace sam2b {
+
+// Serialises one engine call against every other call on the same engine, on the host (mutex) and on the device (event
+// chain across the callers' streams).  Constructed after ENTER_DEVICE; `begin()` reports CUDA errors.
+struct EngineCall {
+  sam2b_engine* e;
+  cudaStream_t st;
+  std::unique_lock<std::mutex> lk;
+  EngineCall(sam2b_engine* eng, cudaStream_t s) : e(eng), st(s), lk(eng->mu) {}
+  int begin() {
+    if (e->done_valid) CUDA_OK(cudaStreamWaitEvent(st, e->done, 0));
+    return 0;
+  }
+  ~EngineCall() {
+    if (cudaEventRecord(e->done, st) == cudaSuccess) e->done_valid = true;
+  }
+};
+#define ENGINE_CALL(h, st)        \
+  EngineCall engine_call__(h, st); \
+  TRY(engine_call__.begin())
 
 static int ws_get(sam2b_engine* e, const char* name, size_t bytes, void** out) {
   Buf& b = e->ws[name];
@@ -694,6 +721,7 @@ int sam2b_create(int device, sam2b_handle* out) {
   CUDA_OK(cudaStreamCreateWithFlags(&e->copy_stream, cudaStreamNonBlocking));
   CUDA_OK(cudaStreamCreateWithFlags(&e->copy_stream2, cudaStreamNonBlocking));
   for (auto& ev : e->ev) CUDA_OK(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
+  CUDA_OK(cudaEventCreateWithFlags(&e->done, cudaEventDisableTiming));
   *out = e;
   return 0;
 }
@@ -705,6 +733,7 @@ int sam2b_destroy(sam2b_handle h) {
   for (auto& kv : h->w) { if (kv.second.f32) cudaFree(kv.second.f32); if (kv.second.b16) cudaFree(kv.second.b16); }
   for (auto& kv : h->ws) if (kv.second.p) cudaFree(kv.second.p);
   for (auto& ev : h->ev) if (ev) cudaEventDestroy(ev);
+  if (h->done) cudaEventDestroy(h->done);
   if (h->copy_stream) cudaStreamDestroy(h->copy_stream);
   if (h->copy_stream2) cudaStreamDestroy(h->copy_stream2);
   delete h;
@@ -714,6 +743,7 @@ int sam2b_destroy(sam2b_handle h) {
 int sam2b_set_tensor(sam2b_handle h, const char* name, const float* dev_data, const int64_t* shape, int ndim) {
   if (!h || !name || !dev_data) { set_error("sam2b_set_tensor: null argument"); return 1; }
   ENTER_DEVICE(h->device);
+  std::lock_guard<std::mutex> lk(h->mu);
   Tensor& t = h->w[name];
   int64_t numel = 1;
   std::vector<int64_t> shp;
@@ -730,6 +760,7 @@ int sam2b_set_tensor(sam2b_handle h, const char* name, const float* dev_data, co
 
 int sam2b_finalize(sam2b_handle h) {
   if (!h) { set_error("sam2b_finalize: null handle"); return 1; }
+  std::lock_guard<std::mutex> lk(h->mu);
   return finalize(h);
 }
 
@@ -739,6 +770,7 @@ int sam2b_image_encode(sam2b_handle h, const float* img, int n, int normalised, 
   if (n <= 0 || !img || !fpn0 || !fpn1 || !fpn2) { set_error("sam2b_image_encode: bad arguments (n=%d)", n); return 1; }
   ENTER_DEVICE(h->device);
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  ENGINE_CALL(h, st);
   const int kMaxMicroBatch = max_micro_batch();
   for (int i0 = 0; i0 < n; i0 += kMaxMicroBatch) {
     const int mb = (n - i0) < kMaxMicroBatch ? (n - i0) : kMaxMicroBatch;
@@ -758,6 +790,7 @@ static int image_encode_host_impl(sam2b_handle h, const void* img_host_v, int u8
   const float* img_host = reinterpret_cast<const float*>(img_host_v);
   const uint8_t* img_host_u8 = reinterpret_cast<const uint8_t*>(img_host_v);
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  ENGINE_CALL(h, st);
   // double-buffered staging: uploads run on copy_stream, downloads on copy_stream2, compute on `st`
   const size_t in_sz = (size_t)3 * 1024 * 1024, o0 = (size_t)32 * 65536, o1 = (size_t)64 * 16384, o2 = (size_t)256 * 4096;
   const int kMaxMicroBatch = max_micro_batch() < kHostMicroBatch ? max_micro_batch() : kHostMicroBatch;
@@ -828,6 +861,7 @@ int sam2b_memory_attention(sam2b_handle h, const float* curr, const float* curr_
   if (L < 1 || L > 16 || P < 0 || P > 64 || (P % 4)) { set_error("sam2b_memory_attention: L=%d must be in [1,16], P=%d in [0,64] and a multiple of 4", L, P); return 1; }
   if (P > 0 && (!memory_exclude || !memory_pos_exclude)) { set_error("sam2b_memory_attention: P=%d but memory_exclude is NULL", P); return 1; }
   ENTER_DEVICE(h->device);
+  ENGINE_CALL(h, reinterpret_cast<cudaStream_t>(stream));
   return memory_attention_mb(h, curr, curr_pos, memory, memory_pos, L, memory_exclude, memory_pos_exclude, P, n, n, out,
                              reinterpret_cast<cudaStream_t>(stream));
 }
@@ -837,6 +871,7 @@ int sam2b_memory_encode(sam2b_handle h, const float* pix_feat, const float* mask
   if (!pix_feat || !masks || !out_x || n <= 0) { set_error("sam2b_memory_encode: null/empty argument"); return 1; }
   ENTER_DEVICE(h->device);
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  ENGINE_CALL(h, st);
   const int kMaxMicroBatch = 16;
   for (int i0 = 0; i0 < n; i0 += kMaxMicroBatch) {
     const int mb = (n - i0) < kMaxMicroBatch ? (n - i0) : kMaxMicroBatch;
@@ -934,6 +969,9 @@ int sam2b_op_upsample_masks(const float* low, float* out, void* mask_u8, int64_t
   if (!low || (!out && !mask_u8)) { set_error("sam2b_op_upsample_masks: null argument"); return 1; }
   return upsample_bilinear_mask(low, out, reinterpret_cast<uint8_t*>(mask_u8), (long)n, h, w, out_h, out_w, threshold,
                                 reinterpret_cast<cudaStream_t>(stream));
+}
+int sam2b_position_encoding(int channels, int h, int w, float* out_chw, void* stream) {
+  return position_sine(out_chw, channels, h, w, reinterpret_cast<cudaStream_t>(stream));
 }
 int sam2b_op_softmax_rows(const float* s, int64_t lds, void* p, int64_t ldp, int64_t rows, int cols, void* stream) {
   return softmax_rows(s, lds, reinterpret_cast<bf16*>(p), ldp, rows, cols, reinterpret_cast<cudaStream_t>(stream));

@@ -106,6 +106,9 @@ int flash_attention_hd256(const bf16* q, long q_batch_stride, const bf16* k, lon
                           long v_batch_stride, int n, int Tq, long Lk, float* o_part, float* ml_part, bf16* out,
                           cudaStream_t stream);
 
+// Sine position encoding of one feature level (reference PositionEmbeddingSine): out [C][H][W] fp32
+int position_sine(float* out, int C, int H, int W, cudaStream_t stream);
+
 // Row softmax over fp32 scores -> bf16 probabilities (row stride lds / ldp elements), `cols` valid columns;
 // columns in [cols, ldp) are written as zero.
 int softmax_rows(const float* s, long lds, bf16* p, long ldp, long rows, int cols, cudaStream_t stream);

@@ -14,8 +14,33 @@ def _ptr(t: Optional[torch.Tensor]):
     return C.c_void_p(0 if t is None else t.data_ptr())
 
 
-def _stream():
-    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+def _stream(t: Optional[torch.Tensor] = None):
+    """the current stream of `t`'s device (of the current device without a tensor)"""
+    return C.c_void_p(torch.cuda.current_stream(None if t is None else t.device).cuda_stream)
+
+
+def on_tensor_device(fn):
+    """Decorator for the single-kernel front ends (ops.py, postprocess.py): run with the device of the first tensor
+    argument current, so that the launch and `_stream()` both mean that tensor's GPU whatever the caller's current device
+    is (the sam2b_op_* entry points launch on the calling thread's current device)."""
+    import functools
+
+    @functools.wraps(fn)
+    def wrapper(t, *a, **k):
+        if torch.is_tensor(t) and t.is_cuda:
+            with torch.cuda.device(t.device):
+                return fn(t, *a, **k)
+        return fn(t, *a, **k)
+    return wrapper
+
+
+def normalise_device(device) -> torch.device:
+    """torch.device("cuda") has no index: bind it to the CURRENT device once, so that the engine, its output tensors and
+    the streams it enqueues on all mean the same GPU (under torchrun the current device is cuda:LOCAL_RANK, not cuda:0)."""
+    d = torch.device(device if device is not None else "cuda")
+    if d.type != "cuda":
+        raise RuntimeError(f"sam2_opt_b200 needs a CUDA (sm_100a) device, got {d}; there is no CPU fallback")
+    return torch.device("cuda", torch.cuda.current_device()) if d.index is None else d
 
 
 def _f32c(t: torch.Tensor, name: str) -> torch.Tensor:
@@ -27,17 +52,19 @@ def _f32c(t: torch.Tensor, name: str) -> torch.Tensor:
 
 
 class Engine:
-    """One engine per (model, device).  Thread-safe: calls are serialised with a lock like the reference executor
-    (ref: sam2/ytools/tensorrt/tensorrt_executor.py:24,248,291) and enqueue on the caller's current stream."""
+    """One engine per (model, device).  Thread-safe: calls enqueue on the caller's current stream and are serialised like
+    the reference executor's (ref: sam2/ytools/tensorrt/tensorrt_executor.py:24,248-252,288-291) — on the host by a lock
+    and on the device by an event chain inside the library (engine.cu `EngineCall`), so two threads with private streams
+    can share one engine (video_multi_thread.py:36-60) without their kernels overlapping on the shared workspaces."""
 
     def __init__(self, state_dict: Dict[str, torch.Tensor], device: Optional[torch.device] = None):
         if not torch.cuda.is_available():
             raise RuntimeError("sam2_opt_b200 needs a CUDA (sm_100a) device; there is no CPU fallback")
         self.lib = _lib.load()
-        self.device = torch.device(device if device is not None else f"cuda:{torch.cuda.current_device()}")
+        self.device = normalise_device(device)
         self._lock = threading.Lock()
         h = C.c_void_p()
-        _lib.check(self.lib.sam2b_create(self.device.index or 0, C.byref(h)), "create")
+        _lib.check(self.lib.sam2b_create(self.device.index, C.byref(h)), "create")
         self._h = h
         self._upload(state_dict)
         self._pos_cache = {}
@@ -48,36 +75,64 @@ class Engine:
 
     # -- weights ---------------------------------------------------------------------------------------------
     def _upload(self, sd: Dict[str, torch.Tensor]):
+        """Snapshot of the live state_dict (ref: the reference bakes the weights into its engine at build time).  The
+        one-time folds (weights.derive) run on the HOST in fp64 and everything crosses to the device as ONE flat buffer:
+        engine start-up launches no torch kernels, only the library's own bf16 repack."""
         with torch.no_grad():
-            sd = {k: v.detach().to(self.device, torch.float32).contiguous() for k, v in sd.items()
+            sd = {k: v.detach().to("cpu", torch.float32).contiguous() for k, v in sd.items()
                   if torch.is_tensor(v) and v.is_floating_point()}
             sd.update(weights.derive(sd))
-            for name, t in sd.items():
+            names = list(sd)
+            offs, total = [], 0
+            for k in names:
+                offs.append(total)
+                total += (sd[k].numel() + 63) // 64 * 64            # 256-byte aligned slices
+            flat = torch.empty(total, dtype=torch.float32).pin_memory()
+            for k, o in zip(names, offs):
+                flat[o:o + sd[k].numel()].copy_(sd[k].reshape(-1))
+            dev_flat = flat.to(self.device)                          # one H2D copy
+            base = dev_flat.data_ptr()
+            for k, o in zip(names, offs):
+                t = sd[k]
                 shape = (C.c_int64 * max(1, t.dim()))(*(t.shape if t.dim() else (1,)))
-                _lib.check(self.lib.sam2b_set_tensor(self._h, name.encode(), _ptr(t), shape, max(1, t.dim())),
-                           f"set_tensor({name})")
+                _lib.check(self.lib.sam2b_set_tensor(self._h, k.encode(), C.c_void_p(base + 4 * o), shape, max(1, t.dim())),
+                           f"set_tensor({k})")
             torch.cuda.synchronize(self.device)
             _lib.check(self.lib.sam2b_finalize(self._h), "finalize")
-        self.no_obj_embed_spatial = sd.get("no_obj_embed_spatial")
+            del dev_flat
+        nos = sd.get("no_obj_embed_spatial")
+        self.no_obj_embed_spatial = None if nos is None else nos.to(self.device)
 
     # -- constants -------------------------------------------------------------------------------------------
     def position_encoding(self, channels: int, size: int, n: int) -> torch.Tensor:
         """Sine position encoding of a (size x size) level, expanded (not copied) to batch n."""
         key = (channels, size)
         if key not in self._pos_cache:
-            self._pos_cache[key] = weights.position_sine(channels, size, size, self.device)
+            pe = torch.empty((channels, size, size), device=self.device, dtype=torch.float32)
+            with self._lock:
+                _lib.check(self.lib.sam2b_position_encoding(channels, size, size, _ptr(pe), self._stream()), "position_encoding")
+            self._pos_cache[key] = pe
         return self._pos_cache[key][None].expand(n, -1, -1, -1)
 
     # -- E1 / E2 ---------------------------------------------------------------------------------------------
-    def image_encode(self, img: torch.Tensor, normalised: bool, add_no_mem_embed: bool):
-        """img [n,3,1024,1024] fp32 CUDA -> (fpn0 [n,32,256,256], fpn1 [n,64,128,128], fpn2 [n,256,64,64])."""
+    def image_encode(self, img: torch.Tensor, normalised: bool, add_no_mem_embed: bool, out=None):
+        """img [n,3,1024,1024] fp32 CUDA -> (fpn0 [n,32,256,256], fpn1 [n,64,128,128], fpn2 [n,256,64,64]).
+        out: optional caller-owned contiguous fp32 CUDA tensors of those shapes (e.g. this rank's slices of an all-gather
+        buffer: the neck then writes its results straight where the collective reads them)."""
         img = _f32c(img, "img")
         if img.dim() != 4 or tuple(img.shape[1:]) != (3, 1024, 1024):
             raise ValueError(f"image_encode expects [n,3,1024,1024], got {tuple(img.shape)}")
         n = img.shape[0]
-        f0 = torch.empty((n, 32, 256, 256), device=self.device, dtype=torch.float32)
-        f1 = torch.empty((n, 64, 128, 128), device=self.device, dtype=torch.float32)
-        f2 = torch.empty((n, 256, 64, 64), device=self.device, dtype=torch.float32)
+        shapes = ((n, 32, 256, 256), (n, 64, 128, 128), (n, 256, 64, 64))
+        if n == 0:
+            return tuple(torch.empty(s, device=self.device, dtype=torch.float32) for s in shapes)
+        if out is None:
+            f0, f1, f2 = (torch.empty(s, device=self.device, dtype=torch.float32) for s in shapes)
+        else:
+            f0, f1, f2 = out
+            for t, s in zip(out, shapes):
+                if tuple(t.shape) != s or t.dtype != torch.float32 or not t.is_contiguous() or t.device != self.device:
+                    raise ValueError(f"image_encode: out tensors must be contiguous fp32 {shapes} on {self.device}")
         with self._lock:
             _lib.check(self.lib.sam2b_image_encode(self._h, _ptr(img), n, int(normalised), int(add_no_mem_embed),
                                                    _ptr(f0), _ptr(f1), _ptr(f2), self._stream()), "image_encode")

@@ -6,11 +6,12 @@ from typing import Optional
 import torch
 
 from . import _lib
-from .engine import _ptr, _stream
+from .engine import _ptr, _stream, on_tensor_device
 
 ACT = {None: 0, "none": 0, "gelu": 1, "relu": 2}
 
 
+@on_tensor_device
 def gemm(a: torch.Tensor, b: torch.Tensor, bias: Optional[torch.Tensor] = None, act=None, alpha: float = 1.0,
          gamma: Optional[torch.Tensor] = None, residual: Optional[torch.Tensor] = None, res_row_mod: int = 0,
          out_dtype=torch.float32, bias_along_m: bool = False, block_n: int = 0) -> torch.Tensor:
@@ -38,6 +39,7 @@ def gemm(a: torch.Tensor, b: torch.Tensor, bias: Optional[torch.Tensor] = None, 
     return out if a.dim() == 3 else out[0]
 
 
+@on_tensor_device
 def layernorm(x: torch.Tensor, gamma: torch.Tensor, beta: torch.Tensor, eps: float, out_dtype=torch.bfloat16):
     lib = _lib.load()
     x = x.contiguous()
@@ -50,6 +52,7 @@ def layernorm(x: torch.Tensor, gamma: torch.Tensor, beta: torch.Tensor, eps: flo
     return y
 
 
+@on_tensor_device
 def cast_bf16(x: torch.Tensor) -> torch.Tensor:
     lib = _lib.load()
     x = x.contiguous()
@@ -58,6 +61,7 @@ def cast_bf16(x: torch.Tensor) -> torch.Tensor:
     return y
 
 
+@on_tensor_device
 def preprocess_u8(hwc: torch.Tensor, normalise: bool = False) -> torch.Tensor:
     """uint8 [N,H,W,3] (or [H,W,3]) on the device -> fp32 [N,3,H,W]: /255 and, if `normalise`, (x - mean) / std with the
     ImageNet constants, bit-identical to the reference's ToTensor -> Normalize (sam2/utils/transforms.py:27-46)."""
@@ -73,6 +77,7 @@ def preprocess_u8(hwc: torch.Tensor, normalise: bool = False) -> torch.Tensor:
     return y
 
 
+@on_tensor_device
 def maxpool2x2_nhwc(x: torch.Tensor) -> torch.Tensor:
     lib = _lib.load()
     B, H, W, Cd = x.shape
@@ -81,6 +86,7 @@ def maxpool2x2_nhwc(x: torch.Tensor) -> torch.Tensor:
     return y
 
 
+@on_tensor_device
 def window_attention(qkv: torch.Tensor, heads: int, ws: int, q_pool: bool) -> torch.Tensor:
     """qkv [B,H,W,3*heads*72] bf16 -> [B,Ho,Wo,heads*72] bf16  (ws == H: global attention)."""
     lib = _lib.load()
@@ -93,6 +99,7 @@ def window_attention(qkv: torch.Tensor, heads: int, ws: int, q_pool: bool) -> to
     return out
 
 
+@on_tensor_device
 def softmax_rows(s: torch.Tensor, ldp: Optional[int] = None) -> torch.Tensor:
     lib = _lib.load()
     rows, cols = s.shape
@@ -102,6 +109,7 @@ def softmax_rows(s: torch.Tensor, ldp: Optional[int] = None) -> torch.Tensor:
     return p
 
 
+@on_tensor_device
 def attention_hd256(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor) -> torch.Tensor:
     """softmax(q k^T / 16) v for q [n,Tq,256], k / v [n,Lk,256] bf16 (single head; the MemoryAttention core)."""
     lib = _lib.load()
@@ -117,6 +125,7 @@ def attention_hd256(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor) -> torch.
     return out
 
 
+@on_tensor_device
 def gemm_ln_producer(a: torch.Tensor, b: torch.Tensor, bias: torch.Tensor, residual: torch.Tensor, block_n: int = 0):
     """x = a @ b^T + bias + residual (fp32) -> (x, bf16(x), stats [M, parts, 2] partial (sum, sum x^2) per row)."""
     lib = _lib.load()
@@ -133,6 +142,7 @@ def gemm_ln_producer(a: torch.Tensor, b: torch.Tensor, bias: torch.Tensor, resid
     return x, xb, stats.flatten()[: M * parts.value * 2].view(M, parts.value, 2)
 
 
+@on_tensor_device
 def gemm_ln_consumer(xb: torch.Tensor, w_scaled: torch.Tensor, bias: torch.Tensor, stats: torch.Tensor,
                      eps: float, act=None, out_dtype=torch.bfloat16, block_n: int = 0) -> torch.Tensor:
     """act(LayerNorm(x) W^T + b) from raw bf16 rows xb: w_scaled = bf16(W diag(gamma) with zero-mean rows), bias = b + W beta."""

@@ -6,9 +6,10 @@ masks in four launches instead of a host loop of six launches per mask."""
 import torch
 
 from . import _lib
-from .engine import _ptr, _stream
+from .engine import _ptr, _stream, on_tensor_device
 
 
+@on_tensor_device
 def get_connected_components(mask: torch.Tensor):
     """mask: bool / uint8 CUDA tensor [N,1,H,W] -> (labels int32 [N,1,H,W], counts int32 [N,1,H,W]).
     Background (False) pixels get label 0 and count 0; every foreground pixel gets a positive label shared by its
@@ -36,6 +37,7 @@ def fill_holes_in_mask_scores(mask: torch.Tensor, max_area: int) -> torch.Tensor
     return torch.where(is_hole, 0.1, mask)
 
 
+@on_tensor_device
 def upsample_masks(low: torch.Tensor, size, threshold=None, return_logits: bool = True):
     """Mask logits [N,C,h,w] (fp32, CUDA) -> output resolution ``size`` = (H, W), bilinear with align_corners=False, in one
     pass; mirrors the ``F.interpolate(masks, orig_hw, mode="bilinear", align_corners=False)`` of

@@ -30,9 +30,8 @@ IMG_STD = (0.229, 0.224, 0.225)
 
 class _Base:
     def __init__(self, state_dict: Dict[str, torch.Tensor], device="cuda", backend="b200"):
-        self.device = torch.device(device)
-        if self.device.type != "cuda":
-            raise RuntimeError("sam2_opt_b200 predictors need a CUDA device (no CPU fallback)")
+        from .engine import normalise_device
+        self.device = normalise_device(device)     # "cuda" -> the current device, once (torchrun: cuda:LOCAL_RANK)
         self.w = {k: v.detach().to(self.device, torch.float32).contiguous() for k, v in state_dict.items() if torch.is_tensor(v)}
         self.engine = None
         self.backend_contexts: List[B200Executor] = []

@@ -8,7 +8,8 @@ sam2/sam2/modeling/sam2_base_official.py:230-276; modeling/memory_attention.py:1
 own ``speedup`` method the new backend name, making ``predictor.speedup("b200")`` work verbatim.
 
 The reference tree is read-only, so this is duck-typed: anything with the same attributes works (the CPU tests drive the
-real reference predictors with a stub engine; on a GPU box the standalone predictors of ``predictor.py`` are used).
+real reference predictors with a stub engine; ``tests/test_speedup_reference_gpu.py`` drives them with the real engine
+on the GPU box, where the unmodified reference sources travel as the git-ignored ``oracle/_ref`` copy).
 """
 import torch
 
@@ -100,6 +101,11 @@ def install(*classes):
         def patched(self, backend="b200", *a, _orig=orig, **k):
             if isinstance(backend, str) and backend.lower() in B200_NAMES:
                 self._sam2b_engine = speedup(self, backend, **{x: k[x] for x in ("engine", "engine_factory", "warmup") if x in k})
+                return None
+            if isinstance(backend, str) and backend.lower() == "torch" and getattr(self, "_sam2b_engine", None) is not None:
+                # the reference's own speedup("torch") resets the image / memory-attention hooks only
+                # (sam2_video_predictor_official.py:58-61); E4 was engaged by us, so it is disengaged here as well
+                speedup(self, "torch")
                 return None
             return _orig(self, backend, *a, **k)
 

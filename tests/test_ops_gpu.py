@@ -96,3 +96,19 @@ def test_attention_hd256(n, Tq, Lk):
     ref = F.scaled_dot_product_attention(q.float()[:, None], k.float()[:, None], v.float()[:, None])[:, 0]
     err = (out.float() - ref).abs().max().item()
     assert err < 2e-2 * ref.abs().max().item(), err     # P rounded to bf16 before PV (2^-8) + bf16 output
+
+
+def test_position_encoding_export_matches_the_reference_formula():
+    """sam2b_position_encoding (the constant vision_pos_enc / mask_memory_pos_enc outputs of E2 / E4) against the oracle's
+    restatement of PositionEmbeddingSine (position_encoding.py:90-124), which oracle/make_golden.py pinned on the
+    reference's own pos outputs.  fp32 sin/cos of arguments up to 2 pi: a few ulp of the argument, 5e-6 absolute."""
+    from oracle import sam2_oracle as O
+    from sam2_opt_b200.engine import Engine
+    from sam2_opt_b200.synth_weights import make_weights
+    eng = Engine(make_weights(0), torch.device("cuda"))
+    for c, size in ((256, 256), (256, 128), (256, 64), (64, 64)):
+        got = eng.position_encoding(c, size, 2)
+        assert got.shape == (2, c, size, size) and got.stride(0) == 0          # a view of one constant, not a copy
+        want = O.position_sine(c, size, size)
+        assert (got[0].cpu() - want).abs().max().item() <= 5e-6, (c, size)
+    eng.release()

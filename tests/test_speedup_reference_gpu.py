@@ -1,0 +1,120 @@
+"""GPU: the REFERENCE's own predictors (unmodified sources: /root/reference, or the oracle/_ref copy on the GPU box) driven
+through `predictor.speedup("b200")` with the REAL sm_100a engine, against the same predictors on the reference torch path
+in strict fp32 on the same device (SURVEY.md §8 rows a19 / b).
+
+Gates (BASELINE.json north_star): predicted-mask IoU >= 0.99, image embeddings / high-res features relative L2 <= 2e-2;
+`speedup("torch")` must restore the reference path bit for bit.  The reference's own per-object batch-1 loop
+(sam2_video_predictor_official.py:689-725), its `.to(device)` hand-offs, the trimmed `none`-variant input list
+(memory_attention.py:376-378) and its executor bookkeeping all run against the real kernels here."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import reference_loader as rl
+
+pytestmark = [pytest.mark.gpu, pytest.mark.skipif(not rl.available(), reason="reference sources not present (run `python -m oracle.build_ref` in the build container)")]
+
+
+def rel_l2(a, b):
+    return ((a.double() - b.double()).norm() / b.double().norm()).item()
+
+
+@pytest.fixture(scope="module")
+def weights():
+    from oracle import sam2_oracle as O
+    return O.make_weights(0)
+
+
+def test_vendored_reference_is_unmodified():
+    """The copy under oracle/_ref (when that is what is being used) still has the sha256 recorded at copy time."""
+    from oracle import build_ref
+    import os
+    if os.path.realpath(rl.REF_ROOT) == os.path.realpath(build_ref.DST_ROOT):
+        assert build_ref.verify()
+
+
+def test_reference_image_predictor_on_the_real_engine(weights, golden):
+    """Config 1 through the reference's SAM2ImagePredictor: set_image + predict, torch path vs speedup("b200")."""
+    import ref_gpu
+    from oracle.synth import synth_image_u8
+    from sam2_opt_b200 import speedup as S
+    from sam2_opt_b200.engine import Engine, launch_count
+    torch.set_grad_enabled(False)
+    m = ref_gpu.build("base", weights)
+    from sam2.sam2_image_predictor import SAM2ImagePredictor
+    S.install(SAM2ImagePredictor)
+    pred = SAM2ImagePredictor(m)
+    img = synth_image_u8(0)
+    kw = dict(point_coords=np.array([[512, 512]]), point_labels=np.array([1]), multimask_output=True, return_logits=True)
+
+    pred.set_image(img)
+    ref_feats = [pred._features["high_res_feats"][0].clone(), pred._features["high_res_feats"][1].clone(), pred._features["image_embed"].clone()]
+    ref_masks, ref_iou, ref_low = pred.predict(**kw)
+    # the reference on this GPU in strict fp32 agrees with the committed CPU fixtures (made by the same sources on CPU)
+    cpu_bits = np.unpackbits(golden["c1_low_res_bits"]).reshape(3, 256, 256).astype(bool)
+    assert min(ref_gpu.iou(ref_low[i] > 0, cpu_bits[i]) for i in range(3)) >= 0.999
+    np.testing.assert_allclose(ref_iou, golden["c1_iou"], atol=1e-4)
+
+    l0 = launch_count()
+    pred.speedup("b200")
+    assert isinstance(pred._sam2b_engine, Engine) and len(pred.backend_contexts) == 1
+    pred.set_image(img)
+    assert launch_count() > l0, "speedup('b200') did not launch a single sam2b kernel"
+    got_feats = [pred._features["high_res_feats"][0], pred._features["high_res_feats"][1], pred._features["image_embed"]]
+    rels = [rel_l2(g, r) for g, r in zip(got_feats, ref_feats)]
+    masks, iou, low = pred.predict(**kw)
+    ious = [ref_gpu.iou(low[i] > 0, ref_low[i] > 0) for i in range(3)]
+    ious_full = [ref_gpu.iou(masks[i] > 0, ref_masks[i] > 0) for i in range(3)]
+    print("reference SAM2ImagePredictor + b200 engine: feature rel-L2", [f"{r:.4%}" for r in rels],
+          "low-res IoU", [f"{v:.4f}" for v in ious], "1024^2 IoU", [f"{v:.4f}" for v in ious_full])
+    assert max(rels) <= 2e-2
+    assert min(ious) >= 0.99 and min(ious_full) >= 0.99
+    assert np.abs(iou - ref_iou).max() < 2e-2
+
+    ctx = pred.backend_contexts[0]
+    pred.speedup("torch")                       # reference path restored, bit for bit
+    assert pred.backend_contexts == [] and ctx._released
+    pred.set_image(img)
+    for a, b in zip([pred._features["high_res_feats"][0], pred._features["high_res_feats"][1], pred._features["image_embed"]], ref_feats):
+        assert torch.equal(a, b)
+    again = pred.predict(**kw)
+    assert np.array_equal(again[2], ref_low)
+    pred._sam2b_engine.release()
+
+
+def test_reference_video_predictor_on_the_real_engine(weights):
+    """Config 3 (first 16 frames: the 7-frame bank fills at frame 7, pointers keep growing to 15) through the reference's
+    SAM2VideoPredictor and its own per-object loop: two objects, torch path vs speedup("b200") on the same device."""
+    import ref_gpu
+    from oracle.synth import synth_video
+    from sam2_opt_b200 import speedup as S
+    from sam2_opt_b200.engine import launch_count
+    torch.set_grad_enabled(False)
+    T = 16
+    frames = synth_video(T, seed=1)
+    clicks = {1: (512.0, 512.0), 2: (300.0, 700.0)}
+    m = ref_gpu.build("video", weights)
+    S.install(type(m))
+    ref = ref_gpu.propagate_low_res(m, frames, clicks)
+
+    l0 = launch_count()
+    m.speedup("b200")
+    assert [c.kind for c in m.memory_attention.backend_contexts] == ["memory_attention_none", "memory_attention_exclude"]
+    got = ref_gpu.propagate_low_res(m, frames, clicks)
+    n_launch = launch_count() - l0
+    assert n_launch > 1000, n_launch
+    assert sorted(got) == list(range(T))
+    for oid in clicks:
+        ious = [ref_gpu.iou(got[t][oid] > 0, ref[t][oid] > 0) for t in range(T)]
+        print(f"reference SAM2VideoPredictor + b200 engine, object {oid}: per-frame IoU min {min(ious):.4f}", [f"{v:.4f}" for v in ious])
+        assert min(ious) >= 0.99
+
+    engine = m._sam2b_engine
+    m.speedup("torch")
+    assert m.inference_image == m.inference_image_torch and m.memory_attention.backend_contexts == []
+    again = ref_gpu.propagate_low_res(m, frames, {1: clicks[1]}, max_track=2)
+    for t in range(3):
+        # frames 0-2 of a one-object run on the restored torch path equal the first torch run's object 1 bit for bit
+        # (the reference tracks every object separately with batch 1)
+        assert torch.equal(again[t][1], ref[t][1])
+    engine.release()
