@@ -1,18 +1,20 @@
 #!/usr/bin/env python
 """Headline benchmark: SAM2.1 Hiera-L image-encoder forward (BASELINE.json configs[1]: batch 32 synthetic
-1024x1024 images per GPU) -> images/s.
+1024x1024 images per GPU) -> images/s, plus the video legs (configs[2] and configs[3]).
 
     python bench.py --gpus 1 --steps 5 --warmup 3
     python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 --master-port P \
         bench.py --gpus N --steps K --warmup W
-    python bench.py --impl reference ...     # the reference algorithm's CPU path (oracle port) on the host cores
+    python bench.py --impl reference ...     # the UNMODIFIED reference's CPU torch path (oracle/_ref) on the host cores
+    python bench.py --sweep                  # config 5 table: batch 1..256 per run, compute-only and with the gather
 
 One "step" = one pass of the hot path (`sam2b_image_encode`: Hiera trunk + FpnNeck + conv_s0/s1, boundary E2) over one
 batch of seeded synthetic, already-normalised images.  `value`: inputs resident in HBM, CUDA-event timed, max over ranks.
 `e2e`: the same metric through the plugin's host-buffer entry point (`sam2b_image_encode_host`, pinned host tensors,
 H2D of the images and D2H of all three outputs inside the timed region).  N > 1: every rank encodes its own batch
-(weak scaling, batch-sharded config 5) and the embeddings (fpn2 level) are all-gathered with NCCL inside the timed
-region, as north_star prescribes.
+(weak scaling, batch-sharded config 5); all three feature levels (feat0, feat1, feat2) are gathered onto every rank inside
+the timed region — the neck writes them straight into this rank's slice of the gather buffer and the transfer of step k
+overlaps the trunk of step k+1 (sam2_opt_b200/shard.py: `EmbeddingGather`).
 """
 import argparse
 import json
@@ -27,6 +29,8 @@ sys.path.insert(0, ROOT)
 
 GFLOP_PER_IMAGE = 1822.8      # algorithmic work of forward_image per 1024^2 image
 METRIC = "Hiera-L 1024^2 image-encoder images/sec"
+CPU_SAMPLE_IMAGES = 4         # bounded sample of the batch-32 workload per CPU step (about 10-30 s of host work per run)
+CPU_VIDEO_FRAMES = 3          # reference propagate_in_video on the host cores: 1 prompted + 2 tracked frames
 
 
 def _peaks():
@@ -35,6 +39,15 @@ def _peaks():
         d = json.load(open(p))
         return d.get("bf16_tflops_sustained", 1400.0), d.get("hbm_gbs", 6650.0), "measured (MEASURED_PEAKS.json, sustained)"
     return 1400.0, 6650.0, "fallback (B200_PROFILING.md)"
+
+
+def host_threads():
+    """All the host threads this process may use.  torchrun exports OMP_NUM_THREADS=1 to its workers; a CPU baseline must
+    not inherit that, so the CPU legs call torch.set_num_threads(host_threads()) explicitly."""
+    try:
+        return len(os.sched_getaffinity(0))
+    except Exception:
+        return os.cpu_count() or 1
 
 
 class ClockSampler:
@@ -76,30 +89,116 @@ class ClockSampler:
                 if v.lower().startswith("active"):
                     reasons.add(name)
         sm.sort()
-        # median over samples under load (upper half of the sorted clocks excludes idle samples at the edges)
         med = sm[len(sm) // 2] if sm else None
         return {"sm_mhz": med, "sm_max_mhz": mx or None, "reasons": sorted(reasons), "samples": len(sm)}
 
 
-CPU_SAMPLE_IMAGES = 4      # bounded sample of the batch-32 workload per CPU step (about 10-30 s of host work per run)
+# ---------------------------------------------------------------------------------------------------------------------
+# The reference on the host cores / on the same GPU (oracle/_ref = byte-identical copy of the reference sources; the oracle
+# port only when that copy is missing)
+# ---------------------------------------------------------------------------------------------------------------------
+def _reference_model(kind, device="cpu"):
+    """-> (callable forward_image(img) or None, model or None, kind string)"""
+    import torch
+    from oracle import reference_loader as rl
+    from oracle import sam2_oracle as O
+    w = O.make_weights(0)
+    if rl.available():
+        m = rl.build_reference(kind)
+        m.load_state_dict(w, strict=True)
+        return m.to(device).eval(), "reference"
+    return w, "port"
 
 
 def cpu_reference_images_per_s(n_images, steps, warmup):
-    """The reference algorithm's fp32 CPU path (oracle port of the reference torch code) on the host cores."""
+    """The reference's own fp32 CPU path (`SAM2Base.forward_image`, sam2_base_official.py:548-564) on all host threads."""
     import torch
     from oracle import sam2_oracle as O
     from sam2_opt_b200.synth import synth_image_norm
     torch.set_grad_enabled(False)
-    w = O.make_weights(0, only_prefix=("image_encoder.", "sam_mask_decoder.conv_s", "no_mem"))
+    cores = host_threads()
+    torch.set_num_threads(cores)
+    m, kind = _reference_model("video")
+    fwd = (lambda x: m.forward_image(x)) if kind == "reference" else (lambda x: O.forward_image(m, x))
     img = synth_image_norm(n_images, seed=1)
     for _ in range(warmup):
-        O.forward_image(w, img[:1])
+        fwd(img[:1])
     times = []
     for _ in range(steps):
         t0 = time.perf_counter()
-        O.forward_image(w, img)
+        fwd(img)
         times.append(time.perf_counter() - t0)
-    return n_images * len(times) / sum(times), torch.get_num_threads(), times
+    return n_images * len(times) / sum(times), torch.get_num_threads(), times, kind
+
+
+def cpu_reference_video_fps(n_frames):
+    """The reference's SAM2VideoPredictor.propagate_in_video on the host cores, first `n_frames` frames of a 64-frame
+    clip (clip length enters the pointer encodings only), one object, one click."""
+    import numpy as np
+    import torch
+    from oracle import reference_loader as rl
+    from sam2_opt_b200.synth import synth_video
+    torch.set_grad_enabled(False)
+    cores = host_threads()
+    torch.set_num_threads(cores)
+    frames = synth_video(n_frames, seed=1)
+    if rl.available():
+        m, _ = _reference_model("video")
+        import sam2.sam2_video_predictor_official as vp
+        vp.load_video_frames = lambda **k: (frames, 1024, 1024)
+        st = m.init_state("synthetic")
+        m.add_new_points_or_box(st, 0, 1, points=np.array([[512, 512]], dtype=np.float32), labels=np.array([1], np.int32))
+        t0 = time.perf_counter()
+        n = sum(1 for _ in m.propagate_in_video(st))
+        return n / (time.perf_counter() - t0), cores, "reference"
+    from oracle import sam2_oracle as O
+    w = O.make_weights(0)
+    t0 = time.perf_counter()
+    n = sum(1 for _ in O.video_propagate(w, frames))
+    return n / (time.perf_counter() - t0), cores, "port"
+
+
+def torch_gpu_baseline(dev, batch):
+    """The "same GPU" comparison: the UNMODIFIED reference `forward_image` (cuBLAS / cuDNN /
+    SDPA eager torch) on this B200, strict fp32 (TF32 off for matmul and cuDNN) and bf16 autocast (the precision precedent of
+    sam2/sam2/benchmark.py:20-92), CUDA-event timed."""
+    import torch
+    from sam2_opt_b200.synth import synth_image_norm
+    torch.set_grad_enabled(False)
+    m, kind = _reference_model("video", dev)
+    if kind != "reference":
+        return {"unavailable": "reference sources (oracle/_ref) not present"}
+    out = {"kind": "reference", "api": "SAM2Base.forward_image (unmodified reference, eager torch)", "unit": "images/s"}
+    for name in ("bf16_autocast", "fp32"):
+        b = batch
+        while b >= 1:
+            try:
+                img = synth_image_norm(b, seed=1).to(dev)
+                torch.backends.cuda.matmul.allow_tf32 = False
+                torch.backends.cudnn.allow_tf32 = False
+                ctx = torch.autocast("cuda", dtype=torch.bfloat16) if name == "bf16_autocast" else torch.autocast("cuda", enabled=False)
+                reps = 3 if name == "bf16_autocast" else 2
+                with ctx:
+                    m.forward_image(img)
+                    torch.cuda.synchronize(dev)
+                    a, z = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                    a.record()
+                    for _ in range(reps):
+                        m.forward_image(img)
+                    z.record()
+                torch.cuda.synchronize(dev)
+                ms = a.elapsed_time(z) / reps
+                out[name] = {"value": b / (ms / 1e3), "batch": b, "ms_per_step": ms, "timed_steps": reps, "warmup": 1,
+                             "tf32": False if name == "fp32" else "n/a"}
+                break
+            except torch.cuda.OutOfMemoryError:
+                torch.cuda.empty_cache()
+                b //= 2
+        del img
+        torch.cuda.empty_cache()
+    del m
+    torch.cuda.empty_cache()
+    return out
 
 
 def run_reference(args):
@@ -107,16 +206,44 @@ def run_reference(args):
     if rank != 0:
         return
     steps, warmup = max(1, min(args.steps, 5)), min(args.warmup, 1)
-    v, cores, times = cpu_reference_images_per_s(CPU_SAMPLE_IMAGES, steps, warmup)
-    sample = f"{steps} step(s) x {CPU_SAMPLE_IMAGES} images of the batch-{args.batch} workload (fp32 torch CPU port of the reference path), {warmup} warm-up"
+    v, cores, times, kind = cpu_reference_images_per_s(CPU_SAMPLE_IMAGES, steps, warmup)
+    what = ("the unmodified reference SAM2Base.forward_image (oracle/_ref), fp32 torch" if kind == "reference"
+            else "fp32 torch CPU port of the reference path (oracle/sam2_oracle.py)")
+    sample = f"{steps} step(s) x {CPU_SAMPLE_IMAGES} images of the batch-{args.batch} workload: {what}, {cores} host threads, {warmup} single-image warm-up"
     print(json.dumps({
         "impl": "reference", "metric": METRIC, "value": v, "unit": "images/s", "n_gpus": args.gpus, "steps": steps,
         "warmup": warmup, "ms_per_step": 1e3 * sum(times) / len(times), "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": f"SAM2.1 Hiera-L image-encoder forward (E2), batch {args.batch} x 1024x1024 per GPU", "sample_images_per_step": CPU_SAMPLE_IMAGES},
-        "cpu_baseline": {"value": v, "unit": "images/s", "cores": cores, "kind": "port", "sample": sample},
+        "config": {"workload": f"SAM2.1 Hiera-L image-encoder forward (E2), batch {args.batch} x 1024x1024 per GPU; CPU arm: a {CPU_SAMPLE_IMAGES}-image sample of that batch per step (CPU throughput is flat in the batch size)",
+                   "sample_images_per_step": CPU_SAMPLE_IMAGES},
+        "cpu_baseline": {"value": v, "unit": "images/s", "cores": cores, "kind": kind, "sample": sample},
         "e2e": {"value": v, "unit": "images/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }))
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# video legs
+# ---------------------------------------------------------------------------------------------------------------------
+def grid_clicks(n_objects):
+    """config 4: clicks on a g x g grid of points (16 objects -> 4 x 4); one object -> the image centre (config 3)."""
+    if n_objects == 1:
+        return [[512.0, 512.0]]
+    g = max(1, int(n_objects ** 0.5 + 0.999))
+    return [[128 + 768.0 * (o % g) / max(1, g - 1), 128 + 768.0 * (o // g) / max(1, g - 1)] for o in range(n_objects)]
+
+
+def run_clip(vp, clip, clicks, obj_lo=0, obj_hi=None, consume=True):
+    """One propagate_in_video pass; returns the per-frame host timestamps (the caller consumes every frame's masks)."""
+    st = vp.init_state(clip)
+    obj_hi = len(clicks) if obj_hi is None else obj_hi
+    for o in range(obj_lo, obj_hi):
+        vp.add_new_points_or_box(st, 0, o, points=[clicks[o]], labels=[1])
+    stamps = [time.perf_counter()]
+    for t, ids, masks in vp.propagate_in_video(st):
+        if consume:
+            (masks > 0).any().item()          # D2H read per frame
+        stamps.append(time.perf_counter())
+    return stamps
 
 
 def main():
@@ -127,16 +254,20 @@ def main():
     ap.add_argument("--batch", type=int, default=32, help="images per GPU per step (configs[1]: 32)")
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--video-frames", type=int, default=40, help="frames of the propagate_in_video leg (0 = skip it)")
-    ap.add_argument("--video-objects", type=int, default=1)
+    ap.add_argument("--no-torch-gpu-baseline", action="store_true")
+    ap.add_argument("--video-frames", type=int, default=64, help="frames per clip of the video legs (configs[2]/[3]: 64; 0 = skip them)")
+    ap.add_argument("--video-objects", type=int, default=16, help="objects per video of the config-4 leg (0 = skip it)")
+    ap.add_argument("--videos", type=int, default=8, help="videos of the config-4 leg, sharded over the ranks")
+    ap.add_argument("--gather", default="auto", choices=["auto", "p2p", "nccl", "none"], help="N > 1: how the three feature levels are gathered")
+    ap.add_argument("--sweep", action="store_true", help="config 5: batch sweep 1..256 (prints one JSON table, no headline line)")
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference(args)
 
     import torch
     import torch.distributed as dist
-    from sam2_opt_b200 import build, engine as E
-    from sam2_opt_b200.synth import synth_image_norm
+    from sam2_opt_b200 import build, engine as E, shard
+    from sam2_opt_b200.synth import synth_image_norm, synth_video
 
     build.build()
     rank, world = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1"))
@@ -149,47 +280,71 @@ def main():
 
     # random-init weights of the exact architecture (no checkpoints offline): same generator the parity tests use
     from sam2_opt_b200.synth_weights import make_weights
-    eng = E.Engine(make_weights(0), dev)
-    B = args.batch
-    img_host = synth_image_norm(B, seed=1 + rank).pin_memory()
-    img = img_host.to(dev)
-    outs_host = None
+    weights = make_weights(0)
+    eng = E.Engine(weights, dev)
 
     def barrier():
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
 
-    gathered = None
-    def step():
-        nonlocal gathered
-        f0, f1, f2 = eng.image_encode(img, True, False)
+    def allmax(vals):
+        t = torch.tensor(vals, device=dev, dtype=torch.float64)
         if world > 1:
-            if gathered is None:
-                gathered = torch.empty((world * B, 256, 64, 64), device=dev, dtype=torch.float32)
-            dist.all_gather_into_tensor(gathered, f2)
-        return f2
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return t.tolist()
 
-    for _ in range(warmup):
-        step()
-    barrier()
-    l0 = E.launch_count()
-    t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    with ClockSampler(local) as clk:
+    def timed_encode(B, steps, warm, gather_mode):
+        """`steps` passes over a batch of B images per rank with the gather of all three levels; -> (ms total, max over ranks)"""
+        img = synth_image_norm(B, seed=1 + rank).to(dev)
+        g = shard.EmbeddingGather(B, dev, mode=gather_mode if world > 1 else "none")
+        k = 0
+        for _ in range(warm):
+            eng.image_encode(img, True, False, out=g.local_out(k)); g.publish(k); k += 1
+        g.drain()
+        barrier()
+        t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         barrier()
         t0.record()
-        for _ in range(args.steps):
-            step()
+        for _ in range(steps):
+            eng.image_encode(img, True, False, out=g.local_out(k)); g.publish(k); k += 1
+        g.drain()                 # the compute stream waits for the last transfers: they are inside the timed region
         t1.record()
         barrier()
-    launches = E.launch_count() - l0
-    ms = torch.tensor([t0.elapsed_time(t1)], device=dev, dtype=torch.float64)
-    if world > 1:
-        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
-    ms_total = ms.item()
+        ms = allmax([t0.elapsed_time(t1)])[0]
+        desc = g.describe()
+        g.close()
+        del img
+        return ms, desc
+
+    if args.sweep:
+        rows = []
+        for B in (1, 2, 4, 8, 16, 32, 64, 128, 256):
+            steps = 3 if B >= 64 else 5
+            ms_c, _ = timed_encode(B, steps, 2, "none")
+            row = {"batch_per_gpu": B, "global_batch": B * world, "images_per_s_compute_only": world * B * steps / (ms_c / 1e3)}
+            if world > 1:
+                ms_g, desc = timed_encode(B, steps, 2, args.gather)
+                row.update({"images_per_s_with_gather": world * B * steps / (ms_g / 1e3), "gather": desc})
+            rows.append(row)
+            torch.cuda.empty_cache()
+        if rank == 0:
+            print(json.dumps({"config": "BASELINE.json configs[4]: Hiera-L image-encoder throughput sweep, batch-sharded", "n_gpus": world, "rows": rows}))
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    B = args.batch
+    # ---- headline: device-resident inputs ---------------------------------------------------------------------------
+    with ClockSampler(local) as clk:
+        l0 = E.launch_count()
+        ms_total, gather_desc = timed_encode(B, args.steps, warmup, args.gather)
+        launches = (E.launch_count() - l0) * args.steps // (args.steps + warmup)
     value = world * B * args.steps / (ms_total / 1e3)
 
     # ---- e2e: host buffers through the plugin entry point -------------------------------------------------
+    img_host = synth_image_norm(B, seed=1 + rank).pin_memory()
+    outs_host = None
     for _ in range(2):
         outs_host = eng.image_encode_host(img_host, True, False, outs_host)
     barrier()
@@ -200,10 +355,8 @@ def main():
         outs_host = eng.image_encode_host(img_host, True, False, outs_host)
     c1.record()
     barrier()
-    e_ms = torch.tensor([max(c0.elapsed_time(c1), 0.0), (time.perf_counter() - e0) * 1e3], device=dev, dtype=torch.float64)
-    if world > 1:
-        dist.all_reduce(e_ms, op=dist.ReduceOp.MAX)
-    e2e_value = world * B * args.steps / (max(e_ms.tolist()) / 1e3)
+    e_ms = allmax([max(c0.elapsed_time(c1), 0.0), (time.perf_counter() - e0) * 1e3])
+    e2e_value = world * B * args.steps / (max(e_ms) / 1e3)
     h2d = img_host.numel() * 4
     d2h = sum(o.numel() * 4 for o in outs_host)
 
@@ -216,77 +369,123 @@ def main():
     for _ in range(args.steps):
         outs_host = eng.image_encode_host_u8(raw_host, False, outs_host)
     barrier()
-    u_ms = torch.tensor([(time.perf_counter() - u0) * 1e3], device=dev, dtype=torch.float64)
-    if world > 1:
-        dist.all_reduce(u_ms, op=dist.ReduceOp.MAX)
-    e2e_u8_value = world * B * args.steps / (u_ms.item() / 1e3)
+    e2e_u8_value = world * B * args.steps / (allmax([(time.perf_counter() - u0) * 1e3])[0] / 1e3)
+    raw_bytes = raw_host.numel()
+    del raw_host, outs_host
 
     # ---- roofline of the dominant kernel (tcgen05 GEMM): live CUDA-event pairs around every launch of one more step
     roof = None
     if rank == 0:
+        img = img_host.to(dev)
         E.profile_begin()
         eng.image_encode(img, True, False)        # rank-local: no collective here (only rank 0 runs this leg)
         rows = E.profile_end()
+        del img
         g = [(ms_, fl) for name, ms_, fl, by in rows if name.startswith("gemm")]
         all_ms = sum(r[1] for r in rows)
         g_ms, g_fl = sum(x[0] for x in g), sum(x[1] for x in g)
         peak, hbm, how = _peaks()
         ach = g_fl / (g_ms * 1e-3) / 1e12
         traffic, traffic_note = None, None
-        tp = os.path.join(ROOT, "profiles", "r1e_traffic.json")
+        tp = os.path.join(ROOT, "profiles", "r2_traffic.json")
         if os.path.exists(tp):
             tj = json.load(open(tp))
             traffic = tj["dram_bytes_per_launch_avg"]
-            traffic_note = ("bytes per launch (dram__bytes_read.sum + dram__bytes_write.sum), mean of the four stage-3 GEMM forms "
-                            "at batch 16 from one ncu --set full capture: " + tj["source"])
+            traffic_note = tj["note"]
+        by_kernel = {}
+        for name, ms_, fl, by in rows:
+            k = name.split(" ")[0]
+            by_kernel[k] = by_kernel.get(k, 0.0) + ms_
         roof = {"bound": "tensor", "achieved": ach, "peak": peak, "unit": "TFLOP/s", "frac": ach / peak, "traffic": traffic,
                 "traffic_note": traffic_note,
                 "kernel": "gemm_bf16_tcgen05_kernel", "launches_per_step": len(g), "avg_launch_ms": g_ms / max(1, len(g)),
                 "share_of_step_kernel_time": g_ms / all_ms, "peak_source": how,
                 "flops_per_launch_avg": g_fl / max(1, len(g)),
+                "kernel_time_ms_by_family": {k: round(v, 3) for k, v in sorted(by_kernel.items(), key=lambda kv: -kv[1])},
                 "note": "algorithmic 2MNK flops of every GEMM launch of one step / sum of their CUDA-event durations on the launching stream"}
+    del img_host
+    eng.release()
+    torch.cuda.empty_cache()
 
-    # ---- second headline metric (BASELINE.json: "video frames/sec propagated"): propagate_in_video through the public
-    # predictor API, one synthetic clip and one prompted object per rank (videos shard across GPUs, config 3/4 shapes)
-    video = None
+    # ---- video legs (BASELINE.json: "video frames/sec propagated") through the public predictor API ----------------------
+    video, video16 = None, None
     if args.video_frames > 0:
         from sam2_opt_b200.predictor import SAM2VideoPredictor
-        from sam2_opt_b200.synth import synth_video
-        eng.release()
-        vp = SAM2VideoPredictor(make_weights(0), device=dev)
-        clip = synth_video(args.video_frames, seed=1 + rank).pin_memory()
-        t_steady, n_steady, t_all = 0.0, 0, 0.0
-        for rep in range(2):                      # first pass warms allocator / workspaces
-            st = vp.init_state(clip)
-            for o in range(args.video_objects):
-                g = max(1, int(args.video_objects ** 0.5 + 0.999))
-                xy = [512.0, 512.0] if args.video_objects == 1 else [128 + 768.0 * (o % g) / max(1, g - 1), 128 + 768.0 * (o // g) / max(1, g - 1)]
-                vp.add_new_points_or_box(st, 0, o, points=[xy], labels=[1])
-            barrier()
-            stamps = [time.perf_counter()]
-            for t, ids, masks in vp.propagate_in_video(st):
-                (masks > 0).any().item()          # the caller consumes every frame's masks (D2H read per frame)
-                stamps.append(time.perf_counter())
-            if rep == 1:
-                t_all = stamps[-1] - stamps[0]
-                s0 = min(16, len(stamps) - 2)      # steady state: full 7-frame bank + 16 object pointers from frame 16 on
-                t_steady, n_steady = stamps[-1] - stamps[s0], len(stamps) - 1 - s0
-        vt = torch.tensor([t_all, t_steady], device=dev, dtype=torch.float64)
-        if world > 1:
-            dist.all_reduce(vt, op=dist.ReduceOp.MAX)
-        t_all, t_steady = vt.tolist()
+        vp = SAM2VideoPredictor(weights, device=dev)
+        T = args.video_frames
+        # config 3: one clip, one object per rank (N ranks = N independent videos)
+        clip = synth_video(T, seed=1 + rank).pin_memory()
+        run_clip(vp, clip, grid_clicks(1))                     # first pass warms allocator / workspaces / the heads graph
+        barrier()
+        stamps = run_clip(vp, clip, grid_clicks(1))
+        s0 = min(16, len(stamps) - 2)      # steady state: full 7-frame bank + 16 object pointers from frame 16 on
+        t_all, t_steady = allmax([stamps[-1] - stamps[0], stamps[-1] - stamps[s0]])
+        n_steady = len(stamps) - 1 - s0
         video = {"metric": "video frames/sec propagated (SAM2VideoPredictor.propagate_in_video)", "unit": "frames/s",
-                 "value_steady": world * n_steady / t_steady, "value_overall": world * args.video_frames / t_all,
-                 "frames_per_video": args.video_frames, "objects_per_video": args.video_objects, "videos": world,
-                 "object_frames_per_s_steady": world * args.video_objects * n_steady / t_steady,
+                 "config": "BASELINE.json configs[2]: 1 object, 64 synthetic 1024x1024 frames, 7-frame memory bank" if T == 64 else f"{T}-frame clip, 1 object",
+                 "value_steady": world * n_steady / t_steady, "value_overall": world * T / t_all,
+                 "frames_per_video": T, "objects_per_video": 1, "videos": world,
                  "timing": "host wall clock around the generator incl. H2D of frames and a D2H read of every frame's masks, max over ranks; steady = frames >= 16 (7-frame memory bank, 16 pointers)"}
+        if rank == 0:
+            # roofline of the video path's dominant kernel (hd-256 flash attention over the memory bank), live CUDA events
+            E.profile_begin()
+            run_clip(vp, clip[:24], grid_clicks(1))
+            rows = E.profile_end()
+            a = [(ms_, fl) for name, ms_, fl, by in rows if name.startswith("attn256 ")]
+            cross = [(ms_, fl) for name, ms_, fl, by in rows if name.startswith("attn256 ") and " k28" in name]
+            a_ms, a_fl = sum(x[0] for x in a), sum(x[1] for x in a)
+            c_ms, c_fl = sum(x[0] for x in cross), sum(x[1] for x in cross)
+            peak, _, how = _peaks()
+            tot = sum(r[1] for r in rows)
+            video["roofline"] = {"bound": "tensor", "kernel": "flash_attn_hd256_tcgen05_kernel", "achieved": a_fl / (a_ms * 1e-3) / 1e12 if a_ms else None,
+                                 "peak": peak, "unit": "TFLOP/s", "frac": (a_fl / (a_ms * 1e-3) / 1e12 / peak) if a_ms else None,
+                                 "achieved_full_bank_cross_attention": c_fl / (c_ms * 1e-3) / 1e12 if c_ms else None,
+                                 "launches": len(a), "share_of_library_kernel_time": a_ms / tot if tot else None, "peak_source": how, "traffic": None,
+                                 "note": "sum of 4*4096*Lk*256 flops over every hd-256 attention launch of a 24-frame clip / sum of their CUDA-event durations"}
+        del clip
+        # config 4: `videos` videos x `video_objects` objects, videos (then objects) sharded over the ranks
+        if args.video_objects > 0:
+            nobj = args.video_objects
+            mine = shard.shard_videos_objects(args.videos, nobj, world, rank)
+            clicks = grid_clicks(nobj)
+            clips = {v: synth_video(T, seed=100 + v).pin_memory() for v, _, _ in mine}
+            if mine:
+                v0, lo0, hi0 = mine[0]
+                run_clip(vp, clips[v0][:20], clicks, lo0, hi0)      # warm-up: workspaces and the heads graph of this object count
+            barrier()
+            w0 = time.perf_counter()
+            per_video = []
+            for v, lo, hi in mine:
+                st_ = run_clip(vp, clips[v], clicks, lo, hi)
+                per_video.append(st_[-1] - st_[0])
+            torch.cuda.synchronize()
+            t_mine = time.perf_counter() - w0
+            t_job = allmax([t_mine])[0]
+            video16 = {"metric": "video propagation, aggregate object-frames/s", "unit": "object-frames/s",
+                       "config": f"BASELINE.json configs[3]: {args.videos} videos x {nobj} objects x {T} frames sharded over {world} GPU(s) (shard.shard_videos_objects: videos first, then objects)",
+                       "value": args.videos * nobj * T / t_job, "video_frames_per_s": args.videos * T / t_job,
+                       "videos": args.videos, "objects_per_video": nobj, "frames_per_video": T, "seconds": t_job,
+                       "rank0_seconds_per_video": [round(x, 3) for x in per_video],
+                       "timing": "host wall clock from a barrier until the slowest rank has consumed its last frame (H2D of frames and a D2H mask read per frame inside)"}
+            del clips
         vp.release()
+        torch.cuda.empty_cache()
 
-    cpu = None
+    # ---- baselines: the reference on the host cores and on this GPU (rank 0, N = 1 only) ---------------------------------
+    cpu, tgpu = None, None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
-        v, cores, times = cpu_reference_images_per_s(CPU_SAMPLE_IMAGES, 2, 1)
-        cpu = {"value": v, "unit": "images/s", "cores": cores, "kind": "port",
-               "sample": f"2 timed forward_image calls on {CPU_SAMPLE_IMAGES} images of the workload (fp32 torch CPU port of the reference path, all host threads), 1 single-image warm-up"}
+        v, cores, times, kind = cpu_reference_images_per_s(CPU_SAMPLE_IMAGES, 2, 1)
+        cpu = {"value": v, "unit": "images/s", "cores": cores, "kind": kind,
+               "sample": f"2 timed forward_image calls on {CPU_SAMPLE_IMAGES} images of the workload ({'the unmodified reference SAM2Base.forward_image from oracle/_ref' if kind == 'reference' else 'oracle port'}, fp32 torch, {cores} host threads), 1 single-image warm-up"}
+        if video is not None:
+            fps, cores, kind = cpu_reference_video_fps(CPU_VIDEO_FRAMES)
+            video["cpu_baseline"] = {"value": fps, "unit": "frames/s", "cores": cores, "kind": kind,
+                                     "sample": f"the reference SAM2VideoPredictor.propagate_in_video on the first {CPU_VIDEO_FRAMES} frames (1 prompted + {CPU_VIDEO_FRAMES - 1} tracked; the bank is not full yet, so this flatters the CPU)"}
+    if rank == 0 and world == 1 and not args.no_torch_gpu_baseline:
+        try:
+            tgpu = torch_gpu_baseline(dev, B)
+        except Exception as ex:      # a baseline must never take the headline line down with it
+            tgpu = {"unavailable": f"{type(ex).__name__}: {ex}"[:300]}
 
     if rank == 0:
         print(json.dumps({
@@ -295,15 +494,15 @@ def main():
             "dtype": "bf16", "data": "synthetic",
             "config": {"workload": f"SAM2.1 Hiera-L image-encoder forward (boundary E2: trunk+FpnNeck+conv_s0/s1), batch {B} x 3x1024x1024 fp32 per GPU, random-init weights",
                        "batch_per_gpu": B, "global_batch": B * world, "sharding": "batch" if world > 1 else "none",
-                       "collective": "nccl all_gather_into_tensor(fpn2 embeddings) in the timed region" if world > 1 else "none",
+                       "collective": gather_desc,
                        "l2": "inputs (403 MB/step) and activations exceed the 126 MB L2; no explicit flush"},
             "tflops_algorithmic": value * GFLOP_PER_IMAGE / 1e3,
             "clocks": clk.summary(), "gpu_launches": int(launches),
             "e2e": {"value": e2e_value, "unit": "images/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "api": "Engine.image_encode_host -> sam2b_image_encode_host (pinned host in/out)"},
-            "e2e_u8_frames": {"value": e2e_u8_value, "unit": "images/s", "h2d_bytes_per_step": raw_host.numel(), "d2h_bytes_per_step": d2h,
+            "e2e_u8_frames": {"value": e2e_u8_value, "unit": "images/s", "h2d_bytes_per_step": raw_bytes, "d2h_bytes_per_step": d2h,
                               "api": "Engine.image_encode_host_u8 -> sam2b_image_encode_host_u8 (raw uint8 HWC frames, pinned; host wall clock)"},
-            "roofline": roof, "cpu_baseline": cpu, "video": video,
+            "roofline": roof, "cpu_baseline": cpu, "torch_gpu_baseline": tgpu, "video": video, "video_config4": video16,
         }))
     if world > 1:
         dist.destroy_process_group()

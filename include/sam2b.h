@@ -79,6 +79,20 @@ int sam2b_memory_attention(sam2b_handle h, const float* curr, const float* curr_
  * (the second reference output, the sine position encoding, is a constant: sam2b_position_encoding) */
 int sam2b_memory_encode(sam2b_handle h, const float* pix_feat, const float* masks, int n, float* out_x, void* stream);
 
+/* ---- peer memory for the embedding gather (the only collective of the path) ----
+ * The reference has no multi-GPU inference path (one process, one GPU: sam2/ytools/tensorrt/tensorrt_executor.py:26-29);
+ * this is the B200-box replacement: one process per GPU, every rank owns a gather buffer that its peers map through CUDA
+ * IPC, the neck writes its results straight into the local buffer and sam2b_peer_copy pushes them to the peers over
+ * NVLink on the copy engines (no SM work, so the next step's persistent kernels keep all 148 SMs).
+ * sam2b_peer_alloc: cudaMalloc of `bytes` on `device` + its 64-byte IPC handle.  sam2b_peer_open: map a peer's handle into
+ * this process for `device` (peer access is enabled lazily).  sam2b_peer_copy: asynchronous copy on `stream`; either side
+ * may be a mapped peer pointer. */
+int sam2b_peer_alloc(int device, int64_t bytes, void** dev_ptr, unsigned char* ipc_handle_64);
+int sam2b_peer_free(int device, void* dev_ptr);
+int sam2b_peer_open(int device, const unsigned char* ipc_handle_64, void** mapped_ptr);
+int sam2b_peer_close(int device, void* mapped_ptr);
+int sam2b_peer_copy(void* dst, const void* src, int64_t bytes, void* stream);
+
 /* ---- per-launch profiling (CUDA event pair around every kernel this library launches, on the launching stream) ----
  * begin: clear + enable.  end: disable, synchronise the device and write a CSV "name,ms,flops,bytes" (one line per
  * launch; flops/bytes are the ALGORITHMIC work of that launch) into buf; *needed receives the full length. */

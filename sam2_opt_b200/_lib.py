@@ -23,6 +23,11 @@ SIGNATURES = {
     "sam2b_position_encoding": (_i, [_i, _i, _i, _vp, _vp]),
     "sam2b_memory_attention": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _vp, _vp, _i, _i, _vp, _vp]),
     "sam2b_memory_encode": (_i, [_vp, _vp, _vp, _i, _vp, _vp]),
+    "sam2b_peer_alloc": (_i, [_i, _i64, C.POINTER(_vp), C.c_char_p]),
+    "sam2b_peer_free": (_i, [_i, _vp]),
+    "sam2b_peer_open": (_i, [_i, C.c_char_p, C.POINTER(_vp)]),
+    "sam2b_peer_close": (_i, [_i, _vp]),
+    "sam2b_peer_copy": (_i, [_vp, _vp, _i64, _vp]),
     "sam2b_profile_begin": (_i, []),
     "sam2b_profile_end": (_i, [C.c_char_p, _i64, C.POINTER(_i64)]),
     "sam2b_op_gemm": (_i, [_vp, _i64, _i64, _vp, _i64, _i64, _i, _i, _i, _i, _f, _vp, _i, _i, _vp, _vp, _i64, _i64, _i,

@@ -185,7 +185,8 @@ class _GraphedHeads:
 class SAM2VideoPredictor(_Base):
     """Forward video propagation with click / box prompts (BASELINE.json configs 3 and 4)."""
 
-    def __init__(self, state_dict, device="cuda", backend="b200", encode_ahead=16, fill_hole_area=0, graph_heads=True):
+    def __init__(self, state_dict, device="cuda", backend="b200", encode_ahead=16, fill_hole_area=0, graph_heads=True,
+                 add_all_frames_to_correct_as_cond=False):
         """fill_hole_area: as the reference's constructor argument (sam2_video_predictor_official.py:25,889-894; the
         reference's builder sets 8 when its native extension is available, build_sam.py:128-129): holes of at most that
         many pixels in the low-res mask scores are filled before the masks are stored / returned.  0 = off, which is what
@@ -197,6 +198,8 @@ class SAM2VideoPredictor(_Base):
         self.encode_ahead = max(1, int(encode_ahead))
         self.fill_hole_area = int(fill_hole_area)
         self.graph_heads = bool(graph_heads)
+        # ref: sam2_video_predictor_official.py:31-33 - whether a correction click on a tracked frame makes it a conditioning frame
+        self.add_all_frames_to_correct_as_cond = bool(add_all_frames_to_correct_as_cond)
         self._heads_graphs = {}            # (object count, host thread) -> _GraphedHeads
         self._tpos_cache = {}              # (num_frames, max_ptrs) -> projected temporal encodings of the object pointers
 
@@ -213,13 +216,14 @@ class SAM2VideoPredictor(_Base):
         st = {"images": frames if offload_video_to_cpu else frames.to(self.device), "num_frames": frames.shape[0],
               "video_height": video_height or 1024, "video_width": video_width or 1024,
               "obj_ids": [], "prompts": OrderedDict(), "cond": OrderedDict(), "non_cond": OrderedDict(),
-              "feat_cache": {}, "frames_tracked": {}, "non_cond_b": {}, "cond_b": {}}
+              "feat_cache": {}, "frames_tracked": {}, "non_cond_b": {}, "cond_b": {}, "pending_non_cond": set()}
         return st
 
     def reset_state(self, st):
         for k in ("prompts", "cond", "non_cond", "non_cond_b", "cond_b"):
             st[k].clear()
         st["obj_ids"], st["feat_cache"], st["frames_tracked"] = [], {}, {}
+        st["pending_non_cond"].clear()
 
     def _prep_frame(self, f, mean, std):
         """one uint8 HWC frame -> normalised [1,3,1024,1024] fp32 (ref: utils/misc.py:96,161-162)"""
@@ -273,22 +277,46 @@ class SAM2VideoPredictor(_Base):
             pts = torch.cat([st["prompts"][key][0].cpu(), pts], 0)
             lab = torch.cat([st["prompts"][key][1].cpu(), lab], 0)
         st["prompts"][key] = (pts.to(self.device), lab.to(self.device))
-        out = self._run_cond_frame(st, frame_idx, [obj_id])
-        st["cond"].setdefault(frame_idx, {})[obj_id] = out
-        st["cond_b"].pop(frame_idx, None)          # stacked copies of this frame's conditioning outputs are stale
-        low = torch.cat([st["cond"][frame_idx][o]["pred_masks"] if o in st["cond"][frame_idx] else
-                         torch.full((1, 1, 256, 256), H.NO_OBJ_SCORE, device=self.device) for o in st["obj_ids"]], 0)
+        # A frame that has not been tracked yet is an initial conditioning frame (SAM on the plain image features, no memory);
+        # a click on an already tracked frame corrects the tracked mask: memory-conditioned features, stored as a
+        # non-conditioning output unless add_all_frames_to_correct_as_cond (ref: :328-349).
+        is_init = frame_idx not in st["frames_tracked"]
+        is_cond = is_init or self.add_all_frames_to_correct_as_cond
+        # the previous mask logits of this object on this frame (conditioning output first, then tracked output), clamped,
+        # go back into the SAM mask decoder as its mask prompt together with the new clicks (ref: :351-366)
+        prev = st["cond"].get(frame_idx, {}).get(obj_id) or st["non_cond"].get(obj_id, {}).get(frame_idx)
+        prev_logits = None if prev is None else torch.clamp(prev["pred_masks"], -32.0, 32.0)
+        out = self._run_click_frame(st, frame_idx, obj_id, is_init, prev_logits)
+        if is_cond:
+            st["cond"].setdefault(frame_idx, {})[obj_id] = out
+            st["cond_b"].pop(frame_idx, None)          # stacked copies of this frame's conditioning outputs are stale
+        else:
+            st["non_cond"].setdefault(obj_id, {})[frame_idx] = out
+            st["pending_non_cond"].add((frame_idx, obj_id))
+        st["non_cond_b"].pop(frame_idx, None)          # the batched record of this frame no longer matches this object
+        low = torch.cat([self._latest_low(st, frame_idx, o) for o in st["obj_ids"]], 0)
         return frame_idx, list(st["obj_ids"]), self._video_res(st, low)
 
-    def _run_cond_frame(self, st, t, obj_ids):
-        f2, _, hr = self._features(st, t)
-        o = obj_ids[0]
+    def _latest_low(self, st, t, o):
+        rec = st["cond"].get(t, {}).get(o) or st["non_cond"].get(o, {}).get(t)
+        if rec is None:
+            return torch.full((1, 1, 256, 256), H.NO_OBJ_SCORE, device=self.device)
+        return rec["pred_masks"]
+
+    def _run_click_frame(self, st, t, o, is_init, prev_logits):
+        """One prompted frame of one object (ref: _run_single_frame_inference with batch 1 and run_mem_encoder=False,
+        sam2_video_predictor_official.py:367-383; track_step, sam2_base_official.py:1028-1087)."""
+        f2, pos2, hr = self._features(st, t)
         pts, lab = st["prompts"][(t, o)]
         pin = {"point_coords": pts[None], "point_labels": lab[None]}
-        pix = f2 + self.w["no_mem_embed"].view(1, -1, 1, 1)
-        multimask = 0 < pts.shape[0] <= 1      # ref: _use_multimask, sam2_base_official.py:1181-1189 (min 0, max 1 point)
-        _, _, _, low, high, ptr, obj = H.forward_sam_heads(self.w, pix, point_inputs=pin, high_res_features=hr,
-                                                           multimask_output=multimask, pe=self._dense_pe)
+        if is_init:
+            pix = f2 + self.w["no_mem_embed"].view(1, -1, 1, 1)
+        else:
+            pix = self._memory_conditioned(st, t, [o], f2, pos2, per_object=True)
+        # ref: _use_multimask, sam2_base_official.py:1181-1189 (multimask_output_for_tracking, 0 <= points <= 1)
+        multimask = pts.shape[0] <= 1
+        _, _, _, low, high, ptr, obj = H.forward_sam_heads(self.w, pix, point_inputs=pin, mask_inputs=prev_logits,
+                                                           high_res_features=hr, multimask_output=multimask, pe=self._dense_pe)
         return {"pred_masks": self._fill_holes(low), "obj_ptr": ptr, "object_score_logits": obj, "maskmem_features": None,
                 "maskmem_pos": None}
 
@@ -317,6 +345,16 @@ class SAM2VideoPredictor(_Base):
             for i, o in enumerate(todo):
                 per_obj[o]["maskmem_features"], per_obj[o]["maskmem_pos"] = mf[i:i + 1], mp[i:i + 1]
             st["cond_b"].pop(t, None)
+        # correction clicks on tracked frames (stored as non-conditioning outputs): their memory is encoded here as well,
+        # from the binarised mask like every frame the user interacted with (ref: :608-629, is_mask_from_pts=True)
+        for t, o in sorted(st["pending_non_cond"]):
+            out = st["non_cond"].get(o, {}).get(t)
+            if out is None or out["maskmem_features"] is not None:
+                continue
+            high = F.interpolate(out["pred_masks"], size=(1024, 1024), mode="bilinear", align_corners=False)
+            mf, mp = self._encode_memory(self._features(st, t)[0], high, out["object_score_logits"], from_points=True)
+            out["maskmem_features"], out["maskmem_pos"] = mf, mp
+        st["pending_non_cond"].clear()
 
     @torch.no_grad()
     def propagate_in_video(self, st, start_frame_idx=None, max_frame_num_to_track=None):
@@ -350,41 +388,52 @@ class SAM2VideoPredictor(_Base):
         if pending is not None:
             yield pending
 
-    def _track_frame(self, st, t, objs):
-        """One non-prompted frame for a list of objects, batched through the engine (ref: track_step,
-        sam2_base_official.py:1028-1179)."""
-        f2, pos2, hr = self._features(st, t)
-        # Objects that share their conditioning frames and their tracked history (the usual case: everything prompted on
-        # the same frame) form one group whose memory bank is assembled once from the per-frame BATCHED outputs
-        # (SURVEY section 8 f-2): no per-object float / add / stack / cat kernels.  Anything else takes the per-object path.
+    def _history_groups(self, st, t, objs):
+        """Objects that share their conditioning frames and their tracked history (the usual case: everything prompted on
+        the same frame) form one group whose memory bank is assembled once from the per-frame BATCHED outputs
+        (SURVEY section 8 f-2): no per-object float / add / stack / cat kernels.  Anything else takes the per-object path."""
         groups = OrderedDict()
         for o in objs:
             cond_keys = tuple(tt for tt, per in st["cond"].items() if o in per and per[o]["maskmem_features"] is not None)
             nc = st["non_cond"].get(o, {})
-            hist = tuple(tt for tt in range(max(0, t - 16), t) if tt in nc)
+            hist = tuple(tt for tt in range(max(0, t - 16), t) if tt in nc and nc[tt]["maskmem_features"] is not None)
             groups.setdefault((cond_keys, hist), []).append(o)
+        return groups
+
+    def _memory_conditioned(self, st, t, g_objs, f2, pos2, per_object=False, cond_keys=None, hist=None):
+        """Current-frame features fused with the memory bank of the objects `g_objs` (which share their history) through
+        boundary E3 (ref: _prepare_memory_conditioned_features, sam2_base_official.py:797-976) -> [n,256,64,64]."""
+        n, key = len(g_objs), tuple(g_objs)
+        if cond_keys is None:
+            (cond_keys, hist), = self._history_groups(st, t, g_objs[:1]).keys()
+        batched = {} if per_object else {tt: st["non_cond_b"].get(tt, {}).get(key) for tt in hist}
+        if not per_object and all(v is not None for v in batched.values()):
+            cond_b = {tt: self._stacked_cond(st, tt, key) for tt in cond_keys}
+            mem = H.assemble_memory(self.w, t, cond_b, batched, st["num_frames"], cache=self._tpos_cache)
+        else:
+            per = []
+            for o in g_objs:
+                cond = {tt: st["cond"][tt][o] for tt in cond_keys}
+                nc = {tt: r for tt, r in st["non_cond"].get(o, {}).items() if r["maskmem_features"] is not None}
+                per.append(H.assemble_memory(self.w, t, cond, nc, st["num_frames"], cache=self._tpos_cache))
+            mem = [torch.cat([m[i] for m in per], dim=2 if i < 2 else 1) for i in range(4)]
+        P = mem[2].shape[0]
+        curr = f2.flatten(2).permute(2, 0, 1).expand(-1, n, -1)
+        curr_pos = pos2.flatten(2).permute(2, 0, 1).expand(-1, n, -1)
+        if P:
+            pix = self._ex["memory_attention_exclude"].Inference([curr, mem[0], curr_pos, mem[1], mem[2], mem[3]], output_type="torch")[0]
+        else:
+            pix = self._ex["memory_attention_none"].Inference([curr, mem[0], curr_pos, mem[1]], output_type="torch")[0]
+        return pix.permute(1, 2, 0).reshape(n, H.D_MODEL, 64, 64)
+
+    def _track_frame(self, st, t, objs):
+        """One non-prompted frame for a list of objects, batched through the engine (ref: track_step,
+        sam2_base_official.py:1028-1179)."""
+        f2, pos2, hr = self._features(st, t)
         results = {}
-        for (cond_keys, hist), g_objs in groups.items():
+        for (cond_keys, hist), g_objs in self._history_groups(st, t, objs).items():
             n, key = len(g_objs), tuple(g_objs)
-            batched = {tt: st["non_cond_b"].get(tt, {}).get(key) for tt in hist}
-            if all(v is not None for v in batched.values()):
-                cond_b = {tt: self._stacked_cond(st, tt, key) for tt in cond_keys}
-                mem = H.assemble_memory(self.w, t, cond_b, batched, st["num_frames"], cache=self._tpos_cache)
-            else:
-                per = []
-                for o in g_objs:
-                    cond = {tt: st["cond"][tt][o] for tt in cond_keys}
-                    per.append(H.assemble_memory(self.w, t, cond, st["non_cond"].get(o, {}), st["num_frames"], cache=self._tpos_cache))
-                mem = [torch.cat([m[i] for m in per], dim=2 if i < 2 else 1) for i in range(4)]
-            L, P = mem[0].shape[0], mem[2].shape[0]
-            cat = lambda i: mem[i]
-            curr = f2.flatten(2).permute(2, 0, 1).expand(-1, n, -1)
-            curr_pos = pos2.flatten(2).permute(2, 0, 1).expand(-1, n, -1)
-            if P:
-                pix = self._ex["memory_attention_exclude"].Inference([curr, cat(0), curr_pos, cat(1), cat(2), cat(3)], output_type="torch")[0]
-            else:
-                pix = self._ex["memory_attention_none"].Inference([curr, cat(0), curr_pos, cat(1)], output_type="torch")[0]
-            pix = pix.permute(1, 2, 0).reshape(n, H.D_MODEL, 64, 64)
+            pix = self._memory_conditioned(st, t, g_objs, f2, pos2, cond_keys=cond_keys, hist=hist)
             if self.graph_heads:
                 gk = (n, threading.get_ident())    # static buffers are per graph: one graph per host thread
                 if gk not in self._heads_graphs:

@@ -163,3 +163,60 @@ def test_video_batched_bank_and_graphed_heads_equal_the_plain_path(weights):
             assert v >= 0.995, f"frame {t} object {i + 1}: IoU {v:.4f} after re-prompting object 3"
     assert all({(1, 2), (3,)} <= set(d) for t, d in st_a["non_cond_b"].items() if t >= 4)
     vp_a.release()
+
+
+def test_refinement_and_correction_clicks_match_the_reference(weights):
+    """Interactive use beyond the first click (reference add_new_points_or_box, sam2_video_predictor_official.py:267-399):
+    (1) a second click on the prompted frame with clear_old_points=False feeds the previous mask logits (clamped to +-32)
+        back into the SAM decoder as its mask prompt;
+    (2) a click on an already TRACKED frame corrects the tracked mask with memory-conditioned features and is stored as a
+        non-conditioning output, whose memory is encoded by the next preflight.
+    Both against the unmodified reference's torch path in strict fp32 on the same device, step by step."""
+    from oracle import reference_loader as rl
+    if not rl.available():
+        pytest.skip("reference sources not present")
+    import ref_gpu
+    from oracle.synth import synth_video
+    from sam2_opt_b200.predictor import SAM2VideoPredictor
+    torch.set_grad_enabled(False)
+    T = 6
+    frames = synth_video(T, seed=5)
+    f32, i32 = np.float32, np.int32
+    script = [
+        ("click", 0, dict(points=np.array([[512, 512]], f32), labels=np.array([1], i32))),
+        ("click", 0, dict(points=np.array([[600, 430]], f32), labels=np.array([1], i32), clear_old_points=False)),
+        ("propagate", None, {}),
+        ("click", 3, dict(points=np.array([[400, 640]], f32), labels=np.array([0], i32))),
+        ("propagate", 3, {}),
+    ]
+
+    def run(pred, st, is_ref):
+        outs = []
+        for kind, t, kw in script:
+            if kind == "click":
+                _, _, m = pred.add_new_points_or_box(st, t, 1, **kw)
+                outs.append([(m[0, 0] > 0).cpu().numpy()])
+            else:
+                outs.append([(m[0, 0] > 0).cpu().numpy() for _, _, m in pred.propagate_in_video(st, start_frame_idx=t)])
+        return outs
+
+    ref_m = ref_gpu.build("video", weights)
+    with ref_gpu.synthetic_video(frames):
+        ref_st = ref_m.init_state("synthetic")
+    want = run(ref_m, ref_st, True)
+    # where the reference keeps the correction: a tracked (non-conditioning) output of frame 3
+    assert 3 in ref_st["output_dict_per_obj"][0]["non_cond_frame_outputs"] and 3 not in ref_st["output_dict_per_obj"][0]["cond_frame_outputs"]
+    del ref_m
+    torch.cuda.empty_cache()
+    vp = SAM2VideoPredictor(weights)
+    st = vp.init_state(frames)
+    got = run(vp, st, False)
+    assert 3 in st["non_cond"][1] and 3 not in st["cond"]
+    for step, (g, w_) in enumerate(zip(got, want)):
+        assert len(g) == len(w_)
+        ious = [iou_bits(a, b) for a, b in zip(g, w_)]
+        print(f"step {step} ({script[step][0]} @ {script[step][1]}): IoU vs reference", [f"{v:.4f}" for v in ious])
+        assert min(ious) >= 0.99, (step, ious)
+    # the refinement click really changed the mask (otherwise step 1 would not test the mask-prompt path)
+    assert iou_bits(want[0][0], want[1][0]) < 0.999
+    vp.release()

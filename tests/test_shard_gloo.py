@@ -81,3 +81,55 @@ def test_encode_images_sharded_gloo_world2(n_images):
         p.join(timeout=60)
         assert p.exitcode == 0
     assert sorted(res) == [(0, True), (1, True)]
+
+
+def _gather_worker(rank, world, port, q):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        # the collective ("nccl") mode of the embedding gather runs unchanged over gloo on host tensors: the "engine" writes
+        # its three levels into local_out(k) (this rank's slice of the gather buffers), publish(k) completes the other slices
+        B = 1
+        g = shard.EmbeddingGather(B, "cpu", mode="nccl")
+        ok = g.mode == "nccl" and g.world == world and "all three levels" in g.describe()
+        for k in range(2):
+            for lvl, t in enumerate(g.local_out(k)):
+                t.fill_(100.0 * k + 10.0 * rank + lvl)
+            g.publish(k)
+            g.wait(k)
+            for lvl, full in enumerate(g.gathered(k)):
+                ok = ok and tuple(full.shape) == (world * B,) + shard.LEVEL_SHAPES[lvl]
+                for r in range(world):
+                    ok = ok and bool((full[r * B:(r + 1) * B] == 100.0 * k + 10.0 * r + lvl).all())
+        g.drain()
+        g.close()
+        # a global batch smaller than the world: the rank with an empty slice contributes zero rows
+        images = torch.arange(3 * 4 * 4, dtype=torch.float32).reshape(1, 3, 4, 4)
+        outs = shard.encode_images_sharded(lambda x: (x * 2.0, x.flatten(1)), images)
+        ok = ok and torch.equal(outs[0], images * 2.0) and torch.equal(outs[1], images.flatten(1))
+        q.put((rank, bool(ok)))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_embedding_gather_collective_mode_gloo_world2():
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_gather_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    res = [q.get(timeout=180) for _ in procs]
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    assert sorted(res) == [(0, True), (1, True)]
+
+
+def test_embedding_gather_single_process_is_local_only():
+    g = shard.EmbeddingGather(2, "cpu", mode="auto")
+    assert g.mode == "none" and g.describe() == "none"
+    outs = g.local_out(5)
+    assert [tuple(t.shape) for t in outs] == [(2,) + s for s in shard.LEVEL_SHAPES]
+    g.publish(5); g.wait(5); g.drain(); g.close()
