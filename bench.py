@@ -207,7 +207,7 @@ def run_reference(args):
         return
     steps, warmup = max(1, min(args.steps, 5)), min(args.warmup, 1)
     v, cores, times, kind = cpu_reference_images_per_s(CPU_SAMPLE_IMAGES, steps, warmup)
-    what = ("the unmodified reference SAM2Base.forward_image (oracle/_ref), fp32 torch" if kind == "reference"
+    what = ("the unmodified reference SAM2Base.forward_image (oracle/_ref on the GPU box), fp32 torch" if kind == "reference"
             else "fp32 torch CPU port of the reference path (oracle/sam2_oracle.py)")
     sample = f"{steps} step(s) x {CPU_SAMPLE_IMAGES} images of the batch-{args.batch} workload: {what}, {cores} host threads, {warmup} single-image warm-up"
     print(json.dumps({
@@ -294,8 +294,10 @@ def main():
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return t.tolist()
 
-    def timed_encode(B, steps, warm, gather_mode):
-        """`steps` passes over a batch of B images per rank with the gather of all three levels; -> (ms total, max over ranks)"""
+    def timed_encode(B, steps, warm, gather_mode, sampler=None):
+        """`steps` passes over a batch of B images per rank with the gather of all three levels; -> (ms total, max over ranks).
+        sampler: context manager entered around the timed region only (clock / throttle sampling)."""
+        import contextlib
         img = synth_image_norm(B, seed=1 + rank).to(dev)
         g = shard.EmbeddingGather(B, dev, mode=gather_mode if world > 1 else "none")
         k = 0
@@ -304,13 +306,14 @@ def main():
         g.drain()
         barrier()
         t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        barrier()
-        t0.record()
-        for _ in range(steps):
-            eng.image_encode(img, True, False, out=g.local_out(k)); g.publish(k); k += 1
-        g.drain()                 # the compute stream waits for the last transfers: they are inside the timed region
-        t1.record()
-        barrier()
+        with (sampler if sampler is not None else contextlib.nullcontext()):
+            barrier()
+            t0.record()
+            for _ in range(steps):
+                eng.image_encode(img, True, False, out=g.local_out(k)); g.publish(k); k += 1
+            g.drain()                 # the compute stream waits for the last transfers: they are inside the timed region
+            t1.record()
+            barrier()
         ms = allmax([t0.elapsed_time(t1)])[0]
         desc = g.describe()
         g.close()
@@ -336,10 +339,10 @@ def main():
 
     B = args.batch
     # ---- headline: device-resident inputs ---------------------------------------------------------------------------
-    with ClockSampler(local) as clk:
-        l0 = E.launch_count()
-        ms_total, gather_desc = timed_encode(B, args.steps, warmup, args.gather)
-        launches = (E.launch_count() - l0) * args.steps // (args.steps + warmup)
+    clk = ClockSampler(local)
+    l0 = E.launch_count()
+    ms_total, gather_desc = timed_encode(B, args.steps, warmup, args.gather, sampler=clk)
+    launches = (E.launch_count() - l0) * args.steps // (args.steps + warmup)
     value = world * B * args.steps / (ms_total / 1e3)
 
     # ---- e2e: host buffers through the plugin entry point -------------------------------------------------
@@ -425,6 +428,7 @@ def main():
                  "config": "BASELINE.json configs[2]: 1 object, 64 synthetic 1024x1024 frames, 7-frame memory bank" if T == 64 else f"{T}-frame clip, 1 object",
                  "value_steady": world * n_steady / t_steady, "value_overall": world * T / t_all,
                  "frames_per_video": T, "objects_per_video": 1, "videos": world,
+                 "rank0_fps_by_16_frame_block": [round(min(16, len(stamps) - 1 - i) / (stamps[min(i + 16, len(stamps) - 1)] - stamps[i]), 1) for i in range(0, len(stamps) - 1, 16)],
                  "timing": "host wall clock around the generator incl. H2D of frames and a D2H read of every frame's masks, max over ranks; steady = frames >= 16 (7-frame memory bank, 16 pointers)"}
         if rank == 0:
             # roofline of the video path's dominant kernel (hd-256 flash attention over the memory bank), live CUDA events

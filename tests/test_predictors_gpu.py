@@ -145,16 +145,23 @@ def test_video_batched_bank_and_graphed_heads_equal_the_plain_path(weights):
     assert len(st_a["non_cond_b"]) == T - 1 and all(tuple(k) == (1, 2, 3) for d in st_a["non_cond_b"].values() for k in d)
     vp_a.release(); vp_b.release()
     # mixed history (7 frames, so that two conditioning frames + recent frames stay within the 7-slot bank of the E3
-    # boundary): object 3 gets a second prompt on frame 3 -> its conditioning frames differ from objects 1-2, the frame
-    # groups split ((1, 2) and (3,)) and no batched record matches: the per-object fallback runs.  Objects 1-2 keep their
-    # history, so their masks stay the same up to the summation order of a batch of 2 instead of 3.
+    # boundary): tracking stops after frame 2, then object 3 gets a prompt on the not yet tracked frame 3, which becomes a
+    # second conditioning frame for it (a click on an already tracked frame would be a correction stored as a tracked
+    # output, see test_refinement_and_correction_clicks_match_the_reference).  Its conditioning frames now differ from
+    # objects 1-2, the frame groups split ((1, 2) and (3,)) and no batched record matches: the per-object fallback runs.
+    # Objects 1-2 keep their history, so their masks stay the same up to the summation order of a batch of 2 instead of 3.
     T2 = 7
     vp_a = SAM2VideoPredictor(weights)
+    st_f = vp_a.init_state(frames[:T2])
+    for o, p in pts.items():
+        vp_a.add_new_points_or_box(st_f, 0, o, points=np.array(p, dtype=np.float32), labels=np.array([1], np.int32))
+    first = {t: m.clone() for t, _, m in vp_a.propagate_in_video(st_f)}
     st_a = vp_a.init_state(frames[:T2])
     for o, p in pts.items():
         vp_a.add_new_points_or_box(st_a, 0, o, points=np.array(p, dtype=np.float32), labels=np.array([1], np.int32))
-    first = {t: m.clone() for t, _, m in vp_a.propagate_in_video(st_a)}
+    assert [t for t, _, _ in vp_a.propagate_in_video(st_a, max_frame_num_to_track=2)] == [0, 1, 2]
     vp_a.add_new_points_or_box(st_a, 3, 3, points=np.array([[705, 305]], dtype=np.float32), labels=np.array([1], np.int32))
+    assert 3 in st_a["cond"] and list(st_a["cond"][3]) == [3]
     again = {t: m for t, _, m in vp_a.propagate_in_video(st_a, start_frame_idx=3)}
     assert sorted(again) == list(range(3, T2)) and all(m.shape[0] == 3 for m in again.values())
     for t in range(4, T2):
