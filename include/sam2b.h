@@ -135,6 +135,16 @@ int sam2b_op_connected_components(const void* mask_u8, int32_t* labels, int32_t*
  * with normalise != 0, (x / 255 - mean) / std with the ImageNet constants of transforms.py:27-28.  Same IEEE operations in
  * the same order as the reference: bit-exact.  w must be a multiple of 4. */
 int sam2b_op_preprocess_u8(const void* hwc_u8, float* out_nchw, int n, int h, int w, int normalise, void* stream);
+/* Frames that are NOT at the model resolution (replaces the Resize of SAM2Transforms, sam2/utils/transforms.py:30, applied to
+ * `images / 255.0` in SAM2ImagePredictor._set_image_, sam2_image_predictor.py:193): antialiased bilinear interpolation
+ * (F.interpolate(mode="bilinear", antialias=True, align_corners=False): a separable triangle filter whose support grows with
+ * the down-scaling factor).  src dev: uint8 [n][h][w][3] when src_is_u8_hwc != 0 (x / 255 first), else fp32 [n][3][h][w];
+ * out_nchw dev fp32 [n][3][out_h][out_w], with normalise != 0 followed by (x - mean) / std.  out_w must be a multiple of 4.
+ * workspace: sam2b_op_resize_frames_workspace(...) bytes of device memory.  Bit-exact against oracle/preprocess_oracle.py:
+ * resize_bilinear_aa, which reproduces the reference framework's CPU operator bit for bit. */
+int64_t sam2b_op_resize_frames_workspace(int n, int h, int w, int out_h, int out_w);
+int sam2b_op_resize_frames(const void* src, int src_is_u8_hwc, int n, int h, int w, float* out_nchw, int out_h, int out_w,
+                           int normalise, void* workspace, void* stream);
 /* Post-processing of predicted masks (replaces the F.interpolate of SAM2Transforms.postprocess_masks, sam2/utils/transforms.py:119,
  * and the `masks > mask_threshold` that follows it, sam2_image_predictor.py:300-302 / the video predictor's `video_res_masks > 0`):
  * low dev fp32 [n][h][w] mask logits -> out dev fp32 [n][out_h][out_w] (bilinear, align_corners = False; may be NULL) and

@@ -964,6 +964,13 @@ int sam2b_op_preprocess_u8(const void* hwc_u8, float* out_nchw, int n, int h, in
   if (!hwc_u8 || !out_nchw) { set_error("sam2b_op_preprocess_u8: null argument"); return 1; }
   return preprocess_u8_hwc(reinterpret_cast<const uint8_t*>(hwc_u8), out_nchw, n, h, w, normalise, reinterpret_cast<cudaStream_t>(stream));
 }
+int64_t sam2b_op_resize_frames_workspace(int n, int h, int w, int out_h, int out_w) {
+  return (int64_t)resize_frames_workspace(n, h, w, out_h, out_w);
+}
+int sam2b_op_resize_frames(const void* src, int src_is_u8_hwc, int n, int h, int w, float* out_nchw, int out_h, int out_w,
+                           int normalise, void* workspace, void* stream) {
+  return resize_frames(src, src_is_u8_hwc, n, h, w, out_nchw, out_h, out_w, normalise, workspace, reinterpret_cast<cudaStream_t>(stream));
+}
 int sam2b_op_upsample_masks(const float* low, float* out, void* mask_u8, int64_t n, int h, int w, int out_h, int out_w, float threshold,
                             void* stream) {
   if (!low || (!out && !mask_u8)) { set_error("sam2b_op_upsample_masks: null argument"); return 1; }

@@ -119,6 +119,11 @@ int connected_components(const uint8_t* mask, int* labels, int* counts, int n, i
 int preprocess_u8_hwc(const uint8_t* in, float* out, int n, int H, int W, int normalise, cudaStream_t stream);
 // low fp32 [n][h][w] -> out fp32 [n][H][W] (nullable) and mask uint8 [n][H][W] = out > threshold (nullable); bilinear, align_corners = False
 int upsample_bilinear_mask(const float* low, float* out, uint8_t* mask, long n, int h, int w, int H, int W, float threshold, cudaStream_t stream);
+// Antialiased bilinear resize of frames (resize.cu): src = uint8 [n][h][w][3] (src_is_u8_hwc) or fp32 [n][3][h][w] ->
+// out fp32 [n][3][out_h][out_w] = resize(x / 255 | x) and, with normalise, (x - mean) / std.  workspace: resize_frames_workspace bytes.
+long resize_frames_workspace(int n, int h, int w, int out_h, int out_w);
+int resize_frames(const void* src, int src_is_u8_hwc, int n, int h, int w, float* out, int out_h, int out_w, int normalise,
+                  void* workspace, cudaStream_t stream);
 // Fused trunk MLP for C = 144 / 288 (mlp_fused.cu): x += fc2(GELU(rstd * (xb W1''^T) + b1)) + b2 in place, bf16 copy and
 // per-row (sum, sum of squares) in two parts for the next folded LayerNorm; the hidden layer never reaches HBM.
 bool mlp_fused_supported(int C);

@@ -78,6 +78,30 @@ def preprocess_u8(hwc: torch.Tensor, normalise: bool = False) -> torch.Tensor:
 
 
 @on_tensor_device
+def resize_frames(src: torch.Tensor, size=(1024, 1024), normalise: bool = False) -> torch.Tensor:
+    """Frames at any resolution -> fp32 [N,3,H_out,W_out] by antialiased bilinear interpolation, the operator behind the
+    reference's Resize((1024, 1024)) (sam2/utils/transforms.py:30; sam2_image_predictor.py:193).  src: CUDA uint8 [N,H,W,3]
+    (raw frames: x / 255 first, as the reference does) or CUDA fp32 [N,3,H,W]; with `normalise`, (x - mean) / std follows."""
+    lib = _lib.load()
+    if not src.is_cuda or src.dim() != 4:
+        raise ValueError(f"resize_frames: expected a 4-D CUDA tensor, got {tuple(src.shape)} on {src.device}")
+    u8 = src.dtype == torch.uint8
+    if u8 and src.shape[-1] != 3:
+        raise ValueError(f"resize_frames: uint8 frames must be [N,H,W,3], got {tuple(src.shape)}")
+    if not u8 and (src.dtype != torch.float32 or src.shape[1] != 3):
+        raise ValueError(f"resize_frames: float frames must be fp32 [N,3,H,W], got {src.dtype} {tuple(src.shape)}")
+    src = src.contiguous()
+    n = src.shape[0]
+    h, w = (src.shape[1], src.shape[2]) if u8 else (src.shape[2], src.shape[3])
+    oh, ow = int(size[0]), int(size[1])
+    out = torch.empty((n, 3, oh, ow), device=src.device, dtype=torch.float32)
+    ws = torch.empty(int(lib.sam2b_op_resize_frames_workspace(n, h, w, oh, ow)), device=src.device, dtype=torch.uint8)
+    _lib.check(lib.sam2b_op_resize_frames(_ptr(src), int(u8), n, h, w, _ptr(out), oh, ow, int(bool(normalise)), _ptr(ws), _stream()),
+               "op_resize_frames")
+    return out
+
+
+@on_tensor_device
 def maxpool2x2_nhwc(x: torch.Tensor) -> torch.Tensor:
     lib = _lib.load()
     B, H, W, Cd = x.shape

@@ -62,15 +62,19 @@ class _Base:
     def release(self):
         self.speedup(None)
 
-    def _prep_image(self, image) -> torch.Tensor:
-        """uint8 HWC numpy -> [1,3,1024,1024] fp32 in [0,1] (ref: sam2_image_predictor.py:173-196: /255 then resize)."""
+    def _prep_image(self, image, normalise: bool = False) -> torch.Tensor:
+        """HWC image (uint8, or float in [0,255]) -> [1,3,1024,1024] fp32 in [0,1] (ref: sam2_image_predictor.py:173-196: /255,
+        then Resize((1024, 1024)) = antialiased bilinear).  Both steps run in libsam2b: `preprocess_u8` at the model
+        resolution (the resize is the identity there), `resize_frames` otherwise; `normalise` appends (x - mean) / std."""
         img = torch.as_tensor(np.ascontiguousarray(image)).to(self.device)
-        if img.dtype == torch.uint8 and tuple(img.shape) == (1024, 1024, 3):
-            return ops.preprocess_u8(img)         # one pass: bytes in, fp32 planes out
-        img = img.permute(2, 0, 1)[None].float() / 255.0
-        if img.shape[-2:] != (1024, 1024):
-            img = F.interpolate(img, size=(1024, 1024), mode="bilinear", align_corners=False, antialias=True)
-        return img
+        if img.dim() != 3 or img.shape[-1] != 3:
+            raise ValueError(f"expected an HWC image with 3 channels, got {tuple(img.shape)}")
+        if img.dtype == torch.uint8:
+            if tuple(img.shape[:2]) == (1024, 1024):
+                return ops.preprocess_u8(img, normalise=normalise)         # one pass: bytes in, fp32 planes out
+            return ops.resize_frames(img[None], (1024, 1024), normalise=normalise)
+        chw = (img.permute(2, 0, 1)[None].float() / 255.0).contiguous()
+        return ops.resize_frames(chw, (1024, 1024), normalise=normalise)
 
 
 class SAM2ImagePredictor(_Base):
@@ -227,9 +231,7 @@ class SAM2VideoPredictor(_Base):
 
     def _prep_frame(self, f, mean, std):
         """one uint8 HWC frame -> normalised [1,3,1024,1024] fp32 (ref: utils/misc.py:96,161-162)"""
-        if isinstance(f, np.ndarray) and f.dtype == np.uint8 and f.shape == (1024, 1024, 3):
-            return ops.preprocess_u8(torch.as_tensor(np.ascontiguousarray(f)).to(self.device), normalise=True)
-        return (self._prep_image(f) - mean) / std
+        return self._prep_image(f, normalise=True)
 
     # -- per-frame image features, produced `encode_ahead` frames at a time --------------------------------------
     def _features(self, st, t):
