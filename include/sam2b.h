@@ -74,6 +74,15 @@ int sam2b_memory_attention(sam2b_handle h, const float* curr, const float* curr_
                            const float* memory_pos, int L, const float* memory_exclude,
                            const float* memory_pos_exclude, int P, int n, float* out, void* stream);
 
+/* The same for objects whose memory banks differ (added on different frames, re-prompted ...; SURVEY.md section 8a "dynamic
+ * shapes"): the tensors are padded to L_max frames / P_max pointer tokens and object b uses memory[0 .. L_rows[b]) and
+ * memory_exclude[0 .. P_rows[b]) only (the padding is never read).  L_rows / P_rows are HOST arrays of n entries (either may be
+ * NULL: that count is the same for every object); 1 <= L_rows[b] <= L_max, 0 <= P_rows[b] <= P_max, multiples of 4. */
+int sam2b_memory_attention_varlen(sam2b_handle h, const float* curr, const float* curr_pos, const float* memory,
+                                  const float* memory_pos, int L_max, const float* memory_exclude,
+                                  const float* memory_pos_exclude, int P_max, int n, const int32_t* L_rows,
+                                  const int32_t* P_rows, float* out, void* stream);
+
 /* ---- E4: MemoryEncoder ----
  * pix_feat dev [n,256,64,64], masks dev [n,1,1024,1024] (already sigmoid-scaled) -> out_x dev [n,64,64,64].
  * (the second reference output, the sine position encoding, is a constant: sam2b_position_encoding) */
@@ -159,6 +168,14 @@ int sam2b_op_softmax_rows(const float* s, int64_t lds, void* p_bf16, int64_t ldp
 int64_t sam2b_op_attention_hd256_workspace(int n, int tq, int64_t lk);
 int sam2b_op_attention_hd256(const void* q_bf16, const void* k_bf16, const void* v_bf16, int n, int tq, int64_t lk,
                              void* out_bf16, void* workspace, void* stream);
+
+/* The cross-attention form of the same core (reference sam/transformer.py:345-424 with kv_in_dim = 64): the values are the
+ * UN-PROJECTED 64-wide memory rows, out[b] = softmax(q[b] k[b]^T / 16) v64[b] with v64 [n][lk][64], out [n][tq][64] (v_proj is
+ * linear and the attention weights sum to one, so it is applied afterwards together with out_proj).  lk_rows_dev: optional DEVICE
+ * int32 array of n per-object key counts (<= lk); k / v64 rows at or past an object's count are ignored but must be finite. */
+int64_t sam2b_op_attention_hd256_v64_workspace(int n, int tq, int64_t lk);
+int sam2b_op_attention_hd256_v64(const void* q_bf16, const void* k_bf16, const void* v64_bf16, int n, int tq, int64_t lk,
+                                 const int32_t* lk_rows_dev, void* out_bf16, void* workspace, void* stream);
 
 #ifdef __cplusplus
 }

@@ -22,6 +22,7 @@ SIGNATURES = {
     "sam2b_image_encode_host_u8": (_i, [_vp, _vp, _i, _i, _vp, _vp, _vp, _vp]),
     "sam2b_position_encoding": (_i, [_i, _i, _i, _vp, _vp]),
     "sam2b_memory_attention": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _vp, _vp, _i, _i, _vp, _vp]),
+    "sam2b_memory_attention_varlen": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _vp, _vp, _i, _i, C.POINTER(C.c_int32), C.POINTER(C.c_int32), _vp, _vp]),
     "sam2b_memory_encode": (_i, [_vp, _vp, _vp, _i, _vp, _vp]),
     "sam2b_peer_alloc": (_i, [_i, _i64, C.POINTER(_vp), C.c_char_p]),
     "sam2b_peer_free": (_i, [_i, _vp]),
@@ -45,6 +46,8 @@ SIGNATURES = {
     "sam2b_op_upsample_masks": (_i, [_vp, _vp, _vp, _i64, _i, _i, _i, _i, _f, _vp]),
     "sam2b_op_softmax_rows": (_i, [_vp, _i64, _vp, _i64, _i64, _i, _vp]),
     "sam2b_op_attention_hd256_workspace": (_i64, [_i, _i, _i64]),
+    "sam2b_op_attention_hd256_v64_workspace": (_i64, [_i, _i, _i64]),
+    "sam2b_op_attention_hd256_v64": (_i, [_vp, _vp, _vp, _i, _i, _i64, _vp, _vp, _vp, _vp]),
     "sam2b_op_attention_hd256": (_i, [_vp, _vp, _vp, _i, _i, _i64, _vp, _vp, _vp]),
 }
 

@@ -1,0 +1,477 @@
+// K4b: flash attention for the CROSS-attention of the MemoryAttention layers with the value projection folded behind P V.
+// Reference: RoPEAttention.forward with kv_in_dim = 64 (sam2/modeling/sam/transformer.py:345-424, memory_attention.py:67-91):
+//   out = out_proj( softmax(q k^T / 16) v_proj(memory) ).
+// The rows of softmax(.) sum to one, so  softmax(.) (memory Wv^T + bv) = (softmax(.) memory) Wv^T + bv:  the attention runs
+// over the UN-PROJECTED 64-wide memory (exactly what the bank stores, bf16) and v_proj o out_proj collapse into one 64 -> 256
+// linear map applied to the [4096 x 64] result (weights composed once, weights.py `derived.memattn.*.ca_ov`).  P V costs a
+// quarter of the 256-wide product, the accumulator shrinks from 256 to 64 tensor-memory columns, and the freed columns hold
+// 128-key score tiles: Q K^T issues as N = 128 instructions (64 clocks each, the full tensor rate) instead of N = 64
+// (~50 clock floor), 1 424 issue clocks per 128 keys against 2 624 in the 256-wide kernel (attn_hd256.cu, still used for
+// self-attention where the values are 256 wide anyway).
+//
+// Same structure as attn_hd256.cu: persistent CTAs over units of (object, 128-query tile, KV split); warp 0 TMA producer
+// (Q once per unit, K [128 keys][256] and V [128 keys][64] through a 2-stage ring), warp 1 MMA issuer (Q and P are tensor-memory
+// A operands), warps 4-7 softmax (thread = query row, 128 scores per tile in registers, lazy 2^8 rescale), fp32 partials
+// (O, m, l) merged over the KV splits by attn64_combine_kernel.
+// Objects of one call may have DIFFERENT key counts (lk_rows): memory banks of objects added on different frames
+// (SURVEY.md section 8a "dynamic shapes"); keys at or past an object's count are masked by index, units that hold no key of
+// their object write a zero-weight partial.
+#include <cstdio>
+#include <mutex>
+
+#include "common.cuh"
+#include "ops.h"
+
+namespace sam2b {
+
+namespace fa64 {
+static constexpr int D = 256;
+static constexpr int TQ = 128;
+static constexpr int DV = 64;                       // value width: the un-projected memory (v_proj is folded behind P V)
+static constexpr int TK = 128;
+static constexpr int NSTAGE = 2;
+static constexpr int Q_BYTES = TQ * D * 2;          // 64 KB: 4 sub-tiles [128 rows][64 d] of 16 KB
+static constexpr int K_BYTES = TK * D * 2;          // 64 KB: 4 sub-tiles [128 keys][64 d] of 16 KB
+static constexpr int V_BYTES = TK * DV * 2;         // 16 KB: one [128 keys][64 d] tile
+static constexpr int OFF_Q = 0;
+static constexpr int OFF_K = OFF_Q + Q_BYTES;
+static constexpr int OFF_V = OFF_K + NSTAGE * K_BYTES;
+static constexpr int OFF_BAR = OFF_V + NSTAGE * V_BYTES;
+static constexpr int SMEM = OFF_BAR + 256 + 1024;   // 230 656 B of the 232 448 B a CTA may have
+static constexpr int THREADS = 256;                 // warp0 TMA, warp1 MMA, warp2 TMEM alloc, warp3 idle, warps4-7 softmax
+static constexpr int COL_S = 0;                     // S buffer b at COL_S + 128 b
+static constexpr int COL_O = 256;                   // O: 64 columns
+static constexpr int COL_Q = 384;                   // Q as the A operand of Q K^T: 128 rows x 256 bf16 = 128 columns
+static constexpr int TMEM_COLS = 512;
+static constexpr float RESCALE_THRESHOLD = 8.0f;    // log2 units
+}  // namespace fa64
+
+struct Fa64Params {
+  float* o_part;      // [splits][n][Tq][64] un-normalised partial outputs
+  float* ml_part;     // [splits][n][Tq][2]  (running max in log2 units, running sum)
+  const int* lk_rows; // per-object key count (nullptr: Lk for every object); rows [lk, Lk) of K are masked, of V must be finite
+  int n, Tq, Lk;
+  int q_tiles;        // Tq / 128
+  int kv_tiles;       // ceil(Lk / 128)
+  int splits;
+  int tiles_per_split;
+  int num_units;      // n * q_tiles * splits
+  float scale_log2;   // (1 / sqrt(256)) * log2(e)
+};
+
+struct Unit64 { int b, qt, sp, kv0, kv1, lk; };
+SAM2B_DEVINL Unit64 unit64(const Fa64Params& p, int u) {
+  Unit64 c;
+  c.sp = u % p.splits;
+  const int r = u / p.splits;
+  c.qt = r % p.q_tiles;
+  c.b = r / p.q_tiles;
+  c.lk = p.lk_rows ? min(p.Lk, max(1, p.lk_rows[c.b])) : p.Lk;     // objects of one call may have different histories
+  const int tiles = (c.lk + fa64::TK - 1) / fa64::TK;
+  c.kv0 = c.sp * p.tiles_per_split;
+  c.kv1 = max(c.kv0, min(tiles, c.kv0 + p.tiles_per_split));       // kv1 == kv0: this split holds no key of this object
+  return c;
+}
+
+__global__ void __launch_bounds__(fa64::THREADS, 1)
+flash_attn_hd256_v64_tcgen05_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant__ CUtensorMap map_k,
+                                const __grid_constant__ CUtensorMap map_v, const Fa64Params p) {
+  using namespace fa64;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + OFF_BAR);
+  uint64_t* q_full = bars + 0;
+  uint64_t* q_empty = bars + 1;
+  uint64_t* k_full = bars + 2;              // [NSTAGE]
+  uint64_t* k_empty = k_full + NSTAGE;
+  uint64_t* v_full = k_empty + NSTAGE;
+  uint64_t* v_empty = v_full + NSTAGE;
+  uint64_t* s_full = v_empty + NSTAGE;      // [2]
+  uint64_t* s_free = s_full + 2;            // [2]
+  uint64_t* p_full = s_free + 2;
+  uint64_t* o_done = p_full + 1;            // one completion per P V product
+  uint64_t* o_free = o_done + 1;            // softmax has read the final O of a unit
+  uint64_t* qt_full = o_free + 1;           // the unit's Q tile has been copied shared -> tensor memory
+  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(qt_full + 1);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&map_q);
+    tma_prefetch_desc(&map_k);
+    tma_prefetch_desc(&map_v);
+  }
+  if (warp == 1 && lane == 0) {
+    mbar_init(q_full, 1); mbar_init(q_empty, 4); mbar_init(qt_full, 4);
+    for (int i = 0; i < NSTAGE; ++i) { mbar_init(&k_full[i], 1); mbar_init(&k_empty[i], 1); mbar_init(&v_full[i], 1); mbar_init(&v_empty[i], 1); }
+    for (int i = 0; i < 2; ++i) { mbar_init(&s_full[i], 1); mbar_init(&s_free[i], 4); }
+    mbar_init(p_full, 4); mbar_init(o_done, 1); mbar_init(o_free, 4);
+    fence_barrier_init();
+  }
+  if (warp == 2) {
+    tmem_alloc(tmem_ptr, TMEM_COLS);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_ptr;
+
+  if (warp == 0) {
+    // ===================== TMA producer =====================
+    if (lane == 0) {
+      int it = 0, nu = 0;
+      for (int u = blockIdx.x; u < p.num_units; u += gridDim.x, ++nu) {
+        const Unit64 c = unit64(p, u);
+        mbar_wait(q_empty, (nu & 1) ^ 1);
+        mbar_arrive_expect_tx(q_full, Q_BYTES);
+#pragma unroll
+        for (int s = 0; s < 4; ++s) tma_load_3d(smem + OFF_Q + s * 16384, &map_q, q_full, 64 * s, c.qt * TQ, c.b);
+        for (int j = c.kv0; j < c.kv1; ++j, ++it) {
+          const int st = it % NSTAGE;
+          const uint32_t ph = (it / NSTAGE) & 1;
+          uint8_t* k = smem + OFF_K + st * K_BYTES;
+          uint8_t* v = smem + OFF_V + st * V_BYTES;
+          mbar_wait(&k_empty[st], ph ^ 1);
+          mbar_arrive_expect_tx(&k_full[st], K_BYTES);
+#pragma unroll
+          for (int s = 0; s < 4; ++s) tma_load_3d(k + s * 16384, &map_k, &k_full[st], 64 * s, j * TK, c.b);
+          mbar_wait(&v_empty[st], ph ^ 1);
+          mbar_arrive_expect_tx(&v_full[st], V_BYTES);
+          tma_load_3d(v, &map_v, &v_full[st], 0, j * TK, c.b);
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===================== MMA issuer (one thread) =====================
+    if (lane == 0) {
+      constexpr uint32_t idesc_qk = make_idesc_ex(128, 128, 0);
+      constexpr uint32_t idesc_pv = make_idesc_ex(128, 64, 1);
+      const uint32_t sbase = smem_u32(smem);
+      uint32_t n_s = 0;       // Q K^T products issued (S buffer = n_s & 1)
+      uint32_t n_o = 0;       // P V products issued
+      int it = 0, nu = 0;
+      auto issue_qk = [&](int st) {
+        const uint32_t bsel = n_s & 1;
+        mbar_wait(&s_free[bsel], ((n_s >> 1) & 1) ^ 1);
+        tc_fence_after();
+        // A = Q from tensor memory; B = 128 keys of one 64-wide slice of d: N = 128 runs at the full tensor rate (64 clocks per
+        // instruction; the 64-key tiles of the 256-wide-value kernel pay the ~50 clock floor of a narrow instruction)
+        const uint32_t k = sbase + OFF_K + st * K_BYTES;
+        const uint32_t d = tmem_base + COL_S + 128 * bsel;
+#pragma unroll
+        for (int ks = 0; ks < 16; ++ks)
+          umma_bf16_ts(d, tmem_base + COL_Q + 8 * ks, make_smem_desc(k + (ks >> 2) * 16384 + (ks & 3) * 32, 16, 1024, 2), idesc_qk,
+                       ks != 0);
+        umma_commit(&s_full[bsel]);
+        ++n_s;
+      };
+      for (int u = blockIdx.x; u < p.num_units; u += gridDim.x, ++nu) {
+        const Unit64 c = unit64(p, u);
+        const int n_kv = c.kv1 - c.kv0;
+        mbar_wait(qt_full, nu & 1);
+        if (n_kv == 0) { mbar_wait(o_free, (nu & 1) ^ 1); continue; }     // no key of this object in this split
+        mbar_wait(&k_full[it % NSTAGE], (it / NSTAGE) & 1);
+        tc_fence_after();
+        issue_qk(it % NSTAGE);
+        umma_commit(&k_empty[it % NSTAGE]);
+        mbar_wait(o_free, (nu & 1) ^ 1);          // previous unit's accumulator has been read out
+        for (int j = 0; j < n_kv; ++j, ++it) {
+          const int st = it % NSTAGE, st1 = (it + 1) % NSTAGE;
+          if (j + 1 < n_kv) {
+            mbar_wait(&k_full[st1], ((it + 1) / NSTAGE) & 1);
+            tc_fence_after();
+            issue_qk(st1);                         // S(j+1) is computed while the softmax warps work on S(j)
+            umma_commit(&k_empty[st1]);
+          }
+          mbar_wait(&v_full[st], (it / NSTAGE) & 1);
+          mbar_wait(p_full, n_o & 1);
+          tc_fence_after();
+          const uint32_t v = sbase + OFF_V + st * V_BYTES;
+          const uint32_t pa = tmem_base + COL_S + 128 * (n_o & 1);     // P(j) lives in the first 64 columns of S(j)'s buffer
+          // one N = 64 instruction per 16 keys: V is MN-major (d contiguous), one 128 B-swizzle atom wide; P is read from tensor memory
+#pragma unroll
+          for (int ks = 0; ks < 8; ++ks)
+            umma_bf16_ts(tmem_base + COL_O, pa + 8 * ks, make_smem_desc(v + ks * 2048, 16384, 1024, 2), idesc_pv, (j | ks) != 0);
+          umma_commit(o_done);
+          umma_commit(&v_empty[st]);
+          ++n_o;
+        }
+      }
+    }
+  } else if (warp >= 4) {
+    // ===================== softmax warpgroup (thread = query row) =====================
+    const int wq = warp & 3;
+    const int r = wq * 32 + lane;
+    const uint32_t lane_sel = (uint32_t)(wq * 32) << 16;
+    const uint32_t to = tmem_base + COL_O + lane_sel;
+    uint32_t n = 0;          // KV tiles seen (S buffer = n & 1)
+    uint32_t n_pv = 0;       // P V completions observed (always in order, never more than one behind)
+    // Q tile: shared (TMA, 128B swizzle) -> registers -> tensor memory, row r -> lane r, two bf16 per column.  Called when no
+    // Q K^T product that reads the previous Q is in flight (start of the kernel / after the unit's last P V has completed).
+    const uint32_t q_row = smem_u32(smem + OFF_Q) + r * 128;
+    const uint32_t q_xor = (uint32_t)(r & 7) << 4;
+    auto stage_q = [&](uint32_t parity) {
+      mbar_wait(q_full, parity);
+#pragma unroll 1
+      for (int sub = 0; sub < 4; ++sub) {
+        uint32_t qv[32];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          const float4 f = ld_shared_f4(q_row + sub * 16384 + (((uint32_t)i << 4) ^ q_xor));
+          qv[4 * i] = __float_as_uint(f.x); qv[4 * i + 1] = __float_as_uint(f.y);
+          qv[4 * i + 2] = __float_as_uint(f.z); qv[4 * i + 3] = __float_as_uint(f.w);
+        }
+        tmem_st_x32(tmem_base + COL_Q + 32 * sub + lane_sel, qv);
+      }
+      tmem_st_wait();
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) { mbar_arrive(q_empty); mbar_arrive(qt_full); }
+    };
+    uint32_t nu = 0;
+    if ((int)blockIdx.x < p.num_units) stage_q(0);
+    for (int u = blockIdx.x; u < p.num_units; u += gridDim.x, ++nu) {
+      const Unit64 c = unit64(p, u);
+      const int n_kv = c.kv1 - c.kv0;
+      float m_run = -INFINITY, l_run = 0.f;
+      for (int j = 0; j < n_kv; ++j, ++n) {
+        const uint32_t bsel = n & 1;
+        mbar_wait(&s_full[bsel], (n >> 1) & 1);
+        tc_fence_after();
+        uint32_t s[128];
+        {
+          uint32_t (&s0)[32] = *reinterpret_cast<uint32_t(*)[32]>(&s[0]);
+          uint32_t (&s1)[32] = *reinterpret_cast<uint32_t(*)[32]>(&s[32]);
+          uint32_t (&s2)[32] = *reinterpret_cast<uint32_t(*)[32]>(&s[64]);
+          uint32_t (&s3)[32] = *reinterpret_cast<uint32_t(*)[32]>(&s[96]);
+          const uint32_t ts = tmem_base + COL_S + 128 * bsel + lane_sel;
+          tmem_ld_x32(ts, s0);
+          tmem_ld_x32(ts + 32, s1);
+          tmem_ld_x32(ts + 64, s2);
+          tmem_ld_x32(ts + 96, s3);
+          tmem_ld_wait();
+        }
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&s_free[bsel]);      // S is in registers: the MMA warp may overwrite this buffer
+        const int valid = c.lk - (c.kv0 + j) * TK;       // keys of this tile that exist (>= 128 except on the object's last tile)
+        if (valid < TK) {                                // ragged last tile only
+#pragma unroll
+          for (int i = 0; i < 128; ++i)
+            if (i >= valid) s[i] = __float_as_uint(-INFINITY);
+        }
+        float mx0 = -INFINITY, mx1 = -INFINITY, mx2 = -INFINITY, mx3 = -INFINITY;
+#pragma unroll
+        for (int i = 0; i < 32; ++i) {
+          mx0 = fmaxf(mx0, __uint_as_float(s[i]));
+          mx1 = fmaxf(mx1, __uint_as_float(s[32 + i]));
+          mx2 = fmaxf(mx2, __uint_as_float(s[64 + i]));
+          mx3 = fmaxf(mx3, __uint_as_float(s[96 + i]));
+        }
+        const float mx = fmaxf(fmaxf(mx0, mx1), fmaxf(mx2, mx3)) * p.scale_log2;
+        // lazy rescale: keep the old reference max unless the new one exceeds it by more than 2^8
+        float corr = 1.0f;
+        const bool grow = mx > m_run + RESCALE_THRESHOLD;
+        if (grow) { corr = exp2f(m_run - mx); m_run = mx; }     // first tile: m_run = -inf -> corr = 0 (nothing accumulated yet)
+        // packed fp32 pairs: one FFMA2 (scale, minus max) and one FADD2 (row sum) per two keys
+        const uint64_t sc2 = f2_pack(p.scale_log2, p.scale_log2), nm2 = f2_pack(-m_run, -m_run);
+        uint64_t rs2a = f2_pack(0.f, 0.f), rs2b = rs2a;
+        uint32_t pk[64];
+#pragma unroll
+        for (int i = 0; i < 64; ++i) {
+          float a0, a1, e0, e1;
+          f2_unpack(f2_fma(f2_pack(__uint_as_float(s[2 * i]), __uint_as_float(s[2 * i + 1])), sc2, nm2), a0, a1);
+          asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e0) : "f"(a0));
+          asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e1) : "f"(a1));
+          if (i & 1) rs2b = f2_add(rs2b, f2_pack(e0, e1)); else rs2a = f2_add(rs2a, f2_pack(e0, e1));
+          pk[i] = pack_bf16x2(e0, e1);
+        }
+        float rs0, rs1;
+        f2_unpack(f2_add(rs2a, rs2b), rs0, rs1);
+        l_run = fmaf(l_run, corr, rs0 + rs1);
+        if (j > 0) {
+          // P V of the previous tile must be complete before P is overwritten / the accumulator is rescaled
+          mbar_wait(o_done, n_pv & 1);
+          ++n_pv;
+          tc_fence_after();
+          if (__any_sync(0xffffffffu, grow)) {
+#pragma unroll 1
+            for (int ch = 0; ch < 2; ++ch) {
+              uint32_t o[32];
+              tmem_ld_x32(to + 32 * ch, o);
+              tmem_ld_wait();
+#pragma unroll
+              for (int i = 0; i < 32; ++i) o[i] = __float_as_uint(__uint_as_float(o[i]) * corr);
+              tmem_st_x32(to + 32 * ch, o);
+            }
+            tmem_st_wait();
+          }
+        }
+        {                                                              // P(j) as the A operand of P V, over S(j)'s columns
+          const uint32_t (&p0)[32] = *reinterpret_cast<const uint32_t(*)[32]>(&pk[0]);
+          const uint32_t (&p1)[32] = *reinterpret_cast<const uint32_t(*)[32]>(&pk[32]);
+          tmem_st_x32(tmem_base + COL_S + 128 * bsel + lane_sel, p0);
+          tmem_st_x32(tmem_base + COL_S + 128 * bsel + 32 + lane_sel, p1);
+        }
+        tmem_st_wait();
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(p_full);
+      }
+      // ---- unit done: un-normalised O, running max and sum -> partial buffers ----
+      if (n_kv > 0) {
+        mbar_wait(o_done, n_pv & 1);
+        ++n_pv;
+        tc_fence_after();
+      }
+      if (u + (int)gridDim.x < p.num_units) stage_q((nu + 1) & 1);   // next unit's first Q K^T overlaps this unit's read-out
+      const long row_g = ((long)c.sp * p.n + c.b) * p.Tq + (long)c.qt * TQ + r;
+      float* op = p.o_part + row_g * DV;
+#pragma unroll 1
+      for (int ch = 0; ch < 2; ++ch) {
+        uint32_t o[32];
+        if (n_kv > 0) {
+          tmem_ld_x32(to + 32 * ch, o);
+          tmem_ld_wait();
+        } else {
+#pragma unroll
+          for (int i = 0; i < 32; ++i) o[i] = 0u;                     // empty split: weight 0 in the combine (m = -inf, l = 0)
+        }
+#pragma unroll
+        for (int i = 0; i < 8; ++i)
+          st_global_f4(op + 32 * ch + 4 * i, make_float4(__uint_as_float(o[4 * i]), __uint_as_float(o[4 * i + 1]),
+                                                          __uint_as_float(o[4 * i + 2]), __uint_as_float(o[4 * i + 3])));
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(o_free);
+      p.ml_part[row_g * 2] = m_run;
+      p.ml_part[row_g * 2 + 1] = l_run;
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, fa64::TMEM_COLS);
+  }
+}
+
+// out[b][t][:] = sum_s O_s 2^(m_s - m) / sum_s l_s 2^(m_s - m)  (bf16, 64 wide), one warp per query row
+__global__ void attn64_combine_kernel(const float* __restrict__ o_part, const float* __restrict__ ml_part, bf16* __restrict__ out,
+                                      long rows, int splits) {
+  const long row = (long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  const int lane = threadIdx.x & 31;
+  if (row >= rows) return;
+  float m = -INFINITY;
+  for (int s = 0; s < splits; ++s) m = fmaxf(m, ml_part[((long)s * rows + row) * 2]);
+  float l = 0.f, a0 = 0.f, a1 = 0.f;
+  for (int s = 0; s < splits; ++s) {
+    const float ms = ml_part[((long)s * rows + row) * 2];
+    const float w = ms == -INFINITY ? 0.f : exp2f(ms - m);
+    l = fmaf(ml_part[((long)s * rows + row) * 2 + 1], w, l);
+    const float2 v = *reinterpret_cast<const float2*>(o_part + ((long)s * rows + row) * 64 + lane * 2);
+    a0 = fmaf(v.x, w, a0); a1 = fmaf(v.y, w, a1);
+  }
+  const float inv = 1.0f / l;
+  *reinterpret_cast<uint32_t*>(out + row * 64 + lane * 2) = pack_bf16x2(a0 * inv, a1 * inv);
+}
+
+// ------------------------------------------------------------------------------------------
+// host side
+// ------------------------------------------------------------------------------------------
+typedef CUresult (*EncodeTiledFn64)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                    const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                    CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static EncodeTiledFn64 fa64_encode_fn() {
+  static EncodeTiledFn64 fn = nullptr;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    void* f = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &f, cudaEnableDefault, &q) == cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiledFn64>(f);
+  });
+  return fn;
+}
+
+// [batch][rows][width] bf16, box {64, 128, 1}, 128B swizzle; rows past `rows` read as zero
+static int fa64_map(CUtensorMap* m, const bf16* ptr, int width, long rows, long batch, long batch_stride) {
+  EncodeTiledFn64 enc = fa64_encode_fn();
+  if (!enc) { set_error("cuTensorMapEncodeTiled entry point not available"); return 1; }
+  if ((reinterpret_cast<uintptr_t>(ptr) & 15) || (batch_stride * 2) % 16) { set_error("flash_attention_hd256_v64: operand not 16B aligned"); return 1; }
+  const cuuint64_t dims[3] = {(cuuint64_t)width, (cuuint64_t)rows, (cuuint64_t)batch};
+  const cuuint64_t strides[2] = {(cuuint64_t)width * 2, (cuuint64_t)batch_stride * 2};
+  const cuuint32_t box[3] = {64, 128, 1};
+  const cuuint32_t estr[3] = {1, 1, 1};
+  CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<bf16*>(ptr), dims, strides, box, estr,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) { set_error("flash_attention_hd256_v64: cuTensorMapEncodeTiled failed (%d)", (int)r); return 1; }
+  return 0;
+}
+
+int flash_attention_hd256_v64_splits(int n, int Tq, long Lk) {
+  // same wave-cost model as the 256-wide kernel, in 128-key tiles; the partials are a quarter of the size
+  const long q_units = (long)n * (Tq / fa64::TQ);
+  const long kv_tiles = (Lk + fa64::TK - 1) / fa64::TK;
+  const long sms = num_sms();
+  long best = 1;
+  double best_cost = 1e30;
+  for (long s = 1; s <= 16 && s <= kv_tiles; ++s) {
+    const long per = (kv_tiles + s - 1) / s;
+    const long eff = (kv_tiles + per - 1) / per;
+    if (eff != s) continue;
+    const long waves = (q_units * s + sms - 1) / sms;
+    const double cost = (double)waves * (per + 2.0) + 0.004 * s * (double)q_units;
+    if (cost < best_cost - 1e-9) { best_cost = cost; best = s; }
+  }
+  return (int)best;
+}
+
+int flash_attention_hd256_v64(const bf16* q, long q_batch_stride, const bf16* k, long k_batch_stride, const bf16* v,
+                              long v_batch_stride, int n, int Tq, long Lk, const int* lk_rows, float* o_part, float* ml_part,
+                              bf16* out, cudaStream_t stream) {
+  using namespace fa64;
+  if (n <= 0 || Tq <= 0 || Tq % TQ || Lk <= 0) { set_error("flash_attention_hd256_v64: bad shape n=%d Tq=%d Lk=%ld", n, Tq, Lk); return 1; }
+  CUtensorMap mq, mk, mv;
+  if (fa64_map(&mq, q, 256, Tq, n, q_batch_stride) || fa64_map(&mk, k, 256, Lk, n, k_batch_stride) ||
+      fa64_map(&mv, v, 64, Lk, n, v_batch_stride)) return 1;
+  static PerDeviceFlag attr;
+  if (!attr.is_set()) {
+    cudaError_t e = cudaFuncSetAttribute(flash_attn_hd256_v64_tcgen05_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM);
+    if (e != cudaSuccess) { set_error("cudaFuncSetAttribute(flash_attn_hd256_v64): %s", cudaGetErrorString(e)); return 1; }
+    attr.set();
+  }
+  Fa64Params p;
+  p.o_part = o_part; p.ml_part = ml_part; p.lk_rows = lk_rows; p.n = n; p.Tq = Tq; p.Lk = (int)Lk;
+  p.q_tiles = Tq / TQ;
+  p.kv_tiles = (int)((Lk + TK - 1) / TK);
+  p.splits = flash_attention_hd256_v64_splits(n, Tq, Lk);
+  p.tiles_per_split = (p.kv_tiles + p.splits - 1) / p.splits;
+  p.num_units = n * p.q_tiles * p.splits;
+  p.scale_log2 = 1.4426950408889634f / 16.0f;
+  const int grid = p.num_units < num_sms() ? p.num_units : num_sms();
+  {
+    char nm[96];
+    if (g_prof_on) snprintf(nm, sizeof(nm), "attn256v64 n%d q%d k%ld splits%d", n, Tq, Lk, p.splits);
+    // algorithmic work of the reference's attention over 256-wide projected values (4 T Lk 256); the kernel itself issues
+    // 2 T Lk (256 + 64) because v_proj is applied after P V
+    ProfRange pr(stream, nm, 4.0 * n * (double)Tq * (double)Lk * D, ((double)n * (Tq * 256.0 + Lk * 320.0)) * 2.0);
+    flash_attn_hd256_v64_tcgen05_kernel<<<grid, THREADS, SMEM, stream>>>(mq, mk, mv, p);
+    SAM2B_CHECK_LAUNCH("flash_attn_hd256_v64_tcgen05");
+  }
+  {
+    const long rows = (long)n * Tq;
+    ProfRange pr(stream, "attn64_combine", 0.0, (double)rows * DV * (4.0 * p.splits + 2.0));
+    attn64_combine_kernel<<<(unsigned)((rows + 7) / 8), 256, 0, stream>>>(o_part, ml_part, out, rows, p.splits);
+    SAM2B_CHECK_LAUNCH("attn64_combine");
+  }
+  return 0;
+}
+
+}  // namespace sam2b

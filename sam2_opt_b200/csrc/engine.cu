@@ -237,6 +237,8 @@ static int finalize(sam2b_engine* e) {
     const std::string d = "derived.memattn." + std::to_string(l) + ".";
     TRY(need(e, d + "sa_qk.weight", nullptr, true));          // [512,256] = cat(q_proj, k_proj)
     TRY(need(e, d + "sa_qk.bias", nullptr, false));
+    TRY(need(e, d + "ca_ov.weight", nullptr, true));          // [256,64] = out_proj o v_proj of the cross-attention
+    TRY(need(e, d + "ca_ov.bias", nullptr, false));
     for (const char* lin : {"self_attn.v_proj.", "self_attn.out_proj.", "cross_attn_image.q_proj.", "cross_attn_image.k_proj.",
                             "cross_attn_image.v_proj.", "cross_attn_image.out_proj.", "linear1.", "linear2."}) {
       TRY(need(e, p + lin + "weight", nullptr, true));
@@ -518,16 +520,31 @@ static int image_encode_mb(sam2b_engine* e, const float* img, int n, int normali
 // projections and FFN run on the tcgen05 GEMM (K1), softmax(q k^T / 16) v on the hd-256 flash kernel (K4): the score and
 // probability matrices never reach HBM.
 // ------------------------------------------------------------------------------------------------------------
+// rows_host (optional, [2][n]): frames L_b and pointer tokens P_b of every object (objects added on different frames have
+// different banks); nullptr = L and P for all.
 static int memory_attention_mb(sam2b_engine* e, const float* curr, const float* curr_pos, const float* memory,
                                const float* memory_pos, int L, const float* excl, const float* pos_excl, int P, int n,
-                               int n_total, float* out, cudaStream_t st) {
+                               int n_total, const int* rows_host, float* out, cudaStream_t st) {
   // curr/memory pointers address object 0 of this micro-batch inside tensors whose batch dimension is n_total
   const int T = 4096, C = 256;
   const long Lk = (long)L * 4096 + P;
-  const long Lkp = (Lk + 63) / 64 * 64;
+  const long Lkp = (Lk + 127) / 128 * 128;
   const long TT = (long)n * T;
   float *X, *QK, *KC32, *OUT;
-  bf16 *XN, *Qb, *Kb, *Vb, *KIN, *VIN, *Kc, *Vc, *O, *HID;
+  bf16 *XN, *Qb, *Kb, *Vb, *KIN, *VIN, *Kc, *O, *O64, *HID;
+  // per-object row counts on the device: [0][b] spatial keys, [1][b] pointer tokens, [2][b] keys in total
+  int* ROWS = nullptr;
+  if (rows_host) {
+    TRY(ws_get_t(e, "ma_rows", (size_t)3 * n, &ROWS));
+    std::vector<int> r(3 * (size_t)n);
+    for (int b = 0; b < n; ++b) {
+      r[b] = rows_host[b] * 4096;
+      r[n + b] = rows_host[n + b];
+      r[2 * n + b] = r[b] + r[n + b];
+    }
+    // pageable source: staged by the runtime before the call returns, stream-ordered afterwards
+    CUDA_OK(cudaMemcpyAsync(ROWS, r.data(), r.size() * sizeof(int), cudaMemcpyHostToDevice, st));
+  }
   TRY(ws_get_t(e, "ma_x", (size_t)TT * C, &X));
   TRY(ws_get_t(e, "ma_qk", (size_t)TT * 512, &QK));
   TRY(ws_get_t(e, "ma_kc32", (size_t)n * Lk * C, &KC32));
@@ -539,15 +556,15 @@ static int memory_attention_mb(sam2b_engine* e, const float* curr, const float* 
   TRY(ws_get_t(e, "ma_kin", (size_t)n * Lkp * 64, &KIN));
   TRY(ws_get_t(e, "ma_vin", (size_t)n * Lkp * 64, &VIN));
   TRY(ws_get_t(e, "ma_kc", (size_t)n * Lkp * C, &Kc));
-  TRY(ws_get_t(e, "ma_vc", (size_t)n * Lkp * C, &Vc));
   TRY(ws_get_t(e, "ma_o", (size_t)TT * C, &O));
+  TRY(ws_get_t(e, "ma_o64", (size_t)TT * 64, &O64));
   TRY(ws_get_t(e, "ma_hid", (size_t)TT * 2048, &HID));
   const float* cos_t = W32(e, "derived.rope.cos");
   const float* sin_t = W32(e, "derived.rope.sin");
 
   if (n == n_total) {
     TRY(memattn_prep_x(curr, curr_pos, X, T, n, C, st));
-    TRY(memattn_prep_memory(memory, memory_pos, L, excl, pos_excl, P, n, KIN, VIN, Lkp, st));
+    TRY(memattn_prep_memory(memory, memory_pos, L, excl, pos_excl, P, n, ROWS, KIN, VIN, Lkp, st));
   } else {
     set_error("memory_attention: object micro-batching of a strided batch is not supported (n=%d of %d)", n, n_total);
     return 1;
@@ -570,6 +587,15 @@ static int memory_attention_mb(sam2b_engine* e, const float* curr, const float* 
     TRY(ws_get_t(e, "ma_part", (size_t)splits * n * T * (C + 2), &part));
     return flash_attention_hd256(q, (long)T * C, k, rows_alloc * C, v, rows_alloc * C, n, T, keys, part,
                                  part + (size_t)splits * n * T * C, O, st);
+  };
+  // cross-attention core (K4b, attn_hd256_v64.cu): the values are the un-projected 64-wide memory rows (VIN), v_proj is applied
+  // together with out_proj afterwards ("ca_ov"); per-object key counts when the objects' banks differ
+  auto attend_v64 = [&](const bf16* q, const bf16* k, const bf16* v) -> int {
+    const int splits = flash_attention_hd256_v64_splits(n, T, Lk);
+    float* part = nullptr;
+    TRY(ws_get_t(e, "ma_part", (size_t)splits * n * T * (64 + 2), &part));
+    return flash_attention_hd256_v64(q, (long)T * C, k, Lkp * C, v, Lkp * 64, n, T, Lk, ROWS ? ROWS + 2 * n : nullptr, part,
+                                     part + (size_t)splits * n * T * 64, O64, st);
   };
   for (int l = 0; l < 4; ++l) {
     const std::string p = "memory_attention.layers." + std::to_string(l) + ".";
@@ -595,10 +621,10 @@ static int memory_attention_mb(sam2b_engine* e, const float* curr, const float* 
       g.out_f32 = KC32; g.ldc = C; g.c_batch_stride = Lk * C;
       TRY(gemm_bf16(g, st));
     }
-    TRY(rope_cast_batched(KC32, C, cos_t, sin_t, Kc, n, Lk, (long)L * 4096, Lkp, st));
-    TRY(linear(VIN, 64, (int)(n * Lkp), p + "cross_attn_image.v_proj.", C, 64, ACT_NONE, nullptr, nullptr, Vc, C));
-    TRY(attend(Qb, Kc, Vc, Lkp, Lk));
-    TRY(linear(O, C, (int)TT, p + "cross_attn_image.out_proj.", C, C, ACT_NONE, X, X, nullptr, C));
+    TRY(rope_cast_batched(KC32, C, cos_t, sin_t, Kc, n, Lk, (long)L * 4096, Lkp, st, ROWS));
+    TRY(attend_v64(Qb, Kc, VIN));
+    // x += (softmax(q k^T / 16) memory) (Wo Wv)^T + (Wo bv + bo): v_proj and out_proj in one 64 -> 256 linear map
+    TRY(linear(O64, 64, (int)TT, d + "ca_ov.", C, 64, ACT_NONE, X, X, nullptr, C));
     // ---- FFN ----
     TRY(layernorm_rows(X, W32(e, p + "norm3.weight"), W32(e, p + "norm3.bias"), 1e-5f, XN, nullptr, TT, C, st));
     TRY(linear(XN, C, (int)TT, p + "linear1.", 2048, C, ACT_RELU, nullptr, nullptr, HID, 2048));
@@ -862,8 +888,32 @@ int sam2b_memory_attention(sam2b_handle h, const float* curr, const float* curr_
   if (P > 0 && (!memory_exclude || !memory_pos_exclude)) { set_error("sam2b_memory_attention: P=%d but memory_exclude is NULL", P); return 1; }
   ENTER_DEVICE(h->device);
   ENGINE_CALL(h, reinterpret_cast<cudaStream_t>(stream));
-  return memory_attention_mb(h, curr, curr_pos, memory, memory_pos, L, memory_exclude, memory_pos_exclude, P, n, n, out,
+  return memory_attention_mb(h, curr, curr_pos, memory, memory_pos, L, memory_exclude, memory_pos_exclude, P, n, n, nullptr, out,
                              reinterpret_cast<cudaStream_t>(stream));
+}
+
+int sam2b_memory_attention_varlen(sam2b_handle h, const float* curr, const float* curr_pos, const float* memory,
+                                  const float* memory_pos, int L_max, const float* memory_exclude, const float* memory_pos_exclude,
+                                  int P_max, int n, const int32_t* L_rows, const int32_t* P_rows, float* out, void* stream) {
+  if (!L_rows && !P_rows)
+    return sam2b_memory_attention(h, curr, curr_pos, memory, memory_pos, L_max, memory_exclude, memory_pos_exclude, P_max, n, out, stream);
+  if (!h || !h->finalized) { set_error("sam2b_memory_attention_varlen: engine not finalized"); return 1; }
+  if (!curr || !curr_pos || !memory || !memory_pos || !out || n <= 0) { set_error("sam2b_memory_attention_varlen: null/empty argument"); return 1; }
+  if (L_max < 1 || L_max > 16 || P_max < 0 || P_max > 64 || (P_max % 4)) { set_error("sam2b_memory_attention_varlen: L_max=%d must be in [1,16], P_max=%d in [0,64] and a multiple of 4", L_max, P_max); return 1; }
+  if (P_max > 0 && (!memory_exclude || !memory_pos_exclude)) { set_error("sam2b_memory_attention_varlen: P_max=%d but memory_exclude is NULL", P_max); return 1; }
+  std::vector<int> rows(2 * (size_t)n);
+  for (int b = 0; b < n; ++b) {
+    const int Lb = L_rows ? L_rows[b] : L_max, Pb = P_rows ? P_rows[b] : P_max;
+    if (Lb < 1 || Lb > L_max || Pb < 0 || Pb > P_max || (Pb % 4)) {
+      set_error("sam2b_memory_attention_varlen: object %d has L=%d (must be in [1,%d]) / P=%d (in [0,%d], multiple of 4)", b, Lb, L_max, Pb, P_max);
+      return 1;
+    }
+    rows[b] = Lb; rows[n + b] = Pb;
+  }
+  ENTER_DEVICE(h->device);
+  ENGINE_CALL(h, reinterpret_cast<cudaStream_t>(stream));
+  return memory_attention_mb(h, curr, curr_pos, memory, memory_pos, L_max, memory_exclude, memory_pos_exclude, P_max, n, n, rows.data(),
+                             out, reinterpret_cast<cudaStream_t>(stream));
 }
 
 int sam2b_memory_encode(sam2b_handle h, const float* pix_feat, const float* masks, int n, float* out_x, void* stream) {
@@ -997,6 +1047,21 @@ int sam2b_op_attention_hd256(const void* q, const void* k, const void* v, int n,
   return flash_attention_hd256(reinterpret_cast<const bf16*>(q), (long)tq * 256, reinterpret_cast<const bf16*>(k), lk * 256,
                                reinterpret_cast<const bf16*>(v), lk * 256, n, tq, lk, o_part, ml_part,
                                reinterpret_cast<bf16*>(out), reinterpret_cast<cudaStream_t>(stream));
+}
+
+int64_t sam2b_op_attention_hd256_v64_workspace(int n, int tq, int64_t lk) {
+  if (n <= 0 || tq <= 0 || lk <= 0) return 0;
+  return (int64_t)flash_attention_hd256_v64_splits(n, tq, lk) * n * tq * (64 + 2) * 4;
+}
+int sam2b_op_attention_hd256_v64(const void* q, const void* k, const void* v64, int n, int tq, int64_t lk, const int32_t* lk_rows_dev,
+                                 void* out, void* workspace, void* stream) {
+  if (!q || !k || !v64 || !out || !workspace) { set_error("sam2b_op_attention_hd256_v64: null argument"); return 1; }
+  const int splits = flash_attention_hd256_v64_splits(n, tq, lk);
+  float* o_part = reinterpret_cast<float*>(workspace);
+  float* ml_part = o_part + (size_t)splits * n * tq * 64;
+  return flash_attention_hd256_v64(reinterpret_cast<const bf16*>(q), (long)tq * 256, reinterpret_cast<const bf16*>(k), lk * 256,
+                                   reinterpret_cast<const bf16*>(v64), lk * 64, n, tq, lk, lk_rows_dev, o_part, ml_part,
+                                   reinterpret_cast<bf16*>(out), reinterpret_cast<cudaStream_t>(stream));
 }
 
 }  // extern "C"

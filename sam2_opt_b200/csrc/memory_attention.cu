@@ -53,20 +53,22 @@ int batch_to_seq(const float* x, float* out, int T, int n, int C, cudaStream_t s
 
 __global__ void __launch_bounds__(256) memattn_prep_memory_kernel(const float4* __restrict__ mem, const float4* __restrict__ mpos, int L,
                                                                   const float4* __restrict__ excl, const float4* __restrict__ pexcl, int P,
-                                                                  int n, uint2* __restrict__ kin, uint2* __restrict__ vin, long ldk) {
+                                                                  int n, const int* __restrict__ rows, uint2* __restrict__ kin,
+                                                                  uint2* __restrict__ vin, long ldk) {
   // one thread per 4 channels: 16 threads per 64-wide row
   const long total = (long)n * ldk * 16;
-  const long Ls = (long)L * 4096;
   for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
     const int c = (int)(i & 15);
     const long r = i >> 4;
     const int b = (int)(r / ldk);
     const long j = r - (long)b * ldk;
+    const long Ls = rows ? (long)rows[b] : (long)L * 4096;      // this object's spatial keys and pointer tokens
+    const int Pb = rows ? rows[n + b] : P;
     float4 m = make_float4(0.f, 0.f, 0.f, 0.f), p = m;
     if (j < Ls) {
       const long src = (j * n + b) * 16 + c;            // [L*4096][n][64]
       m = mem[src]; p = mpos[src];
-    } else if (j < Ls + P) {
+    } else if (j < Ls + Pb) {
       const long src = ((j - Ls) * n + b) * 16 + c;     // [P][n][64]
       m = excl[src]; p = pexcl[src];
     }
@@ -77,21 +79,22 @@ __global__ void __launch_bounds__(256) memattn_prep_memory_kernel(const float4* 
   }
 }
 int memattn_prep_memory(const float* memory, const float* memory_pos, int L, const float* excl, const float* pos_excl, int P,
-                        int n, bf16* kin, bf16* vin, long ldk, cudaStream_t stream) {
+                        int n, const int* rows, bf16* kin, bf16* vin, long ldk, cudaStream_t stream) {
   const long total = (long)n * ldk * 16;
   long blocks = (total + 255) / 256;
   if (blocks > (long)num_sms() * 16) blocks = (long)num_sms() * 16;
   ProfRange pr(stream, "memattn_prep_memory", 0, (double)total * 48.0);
   memattn_prep_memory_kernel<<<(unsigned)blocks, 256, 0, stream>>>(
       reinterpret_cast<const float4*>(memory), reinterpret_cast<const float4*>(memory_pos), L, reinterpret_cast<const float4*>(excl),
-      reinterpret_cast<const float4*>(pos_excl), P, n, reinterpret_cast<uint2*>(kin), reinterpret_cast<uint2*>(vin), ldk);
+      reinterpret_cast<const float4*>(pos_excl), P, n, rows, reinterpret_cast<uint2*>(kin), reinterpret_cast<uint2*>(vin), ldk);
   SAM2B_CHECK_LAUNCH("memattn_prep_memory");
   return 0;
 }
 
 __global__ void __launch_bounds__(256) rope_cast_batched_kernel(const float* __restrict__ x, long ldx, const float2* __restrict__ cos_t,
                                                                 const float2* __restrict__ sin_t, uint2* __restrict__ y, int batch,
-                                                                long rows_per_batch, long rope_rows, long rows_out) {
+                                                                long rows_per_batch, long rope_rows_all, long rows_out,
+                                                                const int* __restrict__ rope_rows_dev) {
   const long total = (long)batch * rows_out * 64;   // one thread per 2 pairs (4 values)
   for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
     const int j = (int)(i & 63);
@@ -99,6 +102,7 @@ __global__ void __launch_bounds__(256) rope_cast_batched_kernel(const float* __r
     const int b = (int)(rr / rows_out);
     const long r = rr - (long)b * rows_out;
     float4 o = make_float4(0.f, 0.f, 0.f, 0.f);
+    const long rope_rows = rope_rows_dev ? (long)rope_rows_dev[b] : rope_rows_all;
     if (r < rows_per_batch) {
       const float4 v = *reinterpret_cast<const float4*>(x + ((long)b * rows_per_batch + r) * ldx + j * 4);
       o = v;
@@ -118,14 +122,14 @@ __global__ void __launch_bounds__(256) rope_cast_batched_kernel(const float* __r
   }
 }
 int rope_cast_batched(const float* x, long ldx, const float* cos_t, const float* sin_t, bf16* y, int batch, long rows_per_batch,
-                      long rope_rows, long rows_out, cudaStream_t stream) {
+                      long rope_rows, long rows_out, cudaStream_t stream, const int* rope_rows_dev) {
   if (ldx % 4) { set_error("rope_cast_batched: ldx=%ld", ldx); return 1; }
   const long total = (long)batch * rows_out * 64;
   long blocks = (total + 255) / 256;
   if (blocks > (long)num_sms() * 16) blocks = (long)num_sms() * 16;
   ProfRange pr(stream, "rope_cast", 0, (double)total * 24.0);
   rope_cast_batched_kernel<<<(unsigned)blocks, 256, 0, stream>>>(x, ldx, reinterpret_cast<const float2*>(cos_t), reinterpret_cast<const float2*>(sin_t),
-                                                                reinterpret_cast<uint2*>(y), batch, rows_per_batch, rope_rows, rows_out);
+                                                                reinterpret_cast<uint2*>(y), batch, rows_per_batch, rope_rows, rows_out, rope_rows_dev);
   SAM2B_CHECK_LAUNCH("rope_cast_batched");
   return 0;
 }

@@ -109,6 +109,15 @@ int flash_attention_hd256(const bf16* q, long q_batch_stride, const bf16* k, lon
 // Sine position encoding of one feature level (reference PositionEmbeddingSine): out [C][H][W] fp32
 int position_sine(float* out, int C, int H, int W, cudaStream_t stream);
 
+// K4b (attn_hd256_v64.cu): cross-attention core with the value projection folded behind P V: q [n][Tq][256], k [n][Lk][256],
+// v [n][Lk][64] (the un-projected memory) bf16 -> out [n][Tq][64] bf16 = softmax(q k^T / 16) v.  lk_rows: optional DEVICE array of
+// per-object key counts (<= Lk); v rows in [lk_rows[b], Lk) must hold finite values.  o_part / ml_part: splits*n*Tq*64 and
+// splits*n*Tq*2 floats with splits = flash_attention_hd256_v64_splits(n, Tq, Lk).
+int flash_attention_hd256_v64_splits(int n, int Tq, long Lk);
+int flash_attention_hd256_v64(const bf16* q, long q_batch_stride, const bf16* k, long k_batch_stride, const bf16* v,
+                              long v_batch_stride, int n, int Tq, long Lk, const int* lk_rows, float* o_part, float* ml_part,
+                              bf16* out, cudaStream_t stream);
+
 // Row softmax over fp32 scores -> bf16 probabilities (row stride lds / ldp elements), `cols` valid columns;
 // columns in [cols, ldp) are written as zero.
 int softmax_rows(const float* s, long lds, bf16* p, long ldp, long rows, int cols, cudaStream_t stream);
@@ -145,12 +154,16 @@ int memattn_prep_x(const float* curr, const float* curr_pos, float* x, int T, in
 int batch_to_seq(const float* x, float* out, int T, int n, int C, cudaStream_t stream);
 // kin[b][j] = bf16(mem + pos), vin[b][j] = bf16(mem);  j = l*4096+t for the L spatial frames then L*4096+p for the P
 // pointer tokens; rows [Lk, ldk) of each batch are zero-filled.
+// rows: optional DEVICE array [2][n] = (spatial keys L_b * 4096, pointer tokens P_b) of every object (nullptr: L * 4096 and
+// P for all); object b then uses memory[0 .. L_b) and excl[0 .. P_b), packed back to back, zero rows behind.
 int memattn_prep_memory(const float* memory, const float* memory_pos, int L, const float* excl, const float* pos_excl,
-                        int P, int n, bf16* kin, bf16* vin, long ldk, cudaStream_t stream);
+                        int P, int n, const int* rows, bf16* kin, bf16* vin, long ldk, cudaStream_t stream);
 // Batch-aware RoPE + cast: x fp32 [batch][rows_per_batch][ldx] (first 256 columns of each row) -> y bf16
 // [batch][rows_out_per_batch][256]; rows r < rope_rows of each batch are rotated with table row (r % 4096).
+// rope_rows_dev: optional DEVICE array [batch] overriding rope_rows per batch entry.
 int rope_cast_batched(const float* x, long ldx, const float* cos_t, const float* sin_t, bf16* y, int batch,
-                      long rows_per_batch, long rope_rows, long rows_out_per_batch, cudaStream_t stream);
+                      long rows_per_batch, long rope_rows, long rows_out_per_batch, cudaStream_t stream,
+                      const int* rope_rows_dev = nullptr);
 }  // namespace sam2b
 
 namespace sam2b {

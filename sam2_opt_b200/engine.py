@@ -170,7 +170,10 @@ class Engine:
         return out
 
     # -- E3 --------------------------------------------------------------------------------------------------
-    def memory_attention(self, curr, memory, curr_pos, memory_pos, memory_exclude=None, memory_pos_exclude=None):
+    def memory_attention(self, curr, memory, curr_pos, memory_pos, memory_exclude=None, memory_pos_exclude=None,
+                         L_rows=None, P_rows=None):
+        """E3.  L_rows / P_rows (optional sequences of n ints): objects whose banks differ share one call — the tensors are
+        padded to the largest bank and object b uses memory[:L_rows[b]] / memory_exclude[:P_rows[b]] only."""
         curr, curr_pos = _f32c(curr, "curr"), _f32c(curr_pos, "curr_pos")
         memory, memory_pos = _f32c(memory, "memory"), _f32c(memory_pos, "memory_pos")
         L, n = memory.shape[0], curr.shape[1]
@@ -178,6 +181,16 @@ class Engine:
         if P:
             memory_exclude, memory_pos_exclude = _f32c(memory_exclude, "memory_exclude"), _f32c(memory_pos_exclude, "memory_pos_exclude")
         out = torch.empty_like(curr)
+        if L_rows is not None or P_rows is not None:
+            arr = lambda v: None if v is None else (C.c_int32 * n)(*[int(x) for x in v])
+            if (L_rows is not None and len(L_rows) != n) or (P_rows is not None and len(P_rows) != n):
+                raise ValueError(f"memory_attention: L_rows / P_rows must have one entry per object ({n})")
+            with self._lock:
+                _lib.check(self.lib.sam2b_memory_attention_varlen(
+                    self._h, _ptr(curr), _ptr(curr_pos), _ptr(memory), _ptr(memory_pos), L,
+                    _ptr(memory_exclude if P else None), _ptr(memory_pos_exclude if P else None), P, n, arr(L_rows), arr(P_rows),
+                    _ptr(out), self._stream()), "memory_attention_varlen")
+            return out
         with self._lock:
             _lib.check(self.lib.sam2b_memory_attention(
                 self._h, _ptr(curr), _ptr(curr_pos), _ptr(memory), _ptr(memory_pos), L,

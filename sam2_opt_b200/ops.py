@@ -150,6 +150,25 @@ def attention_hd256(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor) -> torch.
 
 
 @on_tensor_device
+def attention_hd256_v64(q: torch.Tensor, k: torch.Tensor, v64: torch.Tensor, lk_rows: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """softmax(q k^T / 16) v64 with 64-wide values (cross-attention with v_proj folded behind it): q [n,tq,256], k [n,lk,256],
+    v64 [n,lk,64] bf16 -> [n,tq,64] bf16.  lk_rows: optional int32 CUDA tensor [n] of per-object key counts."""
+    lib = _lib.load()
+    assert q.dtype == k.dtype == v64.dtype == torch.bfloat16 and q.is_cuda
+    q, k, v64 = q.contiguous(), k.contiguous(), v64.contiguous()
+    n, tq, _ = q.shape
+    lk = k.shape[1]
+    assert k.shape == (n, lk, 256) and v64.shape == (n, lk, 64) and q.shape[2] == 256
+    if lk_rows is not None:
+        assert lk_rows.dtype == torch.int32 and lk_rows.is_cuda and lk_rows.numel() == n
+    out = torch.empty((n, tq, 64), device=q.device, dtype=torch.bfloat16)
+    ws = torch.empty(int(lib.sam2b_op_attention_hd256_v64_workspace(n, tq, lk)), device=q.device, dtype=torch.uint8)
+    _lib.check(lib.sam2b_op_attention_hd256_v64(_ptr(q), _ptr(k), _ptr(v64), n, tq, lk, _ptr(lk_rows), _ptr(out), _ptr(ws), _stream()),
+               "op_attention_hd256_v64")
+    return out
+
+
+@on_tensor_device
 def gemm_ln_producer(a: torch.Tensor, b: torch.Tensor, bias: torch.Tensor, residual: torch.Tensor, block_n: int = 0):
     """x = a @ b^T + bias + residual (fp32) -> (x, bf16(x), stats [M, parts, 2] partial (sum, sum x^2) per row)."""
     lib = _lib.load()

@@ -314,7 +314,8 @@ class SAM2VideoPredictor(_Base):
         if is_init:
             pix = f2 + self.w["no_mem_embed"].view(1, -1, 1, 1)
         else:
-            pix = self._memory_conditioned(st, t, [o], f2, pos2, per_object=True)
+            (cond_keys, hist), = self._history_groups(st, t, [o]).keys()
+            pix = self._memory_conditioned(st, t, [(cond_keys, hist, [o])], f2, pos2, per_object=True)
         # ref: _use_multimask, sam2_base_official.py:1181-1189 (multimask_output_for_tracking, 0 <= points <= 1)
         multimask = pts.shape[0] <= 1
         _, _, _, low, high, ptr, obj = H.forward_sam_heads(self.w, pix, point_inputs=pin, mask_inputs=prev_logits,
@@ -402,54 +403,85 @@ class SAM2VideoPredictor(_Base):
             groups.setdefault((cond_keys, hist), []).append(o)
         return groups
 
-    def _memory_conditioned(self, st, t, g_objs, f2, pos2, per_object=False, cond_keys=None, hist=None):
-        """Current-frame features fused with the memory bank of the objects `g_objs` (which share their history) through
-        boundary E3 (ref: _prepare_memory_conditioned_features, sam2_base_official.py:797-976) -> [n,256,64,64]."""
-        n, key = len(g_objs), tuple(g_objs)
+    def _group_memory(self, st, t, g_objs, per_object=False, cond_keys=None, hist=None):
+        """Memory bank + pointer tokens of the objects `g_objs` (which share their history) for frame t
+        (ref: _prepare_memory_conditioned_features, sam2_base_official.py:797-950) ->
+        [memory [L,4096,n,64], memory_pos, ptr tokens [P,n,64], ptr pos]."""
+        key = tuple(g_objs)
         if cond_keys is None:
             (cond_keys, hist), = self._history_groups(st, t, g_objs[:1]).keys()
         batched = {} if per_object else {tt: st["non_cond_b"].get(tt, {}).get(key) for tt in hist}
         if not per_object and all(v is not None for v in batched.values()):
             cond_b = {tt: self._stacked_cond(st, tt, key) for tt in cond_keys}
-            mem = H.assemble_memory(self.w, t, cond_b, batched, st["num_frames"], cache=self._tpos_cache)
-        else:
-            per = []
-            for o in g_objs:
-                cond = {tt: st["cond"][tt][o] for tt in cond_keys}
-                nc = {tt: r for tt, r in st["non_cond"].get(o, {}).items() if r["maskmem_features"] is not None}
-                per.append(H.assemble_memory(self.w, t, cond, nc, st["num_frames"], cache=self._tpos_cache))
-            mem = [torch.cat([m[i] for m in per], dim=2 if i < 2 else 1) for i in range(4)]
-        P = mem[2].shape[0]
+            return list(H.assemble_memory(self.w, t, cond_b, batched, st["num_frames"], cache=self._tpos_cache))
+        per = []
+        for o in g_objs:
+            cond = {tt: st["cond"][tt][o] for tt in cond_keys}
+            nc = {tt: r for tt, r in st["non_cond"].get(o, {}).items() if r["maskmem_features"] is not None}
+            per.append(H.assemble_memory(self.w, t, cond, nc, st["num_frames"], cache=self._tpos_cache))
+        return [torch.cat([m[i] for m in per], dim=2 if i < 2 else 1) for i in range(4)]
+
+    def _memory_conditioned(self, st, t, groups, f2, pos2, per_object=False):
+        """Current-frame features fused with the memory banks through boundary E3 -> [n_total,256,64,64] in the order of the
+        concatenated groups.  `groups`: [(cond_keys, hist, [objects])].  Groups whose banks differ in size (objects added or
+        re-prompted on different frames) still share ONE engine call: the banks are padded to the largest and the engine gets
+        the per-object frame / pointer counts (sam2b_memory_attention_varlen; SURVEY section 8a "dynamic shapes")."""
+        mems = [self._group_memory(st, t, objs, per_object, ck, hs) for ck, hs, objs in groups]
+        sizes = [(m[0].shape[0], m[2].shape[0], m[0].shape[2]) for m in mems]          # (L, P, n) per group
+        n = sum(sz[2] for sz in sizes)
         curr = f2.flatten(2).permute(2, 0, 1).expand(-1, n, -1)
         curr_pos = pos2.flatten(2).permute(2, 0, 1).expand(-1, n, -1)
-        if P:
-            pix = self._ex["memory_attention_exclude"].Inference([curr, mem[0], curr_pos, mem[1], mem[2], mem[3]], output_type="torch")[0]
+        if len({sz[:2] for sz in sizes}) == 1:
+            mem = mems[0] if len(mems) == 1 else [torch.cat([m[i] for m in mems], dim=2 if i < 2 else 1) for i in range(4)]
+            if sizes[0][1]:
+                pix = self._ex["memory_attention_exclude"].Inference([curr, mem[0], curr_pos, mem[1], mem[2], mem[3]], output_type="torch")[0]
+            else:
+                pix = self._ex["memory_attention_none"].Inference([curr, mem[0], curr_pos, mem[1]], output_type="torch")[0]
         else:
-            pix = self._ex["memory_attention_none"].Inference([curr, mem[0], curr_pos, mem[1]], output_type="torch")[0]
+            Lm, Pm = max(sz[0] for sz in sizes), max(sz[1] for sz in sizes)
+            mem = torch.zeros((Lm, 4096, n, H.MEM_DIM), device=self.device)
+            mpos = torch.zeros_like(mem)
+            ptr = torch.zeros((max(Pm, 4), n, H.MEM_DIM), device=self.device)
+            ppos = torch.zeros_like(ptr)
+            L_rows, P_rows, o0 = [], [], 0
+            for m, (L, P, ng) in zip(mems, sizes):
+                mem[:L, :, o0:o0 + ng], mpos[:L, :, o0:o0 + ng] = m[0], m[1]
+                if P:
+                    ptr[:P, o0:o0 + ng], ppos[:P, o0:o0 + ng] = m[2], m[3]
+                L_rows += [L] * ng
+                P_rows += [P] * ng
+                o0 += ng
+            pix = self.engine.memory_attention(curr, mem, curr_pos, mpos, ptr[:Pm] if Pm else None, ppos[:Pm] if Pm else None,
+                                               L_rows=L_rows, P_rows=P_rows)
         return pix.permute(1, 2, 0).reshape(n, H.D_MODEL, 64, 64)
 
     def _track_frame(self, st, t, objs):
         """One non-prompted frame for a list of objects, batched through the engine (ref: track_step,
-        sam2_base_official.py:1028-1179)."""
+        sam2_base_official.py:1028-1179): ONE memory-attention call, ONE pass of the SAM heads and ONE memory-encoder call for
+        all objects, whatever their histories."""
         f2, pos2, hr = self._features(st, t)
-        results = {}
-        for (cond_keys, hist), g_objs in self._history_groups(st, t, objs).items():
-            n, key = len(g_objs), tuple(g_objs)
-            pix = self._memory_conditioned(st, t, g_objs, f2, pos2, cond_keys=cond_keys, hist=hist)
-            if self.graph_heads:
-                gk = (n, threading.get_ident())    # static buffers are per graph: one graph per host thread
-                if gk not in self._heads_graphs:
-                    self._heads_graphs[gk] = _GraphedHeads(self.w, n, self._dense_pe, self.device)
-                low, high, ptr, obj = self._heads_graphs[gk](pix, hr)
-            else:
-                hr_n = [h.expand(n, -1, -1, -1) for h in hr]
-                _, _, _, low, high, ptr, obj = H.forward_sam_heads(self.w, pix, high_res_features=hr_n, multimask_output=True, pe=self._dense_pe)
-            mf, mp = self._encode_memory(f2, high, obj, from_points=False)
-            low = self._fill_holes(low)            # after the memory is encoded from the unfilled masks, as in the reference
-            st["non_cond_b"].setdefault(t, {})[key] = {"maskmem_features": mf, "maskmem_pos": mp, "obj_ptr": ptr}
-            for i, o in enumerate(g_objs):
-                results[o] = {"pred_masks": low[i:i + 1], "obj_ptr": ptr[i:i + 1], "object_score_logits": obj[i:i + 1],
-                              "maskmem_features": mf[i:i + 1], "maskmem_pos": mp[i:i + 1]}
+        groups = [(ck, hs, g) for (ck, hs), g in self._history_groups(st, t, objs).items()]
+        order = [o for _, _, g in groups for o in g]
+        n = len(order)
+        pix = self._memory_conditioned(st, t, groups, f2, pos2)
+        if self.graph_heads:
+            gk = (n, threading.get_ident())    # static buffers are per graph: one graph per host thread
+            if gk not in self._heads_graphs:
+                self._heads_graphs[gk] = _GraphedHeads(self.w, n, self._dense_pe, self.device)
+            low, high, ptr, obj = self._heads_graphs[gk](pix, hr)
+        else:
+            hr_n = [h.expand(n, -1, -1, -1) for h in hr]
+            _, _, _, low, high, ptr, obj = H.forward_sam_heads(self.w, pix, high_res_features=hr_n, multimask_output=True, pe=self._dense_pe)
+        mf, mp = self._encode_memory(f2, high, obj, from_points=False)
+        low = self._fill_holes(low)            # after the memory is encoded from the unfilled masks, as in the reference
+        results, o0 = {}, 0
+        for _, _, g_objs in groups:
+            sl = slice(o0, o0 + len(g_objs))
+            st["non_cond_b"].setdefault(t, {})[tuple(g_objs)] = {"maskmem_features": mf[sl], "maskmem_pos": mp[sl], "obj_ptr": ptr[sl]}
+            o0 += len(g_objs)
+        for i, o in enumerate(order):
+            results[o] = {"pred_masks": low[i:i + 1], "obj_ptr": ptr[i:i + 1], "object_score_logits": obj[i:i + 1],
+                          "maskmem_features": mf[i:i + 1], "maskmem_pos": mp[i:i + 1]}
         return [results[o] for o in objs]
 
     def _stacked_cond(self, st, t, key):

@@ -79,6 +79,16 @@ def derive(w: Dict[str, torch.Tensor]) -> Dict[str, torch.Tensor]:
         if sa + "q_proj.weight" in w:
             d[f"derived.memattn.{l}.sa_qk.weight"] = torch.cat([w[sa + "q_proj.weight"], w[sa + "k_proj.weight"]], 0).float().contiguous()
             d[f"derived.memattn.{l}.sa_qk.bias"] = torch.cat([w[sa + "q_proj.bias"], w[sa + "k_proj.bias"]], 0).float().contiguous()
+    # cross-attention: the attention weights of a row sum to one, so softmax(.) (m Wv^T + bv) = (softmax(.) m) Wv^T + bv and
+    # v_proj composes with out_proj into ONE 64 -> 256 map applied after the attention over the un-projected memory
+    # (ref: modeling/sam/transformer.py:265-296 with kv_in_dim = 64; engine: attn_hd256_v64.cu)
+    for l in range(4):
+        ca = f"memory_attention.layers.{l}.cross_attn_image."
+        if ca + "v_proj.weight" in w:
+            Wv, bv = w[ca + "v_proj.weight"].double(), w[ca + "v_proj.bias"].double()
+            Wo, bo = w[ca + "out_proj.weight"].double(), w[ca + "out_proj.bias"].double()
+            d[f"derived.memattn.{l}.ca_ov.weight"] = (Wo @ Wv).float().contiguous()          # [256, 64]
+            d[f"derived.memattn.{l}.ca_ov.bias"] = (Wo @ bv + bo).float().contiguous()
     # memory encoder: last down-sampler conv as an im2col GEMM with k = (ky,kx,cin); depthwise weights tap-major
     k9 = "memory_encoder.mask_downsampler.encoder.9.weight"
     if k9 in w:

@@ -74,3 +74,86 @@ def test_e3_argument_errors(engine):
     with pytest.raises(RuntimeError, match="L="):
         engine.memory_attention(ins[0], torch.zeros(17, 4096, 1, 64, device="cuda"), ins[2],
                                 torch.zeros(17, 4096, 1, 64, device="cuda"), ins[4], ins[5])
+
+
+def _attn_ref(q, k, v, lk=None):
+    """fp32 softmax(q k^T / 16) v over the first lk keys"""
+    q, k, v = q.float(), k.float(), v.float()
+    if lk is not None:
+        k, v = k[:lk], v[:lk]
+    s = (q @ k.t()) / 16.0
+    return torch.softmax(s, dim=-1) @ v
+
+
+@pytest.mark.parametrize("n,tq,lk", [(1, 4096, 28736), (2, 256, 4104), (3, 128, 300), (1, 128, 128), (16, 256, 8196)])
+def test_attention_hd256_v64_matches_fp32(n, tq, lk):
+    """The cross-attention core over 64-wide (un-projected) values, 128-key tiles, ragged tails and KV splits, against fp32
+    torch on the same bf16 operands.  Tolerance: P is rounded to bf16 before P V (2^-9 relative per term, averaging down
+    over the keys) and the output is bf16: 1e-2 relative L2, as for the 256-wide kernel."""
+    from sam2_opt_b200 import ops
+    g = torch.Generator(device="cuda").manual_seed(n * 1000 + lk)
+    q = torch.randn(n, tq, 256, device="cuda", generator=g).bfloat16()
+    k = (torch.randn(n, lk, 256, device="cuda", generator=g) * 1.5).bfloat16()
+    v = torch.randn(n, lk, 64, device="cuda", generator=g).bfloat16()
+    out = ops.attention_hd256_v64(q, k, v)
+    assert out.shape == (n, tq, 64)
+    for b in range(n):
+        want = _attn_ref(q[b], k[b], v[b])
+        r = ((out[b].float() - want).norm() / want.norm()).item()
+        assert r < 1e-2, (b, r)
+
+
+def test_attention_hd256_v64_per_object_key_counts():
+    """Objects of one call with different key counts: each must match fp32 torch on its own truncated operands and its own
+    single-object call (different KV split counts: fp32 summation order and one bf16 rounding of the output, 5e-3); what lies
+    behind an object's count never reaches the result even when it is huge (masked by index, not by value)."""
+    from sam2_opt_b200 import ops
+    g = torch.Generator(device="cuda").manual_seed(5)
+    n, tq, lk = 4, 256, 12352
+    counts = [12352, 4100, 1, 8196]
+    q = torch.randn(n, tq, 256, device="cuda", generator=g).bfloat16()
+    k = (torch.randn(n, lk, 256, device="cuda", generator=g) * 1.5).bfloat16()
+    v = torch.randn(n, lk, 64, device="cuda", generator=g).bfloat16()
+    for b, c in enumerate(counts):
+        k[b, c:] = 1e4                       # would dominate every softmax if it leaked in
+        v[b, c:] = 3e4                       # finite, as the contract requires
+    out = ops.attention_hd256_v64(q, k, v, torch.tensor(counts, dtype=torch.int32, device="cuda"))
+    for b, c in enumerate(counts):
+        want = _attn_ref(q[b], k[b], v[b], c)
+        r = ((out[b].float() - want).norm() / want.norm()).item()
+        assert r < 1e-2, (b, c, r)
+        alone = ops.attention_hd256_v64(q[b:b + 1], k[b:b + 1, :c].contiguous(), v[b:b + 1, :c].contiguous())
+        assert ((out[b].float() - alone[0].float()).norm() / want.norm()).item() < 5e-3
+
+
+def test_memory_attention_objects_with_different_banks_share_one_call(engine, weights):
+    """sam2b_memory_attention_varlen: three objects with (L, P) = (7, 64), (2, 8), (4, 0) in ONE call, padded to (7, 64); every
+    object must match the fp32 oracle on its own un-padded bank and its own single-object call."""
+    from oracle import sam2_oracle as O
+    from oracle.synth import synth_memattn_inputs
+    shapes = [(7, 64), (2, 8), (4, 0)]
+    Lm, Pm, n = 7, 64, len(shapes)
+    per = [synth_memattn_inputs(L, P, 1, seed=20 + i) for i, (L, P) in enumerate(shapes)]
+    curr = torch.cat([p[0] for p in per], 1)
+    curr_pos = torch.cat([p[2] for p in per], 1)
+    mem = torch.full((Lm, 4096, n, 64), float("nan"))           # the padding must never be read
+    mpos = torch.full((Lm, 4096, n, 64), float("nan"))
+    ex = torch.full((Pm, n, 64), float("nan"))
+    pex = torch.full((Pm, n, 64), float("nan"))
+    for i, ((L, P), p) in enumerate(zip(shapes, per)):
+        mem[:L, :, i], mpos[:L, :, i] = p[1][:, :, 0], p[3][:, :, 0]
+        ex[:P, i], pex[:P, i] = p[4][:, 0], p[5][:, 0]
+    got = engine.memory_attention(curr.cuda(), mem.cuda(), curr_pos.cuda(), mpos.cuda(), ex.cuda(), pex.cuda(),
+                                  L_rows=[s[0] for s in shapes], P_rows=[s[1] for s in shapes]).cpu()
+    assert torch.isfinite(got).all()
+    for i, ((L, P), p) in enumerate(zip(shapes, per)):
+        with torch.no_grad():
+            want = O.memory_attention(weights, *p)[:, 0]
+        r = ((got[:, i].double() - want.double()).norm() / want.double().norm()).item()
+        print(f"varlen object {i} (L={L}, P={P}): rel-L2 vs oracle = {r:.4%}")
+        assert r <= 2e-2
+        dev = [t.cuda() for t in p]
+        alone = engine.memory_attention(dev[0], dev[1], dev[2], dev[3], dev[4] if P else None, dev[5] if P else None).cpu()[:, 0]
+        assert ((got[:, i] - alone).norm() / alone.norm()).item() < 5e-3
+    with pytest.raises(RuntimeError, match="object 1 has L=9"):
+        engine.memory_attention(curr.cuda(), mem.cuda(), curr_pos.cuda(), mpos.cuda(), ex.cuda(), pex.cuda(), L_rows=[7, 9, 1], P_rows=[64, 8, 0])
