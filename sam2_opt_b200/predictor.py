@@ -11,6 +11,7 @@ Differences from the reference that are deliberate: all objects of a video are b
 per frame (the reference loops objects with batch 1, sam2_video_predictor_official.py:689-725), and frame embeddings are
 produced a few frames ahead in one batched encoder call.
 """
+import itertools
 import threading
 from collections import OrderedDict
 from typing import Dict, List, Optional
@@ -186,11 +187,81 @@ class _GraphedHeads:
         return low.clone(), high, ptr.clone(), obj.clone()      # `high` is consumed (memory encoder) before the next replay
 
 
+class _BankRing:
+    """the spatial memory bank of one group of n objects as a device-resident ring in the E3 input layout.
+
+    The reference re-gathers the bank on every frame for every object (sam2_base_official.py:839-884: .to(device), flatten,
+    permute, `torch.cat` over up to 7 frames of [4096, n, 64] features and as many position tensors).  Between consecutive frames
+    the bank changes by ONE frame: the newest tracked frame enters, the oldest leaves.  Attention is invariant to the order of
+    the keys as long as each key keeps its own position encoding, so the slots need not stay in temporal order: the new frame
+    overwrites the slot of the frame that left (one transposing copy of [n,64,64,64] bf16 into [4096, n, 64] fp32) and the
+    position tensor is rebuilt in one pass from constants: the sine encoding (identical for every frame and object) plus the
+    temporal encoding of each slot's CURRENT age (`maskmem_tpos_enc`, :881-883) - the only thing that changes for the frames
+    that stay.  Values are identical to `sam_heads.assemble_memory`; only the slot order (hence the fp32 summation order inside
+    the attention) differs."""
+
+    def __init__(self, w, n, device, capacity=H.NUM_MASKMEM + 1):
+        self.w, self.n, self.device = w, n, device
+        self.mem = torch.empty((capacity, 4096, n, H.MEM_DIM), device=device, dtype=torch.float32)
+        self.pos = torch.empty_like(self.mem)
+        self.frames = []                        # (frame tag, record stamp) held by slot i; conditioning frames are tagged ("c", t)
+        self.pe = None                          # [4096, 1, 64] sine encoding, taken from the first stored frame
+        self._idx = {}                          # tuple of slot ages -> device index tensor (no host-to-device copy per frame)
+
+    def _write(self, slot, rec):
+        self.mem[slot].copy_(rec["maskmem_features"].flatten(2).permute(2, 0, 1))     # bf16 [n,64,4096] -> fp32 [4096,n,64]
+        if self.pe is None:
+            self.pe = rec["maskmem_pos"][:1].flatten(2).permute(2, 0, 1).contiguous()
+
+    def update(self, t, cond_b, non_cond_b):
+        """Bring the ring to the bank of frame t (ref: the selection rule of sam2_base_official.py:829-868: every conditioning
+        frame, then the tracked frames t-6 .. t-1 that exist) and return (memory [L,4096,n,64], memory_pos [L,4096,n,64])."""
+        # a slot is identified by (frame, stamp of the stored record): a frame that was re-tracked or corrected since is new
+        want = {(("c", tt), rec["stamp"]): (0, rec) for tt, rec in cond_b.items()}
+        for t_pos in range(1, H.NUM_MASKMEM):
+            tt = t - (H.NUM_MASKMEM - t_pos)
+            rec = non_cond_b.get(tt)
+            if rec is not None:
+                want[(tt, rec["stamp"])] = (t_pos, rec)
+        if len(want) > self.mem.shape[0]:       # many conditioning frames: grow once
+            extra = len(want) - self.mem.shape[0]
+            self.mem = torch.cat([self.mem, torch.empty((extra,) + tuple(self.mem.shape[1:]), device=self.device)], 0)
+            self.pos = torch.empty_like(self.mem)
+        # slots of frames that left are re-used by the newcomers; the surviving frames keep their slots (steady state: exactly
+        # one frame leaves and one enters)
+        free = [i for i, f in enumerate(self.frames) if f not in want]
+        new = [f for f in want if f not in self.frames]
+        for f in new:
+            if free:
+                slot = free.pop(0)
+                self.frames[slot] = f
+            else:
+                slot = len(self.frames)
+                self.frames.append(f)
+            self._write(slot, want[f][1])
+        if free:                                # the bank shrank (re-prompting): drop the holes, moving the tail down
+            for slot in sorted(free, reverse=True):
+                last = len(self.frames) - 1
+                if slot != last:
+                    self.mem[slot].copy_(self.mem[last])
+                    self.frames[slot] = self.frames[last]
+                self.frames.pop()
+        L = len(self.frames)
+        # memory_pos = sine encoding + temporal encoding of each slot's current age (tpos index NUM_MASKMEM - t_pos - 1)
+        ages = tuple(H.NUM_MASKMEM - want[f][0] - 1 for f in self.frames)
+        idx = self._idx.get(ages)
+        if idx is None:
+            idx = self._idx[ages] = torch.tensor(ages, device=self.device)
+        tpos = self.w["maskmem_tpos_enc"].reshape(H.NUM_MASKMEM, 1, 1, H.MEM_DIM).index_select(0, idx)
+        torch.add(self.pe[None].expand(L, 4096, self.n, H.MEM_DIM), tpos.expand(L, 4096, self.n, H.MEM_DIM), out=self.pos[:L])
+        return self.mem[:L], self.pos[:L]
+
+
 class SAM2VideoPredictor(_Base):
     """Forward video propagation with click / box prompts (BASELINE.json configs 3 and 4)."""
 
     def __init__(self, state_dict, device="cuda", backend="b200", encode_ahead=16, fill_hole_area=0, graph_heads=True,
-                 add_all_frames_to_correct_as_cond=False):
+                 add_all_frames_to_correct_as_cond=False, bank_ring=True):
         """fill_hole_area: as the reference's constructor argument (sam2_video_predictor_official.py:25,889-894; the
         reference's builder sets 8 when its native extension is available, build_sam.py:128-129): holes of at most that
         many pixels in the low-res mask scores are filled before the masks are stored / returned.  0 = off, which is what
@@ -202,6 +273,10 @@ class SAM2VideoPredictor(_Base):
         self.encode_ahead = max(1, int(encode_ahead))
         self.fill_hole_area = int(fill_hole_area)
         self.graph_heads = bool(graph_heads)
+        # bank_ring: keep the spatial memory bank of a group of objects in a device-resident ring in the E3 input layout
+        # (see _BankRing) instead of re-assembling it with stack / cat on every frame
+        self.bank_ring = bool(bank_ring)
+        self._stamps = itertools.count(1)          # identity of stored bank records (see _BankRing.update)
         # ref: sam2_video_predictor_official.py:31-33 - whether a correction click on a tracked frame makes it a conditioning frame
         self.add_all_frames_to_correct_as_cond = bool(add_all_frames_to_correct_as_cond)
         self._heads_graphs = {}            # (object count, host thread) -> _GraphedHeads
@@ -220,7 +295,7 @@ class SAM2VideoPredictor(_Base):
         st = {"images": frames if offload_video_to_cpu else frames.to(self.device), "num_frames": frames.shape[0],
               "video_height": video_height or 1024, "video_width": video_width or 1024,
               "obj_ids": [], "prompts": OrderedDict(), "cond": OrderedDict(), "non_cond": OrderedDict(),
-              "feat_cache": {}, "frames_tracked": {}, "non_cond_b": {}, "cond_b": {}, "pending_non_cond": set()}
+              "feat_cache": {}, "frames_tracked": {}, "non_cond_b": {}, "cond_b": {}, "pending_non_cond": set(), "rings": {}}
         return st
 
     def reset_state(self, st):
@@ -228,6 +303,7 @@ class SAM2VideoPredictor(_Base):
             st[k].clear()
         st["obj_ids"], st["feat_cache"], st["frames_tracked"] = [], {}, {}
         st["pending_non_cond"].clear()
+        st["rings"].clear()
 
     def _prep_frame(self, f, mean, std):
         """one uint8 HWC frame -> normalised [1,3,1024,1024] fp32 (ref: utils/misc.py:96,161-162)"""
@@ -413,6 +489,13 @@ class SAM2VideoPredictor(_Base):
         batched = {} if per_object else {tt: st["non_cond_b"].get(tt, {}).get(key) for tt in hist}
         if not per_object and all(v is not None for v in batched.values()):
             cond_b = {tt: self._stacked_cond(st, tt, key) for tt in cond_keys}
+            if self.bank_ring:
+                ring = st["rings"].get(key)
+                if ring is None:
+                    ring = st["rings"][key] = _BankRing(self.w, len(key), self.device)
+                mem, mpos = ring.update(t, cond_b, batched)
+                ptr, ppos = H.assemble_pointers(self.w, t, cond_b, batched, st["num_frames"], cache=self._tpos_cache)
+                return [mem, mpos, ptr, ppos]
             return list(H.assemble_memory(self.w, t, cond_b, batched, st["num_frames"], cache=self._tpos_cache))
         per = []
         for o in g_objs:
@@ -477,7 +560,8 @@ class SAM2VideoPredictor(_Base):
         results, o0 = {}, 0
         for _, _, g_objs in groups:
             sl = slice(o0, o0 + len(g_objs))
-            st["non_cond_b"].setdefault(t, {})[tuple(g_objs)] = {"maskmem_features": mf[sl], "maskmem_pos": mp[sl], "obj_ptr": ptr[sl]}
+            st["non_cond_b"].setdefault(t, {})[tuple(g_objs)] = {"maskmem_features": mf[sl], "maskmem_pos": mp[sl], "obj_ptr": ptr[sl],
+                                                                 "stamp": next(self._stamps)}
             o0 += len(g_objs)
         for i, o in enumerate(order):
             results[o] = {"pred_masks": low[i:i + 1], "obj_ptr": ptr[i:i + 1], "object_score_logits": obj[i:i + 1],
@@ -490,4 +574,5 @@ class SAM2VideoPredictor(_Base):
         if key not in c:
             per = st["cond"][t]
             c[key] = {k: torch.cat([per[o][k] for o in key], 0) for k in ("maskmem_features", "maskmem_pos", "obj_ptr")}
+            c[key]["stamp"] = next(self._stamps)
         return c[key]

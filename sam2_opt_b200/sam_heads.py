@@ -215,21 +215,10 @@ def _ptr_tpos_table(w: W, num_frames: int, max_ptrs: int, cache: dict):
     return cache[key]
 
 
-def assemble_memory(w: W, frame_idx: int, cond_outputs: dict, non_cond_outputs: dict, num_frames: int, cache: dict = None):
-    """Memory bank + object-pointer tokens for `frame_idx` (forward tracking, stride 1) of one object or of n objects that
-    share the same conditioning / tracked frames.  ref: modeling/sam2_base_official.py:825-950.  Stored outputs hold
-    'maskmem_features' [n,64,64,64] (bf16, as the reference stores them, sam2_video_predictor_official.py:887),
-    'maskmem_pos' [n,64,64,64], 'obj_ptr' [n,256].
-    -> memory [L,4096,n,64], memory_pos [L,4096,n,64], ptr tokens [P,n,64], ptr pos [P,n,64]"""
-    t_pos_prev = [(0, o) for o in cond_outputs.values()]
-    for t_pos in range(1, NUM_MASKMEM):
-        t_pos_prev.append((t_pos, non_cond_outputs.get(frame_idx - (NUM_MASKMEM - t_pos))))
-    mem, mpos = [], []
-    for t_pos, prev in t_pos_prev:
-        if prev is None:
-            continue
-        mem.append(prev["maskmem_features"].float().flatten(2).permute(2, 0, 1))
-        mpos.append(prev["maskmem_pos"].flatten(2).permute(2, 0, 1) + w["maskmem_tpos_enc"][NUM_MASKMEM - t_pos - 1])
+def assemble_pointers(w: W, frame_idx: int, cond_outputs: dict, non_cond_outputs: dict, num_frames: int, cache: dict = None):
+    """Object-pointer tokens of the memory bank (ref: modeling/sam2_base_official.py:886-950): the pointers of the conditioning
+    frames up to `frame_idx` and of up to 15 previous tracked frames, each split into 4 tokens of 64, with the projected sine
+    encoding of its temporal distance -> (tokens [P,n,64], positions [P,n,64])."""
     max_ptrs = min(num_frames, 16)
     pos_ptrs = [(frame_idx - t, o["obj_ptr"]) for t, o in cond_outputs.items() if t <= frame_idx]
     for t_diff in range(1, max_ptrs):
@@ -251,4 +240,23 @@ def assemble_memory(w: W, frame_idx: int, cond_outputs: dict, non_cond_outputs: 
     opos = opos.unsqueeze(1).expand(-1, n, MEM_DIM)
     ptrs = ptrs.reshape(-1, n, D_MODEL // MEM_DIM, MEM_DIM).permute(0, 2, 1, 3).flatten(0, 1)
     opos = opos.repeat_interleave(D_MODEL // MEM_DIM, dim=0)
+    return ptrs, opos
+
+
+def assemble_memory(w: W, frame_idx: int, cond_outputs: dict, non_cond_outputs: dict, num_frames: int, cache: dict = None):
+    """Memory bank + object-pointer tokens for `frame_idx` (forward tracking, stride 1) of one object or of n objects that
+    share the same conditioning / tracked frames.  ref: modeling/sam2_base_official.py:825-950.  Stored outputs hold
+    'maskmem_features' [n,64,64,64] (bf16, as the reference stores them, sam2_video_predictor_official.py:887),
+    'maskmem_pos' [n,64,64,64], 'obj_ptr' [n,256].
+    -> memory [L,4096,n,64], memory_pos [L,4096,n,64], ptr tokens [P,n,64], ptr pos [P,n,64]"""
+    t_pos_prev = [(0, o) for o in cond_outputs.values()]
+    for t_pos in range(1, NUM_MASKMEM):
+        t_pos_prev.append((t_pos, non_cond_outputs.get(frame_idx - (NUM_MASKMEM - t_pos))))
+    mem, mpos = [], []
+    for t_pos, prev in t_pos_prev:
+        if prev is None:
+            continue
+        mem.append(prev["maskmem_features"].float().flatten(2).permute(2, 0, 1))
+        mpos.append(prev["maskmem_pos"].flatten(2).permute(2, 0, 1) + w["maskmem_tpos_enc"][NUM_MASKMEM - t_pos - 1])
+    ptrs, opos = assemble_pointers(w, frame_idx, cond_outputs, non_cond_outputs, num_frames, cache)
     return torch.stack(mem, 0), torch.stack(mpos, 0), ptrs, opos

@@ -123,8 +123,8 @@ def test_video_batched_bank_and_graphed_heads_equal_the_plain_path(weights):
     frames = synth_video(T, seed=4)
     pts = {1: [[512, 512]], 2: [[300, 700]], 3: [[700, 300]]}
 
-    def run(plain):
-        vp = SAM2VideoPredictor(weights, graph_heads=not plain)
+    def run(plain, ring=False):
+        vp = SAM2VideoPredictor(weights, graph_heads=not plain, bank_ring=ring)
         st = vp.init_state(frames)
         for o, p in pts.items():
             vp.add_new_points_or_box(st, 0, o, points=np.array(p, dtype=np.float32), labels=np.array([1], np.int32))
@@ -142,6 +142,15 @@ def test_video_batched_bank_and_graphed_heads_equal_the_plain_path(weights):
     vp_b, st_b, b = run(plain=True)
     for t in range(T):
         assert torch.equal(a[t], b[t]), f"frame {t}: batched/graphed path differs from the plain path"
+    # the device-resident bank ring (default) holds the same values in a rotating slot order: the attention sums the keys in a
+    # different order, so the logits agree to fp32 / bf16 round-off instead of bit for bit
+    vp_r, st_r, r = run(plain=False, ring=True)
+    assert st_r["rings"] and all(len(ring.frames) == min(T - 1, 7) for ring in st_r["rings"].values())
+    for t in range(T):
+        for i in range(3):
+            v = iou_bits((r[t][i, 0] > 0).cpu().numpy(), (a[t][i, 0] > 0).cpu().numpy())
+            assert v >= 0.999, f"frame {t} object {i + 1}: IoU {v:.4f} between the ring and the re-assembled bank"
+    vp_r.release()
     assert len(st_a["non_cond_b"]) == T - 1 and all(tuple(k) == (1, 2, 3) for d in st_a["non_cond_b"].values() for k in d)
     vp_a.release(); vp_b.release()
     # mixed history (7 frames, so that two conditioning frames + recent frames stay within the 7-slot bank of the E3

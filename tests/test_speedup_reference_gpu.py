@@ -118,3 +118,45 @@ def test_reference_video_predictor_on_the_real_engine(weights):
         # (the reference tracks every object separately with batch 1)
         assert torch.equal(again[t][1], ref[t][1])
     engine.release()
+
+
+def test_reference_automatic_mask_generator_on_the_real_engine(weights):
+    """SURVEY section 8 f-4 (other consumers of the same kernels): the reference's SAM2AutomaticMaskGenerator
+    (automatic_mask_generator.py:170-294) owns a SAM2ImagePredictor, so `generator.predictor.speedup("b200")` is all it takes.
+    A 4 x 4 grid of point prompts with every filter that depends on the (random-init) quality heads opened up, torch path vs
+    engine on the same device: the same prompts must survive and every mask must match (IoU >= 0.99)."""
+    import ref_gpu
+    from oracle.synth import synth_image_u8
+    from sam2_opt_b200 import speedup as S
+    torch.set_grad_enabled(False)
+    m = ref_gpu.build("base", weights)
+    from sam2.automatic_mask_generator import SAM2AutomaticMaskGenerator
+    from sam2.sam2_image_predictor import SAM2ImagePredictor
+    S.install(SAM2ImagePredictor)
+    gen = SAM2AutomaticMaskGenerator(m, points_per_side=4, points_per_batch=16, pred_iou_thresh=0.0, stability_score_thresh=0.0,
+                                     box_nms_thresh=1.0, crop_n_layers=0, min_mask_region_area=0)
+    img = synth_image_u8(0)
+    ref = gen.generate(img)
+    gen.predictor.speedup("b200")
+    got = gen.generate(img)
+    gen.predictor.speedup("torch")
+    assert len(ref) >= 16 and len(got) == len(ref), (len(ref), len(got))
+
+    def by_prompt(records):
+        out = {}
+        for r in records:
+            out.setdefault(tuple(np.round(np.asarray(r["point_coords"][0]), 1)), []).append(r)
+        return out
+
+    a, b = by_prompt(ref), by_prompt(got)
+    assert sorted(a) == sorted(b)
+    worst = 1.0
+    for k in a:
+        assert len(a[k]) == len(b[k])
+        # the masks of one prompt come out ordered by the quality heads, whose scores are near-tied with random weights:
+        # match every reference mask with its best counterpart
+        for r in a[k]:
+            worst = min(worst, max(ref_gpu.iou(r["segmentation"], g["segmentation"]) for g in b[k]))
+    print(f"reference SAM2AutomaticMaskGenerator + b200 engine: {len(ref)} masks from 16 prompts, worst matched IoU {worst:.4f}")
+    assert worst >= 0.99
+    gen.predictor._sam2b_engine.release()
