@@ -135,6 +135,36 @@ SAM2B_DEVINL void umma_bf16_ts(uint32_t tmem_d, uint32_t tmem_a, uint64_t desc_b
       : "memory");
 }
 
+// Warp-wide forms: called by ALL 32 lanes of the issuing warp with warp-uniform operands; one elected lane issues.  Keeping the
+// issue loop convergent lets the compiler hold descriptors and ring counters in uniform registers - inside an `if (lane == 0)`
+// region every tcgen05.mma pays four vector-to-uniform register moves and an election loop (~13 dependent instructions), which
+// is more than the 50 - 72 clocks a narrow instruction occupies the tensor pipe.
+SAM2B_DEVINL void umma_bf16_w(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p, e;\n\t"
+      "elect.sync _|e, 0xffffffff;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "@e tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+      ::"r"(tmem_d), "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+SAM2B_DEVINL void umma_bf16_ts_w(uint32_t tmem_d, uint32_t tmem_a, uint64_t desc_b, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p, e;\n\t"
+      "elect.sync _|e, 0xffffffff;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "@e tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n\t}"
+      ::"r"(tmem_d), "r"(tmem_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+SAM2B_DEVINL void umma_commit_w(uint64_t* bar) {
+  asm volatile(
+      "{\n\t.reg .pred e;\n\t"
+      "elect.sync _|e, 0xffffffff;\n\t"
+      "@e tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];\n\t}"
+      ::"r"(smem_u32(bar)) : "memory");
+}
+
 // ------------------------------------------------------------------------------------------
 // CTA pairs (cluster of 2, tcgen05 cta_group::2)
 // ------------------------------------------------------------------------------------------
@@ -358,6 +388,24 @@ SAM2B_DEVINL uint64_t f2_add(uint64_t a, uint64_t b) {
   uint64_t r;
   asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
   return r;
+}
+
+// gelu_fast_bf16 for two values with the polynomial on packed fp32 pairs (FFMA2): per pair 6 FMNMX + 5 FFMA2 + 2 MUFU.EX2
+// instead of 4 FMNMX + 12 FFMA + 2 MUFU.EX2 - the GELU epilogues are bound by instruction issue, not by a pipe.
+// With n = -|x| = min(x, -x) and u = max(n, -5) = -t the exponent is p(t) as a polynomial in u (odd coefficients negated) and
+// GELU(x) = max(x, 0) + n * 2^p.  Bit-identical to gelu_fast_bf16 (same operations on the same values, only paired).
+SAM2B_DEVINL void gelu_fast_bf16x2(float x0, float x1, float& y0, float& y1) {
+  const float n0 = fminf(x0, -x0), n1 = fminf(x1, -x1);
+  const uint64_t n2 = f2_pack(n0, n1);
+  const uint64_t u2 = f2_pack(fmaxf(n0, -5.0f), fmaxf(n1, -5.0f));
+  uint64_t p2 = f2_fma(f2_pack(0.00386557744f, 0.00386557744f), u2, f2_pack(0.0440761234f, 0.0440761234f));
+  p2 = f2_fma(p2, u2, f2_pack(-0.468019552f, -0.468019552f));
+  p2 = f2_fma(p2, u2, f2_pack(1.14736964f, 1.14736964f));
+  p2 = f2_fma(p2, u2, f2_pack(-1.00048006f, -1.00048006f));
+  float p0, p1;
+  f2_unpack(p2, p0, p1);
+  const uint64_t h2 = f2_pack(ex2_approx(p0), ex2_approx(p1));
+  f2_unpack(f2_fma(n2, h2, f2_pack(fmaxf(x0, 0.0f), fmaxf(x1, 0.0f))), y0, y1);
 }
 
 SAM2B_DEVINL uint32_t pack_bf16x2(float lo, float hi) {

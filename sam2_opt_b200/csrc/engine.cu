@@ -404,7 +404,7 @@ static int image_encode_mb(sam2b_engine* e, const float* img, int n, int normali
         // stages 1 and 2: fc1 -> GELU -> fc2 in one kernel, the hidden layer stays in tensor memory
         TRY(mlp_fused(XB2, ST2, parts2, 1e-6f, W16(e, d + "fc1.weight"), W32(e, d + "fc1.bias"), W16(e, b + "mlp.layers.1.weight"),
                       W32(e, b + "mlp.layers.1.bias"), X, xb_out, ST1, Tq, c.dim_out, st));
-        parts1 = 2;
+        parts1 = 1;              // the read-out warp that owns a row sums the whole row
       } else {
       TRY(ln_linear(XB2, c.dim_out, d + "fc1.", 4 * c.dim_out, ST2, parts2, ACT_GELU, nullptr, HID, Tq));
       {

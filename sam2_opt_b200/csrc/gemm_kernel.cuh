@@ -340,9 +340,11 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid
           }
           if (act == ACT_GELU) {
             if (MODE == MODE_BF16_BIAS_GELU) {
+              // packed pairs (FFMA2): the polynomial of two columns per instruction - this epilogue is bound by instruction issue
 #pragma unroll
               for (int j = 0; j < 8; ++j) {
-                v[j].x = gelu_fast_bf16(v[j].x); v[j].y = gelu_fast_bf16(v[j].y); v[j].z = gelu_fast_bf16(v[j].z); v[j].w = gelu_fast_bf16(v[j].w);
+                gelu_fast_bf16x2(v[j].x, v[j].y, v[j].x, v[j].y);
+                gelu_fast_bf16x2(v[j].z, v[j].w, v[j].z, v[j].w);
               }
             } else {
 #pragma unroll

@@ -2,18 +2,28 @@
 // Reference: MLP.forward (sam2/modeling/sam2_utils.py:131-136) inside MultiScaleBlock.forward (backbones/hieradet.py:160-166),
 // with norm2 folded into fc1 as everywhere else in the trunk (weights.py: row-centred W diag(gamma), b + W beta).
 //
-// Why: in stages 1 and 2 (K = 144 / 288) the two MLP GEMMs are not tensor bound - fc1's GELU epilogue is issue bound and
-// the 4C-wide hidden tensor is written to and read back from HBM (1.2 GB / 0.6 GB per block per 16 images).  Here the
-// hidden activations never leave the SM:
+// Why: in stages 1 and 2 (K = 144 / 288) the two MLP GEMMs are HBM bound: the 4C-wide hidden tensor is written by fc1 and read
+// back by fc2 (2.4 GB / 1.2 GB per block per 32 images, more than everything else in the block together).  Here the hidden
+// activations never leave the SM:
 //   for every 96-wide chunk h of the hidden layer
 //     S_b[128 x 96] = A[128 x C] W1[h]^T                  tcgen05.mma, A tile resident in shared memory, W1 streamed by TMA;
 //                                                         b = h & 1: two S buffers, chunk h + 1 is computed while
-//     P             = bf16(GELU(rstd * S_b + b1[h]))       the epilogue warps work on chunk h; P is written back over S_b's
-//                                                         columns as packed pairs
+//     P             = bf16(GELU(rstd * S_b + b1[h]))       the GELU warps work on chunk h; P is written back over S_b's
+//                                                         columns as packed pairs, 32 columns at a time
 //     O[128 x C]   += P W2[:, h]^T                         tcgen05.mma with the A operand (P) read from TENSOR MEMORY
 //   x_out = O + b2 + x; bf16 copy and per-row (sum, sum of squares) for the next block's folded LayerNorm
-// TMEM: S 2 x 96 columns + O C columns (<= 480).  Warps: 0 and 3 TMA producers (A + W1 / W2), 1 MMA issuer, 2 TMEM allocation, 4-11 epilogue:
-// lane quarter = warp & 3; group (warp - 4) >> 2 takes the even / odd hidden chunks and one half of O's columns.
+// Per 128-row tile the kernel must move 128 x 12 C bytes through HBM (x in / out in fp32, the bf16 copies): 9.5k clocks of the
+// SM's share of the bus at C = 144, against 5.3k clocks of MMA issue and 5.5k of GELU arithmetic - so every role has its own
+// warps and nothing but tensor memory and mbarriers couples them:
+//   warp 0      TMA: A tile + W1 ring          warp 3      TMA: W2 ring
+//   warp 1      MMA issuer                     warp 2      TMEM allocation
+//   warps 4-11  GELU: group g = (warp - 4) / 4 takes the hidden chunks of parity g (lane quarter = warp & 3)
+//   warps 12-15 read-out: O -> + b2 + residual -> x (fp32, TMA store), bf16 copy, row statistics.  The residual rows arrive by
+//               TMA in [32 rows x 32 columns] boxes requested a whole tile ahead (a thread owns one ROW of tensor memory: plain
+//               loads of its row would be 64 B pieces with a DRAM round trip each, and 8 warps of them jam the load / store
+//               unit for the GELU warps' bias loads - measured, 37 % of all stall samples in the first version of this kernel)
+// TMEM: S 2 x 96 columns + O: two buffers of C columns at C = 144 (the read-out of tile t overlaps fc2 of tile t + 1), one at
+// C = 288 (480 columns either way).
 #include <cuda.h>
 #include <cuda_runtime.h>
 
@@ -28,11 +38,12 @@ namespace sam2b {
 namespace fm {
 static constexpr int BM = 128;
 static constexpr int BH = 96;                        // hidden chunk
-static constexpr int THREADS = 384;
+static constexpr int THREADS = 512;
 static constexpr int A_KB_BYTES = BM * 128;          // [128 rows][64 k] bf16, 128B swizzle
 static constexpr int W1_BYTES = BH * 128;            // [96 hidden][64 k]
+static constexpr int BOX_BYTES = 32 * 128;           // [32 rows][32 fp32 columns], 128B swizzle
 static constexpr int COL_S = 0;                      // S buffer b at COL_S + 96 b; P over its first 48 columns
-static constexpr int COL_O = 192;
+static constexpr int COL_O = 192;                    // O buffer j at COL_O + j C
 template <int C>
 struct Cfg {
   static constexpr int KB = (C + 63) / 64;           // k-blocks of the A tile (the last one partly zero-filled by TMA)
@@ -40,15 +51,21 @@ struct Cfg {
   static constexpr int NSPLIT = C / 144;             // fc2 instructions per k-step (N = 144 each; tcgen05.mma N <= 256)
   static constexpr int W2_BYTES = C * 128;           // [C rows][64 hidden]
   static constexpr int NB2 = 4 * C / 64;             // 64-wide W2 blocks per tile (a block may straddle two hidden chunks)
-  static constexpr int NS1 = C == 144 ? 4 : 3;       // W1 ring depth
-  static constexpr int NS2 = 3;                      // W2 ring depth
+  static constexpr int NS1 = 3;                      // W1 ring depth
+  static constexpr int NS2 = C == 144 ? 3 : 2;       // W2 ring depth
+  static constexpr int NOB = C == 144 ? 2 : 1;       // O accumulators in tensor memory
+  static constexpr int NCH = (C + 31) / 32;          // 32-column read-out chunks of a row (the last one may be half full)
+  static constexpr int NBOX = C == 144 ? NCH : 2;    // residual boxes per read-out warp: the whole row / a ring of two
   static constexpr int OFF_A = 0;
   static constexpr int OFF_W1 = OFF_A + KB * A_KB_BYTES;
   static constexpr int OFF_W2 = OFF_W1 + NS1 * W1_BYTES;
-  static constexpr int OFF_BAR = OFF_W2 + NS2 * W2_BYTES;
-  static constexpr int SMEM = OFF_BAR + 256 + 1024;
+  static constexpr int OFF_BOX = OFF_W2 + NS2 * W2_BYTES;
+  static constexpr int OFF_BAR = OFF_BOX + 4 * NBOX * BOX_BYTES;
+  static constexpr int SMEM = OFF_BAR + 512 + 1024;
   static_assert(4 * C % BH == 0 && C % 144 == 0 && NH % 2 == 0, "C must be 144 or 288");
-  static_assert(COL_O + C <= 512, "TMEM columns");
+  static_assert(COL_O + NOB * C <= 512, "TMEM columns");
+  static_assert(OFF_BOX % 1024 == 0, "swizzled boxes need 1024 B alignment");
+  static_assert(SMEM <= 227 * 1024, "shared memory");
 };
 }  // namespace fm
 
@@ -58,16 +75,15 @@ struct FusedMlpParams {
   float eps, inv_c;
   const float* b1;           // [4C]  (b + W beta)
   const float* b2;           // [C]
-  float* x;                  // [M][C] fp32 residual stream, updated in place
   bf16* xb_out;              // [M][C] bf16 copy of the new stream
-  float* stats_out;          // [M][2][2]
+  float* stats_out;          // [M][1][2]
   int M, num_tiles;
 };
 
 template <int C>
 __global__ void __launch_bounds__(fm::THREADS, 1)
 mlp_fused_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_w1,
-                 const __grid_constant__ CUtensorMap map_w2, const FusedMlpParams p) {
+                 const __grid_constant__ CUtensorMap map_w2, const __grid_constant__ CUtensorMap map_x, const FusedMlpParams p) {
   using namespace fm;
   using K = Cfg<C>;
   extern __shared__ uint8_t smem_raw[];
@@ -81,22 +97,25 @@ mlp_fused_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
   uint64_t* w2_empty = w2_full + K::NS2;
   uint64_t* s_full = w2_empty + K::NS2;         // [2]
   uint64_t* p_full = s_full + 2;                // [2]
-  uint64_t* o_full = p_full + 2;
-  uint64_t* o_free = o_full + 1;
-  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(o_free + 1);
+  uint64_t* o_full = p_full + 2;                // [NOB]
+  uint64_t* o_free = o_full + K::NOB;           // [NOB]
+  uint64_t* box_full = o_free + K::NOB;         // [4 read-out warps][NBOX]
+  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(box_full + 4 * K::NBOX);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&map_a);
     tma_prefetch_desc(&map_w1);
     tma_prefetch_desc(&map_w2);
+    tma_prefetch_desc(&map_x);
   }
   if (warp == 1 && lane == 0) {
     mbar_init(a_full, 1); mbar_init(a_empty, 1);
     for (int i = 0; i < K::NS1; ++i) { mbar_init(&w1_full[i], 1); mbar_init(&w1_empty[i], 1); }
     for (int i = 0; i < K::NS2; ++i) { mbar_init(&w2_full[i], 1); mbar_init(&w2_empty[i], 1); }
     for (int i = 0; i < 2; ++i) { mbar_init(&s_full[i], 1); mbar_init(&p_full[i], 4); }
-    mbar_init(o_full, 1); mbar_init(o_free, 8);
+    for (int i = 0; i < K::NOB; ++i) { mbar_init(&o_full[i], 1); mbar_init(&o_free[i], 4); }
+    for (int i = 0; i < 4 * K::NBOX; ++i) mbar_init(&box_full[i], 1);
     fence_barrier_init();
   }
   if (warp == 2) { tmem_alloc(tmem_ptr, 512); tmem_relinquish(); }
@@ -140,157 +159,215 @@ mlp_fused_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
       }
     }
   } else if (warp == 1) {
-    // ===================== MMA issuer (one thread) =====================
-    if (lane == 0) {
+    // ===================== MMA issuer (whole warp, one elected lane issues) =====================
+    // The issuing thread is a resource of its own: every instruction it spends on index arithmetic delays the next tcgen05.mma
+    // (the first version of this loop needed ~400 clocks per MMA against the 50 - 72 the tensor pipe takes).  Ring positions are
+    // therefore carried as (stage, phase) counters, descriptors are built once per shared-memory block and advanced by constants,
+    // two hidden chunks are issued per iteration so that every W2 k-step index is a compile-time constant, and the loop is run by
+    // the whole warp with warp-uniform values (common.cuh umma_*_w), so that the descriptors live in uniform registers.
+    {
       constexpr uint32_t idesc_fc1 = make_idesc_ex(128, BH, 0);
       constexpr uint32_t idesc_fc2 = make_idesc_ex(128, 144, 0);
       const uint32_t sbase = smem_u32(smem);
-      int i1 = 0, i2 = 0, nt = 0;
-      uint32_t n_s[2] = {0, 0};         // fc1 products issued on S buffer b
-      uint32_t n_p[2] = {0, 0};         // hidden chunks handed over through buffer b (phase of p_full[b])
-      auto issue_fc1 = [&](int h) {
-        const int b = h & 1;
-        for (int kb = 0; kb < K::KB; ++kb, ++i1) {
-          const int s = i1 % K::NS1;
-          mbar_wait(&w1_full[s], (i1 / K::NS1) & 1);
-          tc_fence_after();
-          const uint32_t a = sbase + K::OFF_A + kb * A_KB_BYTES, w = sbase + K::OFF_W1 + s * W1_BYTES;
-          const int ksteps = (C - kb * 64) >= 64 ? 4 : (C - kb * 64) / 16;
-          for (int k = 0; k < ksteps; ++k)
-            umma_bf16(tmem_base + COL_S + BH * b, make_smem_desc(a + k * 32, 16, 1024, 2), make_smem_desc(w + k * 32, 16, 1024, 2),
-                      idesc_fc1, (kb | k) != 0);
-          umma_commit(&w1_empty[s]);
-        }
-        umma_commit(&s_full[b]);
-        ++n_s[b];
-      };
-      for (int t = blockIdx.x; t < p.num_tiles; t += gridDim.x, ++nt) {
-        mbar_wait(a_full, nt & 1);
-        tc_fence_after();
-        // S_b is reused by chunk h + 2: in order behind fc2 of chunk h, which read P(h) out of it after the epilogue warps had
-        // read S(h) - no extra barrier needed
-        issue_fc1(0);
-        for (int h = 0; h < K::NH; ++h) {
-          if (h + 1 < K::NH) issue_fc1(h + 1);                 // overlaps the GELU pass over chunk h
-          if (h + 1 >= K::NH - 1 && h + 1 <= K::NH - 1) umma_commit(a_empty);   // last fc1 of the tile has been issued
-          const int b = h & 1;
-          mbar_wait(&p_full[b], n_p[b] & 1);
-          ++n_p[b];
-          if (h == 0) mbar_wait(o_free, (nt & 1) ^ 1);          // the previous tile's O has been read out
-          tc_fence_after();
-#pragma unroll 1
-          for (int k = 0; k < BH / 16; ++k) {
-            const int g = h * (BH / 16) + k;                    // k-step of this tile's fc2: 64-wide W2 block g / 4, step g % 4
-            const int st = g & 3;
-            const int s = (i2 + (g >> 2)) % K::NS2;
-            if (st == 0 || k == 0) {
-              if (st == 0) {                                      // first use of the block
-                mbar_wait(&w2_full[s], ((i2 + (g >> 2)) / K::NS2) & 1);
-                tc_fence_after();
-              }
-            }
-            const uint32_t w = sbase + K::OFF_W2 + s * K::W2_BYTES;
-            const uint32_t pa = tmem_base + COL_S + BH * b + k * 8;            // 16 hidden units = 8 columns of bf16 pairs
+      int s1 = 0, s2 = 0, nt = 0;
+      uint32_t ph1 = 0, ph2 = 0;        // phases of the W1 / W2 rings
+      uint32_t php = 0;                 // phase of p_full[0] and p_full[1] (both advance once per pair of chunks)
+      auto issue_fc1 = [&](int b) {     // one hidden chunk: S_b = A W1[h]^T over the KB k-blocks of the resident A tile
+        const uint32_t d = tmem_base + COL_S + BH * b;
 #pragma unroll
-            for (int j = 0; j < K::NSPLIT; ++j)
-              umma_bf16_ts(tmem_base + COL_O + j * 144, pa, make_smem_desc(w + j * 144 * 128 + st * 32, 16, 1024, 2), idesc_fc2,
-                           (h | k) != 0);
-            if (st == 3) umma_commit(&w2_empty[s]);
+        for (int kb = 0; kb < K::KB; ++kb) {
+          mbar_wait(&w1_full[s1], ph1);
+          tc_fence_after();
+          const uint64_t da = make_smem_desc_sw128(sbase + K::OFF_A + kb * A_KB_BYTES);
+          const uint64_t db = make_smem_desc_sw128(sbase + K::OFF_W1 + s1 * W1_BYTES);
+          constexpr int kFull = C / 64;
+          const int ksteps = kb < kFull ? 4 : (C - kFull * 64) / 16;
+#pragma unroll
+          for (int k = 0; k < 4; ++k)
+            if (k < ksteps) umma_bf16_w(d, da + 2 * k, db + 2 * k, idesc_fc1, (kb | k) != 0);
+          umma_commit_w(&w1_empty[s1]);
+          if (++s1 == K::NS1) { s1 = 0; ph1 ^= 1; }
+        }
+        umma_commit_w(&s_full[b]);
+      };
+      // k-steps [k0, k1) of a hidden chunk whose first k-step sits at position st0 of the current 64-wide W2 block
+      auto issue_fc2 = [&](uint32_t o_col, int b, int st0, bool first_chunk) {
+#pragma unroll
+        for (int k = 0; k < BH / 16; ++k) {
+          const int st = (st0 + k) & 3;
+          if (st == 0) {                                        // first use of a W2 block
+            mbar_wait(&w2_full[s2], ph2);
+            tc_fence_after();
+          }
+          const uint32_t pa = tmem_base + COL_S + BH * b + k * 8;             // 16 hidden units = 8 columns of bf16 pairs
+          const uint64_t dw = make_smem_desc_sw128(sbase + K::OFF_W2 + s2 * K::W2_BYTES) + 2 * st;
+#pragma unroll
+          for (int j = 0; j < K::NSPLIT; ++j)
+            umma_bf16_ts_w(o_col + j * 144, pa, dw + (uint64_t)(j * 144 * 128 / 16), idesc_fc2, !(first_chunk && k == 0));
+          if (st == 3) {
+            umma_commit_w(&w2_empty[s2]);
+            if (++s2 == K::NS2) { s2 = 0; ph2 ^= 1; }
           }
         }
-        i2 += K::NB2;
-        umma_commit(o_full);
+      };
+      for (int t = blockIdx.x; t < p.num_tiles; t += gridDim.x, ++nt) {
+        const int ob = nt % K::NOB;
+        const uint32_t o_col = tmem_base + COL_O + ob * C;
+        mbar_wait(a_full, nt & 1);
+        tc_fence_after();
+        // S_b is reused by chunk h + 2: in order behind fc2 of chunk h, which read P(h) out of it after the GELU warps had
+        // read S(h) - no extra barrier needed
+        issue_fc1(0);
+#pragma unroll 1
+        for (int hp = 0; hp < K::NH / 2; ++hp) {
+          // ---- even chunk h = 2 hp (buffer 0): its 6 k-steps start a W2 block (position 0) ----
+          issue_fc1(1);                                          // chunk h + 1 overlaps the GELU pass over chunk h
+          if (hp + 1 == K::NH / 2) umma_commit_w(a_empty);         // the last fc1 of the tile has been issued: A may be refilled
+          mbar_wait(&p_full[0], php);
+          if (hp == 0) mbar_wait(&o_free[ob], ((nt / K::NOB) & 1) ^ 1);      // this accumulator's previous tile has been read out
+          tc_fence_after();
+          issue_fc2(o_col, 0, 0, hp == 0);
+          // ---- odd chunk h + 1 (buffer 1): starts in the middle of a W2 block (position 2) ----
+          if (hp + 1 < K::NH / 2) issue_fc1(0);
+          mbar_wait(&p_full[1], php);
+          tc_fence_after();
+          issue_fc2(o_col, 1, 2, false);
+          php ^= 1;
+        }
+        umma_commit_w(&o_full[ob]);
       }
     }
-  } else if (warp >= 4) {
-    // ===================== epilogue warps =====================
-    const int q = warp & 3, half = (warp - 4) >> 2;          // half: hidden chunks of this parity, and this half of O's columns
+  } else if (warp >= 4 && warp < 12) {
+    // ===================== GELU warps =====================
+    const int q = warp & 3, grp = (warp - 4) >> 2;           // grp: hidden chunks of this parity
     const uint32_t lane_sel = (uint32_t)(q * 32) << 16;
-    uint32_t n_s = 0;                                         // chunks this group has taken (phase of s_full[half])
-    int nt = 0;
-    for (int t = blockIdx.x; t < p.num_tiles; t += gridDim.x, ++nt) {
+    const uint32_t ts = tmem_base + COL_S + BH * grp + lane_sel;
+    uint32_t n_s = 0;                                         // chunks this group has taken (phase of s_full[grp])
+    for (int t = blockIdx.x; t < p.num_tiles; t += gridDim.x) {
       const long row = (long)t * BM + q * 32 + lane;
-      const bool live = row < p.M;
       float rstd = 1.f;
-      if (live) {
+      if (row < p.M) {
         const float2* st = reinterpret_cast<const float2*>(p.stats_in) + row * p.parts_in;
         float s1 = 0.f, s2 = 0.f;
         for (int k = 0; k < p.parts_in; ++k) { const float2 v = __ldg(st + k); s1 += v.x; s2 += v.y; }
         const float mu = s1 * p.inv_c;
         rstd = rsqrtf(fmaxf(fmaf(s2, p.inv_c, -mu * mu), 0.f) + p.eps);
       }
-      const uint32_t ts = tmem_base + COL_S + BH * half + lane_sel;
-      for (int h = half; h < K::NH; h += 2, ++n_s) {
-        mbar_wait(&s_full[half], n_s & 1);
+      for (int h = grp; h < K::NH; h += 2, ++n_s) {
+        mbar_wait(&s_full[grp], n_s & 1);
         tc_fence_after();
-        uint32_t pk[64];                                  // this row's 96 hidden units of the chunk as 48 bf16 pairs (+ slack)
-#pragma unroll
+        // 32 columns at a time: P (16 columns of bf16 pairs) goes back over columns of S this warp has already read
+#pragma unroll 1
         for (int c = 0; c < 3; ++c) {
-          uint32_t r[32];
+          uint32_t r[32], pk[32];
           tmem_ld_x32(ts + c * 32, r);
-          tmem_ld_wait();
           const float4* bsrc = reinterpret_cast<const float4*>(p.b1 + h * BH + c * 32);
+          float4 bv[8];
+#pragma unroll
+          for (int j = 0; j < 8; ++j) bv[j] = __ldg(bsrc + j);
+          tmem_ld_wait();
 #pragma unroll
           for (int j = 0; j < 8; ++j) {
-            const float4 b = __ldg(bsrc + j);
-            const float v0 = gelu_fast_bf16(fmaf(__uint_as_float(r[4 * j]), rstd, b.x));
-            const float v1 = gelu_fast_bf16(fmaf(__uint_as_float(r[4 * j + 1]), rstd, b.y));
-            const float v2 = gelu_fast_bf16(fmaf(__uint_as_float(r[4 * j + 2]), rstd, b.z));
-            const float v3 = gelu_fast_bf16(fmaf(__uint_as_float(r[4 * j + 3]), rstd, b.w));
-            pk[c * 16 + 2 * j] = pack_bf16x2(v0, v1);
-            pk[c * 16 + 2 * j + 1] = pack_bf16x2(v2, v3);
+            float v0, v1, v2, v3;
+            gelu_fast_bf16x2(fmaf(__uint_as_float(r[4 * j]), rstd, bv[j].x), fmaf(__uint_as_float(r[4 * j + 1]), rstd, bv[j].y), v0, v1);
+            gelu_fast_bf16x2(fmaf(__uint_as_float(r[4 * j + 2]), rstd, bv[j].z), fmaf(__uint_as_float(r[4 * j + 3]), rstd, bv[j].w), v2, v3);
+            pk[2 * j] = pack_bf16x2(v0, v1);
+            pk[2 * j + 1] = pack_bf16x2(v2, v3);
           }
+          tmem_st_x16(ts + c * 16, pk);
         }
-        // P over the first 48 columns of the buffer this warp has just read (same lanes, same warp: no cross-warp hazard)
-        tmem_st_x32(ts, *reinterpret_cast<uint32_t(*)[32]>(&pk[0]));
-        tmem_st_x16(ts + 32, *reinterpret_cast<uint32_t(*)[32]>(&pk[32]));
         tmem_st_wait();
         tc_fence_before();
         __syncwarp();
-        if (lane == 0) mbar_arrive(&p_full[half]);
+        if (lane == 0) mbar_arrive(&p_full[grp]);
       }
-      // ---- tile done: x = O + b2 + x, bf16 copy, row statistics ----
-      mbar_wait(o_full, nt & 1);
-      tc_fence_after();
-      constexpr int NC = C / 16, NC0 = (NC + 1) / 2;
-      const int c0 = half == 0 ? 0 : NC0, c1 = half == 0 ? NC0 : NC;
-      float* xr = p.x + row * C;
+    }
+  } else if (warp >= 12) {
+    // ===================== read-out warps =====================
+    const int q = warp & 3;
+    const uint32_t lane_sel = (uint32_t)(q * 32) << 16;
+    const uint32_t box0 = smem_u32(smem + K::OFF_BOX) + q * K::NBOX * BOX_BYTES;
+    uint64_t* my_full = box_full + q * K::NBOX;
+    const uint32_t row_off = (uint32_t)lane * 128, xr = (uint32_t)(lane & 7) << 4;
+    uint32_t uses[K::NBOX];                                   // residual boxes received per slot (phase of my_full[slot])
+#pragma unroll
+    for (int i = 0; i < K::NBOX; ++i) uses[i] = 0;
+    auto request = [&](int slot, int tile, int ch) {          // lane 0: residual chunk `ch` of `tile` -> box `slot`
+      mbar_arrive_expect_tx(&my_full[slot], BOX_BYTES);
+      tma_load_3d_addr(box0 + slot * BOX_BYTES, &map_x, &my_full[slot], ch * 32, tile * BM + q * 32, 0);
+    };
+    if (lane == 0 && (int)blockIdx.x < p.num_tiles) {
+#pragma unroll
+      for (int i = 0; i < K::NBOX; ++i) request(i, blockIdx.x, i);
+    }
+    int nt = 0;
+    for (int t = blockIdx.x; t < p.num_tiles; t += gridDim.x, ++nt) {
+      const int ob = nt % K::NOB;
+      const long row = (long)t * BM + q * 32 + lane;
+      const uint32_t to = tmem_base + COL_O + ob * C + lane_sel;
       bf16* xbr = p.xb_out + row * C;
       float s1 = 0.f, s2 = 0.f;
-#pragma unroll 3
-      for (int c = c0; c < c1; ++c) {
+      mbar_wait(&o_full[ob], (nt / K::NOB) & 1);
+      tc_fence_after();
+#pragma unroll
+      for (int ch = 0; ch < K::NCH; ++ch) {
+        constexpr int kFull = C / 32;                          // chunks with all 32 columns inside the row
+        const int slot = ch % K::NBOX;
+        const int nq = ch < kFull ? 8 : (C - kFull * 32) / 4;  // float4 groups of this chunk: 8, or 4 in the half chunk
         uint32_t r[32];
-        tmem_ld_x16(tmem_base + COL_O + c * 16 + lane_sel, r);
+        if (ch < kFull) tmem_ld_x32(to + ch * 32, r); else tmem_ld_x16(to + ch * 32, r);
         tmem_ld_wait();
-        if (c == c1 - 1) {                                // O has left tensor memory: the next tile's fc2 may overwrite it
+        if (ch == K::NCH - 1) {                                // O has left tensor memory: fc2 of a later tile may overwrite it
           tc_fence_before();
           __syncwarp();
-          if (lane == 0) mbar_arrive(o_free);
+          if (lane == 0) mbar_arrive(&o_free[ob]);
         }
-        if (live) {
-          float v[16];
+        mbar_wait(&my_full[slot], uses[slot] & 1);
+        ++uses[slot];
+        const uint32_t box = box0 + slot * BOX_BYTES + row_off;
+        uint32_t pk[16];
 #pragma unroll
-          for (int j = 0; j < 4; ++j) {
-            const float4 b = __ldg(reinterpret_cast<const float4*>(p.b2 + c * 16) + j);
-            const float4 x = ld_global_f4(xr + c * 16 + 4 * j);
-            v[4 * j] = __uint_as_float(r[4 * j]) + b.x + x.x;
-            v[4 * j + 1] = __uint_as_float(r[4 * j + 1]) + b.y + x.y;
-            v[4 * j + 2] = __uint_as_float(r[4 * j + 2]) + b.z + x.z;
-            v[4 * j + 3] = __uint_as_float(r[4 * j + 3]) + b.w + x.w;
+        for (int j = 0; j < 8; ++j) {
+          if (j < nq) {
+            const float4 b = __ldg(reinterpret_cast<const float4*>(p.b2 + ch * 32) + j);
+            const uint32_t addr = box + (((uint32_t)j << 4) ^ xr);
+            const float4 x = ld_shared_f4(addr);
+            float4 v;
+            v.x = __uint_as_float(r[4 * j]) + b.x + x.x;
+            v.y = __uint_as_float(r[4 * j + 1]) + b.y + x.y;
+            v.z = __uint_as_float(r[4 * j + 2]) + b.z + x.z;
+            v.w = __uint_as_float(r[4 * j + 3]) + b.w + x.w;
+            s1 += (v.x + v.y) + (v.z + v.w);
+            s2 = fmaf(v.x, v.x, s2); s2 = fmaf(v.y, v.y, s2); s2 = fmaf(v.z, v.z, s2); s2 = fmaf(v.w, v.w, s2);
+            st_shared_u4(addr, __float_as_uint(v.x), __float_as_uint(v.y), __float_as_uint(v.z), __float_as_uint(v.w));
+            pk[2 * j] = pack_bf16x2(v.x, v.y);
+            pk[2 * j + 1] = pack_bf16x2(v.z, v.w);
           }
+        }
+        if (row < p.M) {                                       // bf16 copy: 64 B (32 B in the half chunk) per row, straight from registers
 #pragma unroll
-          for (int j = 0; j < 16; ++j) { s1 += v[j]; s2 = fmaf(v[j], v[j], s2); }
-#pragma unroll
-          for (int j = 0; j < 4; ++j) st_global_f4(xr + c * 16 + 4 * j, make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]));
-          uint4 lo, hi;
-          lo.x = pack_bf16x2(v[0], v[1]); lo.y = pack_bf16x2(v[2], v[3]); lo.z = pack_bf16x2(v[4], v[5]); lo.w = pack_bf16x2(v[6], v[7]);
-          hi.x = pack_bf16x2(v[8], v[9]); hi.y = pack_bf16x2(v[10], v[11]); hi.z = pack_bf16x2(v[12], v[13]); hi.w = pack_bf16x2(v[14], v[15]);
-          *reinterpret_cast<uint4*>(xbr + c * 16) = lo;
-          *reinterpret_cast<uint4*>(xbr + c * 16 + 8) = hi;
+          for (int j = 0; j < 4; ++j)
+            if (2 * j < nq) *reinterpret_cast<uint4*>(xbr + ch * 32 + 8 * j) = make_uint4(pk[4 * j], pk[4 * j + 1], pk[4 * j + 2], pk[4 * j + 3]);
+        }
+        fence_proxy_async_smem();
+        __syncwarp();
+        if (lane == 0) {
+          tma_store_3d(&map_x, box0 + slot * BOX_BYTES, ch * 32, t * BM + q * 32, 0);     // clips the columns / rows outside x
+          bulk_commit();
+          if (K::NBOX < K::NCH && ch + K::NBOX < K::NCH) {     // ring: the box is refilled as soon as its store has read it
+            bulk_wait_read<0>();
+            request(slot, t, ch + K::NBOX);
+          }
         }
       }
-      if (live) reinterpret_cast<float2*>(p.stats_out)[row * 2 + half] = make_float2(s1, s2);
+      if (row < p.M) reinterpret_cast<float2*>(p.stats_out)[row] = make_float2(s1, s2);
+      if (lane == 0 && t + (int)gridDim.x < p.num_tiles) {     // next tile's residual rows: a whole tile of lead time
+        bulk_wait_read<0>();
+#pragma unroll
+        for (int i = 0; i < K::NBOX; ++i) request(i, t + gridDim.x, i);
+      }
     }
+    if (lane == 0) bulk_wait_read<0>();                        // staging smem must outlive the last store's read
   }
 
   tc_fence_before();
@@ -335,8 +412,24 @@ static int fm_map(CUtensorMap* m, const bf16* ptr, long rows, long cols, long ld
   return 0;
 }
 
+// x [rows][C] fp32 row-major, box {32 columns, 32 rows, 1}, 128B swizzle: loads zero-fill and stores clip what lies outside
+static int fm_map_x(CUtensorMap* m, float* ptr, long rows, long C) {
+  EncodeTiledFnM enc = fm_encode_fn();
+  if (!enc) { set_error("cuTensorMapEncodeTiled entry point not available"); return 1; }
+  if ((reinterpret_cast<uintptr_t>(ptr) & 15) || (C * 4) % 16) { set_error("mlp_fused: x not 16 B aligned"); return 1; }
+  const cuuint64_t dims[3] = {(cuuint64_t)C, (cuuint64_t)rows, 1};
+  const cuuint64_t strides[2] = {(cuuint64_t)C * 4, (cuuint64_t)C * 4 * (cuuint64_t)rows};
+  const cuuint32_t box[3] = {32, 32, 1};
+  const cuuint32_t estr[3] = {1, 1, 1};
+  CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, ptr, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                   CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) { set_error("mlp_fused: cuTensorMapEncodeTiled(x) failed (%d)", (int)r); return 1; }
+  return 0;
+}
+
 template <int C>
-static int launch_mlp_fused(const CUtensorMap& ma, const CUtensorMap& m1, const CUtensorMap& m2, const FusedMlpParams& p, cudaStream_t stream) {
+static int launch_mlp_fused(const CUtensorMap& ma, const CUtensorMap& m1, const CUtensorMap& m2, const CUtensorMap& mx,
+                            const FusedMlpParams& p, cudaStream_t stream) {
   using K = fm::Cfg<C>;
   static PerDeviceFlag attr;
   if (!attr.is_set()) {
@@ -345,26 +438,27 @@ static int launch_mlp_fused(const CUtensorMap& ma, const CUtensorMap& m1, const 
     attr.set();
   }
   const int grid = p.num_tiles < num_sms() ? p.num_tiles : num_sms();
-  mlp_fused_kernel<C><<<grid, fm::THREADS, K::SMEM, stream>>>(ma, m1, m2, p);
+  mlp_fused_kernel<C><<<grid, fm::THREADS, K::SMEM, stream>>>(ma, m1, m2, mx, p);
   return 0;
 }
 
 bool mlp_fused_supported(int C) { return C == 144 || C == 288; }
 
-// x[M][C] (fp32, in place) += fc2(GELU(rstd(row) * (xb W1''^T) + b1)) + b2; xb_out = bf16(x); stats_out[M][2][2]
+// x[M][C] (fp32, in place) += fc2(GELU(rstd(row) * (xb W1''^T) + b1)) + b2; xb_out = bf16(x); stats_out[M][1][2] (one part per row)
 int mlp_fused(const bf16* xb, const float* stats_in, int parts_in, float eps, const bf16* w1, const float* b1, const bf16* w2,
               const float* b2, float* x, bf16* xb_out, float* stats_out, long M, int C, cudaStream_t stream) {
   if (!mlp_fused_supported(C) || M <= 0) { set_error("mlp_fused: unsupported C=%d M=%ld", C, M); return 1; }
-  CUtensorMap ma, m1, m2;
-  if (fm_map(&ma, xb, M, C, C, fm::BM) || fm_map(&m1, w1, 4L * C, C, C, fm::BH) || fm_map(&m2, w2, C, 4L * C, 4L * C, 144)) return 1;
+  CUtensorMap ma, m1, m2, mx;
+  if (fm_map(&ma, xb, M, C, C, fm::BM) || fm_map(&m1, w1, 4L * C, C, C, fm::BH) || fm_map(&m2, w2, C, 4L * C, 4L * C, 144) ||
+      fm_map_x(&mx, x, M, C)) return 1;
   FusedMlpParams p;
   p.stats_in = stats_in; p.parts_in = parts_in; p.eps = eps; p.inv_c = 1.0f / (float)C;
-  p.b1 = b1; p.b2 = b2; p.x = x; p.xb_out = xb_out; p.stats_out = stats_out;
+  p.b1 = b1; p.b2 = b2; p.xb_out = xb_out; p.stats_out = stats_out;
   p.M = (int)M; p.num_tiles = (int)((M + fm::BM - 1) / fm::BM);
   char nm[64];
   if (g_prof_on) snprintf(nm, sizeof(nm), "mlp_fused m%ld c%d", M, C);
   ProfRange pr(stream, nm, 16.0 * (double)M * C * C, (double)M * C * (2.0 + 4.0 + 4.0 + 2.0));
-  const int rc = C == 144 ? launch_mlp_fused<144>(ma, m1, m2, p, stream) : launch_mlp_fused<288>(ma, m1, m2, p, stream);
+  const int rc = C == 144 ? launch_mlp_fused<144>(ma, m1, m2, mx, p, stream) : launch_mlp_fused<288>(ma, m1, m2, mx, p, stream);
   if (rc) return rc;
   SAM2B_CHECK_LAUNCH("mlp_fused");
   return 0;
