@@ -144,8 +144,8 @@ flash_attn_hd256_v64_tcgen05_kernel(const __grid_constant__ CUtensorMap map_q, c
       }
     }
   } else if (warp == 1) {
-    // ===================== MMA issuer (one thread) =====================
-    if (lane == 0) {
+    // ===================== MMA issuer (whole warp, warp-uniform values; one elected lane issues: common.cuh umma_*_w) =====================
+    {
       constexpr uint32_t idesc_qk = make_idesc_ex(128, 128, 0);
       constexpr uint32_t idesc_pv = make_idesc_ex(128, 64, 1);
       const uint32_t sbase = smem_u32(smem);
@@ -162,9 +162,9 @@ flash_attn_hd256_v64_tcgen05_kernel(const __grid_constant__ CUtensorMap map_q, c
         const uint32_t d = tmem_base + COL_S + 128 * bsel;
 #pragma unroll
         for (int ks = 0; ks < 16; ++ks)
-          umma_bf16_ts(d, tmem_base + COL_Q + 8 * ks, make_smem_desc(k + (ks >> 2) * 16384 + (ks & 3) * 32, 16, 1024, 2), idesc_qk,
+          umma_bf16_ts_w(d, tmem_base + COL_Q + 8 * ks, make_smem_desc(k + (ks >> 2) * 16384 + (ks & 3) * 32, 16, 1024, 2), idesc_qk,
                        ks != 0);
-        umma_commit(&s_full[bsel]);
+        umma_commit_w(&s_full[bsel]);
         ++n_s;
       };
       for (int u = blockIdx.x; u < p.num_units; u += gridDim.x, ++nu) {
@@ -175,7 +175,7 @@ flash_attn_hd256_v64_tcgen05_kernel(const __grid_constant__ CUtensorMap map_q, c
         mbar_wait(&k_full[it % NSTAGE], (it / NSTAGE) & 1);
         tc_fence_after();
         issue_qk(it % NSTAGE);
-        umma_commit(&k_empty[it % NSTAGE]);
+        umma_commit_w(&k_empty[it % NSTAGE]);
         mbar_wait(o_free, (nu & 1) ^ 1);          // previous unit's accumulator has been read out
         for (int j = 0; j < n_kv; ++j, ++it) {
           const int st = it % NSTAGE, st1 = (it + 1) % NSTAGE;
@@ -183,7 +183,7 @@ flash_attn_hd256_v64_tcgen05_kernel(const __grid_constant__ CUtensorMap map_q, c
             mbar_wait(&k_full[st1], ((it + 1) / NSTAGE) & 1);
             tc_fence_after();
             issue_qk(st1);                         // S(j+1) is computed while the softmax warps work on S(j)
-            umma_commit(&k_empty[st1]);
+            umma_commit_w(&k_empty[st1]);
           }
           mbar_wait(&v_full[st], (it / NSTAGE) & 1);
           mbar_wait(p_full, n_o & 1);
@@ -193,9 +193,9 @@ flash_attn_hd256_v64_tcgen05_kernel(const __grid_constant__ CUtensorMap map_q, c
           // one N = 64 instruction per 16 keys: V is MN-major (d contiguous), one 128 B-swizzle atom wide; P is read from tensor memory
 #pragma unroll
           for (int ks = 0; ks < 8; ++ks)
-            umma_bf16_ts(tmem_base + COL_O, pa + 8 * ks, make_smem_desc(v + ks * 2048, 16384, 1024, 2), idesc_pv, (j | ks) != 0);
-          umma_commit(o_done);
-          umma_commit(&v_empty[st]);
+            umma_bf16_ts_w(tmem_base + COL_O, pa + 8 * ks, make_smem_desc(v + ks * 2048, 16384, 1024, 2), idesc_pv, (j | ks) != 0);
+          umma_commit_w(o_done);
+          umma_commit_w(&v_empty[st]);
           ++n_o;
         }
       }
