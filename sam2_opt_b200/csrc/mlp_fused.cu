@@ -37,21 +37,21 @@ namespace sam2b {
 
 namespace fm {
 static constexpr int BM = 128;
-static constexpr int BH = 96;                        // hidden chunk
+static constexpr int BH = 64;                        // hidden chunk = one 64-wide W2 block
+static constexpr int NSB = 3;                        // S buffers: fc1 of chunk c + 2 never waits for the GELU pass over chunk c
 static constexpr int THREADS = 512;
 static constexpr int A_KB_BYTES = BM * 128;          // [128 rows][64 k] bf16, 128B swizzle
-static constexpr int W1_BYTES = BH * 128;            // [96 hidden][64 k]
+static constexpr int W1_BYTES = BH * 128;            // [64 hidden][64 k]
 static constexpr int BOX_BYTES = 32 * 128;           // [32 rows][32 fp32 columns], 128B swizzle
-static constexpr int COL_S = 0;                      // S buffer b at COL_S + 96 b; P over its first 48 columns
-static constexpr int COL_O = 192;                    // O buffer j at COL_O + j C
+static constexpr int COL_S = 0;                      // S buffer b at COL_S + 64 b; P over its first 32 columns
+static constexpr int COL_O = NSB * BH;               // O buffer j at COL_O + j C
 template <int C>
 struct Cfg {
   static constexpr int KB = (C + 63) / 64;           // k-blocks of the A tile (the last one partly zero-filled by TMA)
   static constexpr int NH = 4 * C / BH;              // hidden chunks
   static constexpr int NSPLIT = C / 144;             // fc2 instructions per k-step (N = 144 each; tcgen05.mma N <= 256)
   static constexpr int W2_BYTES = C * 128;           // [C rows][64 hidden]
-  static constexpr int NB2 = 4 * C / 64;             // 64-wide W2 blocks per tile (a block may straddle two hidden chunks)
-  static constexpr int NS1 = 3;                      // W1 ring depth
+  static constexpr int NS1 = 4;                      // W1 ring depth (8 KB blocks)
   static constexpr int NS2 = C == 144 ? 3 : 2;       // W2 ring depth
   static constexpr int NOB = C == 144 ? 2 : 1;       // O accumulators in tensor memory
   static constexpr int NCH = (C + 31) / 32;          // 32-column read-out chunks of a row (the last one may be half full)
@@ -62,7 +62,7 @@ struct Cfg {
   static constexpr int OFF_BOX = OFF_W2 + NS2 * W2_BYTES;
   static constexpr int OFF_BAR = OFF_BOX + 4 * NBOX * BOX_BYTES;
   static constexpr int SMEM = OFF_BAR + 512 + 1024;
-  static_assert(4 * C % BH == 0 && C % 144 == 0 && NH % 2 == 0, "C must be 144 or 288");
+  static_assert(4 * C % BH == 0 && C % 144 == 0, "C must be 144 or 288");
   static_assert(COL_O + NOB * C <= 512, "TMEM columns");
   static_assert(OFF_BOX % 1024 == 0, "swizzled boxes need 1024 B alignment");
   static_assert(SMEM <= 227 * 1024, "shared memory");
@@ -95,9 +95,9 @@ mlp_fused_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
   uint64_t* w1_empty = w1_full + K::NS1;
   uint64_t* w2_full = w1_empty + K::NS1;        // [NS2]
   uint64_t* w2_empty = w2_full + K::NS2;
-  uint64_t* s_full = w2_empty + K::NS2;         // [2]
-  uint64_t* p_full = s_full + 2;                // [2]
-  uint64_t* o_full = p_full + 2;                // [NOB]
+  uint64_t* s_full = w2_empty + K::NS2;         // [NSB]
+  uint64_t* p_full = s_full + NSB;              // [NSB]
+  uint64_t* o_full = p_full + NSB;              // [NOB]
   uint64_t* o_free = o_full + K::NOB;           // [NOB]
   uint64_t* box_full = o_free + K::NOB;         // [4 read-out warps][NBOX]
   uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(box_full + 4 * K::NBOX);
@@ -113,7 +113,7 @@ mlp_fused_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
     mbar_init(a_full, 1); mbar_init(a_empty, 1);
     for (int i = 0; i < K::NS1; ++i) { mbar_init(&w1_full[i], 1); mbar_init(&w1_empty[i], 1); }
     for (int i = 0; i < K::NS2; ++i) { mbar_init(&w2_full[i], 1); mbar_init(&w2_empty[i], 1); }
-    for (int i = 0; i < 2; ++i) { mbar_init(&s_full[i], 1); mbar_init(&p_full[i], 4); }
+    for (int i = 0; i < NSB; ++i) { mbar_init(&s_full[i], 1); mbar_init(&p_full[i], 4); }
     for (int i = 0; i < K::NOB; ++i) { mbar_init(&o_full[i], 1); mbar_init(&o_free[i], 4); }
     for (int i = 0; i < 4 * K::NBOX; ++i) mbar_init(&box_full[i], 1);
     fence_barrier_init();
@@ -148,7 +148,7 @@ mlp_fused_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
     if (lane == 0) {
       int i2 = 0;
       for (int t = blockIdx.x; t < p.num_tiles; t += gridDim.x) {
-        for (int blk = 0; blk < K::NB2; ++blk, ++i2) {
+        for (int blk = 0; blk < K::NH; ++blk, ++i2) {
           const int s = i2 % K::NS2;
           mbar_wait(&w2_empty[s], ((i2 / K::NS2) & 1) ^ 1);
           mbar_arrive_expect_tx(&w2_full[s], K::W2_BYTES);
@@ -162,18 +162,21 @@ mlp_fused_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
     // ===================== MMA issuer (whole warp, one elected lane issues) =====================
     // The issuing thread is a resource of its own: every instruction it spends on index arithmetic delays the next tcgen05.mma
     // (the first version of this loop needed ~400 clocks per MMA against the 50 - 72 the tensor pipe takes).  Ring positions are
-    // therefore carried as (stage, phase) counters, descriptors are built once per shared-memory block and advanced by constants,
-    // two hidden chunks are issued per iteration so that every W2 k-step index is a compile-time constant, and the loop is run by
-    // the whole warp with warp-uniform values (common.cuh umma_*_w), so that the descriptors live in uniform registers.
+    // carried as (stage, phase) counters, descriptors are built once per shared-memory block and advanced by constants, and the
+    // loop is run by the whole warp with warp-uniform values (common.cuh umma_*_w), so that the descriptors live in uniform
+    // registers.  Order per tile: fc1(0), fc1(1), then for every chunk c: fc1(c + 2), wait P(c), fc2(c) - with three S buffers the
+    // tensor pipe always holds the next two chunks' fc1 while the GELU warps work, and S_b is reused by chunk c + 3 in order
+    // behind fc2(c), which read P(c) out of it.
     {
       constexpr uint32_t idesc_fc1 = make_idesc_ex(128, BH, 0);
       constexpr uint32_t idesc_fc2 = make_idesc_ex(128, 144, 0);
       const uint32_t sbase = smem_u32(smem);
       int s1 = 0, s2 = 0, nt = 0;
       uint32_t ph1 = 0, ph2 = 0;        // phases of the W1 / W2 rings
-      uint32_t php = 0;                 // phase of p_full[0] and p_full[1] (both advance once per pair of chunks)
-      auto issue_fc1 = [&](int b) {     // one hidden chunk: S_b = A W1[h]^T over the KB k-blocks of the resident A tile
-        const uint32_t d = tmem_base + COL_S + BH * b;
+      int bi = 0, bc = 0;               // S buffer of the next fc1 / of the next fc2
+      uint32_t php = 0;                 // phase of p_full[bc] (flips when bc wraps)
+      auto issue_fc1 = [&]() {          // one hidden chunk: S_bi = A W1[h]^T over the KB k-blocks of the resident A tile
+        const uint32_t d = tmem_base + COL_S + BH * bi;
 #pragma unroll
         for (int kb = 0; kb < K::KB; ++kb) {
           mbar_wait(&w1_full[s1], ph1);
@@ -188,62 +191,47 @@ mlp_fused_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
           umma_commit_w(&w1_empty[s1]);
           if (++s1 == K::NS1) { s1 = 0; ph1 ^= 1; }
         }
-        umma_commit_w(&s_full[b]);
-      };
-      // k-steps [k0, k1) of a hidden chunk whose first k-step sits at position st0 of the current 64-wide W2 block
-      auto issue_fc2 = [&](uint32_t o_col, int b, int st0, bool first_chunk) {
-#pragma unroll
-        for (int k = 0; k < BH / 16; ++k) {
-          const int st = (st0 + k) & 3;
-          if (st == 0) {                                        // first use of a W2 block
-            mbar_wait(&w2_full[s2], ph2);
-            tc_fence_after();
-          }
-          const uint32_t pa = tmem_base + COL_S + BH * b + k * 8;             // 16 hidden units = 8 columns of bf16 pairs
-          const uint64_t dw = make_smem_desc_sw128(sbase + K::OFF_W2 + s2 * K::W2_BYTES) + 2 * st;
-#pragma unroll
-          for (int j = 0; j < K::NSPLIT; ++j)
-            umma_bf16_ts_w(o_col + j * 144, pa, dw + (uint64_t)(j * 144 * 128 / 16), idesc_fc2, !(first_chunk && k == 0));
-          if (st == 3) {
-            umma_commit_w(&w2_empty[s2]);
-            if (++s2 == K::NS2) { s2 = 0; ph2 ^= 1; }
-          }
-        }
+        umma_commit_w(&s_full[bi]);
+        if (++bi == NSB) bi = 0;
       };
       for (int t = blockIdx.x; t < p.num_tiles; t += gridDim.x, ++nt) {
         const int ob = nt % K::NOB;
         const uint32_t o_col = tmem_base + COL_O + ob * C;
         mbar_wait(a_full, nt & 1);
         tc_fence_after();
-        // S_b is reused by chunk h + 2: in order behind fc2 of chunk h, which read P(h) out of it after the GELU warps had
-        // read S(h) - no extra barrier needed
-        issue_fc1(0);
+        issue_fc1();
+        issue_fc1();
 #pragma unroll 1
-        for (int hp = 0; hp < K::NH / 2; ++hp) {
-          // ---- even chunk h = 2 hp (buffer 0): its 6 k-steps start a W2 block (position 0) ----
-          issue_fc1(1);                                          // chunk h + 1 overlaps the GELU pass over chunk h
-          if (hp + 1 == K::NH / 2) umma_commit_w(a_empty);         // the last fc1 of the tile has been issued: A may be refilled
-          mbar_wait(&p_full[0], php);
-          if (hp == 0) mbar_wait(&o_free[ob], ((nt / K::NOB) & 1) ^ 1);      // this accumulator's previous tile has been read out
+        for (int c = 0; c < K::NH; ++c) {
+          if (c + 2 < K::NH) issue_fc1();
+          if (c + 2 == K::NH - 1) umma_commit_w(a_empty);                    // the last fc1 of the tile has been issued: A may be refilled
+          mbar_wait(&p_full[bc], php);
+          if (c == 0) mbar_wait(&o_free[ob], ((nt / K::NOB) & 1) ^ 1);      // this accumulator's previous tile has been read out
+          mbar_wait(&w2_full[s2], ph2);
           tc_fence_after();
-          issue_fc2(o_col, 0, 0, hp == 0);
-          // ---- odd chunk h + 1 (buffer 1): starts in the middle of a W2 block (position 2) ----
-          if (hp + 1 < K::NH / 2) issue_fc1(0);
-          mbar_wait(&p_full[1], php);
-          tc_fence_after();
-          issue_fc2(o_col, 1, 2, false);
-          php ^= 1;
+          const uint32_t pa = tmem_base + COL_S + BH * bc;                   // P(c): 64 hidden units = 32 columns of bf16 pairs
+          const uint64_t dw = make_smem_desc_sw128(sbase + K::OFF_W2 + s2 * K::W2_BYTES);
+#pragma unroll
+          for (int k = 0; k < BH / 16; ++k) {
+#pragma unroll
+            for (int j = 0; j < K::NSPLIT; ++j)
+              umma_bf16_ts_w(o_col + j * 144, pa + k * 8, dw + 2 * k + (uint64_t)(j * 144 * 128 / 16), idesc_fc2, (c | k) != 0);
+          }
+          umma_commit_w(&w2_empty[s2]);
+          if (++s2 == K::NS2) { s2 = 0; ph2 ^= 1; }
+          if (++bc == NSB) { bc = 0; php ^= 1; }
         }
         umma_commit_w(&o_full[ob]);
       }
     }
   } else if (warp >= 4 && warp < 12) {
     // ===================== GELU warps =====================
-    const int q = warp & 3, grp = (warp - 4) >> 2;           // grp: hidden chunks of this parity
+    // Chunks are numbered through the whole kernel (n = tile count * NH + c); group `grp` takes the chunks of its parity, chunk n
+    // lives in S buffer n % 3.
+    const int q = warp & 3, grp = (warp - 4) >> 2;
     const uint32_t lane_sel = (uint32_t)(q * 32) << 16;
-    const uint32_t ts = tmem_base + COL_S + BH * grp + lane_sel;
-    uint32_t n_s = 0;                                         // chunks this group has taken (phase of s_full[grp])
-    for (int t = blockIdx.x; t < p.num_tiles; t += gridDim.x) {
+    int nt = 0;
+    for (int t = blockIdx.x; t < p.num_tiles; t += gridDim.x, ++nt) {
       const long row = (long)t * BM + q * 32 + lane;
       float rstd = 1.f;
       if (row < p.M) {
@@ -253,19 +241,25 @@ mlp_fused_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
         const float mu = s1 * p.inv_c;
         rstd = rsqrtf(fmaxf(fmaf(s2, p.inv_c, -mu * mu), 0.f) + p.eps);
       }
-      for (int h = grp; h < K::NH; h += 2, ++n_s) {
-        mbar_wait(&s_full[grp], n_s & 1);
+      const uint32_t n0 = (uint32_t)nt * K::NH;
+      for (int c = (int)((n0 + grp) & 1); c < K::NH; c += 2) {
+        const uint32_t n = n0 + c, buf = n % NSB;
+        const uint32_t ts = tmem_base + COL_S + BH * buf + lane_sel;
+        mbar_wait(&s_full[buf], (n / NSB) & 1);
         tc_fence_after();
+        uint32_t r0[32], r1[32];
+        tmem_ld_x32(ts, r0);
+        tmem_ld_x32(ts + 32, r1);
         // 32 columns at a time: P (16 columns of bf16 pairs) goes back over columns of S this warp has already read
-#pragma unroll 1
-        for (int c = 0; c < 3; ++c) {
-          uint32_t r[32], pk[32];
-          tmem_ld_x32(ts + c * 32, r);
-          const float4* bsrc = reinterpret_cast<const float4*>(p.b1 + h * BH + c * 32);
+#pragma unroll
+        for (int half = 0; half < 2; ++half) {
+          uint32_t (&r)[32] = half == 0 ? r0 : r1;
+          uint32_t pk[32];
+          const float4* bsrc = reinterpret_cast<const float4*>(p.b1 + c * BH + half * 32);
           float4 bv[8];
 #pragma unroll
           for (int j = 0; j < 8; ++j) bv[j] = __ldg(bsrc + j);
-          tmem_ld_wait();
+          if (half == 0) tmem_ld_wait();
 #pragma unroll
           for (int j = 0; j < 8; ++j) {
             float v0, v1, v2, v3;
@@ -274,12 +268,12 @@ mlp_fused_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
             pk[2 * j] = pack_bf16x2(v0, v1);
             pk[2 * j + 1] = pack_bf16x2(v2, v3);
           }
-          tmem_st_x16(ts + c * 16, pk);
+          tmem_st_x16(ts + half * 16, pk);
         }
         tmem_st_wait();
         tc_fence_before();
         __syncwarp();
-        if (lane == 0) mbar_arrive(&p_full[grp]);
+        if (lane == 0) mbar_arrive(&p_full[buf]);
       }
     }
   } else if (warp >= 12) {
