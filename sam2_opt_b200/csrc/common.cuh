@@ -165,6 +165,22 @@ SAM2B_DEVINL void umma_commit_w(uint64_t* bar) {
       ::"r"(smem_u32(bar)) : "memory");
 }
 
+// Cluster multicast: one TMA load lands at the same shared-memory offset of every CTA in `mask` and credits the transaction
+// bytes to the barrier at the same offset in each of them; one commit arrives on the barrier at this offset in every CTA in `mask`.
+SAM2B_DEVINL void tma_load_3d_mc(void* smem_dst, const CUtensorMap* map, uint64_t* bar, int c0, int c1, int c2, uint16_t mask) {
+  asm volatile(
+      "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes.multicast::cluster [%0], [%1, {%3, %4, %5}], [%2], %6;"
+      ::"r"(smem_u32(smem_dst)), "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2), "h"(mask)
+      : "memory");
+}
+SAM2B_DEVINL void umma_commit_mc_w(uint64_t* bar, uint16_t mask) {
+  asm volatile(
+      "{\n\t.reg .pred e;\n\t"
+      "elect.sync _|e, 0xffffffff;\n\t"
+      "@e tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;\n\t}"
+      ::"r"(smem_u32(bar)), "h"(mask) : "memory");
+}
+
 // ------------------------------------------------------------------------------------------
 // CTA pairs (cluster of 2, tcgen05 cta_group::2)
 // ------------------------------------------------------------------------------------------

@@ -51,14 +51,15 @@ struct Cfg {
   static constexpr int NH = 4 * C / BH;              // hidden chunks
   static constexpr int NSPLIT = C / 144;             // fc2 instructions per k-step (N = 144 each; tcgen05.mma N <= 256)
   static constexpr int W2_BYTES = C * 128;           // [C rows][64 hidden]
-  static constexpr int NS1 = 4;                      // W1 ring depth (8 KB blocks)
-  static constexpr int NS2 = C == 144 ? 3 : 2;       // W2 ring depth
+  static constexpr int NS1 = 3;                      // W1 ring depth in CHUNKS, one per S buffer (KB blocks of 8 KB each: one wait / commit per chunk)
+  static constexpr int W1_STAGE = KB * W1_BYTES;
+  static constexpr int NS2 = 2;                      // W2 ring depth
   static constexpr int NOB = C == 144 ? 2 : 1;       // O accumulators in tensor memory
   static constexpr int NCH = (C + 31) / 32;          // 32-column read-out chunks of a row (the last one may be half full)
-  static constexpr int NBOX = C == 144 ? NCH : 2;    // residual boxes per read-out warp: the whole row / a ring of two
+  static constexpr int NBOX = 3;                     // residual boxes per read-out warp (a ring: NCH = 5 chunks per row)
   static constexpr int OFF_A = 0;
   static constexpr int OFF_W1 = OFF_A + KB * A_KB_BYTES;
-  static constexpr int OFF_W2 = OFF_W1 + NS1 * W1_BYTES;
+  static constexpr int OFF_W2 = OFF_W1 + NS1 * W1_STAGE;
   static constexpr int OFF_BOX = OFF_W2 + NS2 * W2_BYTES;
   static constexpr int OFF_BAR = OFF_BOX + 4 * NBOX * BOX_BYTES;
   static constexpr int SMEM = OFF_BAR + 512 + 1024;
@@ -78,9 +79,23 @@ struct FusedMlpParams {
   bf16* xb_out;              // [M][C] bf16 copy of the new stream
   float* stats_out;          // [M][1][2]
   int M, num_tiles;
+  long long* trace;          // development only (SAM2B_MLP_TRACE): [role][256] pairs (event code, SM clock) written by CTA 0
 };
+#define FM_TR(role, code)                                                                                   \
+  do {                                                                                                      \
+    if (p.trace && blockIdx.x == 0 && lane == 0 && tr_n < 256) {                                            \
+      p.trace[((role) * 256 + tr_n) * 2] = (code);                                                          \
+      p.trace[((role) * 256 + tr_n) * 2 + 1] = clock64();                                                   \
+      ++tr_n;                                                                                               \
+    }                                                                                                       \
+  } while (0)
 
-template <int C>
+// CL = 2: the kernel runs as clusters of two CTAs that work on neighbouring row tiles and SHARE the weight stream: each CTA
+// loads half of every W1 / W2 block and multicasts it into both CTAs' rings, so a CTA pulls half the weight bytes through its
+// own L2 -> shared-memory path and the ring covers twice the latency (the weights, 332 KB / 1.3 MB per tile at C = 144 / 288,
+// are the dominant on-chip traffic of this kernel).  A ring slot is free again when BOTH CTAs have consumed it: the "empty"
+// barriers count two arrivals, one multicast commit from each CTA's MMA warp.
+template <int C, int CL>
 __global__ void __launch_bounds__(fm::THREADS, 1)
 mlp_fused_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_w1,
                  const __grid_constant__ CUtensorMap map_w2, const __grid_constant__ CUtensorMap map_x, const FusedMlpParams p) {
@@ -103,6 +118,7 @@ mlp_fused_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
   uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(box_full + 4 * K::NBOX);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  int tr_n = 0;
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&map_a);
     tma_prefetch_desc(&map_w1);
@@ -111,8 +127,8 @@ mlp_fused_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
   }
   if (warp == 1 && lane == 0) {
     mbar_init(a_full, 1); mbar_init(a_empty, 1);
-    for (int i = 0; i < K::NS1; ++i) { mbar_init(&w1_full[i], 1); mbar_init(&w1_empty[i], 1); }
-    for (int i = 0; i < K::NS2; ++i) { mbar_init(&w2_full[i], 1); mbar_init(&w2_empty[i], 1); }
+    for (int i = 0; i < K::NS1; ++i) { mbar_init(&w1_full[i], 1); mbar_init(&w1_empty[i], CL); }
+    for (int i = 0; i < K::NS2; ++i) { mbar_init(&w2_full[i], 1); mbar_init(&w2_empty[i], CL); }
     for (int i = 0; i < NSB; ++i) { mbar_init(&s_full[i], 1); mbar_init(&p_full[i], 4); }
     for (int i = 0; i < K::NOB; ++i) { mbar_init(&o_full[i], 1); mbar_init(&o_free[i], 4); }
     for (int i = 0; i < 4 * K::NBOX; ++i) mbar_init(&box_full[i], 1);
@@ -120,9 +136,11 @@ mlp_fused_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
   }
   if (warp == 2) { tmem_alloc(tmem_ptr, 512); tmem_relinquish(); }
   tc_fence_before();
-  __syncthreads();
+  if (CL == 2) cluster_sync_all(); else __syncthreads();     // the pair's barriers are initialised before any remote arrival
   tc_fence_after();
   const uint32_t tmem_base = *tmem_ptr;
+  const int crank = CL == 2 ? (int)cluster_ctarank() : 0;
+  constexpr uint16_t kMask = CL == 2 ? 3 : 1;
 
   if (warp == 0) {
     // ===================== TMA producer 1: the A tile and the W1 ring =====================
@@ -133,12 +151,17 @@ mlp_fused_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
         mbar_arrive_expect_tx(a_full, K::KB * A_KB_BYTES);
 #pragma unroll
         for (int kb = 0; kb < K::KB; ++kb) tma_load_3d(smem + K::OFF_A + kb * A_KB_BYTES, &map_a, a_full, kb * 64, t * BM, 0);
-        for (int h = 0; h < K::NH; ++h) {
-          for (int kb = 0; kb < K::KB; ++kb, ++i1) {
-            const int s = i1 % K::NS1;
-            mbar_wait(&w1_empty[s], ((i1 / K::NS1) & 1) ^ 1);
-            mbar_arrive_expect_tx(&w1_full[s], W1_BYTES);
-            tma_load_3d(smem + K::OFF_W1 + s * W1_BYTES, &map_w1, &w1_full[s], kb * 64, h * BH, 0);
+        for (int h = 0; h < K::NH; ++h, ++i1) {
+          const int s = i1 % K::NS1;
+          mbar_wait(&w1_empty[s], ((i1 / K::NS1) & 1) ^ 1);
+          mbar_arrive_expect_tx(&w1_full[s], K::W1_STAGE);
+#pragma unroll
+          for (int kb = 0; kb < K::KB; ++kb) {
+            uint8_t* dst = smem + K::OFF_W1 + s * K::W1_STAGE + kb * W1_BYTES;
+            if (CL == 2)     // this CTA's half of the block (32 hidden units), into both rings
+              tma_load_3d_mc(dst + crank * (W1_BYTES / 2), &map_w1, &w1_full[s], kb * 64, h * BH + crank * (BH / 2), 0, kMask);
+            else
+              tma_load_3d(dst, &map_w1, &w1_full[s], kb * 64, h * BH, 0);
           }
         }
       }
@@ -153,8 +176,12 @@ mlp_fused_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
           mbar_wait(&w2_empty[s], ((i2 / K::NS2) & 1) ^ 1);
           mbar_arrive_expect_tx(&w2_full[s], K::W2_BYTES);
 #pragma unroll
-          for (int j = 0; j < K::NSPLIT; ++j)
-            tma_load_3d(smem + K::OFF_W2 + s * K::W2_BYTES + j * 144 * 128, &map_w2, &w2_full[s], blk * 64, j * 144, 0);
+          for (int j = 0; j < K::NSPLIT; ++j) {
+            if (CL == 2)     // 72 of the 144 rows of every piece (9 whole swizzle atoms), into both rings
+              tma_load_3d_mc(smem + K::OFF_W2 + s * K::W2_BYTES + (j * 144 + crank * 72) * 128, &map_w2, &w2_full[s], blk * 64, j * 144 + crank * 72, 0, kMask);
+            else
+              tma_load_3d(smem + K::OFF_W2 + s * K::W2_BYTES + j * 144 * 128, &map_w2, &w2_full[s], blk * 64, j * 144, 0);
+          }
         }
       }
     }
@@ -177,20 +204,21 @@ mlp_fused_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
       uint32_t php = 0;                 // phase of p_full[bc] (flips when bc wraps)
       auto issue_fc1 = [&]() {          // one hidden chunk: S_bi = A W1[h]^T over the KB k-blocks of the resident A tile
         const uint32_t d = tmem_base + COL_S + BH * bi;
+        mbar_wait(&w1_full[s1], ph1);
+        tc_fence_after();
+        const uint64_t da0 = make_smem_desc_sw128(sbase + K::OFF_A);
+        const uint64_t db0 = make_smem_desc_sw128(sbase + K::OFF_W1 + s1 * K::W1_STAGE);
 #pragma unroll
         for (int kb = 0; kb < K::KB; ++kb) {
-          mbar_wait(&w1_full[s1], ph1);
-          tc_fence_after();
-          const uint64_t da = make_smem_desc_sw128(sbase + K::OFF_A + kb * A_KB_BYTES);
-          const uint64_t db = make_smem_desc_sw128(sbase + K::OFF_W1 + s1 * W1_BYTES);
           constexpr int kFull = C / 64;
           const int ksteps = kb < kFull ? 4 : (C - kFull * 64) / 16;
 #pragma unroll
           for (int k = 0; k < 4; ++k)
-            if (k < ksteps) umma_bf16_w(d, da + 2 * k, db + 2 * k, idesc_fc1, (kb | k) != 0);
-          umma_commit_w(&w1_empty[s1]);
-          if (++s1 == K::NS1) { s1 = 0; ph1 ^= 1; }
+            if (k < ksteps)
+              umma_bf16_w(d, da0 + (uint64_t)(kb * A_KB_BYTES / 16 + 2 * k), db0 + (uint64_t)(kb * W1_BYTES / 16 + 2 * k), idesc_fc1, (kb | k) != 0);
         }
+        if (CL == 2) umma_commit_mc_w(&w1_empty[s1], kMask); else umma_commit_w(&w1_empty[s1]);
+        if (++s1 == K::NS1) { s1 = 0; ph1 ^= 1; }
         umma_commit_w(&s_full[bi]);
         if (++bi == NSB) bi = 0;
       };
@@ -199,16 +227,20 @@ mlp_fused_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
         const uint32_t o_col = tmem_base + COL_O + ob * C;
         mbar_wait(a_full, nt & 1);
         tc_fence_after();
+        FM_TR(0, 1000 + nt);
         issue_fc1();
         issue_fc1();
 #pragma unroll 1
         for (int c = 0; c < K::NH; ++c) {
           if (c + 2 < K::NH) issue_fc1();
+          FM_TR(0, 100 + c);
           if (c + 2 == K::NH - 1) umma_commit_w(a_empty);                    // the last fc1 of the tile has been issued: A may be refilled
           mbar_wait(&p_full[bc], php);
+          FM_TR(0, 200 + c);
           if (c == 0) mbar_wait(&o_free[ob], ((nt / K::NOB) & 1) ^ 1);      // this accumulator's previous tile has been read out
           mbar_wait(&w2_full[s2], ph2);
           tc_fence_after();
+          FM_TR(0, 300 + c);
           const uint32_t pa = tmem_base + COL_S + BH * bc;                   // P(c): 64 hidden units = 32 columns of bf16 pairs
           const uint64_t dw = make_smem_desc_sw128(sbase + K::OFF_W2 + s2 * K::W2_BYTES);
 #pragma unroll
@@ -217,7 +249,7 @@ mlp_fused_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
             for (int j = 0; j < K::NSPLIT; ++j)
               umma_bf16_ts_w(o_col + j * 144, pa + k * 8, dw + 2 * k + (uint64_t)(j * 144 * 128 / 16), idesc_fc2, (c | k) != 0);
           }
-          umma_commit_w(&w2_empty[s2]);
+          if (CL == 2) umma_commit_mc_w(&w2_empty[s2], kMask); else umma_commit_w(&w2_empty[s2]);
           if (++s2 == K::NS2) { s2 = 0; ph2 ^= 1; }
           if (++bc == NSB) { bc = 0; php ^= 1; }
         }
@@ -245,8 +277,10 @@ mlp_fused_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
       for (int c = (int)((n0 + grp) & 1); c < K::NH; c += 2) {
         const uint32_t n = n0 + c, buf = n % NSB;
         const uint32_t ts = tmem_base + COL_S + BH * buf + lane_sel;
+        if (q == 0) FM_TR(1 + grp, 100 + c);
         mbar_wait(&s_full[buf], (n / NSB) & 1);
         tc_fence_after();
+        if (q == 0) FM_TR(1 + grp, 200 + c);
         uint32_t r0[32], r1[32];
         tmem_ld_x32(ts, r0);
         tmem_ld_x32(ts + 32, r1);
@@ -274,6 +308,7 @@ mlp_fused_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
         tc_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive(&p_full[buf]);
+        if (q == 0) FM_TR(1 + grp, 300 + c);
       }
     }
   } else if (warp >= 12) {
@@ -301,8 +336,10 @@ mlp_fused_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
       const uint32_t to = tmem_base + COL_O + ob * C + lane_sel;
       bf16* xbr = p.xb_out + row * C;
       float s1 = 0.f, s2 = 0.f;
+      if (q == 0) FM_TR(3, 100 + nt);
       mbar_wait(&o_full[ob], (nt / K::NOB) & 1);
       tc_fence_after();
+      if (q == 0) FM_TR(3, 200 + nt);
 #pragma unroll
       for (int ch = 0; ch < K::NCH; ++ch) {
         constexpr int kFull = C / 32;                          // chunks with all 32 columns inside the row
@@ -354,6 +391,7 @@ mlp_fused_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
           }
         }
       }
+      if (q == 0) FM_TR(3, 300 + nt);
       if (row < p.M) reinterpret_cast<float2*>(p.stats_out)[row] = make_float2(s1, s2);
       if (lane == 0 && t + (int)gridDim.x < p.num_tiles) {     // next tile's residual rows: a whole tile of lead time
         bulk_wait_read<0>();
@@ -365,7 +403,7 @@ mlp_fused_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
   }
 
   tc_fence_before();
-  __syncthreads();
+  if (CL == 2) cluster_sync_all(); else __syncthreads();     // the peer's rings and barriers stay alive until both CTAs are done
   if (warp == 2) {
     tc_fence_after();
     tmem_dealloc(tmem_base, 512);
@@ -421,40 +459,74 @@ static int fm_map_x(CUtensorMap* m, float* ptr, long rows, long C) {
   return 0;
 }
 
-template <int C>
+template <int C, int CL>
 static int launch_mlp_fused(const CUtensorMap& ma, const CUtensorMap& m1, const CUtensorMap& m2, const CUtensorMap& mx,
                             const FusedMlpParams& p, cudaStream_t stream) {
   using K = fm::Cfg<C>;
   static PerDeviceFlag attr;
+  auto kern = mlp_fused_kernel<C, CL>;
   if (!attr.is_set()) {
-    cudaError_t e = cudaFuncSetAttribute(mlp_fused_kernel<C>, cudaFuncAttributeMaxDynamicSharedMemorySize, K::SMEM);
-    if (e != cudaSuccess) { set_error("cudaFuncSetAttribute(mlp_fused<%d>): %s", C, cudaGetErrorString(e)); return 1; }
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, K::SMEM);
+    if (e != cudaSuccess) { set_error("cudaFuncSetAttribute(mlp_fused<%d,%d>): %s", C, CL, cudaGetErrorString(e)); return 1; }
     attr.set();
   }
-  const int grid = p.num_tiles < num_sms() ? p.num_tiles : num_sms();
-  mlp_fused_kernel<C><<<grid, fm::THREADS, K::SMEM, stream>>>(ma, m1, m2, mx, p);
+  int grid = p.num_tiles < num_sms() ? p.num_tiles : num_sms();
+  if (CL == 2) grid &= ~1;                      // whole pairs; both CTAs of a pair then walk the same number of tiles
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(grid); cfg.blockDim = dim3(fm::THREADS); cfg.dynamicSmemBytes = K::SMEM; cfg.stream = stream;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeClusterDimension; at[0].val.clusterDim.x = CL; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+  cfg.attrs = at; cfg.numAttrs = 1;
+  cudaError_t e = cudaLaunchKernelEx(&cfg, kern, ma, m1, m2, mx, p);
+  if (e != cudaSuccess) { set_error("cudaLaunchKernelEx(mlp_fused<%d,%d>): %s", C, CL, cudaGetErrorString(e)); return 1; }
   return 0;
 }
 
-bool mlp_fused_supported(int C) { return C == 144 || C == 288; }
+// Stage 1 only (C = 144).  At C = 288 the same design is bound by MMA issue (fc1 as N = 64 instructions) and by the single O
+// accumulator that fits next to three S buffers, and lands at the speed of the two HBM-bound GEMMs it would replace (measured:
+// 1.11 - 1.15 ms against 0.99 - 1.24 ms per block per 32 images, profiles/r2u_mlp_fused_trace.md), so stage 2 keeps the GEMM pair.
+bool mlp_fused_supported(int C) { return C == 144; }
 
 // x[M][C] (fp32, in place) += fc2(GELU(rstd(row) * (xb W1''^T) + b1)) + b2; xb_out = bf16(x); stats_out[M][1][2] (one part per row)
 int mlp_fused(const bf16* xb, const float* stats_in, int parts_in, float eps, const bf16* w1, const float* b1, const bf16* w2,
               const float* b2, float* x, bf16* xb_out, float* stats_out, long M, int C, cudaStream_t stream) {
   if (!mlp_fused_supported(C) || M <= 0) { set_error("mlp_fused: unsupported C=%d M=%ld", C, M); return 1; }
   CUtensorMap ma, m1, m2, mx;
-  if (fm_map(&ma, xb, M, C, C, fm::BM) || fm_map(&m1, w1, 4L * C, C, C, fm::BH) || fm_map(&m2, w2, C, 4L * C, 4L * C, 144) ||
-      fm_map_x(&mx, x, M, C)) return 1;
+  const int num_tiles = (int)((M + fm::BM - 1) / fm::BM);
+  const bool pairs = num_tiles % 2 == 0 && num_tiles >= 2;      // CTA pairs sharing the weight stream need tiles in twos
+  if (fm_map(&ma, xb, M, C, C, fm::BM) || fm_map(&m1, w1, 4L * C, C, C, pairs ? fm::BH / 2 : fm::BH) ||
+      fm_map(&m2, w2, C, 4L * C, 4L * C, pairs ? 72 : 144) || fm_map_x(&mx, x, M, C)) return 1;
   FusedMlpParams p;
   p.stats_in = stats_in; p.parts_in = parts_in; p.eps = eps; p.inv_c = 1.0f / (float)C;
   p.b1 = b1; p.b2 = b2; p.xb_out = xb_out; p.stats_out = stats_out;
   p.M = (int)M; p.num_tiles = (int)((M + fm::BM - 1) / fm::BM);
+  p.trace = nullptr;
+  static long long* trace_dev = nullptr;
+  const bool tracing = getenv("SAM2B_MLP_TRACE") != nullptr;
+  if (tracing) {
+    if (!trace_dev) cudaMalloc(&trace_dev, 4 * 256 * 2 * sizeof(long long));
+    cudaMemsetAsync(trace_dev, 0, 4 * 256 * 2 * sizeof(long long), stream);
+    p.trace = trace_dev;
+  }
   char nm[64];
   if (g_prof_on) snprintf(nm, sizeof(nm), "mlp_fused m%ld c%d", M, C);
   ProfRange pr(stream, nm, 16.0 * (double)M * C * C, (double)M * C * (2.0 + 4.0 + 4.0 + 2.0));
-  const int rc = C == 144 ? launch_mlp_fused<144>(ma, m1, m2, mx, p, stream) : launch_mlp_fused<288>(ma, m1, m2, mx, p, stream);
+  const int rc = pairs ? launch_mlp_fused<144, 2>(ma, m1, m2, mx, p, stream) : launch_mlp_fused<144, 1>(ma, m1, m2, mx, p, stream);
   if (rc) return rc;
   SAM2B_CHECK_LAUNCH("mlp_fused");
+  if (tracing) {       // development: dump CTA 0's event trace of this launch
+    static long long host[4 * 256 * 2];
+    cudaStreamSynchronize(stream);
+    cudaMemcpy(host, trace_dev, sizeof(host), cudaMemcpyDeviceToHost);
+    static const char* roles[4] = {"mma", "gelu0", "gelu1", "readout"};
+    long long t0 = 0;
+    for (int r = 0; r < 4; ++r) for (int i = 0; i < 256; ++i) if (host[(r * 256 + i) * 2 + 1] && (!t0 || host[(r * 256 + i) * 2 + 1] < t0)) t0 = host[(r * 256 + i) * 2 + 1];
+    for (int r = 0; r < 4; ++r) {
+      fprintf(stderr, "MLPTRACE C=%d %s:", C, roles[r]);
+      for (int i = 0; i < 256 && host[(r * 256 + i) * 2 + 1]; ++i) fprintf(stderr, " %lld@%lld", host[(r * 256 + i) * 2], host[(r * 256 + i) * 2 + 1] - t0);
+      fprintf(stderr, "\n");
+    }
+  }
   return 0;
 }
 

@@ -99,19 +99,23 @@ def test_host_buffer_entry_point_matches_device_path(engine):
 
 
 def test_fused_mlp_path_matches_the_two_gemm_path(monkeypatch):
-    """mlp_fused.cu (fc1 -> GELU -> fc2 in one kernel for the C = 144 / 288 blocks, hidden layer in tensor memory; off by
-    default) against the default schedule on the same engine: same arithmetic up to the order of the fp32 sums."""
+    """mlp_fused.cu (fc1 -> GELU -> fc2 in one kernel for the stage-1 blocks, hidden layer in tensor memory; the default)
+    against the fc1 / fc2 GEMM pair (SAM2B_FUSED_MLP=0) on the same engine: same arithmetic up to the order of the fp32 sums
+    (and one bf16 rounding of the hidden layer each way)."""
     from oracle import sam2_oracle as O
     from sam2_opt_b200.engine import Engine
     e = Engine(O.make_weights(0))
     g = torch.Generator(device="cuda").manual_seed(5)
     img = torch.randn(2, 3, 1024, 1024, device="cuda", generator=g)
-    monkeypatch.delenv("SAM2B_FUSED_MLP", raising=False)
+    from sam2_opt_b200.engine import profile_begin, profile_end
+    monkeypatch.setenv("SAM2B_FUSED_MLP", "0")
     ref = [o.clone() for o in e.image_encode(img, True, False)]
-    monkeypatch.setenv("SAM2B_FUSED_MLP", "1")
+    monkeypatch.delenv("SAM2B_FUSED_MLP", raising=False)
+    profile_begin()
     got = e.image_encode(img, True, False)
+    assert sum(1 for r in profile_end() if r[0].startswith("mlp_fused")) == 2, "the fused MLP is not the default for blocks 0 and 1"
     for a, b in zip(got, ref):
         r = float((a - b).norm() / b.norm())
-        print(f"fused-MLP vs default: rel-L2 {r:.3e}")
+        print(f"fused MLP (default) vs GEMM pair: rel-L2 {r:.3e}")
         assert r < 5e-3
     e.release()
