@@ -60,7 +60,16 @@ struct FaParams {
   int rows_per_tile;   // grid rows covered by one 128-token tile = 128 / ws
   int num_units;
   float scale_log2;
+  long long* trace;    // development only (SAM2B_ATTN_TRACE): [role][256] pairs (event code, SM clock) written by CTA 0
 };
+#define FA_TR(role, code)                                                                                   \
+  do {                                                                                                      \
+    if (p.trace && blockIdx.x == 0 && lane == 0 && tr_n < 256) {                                            \
+      p.trace[((role) * 256 + tr_n) * 2] = (code);                                                          \
+      p.trace[((role) * 256 + tr_n) * 2 + 1] = clock64();                                                   \
+      ++tr_n;                                                                                               \
+    }                                                                                                       \
+  } while (0)
 
 struct UnitCoord { int b, head, x0, y0; };
 SAM2B_DEVINL UnitCoord unit_coord(const FaParams& p, int u) {
@@ -76,7 +85,7 @@ SAM2B_DEVINL UnitCoord unit_coord(const FaParams& p, int u) {
 
 __global__ void __launch_bounds__(fa::THREADS, 1)
 flash_attn_hd72_tcgen05_kernel(const __grid_constant__ CUtensorMap map_lo, const __grid_constant__ CUtensorMap map_hi,
-                               const FaParams p) {
+                               const __grid_constant__ CUtensorMap map_out, const FaParams p) {
   using namespace fa;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -96,10 +105,12 @@ flash_attn_hd72_tcgen05_kernel(const __grid_constant__ CUtensorMap map_lo, const
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
+  int tr_n = 0;
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&map_lo);
     tma_prefetch_desc(&map_hi);
+    tma_prefetch_desc(&map_out);
   }
   if (warp == 1 && lane == 0) {
     mbar_init(q_full, 1); mbar_init(q_empty, 1);
@@ -125,7 +136,9 @@ flash_attn_hd72_tcgen05_kernel(const __grid_constant__ CUtensorMap map_lo, const
       int it = 0, nu = 0;
       for (int u = blockIdx.x; u < p.num_units; u += gridDim.x, ++nu) {
         const UnitCoord c = unit_coord(p, u);
+        FA_TR(0, 100 + nu);
         mbar_wait(q_empty, (nu & 1) ^ 1);
+        FA_TR(0, 200 + nu);
         mbar_arrive_expect_tx(q_full, 2 * TILE_BYTES);
 #pragma unroll
         for (int t = 0; t < 2; ++t) {
@@ -188,14 +201,18 @@ flash_attn_hd72_tcgen05_kernel(const __grid_constant__ CUtensorMap map_lo, const
         ++n_o[t];
       };
       for (int u = blockIdx.x; u < p.num_units; u += gridDim.x, ++nu) {
+        FA_TR(1, 100 + nu);
         mbar_wait(q_full, nu & 1);
         tc_fence_after();
+        FA_TR(1, 200 + nu);
         {
           const int st = it % NSTAGE;
           mbar_wait(&k_full[st], (it / NSTAGE) & 1);
           tc_fence_after();
+          FA_TR(1, 300 + nu);
           issue_qk(0, st);
           issue_qk(1, st);
+          FA_TR(1, 400 + nu);
           umma_commit(&k_empty[st]);
           if (p.n_kv == 1) umma_commit(q_empty);
         }
@@ -215,8 +232,11 @@ flash_attn_hd72_tcgen05_kernel(const __grid_constant__ CUtensorMap map_lo, const
             umma_commit(&k_empty[st1]);
             if (j + 2 == p.n_kv) umma_commit(q_empty);
           }
+          FA_TR(1, 500 + 10 * nu + j);
           issue_pv(0, st, j);
+          FA_TR(1, 600 + 10 * nu + j);
           issue_pv(1, st, j);
+          FA_TR(1, 700 + 10 * nu + j);
           umma_commit(&v_empty[st]);
         }
       }
@@ -238,8 +258,10 @@ flash_attn_hd72_tcgen05_kernel(const __grid_constant__ CUtensorMap map_lo, const
       const UnitCoord c = unit_coord(p, u);
       float m_run = -INFINITY, l_run = 0.f;
       for (int j = 0; j < p.n_kv; ++j, ++n) {
+        if (wq == 0) FA_TR(2 + t, 100 + j);
         mbar_wait(&s_full[t], n & 1);
         tc_fence_after();
+        if (wq == 0) FA_TR(2 + t, 200 + j);
         // the 128 scores of this row: one pass through TMEM, held in registers for max and exp
         uint32_t s[128];
         {
@@ -273,9 +295,11 @@ flash_attn_hd72_tcgen05_kernel(const __grid_constant__ CUtensorMap map_lo, const
         if (j > 0) {
           // P V of the previous tile has completed (it was issued before this tile's Q K^T): P_t may be overwritten and
           // the accumulator rescaled
+          if (wq == 0) FA_TR(2 + t, 300 + j);
           mbar_wait(&o_full[t], n_pv & 1);
           ++n_pv;
           tc_fence_after();
+          if (wq == 0) FA_TR(2 + t, 400 + j);
           if (__any_sync(0xffffffffu, grow)) {
             uint32_t a[32];
 #pragma unroll 1
@@ -322,11 +346,13 @@ flash_attn_hd72_tcgen05_kernel(const __grid_constant__ CUtensorMap map_lo, const
         tc_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive(&p_full[t]);
+        if (wq == 0) FA_TR(2 + t, 500 + j);
       }
       // ---- unit done: O_t / l -> bf16 -> out[token][head*72 ..] ----
       mbar_wait(&o_full[t], n_pv & 1);
       ++n_pv;
       tc_fence_after();
+      if (wq == 0) FA_TR(2 + t, 600);
       uint32_t oa[32], ob[32], oc[32];
       tmem_ld_x32(to, oa);
       tmem_ld_x32(to + 32, ob);
@@ -335,36 +361,40 @@ flash_attn_hd72_tcgen05_kernel(const __grid_constant__ CUtensorMap map_lo, const
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(&o_free[t]);
+      // A thread owns one query row (144 B of output): written straight to global memory that is 32 separate 16 B pieces per
+      // store instruction, nine times per warp - the load / store unit was busy with them for ~5 000 clocks per unit (traced).
+      // The rows therefore go to shared memory (the P tile is free: its last P V has completed) and leave as ONE TMA store per
+      // warp, 32 consecutive tokens of the tile each.
       const float inv = 1.0f / l_run;
-      const int rr = t * TQ + r;
-      const int y = c.y0 + rr / p.ws, x = c.x0 + rr % p.ws;
-      bf16* op = p.out + (((long)c.b * p.H + y) * p.W + x) * C + c.head * HD;
+      const uint32_t stg = smem_u32(smem + OFF_P + t * P_BYTES) + (uint32_t)r * 144u;
 #pragma unroll
-      for (int i = 0; i < 4; ++i) {
-        uint4 v;
-        v.x = pack_bf16x2(__uint_as_float(oa[8 * i]) * inv, __uint_as_float(oa[8 * i + 1]) * inv);
-        v.y = pack_bf16x2(__uint_as_float(oa[8 * i + 2]) * inv, __uint_as_float(oa[8 * i + 3]) * inv);
-        v.z = pack_bf16x2(__uint_as_float(oa[8 * i + 4]) * inv, __uint_as_float(oa[8 * i + 5]) * inv);
-        v.w = pack_bf16x2(__uint_as_float(oa[8 * i + 6]) * inv, __uint_as_float(oa[8 * i + 7]) * inv);
-        *reinterpret_cast<uint4*>(op + 8 * i) = v;
-      }
+      for (int i = 0; i < 4; ++i)
+        st_shared_u4(stg + 16 * i, pack_bf16x2(__uint_as_float(oa[8 * i]) * inv, __uint_as_float(oa[8 * i + 1]) * inv),
+                     pack_bf16x2(__uint_as_float(oa[8 * i + 2]) * inv, __uint_as_float(oa[8 * i + 3]) * inv),
+                     pack_bf16x2(__uint_as_float(oa[8 * i + 4]) * inv, __uint_as_float(oa[8 * i + 5]) * inv),
+                     pack_bf16x2(__uint_as_float(oa[8 * i + 6]) * inv, __uint_as_float(oa[8 * i + 7]) * inv));
 #pragma unroll
-      for (int i = 0; i < 4; ++i) {
-        uint4 v;
-        v.x = pack_bf16x2(__uint_as_float(ob[8 * i]) * inv, __uint_as_float(ob[8 * i + 1]) * inv);
-        v.y = pack_bf16x2(__uint_as_float(ob[8 * i + 2]) * inv, __uint_as_float(ob[8 * i + 3]) * inv);
-        v.z = pack_bf16x2(__uint_as_float(ob[8 * i + 4]) * inv, __uint_as_float(ob[8 * i + 5]) * inv);
-        v.w = pack_bf16x2(__uint_as_float(ob[8 * i + 6]) * inv, __uint_as_float(ob[8 * i + 7]) * inv);
-        *reinterpret_cast<uint4*>(op + 32 + 8 * i) = v;
+      for (int i = 0; i < 4; ++i)
+        st_shared_u4(stg + 64 + 16 * i, pack_bf16x2(__uint_as_float(ob[8 * i]) * inv, __uint_as_float(ob[8 * i + 1]) * inv),
+                     pack_bf16x2(__uint_as_float(ob[8 * i + 2]) * inv, __uint_as_float(ob[8 * i + 3]) * inv),
+                     pack_bf16x2(__uint_as_float(ob[8 * i + 4]) * inv, __uint_as_float(ob[8 * i + 5]) * inv),
+                     pack_bf16x2(__uint_as_float(ob[8 * i + 6]) * inv, __uint_as_float(ob[8 * i + 7]) * inv));
+      st_shared_u4(stg + 128, pack_bf16x2(__uint_as_float(oc[0]) * inv, __uint_as_float(oc[1]) * inv),
+                   pack_bf16x2(__uint_as_float(oc[2]) * inv, __uint_as_float(oc[3]) * inv),
+                   pack_bf16x2(__uint_as_float(oc[4]) * inv, __uint_as_float(oc[5]) * inv),
+                   pack_bf16x2(__uint_as_float(oc[6]) * inv, __uint_as_float(oc[7]) * inv));
+      fence_proxy_async_smem();
+      __syncwarp();
+      if (lane == 0) {
+        const int tok = t * TQ + wq * 32;                       // first token of this warp inside the 256-query unit
+        tma_store_5d(&map_out, smem_u32(smem + OFF_P + t * P_BYTES) + (uint32_t)(wq * 32) * 144u, 0, c.head, c.x0 + tok % p.ws,
+                     c.y0 + tok / p.ws, c.b);
+        bulk_commit();
+        bulk_wait_read<0>();                                    // the staging rows have been read: P may be written again
       }
-      {
-        uint4 v;
-        v.x = pack_bf16x2(__uint_as_float(oc[0]) * inv, __uint_as_float(oc[1]) * inv);
-        v.y = pack_bf16x2(__uint_as_float(oc[2]) * inv, __uint_as_float(oc[3]) * inv);
-        v.z = pack_bf16x2(__uint_as_float(oc[4]) * inv, __uint_as_float(oc[5]) * inv);
-        v.w = pack_bf16x2(__uint_as_float(oc[6]) * inv, __uint_as_float(oc[7]) * inv);
-        *reinterpret_cast<uint4*>(op + 64) = v;
-      }
+      __syncwarp();
+      named_bar_sync(1 + t, 128);                               // ... by any warp of this group (P rows are not warp-private)
+      if (wq == 0) FA_TR(2 + t, 700);
     }
   }
 
@@ -418,6 +448,16 @@ int flash_attention_hd72(const bf16* qkv, bf16* out, int B, int H, int W, int he
                      CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) { set_error("flash_attention_hd72: cuTensorMapEncodeTiled failed (%d) map %d", (int)r, i); return 1; }
   }
+  // output [B,H,W,heads,72] bf16: boxes of 32 consecutive tokens of a tile (one per softmax warp), 144 B per token
+  CUtensorMap map_out;
+  {
+    const cuuint64_t odims[5] = {(cuuint64_t)HD, (cuuint64_t)heads, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)B};
+    const cuuint64_t ostrides[4] = {(cuuint64_t)HD * 2, (cuuint64_t)(C * 2), (cuuint64_t)W * C * 2, (cuuint64_t)H * W * C * 2};
+    const cuuint32_t obox[5] = {(cuuint32_t)HD, 1, (cuuint32_t)(ws >= 32 ? 32 : ws), (cuuint32_t)(ws >= 32 ? 1 : 32 / ws), 1};
+    CUresult r = enc(&map_out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 5, out, odims, ostrides, obox, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                     CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) { set_error("flash_attention_hd72: cuTensorMapEncodeTiled failed (%d) for the output", (int)r); return 1; }
+  }
   static PerDeviceFlag attr;
   if (!attr.is_set()) {
     cudaError_t e = cudaFuncSetAttribute(flash_attn_hd72_tcgen05_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM);
@@ -432,13 +472,34 @@ int flash_attention_hd72(const bf16* qkv, bf16* out, int B, int H, int W, int he
   p.nwx = W / ws;
   p.num_units = B * heads * p.blocks_per_img;
   p.scale_log2 = 1.4426950408889634f / sqrtf((float)HD);
+  p.trace = nullptr;
+  static long long* trace_dev = nullptr;
+  const bool tracing = getenv("SAM2B_ATTN_TRACE") != nullptr;
+  if (tracing) {
+    if (!trace_dev) cudaMalloc(&trace_dev, 4 * 256 * 2 * sizeof(long long));
+    cudaMemsetAsync(trace_dev, 0, 4 * 256 * 2 * sizeof(long long), stream);
+    p.trace = trace_dev;
+  }
   const int grid = p.num_units < num_sms() ? p.num_units : num_sms();
   char nm[96];
   if (g_prof_on) snprintf(nm, sizeof(nm), "attn h%d heads%d ws%d pool0 b%d tc", H, heads, ws, B);
   const double nq = (double)B * H * W * heads;
   ProfRange pr(stream, nm, 4.0 * nq * (ws == W ? H * W : 256) * HD, (double)B * H * W * 4 * C * 2.0);
-  flash_attn_hd72_tcgen05_kernel<<<grid, THREADS, SMEM, stream>>>(maps[0], maps[1], p);
+  flash_attn_hd72_tcgen05_kernel<<<grid, THREADS, SMEM, stream>>>(maps[0], maps[1], map_out, p);
   SAM2B_CHECK_LAUNCH("flash_attn_hd72_tcgen05");
+  if (tracing) {       // development: dump CTA 0's event trace of this launch
+    static long long host[4 * 256 * 2];
+    cudaStreamSynchronize(stream);
+    cudaMemcpy(host, trace_dev, sizeof(host), cudaMemcpyDeviceToHost);
+    static const char* roles[4] = {"tma", "mma", "softmax0", "softmax1"};
+    long long t0 = 0;
+    for (int r = 0; r < 4; ++r) for (int i = 0; i < 256; ++i) if (host[(r * 256 + i) * 2 + 1] && (!t0 || host[(r * 256 + i) * 2 + 1] < t0)) t0 = host[(r * 256 + i) * 2 + 1];
+    for (int r = 0; r < 4; ++r) {
+      fprintf(stderr, "ATTNTRACE ws=%d %s:", ws, roles[r]);
+      for (int i = 0; i < 256 && host[(r * 256 + i) * 2 + 1]; ++i) fprintf(stderr, " %lld@%lld", host[(r * 256 + i) * 2], host[(r * 256 + i) * 2 + 1] - t0);
+      fprintf(stderr, "\n");
+    }
+  }
   return 0;
 }
 

@@ -86,6 +86,13 @@ SAM2B_DEVINL void tma_store_3d(const CUtensorMap* map, uint32_t smem_src, int c0
                ::"l"(map), "r"(smem_src), "r"(c0), "r"(c1), "r"(c2)
                : "memory");
 }
+SAM2B_DEVINL void tma_store_5d(const CUtensorMap* map, uint32_t smem_src, int c0, int c1, int c2, int c3, int c4) {
+  asm volatile("cp.async.bulk.tensor.5d.global.shared::cta.bulk_group [%0, {%2, %3, %4, %5, %6}], [%1];"
+               ::"l"(map), "r"(smem_src), "r"(c0), "r"(c1), "r"(c2), "r"(c3), "r"(c4)
+               : "memory");
+}
+// named barrier among `count` threads (ids 1..15; 0 is __syncthreads)
+SAM2B_DEVINL void named_bar_sync(int id, int count) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(count) : "memory"); }
 SAM2B_DEVINL void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
 template <int N>
 SAM2B_DEVINL void bulk_wait_read() { asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory"); }
