@@ -254,6 +254,7 @@ flash_attn_hd72_tcgen05_kernel(const __grid_constant__ CUtensorMap map_lo, const
     const int C = p.heads * HD;
     uint32_t n = 0;                           // KV tiles processed by this warpgroup (all units): phase of s_full[t]
     uint32_t n_pv = 0;                        // P V completions observed on o_full[t] (in order)
+    bool stores_pending = false;
     for (int u = blockIdx.x; u < p.num_units; u += gridDim.x) {
       const UnitCoord c = unit_coord(p, u);
       float m_run = -INFINITY, l_run = 0.f;
@@ -317,6 +318,14 @@ flash_attn_hd72_tcgen05_kernel(const __grid_constant__ CUtensorMap map_lo, const
             tmem_st_x16(to + 64, a);
             tmem_st_wait();
           }
+        }
+        if (stores_pending) {
+          // the previous unit's output rows were staged in this P tile: every warp's TMA store must have read them before any
+          // warp writes P again (P rows are not warp-private).  The stores were issued a whole score tile ago, so this is free.
+          if (lane == 0) bulk_wait_read<0>();
+          __syncwarp();
+          named_bar_sync(1 + t, 128);
+          stores_pending = false;
         }
         // P = exp2(S * scale - m) -> bf16 -> swizzled K-major smem tile; fp32 row sum
         // packed fp32 pairs: one FFMA2 (scale, minus max) and one FADD2 (row sum) per two keys
@@ -390,12 +399,11 @@ flash_attn_hd72_tcgen05_kernel(const __grid_constant__ CUtensorMap map_lo, const
         tma_store_5d(&map_out, smem_u32(smem + OFF_P + t * P_BYTES) + (uint32_t)(wq * 32) * 144u, 0, c.head, c.x0 + tok % p.ws,
                      c.y0 + tok / p.ws, c.b);
         bulk_commit();
-        bulk_wait_read<0>();                                    // the staging rows have been read: P may be written again
       }
-      __syncwarp();
-      named_bar_sync(1 + t, 128);                               // ... by any warp of this group (P rows are not warp-private)
+      stores_pending = true;      // P_t doubles as the staging area: see the wait before the next unit's first P write
       if (wq == 0) FA_TR(2 + t, 700);
     }
+    if (lane == 0) bulk_wait_read<0>();       // staging smem must outlive the last store's read
   }
 
   tc_fence_before();
