@@ -390,8 +390,8 @@ def main():
         peak, hbm, how = _peaks()
         ach = g_fl / (g_ms * 1e-3) / 1e12
         traffic, traffic_note = None, None
-        tp = os.path.join(ROOT, "profiles", "r2_traffic.json")
-        if os.path.exists(tp):
+        tp = next((q for q in (os.path.join(ROOT, "profiles", n) for n in ("r2_traffic.json", "r2b_traffic.json")) if os.path.exists(q)), None)
+        if tp:
             tj = json.load(open(tp))
             traffic = tj["dram_bytes_per_launch_avg"]
             traffic_note = tj["note"]

@@ -1,29 +1,33 @@
-// Fused trunk MLP for the narrow stages (C = 144, 288): out = x + fc2(GELU(fc1(LN(x)))) in one kernel per 128 rows.
+// Fused trunk MLP for stage 1 (C = 144): out = x + fc2(GELU(fc1(LN(x)))) in one kernel per 128 rows.
 // Reference: MLP.forward (sam2/modeling/sam2_utils.py:131-136) inside MultiScaleBlock.forward (backbones/hieradet.py:160-166),
 // with norm2 folded into fc1 as everywhere else in the trunk (weights.py: row-centred W diag(gamma), b + W beta).
 //
-// Why: in stages 1 and 2 (K = 144 / 288) the two MLP GEMMs are HBM bound: the 4C-wide hidden tensor is written by fc1 and read
-// back by fc2 (2.4 GB / 1.2 GB per block per 32 images, more than everything else in the block together).  Here the hidden
-// activations never leave the SM:
-//   for every 96-wide chunk h of the hidden layer
-//     S_b[128 x 96] = A[128 x C] W1[h]^T                  tcgen05.mma, A tile resident in shared memory, W1 streamed by TMA;
-//                                                         b = h & 1: two S buffers, chunk h + 1 is computed while
+// Why: in stage 1 (K = 144) the two MLP GEMMs are HBM bound: the 4C-wide hidden tensor is written by fc1 and read back by
+// fc2 (2.4 GB per block per 32 images, more than everything else in the block together).  Here the hidden activations never
+// leave the SM:
+//   for every 64-wide chunk h of the hidden layer (9 chunks)
+//     S_b[128 x 64] = A[128 x C] W1[h]^T                  tcgen05.mma, A tile resident in shared memory, W1 streamed by TMA;
+//                                                         b = h % 3: three S buffers, chunk h + 2 is computed while
 //     P             = bf16(GELU(rstd * S_b + b1[h]))       the GELU warps work on chunk h; P is written back over S_b's
-//                                                         columns as packed pairs, 32 columns at a time
+//                                                         first 32 columns as packed pairs
 //     O[128 x C]   += P W2[:, h]^T                         tcgen05.mma with the A operand (P) read from TENSOR MEMORY
 //   x_out = O + b2 + x; bf16 copy and per-row (sum, sum of squares) for the next block's folded LayerNorm
 // Per 128-row tile the kernel must move 128 x 12 C bytes through HBM (x in / out in fp32, the bf16 copies): 9.5k clocks of the
 // SM's share of the bus at C = 144, against 5.3k clocks of MMA issue and 5.5k of GELU arithmetic - so every role has its own
 // warps and nothing but tensor memory and mbarriers couples them:
 //   warp 0      TMA: A tile + W1 ring          warp 3      TMA: W2 ring
-//   warp 1      MMA issuer                     warp 2      TMEM allocation
+//   warp 1      MMA issuer (warp-uniform issue: elect.sync inside the asm keeps the descriptors in uniform registers)
+//   warp 2      TMEM allocation
 //   warps 4-11  GELU: group g = (warp - 4) / 4 takes the hidden chunks of parity g (lane quarter = warp & 3)
 //   warps 12-15 read-out: O -> + b2 + residual -> x (fp32, TMA store), bf16 copy, row statistics.  The residual rows arrive by
 //               TMA in [32 rows x 32 columns] boxes requested a whole tile ahead (a thread owns one ROW of tensor memory: plain
 //               loads of its row would be 64 B pieces with a DRAM round trip each, and 8 warps of them jam the load / store
 //               unit for the GELU warps' bias loads - measured, 37 % of all stall samples in the first version of this kernel)
-// TMEM: S 2 x 96 columns + O: two buffers of C columns at C = 144 (the read-out of tile t overlaps fc2 of tile t + 1), one at
-// C = 288 (480 columns either way).
+// TMEM: S 3 x 64 columns + two O buffers of C columns (the read-out of tile t overlaps fc2 of tile t + 1): 480 columns.
+// CTA pairs (CL = 2): both CTAs of a cluster walk the same chunk sequence, each loads HALF of every W1 / W2 block and
+// multicasts it to both - the weight traffic out of L2 halves.
+// C = 288 (stage 2) compiles in this design only with one O buffer and measured no faster than the GEMM pair (its hidden tensor is
+// a quarter of stage 1's per block): it is not instantiated, mlp_fused_supported() says so.
 #include <cuda.h>
 #include <cuda_runtime.h>
 
