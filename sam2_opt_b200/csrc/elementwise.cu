@@ -474,43 +474,4 @@ int softmax_rows(const float* s, long lds, bf16* p, long ldp, long rows, int col
   return 0;
 }
 
-// ------------------------------------------------------------------------------------------
-// RoPE + cast (reference: apply_rotary_emb, position_encoding_fix.py:192-205; RoPEAttention.forward
-// transformer.py:380-418: table repeats every 4096 rows, rows >= rope_rows are left un-rotated).
-// cos_t / sin_t: [4096,128] (angle of pair i at grid position r).
-// ------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) rope_cast_rows_kernel(const float* __restrict__ x, const float* __restrict__ cos_t,
-                                                             const float* __restrict__ sin_t, bf16* __restrict__ y, long rows, long rope_rows) {
-  // one thread per 2 pairs (4 floats): 64 threads per row
-  const long total = rows * 64;
-  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
-    const long r = i >> 6;
-    const int j = (int)(i & 63);
-    const float4 v = reinterpret_cast<const float4*>(x)[i];
-    float4 o = v;
-    if (r < rope_rows) {
-      const int pos = (int)(r & 4095);
-      const float2 c = reinterpret_cast<const float2*>(cos_t)[pos * 64 + j];
-      const float2 s = reinterpret_cast<const float2*>(sin_t)[pos * 64 + j];
-      o.x = v.x * c.x - v.y * s.x;
-      o.y = v.x * s.x + v.y * c.x;
-      o.z = v.z * c.y - v.w * s.y;
-      o.w = v.z * s.y + v.w * c.y;
-    }
-    uint2 pk;
-    pk.x = pack_bf16x2(o.x, o.y);
-    pk.y = pack_bf16x2(o.z, o.w);
-    reinterpret_cast<uint2*>(y)[i] = pk;
-  }
-}
-int rope_cast_rows(const float* x, const float* cos_t, const float* sin_t, bf16* y, long rows, long rope_rows, cudaStream_t stream) {
-  const long total = rows * 64;
-  long blocks = (total + 255) / 256;
-  if (blocks > (long)num_sms() * 16) blocks = (long)num_sms() * 16;
-  ProfRange pr(stream, "rope_cast", 0, (double)rows * 256 * 6.0);
-  rope_cast_rows_kernel<<<(unsigned)blocks, 256, 0, stream>>>(x, cos_t, sin_t, y, rows, rope_rows);
-  SAM2B_CHECK_LAUNCH("rope_cast_rows");
-  return 0;
-}
-
 }  // namespace sam2b

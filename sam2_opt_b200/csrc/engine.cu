@@ -278,8 +278,7 @@ static int finalize(sam2b_engine* e) {
       }
     }
   }
-  TRY(need(e, "derived.rope.cos", nullptr, false));            // [4096,128]
-  TRY(need(e, "derived.rope.sin", nullptr, false));
+  TRY(need(e, "derived.rope.cs", nullptr, false));             // [4096,256]: (cos, sin) interleaved per column pair
   CUDA_OK(cudaStreamSynchronize(0));
   e->finalized = true;
   return 0;
@@ -531,7 +530,7 @@ static int memory_attention_mb(sam2b_engine* e, const float* curr, const float* 
   const long Lk = (long)L * 4096 + P;
   const long Lkp = (Lk + 127) / 128 * 128;
   const long TT = (long)n * T;
-  float *X, *QK, *KC32, *OUT;
+  float *X, *OUT;
   bf16 *XN, *Qb, *Kb, *Vb, *KIN, *VIN, *Kc, *O, *O64, *HID;
   // per-object row counts on the device: [0][b] spatial keys, [1][b] pointer tokens, [2][b] keys in total
   int* ROWS = nullptr;
@@ -547,8 +546,6 @@ static int memory_attention_mb(sam2b_engine* e, const float* curr, const float* 
     CUDA_OK(cudaMemcpyAsync(ROWS, r.data(), r.size() * sizeof(int), cudaMemcpyHostToDevice, st));
   }
   TRY(ws_get_t(e, "ma_x", (size_t)TT * C, &X));
-  TRY(ws_get_t(e, "ma_qk", (size_t)TT * 512, &QK));
-  TRY(ws_get_t(e, "ma_kc32", (size_t)n * Lk * C, &KC32));
   TRY(ws_get_t(e, "ma_out", (size_t)TT * C, &OUT));
   TRY(ws_get_t(e, "ma_xn", (size_t)TT * C, &XN));
   TRY(ws_get_t(e, "ma_qb", (size_t)TT * C, &Qb));
@@ -560,8 +557,7 @@ static int memory_attention_mb(sam2b_engine* e, const float* curr, const float* 
   TRY(ws_get_t(e, "ma_o", (size_t)TT * C, &O));
   TRY(ws_get_t(e, "ma_o64", (size_t)TT * 64, &O64));
   TRY(ws_get_t(e, "ma_hid", (size_t)TT * 2048, &HID));
-  const float* cos_t = W32(e, "derived.rope.cos");
-  const float* sin_t = W32(e, "derived.rope.sin");
+  const float* rope_cs = W32(e, "derived.rope.cs");
 
   if (n == n_total) {
     TRY(memattn_prep_x(curr, curr_pos, X, T, n, C, st));
@@ -582,6 +578,18 @@ static int memory_attention_mb(sam2b_engine* e, const float* curr, const float* 
     return gemm_bf16(g, st);
   };
   // attention core (K4, attn_hd256.cu) on prepared operands: q [n][T][256], k / v [n][rows_alloc][256], `keys` valid rows
+  // projection + RoPE + bf16 cast in one GEMM (rotation in the epilogue, table rows = token position m % 4096):
+  // rows [w0, w0 + N) of the weight `wname`, A [batch][M][K], out [batch][M][N]; rows at or past rope_rows stay un-rotated
+  auto linear_rope = [&](const bf16* A, long a_batch_stride, int M, int batch, const std::string& wname, int w0, int K, bf16* o16,
+                         long c_batch_stride, int rope_rows, const int* rope_rows_dev) -> int {
+    GemmArgs g;
+    g.A = A; g.lda = K; g.a_batch_stride = a_batch_stride; g.M = M; g.K = K; g.batch = batch;
+    g.B = W16(e, wname + "weight") + (size_t)w0 * K; g.ldb = K; g.N = C;
+    g.bias = W32(e, wname + "bias") + w0;
+    g.out_bf16 = o16; g.ldc = C; g.c_batch_stride = c_batch_stride;
+    g.rope_table = rope_cs; g.rope_positions = 4096; g.rope_rows = rope_rows; g.rope_rows_dev = rope_rows_dev;
+    return gemm_bf16(g, st);
+  };
   auto attend = [&](const bf16* q, const bf16* k, const bf16* v, long rows_alloc, long keys) -> int {
     const int splits = flash_attention_hd256_splits(n, T, keys);
     float* part = nullptr;
@@ -603,26 +611,17 @@ static int memory_attention_mb(sam2b_engine* e, const float* curr, const float* 
     const std::string d = "derived.memattn." + std::to_string(l) + ".";
     // ---- self attention (RoPE on q and k) ----
     TRY(layernorm_rows(X, W32(e, p + "norm1.weight"), W32(e, p + "norm1.bias"), 1e-5f, XN, nullptr, TT, C, st));
-    TRY(linear(XN, C, (int)TT, d + "sa_qk.", 512, C, ACT_NONE, nullptr, QK, nullptr, 512));
-    TRY(rope_cast_batched(QK, 512, cos_t, sin_t, Qb, n, T, T, T, st));
-    TRY(rope_cast_batched(QK + 256, 512, cos_t, sin_t, Kb, n, T, T, T, st));
+    TRY(linear_rope(XN, (long)T * C, T, n, d + "sa_qk.", 0, C, Qb, (long)T * C, T, nullptr));       // q, rotated
+    TRY(linear_rope(XN, (long)T * C, T, n, d + "sa_qk.", 256, C, Kb, (long)T * C, T, nullptr));     // k, rotated
     TRY(linear(XN, C, (int)TT, p + "self_attn.v_proj.", C, C, ACT_NONE, nullptr, nullptr, Vb, C));
     TRY(attend(Qb, Kb, Vb, T, T));
     TRY(linear(O, C, (int)TT, p + "self_attn.out_proj.", C, C, ACT_NONE, X, X, nullptr, C));
     // ---- cross attention over the memory bank (RoPE on q and on the L*4096 spatial keys only) ----
     TRY(layernorm_rows(X, W32(e, p + "norm2.weight"), W32(e, p + "norm2.bias"), 1e-5f, XN, nullptr, TT, C, st));
-    TRY(linear(XN, C, (int)TT, p + "cross_attn_image.q_proj.", C, C, ACT_NONE, nullptr, QK, nullptr, C));
-    TRY(rope_cast_batched(QK, C, cos_t, sin_t, Qb, n, T, T, T, st));
-    {
-      GemmArgs g;   // k = k_proj(memory + pos): [n][Lk][256] fp32
-      g.A = KIN; g.lda = 64; g.a_batch_stride = Lkp * 64; g.M = (int)Lk; g.K = 64;
-      g.B = W16(e, p + "cross_attn_image.k_proj.weight"); g.ldb = 64; g.N = C;
-      g.batch = n;
-      g.bias = W32(e, p + "cross_attn_image.k_proj.bias");
-      g.out_f32 = KC32; g.ldc = C; g.c_batch_stride = Lk * C;
-      TRY(gemm_bf16(g, st));
-    }
-    TRY(rope_cast_batched(KC32, C, cos_t, sin_t, Kc, n, Lk, (long)L * 4096, Lkp, st, ROWS));
+    TRY(linear_rope(XN, (long)T * C, T, n, p + "cross_attn_image.q_proj.", 0, C, Qb, (long)T * C, T, nullptr));
+    // k = k_proj(memory + pos) over all Lkp rows of every object (the padding rows of KIN are zero: finite keys the attention
+    // kernel masks); only the spatial keys are rotated, the pointer tokens pass through
+    TRY(linear_rope(KIN, Lkp * 64, (int)Lkp, n, p + "cross_attn_image.k_proj.", 0, 64, Kc, Lkp * C, L * 4096, ROWS));
     TRY(attend_v64(Qb, Kc, VIN));
     // x += (softmax(q k^T / 16) memory) (Wo Wv)^T + (Wo bv + bo): v_proj and out_proj in one 64 -> 256 linear map
     TRY(linear(O64, 64, (int)TT, d + "ca_ov.", C, 64, ACT_NONE, X, X, nullptr, C));

@@ -51,6 +51,10 @@ struct GemmKernelParams {
   int act;
   const float* gamma;
   int has_res; int res_batched; int res_row_mod;
+  // RoPE epilogue (MODE_GENERIC, bf16 output): the "residual" boxes are (cos, sin) pairs of the rotation table
+  // [res_row_mod positions][256], column pair (2i, 2i + 1) of a row is rotated by its angle; rows (within a batch) at or past
+  // rope_rows (rope_rows_dev[b] when given) pass through un-rotated
+  int rope; int rope_rows; const int* rope_rows_dev;
   int out_is_bf16;
   // LayerNorm fold, consumer side: rows of A are raw (un-normalised); ln_stats [M][ln_parts][2] partial (sum, sum of squares)
   const float* ln_stats; int ln_parts; float ln_inv_c; float ln_eps;
@@ -216,8 +220,9 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid
     const bool ln_fold = !LNP && MODE != MODE_F32_BIAS_RES && p.ln_stats != nullptr;   // consumer of LayerNorm inputs
     const bool bias_n = GEN ? (p.bias != nullptr && !p.bias_along_m) : true;
     const int act = GEN ? p.act : (MODE == MODE_BF16_BIAS_GELU ? (int)ACT_GELU : (int)ACT_NONE);
-    const uint32_t buf_bytes = bf ? 2048u : 4096u;
-    const bool two_buf = bf || Cfg::EPI_F32_BYTES >= 8192;
+    const bool rope = GEN && p.rope != 0;                       // fp32 table boxes in, bf16 boxes out of the same staging buffer
+    const uint32_t buf_bytes = (bf && !rope) ? 2048u : 4096u;
+    const bool two_buf = (bf && !rope) || Cfg::EPI_F32_BYTES >= 8192;
     const uint32_t buf16 = smem_u32(smem_epi + we * WB) + Cfg::EPI_F32_BYTES;     // LNP: bf16 copy staging
     const uint32_t buf_base = smem_u32(smem_epi + we * WB);
     uint64_t* my_res_bar = res_bar + 2 * we;
@@ -239,8 +244,9 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid
       auto issue_res = [&](uint32_t ii, int c) {          // lane 0: residual chunk c -> staging buffer of chunk ii
         const uint32_t bsel = two_buf ? (ii & 1) : 0;
         mbar_arrive_expect_tx(&my_res_bar[bsel], 4096);
-        tma_load_3d_addr(buf_base + bsel * buf_bytes, &tma_r, &my_res_bar[bsel], n0 + c * 32, res_row, res_b);
+        tma_load_3d_addr(buf_base + bsel * buf_bytes, &tma_r, &my_res_bar[bsel], rope ? ((n0 + c * 32) & 255) : (n0 + c * 32), res_row, res_b);
       };
+      const int rope_limit = rope ? (p.rope_rows_dev ? __ldg(p.rope_rows_dev + b) : p.rope_rows) : 0;
       auto load_vec8 = [&](const float* base, int c, float fill, float4 (&o)[8]) {
         // 32 consecutive per-column values (bias / gamma), same addresses for every lane (L1 broadcast)
         const int col0 = n0 + c * 32;
@@ -366,10 +372,25 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid
           }
           if (has_res) {
             mbar_wait(&my_res_bar[bsel], (two_buf ? (i >> 1) : i) & 1);
+            if (rope) {
+              const bool rot = row_g + lane < rope_limit;
 #pragma unroll
-            for (int j = 0; j < 8; ++j) {
-              const float4 rv = ld_shared_f4(buf + row_f32 + (((uint32_t)j << 4) ^ xor_f32));
-              v[j].x += rv.x; v[j].y += rv.y; v[j].z += rv.z; v[j].w += rv.w;
+              for (int j = 0; j < 8; ++j) {
+                float4 cs = ld_shared_f4(buf + row_f32 + (((uint32_t)j << 4) ^ xor_f32));     // (cos, sin) of two column pairs
+                if (!rot) cs = make_float4(1.f, 0.f, 1.f, 0.f);
+                const float4 x = v[j];
+                v[j].x = x.x * cs.x - x.y * cs.y;
+                v[j].y = x.x * cs.y + x.y * cs.x;
+                v[j].z = x.z * cs.z - x.w * cs.w;
+                v[j].w = x.z * cs.w + x.w * cs.z;
+              }
+              __syncwarp();          // every lane has read its table row before the (narrower) bf16 rows overwrite the box
+            } else {
+#pragma unroll
+              for (int j = 0; j < 8; ++j) {
+                const float4 rv = ld_shared_f4(buf + row_f32 + (((uint32_t)j << 4) ^ xor_f32));
+                v[j].x += rv.x; v[j].y += rv.y; v[j].z += rv.z; v[j].w += rv.w;
+              }
             }
           }
           if (LNP) {
@@ -484,7 +505,9 @@ static int launch_gemm(const GemmArgs& a, cudaStream_t stream) {
   if (make_tmap_out(&tc, out_bf16 ? (const void*)a.out_bf16 : (const void*)a.out_f32, out_bf16, a.M, a.N, a.ldc, a.batch,
                     a.c_batch_stride)) return 1;
   const bool res_batched = a.residual && a.batch > 1 && a.res_batch_stride != 0;
-  if (a.residual) {
+  if (a.rope_table) {
+    if (make_tmap_out(&tr, a.rope_table, 0, a.rope_positions, 256, 256, 1, 0)) return 1;
+  } else if (a.residual) {
     const long res_rows = a.res_row_mod ? a.res_row_mod : a.M;
     if (make_tmap_out(&tr, a.residual, 0, res_rows, a.N, a.ld_res, res_batched ? a.batch : 1, a.res_batch_stride)) return 1;
   } else {
@@ -503,6 +526,11 @@ static int launch_gemm(const GemmArgs& a, cudaStream_t stream) {
   p.b_batched = b_batched ? 1 : 0;
   p.alpha = a.alpha; p.bias = a.bias; p.bias_along_m = a.bias_along_m; p.act = a.act; p.gamma = a.gamma;
   p.has_res = a.residual ? 1 : 0; p.res_batched = res_batched ? 1 : 0; p.res_row_mod = a.res_row_mod;
+  p.rope = 0; p.rope_rows = 0; p.rope_rows_dev = nullptr;
+  if (a.rope_table) {
+    p.has_res = 1; p.res_batched = 0; p.res_row_mod = a.rope_positions;
+    p.rope = 1; p.rope_rows = a.rope_rows; p.rope_rows_dev = a.rope_rows_dev;
+  }
   p.out_is_bf16 = out_bf16;
   p.ln_stats = a.ln_stats; p.ln_parts = a.ln_parts; p.ln_inv_c = a.ln_stats ? 1.0f / (float)a.K : 0.f; p.ln_eps = a.ln_eps;
   p.stats_out = a.stats_out;
@@ -510,7 +538,7 @@ static int launch_gemm(const GemmArgs& a, cudaStream_t stream) {
   const long tiles = (long)p.tiles_m * p.tiles_n * p.batch;
   const int grid = (int)(tiles < max_pairs ? tiles : max_pairs) * NCTA;
   char nm[96];
-  if (g_prof_on) snprintf(nm, sizeof(nm), "gemm m%d n%d k%d b%d bn%d%s%s md%d act%d%s%s%s", a.M, a.N, a.K, a.batch, BN, NCTA == 2 ? "x2" : "", EW == 16 ? "w16" : "", MODE, a.act, a.residual ? " res" : "", a.out_bf16 ? " o16" : " o32", a.ln_stats ? " ln" : "");
+  if (g_prof_on) snprintf(nm, sizeof(nm), "gemm m%d n%d k%d b%d bn%d%s%s md%d act%d%s%s%s", a.M, a.N, a.K, a.batch, BN, NCTA == 2 ? "x2" : "", EW == 16 ? "w16" : "", MODE, a.act, a.residual ? " res" : (a.rope_table ? " rope" : ""), a.out_bf16 ? " o16" : " o32", a.ln_stats ? " ln" : "");
   const double esz = a.out_bf16 ? 2.0 : 4.0;
   ProfRange pr(stream, nm, 2.0 * a.M * a.N * (double)a.K * a.batch,
                ((double)a.M * a.K * 2 + (b_batched ? 1.0 : 1.0 / a.batch) * (double)a.N * a.K * 2 + (double)a.M * a.N * (esz + (a.residual ? 4.0 : 0.0))) * a.batch);

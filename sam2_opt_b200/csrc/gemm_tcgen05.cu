@@ -135,6 +135,10 @@ int gemm_bf16(const GemmArgs& a, cudaStream_t stream) {
     set_error("gemm: res_row_mod=%d must be a multiple of %d", a.res_row_mod, BM);
     return 1;
   }
+  if (a.rope_table && (a.residual || !a.out_bf16 || a.N % 256 || a.rope_positions <= 0 || a.rope_positions % (2 * BM) || a.ln_stats || a.out2_bf16)) {
+    set_error("gemm: the RoPE epilogue needs a bf16 output, N %% 256 == 0, no residual, a table of a multiple of %d positions", 2 * BM);
+    return 1;
+  }
   int bn = 0, cta2 = 0, ew16 = 0;
   if (a.force_bn) {     // tests / tuning: BLOCK_N + 1000 (CTA pairs) + 2000 (16 epilogue warps)
     bn = a.force_bn % 1000; cta2 = (a.force_bn / 1000) & 1; ew16 = (a.force_bn / 2000) & 1;
@@ -146,7 +150,7 @@ int gemm_bf16(const GemmArgs& a, cudaStream_t stream) {
   if (cta2 && (bn < 128 || (a.res_row_mod && a.res_row_mod % (2 * BM)))) { set_error("gemm: CTA pairs need BLOCK_N >= 128 and res_row_mod %% 256 == 0"); return 1; }
   // compile-time specialised epilogues for the trunk's three dominant GEMM forms (fewer instructions per element)
   int mode = MODE_GENERIC;
-  const bool plain = a.alpha == 1.0f && a.bias && !a.bias_along_m && !a.gamma && (a.N % 4) == 0 && !getenv("SAM2B_GEMM_GENERIC");
+  const bool plain = a.alpha == 1.0f && a.bias && !a.bias_along_m && !a.gamma && (a.N % 4) == 0 && !a.rope_table && !getenv("SAM2B_GEMM_GENERIC");
   if (plain && a.out_bf16 && !a.residual && a.act == ACT_NONE) mode = MODE_BF16_BIAS;
   else if (plain && a.out_bf16 && !a.residual && a.act == ACT_GELU) mode = MODE_BF16_BIAS_GELU;
   else if (plain && a.out_f32 && a.residual && a.act == ACT_NONE) mode = a.out2_bf16 ? MODE_F32_BIAS_RES_LN : MODE_F32_BIAS_RES;

@@ -91,47 +91,4 @@ int memattn_prep_memory(const float* memory, const float* memory_pos, int L, con
   return 0;
 }
 
-__global__ void __launch_bounds__(256) rope_cast_batched_kernel(const float* __restrict__ x, long ldx, const float2* __restrict__ cos_t,
-                                                                const float2* __restrict__ sin_t, uint2* __restrict__ y, int batch,
-                                                                long rows_per_batch, long rope_rows_all, long rows_out,
-                                                                const int* __restrict__ rope_rows_dev) {
-  const long total = (long)batch * rows_out * 64;   // one thread per 2 pairs (4 values)
-  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
-    const int j = (int)(i & 63);
-    const long rr = i >> 6;
-    const int b = (int)(rr / rows_out);
-    const long r = rr - (long)b * rows_out;
-    float4 o = make_float4(0.f, 0.f, 0.f, 0.f);
-    const long rope_rows = rope_rows_dev ? (long)rope_rows_dev[b] : rope_rows_all;
-    if (r < rows_per_batch) {
-      const float4 v = *reinterpret_cast<const float4*>(x + ((long)b * rows_per_batch + r) * ldx + j * 4);
-      o = v;
-      if (r < rope_rows) {
-        const int pos = (int)(r & 4095);
-        const float2 c = cos_t[pos * 64 + j], s = sin_t[pos * 64 + j];
-        o.x = v.x * c.x - v.y * s.x;
-        o.y = v.x * s.x + v.y * c.x;
-        o.z = v.z * c.y - v.w * s.y;
-        o.w = v.z * s.y + v.w * c.y;
-      }
-    }
-    uint2 pk;
-    pk.x = pack_bf16x2(o.x, o.y);
-    pk.y = pack_bf16x2(o.z, o.w);
-    y[i] = pk;
-  }
-}
-int rope_cast_batched(const float* x, long ldx, const float* cos_t, const float* sin_t, bf16* y, int batch, long rows_per_batch,
-                      long rope_rows, long rows_out, cudaStream_t stream, const int* rope_rows_dev) {
-  if (ldx % 4) { set_error("rope_cast_batched: ldx=%ld", ldx); return 1; }
-  const long total = (long)batch * rows_out * 64;
-  long blocks = (total + 255) / 256;
-  if (blocks > (long)num_sms() * 16) blocks = (long)num_sms() * 16;
-  ProfRange pr(stream, "rope_cast", 0, (double)total * 24.0);
-  rope_cast_batched_kernel<<<(unsigned)blocks, 256, 0, stream>>>(x, ldx, reinterpret_cast<const float2*>(cos_t), reinterpret_cast<const float2*>(sin_t),
-                                                                reinterpret_cast<uint2*>(y), batch, rows_per_batch, rope_rows, rows_out, rope_rows_dev);
-  SAM2B_CHECK_LAUNCH("rope_cast_batched");
-  return 0;
-}
-
 }  // namespace sam2b

@@ -63,6 +63,9 @@ struct GemmArgs {
   int act = ACT_NONE;
   const float* gamma = nullptr;
   const float* residual = nullptr; long ld_res = 0; long res_batch_stride = 0; int res_row_mod = 0;
+  // RoPE in the epilogue (bf16 output, N % 256 == 0): rope_table [rope_positions][256] holds (cos, sin) of column pair i at
+  // columns (2i, 2i + 1); row m of a batch is rotated by position m % rope_positions if m < rope_rows (rope_rows_dev[b] when given)
+  const float* rope_table = nullptr; int rope_positions = 0; int rope_rows = 0; const int* rope_rows_dev = nullptr;
   float* out_f32 = nullptr; bf16* out_bf16 = nullptr; long ldc = 0; long c_batch_stride = 0;
   int force_bn = 0;  // 0 = pick automatically; 1000 + BLOCK_N forces CTA pairs
   // ---- LayerNorm fold (see GemmMode in gemm_kernel.cuh) ----
@@ -139,11 +142,6 @@ bool mlp_fused_supported(int C);
 int mlp_fused(const bf16* xb, const float* stats_in, int parts_in, float eps, const bf16* w1, const float* b1, const bf16* w2,
               const float* b2, float* x, bf16* xb_out, float* stats_out, long M, int C, cudaStream_t stream);
 
-// Axial RoPE (interleaved pairs) applied in place on x [rows, 256] fp32->bf16 conversion included:
-// y_bf16[r] = rope(x[r]) with table row (r % 4096) when r < rope_rows, else plain cast.
-int rope_cast_rows(const float* x, const float* cos_t, const float* sin_t, bf16* y, long rows, long rope_rows,
-                   cudaStream_t stream);
-
 }  // namespace sam2b
 
 namespace sam2b {
@@ -158,12 +156,6 @@ int batch_to_seq(const float* x, float* out, int T, int n, int C, cudaStream_t s
 // P for all); object b then uses memory[0 .. L_b) and excl[0 .. P_b), packed back to back, zero rows behind.
 int memattn_prep_memory(const float* memory, const float* memory_pos, int L, const float* excl, const float* pos_excl,
                         int P, int n, const int* rows, bf16* kin, bf16* vin, long ldk, cudaStream_t stream);
-// Batch-aware RoPE + cast: x fp32 [batch][rows_per_batch][ldx] (first 256 columns of each row) -> y bf16
-// [batch][rows_out_per_batch][256]; rows r < rope_rows of each batch are rotated with table row (r % 4096).
-// rope_rows_dev: optional DEVICE array [batch] overriding rope_rows per batch entry.
-int rope_cast_batched(const float* x, long ldx, const float* cos_t, const float* sin_t, bf16* y, int batch,
-                      long rows_per_batch, long rope_rows, long rows_out_per_batch, cudaStream_t stream,
-                      const int* rope_rows_dev = nullptr);
 }  // namespace sam2b
 
 namespace sam2b {

@@ -116,5 +116,6 @@ def derive(w: Dict[str, torch.Tensor]) -> Dict[str, torch.Tensor]:
             d[f"derived.blocks.{i}.{short}.bias"] = (bias + W @ beta).float().contiguous()
         i += 1
     cos, sin = rope_tables(dev)
-    d["derived.rope.cos"], d["derived.rope.sin"] = cos, sin
+    # (cos, sin) of column pair i at columns (2i, 2i + 1): the layout the GEMM's RoPE epilogue reads as 32 x 32 boxes
+    d["derived.rope.cs"] = torch.stack([cos, sin], -1).reshape(cos.shape[0], -1).contiguous()
     return d
