@@ -2,7 +2,7 @@
 """Dev tool (not a test): two launches of each dominant kernel on its real shape at BATCH 32 (the bench configuration), for
 an `ncu --set full` capture of the second (warm) one.  Order: attn.proj and fc2 (LayerNorm producers: fp32 + residual + bf16
 copy + row statistics), qkv (LayerNorm-fold consumer), fc1 (consumer + GELU); hd72 attention 16x16 windows and global; 8x8
-small-window kernel; hd256 attention (28 736 keys).
+small-window kernel; hd256 attention (28 736 keys); hd256 / 64-wide-value cross-attention (16 objects).
 
     ncu --set full --clock-control none --import-source on -k regex:'gemm_bf16|flash_attn|window_attn' -o gpurun_out/r2_top python tools/ncu_top_kernels.py
 """
@@ -55,5 +55,12 @@ k = rnd(1, 28736, 256).bfloat16()
 v = rnd(1, 28736, 256).bfloat16()
 for _ in range(2):
     ops.attention_hd256(q, k, v)
+torch.cuda.synchronize()
+# cross-attention of the memory attention, 16 objects: 64-wide values (v_proj folded behind P V)
+q = rnd(16, 4096, 256).bfloat16()
+k = rnd(16, 28800, 256).bfloat16()
+v = rnd(16, 28800, 64).bfloat16()
+for _ in range(2):
+    ops.attention_hd256_v64(q, k, v)
 torch.cuda.synchronize()
 print("ok")
