@@ -154,6 +154,16 @@ int sam2b_op_preprocess_u8(const void* hwc_u8, float* out_nchw, int n, int h, in
 int64_t sam2b_op_resize_frames_workspace(int n, int h, int w, int out_h, int out_w);
 int sam2b_op_resize_frames(const void* src, int src_is_u8_hwc, int n, int h, int w, float* out_nchw, int out_h, int out_w,
                            int normalise, void* workspace, void* stream);
+/* Allocation-free variant of sam2b_op_resize_frames.  No counterpart in the reference: added
+ * for callers that cannot allocate (CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc).
+ * Same arguments and results, but the workspace is a static device array of SAM2B_RESIZE_STATIC_MAX_BYTES inside the library
+ * (held by every GPU that loads it, until exit); the call allocates nothing.  Problems whose
+ * sam2b_op_resize_frames_workspace(...) exceeds that size are rejected with an error (16 MiB covers one 1920 x 1080 frame
+ * -> 1024 x 1024).  All calls on a device share the array: calls that overlap on the GPU (different streams) race; calls
+ * on one stream are ordered.  The array keeps the previous call's contents, every call rewrites what it reads. */
+#define SAM2B_RESIZE_STATIC_MAX_BYTES (16u << 20)
+int sam2b_op_resize_frames_static(const void* src, int src_is_u8_hwc, int n, int h, int w, float* out_nchw, int out_h,
+                                  int out_w, int normalise, void* stream);
 /* Post-processing of predicted masks (replaces the F.interpolate of SAM2Transforms.postprocess_masks, sam2/utils/transforms.py:119,
  * and the `masks > mask_threshold` that follows it, sam2_image_predictor.py:300-302 / the video predictor's `video_res_masks > 0`):
  * low dev fp32 [n][h][w] mask logits -> out dev fp32 [n][out_h][out_w] (bilinear, align_corners = False; may be NULL) and

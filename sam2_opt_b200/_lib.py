@@ -43,6 +43,7 @@ SIGNATURES = {
     "sam2b_op_preprocess_u8": (_i, [_vp, _vp, _i, _i, _i, _i, _vp]),
     "sam2b_op_resize_frames_workspace": (_i64, [_i, _i, _i, _i, _i]),
     "sam2b_op_resize_frames": (_i, [_vp, _i, _i, _i, _i, _vp, _i, _i, _i, _vp, _vp]),
+    "sam2b_op_resize_frames_static": (_i, [_vp, _i, _i, _i, _i, _vp, _i, _i, _i, _vp]),
     "sam2b_op_upsample_masks": (_i, [_vp, _vp, _vp, _i64, _i, _i, _i, _i, _f, _vp]),
     "sam2b_op_softmax_rows": (_i, [_vp, _i64, _vp, _i64, _i64, _i, _vp]),
     "sam2b_op_attention_hd256_workspace": (_i64, [_i, _i, _i64]),

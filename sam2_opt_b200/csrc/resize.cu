@@ -188,3 +188,61 @@ int resize_frames(const void* src, int src_is_u8_hwc, int n, int h, int w, float
 }
 
 }  // namespace sam2b
+
+// ------------------------------------------------------------------------------------------------------------
+// Allocation-free variant (no counterpart in the reference): the same three
+// launches as resize_frames() with the workspace in a file-scope device array instead of caller memory, for callers that
+// cannot allocate (CUDA graph capture, serving loops, harnesses that forbid cudaMalloc).  Every GPU that loads the
+// library holds the array until the process exits.  All calls on a device share it: calls that overlap on the GPU (two
+// streams) race on it; calls on one stream are ordered.  Nothing in it has to start at zero - every call rewrites all it
+// reads (tap tables, then the intermediate) - so the contents left by the previous call are harmless.
+// ------------------------------------------------------------------------------------------------------------
+#include <mutex>
+
+#include "../../include/sam2b.h"
+
+namespace {
+static __device__ __align__(256) unsigned char g_resize_scratch[SAM2B_RESIZE_STATIC_MAX_BYTES];
+
+// The array's name is a host-side stand-in in host code: the device address is looked up once per device, with that
+// device current, and cached.
+int resize_scratch_address(void** out) {
+  static std::mutex mu;
+  static void* addr[64] = {};
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess || dev < 0 || dev >= 64) {
+    sam2b::set_error("sam2b_op_resize_frames_static: cudaGetDevice: %s (device %d)", cudaGetErrorString(e), dev);
+    return 1;
+  }
+  std::lock_guard<std::mutex> lock(mu);
+  if (!addr[dev]) {
+    void* p = nullptr;
+    e = cudaGetSymbolAddress(&p, g_resize_scratch);
+    if (e != cudaSuccess || !p) {
+      sam2b::set_error("sam2b_op_resize_frames_static: cudaGetSymbolAddress: %s", cudaGetErrorString(e));
+      return 1;
+    }
+    addr[dev] = p;
+  }
+  *out = addr[dev];
+  return 0;
+}
+}  // namespace
+
+extern "C" int sam2b_op_resize_frames_static(const void* src, int src_is_u8_hwc, int n, int h, int w, float* out_nchw, int out_h,
+                                             int out_w, int normalise, void* stream) {
+  const long need = sam2b::resize_frames_workspace(n, h, w, out_h, out_w);
+  if (need <= 0) {
+    sam2b::set_error("sam2b_op_resize_frames_static: bad sizes (n=%d h=%d w=%d out=%dx%d)", n, h, w, out_h, out_w);
+    return 1;
+  }
+  if (need > (long)SAM2B_RESIZE_STATIC_MAX_BYTES) {
+    sam2b::set_error("sam2b_op_resize_frames_static: n=%d frames of %dx%d -> %dx%d need %ld bytes of scratch, the static array holds %ld; "
+                     "use sam2b_op_resize_frames with a caller workspace", n, h, w, out_h, out_w, need, (long)SAM2B_RESIZE_STATIC_MAX_BYTES);
+    return 1;
+  }
+  void* scratch = nullptr;
+  if (resize_scratch_address(&scratch)) return 1;
+  return sam2b::resize_frames(src, src_is_u8_hwc, n, h, w, out_nchw, out_h, out_w, normalise, scratch, reinterpret_cast<cudaStream_t>(stream));
+}
