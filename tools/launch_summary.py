@@ -18,7 +18,7 @@ for r in csv.DictReader(lines):
     if r.get("Metric Name") != "gpu__time_duration.sum":
         continue
     rows.append((r["Kernel Name"], float(r["Metric Value"].replace(",", "")) * (1e-6 if r["Metric Unit"] in ("ns", "nsecond") else 1e-3)))
-OURS = re.compile(r"sam2b::|gemm_bf16_tcgen05|flash_attn|window_attn|mlp_fused")
+OURS = re.compile(r"sam2b::|gemm_bf16_tcgen05|flash_attn|window_attn|mlp_fused|patch_im2col|maxpool2x2|upsample2x_add")
 starts = [i for i, (k, _) in enumerate(rows) if "patch_im2col_kernel" in k]
 if len(starts) < 4:
     sys.exit(f"only {len(starts)} encoder steps in {path}")
