@@ -60,6 +60,7 @@ struct FaParams {
   int rows_per_tile;   // grid rows covered by one 128-token tile = 128 / ws
   int num_units;
   float scale_log2;
+  int pingpong;        // the two soft-max warpgroups take turns in their exponential phase (see the exp loop)
   long long* trace;    // development only (SAM2B_ATTN_TRACE): [role][256] pairs (event code, SM clock) written by CTA 0
 };
 #define FA_TR(role, code)                                                                                   \
@@ -255,6 +256,7 @@ flash_attn_hd72_tcgen05_kernel(const __grid_constant__ CUtensorMap map_lo, const
     uint32_t n = 0;                           // KV tiles processed by this warpgroup (all units): phase of s_full[t]
     uint32_t n_pv = 0;                        // P V completions observed on o_full[t] (in order)
     bool stores_pending = false;
+    if (p.pingpong && t == 1) named_bar_arrive(3, 256);       // warpgroup 0 takes the first turn
     for (int u = blockIdx.x; u < p.num_units; u += gridDim.x) {
       const UnitCoord c = unit_coord(p, u);
       float m_run = -INFINITY, l_run = 0.f;
@@ -327,6 +329,12 @@ flash_attn_hd72_tcgen05_kernel(const __grid_constant__ CUtensorMap map_lo, const
           named_bar_sync(1 + t, 128);
           stores_pending = false;
         }
+        // Turn-taking on the special-function unit: the exponentials of a tile keep MUFU busy for 1 024 clocks when one warpgroup
+        // has it alone and for 2 048 when both are in this loop at once - and both arrive here together (their score tiles are
+        // issued back to back), after which both do their MUFU-free work (S wait, tcgen05.ld, row maximum, rescale) together
+        // too.  Strict alternation (warpgroup 0 first; same number of tiles on both sides, so it cannot deadlock) puts one
+        // warpgroup's MUFU-free phase under the other one's exponentials.
+        if (p.pingpong) named_bar_sync(3 + t, 256);
         // P = exp2(S * scale - m) -> bf16 -> swizzled K-major smem tile; fp32 row sum
         // packed fp32 pairs: one FFMA2 (scale, minus max) and one FADD2 (row sum) per two keys
         const uint64_t sc2 = f2_pack(p.scale_log2, p.scale_log2), nm2 = f2_pack(-m_run, -m_run);
@@ -348,6 +356,7 @@ flash_attn_hd72_tcgen05_kernel(const __grid_constant__ CUtensorMap map_lo, const
           for (int i = 0; i < 4; ++i)
             st_shared_u4(base + (((uint32_t)((ch & 1) * 4 + i) << 4) ^ p_xor), pk[4 * i], pk[4 * i + 1], pk[4 * i + 2], pk[4 * i + 3]);
         }
+        if (p.pingpong) named_bar_arrive(3 + (t ^ 1), 256);
         float rs0, rs1;
         f2_unpack(f2_add(rs2a, rs2b), rs0, rs1);
         l_run = fmaf(l_run, corr, rs0 + rs1);
@@ -480,6 +489,7 @@ int flash_attention_hd72(const bf16* qkv, bf16* out, int B, int H, int W, int he
   p.nwx = W / ws;
   p.num_units = B * heads * p.blocks_per_img;
   p.scale_log2 = 1.4426950408889634f / sqrtf((float)HD);
+  { static int pp = -1; if (pp < 0) { const char* e = getenv("SAM2B_ATTN_PINGPONG"); pp = e ? atoi(e) : 1; } p.pingpong = pp; }
   p.trace = nullptr;
   static long long* trace_dev = nullptr;
   const bool tracing = getenv("SAM2B_ATTN_TRACE") != nullptr;

@@ -93,6 +93,7 @@ SAM2B_DEVINL void tma_store_5d(const CUtensorMap* map, uint32_t smem_src, int c0
 }
 // named barrier among `count` threads (ids 1..15; 0 is __syncthreads)
 SAM2B_DEVINL void named_bar_sync(int id, int count) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(count) : "memory"); }
+SAM2B_DEVINL void named_bar_arrive(int id, int count) { asm volatile("bar.arrive %0, %1;" ::"r"(id), "r"(count) : "memory"); }
 SAM2B_DEVINL void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
 template <int N>
 SAM2B_DEVINL void bulk_wait_read() { asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory"); }

@@ -261,6 +261,7 @@ static int finalize(sam2b_engine* e) {
       TRY(need(e, en + std::to_string(3 * j + 1) + ".bias", nullptr, false));
     }
     TRY(need(e, "derived.memenc.ds4.weight", nullptr, true));   // [256, (ky,kx,cin)=576]
+    TRY(need(e, "derived.memenc.ds3.weight", nullptr, true));   // [64, (ky,kx,cin)=144]
     for (const char* c : {"mask_downsampler.encoder.12.", "pix_feat_proj.", "out_proj."}) {
       TRY(need(e, m + c + "weight", nullptr, true));
       TRY(need(e, m + c + "bias", nullptr, false));
@@ -642,7 +643,7 @@ static int memory_attention_mb(sam2b_engine* e, const float* curr, const float* 
 static int memory_encode_mb(sam2b_engine* e, const float* pix_feat, const float* masks, int n, float* out_x, cudaStream_t st) {
   const long T = 4096L * n;
   float *D1, *D2, *D3, *D4, *MDS, *X;
-  bf16 *COLS, *D4N, *PIXT, *XN, *HID, *XB;
+  bf16 *COLS, *D3B, *D4N, *PIXT, *XN, *HID, *XB;
   TRY(ws_get_t(e, "me_d1", (size_t)n * 512 * 512 * 4, &D1));
   TRY(ws_get_t(e, "me_d2", (size_t)n * 256 * 256 * 16, &D2));
   TRY(ws_get_t(e, "me_d3", (size_t)n * 128 * 128 * 64, &D3));
@@ -650,6 +651,7 @@ static int memory_encode_mb(sam2b_engine* e, const float* pix_feat, const float*
   TRY(ws_get_t(e, "me_mds", (size_t)T * 256, &MDS));
   TRY(ws_get_t(e, "me_x", (size_t)T * 256, &X));
   TRY(ws_get_t(e, "me_cols", (size_t)T * 576, &COLS));
+  TRY(ws_get_t(e, "me_d3b", (size_t)n * 128 * 128 * 64, &D3B));
   TRY(ws_get_t(e, "me_d4n", (size_t)T * 256, &D4N));
   TRY(ws_get_t(e, "me_pixt", (size_t)T * 256, &PIXT));
   TRY(ws_get_t(e, "me_xn", (size_t)T * 256, &XN));
@@ -657,37 +659,42 @@ static int memory_encode_mb(sam2b_engine* e, const float* pix_feat, const float*
   TRY(ws_get_t(e, "me_xb", (size_t)T * 256, &XB));
   const std::string m = "memory_encoder.", en = m + "mask_downsampler.encoder.";
   auto P = [&](const std::string& name) { return W32(e, name); };
-  float* stage_out[3] = {D1, D2, D3};
+  float* stage_out[2] = {D1, D2};
   const float* stage_in = masks;
   int H = 1024;
-  for (int j = 0; j < 3; ++j) {
+  for (int j = 0; j < 2; ++j) {       // 1 -> 4 -> 16 channels: a few taps per output, fp32 FMA kernels (HBM bound)
     const std::string c = en + std::to_string(3 * j) + ".", l = en + std::to_string(3 * j + 1) + ".";
     TRY(mask_ds_stage(j + 1, stage_in, stage_out[j], n, H, P(c + "weight"), P(c + "bias"), P(l + "weight"), P(l + "bias"), st));
     stage_in = stage_out[j];
     H /= 2;
   }
-  TRY(im2col3x3s2_nhwc(D3, COLS, n, 128, 64, st));
-  auto linear = [&](const bf16* A, int K, const bf16* Wt, const float* bias, int N, int act, const float* gamma,
+  auto linear = [&](const bf16* A, long M, int K, const bf16* Wt, const float* bias, int N, int act, const float* gamma,
                     const float* residual, float* o32, bf16* o16) -> int {
     GemmArgs g;
-    g.A = A; g.lda = K; g.M = (int)T; g.K = K;
+    g.A = A; g.lda = K; g.M = (int)M; g.K = K;
     g.B = Wt; g.ldb = K; g.N = N;
     g.bias = bias; g.act = act; g.gamma = gamma;
     g.residual = residual; g.ld_res = N;
     g.out_f32 = o32; g.out_bf16 = o16; g.ldc = N;
     return gemm_bf16(g, st);
   };
-  TRY(linear(COLS, 576, W16(e, "derived.memenc.ds4.weight"), P(en + "9.bias"), 256, ACT_NONE, nullptr, nullptr, D4, nullptr));
+  // 16 -> 64 and 64 -> 256 channels: dense contractions over (3 x 3 x C_in) = 144 / 576 -> im2col + tcgen05 GEMM + LN2d + GELU
+  // (the 16 -> 64 stage as a direct fp32 FMA kernel ran at 8 TFLOP/s: 0.59 ms per frame at 16 objects)
+  TRY(im2col3x3s2_nhwc(D2, COLS, n, 256, 16, st));
+  TRY(linear(COLS, 16384L * n, 144, W16(e, "derived.memenc.ds3.weight"), P(en + "6.bias"), 64, ACT_NONE, nullptr, nullptr, D3, nullptr));
+  TRY(layernorm_gelu_rows(D3, P(en + "7.weight"), P(en + "7.bias"), 1e-6f, D3B, 16384L * n, 64, st));
+  TRY(im2col3x3s2_nhwc_bf16(D3B, COLS, n, 128, 64, st));
+  TRY(linear(COLS, T, 576, W16(e, "derived.memenc.ds4.weight"), P(en + "9.bias"), 256, ACT_NONE, nullptr, nullptr, D4, nullptr));
   TRY(layernorm_gelu_rows(D4, P(en + "10.weight"), P(en + "10.bias"), 1e-6f, D4N, T, 256, st));
-  TRY(linear(D4N, 256, W16(e, en + "12.weight"), P(en + "12.bias"), 256, ACT_NONE, nullptr, nullptr, MDS, nullptr));
+  TRY(linear(D4N, T, 256, W16(e, en + "12.weight"), P(en + "12.bias"), 256, ACT_NONE, nullptr, nullptr, MDS, nullptr));
   TRY(nchw_to_nhwc_bf16(pix_feat, PIXT, n, 256, 4096, st));
-  TRY(linear(PIXT, 256, W16(e, m + "pix_feat_proj.weight"), P(m + "pix_feat_proj.bias"), 256, ACT_NONE, nullptr, MDS, X, nullptr));
+  TRY(linear(PIXT, T, 256, W16(e, m + "pix_feat_proj.weight"), P(m + "pix_feat_proj.bias"), 256, ACT_NONE, nullptr, MDS, X, nullptr));
   for (int l = 0; l < 2; ++l) {
     const std::string f = m + "fuser.layers." + std::to_string(l) + ".";
     TRY(dwconv7_ln_nhwc(X, XN, n, 64, P("derived.memenc.fuser." + std::to_string(l) + ".dw.weight"), P(f + "dwconv.bias"),
                         P(f + "norm.weight"), P(f + "norm.bias"), st));
-    TRY(linear(XN, 256, W16(e, f + "pwconv1.weight"), P(f + "pwconv1.bias"), 1024, ACT_GELU, nullptr, nullptr, nullptr, HID));
-    TRY(linear(HID, 1024, W16(e, f + "pwconv2.weight"), P(f + "pwconv2.bias"), 256, ACT_NONE, P(f + "gamma"), X, X, nullptr));
+    TRY(linear(XN, T, 256, W16(e, f + "pwconv1.weight"), P(f + "pwconv1.bias"), 1024, ACT_GELU, nullptr, nullptr, nullptr, HID));
+    TRY(linear(HID, T, 1024, W16(e, f + "pwconv2.weight"), P(f + "pwconv2.bias"), 256, ACT_NONE, P(f + "gamma"), X, X, nullptr));
   }
   TRY(cast_f32_bf16(X, XB, T * 256, st));
   {

@@ -153,78 +153,7 @@ __global__ void __launch_bounds__(128) mask_ds2_kernel(const float4* __restrict_
   }
 }
 
-// stage 3: 16 -> 64 channels, NHWC in, 4 threads per output pixel (16 output channels each)
-__global__ void __launch_bounds__(256) mask_ds3_kernel(const float4* __restrict__ in, float4* __restrict__ out, int n, int H,
-                                                       const float* __restrict__ w, const float* __restrict__ b,
-                                                       const float* __restrict__ ln_w, const float* __restrict__ ln_b) {
-  extern __shared__ __align__(16) float smem3[];
-  float* sw = smem3;                 // [tap][cin 16][cout 64]
-  float* sp = smem3 + 9 * 16 * 64;   // bias, ln_w, ln_b (64 each)
-  for (int i = threadIdx.x; i < 9216; i += blockDim.x) {
-    const int co = i / 144, r = i % 144, ci = r / 9, tap = r % 9;
-    sw[(tap * 16 + ci) * 64 + co] = w[i];
-  }
-  if (threadIdx.x < 64) { sp[threadIdx.x] = b[threadIdx.x]; sp[64 + threadIdx.x] = ln_w[threadIdx.x]; sp[128 + threadIdx.x] = ln_b[threadIdx.x]; }
-  __syncthreads();
-  const int Ho = H >> 1;
-  const long total = (long)n * Ho * Ho * 4;
-  const long stride = (long)gridDim.x * blockDim.x;     // multiple of 4: quads stay together
-  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < ((total + stride - 1) / stride) * stride; i += stride) {
-    const bool ok = i < total;
-    const long pix = ok ? (i >> 2) : 0;
-    const int part = (int)(i & 3);
-    const int ox = (int)(pix % Ho);
-    const int oy = (int)((pix / Ho) % Ho);
-    const long img = pix / ((long)Ho * Ho);
-    float o[16];
-#pragma unroll
-    for (int c = 0; c < 16; ++c) o[c] = sp[part * 16 + c];
-    for (int ky = 0; ky < 3; ++ky) {
-      const int y = 2 * oy - 1 + ky;
-      if (y < 0 || y >= H) continue;
-      for (int kx = 0; kx < 3; ++kx) {
-        const int x = 2 * ox - 1 + kx;
-        if (x < 0 || x >= H) continue;
-        const float4* src = in + ((img * H + y) * H + x) * 4;
-        const float* wt = sw + (ky * 3 + kx) * 16 * 64 + part * 16;
-#pragma unroll
-        for (int c4 = 0; c4 < 4; ++c4) {
-          const float4 v = __ldg(src + c4);
-          const float vv[4] = {v.x, v.y, v.z, v.w};
-#pragma unroll
-          for (int e = 0; e < 4; ++e) {
-            const float4* wr = reinterpret_cast<const float4*>(wt + (c4 * 4 + e) * 64);
-#pragma unroll
-            for (int g = 0; g < 4; ++g) {
-              const float4 ww = wr[g];
-              o[4 * g + 0] = fmaf(vv[e], ww.x, o[4 * g + 0]);
-              o[4 * g + 1] = fmaf(vv[e], ww.y, o[4 * g + 1]);
-              o[4 * g + 2] = fmaf(vv[e], ww.z, o[4 * g + 2]);
-              o[4 * g + 3] = fmaf(vv[e], ww.w, o[4 * g + 3]);
-            }
-          }
-        }
-      }
-    }
-    float s = 0.f;
-#pragma unroll
-    for (int c = 0; c < 16; ++c) s += o[c];
-    s += __shfl_xor_sync(0xffffffffu, s, 1);
-    s += __shfl_xor_sync(0xffffffffu, s, 2);
-    const float mean = s * (1.f / 64.f);
-    float q = 0.f;
-#pragma unroll
-    for (int c = 0; c < 16; ++c) q += (o[c] - mean) * (o[c] - mean);
-    q += __shfl_xor_sync(0xffffffffu, q, 1);
-    q += __shfl_xor_sync(0xffffffffu, q, 2);
-    const float rstd = rsqrtf(q * (1.f / 64.f) + 1e-6f);
-    ln_gelu_inplace<16>(o, sp + 64, sp + 128, part * 16, mean, rstd);
-    if (ok) {
-#pragma unroll
-      for (int c = 0; c < 4; ++c) out[pix * 16 + part * 4 + c] = make_float4(o[4 * c], o[4 * c + 1], o[4 * c + 2], o[4 * c + 3]);
-    }
-  }
-}
+// stage 3 (16 -> 64 channels) and stage 4 are dense enough for the tensor cores: im2col + tcgen05 GEMM + layernorm_gelu_rows (engine.cu)
 
 int mask_ds_stage(int stage, const float* in, float* out, int n, int H_in, const float* w, const float* b, const float* ln_w,
                   const float* ln_b, cudaStream_t stream) {
@@ -240,13 +169,6 @@ int mask_ds_stage(int stage, const float* in, float* out, int n, int H_in, const
     ProfRange pr(stream, nm, 2.0 * pix * 576, (double)pix * (64.0 + 64.0));
     long blocks = (pix + 127) / 128; if (blocks > (long)num_sms() * 16) blocks = (long)num_sms() * 16;
     mask_ds2_kernel<<<(unsigned)blocks, 128, 0, stream>>>(reinterpret_cast<const float4*>(in), reinterpret_cast<float4*>(out), n, H_in, w, b, ln_w, ln_b);
-  } else if (stage == 3) {
-    ProfRange pr(stream, nm, 2.0 * pix * 9216, (double)pix * (256.0 + 256.0));
-    const size_t smem = (9216 + 192) * sizeof(float);
-    static PerDeviceFlag attr;
-    if (!attr.is_set()) { cudaFuncSetAttribute(mask_ds3_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); attr.set(); }
-    long blocks = (pix * 4 + 255) / 256; if (blocks > (long)num_sms() * 4) blocks = (long)num_sms() * 4;
-    mask_ds3_kernel<<<(unsigned)blocks, 256, smem, stream>>>(reinterpret_cast<const float4*>(in), reinterpret_cast<float4*>(out), n, H_in, w, b, ln_w, ln_b);
   } else {
     set_error("mask_ds_stage: bad stage %d", stage);
     return 1;
@@ -284,6 +206,33 @@ int im2col3x3s2_nhwc(const float* in, bf16* cols, int n, int H, int C, cudaStrea
   ProfRange pr(stream, "im2col3x3s2", 0, (double)total * 16.0 + (double)n * H * H * C * 4.0);
   im2col3x3s2_kernel<<<(unsigned)blocks, 256, 0, stream>>>(reinterpret_cast<const float4*>(in), reinterpret_cast<uint4*>(cols), n, H, C / 8);
   SAM2B_CHECK_LAUNCH("im2col3x3s2");
+  return 0;
+}
+
+// the same from a bf16 NHWC map (stage 4 after the GEMM form of stage 3): 8 channels = one 16-byte move
+__global__ void __launch_bounds__(256) im2col3x3s2_bf16_kernel(const uint4* __restrict__ in, uint4* __restrict__ cols, int n, int H, int C8) {
+  const int Ho = H >> 1;
+  const long total = (long)n * Ho * Ho * 9 * C8;
+  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
+    const int c = (int)(i % C8);
+    long t = i / C8;
+    const int tap = (int)(t % 9); t /= 9;
+    const int ox = (int)(t % Ho); t /= Ho;
+    const int oy = (int)(t % Ho);
+    const long img = t / Ho;
+    const int y = 2 * oy - 1 + tap / 3, x = 2 * ox - 1 + tap % 3;
+    uint4 pk = make_uint4(0, 0, 0, 0);
+    if (y >= 0 && y < H && x >= 0 && x < H) pk = __ldg(in + ((img * H + y) * H + x) * C8 + c);
+    cols[i] = pk;
+  }
+}
+int im2col3x3s2_nhwc_bf16(const bf16* in, bf16* cols, int n, int H, int C, cudaStream_t stream) {
+  if (C % 8 || H % 2) { set_error("im2col3x3s2_bf16: bad shape"); return 1; }
+  const long total = (long)n * (H / 2) * (H / 2) * 9 * (C / 8);
+  long blocks = (total + 255) / 256; if (blocks > (long)num_sms() * 16) blocks = (long)num_sms() * 16;
+  ProfRange pr(stream, "im2col3x3s2", 0, (double)total * 16.0 + (double)n * H * H * C * 2.0);
+  im2col3x3s2_bf16_kernel<<<(unsigned)blocks, 256, 0, stream>>>(reinterpret_cast<const uint4*>(in), reinterpret_cast<uint4*>(cols), n, H, C / 8);
+  SAM2B_CHECK_LAUNCH("im2col3x3s2_bf16");
   return 0;
 }
 

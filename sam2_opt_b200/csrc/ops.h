@@ -172,6 +172,7 @@ int mask_ds_stage(int stage, const float* in, float* out, int n, int H_in, const
                   const float* ln_w, const float* ln_b, cudaStream_t stream);
 // im2col for conv3x3 s2 p1 on NHWC fp32 [n,H,H,C] -> bf16 [n*(H/2)^2, 9*C], k = (ky*3+kx)*C + c
 int im2col3x3s2_nhwc(const float* in, bf16* cols, int n, int H, int C, cudaStream_t stream);
+int im2col3x3s2_nhwc_bf16(const bf16* in, bf16* cols, int n, int H, int C, cudaStream_t stream);
 // [n,C,HW] fp32 -> [n,HW,C] bf16
 int nchw_to_nhwc_bf16(const float* in, bf16* out, int n, int C, int HW, cudaStream_t stream);
 // CXBlock front half: depthwise 7x7 (pad 3) + LayerNorm2d(eps 1e-6) on NHWC fp32 [n,H,H,256] -> bf16 [n*H*H,256].

@@ -93,6 +93,8 @@ def derive(w: Dict[str, torch.Tensor]) -> Dict[str, torch.Tensor]:
     k9 = "memory_encoder.mask_downsampler.encoder.9.weight"
     if k9 in w:
         d["derived.memenc.ds4.weight"] = w[k9].float().permute(0, 2, 3, 1).reshape(256, 576).contiguous()
+        # the 16 -> 64 channel stage in the same form: [64, (ky,kx,cin) = 144]
+        d["derived.memenc.ds3.weight"] = w["memory_encoder.mask_downsampler.encoder.6.weight"].float().permute(0, 2, 3, 1).reshape(64, 144).contiguous()
         for l in range(2):
             dw = w[f"memory_encoder.fuser.layers.{l}.dwconv.weight"].float()
             d[f"derived.memenc.fuser.{l}.dw.weight"] = dw.reshape(256, 49).t().contiguous()
