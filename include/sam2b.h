@@ -88,6 +88,33 @@ int sam2b_memory_attention_varlen(sam2b_handle h, const float* curr, const float
  * (the second reference output, the sine position encoding, is a constant: sam2b_position_encoding) */
 int sam2b_memory_encode(sam2b_handle h, const float* pix_feat, const float* masks, int n, float* out_x, void* stream);
 
+/* ---- SAM heads: prompt encoder (points) + two-way mask decoder + object-pointer head ----
+ * Replaces SAM2Base._forward_sam_heads (sam2/sam2/modeling/sam2_base_official.py:338-494), i.e. PromptEncoder._embed_points
+ * (sam/prompt_encoder.py:124-150), MaskDecoder.forward / predict_masks (sam/mask_decoder.py:116-316, incl. the dynamic
+ * multimask fallback :337-382) and TwoWayTransformer (sam/transformer.py:97-219), for n prompts / objects in one call.
+ * backbone_features dev: the 256-channel 64x64 embedding of every prompt, element (b, c, p = y*64+x) at
+ *                  backbone_features[b*feat_stride_n + c*feat_stride_c + p*feat_stride_p]; one of the two inner strides must be 1
+ *                  (NCHW [n,256,64,64]: 1048576, 4096, 1; the E3 output [4096,n,256]: 256, 1, n*256; feat_stride_n = 0 repeats
+ *                  one image for every prompt, mask_decoder.py:252-259 repeat_image)
+ * feat_s0 dev [.,32,256,256], feat_s1 dev [.,64,128,128]: the conv_s0 / conv_s1 levels (fpn0 / fpn1 of sam2b_image_encode), batch
+ *                  strides in elements (0: one image for every prompt)
+ * point_coords dev [n,num_points,2] (x, y in the 1024 frame, before the +0.5 shift), point_labels dev int32 [n,num_points]
+ *                  (-1 padding, 0/1 negative/positive click, 2/3 box corners); num_points = 0: no prompt (a tracked frame).
+ *                  The padding point the reference appends is added internally; num_points <= 25.
+ * dense_embedding  dev [n,256,64,64] (the prompt encoder's mask_downscaling output) or NULL: no_mask_embed
+ * multimask_output 1: the 3 multimask outputs and the best of them; 0: mask 0 unless it is unstable (dynamic fallback)
+ * decoder_only     1: plain MaskDecoder.forward semantics (no NO_OBJ_SCORE fill: what SAM2ImagePredictor.predict uses)
+ * outputs (any may be NULL), M = multimask_output ? 3 : 1:
+ *   low_res_multimasks dev [n,M,256,256], high_res_multimasks dev [n,M,1024,1024], ious dev [n,M],
+ *   low_res_masks dev [n,1,256,256] / high_res_masks dev [n,1,1024,1024] (the best mask), obj_ptr dev [n,256],
+ *   object_score_logits dev [n,1]. */
+int sam2b_sam_heads(sam2b_handle h, const float* backbone_features, int64_t feat_stride_n, int64_t feat_stride_c,
+                    int64_t feat_stride_p, const float* feat_s0, int64_t s0_batch_stride, const float* feat_s1,
+                    int64_t s1_batch_stride, const float* point_coords, const int32_t* point_labels, int num_points,
+                    const float* dense_embedding, int n, int multimask_output, int decoder_only, float* low_res_multimasks,
+                    float* high_res_multimasks, float* ious, float* low_res_masks, float* high_res_masks, float* obj_ptr,
+                    float* object_score_logits, void* stream);
+
 /* ---- peer memory for the embedding gather (the only collective of the path) ----
  * The reference has no multi-GPU inference path (one process, one GPU: sam2/ytools/tensorrt/tensorrt_executor.py:26-29);
  * this is the B200-box replacement: one process per GPU, every rank owns a gather buffer that its peers map through CUDA

@@ -24,6 +24,8 @@ SIGNATURES = {
     "sam2b_memory_attention": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _vp, _vp, _i, _i, _vp, _vp]),
     "sam2b_memory_attention_varlen": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _vp, _vp, _i, _i, C.POINTER(C.c_int32), C.POINTER(C.c_int32), _vp, _vp]),
     "sam2b_memory_encode": (_i, [_vp, _vp, _vp, _i, _vp, _vp]),
+    "sam2b_sam_heads": (_i, [_vp, _vp, _i64, _i64, _i64, _vp, _i64, _vp, _i64, _vp, _vp, _i, _vp, _i, _i, _i,
+                             _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "sam2b_peer_alloc": (_i, [_i, _i64, C.POINTER(_vp), C.c_char_p]),
     "sam2b_peer_free": (_i, [_i, _vp]),
     "sam2b_peer_open": (_i, [_i, C.c_char_p, C.POINTER(_vp)]),

@@ -101,6 +101,7 @@ using namespace sam2b;
 struct sam2b_engine {
   int device = 0;
   bool finalized = false;
+  bool has_heads = false;                 // the SAM-heads tensors were registered (sam2b_sam_heads is available)
   std::map<std::string, Tensor> w;
   std::map<std::string, Buf> ws;   // named workspace buffers, grow-only
   std::vector<BlockCfg> blocks;
@@ -280,6 +281,53 @@ static int finalize(sam2b_engine* e) {
     }
   }
   TRY(need(e, "derived.rope.cs", nullptr, false));             // [4096,256]: (cos, sin) interleaved per column pair
+  // ---- SAM heads (optional: an engine built from encoder-only weights has no sam2b_sam_heads) ----
+  if (e->find("sam_mask_decoder.iou_token.weight") && e->find("derived.heads.up1.weight")) {
+    const std::string md = "sam_mask_decoder.", tr = md + "transformer.", pe = "sam_prompt_encoder.";
+    for (const char* nm : {"pe_layer.positional_encoding_gaussian_matrix", "not_a_point_embed.weight", "no_mask_embed.weight",
+                           "point_embeddings.0.weight", "point_embeddings.1.weight", "point_embeddings.2.weight",
+                           "point_embeddings.3.weight"})
+      TRY(need(e, pe + nm, nullptr, false));
+    for (const char* nm : {"obj_score_token.weight", "iou_token.weight", "mask_tokens.weight", "output_upscaling.0.bias",
+                           "output_upscaling.1.weight", "output_upscaling.1.bias", "output_upscaling.3.bias"})
+      TRY(need(e, md + nm, nullptr, false));
+    auto attn = [&](const std::string& p) -> int {
+      for (const char* nm : {"q_proj.", "k_proj.", "v_proj.", "out_proj."}) {
+        TRY(need(e, p + nm + "weight", nullptr, false));
+        TRY(need(e, p + nm + "bias", nullptr, false));
+      }
+      return 0;
+    };
+    for (int l = 0; l < 2; ++l) {
+      const std::string p = tr + "layers." + std::to_string(l) + ".", d = "derived.heads." + std::to_string(l) + ".";
+      TRY(attn(p + "self_attn."));
+      TRY(attn(p + "cross_attn_token_to_image."));
+      TRY(attn(p + "cross_attn_image_to_token."));
+      for (const char* nm : {"norm1.", "norm2.", "norm3.", "norm4.", "mlp.layers.0.", "mlp.layers.1."}) {
+        TRY(need(e, p + nm + "weight", nullptr, false));
+        TRY(need(e, p + nm + "bias", nullptr, false));
+      }
+      TRY(need(e, d + "kvq.weight", nullptr, true));       // [384, 768] split form of (t2i k | t2i v | i2t q)
+      TRY(need(e, d + "kvq.table", nullptr, false));       // [4096, 384] = dense_pe W^T + bias of the same three projections
+      TRY(need(e, d + "i2t_out.weight", nullptr, true));   // [256, 384] split form of the i2t out_proj
+    }
+    TRY(attn(tr + "final_attn_token_to_image."));
+    TRY(need(e, tr + "norm_final_attn.weight", nullptr, false));
+    TRY(need(e, tr + "norm_final_attn.bias", nullptr, false));
+    TRY(need(e, "derived.heads.final.kv.weight", nullptr, true));   // [256, 768]
+    TRY(need(e, "derived.heads.final.kv.table", nullptr, false));   // [4096, 256]
+    TRY(need(e, "derived.heads.up1.weight", nullptr, true));        // [256 = (dy,dx,c), 768] ConvTranspose2d(256 -> 64) as a GEMM
+    TRY(need(e, "derived.heads.up2.weight", nullptr, false));       // [64][4 = (ey,ex)][32]
+    for (const char* head : {"sam_mask_decoder.iou_prediction_head.", "sam_mask_decoder.pred_obj_score_head.", "obj_ptr_proj.",
+                             "sam_mask_decoder.output_hypernetworks_mlps.0.", "sam_mask_decoder.output_hypernetworks_mlps.1.",
+                             "sam_mask_decoder.output_hypernetworks_mlps.2.", "sam_mask_decoder.output_hypernetworks_mlps.3."})
+      for (int i = 0; i < 3; ++i) {
+        TRY(need(e, std::string(head) + "layers." + std::to_string(i) + ".weight", nullptr, false));
+        TRY(need(e, std::string(head) + "layers." + std::to_string(i) + ".bias", nullptr, false));
+      }
+    TRY(need(e, "no_obj_ptr", nullptr, false));
+    e->has_heads = true;
+  }
   CUDA_OK(cudaStreamSynchronize(0));
   e->finalized = true;
   return 0;
@@ -709,6 +757,190 @@ static int memory_encode_mb(sam2b_engine* e, const float* pix_feat, const float*
   return 0;
 }
 
+
+// ------------------------------------------------------------------------------------------------------------
+// SAM heads for n prompts / objects: prompt encoder (points), two-way transformer, up-scaling,
+// hyper-network masks, IoU / object-score heads, best-mask selection, object pointer.  Reference:
+// modeling/sam2_base_official.py:338-494 (_forward_sam_heads), modeling/sam/mask_decoder.py:116-316,
+// modeling/sam/transformer.py:97-219.  Image side (4096 rows per object): split-bf16 tcgen05 GEMMs (sam_heads.cu header);
+// token side: fp32 kernels.
+// ------------------------------------------------------------------------------------------------------------
+struct HeadsIO {
+  const float* pix; long sn, sc, sp;             // image embedding, addressed pix[b*sn + c*sc + p*sp]
+  const float* s0; long s0_bs;                   // conv_s0 level [.,32,256,256], batch stride (0: one image for all)
+  const float* s1; long s1_bs;                   // conv_s1 level [.,64,128,128]
+  const float* coords; const int* labels; int P; // device, [n,P,2] / [n,P]
+  const float* dense;                            // optional dense prompt embedding [n,256,64,64]
+  int multimask, decoder_only;
+  float *low_multi, *high_multi, *ious, *low_best, *high_best, *obj_ptr, *obj_logits;
+};
+
+static int sam_heads_mb(sam2b_engine* e, const HeadsIO& io, int n, cudaStream_t st) {
+  const int P = io.P > 0 ? io.P : 1, T = 6 + P + 1, nT = n * T;
+  const long R = 4096L * n;
+  float *KEYS, *KVQ, *XR, *TOK, *QPE, *TQ, *TK, *TV, *TA, *PART, *HID, *TPART, *H1, *H2, *IOU, *OBJ, *HYP, *PTR4, *MASKS, *IOUT, *OBJT, *PTRT;
+  bf16 *KS, *OS;
+  int *STAB, *SEL, *LABP;
+  TRY(ws_get_t(e, "sh_keys", (size_t)R * 256, &KEYS));
+  TRY(ws_get_t(e, "sh_ks", (size_t)R * 768, &KS));
+  TRY(ws_get_t(e, "sh_kvq", (size_t)R * 384, &KVQ));
+  TRY(ws_get_t(e, "sh_os", (size_t)R * 384, &OS));
+  TRY(ws_get_t(e, "sh_xr", (size_t)R * 256, &XR));
+  TRY(ws_get_t(e, "sh_tok", (size_t)nT * 256, &TOK));
+  TRY(ws_get_t(e, "sh_qpe", (size_t)nT * 256, &QPE));
+  TRY(ws_get_t(e, "sh_tq", (size_t)nT * 256, &TQ));
+  TRY(ws_get_t(e, "sh_tk", (size_t)nT * 256, &TK));
+  TRY(ws_get_t(e, "sh_tv", (size_t)nT * 256, &TV));
+  TRY(ws_get_t(e, "sh_ta", (size_t)nT * 256, &TA));
+  TRY(ws_get_t(e, "sh_part", (size_t)8 * nT * 256, &PART));
+  TRY(ws_get_t(e, "sh_hid", (size_t)nT * 2048, &HID));
+  TRY(ws_get_t(e, "sh_tpart", (size_t)n * 8 * 16 * T * 18, &TPART));
+  TRY(ws_get_t(e, "sh_h1", (size_t)10 * n * 256, &H1));
+  TRY(ws_get_t(e, "sh_h2", (size_t)10 * n * 256, &H2));
+  TRY(ws_get_t(e, "sh_iou", (size_t)n * 4, &IOU));
+  TRY(ws_get_t(e, "sh_obj", (size_t)n, &OBJ));
+  TRY(ws_get_t(e, "sh_hyp", (size_t)n * 128, &HYP));
+  TRY(ws_get_t(e, "sh_ptr4", (size_t)n * 4 * 256, &PTR4));
+  TRY(ws_get_t(e, "sh_masks", (size_t)n * 4 * 65536, &MASKS));
+  TRY(ws_get_t(e, "sh_iout", (size_t)n * 4, &IOUT));
+  TRY(ws_get_t(e, "sh_objt", (size_t)n, &OBJT));
+  TRY(ws_get_t(e, "sh_ptrt", (size_t)n * 256, &PTRT));
+  TRY(ws_get_t(e, "sh_stab", (size_t)n * 2, &STAB));
+  TRY(ws_get_t(e, "sh_sel", (size_t)n * 4, &SEL));
+  TRY(ws_get_t(e, "sh_labp", (size_t)n * 4, &LABP));
+  auto P32 = [&](const std::string& name) { return W32(e, name); };
+  const std::string md = "sam_mask_decoder.", tr = md + "transformer.", pe = "sam_prompt_encoder.";
+
+  // prompt encoder: no prompt at all = one point with label -1 (sam2_base_official.py:391-395) + the padding point
+  const float* coords = io.coords;
+  const int* labels = io.labels;
+  if (io.P <= 0) {
+    CUDA_OK(cudaMemsetAsync(LABP, 0xFF, (size_t)n * 4 * sizeof(int), st));     // labels = -1; the coordinates are never read
+    labels = LABP;
+    coords = reinterpret_cast<const float*>(LABP);
+  }
+  const float* pt_emb[4] = {P32(pe + "point_embeddings.0.weight"), P32(pe + "point_embeddings.1.weight"),
+                            P32(pe + "point_embeddings.2.weight"), P32(pe + "point_embeddings.3.weight")};
+  TRY(heads_tokens(coords, labels, P, n, P32(pe + "pe_layer.positional_encoding_gaussian_matrix"), P32(pe + "not_a_point_embed.weight"),
+                   pt_emb, P32(md + "obj_score_token.weight"), P32(md + "iou_token.weight"), P32(md + "mask_tokens.weight"), TOK,
+                   QPE, st));
+  TRY(heads_prep_src(io.pix, io.sn, io.sc, io.sp, io.dense, P32(pe + "no_mask_embed.weight"), KEYS, KS, n, st));
+
+  auto job = [&](const float* X, long ldx, const float* X2, const float* Wt, long ldw, const float* b, float* Y, long ldy, int rows,
+                 int N, int K, int act) {
+    LinJob j;
+    j.X = X; j.ldx = ldx; j.X2 = X2; j.ldx2 = ldx; j.W = Wt; j.ldw = ldw; j.b = b; j.Y = Y; j.ldy = ldy;
+    j.rows = rows; j.N = N; j.K = K; j.act = act;
+    return j;
+  };
+  // linear (no bias) into PART, then bias + residual + LayerNorm -> TOK
+  auto proj_res_ln = [&](const float* X, int K, const std::string& lin, const float* res, const std::string& norm) -> int {
+    LinJobs J;
+    const int S = K > 256 ? K / 256 : 1;
+    for (int s = 0; s < S; ++s)
+      J.j[s] = job(X + s * 256, K, nullptr, P32(lin + "weight") + s * 256, K, nullptr, PART + (size_t)s * nT * 256, 256, nT, 256,
+                   S > 1 ? 256 : K, 0);
+    TRY(tok_linear(J, S, st));
+    return tok_sum_res_ln(PART, (long)nT * 256, S, P32(lin + "bias"), res, P32(norm + "weight"), P32(norm + "bias"), 1e-5f, TOK, nT, st);
+  };
+  auto image_gemm = [&](const bf16* A, int K, const std::string& wname, int N, const float* bias, const float* residual, long ld_res,
+                        int res_row_mod, float* out, long ldc) -> int {
+    GemmArgs g;
+    g.A = A; g.lda = K; g.M = (int)R; g.K = K;
+    g.B = W16(e, wname); g.ldb = K; g.N = N;
+    g.bias = bias; g.residual = residual; g.ld_res = ld_res; g.res_row_mod = res_row_mod;
+    g.out_f32 = out; g.ldc = ldc;
+    return gemm_bf16(g, st);
+  };
+  // token -> image attention block shared by the two layers and the final attention
+  auto t2i_block = [&](const std::string& p, int ld, const std::string& norm) -> int {
+    LinJobs J;
+    J.j[0] = job(TOK, 256, QPE, P32(p + "q_proj.weight"), 256, P32(p + "q_proj.bias"), TQ, 128, nT, 128, 256, 0);
+    TRY(tok_linear(J, 1, st));
+    TRY(t2i_attention(KVQ, ld, TQ, n, T, TPART, TA, st));
+    return proj_res_ln(TA, 128, p + "out_proj.", TOK, norm);
+  };
+
+  for (int l = 0; l < 2; ++l) {
+    const std::string p = tr + "layers." + std::to_string(l) + ".", d = "derived.heads." + std::to_string(l) + ".";
+    {   // self-attention of the tokens (transformer.py:164-172): layer 0 without the positional term and without residual
+      const std::string sa = p + "self_attn.";
+      const float* qpe = l ? QPE : nullptr;
+      LinJobs J;
+      J.j[0] = job(TOK, 256, qpe, P32(sa + "q_proj.weight"), 256, P32(sa + "q_proj.bias"), TQ, 256, nT, 256, 256, 0);
+      J.j[1] = job(TOK, 256, qpe, P32(sa + "k_proj.weight"), 256, P32(sa + "k_proj.bias"), TK, 256, nT, 256, 256, 0);
+      J.j[2] = job(TOK, 256, nullptr, P32(sa + "v_proj.weight"), 256, P32(sa + "v_proj.bias"), TV, 256, nT, 256, 256, 0);
+      TRY(tok_linear(J, 3, st));
+      TRY(tok_self_attn(TQ, TK, TV, n, T, TA, st));
+      TRY(proj_res_ln(TA, 256, sa + "out_proj.", l ? TOK : nullptr, p + "norm1."));
+    }
+    // k, v of the token -> image attention and q of the image -> token attention: one GEMM over the keys of this layer,
+    // the dense positional encoding enters as the constant table (dense_pe W^T + b) added per position
+    TRY(image_gemm(KS, 768, d + "kvq.weight", 384, nullptr, P32(d + "kvq.table"), 384, 4096, KVQ, 384));
+    TRY(t2i_block(p + "cross_attn_token_to_image.", 384, p + "norm2."));
+    {   // MLP 256 -> 2048 -> 256 (ReLU), transformer.py:184-187
+      LinJobs J;
+      J.j[0] = job(TOK, 256, nullptr, P32(p + "mlp.layers.0.weight"), 256, P32(p + "mlp.layers.0.bias"), HID, 2048, nT, 2048, 256, 1);
+      TRY(tok_linear(J, 1, st));
+      TRY(proj_res_ln(HID, 2048, p + "mlp.layers.1.", TOK, p + "norm3."));
+    }
+    {   // image -> token attention (transformer.py:189-196): keys = norm4(keys + attn(q = keys + pe, k = queries + pe, v = queries))
+      const std::string ca = p + "cross_attn_image_to_token.";
+      LinJobs J;
+      J.j[0] = job(TOK, 256, QPE, P32(ca + "k_proj.weight"), 256, P32(ca + "k_proj.bias"), TK, 128, nT, 128, 256, 0);
+      J.j[1] = job(TOK, 256, nullptr, P32(ca + "v_proj.weight"), 256, P32(ca + "v_proj.bias"), TV, 128, nT, 128, 256, 0);
+      TRY(tok_linear(J, 2, st));
+      TRY(i2t_attention(KVQ, 384, 256, TK, TV, n, T, OS, st));
+      TRY(image_gemm(OS, 384, d + "i2t_out.weight", 256, P32(ca + "out_proj.bias"), KEYS, 256, 0, XR, 256));
+      TRY(ln256_split(XR, P32(p + "norm4.weight"), P32(p + "norm4.bias"), 1e-5f, KEYS, KS, R, st));
+    }
+  }
+  TRY(image_gemm(KS, 768, "derived.heads.final.kv.weight", 256, nullptr, P32("derived.heads.final.kv.table"), 256, 4096, KVQ, 256));
+  TRY(t2i_block(tr + "final_attn_token_to_image.", 256, tr + "norm_final_attn."));
+
+  // the small heads on the output tokens (mask_decoder.py:302-316, sam2_base_official.py:474-494): IoU (token 1), object score
+  // (token 0), the four hyper-network MLPs and obj_ptr_proj on the four mask tokens (tokens 2..5); three launches of 10 jobs
+  const std::string heads[10] = {md + "iou_prediction_head.", md + "pred_obj_score_head.", md + "output_hypernetworks_mlps.0.",
+                                 md + "output_hypernetworks_mlps.1.", md + "output_hypernetworks_mlps.2.",
+                                 md + "output_hypernetworks_mlps.3.", "obj_ptr_proj.", "obj_ptr_proj.", "obj_ptr_proj.", "obj_ptr_proj."};
+  const int head_tok[10] = {1, 0, 2, 3, 4, 5, 2, 3, 4, 5};
+  {
+    LinJobs J0, J1, J2;
+    for (int i = 0; i < 10; ++i) {
+      const std::string L = heads[i] + "layers.";
+      J0.j[i] = job(TOK + head_tok[i] * 256, (long)T * 256, nullptr, P32(L + "0.weight"), 256, P32(L + "0.bias"), H1 + (size_t)i * n * 256,
+                    256, n, 256, 256, 1);
+      J1.j[i] = job(H1 + (size_t)i * n * 256, 256, nullptr, P32(L + "1.weight"), 256, P32(L + "1.bias"), H2 + (size_t)i * n * 256, 256, n,
+                    256, 256, 1);
+      float* Y; long ldy; int N, act = 0;
+      if (i == 0) { Y = IOU; ldy = 4; N = 4; act = 2; }
+      else if (i == 1) { Y = OBJ; ldy = 1; N = 1; }
+      else if (i < 6) { Y = HYP + (i - 2) * 32; ldy = 128; N = 32; }
+      else { Y = PTR4 + (i - 6) * 256; ldy = 1024; N = 256; }
+      J2.j[i] = job(H2 + (size_t)i * n * 256, 256, nullptr, P32(L + "2.weight"), 256, P32(L + "2.bias"), Y, ldy, n, N, 256, act);
+    }
+    TRY(tok_linear(J0, 10, st));
+    TRY(tok_linear(J1, 10, st));
+    TRY(tok_linear(J2, 10, st));
+  }
+  // up-scaling: ConvTranspose2d(256 -> 64, k2 s2) of the final keys as a GEMM, everything after it in one kernel
+  TRY(image_gemm(KS, 768, "derived.heads.up1.weight", 256, nullptr, nullptr, 0, 0, XR, 256));
+  const int dynamic = !io.multimask;        // dynamic_multimask_via_stability (mask_decoder.py:215-219; on in every SAM2.1 config)
+  if (dynamic) CUDA_OK(cudaMemsetAsync(STAB, 0, (size_t)n * 2 * sizeof(int), st));
+  TRY(heads_upscale(XR, P32(md + "output_upscaling.0.bias"), io.s1, io.s1_bs, P32(md + "output_upscaling.1.weight"),
+                    P32(md + "output_upscaling.1.bias"), P32("derived.heads.up2.weight"), P32(md + "output_upscaling.3.bias"), io.s0,
+                    io.s0_bs, HYP, MASKS, dynamic ? STAB : nullptr, 0.05f, n, st));
+  TRY(heads_select(IOU, OBJ, PTR4, STAB, P32("no_obj_ptr"), io.multimask, dynamic, 0.98f, io.ious ? io.ious : IOUT,
+                   io.obj_ptr ? io.obj_ptr : PTRT, io.obj_logits ? io.obj_logits : OBJT, SEL, io.decoder_only, n, st));
+  float* low_best = io.low_best;
+  if (!low_best && io.high_best) { TRY(ws_get_t(e, "sh_lowbest", (size_t)n * 65536, &low_best)); }
+  TRY(heads_write_masks(MASKS, SEL, io.multimask, -1024.0f, io.low_multi, low_best, n, st));
+  if (io.high_best) TRY(upsample_bilinear_mask(low_best, io.high_best, nullptr, n, 256, 256, 1024, 1024, 0.f, st));
+  if (io.high_multi && io.low_multi)
+    TRY(upsample_bilinear_mask(io.low_multi, io.high_multi, nullptr, (long)n * (io.multimask ? 3 : 1), 256, 256, 1024, 1024, 0.f, st));
+  return 0;
+}
+
 static const int kMaxMicroBatchCap = 32;
 static const int kHostMicroBatch = 16;     // host path: two or more micro-batches so that copies overlap compute
 // images per pass through the trunk (SAM2B_MICROBATCH overrides).  Every GEMM is a persistent kernel over 148 SMs (74 CTA
@@ -933,6 +1165,45 @@ int sam2b_memory_encode(sam2b_handle h, const float* pix_feat, const float* mask
   for (int i0 = 0; i0 < n; i0 += kMaxMicroBatch) {
     const int mb = (n - i0) < kMaxMicroBatch ? (n - i0) : kMaxMicroBatch;
     TRY(memory_encode_mb(h, pix_feat + (size_t)i0 * 256 * 4096, masks + (size_t)i0 * 1024 * 1024, mb, out_x + (size_t)i0 * 64 * 4096, st));
+  }
+  return 0;
+}
+
+int sam2b_sam_heads(sam2b_handle h, const float* backbone_features, int64_t feat_stride_n, int64_t feat_stride_c,
+                    int64_t feat_stride_p, const float* feat_s0, int64_t s0_batch_stride, const float* feat_s1,
+                    int64_t s1_batch_stride, const float* point_coords, const int32_t* point_labels, int num_points,
+                    const float* dense_embedding, int n, int multimask_output, int decoder_only, float* low_res_multimasks,
+                    float* high_res_multimasks, float* ious, float* low_res_masks, float* high_res_masks, float* obj_ptr,
+                    float* object_score_logits, void* stream) {
+  if (!h || !h->finalized) { set_error("sam2b_sam_heads: engine not finalized"); return 1; }
+  if (!h->has_heads) { set_error("sam2b_sam_heads: the engine was built without the sam_mask_decoder / sam_prompt_encoder tensors"); return 1; }
+  if (!backbone_features || !feat_s0 || !feat_s1 || n <= 0) { set_error("sam2b_sam_heads: null/empty argument"); return 1; }
+  if (num_points < 0 || num_points > 25) { set_error("sam2b_sam_heads: %d points per prompt (0..25)", num_points); return 1; }
+  if (num_points > 0 && (!point_coords || !point_labels)) { set_error("sam2b_sam_heads: num_points=%d but the point arrays are NULL", num_points); return 1; }
+  if (high_res_multimasks && !low_res_multimasks) { set_error("sam2b_sam_heads: high_res_multimasks needs low_res_multimasks"); return 1; }
+  ENTER_DEVICE(h->device);
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  ENGINE_CALL(h, st);
+  const int kMaxMicroBatch = 64, M = multimask_output ? 3 : 1;
+  for (int i0 = 0; i0 < n; i0 += kMaxMicroBatch) {
+    const int mb = (n - i0) < kMaxMicroBatch ? (n - i0) : kMaxMicroBatch;
+    HeadsIO io;
+    io.pix = backbone_features + (size_t)i0 * feat_stride_n; io.sn = feat_stride_n; io.sc = feat_stride_c; io.sp = feat_stride_p;
+    io.s0 = feat_s0 + (size_t)i0 * s0_batch_stride; io.s0_bs = s0_batch_stride;
+    io.s1 = feat_s1 + (size_t)i0 * s1_batch_stride; io.s1_bs = s1_batch_stride;
+    io.coords = point_coords ? point_coords + (size_t)i0 * num_points * 2 : nullptr;
+    io.labels = point_labels ? point_labels + (size_t)i0 * num_points : nullptr;
+    io.P = num_points;
+    io.dense = dense_embedding ? dense_embedding + (size_t)i0 * 256 * 4096 : nullptr;
+    io.multimask = multimask_output ? 1 : 0; io.decoder_only = decoder_only ? 1 : 0;
+    io.low_multi = low_res_multimasks ? low_res_multimasks + (size_t)i0 * M * 65536 : nullptr;
+    io.high_multi = high_res_multimasks ? high_res_multimasks + (size_t)i0 * M * 1048576 : nullptr;
+    io.ious = ious ? ious + (size_t)i0 * M : nullptr;
+    io.low_best = low_res_masks ? low_res_masks + (size_t)i0 * 65536 : nullptr;
+    io.high_best = high_res_masks ? high_res_masks + (size_t)i0 * 1048576 : nullptr;
+    io.obj_ptr = obj_ptr ? obj_ptr + (size_t)i0 * 256 : nullptr;
+    io.obj_logits = object_score_logits ? object_score_logits + i0 : nullptr;
+    TRY(sam_heads_mb(h, io, mb, st));
   }
   return 0;
 }

@@ -180,3 +180,39 @@ int nchw_to_nhwc_bf16(const float* in, bf16* out, int n, int C, int HW, cudaStre
 int dwconv7_ln_nhwc(const float* x, bf16* y, int n, int H, const float* dw_w, const float* dw_b, const float* ln_w,
                     const float* ln_b, cudaStream_t stream);
 }  // namespace sam2b
+
+namespace sam2b {
+// ---- SAM heads (sam_heads.cu); reference modeling/sam/{prompt_encoder,transformer,mask_decoder}.py, sam2_base_official.py:338-494 ----
+// One small fp32 linear problem of the token side: Y[r][j] = act(sum_k (X[r][k] + X2[r][k]) W[j][k] + b[j]); act: 0 none, 1 ReLU, 2 sigmoid
+struct LinJob {
+  const float* X = nullptr; long ldx = 0; const float* X2 = nullptr; long ldx2 = 0;
+  const float* W = nullptr; long ldw = 0; const float* b = nullptr;
+  float* Y = nullptr; long ldy = 0;
+  int rows = 0, N = 0, K = 0, act = 0;
+};
+struct LinJobs { static const int kMax = 16; LinJob j[kMax]; };
+int tok_linear(const LinJobs& jobs, int njobs, cudaStream_t st);
+// y[r][0..256) = LN(sum_s part[s][r] + bias + res[r]) (g == nullptr: no LayerNorm)
+int tok_sum_res_ln(const float* part, long part_stride, int S, const float* bias, const float* res, const float* g,
+                   const float* be, float eps, float* y, int rows, cudaStream_t st);
+int tok_self_attn(const float* q, const float* k, const float* v, int n, int T, float* o, cudaStream_t st);
+// src = image embedding + dense embedding -> keys fp32 [n*4096][256] + split bf16 operand [n*4096][768] = [hi | lo | hi]
+int heads_prep_src(const float* pix, long sn, long sc, long sp, const float* dense, const float* nomask, float* keys, bf16* ks,
+                   int n, cudaStream_t st);
+int ln256_split(const float* x, const float* g, const float* b, float eps, float* y, bf16* ys, long rows, cudaStream_t st);
+int heads_tokens(const float* coords, const int* labels, int P, int n, const float* gauss, const float* not_a_point,
+                 const float* const pt_emb[4], const float* obj_tok, const float* iou_tok, const float* mask_toks, float* tok,
+                 float* qpe, cudaStream_t st);
+// token -> image attention: kv rows of ld floats (k at column 0, v at column 128), q [n*T][128]; part: n*8*16*T*18 floats; out [n*T][128]
+int t2i_attention(const float* kv, int ld, const float* q, int n, int T, float* part, float* out, cudaStream_t st);
+// image -> token attention: q = columns [q_col, q_col+128) of kvq; tk / tv [n*T][128]; os [n*4096][384] split operand
+int i2t_attention(const float* kvq, int ld, int q_col, const float* tk, const float* tv, int n, int T, bf16* os, cudaStream_t st);
+int heads_upscale(const float* u1, const float* b1, const float* s1, long s1_bs, const float* ln_g, const float* ln_b,
+                  const float* w2, const float* b2, const float* s0, long s0_bs, const float* hyper, float* masks, int* stab,
+                  float delta, int n, cudaStream_t st);
+int heads_select(const float* iou, const float* obj, const float* ptr4, const int* stab, const float* no_obj_ptr, int multimask,
+                 int dynamic, float thresh, float* iou_out, float* ptr_out, float* obj_out, int* sel, int decoder_only, int n,
+                 cudaStream_t st);
+int heads_write_masks(const float* masks, const int* sel, int multimask, float no_obj_score, float* low_multi, float* low_best,
+                      int n, cudaStream_t st);
+}  // namespace sam2b

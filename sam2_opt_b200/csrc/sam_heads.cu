@@ -1,0 +1,669 @@
+// SAM heads: prompt encoder (points), two-way mask decoder, up-scaling + hyper-network masks,
+// IoU / object-score / object-pointer heads -- the kernels around the tcgen05 GEMMs that engine.cu's sam_heads_mb() strings
+// together.  Reference (paths relative to the reference tree's sam2/sam2/): modeling/sam/prompt_encoder.py:70-231,
+// modeling/sam/transformer.py:51-294, modeling/sam/mask_decoder.py:116-316, modeling/sam2_base_official.py:338-494.
+//
+// Numerics: the reference keeps these heads in fp32 (the multimask arg-max runs over near-tied predicted IoUs).  The image
+// side (4096 rows per object) goes through the bf16 tensor cores with BOTH operands split into two bf16 terms,
+// x = hi + lo: A' = [hi | lo | hi], B' = [hi | hi | lo] over 3K columns gives hi*hi + lo*hi + hi*lo with fp32 accumulation,
+// i.e. a relative error of ~2^-16 per product instead of bf16's 2^-8 (the kernels here emit A' directly).  Everything on the
+// token side (<= 32 tokens per object) and every soft-max, LayerNorm and GELU is plain fp32.
+#include <math.h>
+
+#include "ops.h"
+
+namespace sam2b {
+
+namespace {
+
+__device__ __forceinline__ void split2(float x, bf16& hi, bf16& lo) {
+  hi = __float2bfloat16_rn(x);
+  lo = __float2bfloat16_rn(x - __bfloat162float(hi));
+}
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+__device__ __forceinline__ float warp_max(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+  return v;
+}
+__device__ __forceinline__ float gelu_exact(float x) { return 0.5f * x * (1.0f + erff(x * 0.70710678118654752440f)); }
+
+// ---------------------------------------------------------------------------------------------------------------------
+// src = image_embedding + dense prompt embedding (mask_decoder.py:262-266), token-major: keys fp32 [n*4096][256] and the
+// split operand ks [n*4096][768].  pix is addressed as pix[b*sn + c*sc + p*sp] (NCHW: sp == 1; the E3 output
+// [4096][n][256]: sc == 1; sn == 0 repeats one image for every prompt); dense [n][256][4096] or nullptr (no_mask_embed [256]).
+// ---------------------------------------------------------------------------------------------------------------------
+__global__ void heads_prep_src_kernel(const float* __restrict__ pix, long sn, long sc, long sp, const float* __restrict__ dense,
+                                      const float* __restrict__ nomask, float* __restrict__ keys, bf16* __restrict__ ks) {
+  __shared__ float tile[32][33];
+  const int b = blockIdx.z, p0 = blockIdx.x * 32, c0 = blockIdx.y * 32, tx = threadIdx.x, ty = threadIdx.y;
+  const bool chw = (sp == 1);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int c = c0 + ty + 8 * i, p = p0 + tx;
+    float v = 0.f;
+    if (chw) v = pix[b * sn + c * sc + p];
+    if (dense) v += dense[((long)b * 256 + c) * 4096 + p];
+    tile[ty + 8 * i][tx] = v;
+  }
+  __syncthreads();
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int p = p0 + ty + 8 * i, c = c0 + tx;
+    float v = tile[tx][ty + 8 * i];
+    if (!chw) v = pix[b * sn + c * sc + p * sp] + v;
+    if (!dense) v += nomask[c];
+    const long row = (long)b * 4096 + p;
+    keys[row * 256 + c] = v;
+    bf16 hi, lo;
+    split2(v, hi, lo);
+    ks[row * 768 + c] = hi; ks[row * 768 + 256 + c] = lo; ks[row * 768 + 512 + c] = hi;
+  }
+}
+
+// LayerNorm over 256 channels (one warp per row), fp32 out + split operand out (either may be nullptr)
+__global__ void ln256_split_kernel(const float* __restrict__ x, const float* __restrict__ g, const float* __restrict__ be, float eps,
+                                   float* __restrict__ y, bf16* __restrict__ ys, long rows) {
+  const long row = (long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (row >= rows) return;
+  const int lane = threadIdx.x & 31;
+  const float4 a = *reinterpret_cast<const float4*>(x + row * 256 + lane * 4);
+  const float4 c = *reinterpret_cast<const float4*>(x + row * 256 + 128 + lane * 4);
+  float v[8] = {a.x, a.y, a.z, a.w, c.x, c.y, c.z, c.w};
+  float s = 0.f;
+#pragma unroll
+  for (int i = 0; i < 8; ++i) s += v[i];
+  const float mean = warp_sum(s) * (1.0f / 256.0f);
+  float q = 0.f;
+#pragma unroll
+  for (int i = 0; i < 8; ++i) { v[i] -= mean; q += v[i] * v[i]; }
+  const float rstd = rsqrtf(warp_sum(q) * (1.0f / 256.0f) + eps);
+#pragma unroll
+  for (int h = 0; h < 2; ++h) {
+    const int col = h * 128 + lane * 4;
+    const float4 gg = *reinterpret_cast<const float4*>(g + col), bb = *reinterpret_cast<const float4*>(be + col);
+    float o[4] = {v[h * 4 + 0] * rstd * gg.x + bb.x, v[h * 4 + 1] * rstd * gg.y + bb.y, v[h * 4 + 2] * rstd * gg.z + bb.z,
+                  v[h * 4 + 3] * rstd * gg.w + bb.w};
+    if (y) *reinterpret_cast<float4*>(y + row * 256 + col) = make_float4(o[0], o[1], o[2], o[3]);
+    if (ys) {
+      __align__(8) bf16 hi[4], lo[4];
+#pragma unroll
+      for (int i = 0; i < 4; ++i) split2(o[i], hi[i], lo[i]);
+      *reinterpret_cast<uint2*>(ys + row * 768 + col) = *reinterpret_cast<const uint2*>(hi);
+      *reinterpret_cast<uint2*>(ys + row * 768 + 256 + col) = *reinterpret_cast<const uint2*>(lo);
+      *reinterpret_cast<uint2*>(ys + row * 768 + 512 + col) = *reinterpret_cast<const uint2*>(hi);
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// Tokens of every object (prompt_encoder.py:124-150 `_embed_points` with the padding point, mask_decoder.py:235-247):
+// rows 0..5 = obj_score / iou / 4 mask tokens, rows 6..6+P-1 = the points, last row = the padding point (label -1).
+// tok [n][T][256] (queries) and qpe (the same values: the reference's query_pe is the initial point embedding).
+// ---------------------------------------------------------------------------------------------------------------------
+__global__ void heads_tokens_kernel(const float* __restrict__ coords, const int* __restrict__ labels, int P,
+                                    const float* __restrict__ gauss /*[2][128]*/, const float* __restrict__ not_a_point,
+                                    const float* __restrict__ pt_emb0, const float* __restrict__ pt_emb1,
+                                    const float* __restrict__ pt_emb2, const float* __restrict__ pt_emb3,
+                                    const float* __restrict__ obj_tok, const float* __restrict__ iou_tok,
+                                    const float* __restrict__ mask_toks /*[4][256]*/, float* __restrict__ tok, float* __restrict__ qpe) {
+  const int b = blockIdx.x, c = threadIdx.x, T = 6 + P + 1;
+  float* t0 = tok + (long)b * T * 256;
+  float* q0 = qpe + (long)b * T * 256;
+  for (int r = 0; r < T; ++r) {
+    float v;
+    if (r == 0) v = obj_tok[c];
+    else if (r == 1) v = iou_tok[c];
+    else if (r < 6) v = mask_toks[(r - 2) * 256 + c];
+    else {
+      const int i = r - 6;
+      const int lab = (i < P) ? labels[b * P + i] : -1;
+      if (lab == -1) v = not_a_point[c];
+      else {
+        // pe_layer._pe_encoding (position_encoding.py:146-154): coords in [0,1] -> [-1,1] -> @ gaussian matrix -> 2 pi -> sin | cos
+        const float x = 2.0f * ((coords[(b * P + i) * 2 + 0] + 0.5f) / 1024.0f) - 1.0f;
+        const float y = 2.0f * ((coords[(b * P + i) * 2 + 1] + 0.5f) / 1024.0f) - 1.0f;
+        const int j = c & 127;
+        const float ang = 6.283185307179586f * (x * gauss[j] + y * gauss[128 + j]);
+        v = (c < 128) ? sinf(ang) : cosf(ang);
+        const float* e = lab == 0 ? pt_emb0 : lab == 1 ? pt_emb1 : lab == 2 ? pt_emb2 : pt_emb3;
+        if (lab >= 0 && lab <= 3) v += e[c];
+      }
+    }
+    t0[r * 256 + c] = v;
+    q0[r * 256 + c] = v;
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// Small fp32 linear layers on the token side, several independent problems ("jobs") per launch:
+//   Y[r][j] = act( sum_k (X[r][k] + X2[r][k]) * W[j][k] + b[j] ),  r < rows, j < N, K % 32 == 0.
+// A job may be one K slice of a larger problem (split K: the partial sums are added by tok_sum_res_ln_kernel).
+// Tile: 16 rows x 64 columns per CTA, 32-wide K chunks through shared memory.
+// ---------------------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) tok_linear_kernel(const __grid_constant__ LinJobs jobs) {
+  const LinJob& J = jobs.j[blockIdx.z];
+  const int n0 = blockIdx.x * 64, r0 = blockIdx.y * 16;
+  if (n0 >= J.N || r0 >= J.rows) return;
+  __shared__ float Xs[16][33];
+  __shared__ float Ws[64][33];
+  const int tid = threadIdx.x, tr = tid >> 4, tc = tid & 15;
+  float acc[4] = {0.f, 0.f, 0.f, 0.f};
+  for (int k0 = 0; k0 < J.K; k0 += 32) {
+    {
+      const int kk = tid & 31;
+#pragma unroll
+      for (int i = 0; i < 2; ++i) {
+        const int r = (tid >> 5) + 8 * i;
+        float v = 0.f;
+        if (r0 + r < J.rows) {
+          v = J.X[(long)(r0 + r) * J.ldx + k0 + kk];
+          if (J.X2) v += J.X2[(long)(r0 + r) * J.ldx2 + k0 + kk];
+        }
+        Xs[r][kk] = v;
+      }
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        const int j = (tid >> 5) + 8 * i;
+        Ws[j][kk] = (n0 + j < J.N) ? J.W[(long)(n0 + j) * J.ldw + k0 + kk] : 0.f;
+      }
+    }
+    __syncthreads();
+#pragma unroll
+    for (int kk = 0; kk < 32; ++kk) {
+      const float x = Xs[tr][kk];
+#pragma unroll
+      for (int jj = 0; jj < 4; ++jj) acc[jj] = fmaf(x, Ws[tc + 16 * jj][kk], acc[jj]);
+    }
+    __syncthreads();
+  }
+  if (r0 + tr >= J.rows) return;
+#pragma unroll
+  for (int jj = 0; jj < 4; ++jj) {
+    const int j = n0 + tc + 16 * jj;
+    if (j >= J.N) continue;
+    float v = acc[jj] + (J.b ? J.b[j] : 0.f);
+    if (J.act == 1) v = fmaxf(v, 0.f);
+    else if (J.act == 2) v = 1.0f / (1.0f + expf(-v));
+    J.Y[(long)(r0 + tr) * J.ldy + j] = v;
+  }
+}
+
+// Y[r][:] = LN( sum_s part[s][r][:] + bias + residual[r][:] )  over 256 columns (one warp per row; LN optional: g == nullptr)
+__global__ void tok_sum_res_ln_kernel(const float* __restrict__ part, long part_stride, int S, const float* __restrict__ bias,
+                                      const float* __restrict__ res, const float* __restrict__ g, const float* __restrict__ be,
+                                      float eps, float* __restrict__ y, int rows) {
+  const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (row >= rows) return;
+  const int lane = threadIdx.x & 31;
+  float v[8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    const int c = (i >> 2) * 128 + lane * 4 + (i & 3);
+    float a = 0.f;
+    for (int s = 0; s < S; ++s) a += part[s * part_stride + (long)row * 256 + c];
+    a += bias[c];
+    if (res) a += res[(long)row * 256 + c];
+    v[i] = a;
+  }
+  if (g) {
+    float s = 0.f;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) s += v[i];
+    const float mean = warp_sum(s) * (1.0f / 256.0f);
+    float q = 0.f;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) { v[i] -= mean; q += v[i] * v[i]; }
+    const float rstd = rsqrtf(warp_sum(q) * (1.0f / 256.0f) + eps);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      const int c = (i >> 2) * 128 + lane * 4 + (i & 3);
+      v[i] = v[i] * rstd * g[c] + be[c];
+    }
+  }
+#pragma unroll
+  for (int i = 0; i < 8; ++i) y[(long)row * 256 + (i >> 2) * 128 + lane * 4 + (i & 3)] = v[i];
+}
+
+// Self-attention over the T <= 32 tokens of one object (transformer.py:222-294 with 8 heads of 32): one CTA per object,
+// one warp per head, lane = query.  q, k, v, o: [n*T][256].
+__global__ void __launch_bounds__(256) tok_self_attn_kernel(const float* __restrict__ q, const float* __restrict__ k,
+                                                            const float* __restrict__ v, int T, float* __restrict__ o) {
+  __shared__ float sm[32 * 256];
+  const int b = blockIdx.x, tid = threadIdx.x, h = tid >> 5, t = tid & 31;
+  const long base = (long)b * T * 256;
+  for (int i = tid; i < T * 256; i += 256) sm[i] = k[base + i];
+  float qr[32], s[32];
+  if (t < T) {
+#pragma unroll
+    for (int d = 0; d < 32; ++d) qr[d] = q[base + t * 256 + h * 32 + d] * 0.17677669529663687f;   // 1 / sqrt(32)
+  } else {
+#pragma unroll
+    for (int d = 0; d < 32; ++d) qr[d] = 0.f;
+  }
+  __syncthreads();
+  float m = -INFINITY;
+#pragma unroll
+  for (int j = 0; j < 32; ++j) {
+    float a = -INFINITY;
+    if (j < T) {
+      a = 0.f;
+#pragma unroll
+      for (int d = 0; d < 32; ++d) a = fmaf(qr[d], sm[j * 256 + h * 32 + d], a);
+    }
+    s[j] = a;
+    m = fmaxf(m, a);
+  }
+  float l = 0.f;
+#pragma unroll
+  for (int j = 0; j < 32; ++j) { s[j] = (j < T) ? expf(s[j] - m) : 0.f; l += s[j]; }
+  __syncthreads();
+  for (int i = tid; i < T * 256; i += 256) sm[i] = v[base + i];
+  __syncthreads();
+  float acc[32];
+#pragma unroll
+  for (int d = 0; d < 32; ++d) acc[d] = 0.f;
+#pragma unroll
+  for (int j = 0; j < 32; ++j) {
+    if (j < T) {
+#pragma unroll
+      for (int d = 0; d < 32; ++d) acc[d] = fmaf(s[j], sm[j * 256 + h * 32 + d], acc[d]);
+    }
+  }
+  if (t < T) {
+    const float inv = 1.0f / l;
+#pragma unroll
+    for (int d = 0; d < 32; ++d) o[base + t * 256 + h * 32 + d] = acc[d] * inv;
+  }
+}
+
+// Token -> image cross-attention (8 heads of 16 over the 4096 image keys): one CTA per (256-key split, head, object), one key
+// per thread held in registers for all T queries.  kv: fp32 rows of `ld` floats with k at column 0 and v at column 128;
+// q [n*T][128].  part [n][8][16][T][18] = (max, sum, 16 un-normalised outputs) per split.
+__global__ void __launch_bounds__(256) t2i_partial_kernel(const float* __restrict__ kv, int ld, const float* __restrict__ q, int T,
+                                                          float* __restrict__ part) {
+  __shared__ float qs[32][16];
+  __shared__ float red[8][32][18];
+  const int s = blockIdx.x, h = blockIdx.y, b = blockIdx.z, tid = threadIdx.x, w = tid >> 5, lane = tid & 31;
+  for (int i = tid; i < T * 16; i += 256) qs[i >> 4][i & 15] = q[((long)b * T + (i >> 4)) * 128 + h * 16 + (i & 15)] * 0.25f;
+  const float* row = kv + ((long)b * 4096 + s * 256 + tid) * ld + h * 16;
+  float kr[16], vr[16];
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const float4 a = *reinterpret_cast<const float4*>(row + 4 * i), c = *reinterpret_cast<const float4*>(row + 128 + 4 * i);
+    kr[4 * i] = a.x; kr[4 * i + 1] = a.y; kr[4 * i + 2] = a.z; kr[4 * i + 3] = a.w;
+    vr[4 * i] = c.x; vr[4 * i + 1] = c.y; vr[4 * i + 2] = c.z; vr[4 * i + 3] = c.w;
+  }
+  __syncthreads();
+  for (int t = 0; t < T; ++t) {
+    float a = 0.f;
+#pragma unroll
+    for (int d = 0; d < 16; ++d) a = fmaf(qs[t][d], kr[d], a);
+    const float m = warp_max(a);
+    const float p = expf(a - m);
+    const float l = warp_sum(p);
+    if (lane == 0) { red[w][t][0] = m; red[w][t][1] = l; }
+#pragma unroll
+    for (int d = 0; d < 16; ++d) {
+      const float o = warp_sum(p * vr[d]);
+      if (lane == 0) red[w][t][2 + d] = o;
+    }
+  }
+  __syncthreads();
+  float* dst = part + (((long)(b * 8 + h) * 16 + s) * T) * 18;
+  for (int i = tid; i < T * 16; i += 256) {
+    const int t = i >> 4, d = i & 15;
+    float M = -INFINITY;
+#pragma unroll
+    for (int ww = 0; ww < 8; ++ww) M = fmaxf(M, red[ww][t][0]);
+    float L = 0.f, O = 0.f;
+#pragma unroll
+    for (int ww = 0; ww < 8; ++ww) {
+      const float e = expf(red[ww][t][0] - M);
+      L = fmaf(red[ww][t][1], e, L);
+      O = fmaf(red[ww][t][2 + d], e, O);
+    }
+    dst[t * 18 + 2 + d] = O;
+    if (d == 0) { dst[t * 18] = M; dst[t * 18 + 1] = L; }
+  }
+}
+
+// merge the 16 key splits: out [n*T][128], column = head * 16 + d
+__global__ void t2i_combine_kernel(const float* __restrict__ part, int T, float* __restrict__ out, int total) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= total) return;
+  const int d = i & 15, h = (i >> 4) & 7, bt = i >> 7, b = bt / T, t = bt % T;
+  const float* p = part + (((long)(b * 8 + h) * 16) * T + t) * 18;
+  const long ss = (long)T * 18;
+  float M = -INFINITY;
+  for (int s = 0; s < 16; ++s) M = fmaxf(M, p[s * ss]);
+  float L = 0.f, O = 0.f;
+  for (int s = 0; s < 16; ++s) {
+    const float e = expf(p[s * ss] - M);
+    L = fmaf(p[s * ss + 1], e, L);
+    O = fmaf(p[s * ss + 2 + d], e, O);
+  }
+  out[i] = O / L;
+}
+
+// Image -> token cross-attention: every pixel attends to the T tokens (8 heads of 16).  One thread per (pixel, head);
+// q = columns [q_col, q_col + 128) of the fp32 rows `kvq` (ld floats); tk, tv [n*T][128] (token keys / values).
+// Output: the split operand os [n*4096][384] = [hi | lo | hi] of the 128 attention outputs (A of the out_proj GEMM).
+__global__ void __launch_bounds__(256) i2t_attn_kernel(const float* __restrict__ kvq, int ld, int q_col, const float* __restrict__ tk,
+                                                       const float* __restrict__ tv, int T, bf16* __restrict__ os) {
+  __shared__ float ks[32 * 128];
+  __shared__ float vs[32 * 128];
+  const int b = blockIdx.y, tid = threadIdx.x;
+  for (int i = tid; i < T * 128; i += 256) { ks[i] = tk[(long)b * T * 128 + i]; vs[i] = tv[(long)b * T * 128 + i]; }
+  __syncthreads();
+  const int h = tid & 7, p = blockIdx.x * 32 + (tid >> 3);
+  const long row = (long)b * 4096 + p;
+  const float* qp = kvq + row * ld + q_col + h * 16;
+  float qr[16];
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const float4 a = *reinterpret_cast<const float4*>(qp + 4 * i);
+    qr[4 * i] = a.x * 0.25f; qr[4 * i + 1] = a.y * 0.25f; qr[4 * i + 2] = a.z * 0.25f; qr[4 * i + 3] = a.w * 0.25f;
+  }
+  float m = -INFINITY, l = 0.f, acc[16];
+#pragma unroll
+  for (int d = 0; d < 16; ++d) acc[d] = 0.f;
+  // two passes over the (few) tokens: exact max first, then the weighted sum
+  for (int t = 0; t < T; ++t) {
+    float a = 0.f;
+#pragma unroll
+    for (int d = 0; d < 16; ++d) a = fmaf(qr[d], ks[t * 128 + h * 16 + d], a);
+    m = fmaxf(m, a);
+  }
+  for (int t = 0; t < T; ++t) {
+    float a = 0.f;
+#pragma unroll
+    for (int d = 0; d < 16; ++d) a = fmaf(qr[d], ks[t * 128 + h * 16 + d], a);
+    const float e = expf(a - m);
+    l += e;
+#pragma unroll
+    for (int d = 0; d < 16; ++d) acc[d] = fmaf(e, vs[t * 128 + h * 16 + d], acc[d]);
+  }
+  const float inv = 1.0f / l;
+  __align__(16) bf16 hi[16], lo[16];
+#pragma unroll
+  for (int d = 0; d < 16; ++d) split2(acc[d] * inv, hi[d], lo[d]);
+  bf16* o = os + row * 384 + h * 16;
+#pragma unroll
+  for (int i = 0; i < 2; ++i) {
+    reinterpret_cast<uint4*>(o)[i] = reinterpret_cast<const uint4*>(hi)[i];
+    reinterpret_cast<uint4*>(o + 128)[i] = reinterpret_cast<const uint4*>(lo)[i];
+    reinterpret_cast<uint4*>(o + 256)[i] = reinterpret_cast<const uint4*>(hi)[i];
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// Up-scaling tail (mask_decoder.py:283-300): u1 [n*4096][256 = (dy,dx,c)] is ConvTranspose2d(256 -> 64, k2 s2) of the
+// final keys (a GEMM); per 128x128 position: + feat_s1, LayerNorm2d(64), GELU, ConvTranspose2d(64 -> 32, k2 s2), + feat_s0, GELU,
+// then the 4 hyper-network dot products -> masks [n][4][256][256].  The 32-channel 256x256 map never exists.
+// One thread per (object, 128x128 position); w2 [64][4 = (ey,ex)][32] and the biases live in shared memory.
+// stab [n][2]: number of pixels of mask 0 above +delta / above -delta (mask_decoder.py:320-335), only if stab != nullptr.
+// ---------------------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) heads_upscale_kernel(const float* __restrict__ u1, const float* __restrict__ b1 /*[64]*/,
+                                                            const float* __restrict__ s1, long s1_bs, const float* __restrict__ ln_g,
+                                                            const float* __restrict__ ln_b, const float* __restrict__ w2,
+                                                            const float* __restrict__ b2 /*[32]*/, const float* __restrict__ s0,
+                                                            long s0_bs, const float* __restrict__ hyper /*[n][4][32]*/,
+                                                            float* __restrict__ masks, int* __restrict__ stab, float delta) {
+  extern __shared__ float smem[];
+  float* w2s = smem;              // [64][4][32]
+  float* hs = w2s + 64 * 128;     // [4][32]
+  float* b2s = hs + 128;          // [32]
+  const int b = blockIdx.y, tid = threadIdx.x;
+  for (int i = tid; i < 64 * 128; i += 256) w2s[i] = w2[i];
+  if (tid < 128) hs[tid] = hyper[(long)b * 128 + tid];
+  if (tid < 32) b2s[tid] = b2[tid];
+  __syncthreads();
+  const int pos = blockIdx.x * 256 + tid;          // 0 .. 16383 on the 128 x 128 grid
+  const int y1 = pos >> 7, x1 = pos & 127;
+  const long pix = (long)b * 4096 + (y1 >> 1) * 64 + (x1 >> 1);
+  const float* up = u1 + pix * 256 + ((y1 & 1) * 2 + (x1 & 1)) * 64;
+  const float* f1 = s1 + b * s1_bs + (long)y1 * 128 + x1;
+  float x[64];
+  float sum = 0.f;
+#pragma unroll
+  for (int c4 = 0; c4 < 16; ++c4) {
+    const float4 a = *reinterpret_cast<const float4*>(up + 4 * c4);
+    x[4 * c4 + 0] = a.x + b1[4 * c4 + 0] + f1[(long)(4 * c4 + 0) * 16384];
+    x[4 * c4 + 1] = a.y + b1[4 * c4 + 1] + f1[(long)(4 * c4 + 1) * 16384];
+    x[4 * c4 + 2] = a.z + b1[4 * c4 + 2] + f1[(long)(4 * c4 + 2) * 16384];
+    x[4 * c4 + 3] = a.w + b1[4 * c4 + 3] + f1[(long)(4 * c4 + 3) * 16384];
+  }
+#pragma unroll
+  for (int c = 0; c < 64; ++c) sum += x[c];
+  const float mean = sum * (1.0f / 64.0f);
+  float var = 0.f;
+#pragma unroll
+  for (int c = 0; c < 64; ++c) { x[c] -= mean; var = fmaf(x[c], x[c], var); }
+  const float rstd = 1.0f / sqrtf(var * (1.0f / 64.0f) + 1e-6f);
+#pragma unroll
+  for (int c = 0; c < 64; ++c) x[c] = gelu_exact(ln_g[c] * (x[c] * rstd) + ln_b[c]);
+  int cnt_hi = 0, cnt_lo = 0;
+  for (int q = 0; q < 4; ++q) {
+    float acc[32];
+#pragma unroll
+    for (int o = 0; o < 32; ++o) acc[o] = b2s[o];
+#pragma unroll
+    for (int c = 0; c < 64; ++c) {
+      const float4* wr = reinterpret_cast<const float4*>(w2s + (c * 4 + q) * 32);
+#pragma unroll
+      for (int o4 = 0; o4 < 8; ++o4) {
+        const float4 wv = wr[o4];
+        acc[4 * o4 + 0] = fmaf(x[c], wv.x, acc[4 * o4 + 0]);
+        acc[4 * o4 + 1] = fmaf(x[c], wv.y, acc[4 * o4 + 1]);
+        acc[4 * o4 + 2] = fmaf(x[c], wv.z, acc[4 * o4 + 2]);
+        acc[4 * o4 + 3] = fmaf(x[c], wv.w, acc[4 * o4 + 3]);
+      }
+    }
+    const int y2 = 2 * y1 + (q >> 1), x2 = 2 * x1 + (q & 1);
+    const float* f0 = s0 + b * s0_bs + (long)y2 * 256 + x2;
+    float m[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+    for (int o = 0; o < 32; ++o) {
+      const float gv = gelu_exact(acc[o] + f0[(long)o * 65536]);
+#pragma unroll
+      for (int k = 0; k < 4; ++k) m[k] = fmaf(hs[k * 32 + o], gv, m[k]);
+    }
+#pragma unroll
+    for (int k = 0; k < 4; ++k) masks[(((long)b * 4 + k) * 256 + y2) * 256 + x2] = m[k];
+    cnt_hi += (m[0] > delta);
+    cnt_lo += (m[0] > -delta);
+  }
+  if (stab) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      cnt_hi += __shfl_xor_sync(0xffffffffu, cnt_hi, o);
+      cnt_lo += __shfl_xor_sync(0xffffffffu, cnt_lo, o);
+    }
+    if ((tid & 31) == 0) { atomicAdd(stab + b * 2, cnt_hi); atomicAdd(stab + b * 2 + 1, cnt_lo); }
+  }
+}
+
+// Per object: which of the 4 masks is returned / tracked, the IoU outputs and the object pointer
+// (mask_decoder.py:192-224,337-382; sam2_base_official.py:435-494).  One CTA of 256 threads per object.
+// sel [n][4]: sel[0] = index of the best (tracked) mask among the 4, sel[1] = is_obj.
+__global__ void heads_select_kernel(const float* __restrict__ iou /*[n][4]*/, const float* __restrict__ obj /*[n]*/,
+                                    const float* __restrict__ ptr4 /*[n][4][256]*/, const int* __restrict__ stab,
+                                    const float* __restrict__ no_obj_ptr, int multimask, int dynamic, float thresh,
+                                    float* __restrict__ iou_out, float* __restrict__ ptr_out, float* __restrict__ obj_out,
+                                    int* __restrict__ sel, int decoder_only) {
+  const int b = blockIdx.x, c = threadIdx.x;
+  const float i0 = iou[b * 4], i1 = iou[b * 4 + 1], i2 = iou[b * 4 + 2], i3 = iou[b * 4 + 3];
+  int best = 1;                                   // torch.argmax: the first maximum
+  float bi = i1;
+  if (i2 > bi) { bi = i2; best = 2; }
+  if (i3 > bi) { bi = i3; best = 3; }
+  const bool is_obj = obj[b] > 0.f;
+  int mask_idx, tok_idx;
+  if (multimask) {
+    mask_idx = best; tok_idx = best;
+    if (c < 3) iou_out[b * 3 + c] = (c == 0) ? i1 : (c == 1) ? i2 : i3;
+  } else {
+    mask_idx = 0; tok_idx = 0;
+    float io = i0;
+    if (dynamic) {
+      const float ai = (float)stab[b * 2], au = (float)stab[b * 2 + 1];
+      const float score = au > 0.f ? ai / au : 1.0f;
+      if (!(score >= thresh)) { mask_idx = best; io = bi; }
+    }
+    if (c == 0) iou_out[b] = io;
+  }
+  const float lam = is_obj ? 1.0f : 0.0f;
+  ptr_out[(long)b * 256 + c] = lam * ptr4[((long)b * 4 + tok_idx) * 256 + c] + (1.0f - lam) * no_obj_ptr[c];
+  // decoder_only: the plain SamMaskDecoder.forward outputs, without _forward_sam_heads' NO_OBJ_SCORE fill
+  if (c == 0) { sel[b * 4] = mask_idx; sel[b * 4 + 1] = (is_obj || decoder_only) ? 1 : 0; obj_out[b] = obj[b]; }
+}
+
+// low_multi [n][M][256][256] = is_obj ? masks[b][k] : NO_OBJ_SCORE  (k = 1..3 for multimask, the selected mask otherwise);
+// low_best [n][1][256][256] = the selected mask.  4 pixels per thread.
+__global__ void heads_write_masks_kernel(const float* __restrict__ masks, const int* __restrict__ sel, int multimask,
+                                         float no_obj_score, float* __restrict__ low_multi, float* __restrict__ low_best) {
+  const int b = blockIdx.y;
+  const int i = (blockIdx.x * blockDim.x + threadIdx.x) * 4;
+  const int best = sel[b * 4];
+  const bool is_obj = sel[b * 4 + 1] != 0;
+  const float4 fill = make_float4(no_obj_score, no_obj_score, no_obj_score, no_obj_score);
+  const float* mb = masks + (long)b * 4 * 65536;
+  if (multimask) {
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+      const float4 v = is_obj ? *reinterpret_cast<const float4*>(mb + (long)(k + 1) * 65536 + i) : fill;
+      if (low_multi) *reinterpret_cast<float4*>(low_multi + ((long)b * 3 + k) * 65536 + i) = v;
+      if (low_best && k + 1 == best) *reinterpret_cast<float4*>(low_best + (long)b * 65536 + i) = v;
+    }
+  } else {
+    const float4 v = is_obj ? *reinterpret_cast<const float4*>(mb + (long)best * 65536 + i) : fill;
+    if (low_multi) *reinterpret_cast<float4*>(low_multi + (long)b * 65536 + i) = v;
+    if (low_best) *reinterpret_cast<float4*>(low_best + (long)b * 65536 + i) = v;
+  }
+}
+
+}  // namespace
+
+// ---------------------------------------------------------------------------------------------------------------------
+// host launchers
+// ---------------------------------------------------------------------------------------------------------------------
+int heads_prep_src(const float* pix, long sn, long sc, long sp, const float* dense, const float* nomask, float* keys, bf16* ks,
+                   int n, cudaStream_t st) {
+  if (sp != 1 && sc != 1) { set_error("sam heads: image embedding must be contiguous along pixels or along channels"); return 1; }
+  ProfRange pr(st, "heads_prep_src", 0, (double)n * 4096 * 256 * (4 + 4 + 6));
+  heads_prep_src_kernel<<<dim3(128, 8, n), dim3(32, 8), 0, st>>>(pix, sn, sc, sp, dense, nomask, keys, ks);
+  SAM2B_CHECK_LAUNCH("heads_prep_src");
+  return 0;
+}
+
+int ln256_split(const float* x, const float* g, const float* b, float eps, float* y, bf16* ys, long rows, cudaStream_t st) {
+  ProfRange pr(st, "heads_ln256_split", 0, (double)rows * 256 * (4 + 4 + 6));
+  ln256_split_kernel<<<(unsigned)((rows + 7) / 8), 256, 0, st>>>(x, g, b, eps, y, ys, rows);
+  SAM2B_CHECK_LAUNCH("ln256_split");
+  return 0;
+}
+
+int heads_tokens(const float* coords, const int* labels, int P, int n, const float* gauss, const float* not_a_point,
+                 const float* const pt_emb[4], const float* obj_tok, const float* iou_tok, const float* mask_toks, float* tok,
+                 float* qpe, cudaStream_t st) {
+  ProfRange pr(st, "heads_tokens", 0, 0);
+  heads_tokens_kernel<<<n, 256, 0, st>>>(coords, labels, P, gauss, not_a_point, pt_emb[0], pt_emb[1], pt_emb[2], pt_emb[3], obj_tok,
+                                         iou_tok, mask_toks, tok, qpe);
+  SAM2B_CHECK_LAUNCH("heads_tokens");
+  return 0;
+}
+
+int tok_linear(const LinJobs& jobs, int njobs, cudaStream_t st) {
+  if (njobs <= 0 || njobs > LinJobs::kMax) { set_error("tok_linear: %d jobs (1..%d)", njobs, LinJobs::kMax); return 1; }
+  int max_n = 0, max_r = 0;
+  double flops = 0;
+  for (int i = 0; i < njobs; ++i) {
+    const LinJob& j = jobs.j[i];
+    if (j.K % 32 || j.rows <= 0 || j.N <= 0) { set_error("tok_linear: job %d rows=%d N=%d K=%d (K %% 32 == 0)", i, j.rows, j.N, j.K); return 1; }
+    max_n = j.N > max_n ? j.N : max_n;
+    max_r = j.rows > max_r ? j.rows : max_r;
+    flops += 2.0 * j.rows * j.N * j.K;
+  }
+  ProfRange pr(st, "heads_tok_linear", flops, 0);
+  tok_linear_kernel<<<dim3((max_n + 63) / 64, (max_r + 15) / 16, njobs), 256, 0, st>>>(jobs);
+  SAM2B_CHECK_LAUNCH("tok_linear");
+  return 0;
+}
+
+int tok_sum_res_ln(const float* part, long part_stride, int S, const float* bias, const float* res, const float* g,
+                   const float* be, float eps, float* y, int rows, cudaStream_t st) {
+  ProfRange pr(st, "heads_tok_sum_res_ln", 0, 0);
+  tok_sum_res_ln_kernel<<<(rows + 7) / 8, 256, 0, st>>>(part, part_stride, S, bias, res, g, be, eps, y, rows);
+  SAM2B_CHECK_LAUNCH("tok_sum_res_ln");
+  return 0;
+}
+
+int tok_self_attn(const float* q, const float* k, const float* v, int n, int T, float* o, cudaStream_t st) {
+  ProfRange pr(st, "heads_tok_self_attn", 0, 0);
+  tok_self_attn_kernel<<<n, 256, 0, st>>>(q, k, v, T, o);
+  SAM2B_CHECK_LAUNCH("tok_self_attn");
+  return 0;
+}
+
+int t2i_attention(const float* kv, int ld, const float* q, int n, int T, float* part, float* out, cudaStream_t st) {
+  {
+    ProfRange pr(st, "heads_t2i_partial", 4.0 * n * T * 4096 * 128, (double)n * 4096 * 256 * 4);
+    t2i_partial_kernel<<<dim3(16, 8, n), 256, 0, st>>>(kv, ld, q, T, part);
+    SAM2B_CHECK_LAUNCH("t2i_partial");
+  }
+  ProfRange pr(st, "heads_t2i_combine", 0, 0);
+  const int total = n * T * 128;
+  t2i_combine_kernel<<<(total + 255) / 256, 256, 0, st>>>(part, T, out, total);
+  SAM2B_CHECK_LAUNCH("t2i_combine");
+  return 0;
+}
+
+int i2t_attention(const float* kvq, int ld, int q_col, const float* tk, const float* tv, int n, int T, bf16* os, cudaStream_t st) {
+  ProfRange pr(st, "heads_i2t_attn", 4.0 * n * T * 4096 * 128, (double)n * 4096 * (128 * 4 + 384 * 2));
+  i2t_attn_kernel<<<dim3(128, n), 256, 0, st>>>(kvq, ld, q_col, tk, tv, T, os);
+  SAM2B_CHECK_LAUNCH("i2t_attn");
+  return 0;
+}
+
+int heads_upscale(const float* u1, const float* b1, const float* s1, long s1_bs, const float* ln_g, const float* ln_b,
+                  const float* w2, const float* b2, const float* s0, long s0_bs, const float* hyper, float* masks, int* stab,
+                  float delta, int n, cudaStream_t st) {
+  static PerDeviceFlag attr;
+  const int smem = (64 * 128 + 128 + 32) * 4;
+  if (!attr.is_set()) {
+    if (cudaFuncSetAttribute(heads_upscale_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem) != cudaSuccess) {
+      set_error("heads_upscale: cannot set the shared-memory size");
+      return 1;
+    }
+    attr.set();
+  }
+  ProfRange pr(st, "heads_upscale", 2.0 * n * 16384 * (64.0 * 128 + 4 * 32), (double)n * (4096.0 * 256 + 4 * 65536) * 4);
+  heads_upscale_kernel<<<dim3(64, n), 256, smem, st>>>(u1, b1, s1, s1_bs, ln_g, ln_b, w2, b2, s0, s0_bs, hyper, masks, stab, delta);
+  SAM2B_CHECK_LAUNCH("heads_upscale");
+  return 0;
+}
+
+int heads_select(const float* iou, const float* obj, const float* ptr4, const int* stab, const float* no_obj_ptr, int multimask,
+                 int dynamic, float thresh, float* iou_out, float* ptr_out, float* obj_out, int* sel, int decoder_only, int n,
+                 cudaStream_t st) {
+  ProfRange pr(st, "heads_select", 0, 0);
+  heads_select_kernel<<<n, 256, 0, st>>>(iou, obj, ptr4, stab, no_obj_ptr, multimask, dynamic, thresh, iou_out, ptr_out, obj_out, sel,
+                                         decoder_only);
+  SAM2B_CHECK_LAUNCH("heads_select");
+  return 0;
+}
+
+int heads_write_masks(const float* masks, const int* sel, int multimask, float no_obj_score, float* low_multi, float* low_best,
+                      int n, cudaStream_t st) {
+  ProfRange pr(st, "heads_write_masks", 0, (double)n * 65536 * 4 * 5);
+  heads_write_masks_kernel<<<dim3(64, n), 256, 0, st>>>(masks, sel, multimask, no_obj_score, low_multi, low_best);
+  SAM2B_CHECK_LAUNCH("heads_write_masks");
+  return 0;
+}
+
+}  // namespace sam2b

@@ -208,6 +208,56 @@ class Engine:
                        "memory_encode")
         return x, self.position_encoding(64, 64, n)
 
+    # -- SAM heads --------------------------------------------------------------------------
+    def sam_heads(self, backbone_features, high_res_features, point_coords=None, point_labels=None, dense_embedding=None,
+                  multimask_output=False, decoder_only=False, high_res=True, high_res_multimasks=False):
+        """Prompt encoder (points) + mask decoder + object-pointer head for n prompts / objects in one library call
+        (ref: sam2_base_official.py:338-494).  backbone_features [n,256,64,64] may be any view whose channel or pixel
+        dimension is contiguous (the permuted E3 output, an expanded single image ...); high_res_features = [fpn0, fpn1]
+        with batch 1 (shared) or n.  point_coords [n,P,2] / point_labels [n,P] or None (a tracked frame).
+        -> (low_res_multimasks [n,M,256,256], high_res_multimasks or None, ious [n,M], low_res_masks [n,1,256,256],
+            high_res_masks [n,1,1024,1024] or None, obj_ptr [n,256], object_score_logits [n,1])"""
+        bf = backbone_features
+        if not bf.is_cuda or bf.dtype != torch.float32:
+            raise RuntimeError("sam_heads: expected a CUDA fp32 tensor (sam2_opt_b200 has no CPU path)")
+        if bf.dim() != 4 or tuple(bf.shape[1:]) != (256, 64, 64):
+            raise ValueError(f"sam_heads expects backbone_features [n,256,64,64], got {tuple(bf.shape)}")
+        n = bf.shape[0]
+        sn, sc, sy, sx = bf.stride()
+        if sy != 64 * sx or (sx != 1 and sc != 1):
+            bf = bf.contiguous()
+            sn, sc, sy, sx = bf.stride()
+        if n == 1:
+            sn = 0
+        hr = []
+        for f, shp in zip(high_res_features, ((32, 256, 256), (64, 128, 128))):
+            if tuple(f.shape[1:]) != shp or f.shape[0] not in (1, n):
+                raise ValueError(f"sam_heads: high-res feature {tuple(f.shape)} does not match [1|{n},{shp}]")
+            if f.dtype != torch.float32 or f.stride()[1:] != (shp[1] * shp[2], shp[2], 1):
+                f = f.float().contiguous()
+            hr.append((f, 0 if f.shape[0] == 1 else f.stride(0)))
+        P = 0
+        if point_coords is not None:
+            point_coords = _f32c(point_coords, "point_coords").reshape(n, -1, 2)
+            P = point_coords.shape[1]
+            point_labels = point_labels.to(torch.int32).contiguous().reshape(n, P)
+        if dense_embedding is not None:
+            dense_embedding = _f32c(dense_embedding, "dense_embedding")
+            if tuple(dense_embedding.shape) != (n, 256, 64, 64):
+                raise ValueError(f"sam_heads: dense_embedding {tuple(dense_embedding.shape)} != {(n, 256, 64, 64)}")
+        M = 3 if multimask_output else 1
+        new = lambda *shape: torch.empty(shape, device=self.device, dtype=torch.float32)
+        low_multi, ious, low, ptr, obj = new(n, M, 256, 256), new(n, M), new(n, 1, 256, 256), new(n, 256), new(n, 1)
+        high = new(n, 1, 1024, 1024) if high_res else None
+        high_multi = new(n, M, 1024, 1024) if high_res_multimasks else None
+        with self._lock:
+            _lib.check(self.lib.sam2b_sam_heads(
+                self._h, _ptr(bf), sn, sc, sx, _ptr(hr[0][0]), hr[0][1], _ptr(hr[1][0]), hr[1][1],
+                _ptr(point_coords if P else None), _ptr(point_labels if P else None), P, _ptr(dense_embedding), n,
+                int(bool(multimask_output)), int(bool(decoder_only)), _ptr(low_multi), _ptr(high_multi), _ptr(ious), _ptr(low),
+                _ptr(high), _ptr(ptr), _ptr(obj), self._stream()), "sam_heads")
+        return low_multi, high_multi, ious, low, high, ptr, obj
+
     # -- life cycle ------------------------------------------------------------------------------------------
     def release(self):
         """Idempotent (ref: TensorRTExecutor.Release also runs from __del__, tensorrt_executor.py:311-334)."""

@@ -30,13 +30,16 @@ IMG_STD = (0.229, 0.224, 0.225)
 
 
 class _Base:
-    def __init__(self, state_dict: Dict[str, torch.Tensor], device="cuda", backend="b200"):
+    def __init__(self, state_dict: Dict[str, torch.Tensor], device="cuda", backend="b200", native_heads=True):
         from .engine import normalise_device
         self.device = normalise_device(device)     # "cuda" -> the current device, once (torchrun: cuda:LOCAL_RANK)
         self.w = {k: v.detach().to(self.device, torch.float32).contiguous() for k, v in state_dict.items() if torch.is_tensor(v)}
         self.engine = None
         self.backend_contexts: List[B200Executor] = []
         self._dense_pe = H.dense_pe(self.w)
+        # prompt encoder / mask decoder / pointer head inside libsam2b (Engine.sam_heads); False keeps the
+        # fp32 torch restatement (sam_heads.py), which the GPU tests compare against
+        self.native_heads = bool(native_heads)
         self.speedup(backend)
 
     def speedup(self, backend="b200", use_cache=True, model_root_path=None):
@@ -79,8 +82,8 @@ class _Base:
 
 
 class SAM2ImagePredictor(_Base):
-    def __init__(self, state_dict, device="cuda", mask_threshold=0.0, backend="b200"):
-        super().__init__(state_dict, device, backend)
+    def __init__(self, state_dict, device="cuda", mask_threshold=0.0, backend="b200", native_heads=True):
+        super().__init__(state_dict, device, backend, native_heads)
         self.mask_threshold = mask_threshold
         self.reset_predictor()
 
@@ -139,11 +142,19 @@ class SAM2ImagePredictor(_Base):
             mask_t = torch.as_tensor(mask_input, dtype=torch.float32, device=self.device)
             if mask_t.dim() == 3:
                 mask_t = mask_t[None]
-        sparse, dense = H.prompt_encoder(self.w, coords, labels, mask_t)
-        batched = coords is not None and coords.shape[0] > 1
         hr = [f[img_idx:img_idx + 1] for f in self._features["high_res_feats"]]
-        low, iou, _, _ = H.mask_decoder(self.w, self._features["image_embed"][img_idx:img_idx + 1], sparse, dense,
-                                        multimask_output, hr, repeat_image=batched, pe=self._dense_pe)
+        emb = self._features["image_embed"][img_idx:img_idx + 1]
+        if self.native_heads and coords is not None:
+            # prompt encoder (points) + mask decoder inside libsam2b (sam2b_sam_heads, decoder-only semantics); a mask prompt
+            # enters as the dense embedding of the reference's mask_downscaling convolutions
+            nb = coords.shape[0]
+            dense = None if mask_t is None else H.prompt_encoder(self.w, None, None, mask_t)[1].expand(nb, -1, -1, -1)
+            low, _, iou, _, _, _, _ = self.engine.sam_heads(emb.expand(nb, -1, -1, -1), hr, coords, labels, dense,
+                                                            multimask_output=multimask_output, decoder_only=True, high_res=False)
+        else:
+            sparse, dense = H.prompt_encoder(self.w, coords, labels, mask_t)
+            batched = coords is not None and coords.shape[0] > 1
+            low, iou, _, _ = H.mask_decoder(self.w, emb, sparse, dense, multimask_output, hr, repeat_image=batched, pe=self._dense_pe)
         # postprocess_masks (ref: utils/transforms.py:119) and the threshold in one pass: sam2b_op_upsample_masks
         if return_logits:
             masks = upsample_masks(low.float(), (oh, ow))
@@ -261,7 +272,7 @@ class SAM2VideoPredictor(_Base):
     """Forward video propagation with click / box prompts (BASELINE.json configs 3 and 4)."""
 
     def __init__(self, state_dict, device="cuda", backend="b200", encode_ahead=16, fill_hole_area=0, graph_heads=True,
-                 add_all_frames_to_correct_as_cond=False, bank_ring=True):
+                 add_all_frames_to_correct_as_cond=False, bank_ring=True, native_heads=True):
         """fill_hole_area: as the reference's constructor argument (sam2_video_predictor_official.py:25,889-894; the
         reference's builder sets 8 when its native extension is available, build_sam.py:128-129): holes of at most that
         many pixels in the low-res mask scores are filled before the masks are stored / returned.  0 = off, which is what
@@ -269,7 +280,7 @@ class SAM2VideoPredictor(_Base):
         encode_ahead: frames pushed through the image encoder per engine call (one micro-batch of 16 runs at 3.0 ms per
         frame against 3.3 ms at 8; per-frame results do not depend on it — the encoder is batch-invariant, tested).
         graph_heads: replay the SAM heads of tracked frames from a CUDA graph (see _GraphedHeads)."""
-        super().__init__(state_dict, device, backend)
+        super().__init__(state_dict, device, backend, native_heads)
         self.encode_ahead = max(1, int(encode_ahead))
         self.fill_hole_area = int(fill_hole_area)
         self.graph_heads = bool(graph_heads)
@@ -394,8 +405,13 @@ class SAM2VideoPredictor(_Base):
             pix = self._memory_conditioned(st, t, [(cond_keys, hist, [o])], f2, pos2, per_object=True)
         # ref: _use_multimask, sam2_base_official.py:1181-1189 (multimask_output_for_tracking, 0 <= points <= 1)
         multimask = pts.shape[0] <= 1
-        _, _, _, low, high, ptr, obj = H.forward_sam_heads(self.w, pix, point_inputs=pin, mask_inputs=prev_logits,
-                                                           high_res_features=hr, multimask_output=multimask, pe=self._dense_pe)
+        if self.native_heads and pts.shape[0] > 0:
+            dense = None if prev_logits is None else H.prompt_encoder(self.w, None, None, H.mask_prompt_256(prev_logits))[1]
+            _, _, _, low, _, ptr, obj = self.engine.sam_heads(pix, hr, pts[None], lab[None], dense, multimask_output=multimask,
+                                                              high_res=False)
+        else:
+            _, _, _, low, high, ptr, obj = H.forward_sam_heads(self.w, pix, point_inputs=pin, mask_inputs=prev_logits,
+                                                               high_res_features=hr, multimask_output=multimask, pe=self._dense_pe)
         return {"pred_masks": self._fill_holes(low), "obj_ptr": ptr, "object_score_logits": obj, "maskmem_features": None,
                 "maskmem_pos": None}
 
@@ -547,7 +563,10 @@ class SAM2VideoPredictor(_Base):
         order = [o for _, _, g in groups for o in g]
         n = len(order)
         pix = self._memory_conditioned(st, t, groups, f2, pos2)
-        if self.graph_heads:
+        if self.native_heads:
+            # ONE library call: ~50 launches of libsam2b's own kernels (split-bf16 tcgen05 GEMMs on the image side, fp32 token side)
+            _, _, _, low, high, ptr, obj = self.engine.sam_heads(pix, hr, multimask_output=True)
+        elif self.graph_heads:
             gk = (n, threading.get_ident())    # static buffers are per graph: one graph per host thread
             if gk not in self._heads_graphs:
                 self._heads_graphs[gk] = _GraphedHeads(self.w, n, self._dense_pe, self.device)

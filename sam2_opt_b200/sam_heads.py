@@ -160,6 +160,13 @@ def mask_decoder(w: W, image_emb, sparse, dense, multimask: bool, high_res: List
     return masks, iou, sam_tok, obj
 
 
+def mask_prompt_256(mask_inputs):
+    """ref: modeling/sam2_base_official.py:397-411 - a mask prompt of another size is resized to the prompt encoder's 256 x 256"""
+    if mask_inputs.shape[-2:] != (256, 256):
+        return F.interpolate(mask_inputs.float(), size=(256, 256), align_corners=False, mode="bilinear", antialias=True)
+    return mask_inputs
+
+
 def forward_sam_heads(w: W, backbone_features, point_inputs=None, mask_inputs=None, high_res_features=None,
                       multimask_output=False, pe=None):
     """ref: modeling/sam2_base_official.py:338-494"""

@@ -51,6 +51,44 @@ def rope_tables(device, dim: int = 256, end: int = 64, theta: float = 10000.0):
     return ang.cos().contiguous(), ang.sin().contiguous()
 
 
+def split3(wt: torch.Tensor) -> torch.Tensor:
+    """[N,K] fp32 -> [N,3K] = (hi | hi | lo) with hi = bf16(w), lo = bf16(w - hi), every entry exactly representable in bf16:
+    the B operand of the split-bf16 GEMMs of the SAM heads (csrc/sam_heads.cu; the A operand is laid out (hi | lo | hi), so one
+    bf16 GEMM over 3K columns accumulates hi*hi + lo*hi + hi*lo in fp32)."""
+    wt = wt.float()
+    hi = wt.to(torch.bfloat16).float()
+    lo = (wt - hi).to(torch.bfloat16).float()
+    return torch.cat([hi, hi, lo], 1).contiguous()
+
+
+def derive_heads(w: Dict[str, torch.Tensor]) -> Dict[str, torch.Tensor]:
+    """Constants of the SAM heads (engine.cu sam_heads_mb).  ref: modeling/sam/transformer.py:97-219 (the image-side
+    projections of TwoWayAttentionBlock all act on keys + dense_pe: the dense_pe part is a per-position constant, folded here
+    into a table that the GEMM adds as a row-modulo residual), modeling/sam/mask_decoder.py:283-300 (ConvTranspose2d k2 s2 as
+    a GEMM over (dy,dx,cout))."""
+    md, tr = "sam_mask_decoder.", "sam_mask_decoder.transformer."
+    if md + "iou_token.weight" not in w or "sam_prompt_encoder.pe_layer.positional_encoding_gaussian_matrix" not in w:
+        return {}
+    from .sam_heads import dense_pe
+    d = {}
+    pe = dense_pe(w).flatten(2)[0].t().double()                                  # [4096, 256], position-major
+    lin = lambda p: (w[p + "weight"].double(), w[p + "bias"].double())
+    for l in range(2):
+        p = f"{tr}layers.{l}."
+        (wk, bk), (wv, bv) = lin(p + "cross_attn_token_to_image.k_proj."), lin(p + "cross_attn_token_to_image.v_proj.")
+        wq, bq = lin(p + "cross_attn_image_to_token.q_proj.")
+        d[f"derived.heads.{l}.kvq.weight"] = split3(torch.cat([wk, wv, wq], 0).float())
+        d[f"derived.heads.{l}.kvq.table"] = torch.cat([pe @ wk.t() + bk, bv[None].expand(4096, -1), pe @ wq.t() + bq], 1).float().contiguous()
+        d[f"derived.heads.{l}.i2t_out.weight"] = split3(w[p + "cross_attn_image_to_token.out_proj.weight"])
+    (wk, bk), (wv, bv) = lin(tr + "final_attn_token_to_image.k_proj."), lin(tr + "final_attn_token_to_image.v_proj.")
+    d["derived.heads.final.kv.weight"] = split3(torch.cat([wk, wv], 0).float())
+    d["derived.heads.final.kv.table"] = torch.cat([pe @ wk.t() + bk, bv[None].expand(4096, -1)], 1).float().contiguous()
+    u0, u3 = w[md + "output_upscaling.0.weight"].float(), w[md + "output_upscaling.3.weight"].float()
+    d["derived.heads.up1.weight"] = split3(u0.permute(2, 3, 1, 0).reshape(256, 256))         # [(dy,dx,cout), cin]
+    d["derived.heads.up2.weight"] = u3.permute(0, 2, 3, 1).reshape(64, 4, 32).contiguous()      # [cin][(ey,ex)][cout]
+    return d
+
+
 def derive(w: Dict[str, torch.Tensor]) -> Dict[str, torch.Tensor]:
     """Derived constants for the engine (all fp32, same device as the weights)."""
     d = {}
@@ -117,6 +155,7 @@ def derive(w: Dict[str, torch.Tensor]) -> Dict[str, torch.Tensor]:
             d[f"derived.blocks.{i}.{short}.weight"] = ws.float().contiguous()
             d[f"derived.blocks.{i}.{short}.bias"] = (bias + W @ beta).float().contiguous()
         i += 1
+    d.update(derive_heads(w))
     cos, sin = rope_tables(dev)
     # (cos, sin) of column pair i at columns (2i, 2i + 1): the layout the GEMM's RoPE epilogue reads as 32 x 32 boxes
     d["derived.rope.cs"] = torch.stack([cos, sin], -1).reshape(cos.shape[0], -1).contiguous()
