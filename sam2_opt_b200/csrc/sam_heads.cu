@@ -141,43 +141,60 @@ __global__ void heads_tokens_kernel(const float* __restrict__ coords, const int*
 
 // ---------------------------------------------------------------------------------------------------------------------
 // Small fp32 linear layers on the token side, several independent problems ("jobs") per launch:
-//   Y[r][j] = act( sum_k (X[r][k] + X2[r][k]) * W[j][k] + b[j] ),  r < rows, j < N, K % 32 == 0.
+//   Y[r][j] = act( sum_k (X[r][k] + X2[r][k]) * W[j][k] + b[j] ),  r < rows, j < N, K % 128 == 0.
 // A job may be one K slice of a larger problem (split K: the partial sums are added by tok_sum_res_ln_kernel).
-// Tile: 16 rows x 64 columns per CTA, 32-wide K chunks through shared memory.
+// Tile: 16 rows x 64 columns per CTA, 128-wide K chunks through shared memory.
 // ---------------------------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256) tok_linear_kernel(const __grid_constant__ LinJobs jobs) {
   const LinJob& J = jobs.j[blockIdx.z];
   const int n0 = blockIdx.x * 64, r0 = blockIdx.y * 16;
   if (n0 >= J.N || r0 >= J.rows) return;
-  __shared__ float Xs[16][33];
-  __shared__ float Ws[64][33];
+  // 128-wide K chunks; rows of 132 floats keep every float4 16-byte aligned and the LDS.128 of 8 consecutive rows on 32
+  // distinct banks.  The next chunk is fetched into registers while the current one is multiplied (these problems are tiny:
+  // what a launch costs is its chain of dependent memory round trips, not its arithmetic).
+  constexpr int KC = 128, LD = KC + 4;
+  __shared__ __align__(16) float Xs[16 * LD];
+  __shared__ __align__(16) float Ws[64 * LD];
   const int tid = threadIdx.x, tr = tid >> 4, tc = tid & 15;
-  float acc[4] = {0.f, 0.f, 0.f, 0.f};
-  for (int k0 = 0; k0 < J.K; k0 += 32) {
-    {
-      const int kk = tid & 31;
+  float4 xr[2], wr[8];
+  auto fetch = [&](int k0) {
 #pragma unroll
-      for (int i = 0; i < 2; ++i) {
-        const int r = (tid >> 5) + 8 * i;
-        float v = 0.f;
-        if (r0 + r < J.rows) {
-          v = J.X[(long)(r0 + r) * J.ldx + k0 + kk];
-          if (J.X2) v += J.X2[(long)(r0 + r) * J.ldx2 + k0 + kk];
+    for (int i = 0; i < 2; ++i) {
+      const int idx = tid + 256 * i, r = idx >> 5, k4 = idx & 31;
+      float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (r0 + r < J.rows) {
+        v = *reinterpret_cast<const float4*>(J.X + (long)(r0 + r) * J.ldx + k0 + 4 * k4);
+        if (J.X2) {
+          const float4 u = *reinterpret_cast<const float4*>(J.X2 + (long)(r0 + r) * J.ldx2 + k0 + 4 * k4);
+          v.x += u.x; v.y += u.y; v.z += u.z; v.w += u.w;
         }
-        Xs[r][kk] = v;
       }
-#pragma unroll
-      for (int i = 0; i < 8; ++i) {
-        const int j = (tid >> 5) + 8 * i;
-        Ws[j][kk] = (n0 + j < J.N) ? J.W[(long)(n0 + j) * J.ldw + k0 + kk] : 0.f;
-      }
+      xr[i] = v;
     }
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      const int idx = tid + 256 * i, j = idx >> 5, k4 = idx & 31;
+      wr[i] = (n0 + j < J.N) ? *reinterpret_cast<const float4*>(J.W + (long)(n0 + j) * J.ldw + k0 + 4 * k4) : make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+  };
+  float acc[4] = {0.f, 0.f, 0.f, 0.f};
+  fetch(0);
+  for (int k0 = 0; k0 < J.K; k0 += KC) {
+#pragma unroll
+    for (int i = 0; i < 2; ++i) { const int idx = tid + 256 * i; *reinterpret_cast<float4*>(Xs + (idx >> 5) * LD + 4 * (idx & 31)) = xr[i]; }
+#pragma unroll
+    for (int i = 0; i < 8; ++i) { const int idx = tid + 256 * i; *reinterpret_cast<float4*>(Ws + (idx >> 5) * LD + 4 * (idx & 31)) = wr[i]; }
     __syncthreads();
+    if (k0 + KC < J.K) fetch(k0 + KC);
+#pragma unroll 8
+    for (int k4 = 0; k4 < KC / 4; ++k4) {
+      const float4 x = *reinterpret_cast<const float4*>(Xs + tr * LD + 4 * k4);
 #pragma unroll
-    for (int kk = 0; kk < 32; ++kk) {
-      const float x = Xs[tr][kk];
-#pragma unroll
-      for (int jj = 0; jj < 4; ++jj) acc[jj] = fmaf(x, Ws[tc + 16 * jj][kk], acc[jj]);
+      for (int jj = 0; jj < 4; ++jj) {
+        const float4 w = *reinterpret_cast<const float4*>(Ws + (tc + 16 * jj) * LD + 4 * k4);
+        acc[jj] = fmaf(x.x, w.x, acc[jj]); acc[jj] = fmaf(x.y, w.y, acc[jj]);
+        acc[jj] = fmaf(x.z, w.z, acc[jj]); acc[jj] = fmaf(x.w, w.w, acc[jj]);
+      }
     }
     __syncthreads();
   }
@@ -584,7 +601,10 @@ int tok_linear(const LinJobs& jobs, int njobs, cudaStream_t st) {
   double flops = 0;
   for (int i = 0; i < njobs; ++i) {
     const LinJob& j = jobs.j[i];
-    if (j.K % 32 || j.rows <= 0 || j.N <= 0) { set_error("tok_linear: job %d rows=%d N=%d K=%d (K %% 32 == 0)", i, j.rows, j.N, j.K); return 1; }
+    if (j.K % 128 || (j.ldx % 4) || (j.ldw % 4) || (j.X2 && j.ldx2 % 4) || j.rows <= 0 || j.N <= 0) {
+      set_error("tok_linear: job %d rows=%d N=%d K=%d (K %% 128 == 0, leading dimensions %% 4 == 0)", i, j.rows, j.N, j.K);
+      return 1;
+    }
     max_n = j.N > max_n ? j.N : max_n;
     max_r = j.rows > max_r ? j.rows : max_r;
     flops += 2.0 * j.rows * j.N * j.K;

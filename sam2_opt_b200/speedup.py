@@ -31,11 +31,54 @@ def _make_engine(model, device, engine_factory):
     return engine_factory(model.state_dict(), device)
 
 
-def speedup(predictor, backend="b200", engine=None, engine_factory=None, warmup=True):
+def _native_forward_sam_heads(model, engine):
+    """SAM2Base._forward_sam_heads (ref: modeling/sam2_base_official.py:338-494) on the engine: same arguments, same 7 outputs.
+    The mask prompt keeps the reference's own down-scaling convolutions (sam/prompt_encoder.py:152-155) and enters the
+    library as the dense embedding; everything else is one sam2b_sam_heads call."""
+    import torch.nn.functional as F
+
+    def forward(backbone_features, point_inputs=None, mask_inputs=None, high_res_features=None, multimask_output=False):
+        if high_res_features is None or (point_inputs is not None and point_inputs["point_coords"].shape[1] > 25):
+            return type(model)._forward_sam_heads(model, backbone_features, point_inputs, mask_inputs, high_res_features, multimask_output)
+        coords = labels = dense = None
+        if point_inputs is not None:
+            coords, labels = point_inputs["point_coords"], point_inputs["point_labels"]
+        if mask_inputs is not None:
+            size = tuple(model.sam_prompt_encoder.mask_input_size)
+            m = mask_inputs.float()
+            if tuple(m.shape[-2:]) != size:
+                m = F.interpolate(m, size=size, align_corners=False, mode="bilinear", antialias=True)
+            dense = model.sam_prompt_encoder._embed_masks(m)
+        dev = backbone_features.device
+        low_multi, high_multi, ious, low, high, ptr, obj = engine.sam_heads(
+            backbone_features.float(), [f.float() for f in high_res_features], coords, labels, dense,
+            multimask_output=multimask_output, high_res_multimasks=True)
+        return tuple(t.to(dev) for t in (low_multi, high_multi, ious, low, high, ptr, obj))
+
+    return forward
+
+
+def _heads_config_supported(model) -> bool:
+    """The library implements the SAM2.1 head configuration (configs/sam2.1/sam2.1_hiera_*.yaml:98-117): high-resolution
+    features, object scores from an MLP, fixed (hard) no-object pointer, the multimask token for the pointer, dynamic
+    multimask fall-back with the default thresholds, sigmoid IoU head.  Any other configuration keeps the torch heads."""
+    md = getattr(model, "sam_mask_decoder", None)
+    if md is None:
+        return False
+    want_model = dict(use_high_res_features_in_sam=True, pred_obj_scores=True, fixed_no_obj_ptr=True, soft_no_obj_ptr=False,
+                      use_obj_ptrs_in_encoder=True)
+    want_md = dict(use_multimask_token_for_obj_ptr=True, dynamic_multimask_via_stability=True, pred_obj_scores=True,
+                   use_high_res_features=True, dynamic_multimask_stability_delta=0.05, dynamic_multimask_stability_thresh=0.98)
+    return all(getattr(model, k, None) == v for k, v in want_model.items()) and \
+        all(getattr(md, k, None) == v for k, v in want_md.items()) and not getattr(model, "training", False)
+
+
+def speedup(predictor, backend="b200", engine=None, engine_factory=None, warmup=True, heads=True):
     """Engage (``backend="b200"``) or disengage (``"torch"``) the sm_100a engine on a reference predictor.
 
     Image predictor (has ``set_image_e2e``): rebinds E1.  Video predictor / SAM2Base (has ``inference_image``): rebinds
-    E2, E3 (both ``none`` and ``exclude`` variants) and E4.  Returns the engine in use (None for "torch")."""
+    E2, E3 (both ``none`` and ``exclude`` variants) and E4 and, with ``heads``, the model's
+    ``_forward_sam_heads`` (prompt encoder + mask decoder + pointer head).  Returns the engine in use (None for "torch")."""
     b = backend.lower()
     is_image = hasattr(predictor, "set_image_e2e") and hasattr(predictor, "model")
     model = predictor.model if is_image else predictor
@@ -44,6 +87,7 @@ def speedup(predictor, backend="b200", engine=None, engine_factory=None, warmup=
         if not is_image:
             model.memory_attention.set_runtime_backend(backend="torch")
             model.memory_encoder.set_runtime_backend(backend="torch")
+            model.__dict__.pop("_forward_sam_heads", None)          # back to the class's own torch heads
         return None
     if b not in B200_NAMES:
         raise Exception(f"unsupported runtime backend={backend}")
@@ -80,6 +124,8 @@ def speedup(predictor, backend="b200", engine=None, engine_factory=None, warmup=
         return x.to(pix_feat.device), pos.to(pix_feat.device)
 
     me.inference_memory = inference_memory
+    if heads and hasattr(engine, "sam_heads") and _heads_config_supported(model):
+        model._forward_sam_heads = _native_forward_sam_heads(model, engine)
     if warmup:
         ex_img.warmup([torch.randn(1, 3, 1024, 1024)])
         for L in (1, 7):
@@ -100,7 +146,7 @@ def install(*classes):
 
         def patched(self, backend="b200", *a, _orig=orig, **k):
             if isinstance(backend, str) and backend.lower() in B200_NAMES:
-                self._sam2b_engine = speedup(self, backend, **{x: k[x] for x in ("engine", "engine_factory", "warmup") if x in k})
+                self._sam2b_engine = speedup(self, backend, **{x: k[x] for x in ("engine", "engine_factory", "warmup", "heads") if x in k})
                 return None
             if isinstance(backend, str) and backend.lower() == "torch" and getattr(self, "_sam2b_engine", None) is not None:
                 # the reference's own speedup("torch") resets the image / memory-attention hooks only
