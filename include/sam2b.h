@@ -115,6 +115,18 @@ int sam2b_sam_heads(sam2b_handle h, const float* backbone_features, int64_t feat
                     float* high_res_multimasks, float* ious, float* low_res_masks, float* high_res_masks, float* obj_ptr,
                     float* object_score_logits, void* stream);
 
+/* ---- CUDA graphs over engine calls ----
+ * The reference replays nothing: every frame re-enqueues its TensorRT contexts (tensorrt_executor.py:232-309).  Here the
+ * engine calls are capturable (cudaStreamBeginCapture on `stream`, then sam2b_memory_attention / sam2b_sam_heads /
+ * sam2b_memory_encode ... with sizes the workspaces already hold: a capture must follow one eager run of the same calls):
+ * under capture the calls leave out the cross-stream hand-off events that serialise callers on the shared workspaces, so a
+ * REPLAY must be bracketed by sam2b_stream_acquire(h, stream) / sam2b_stream_release(h, stream) on the replaying stream.
+ * sam2b_workspace_generation changes whenever a workspace buffer was re-allocated (a larger problem arrived): graphs captured
+ * under an older generation hold stale addresses and must be captured again. */
+int sam2b_stream_acquire(sam2b_handle h, void* stream);
+int sam2b_stream_release(sam2b_handle h, void* stream);
+unsigned long long sam2b_workspace_generation(sam2b_handle h);
+
 /* ---- peer memory for the embedding gather (the only collective of the path) ----
  * The reference has no multi-GPU inference path (one process, one GPU: sam2/ytools/tensorrt/tensorrt_executor.py:26-29);
  * this is the B200-box replacement: one process per GPU, every rank owns a gather buffer that its peers map through CUDA

@@ -26,6 +26,9 @@ SIGNATURES = {
     "sam2b_memory_encode": (_i, [_vp, _vp, _vp, _i, _vp, _vp]),
     "sam2b_sam_heads": (_i, [_vp, _vp, _i64, _i64, _i64, _vp, _i64, _vp, _i64, _vp, _vp, _i, _vp, _i, _i, _i,
                              _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
+    "sam2b_stream_acquire": (_i, [_vp, _vp]),
+    "sam2b_stream_release": (_i, [_vp, _vp]),
+    "sam2b_workspace_generation": (C.c_ulonglong, [_vp]),
     "sam2b_peer_alloc": (_i, [_i, _i64, C.POINTER(_vp), C.c_char_p]),
     "sam2b_peer_free": (_i, [_i, _vp]),
     "sam2b_peer_open": (_i, [_i, C.c_char_p, C.POINTER(_vp)]),

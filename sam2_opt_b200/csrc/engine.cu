@@ -115,6 +115,7 @@ struct sam2b_engine {
   std::mutex mu;
   cudaEvent_t done = nullptr;
   bool done_valid = false;
+  unsigned long long ws_generation = 0;   // bumped whenever a workspace buffer is re-allocated
 
   Tensor* find(const std::string& n) {
     auto it = w.find(n);
@@ -130,13 +131,20 @@ struct EngineCall {
   sam2b_engine* e;
   cudaStream_t st;
   std::unique_lock<std::mutex> lk;
+  bool capturing = false;
   EngineCall(sam2b_engine* eng, cudaStream_t s) : e(eng), st(s), lk(eng->mu) {}
   int begin() {
-    if (e->done_valid) CUDA_OK(cudaStreamWaitEvent(st, e->done, 0));
+    // Under CUDA graph capture the hand-off events must stay out of the graph (waiting on an event recorded outside the
+    // capture is an error, and an event recorded inside would become a captured one): a caller that replays a captured
+    // sequence brackets the replay with sam2b_stream_acquire / sam2b_stream_release instead.
+    cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
+    CUDA_OK(cudaStreamIsCapturing(st, &cs));
+    capturing = (cs != cudaStreamCaptureStatusNone);
+    if (!capturing && e->done_valid) CUDA_OK(cudaStreamWaitEvent(st, e->done, 0));
     return 0;
   }
   ~EngineCall() {
-    if (cudaEventRecord(e->done, st) == cudaSuccess) e->done_valid = true;
+    if (!capturing && cudaEventRecord(e->done, st) == cudaSuccess) e->done_valid = true;
   }
 };
 #define ENGINE_CALL(h, st)        \
@@ -146,6 +154,7 @@ struct EngineCall {
 static int ws_get(sam2b_engine* e, const char* name, size_t bytes, void** out) {
   Buf& b = e->ws[name];
   if (b.bytes < bytes) {
+    ++e->ws_generation;               // captured graphs that baked the old address must be re-captured (sam2b_workspace_generation)
     if (b.p) CUDA_OK(cudaFree(b.p));
     b.p = nullptr; b.bytes = 0;
     CUDA_OK(cudaMalloc(&b.p, bytes));
@@ -1207,6 +1216,24 @@ int sam2b_sam_heads(sam2b_handle h, const float* backbone_features, int64_t feat
   }
   return 0;
 }
+
+// ---- CUDA-graph support: replaying a captured sequence of engine calls ----
+int sam2b_stream_acquire(sam2b_handle h, void* stream) {
+  if (!h) { set_error("sam2b_stream_acquire: null engine"); return 1; }
+  ENTER_DEVICE(h->device);
+  std::lock_guard<std::mutex> lk(h->mu);
+  if (h->done_valid) CUDA_OK(cudaStreamWaitEvent(reinterpret_cast<cudaStream_t>(stream), h->done, 0));
+  return 0;
+}
+int sam2b_stream_release(sam2b_handle h, void* stream) {
+  if (!h) { set_error("sam2b_stream_release: null engine"); return 1; }
+  ENTER_DEVICE(h->device);
+  std::lock_guard<std::mutex> lk(h->mu);
+  CUDA_OK(cudaEventRecord(h->done, reinterpret_cast<cudaStream_t>(stream)));
+  h->done_valid = true;
+  return 0;
+}
+unsigned long long sam2b_workspace_generation(sam2b_handle h) { return h ? h->ws_generation : 0; }
 
 // ---- profiling ----
 int sam2b_profile_begin(void) {

@@ -258,6 +258,20 @@ class Engine:
                 _ptr(high), _ptr(ptr), _ptr(obj), self._stream()), "sam_heads")
         return low_multi, high_multi, ious, low, high, ptr, obj
 
+    # -- CUDA graphs over engine calls -----------------------------------------------------------------------------
+    def workspace_generation(self) -> int:
+        """Changes whenever the library re-allocated a workspace buffer: graphs captured before hold stale addresses."""
+        return int(self.lib.sam2b_workspace_generation(self._h))
+
+    def replay(self, graph: "torch.cuda.CUDAGraph"):
+        """Replay a graph captured over engine calls on the caller's current stream, serialised against every other use
+        of the engine's shared workspaces like a plain call (host lock + the library's cross-stream event chain)."""
+        st = self._stream()
+        with self._lock:
+            _lib.check(self.lib.sam2b_stream_acquire(self._h, st), "stream_acquire")
+            graph.replay()
+            _lib.check(self.lib.sam2b_stream_release(self._h, st), "stream_release")
+
     # -- life cycle ------------------------------------------------------------------------------------------
     def release(self):
         """Idempotent (ref: TensorRTExecutor.Release also runs from __del__, tensorrt_executor.py:311-334)."""

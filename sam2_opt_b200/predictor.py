@@ -50,6 +50,7 @@ class _Base:
             ctx.Release()
         self.backend_contexts = []
         getattr(self, "_heads_graphs", {}).clear()      # captured SAM-heads graphs (video predictor)
+        getattr(self, "_track_graphs", {}).clear()      # captured tracked-frame graphs
         if self.engine is not None:
             self.engine.release()
             self.engine = None
@@ -268,11 +269,120 @@ class _BankRing:
         return self.mem[:L], self.pos[:L]
 
 
+class _GraphedTrack:
+    """the steady-state tracked frame of one group of n objects as ONE CUDA graph.
+
+    Once the memory bank is full (one conditioning frame + the 6 most recent frames) and 16 object pointers exist, every
+    tracked frame runs the same ~150 kernels on the same shapes: memory_pos assembly, E3 (L = 7, P = 64), the SAM heads, E4
+    and the bank update.  At one object the GPU needs 1.2 ms for them while the host needs 1.9 ms to enqueue them
+    (tools/frame_timeline.py), so the sequence is captured once and replayed.  What differs from frame to frame is DATA on the
+    device: the bank lives in a ring `mem [7,4096,n,64]` (slot 0 the conditioning frame, frame t in slot 1 + t % 6), the object
+    pointers in `ptrs [16,n,256]` (slot 0 the conditioning frame, frame t in slot 1 + t % 15), and a small control vector
+    (one pinned H2D copy per frame) carries each slot's current age / temporal distance and the slots the new frame
+    overwrites.  Attention does not depend on the order of its keys as long as each keeps its own position term, so the
+    values equal `sam_heads.assemble_memory` up to fp32 summation order (ref: sam2_base_official.py:825-950)."""
+
+    TABLE_ROWS = 2049          # projected temporal encodings of the pointer distances 0 .. 2048 (longer videos: a larger table)
+
+    def __init__(self, vp, n):
+        dev, w = vp.device, vp.w
+        self.vp, self.n = vp, n
+        self.mem = torch.empty((H.NUM_MASKMEM, 4096, n, H.MEM_DIM), device=dev)
+        self.pos = torch.empty_like(self.mem)
+        self.ptrs = torch.empty((16, n, H.D_MODEL), device=dev)
+        self.pe = torch.empty((4096, 1, H.MEM_DIM), device=dev)           # sine encoding of the bank frames
+        self.table = torch.zeros((self.TABLE_ROWS, H.MEM_DIM), device=dev)
+        self.tpos = w["maskmem_tpos_enc"].reshape(H.NUM_MASKMEM, 1, 1, H.MEM_DIM)
+        self.ctl = torch.zeros(25, dtype=torch.int64, device=dev)          # ages[7] | distances[16] | mem slot | ptr slot
+        self.ctl_host = [torch.zeros(25, dtype=torch.int64).pin_memory() for _ in range(4)]
+        self.f2 = torch.empty((1, 256, 64, 64), device=dev)
+        self.hr = [torch.empty((1, 32, 256, 256), device=dev), torch.empty((1, 64, 128, 128), device=dev)]
+        self.pos2 = vp.engine.position_encoding(256, 64, 1).flatten(2).permute(2, 0, 1).expand(-1, n, -1).contiguous()
+        self.graph, self.out, self.gen, self.warm = None, None, -1, False
+        self.owner, self.next_t, self.t_cond, self.served = None, -1, 0, 0
+
+    def bind(self, owner, num_frames, t_cond, cond_rec, recs, t):
+        """Load the state of one video at frame t (the captured graph and the static buffers are kept across videos)."""
+        rows = lambda m: m.flatten(2).permute(2, 0, 1)                    # [n,64,64,64] -> [4096,n,64]
+        self.owner, self.next_t, self.t_cond, self.served = owner, t, t_cond, 0
+        self.mem[0].copy_(rows(cond_rec["maskmem_features"]))
+        self.ptrs[0].copy_(cond_rec["obj_ptr"])
+        self.pe.copy_(rows(cond_rec["maskmem_pos"][:1]))
+        for tt in range(t - 6, t):
+            self.mem[1 + tt % 6].copy_(rows(recs[tt]["maskmem_features"]))
+        for tt in range(t - 15, t):
+            self.ptrs[1 + tt % 15].copy_(recs[tt]["obj_ptr"])
+        table = H._ptr_tpos_table(self.vp.w, num_frames, 16, self.vp._tpos_cache)  # [num_frames + 1, 64]
+        if table.shape[0] > self.table.shape[0]:
+            self.table = torch.zeros((table.shape[0], H.MEM_DIM), device=self.vp.device)
+            self.graph = None                                              # the captured address is stale
+        self.table[:table.shape[0]].copy_(table)
+
+    def _control(self, t):
+        ages = [H.NUM_MASKMEM - 1]                                         # conditioning frame: t_pos 0
+        for s in range(1, H.NUM_MASKMEM):
+            tt = t - 1 - ((t - 1 - (s - 1)) % 6)                           # the frame in slot s: tt = s - 1 (mod 6), t-6 <= tt < t
+            ages.append(t - tt - 1)                                        # t_pos = 7 - (t - tt) -> index 7 - t_pos - 1
+        dists = [t - self.t_cond]
+        for p in range(1, 16):
+            tt = t - 1 - ((t - 1 - (p - 1)) % 15)
+            dists.append(t - tt)
+        return ages + dists + [1 + t % 6, 1 + t % 15]
+
+    def _body(self):
+        vp, n = self.vp, self.n
+        torch.add(self.pe[None].expand(H.NUM_MASKMEM, 4096, n, H.MEM_DIM),
+                  self.tpos.index_select(0, self.ctl[0:7]).expand(H.NUM_MASKMEM, 4096, n, H.MEM_DIM), out=self.pos)
+        ptr_tok = self.ptrs.reshape(16, n, 4, H.MEM_DIM).permute(0, 2, 1, 3).flatten(0, 1)                    # [64,n,64]
+        ppos = self.table.index_select(0, self.ctl[7:23]).unsqueeze(1).expand(-1, n, H.MEM_DIM).repeat_interleave(4, dim=0)
+        curr = self.f2.flatten(2).permute(2, 0, 1).expand(-1, n, -1)
+        pix = vp.engine.memory_attention(curr, self.mem, self.pos2, self.pos, ptr_tok, ppos)
+        pix = pix.permute(1, 2, 0).reshape(n, H.D_MODEL, 64, 64)
+        _, _, _, low, high, ptr, obj = vp.engine.sam_heads(pix, self.hr, multimask_output=True)
+        x, mp = vp.engine.memory_encode(self.f2.expand(n, -1, -1, -1), torch.sigmoid(high) * 20.0 - 10.0)
+        is_obj = (obj > 0).float()
+        x = x + (1 - is_obj[..., None, None]) * vp.w["no_obj_embed_spatial"][..., None, None].expand(*x.shape)
+        mf = x.to(torch.bfloat16)
+        # the new frame replaces the oldest one in both rings (after everything that read them)
+        self.mem.index_copy_(0, self.ctl[23:24], mf.float().flatten(2).permute(2, 0, 1)[None])
+        self.ptrs.index_copy_(0, self.ctl[24:25], ptr[None])
+        return low, ptr, obj, mf, mp
+
+    def step(self, t, f2, hr):
+        assert t == self.next_t
+        vp = self.vp
+        h = self.ctl_host[t % len(self.ctl_host)]
+        h.copy_(torch.tensor(self._control(t), dtype=torch.int64))
+        self.ctl.copy_(h, non_blocking=True)
+        self.f2.copy_(f2)
+        self.hr[0].copy_(hr[0])
+        self.hr[1].copy_(hr[1])
+        if not self.warm:
+            out = self._body()                        # eager: the real frame, and the warm-up every capture needs
+            self.warm = True
+        else:
+            if self.graph is None or self.gen != vp.engine.workspace_generation():
+                # (re-)capture: no kernel runs here; a workspace that another call re-allocated invalidates the old graph
+                side = torch.cuda.Stream(device=vp.device)
+                side.wait_stream(torch.cuda.current_stream(vp.device))
+                self.graph = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(self.graph, stream=side, capture_error_mode="thread_local"):
+                    self.out = self._body()
+                torch.cuda.current_stream(vp.device).wait_stream(side)
+                self.gen = vp.engine.workspace_generation()
+            vp.engine.replay(self.graph)
+            out = self.out
+        self.served += 1
+        self.next_t = t + 1
+        low, ptr, obj, mf, mp = out
+        return low.clone(), ptr.clone(), obj.clone(), mf.clone(), mp
+
+
 class SAM2VideoPredictor(_Base):
     """Forward video propagation with click / box prompts (BASELINE.json configs 3 and 4)."""
 
     def __init__(self, state_dict, device="cuda", backend="b200", encode_ahead=16, fill_hole_area=0, graph_heads=True,
-                 add_all_frames_to_correct_as_cond=False, bank_ring=True, native_heads=True):
+                 add_all_frames_to_correct_as_cond=False, bank_ring=True, native_heads=True, graph_track=True):
         """fill_hole_area: as the reference's constructor argument (sam2_video_predictor_official.py:25,889-894; the
         reference's builder sets 8 when its native extension is available, build_sam.py:128-129): holes of at most that
         many pixels in the low-res mask scores are filled before the masks are stored / returned.  0 = off, which is what
@@ -290,7 +400,10 @@ class SAM2VideoPredictor(_Base):
         self._stamps = itertools.count(1)          # identity of stored bank records (see _BankRing.update)
         # ref: sam2_video_predictor_official.py:31-33 - whether a correction click on a tracked frame makes it a conditioning frame
         self.add_all_frames_to_correct_as_cond = bool(add_all_frames_to_correct_as_cond)
+        # graph_track: replay the steady-state tracked frame (full bank, 16 pointers) from one CUDA graph (see _GraphedTrack)
+        self.graph_track = bool(graph_track)
         self._heads_graphs = {}            # (object count, host thread) -> _GraphedHeads
+        self._track_graphs = {}            # (object count, host thread) -> _GraphedTrack
         self._tpos_cache = {}              # (num_frames, max_ptrs) -> projected temporal encodings of the object pointers
 
     @torch.no_grad()
@@ -306,7 +419,8 @@ class SAM2VideoPredictor(_Base):
         st = {"images": frames if offload_video_to_cpu else frames.to(self.device), "num_frames": frames.shape[0],
               "video_height": video_height or 1024, "video_width": video_width or 1024,
               "obj_ids": [], "prompts": OrderedDict(), "cond": OrderedDict(), "non_cond": OrderedDict(),
-              "feat_cache": {}, "frames_tracked": {}, "non_cond_b": {}, "cond_b": {}, "pending_non_cond": set(), "rings": {}}
+              "feat_cache": {}, "frames_tracked": {}, "non_cond_b": {}, "cond_b": {}, "pending_non_cond": set(), "rings": {},
+              "gtrack": {}}
         return st
 
     def reset_state(self, st):
@@ -315,6 +429,7 @@ class SAM2VideoPredictor(_Base):
         st["obj_ids"], st["feat_cache"], st["frames_tracked"] = [], {}, {}
         st["pending_non_cond"].clear()
         st["rings"].clear()
+        st["gtrack"].clear()
 
     def _prep_frame(self, f, mean, std):
         """one uint8 HWC frame -> normalised [1,3,1024,1024] fp32 (ref: utils/misc.py:96,161-162)"""
@@ -361,6 +476,7 @@ class SAM2VideoPredictor(_Base):
         if normalize_coords:
             pts[:, 0] = pts[:, 0] / st["video_width"] * 1024
             pts[:, 1] = pts[:, 1] / st["video_height"] * 1024
+        st["gtrack"].clear()                       # the banks change: captured steady-state trackers start over
         key = (frame_idx, obj_id)
         if not clear_old_points and key in st["prompts"]:
             pts = torch.cat([st["prompts"][key][0].cpu(), pts], 0)
@@ -562,6 +678,10 @@ class SAM2VideoPredictor(_Base):
         groups = [(ck, hs, g) for (ck, hs), g in self._history_groups(st, t, objs).items()]
         order = [o for _, _, g in groups for o in g]
         n = len(order)
+        if self.graph_track and self.native_heads and len(groups) == 1:
+            outs = self._graph_track_frame(st, t, groups[0], f2, hr)
+            if outs is not None:
+                return [outs[o] for o in objs]
         pix = self._memory_conditioned(st, t, groups, f2, pos2)
         if self.native_heads:
             # ONE library call: ~50 launches of libsam2b's own kernels (split-bf16 tcgen05 GEMMs on the image side, fp32 token side)
@@ -586,6 +706,30 @@ class SAM2VideoPredictor(_Base):
             results[o] = {"pred_masks": low[i:i + 1], "obj_ptr": ptr[i:i + 1], "object_score_logits": obj[i:i + 1],
                           "maskmem_features": mf[i:i + 1], "maskmem_pos": mp[i:i + 1]}
         return [results[o] for o in objs]
+
+    def _graph_track_frame(self, st, t, group, f2, hr):
+        """The steady-state tracked frame through _GraphedTrack, or None when the frame is not in steady state: one
+        conditioning frame before t, tracked frames t-15 .. t-1 all present as batched records of this very group."""
+        cond_keys, hist, g_objs = group
+        key = tuple(g_objs)
+        if len(cond_keys) != 1 or cond_keys[0] >= t or st["num_frames"] < 17 or len(st["cond"]) != 1:
+            return None
+        gk = (len(key), threading.get_ident())          # static buffers and graph: one per object count and host thread
+        tr = self._track_graphs.get(gk)
+        owner = (id(st), key)
+        if tr is None or tr.owner != owner or tr.next_t != t or st["gtrack"].get(key) is not tr:
+            recs = {tt: st["non_cond_b"].get(tt, {}).get(key) for tt in range(t - 15, t)}
+            if t - 15 <= cond_keys[0] or any(r is None for r in recs.values()):
+                return None
+            if tr is None:
+                tr = self._track_graphs[gk] = _GraphedTrack(self, len(key))
+            tr.bind(owner, st["num_frames"], cond_keys[0], self._stacked_cond(st, cond_keys[0], key), recs, t)
+            st["gtrack"][key] = tr
+        low, ptr, obj, mf, mp = tr.step(t, f2, hr)
+        st["non_cond_b"].setdefault(t, {})[key] = {"maskmem_features": mf, "maskmem_pos": mp, "obj_ptr": ptr, "stamp": next(self._stamps)}
+        low = self._fill_holes(low)
+        return {o: {"pred_masks": low[i:i + 1], "obj_ptr": ptr[i:i + 1], "object_score_logits": obj[i:i + 1],
+                    "maskmem_features": mf[i:i + 1], "maskmem_pos": mp[i:i + 1]} for i, o in enumerate(g_objs)}
 
     def _stacked_cond(self, st, t, key):
         """Conditioning-frame outputs of the objects `key`, stacked once along the batch dimension."""

@@ -12,7 +12,7 @@ from sam2_opt_b200.synth_weights import make_weights
 T = int(sys.argv[1]) if len(sys.argv) > 1 else 64
 import os
 vp = SAM2VideoPredictor(make_weights(0), encode_ahead=int(os.environ.get('VP_AHEAD', '16')),
-                        native_heads=os.environ.get('VP_NATIVE', '1') == '1')
+                        native_heads=os.environ.get('VP_NATIVE', '1') == '1', graph_track=os.environ.get('VP_GRAPH', '1') == '1')
 frames = synth_video(T, seed=1).pin_memory()
 
 

@@ -21,7 +21,7 @@ nobj = int(sys.argv[1]) if len(sys.argv) > 1 else 1
 nprof = int(sys.argv[2]) if len(sys.argv) > 2 else 8
 g = max(1, int(nobj ** 0.5 + 0.999))
 clicks = [[512.0, 512.0]] if nobj == 1 else [[128 + 768.0 * (o % g) / max(1, g - 1), 128 + 768.0 * (o // g) / max(1, g - 1)] for o in range(nobj)]
-vp = SAM2VideoPredictor(make_weights(0), device="cuda:0")
+vp = SAM2VideoPredictor(make_weights(0), device="cuda:0", graph_track=os.environ.get("VP_GRAPH", "1") == "1")
 # 17 warm frames, then the profiled ones start right after an encode-ahead block boundary (frame 32) so that no image
 # encoding falls inside the window
 clip = synth_video(33 + nprof, seed=1).pin_memory()

@@ -22,7 +22,7 @@ nobj = int(sys.argv[1]) if len(sys.argv) > 1 else 1
 T = int(sys.argv[2]) if len(sys.argv) > 2 else 40
 g = max(1, int(nobj ** 0.5 + 0.999))
 clicks = [[512.0, 512.0]] if nobj == 1 else [[128 + 768.0 * (o % g) / max(1, g - 1), 128 + 768.0 * (o // g) / max(1, g - 1)] for o in range(nobj)]
-vp = SAM2VideoPredictor(make_weights(0), device="cuda:0", native_heads=os.environ.get("VP_NATIVE", "1") == "1")
+vp = SAM2VideoPredictor(make_weights(0), device="cuda:0", native_heads=os.environ.get("VP_NATIVE", "1") == "1", graph_track=False)
 clip = synth_video(T, seed=1).pin_memory()
 
 
