@@ -436,13 +436,17 @@ def main():
                  "config": "BASELINE.json configs[2]: 1 object, 64 synthetic 1024x1024 frames, 7-frame memory bank" if T == 64 else f"{T}-frame clip, 1 object",
                  "value_steady": world * n_steady / t_steady, "value_overall": world * T / t_all,
                  "frames_per_video": T, "objects_per_video": 1, "videos": world,
+                 "sam_heads": "libsam2b (sam2b_sam_heads)" if vp.native_heads else "torch fp32",
+                 "tracked_frame": "one CUDA graph per steady-state frame (E3 + SAM heads + E4 + bank update)" if vp.graph_track else "enqueued per call",
                  "rank0_fps_by_16_frame_block": [round(min(16, len(stamps) - 1 - i) / (stamps[min(i + 16, len(stamps) - 1)] - stamps[i]), 1) for i in range(0, len(stamps) - 1, 16)],
                  "timing": "host wall clock around the generator incl. H2D of frames and a D2H read of every frame's masks, max over ranks; steady = frames >= 16 (7-frame memory bank, 16 pointers)"}
         if rank == 0:
             # roofline of the video path's dominant kernel (hd-256 flash attention over the memory bank), live CUDA events
+            vp.graph_track = False            # the per-launch event profile needs the calls enqueued, not replayed from the graph
             E.profile_begin()
             run_clip(vp, clip[:24], grid_clicks(1))
             rows = E.profile_end()
+            vp.graph_track = True
             a = [(ms_, fl) for name, ms_, fl, by in rows if name.startswith("attn256 ")]
             cross = [(ms_, fl) for name, ms_, fl, by in rows if name.startswith("attn256 ") and " k28" in name]
             a_ms, a_fl = sum(x[0] for x in a), sum(x[1] for x in a)

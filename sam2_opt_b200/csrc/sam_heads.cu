@@ -372,10 +372,15 @@ __global__ void t2i_combine_kernel(const float* __restrict__ part, int T, float*
 // Output: the split operand os [n*4096][384] = [hi | lo | hi] of the 128 attention outputs (A of the out_proj GEMM).
 __global__ void __launch_bounds__(256) i2t_attn_kernel(const float* __restrict__ kvq, int ld, int q_col, const float* __restrict__ tk,
                                                        const float* __restrict__ tv, int T, bf16* __restrict__ os) {
-  __shared__ float ks[32 * 128];
-  __shared__ float vs[32 * 128];
+  // token keys / values as [t][head][17]: the 8 heads a warp reads at once fall on 8 different banks
+  __shared__ float ks[32 * 8 * 17];
+  __shared__ float vs[32 * 8 * 17];
   const int b = blockIdx.y, tid = threadIdx.x;
-  for (int i = tid; i < T * 128; i += 256) { ks[i] = tk[(long)b * T * 128 + i]; vs[i] = tv[(long)b * T * 128 + i]; }
+  for (int i = tid; i < T * 128; i += 256) {
+    const int j = (i >> 4) * 17 + (i & 15);
+    ks[j] = tk[(long)b * T * 128 + i];
+    vs[j] = tv[(long)b * T * 128 + i];
+  }
   __syncthreads();
   const int h = tid & 7, p = blockIdx.x * 32 + (tid >> 3);
   const long row = (long)b * 4096 + p;
@@ -391,19 +396,22 @@ __global__ void __launch_bounds__(256) i2t_attn_kernel(const float* __restrict__
   for (int d = 0; d < 16; ++d) acc[d] = 0.f;
   // two passes over the (few) tokens: exact max first, then the weighted sum
   for (int t = 0; t < T; ++t) {
+    const float* kk = ks + (t * 8 + h) * 17;
     float a = 0.f;
 #pragma unroll
-    for (int d = 0; d < 16; ++d) a = fmaf(qr[d], ks[t * 128 + h * 16 + d], a);
+    for (int d = 0; d < 16; ++d) a = fmaf(qr[d], kk[d], a);
     m = fmaxf(m, a);
   }
   for (int t = 0; t < T; ++t) {
+    const float* kk = ks + (t * 8 + h) * 17;
+    const float* vv = vs + (t * 8 + h) * 17;
     float a = 0.f;
 #pragma unroll
-    for (int d = 0; d < 16; ++d) a = fmaf(qr[d], ks[t * 128 + h * 16 + d], a);
+    for (int d = 0; d < 16; ++d) a = fmaf(qr[d], kk[d], a);
     const float e = expf(a - m);
     l += e;
 #pragma unroll
-    for (int d = 0; d < 16; ++d) acc[d] = fmaf(e, vs[t * 128 + h * 16 + d], acc[d]);
+    for (int d = 0; d < 16; ++d) acc[d] = fmaf(e, vv[d], acc[d]);
   }
   const float inv = 1.0f / l;
   __align__(16) bf16 hi[16], lo[16];

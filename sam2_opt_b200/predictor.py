@@ -404,6 +404,7 @@ class SAM2VideoPredictor(_Base):
         self.graph_track = bool(graph_track)
         self._heads_graphs = {}            # (object count, host thread) -> _GraphedHeads
         self._track_graphs = {}            # (object count, host thread) -> _GraphedTrack
+        self._copy_stream = None           # host -> device copies of the next block of frames (see _upload)
         self._tpos_cache = {}              # (num_frames, max_ptrs) -> projected temporal encodings of the object pointers
 
     @torch.no_grad()
@@ -430,16 +431,42 @@ class SAM2VideoPredictor(_Base):
         st["pending_non_cond"].clear()
         st["rings"].clear()
         st["gtrack"].clear()
+        st.pop("prefetch", None)
 
     def _prep_frame(self, f, mean, std):
         """one uint8 HWC frame -> normalised [1,3,1024,1024] fp32 (ref: utils/misc.py:96,161-162)"""
         return self._prep_image(f, normalise=True)
 
     # -- per-frame image features, produced `encode_ahead` frames at a time --------------------------------------
+    def _upload(self, st, t):
+        """Frames [t, t + encode_ahead) on the device + the block's end.  Host-resident frames (offload_video_to_cpu) cross PCIe
+        on a side stream one block AHEAD: while block k is encoded and tracked, block k + 1 is already being copied, so the
+        encoder never waits for its 200 MB of input (0.5 ms per frame at 25 GB/s when the copy sat on the compute stream)."""
+        t1 = min(st["num_frames"], t + self.encode_ahead)
+        if st["images"].is_cuda:
+            return st["images"][t:t1], t1
+        cur = torch.cuda.current_stream(self.device)
+        if self._copy_stream is None:
+            self._copy_stream = torch.cuda.Stream(device=self.device)
+        pre = st.pop("prefetch", None)
+        if pre is not None and pre[0] == (t, t1):
+            cur.wait_event(pre[2])
+            imgs = pre[1]
+        else:
+            imgs = st["images"][t:t1].to(self.device, non_blocking=True)
+        if t1 < st["num_frames"]:
+            t2 = min(st["num_frames"], t1 + self.encode_ahead)
+            with torch.cuda.stream(self._copy_stream):
+                nxt = st["images"][t1:t2].to(self.device, non_blocking=True)
+                ev = torch.cuda.Event()
+                ev.record(self._copy_stream)
+            nxt.record_stream(cur)                   # allocated on the copy stream, consumed on the compute stream
+            st["prefetch"] = ((t1, t2), nxt, ev)
+        return imgs, t1
+
     def _features(self, st, t):
         if t not in st["feat_cache"]:
-            t1 = min(st["num_frames"], t + self.encode_ahead)
-            imgs = st["images"][t:t1].to(self.device, non_blocking=True)
+            imgs, t1 = self._upload(st, t)
             outs = self._ex["inference_image"].Inference([imgs], output_type="torch")
             st["feat_cache"] = {t + i: (outs[6][i:i + 1], outs[3][i:i + 1], [outs[4][i:i + 1], outs[5][i:i + 1]]) for i in range(t1 - t)}
         return st["feat_cache"][t]      # fpn2 [1,256,64,64], pos2 [1,256,64,64], [fpn0, fpn1]
@@ -501,6 +528,51 @@ class SAM2VideoPredictor(_Base):
         st["non_cond_b"].pop(frame_idx, None)          # the batched record of this frame no longer matches this object
         low = torch.cat([self._latest_low(st, frame_idx, o) for o in st["obj_ids"]], 0)
         return frame_idx, list(st["obj_ids"]), self._video_res(st, low)
+
+    def add_new_points(self, *args, **kwargs):
+        """Deprecated alias kept by the reference (sam2_video_predictor_official.py:401-404)."""
+        return self.add_new_points_or_box(*args, **kwargs)
+
+    @torch.no_grad()
+    def add_new_mask(self, st, frame_idx, obj_id, mask):
+        """A mask prompt (what the reference's VOS tool feeds, tools/vos_inference.py:175-190).  ref:
+        sam2_video_predictor_official.py:406-486 and SAM2Base._use_mask_as_output (sam2_base_official.py:496-545): the mask itself
+        becomes the frame's output (+10 / -10 logits), only the object pointer comes from the SAM heads, which see the mask
+        through `mask_downsample` as their dense prompt.  Returns (frame_idx, obj_ids, video_res_masks)."""
+        if obj_id not in st["obj_ids"]:
+            if st["frames_tracked"]:
+                raise RuntimeError(f"Cannot add new object id {obj_id} after tracking starts; call reset_state first.")
+            st["obj_ids"].append(obj_id)
+        m = torch.as_tensor(np.asarray(mask))
+        assert m.dim() == 2, "add_new_mask expects a 2-D mask"
+        m = m.bool()[None, None].float().to(self.device)
+        if tuple(m.shape[-2:]) != (1024, 1024):
+            m = (F.interpolate(m, size=(1024, 1024), align_corners=False, mode="bilinear", antialias=True) >= 0.5).float()
+        st["gtrack"].clear()
+        st["prompts"].pop((frame_idx, obj_id), None)          # a mask prompt replaces the clicks of that frame (ref: :437)
+        is_init = frame_idx not in st["frames_tracked"]
+        is_cond = is_init or self.add_all_frames_to_correct_as_cond
+        f2, _, hr = self._features(st, frame_idx)
+        high = m * 20.0 - 10.0
+        low = F.interpolate(high, size=(256, 256), align_corners=False, mode="bilinear", antialias=True)
+        prompt = F.conv2d(m, self.w["mask_downsample.weight"], self.w["mask_downsample.bias"], stride=4)     # [1,1,256,256]
+        if self.native_heads:
+            dense = H.prompt_encoder(self.w, None, None, H.mask_prompt_256(prompt))[1]
+            ptr = self.engine.sam_heads(f2, hr, None, None, dense, multimask_output=False, high_res=False)[5]
+        else:
+            ptr = H.forward_sam_heads(self.w, f2, mask_inputs=prompt, high_res_features=hr, multimask_output=False, pe=self._dense_pe)[5]
+        lam = (m.flatten(1) > 0).any(dim=1, keepdim=True).float()             # the mask, not the decoder, says whether the object is there
+        out = {"pred_masks": self._fill_holes(low), "obj_ptr": lam * ptr + (1 - lam) * self.w["no_obj_ptr"],
+               "object_score_logits": 20.0 * lam - 10.0, "maskmem_features": None, "maskmem_pos": None}
+        if is_cond:
+            st["cond"].setdefault(frame_idx, {})[obj_id] = out
+            st["cond_b"].pop(frame_idx, None)
+        else:
+            st["non_cond"].setdefault(obj_id, {})[frame_idx] = out
+            st["pending_non_cond"].add((frame_idx, obj_id))
+        st["non_cond_b"].pop(frame_idx, None)
+        low_all = torch.cat([self._latest_low(st, frame_idx, o) for o in st["obj_ids"]], 0)
+        return frame_idx, list(st["obj_ids"]), self._video_res(st, low_all)
 
     def _latest_low(self, st, t, o):
         rec = st["cond"].get(t, {}).get(o) or st["non_cond"].get(o, {}).get(t)
