@@ -52,6 +52,13 @@ int sam2b_image_encode(sam2b_handle h, const float* img, int n, int normalised, 
  * in micro-batches overlapped with compute; returns after the stream has been synchronised. */
 int sam2b_image_encode_host(sam2b_handle h, const float* img_host, int n, int normalised, int add_no_mem_embed,
                             float* fpn0_host, float* fpn1_host, float* fpn2_host, void* stream);
+/* The same call for a serving loop: returns as soon as everything is enqueued, so that the uploads of call k + 1 overlap the
+ * compute of call k (the reference's executor is synchronous per call, tensorrt_executor.py:240-309; this is what a
+ * maintainer would use from a double-buffered loader).  The host buffers of a call must stay valid and untouched until
+ * sam2b_host_sync(h, stream) has returned, which waits for all uploads, compute and downloads issued so far. */
+int sam2b_image_encode_host_async(sam2b_handle h, const float* img_host, int n, int normalised, int add_no_mem_embed,
+                                  float* fpn0_host, float* fpn1_host, float* fpn2_host, void* stream);
+int sam2b_host_sync(sam2b_handle h, void* stream);
 /* Same, from raw frames: hwc_u8_host is HOST uint8 [n][1024][1024][3] (what set_image / set_image_batch receive,
  * sam2_image_predictor.py:173-196, already at the model resolution).  The frames cross PCIe as bytes (a quarter of the fp32
  * traffic) and ToTensor -> Normalize (sam2/utils/transforms.py:27-46) runs on the device, bit-identical to the reference;

@@ -19,6 +19,8 @@ SIGNATURES = {
     "sam2b_finalize": (_i, [_vp]),
     "sam2b_image_encode": (_i, [_vp, _vp, _i, _i, _i, _vp, _vp, _vp, _vp]),
     "sam2b_image_encode_host": (_i, [_vp, _vp, _i, _i, _i, _vp, _vp, _vp, _vp]),
+    "sam2b_image_encode_host_async": (_i, [_vp, _vp, _i, _i, _i, _vp, _vp, _vp, _vp]),
+    "sam2b_host_sync": (_i, [_vp, _vp]),
     "sam2b_image_encode_host_u8": (_i, [_vp, _vp, _i, _i, _vp, _vp, _vp, _vp]),
     "sam2b_position_encoding": (_i, [_i, _i, _i, _vp, _vp]),
     "sam2b_memory_attention": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _vp, _vp, _i, _i, _vp, _vp]),

@@ -116,6 +116,7 @@ struct sam2b_engine {
   cudaEvent_t done = nullptr;
   bool done_valid = false;
   unsigned long long ws_generation = 0;   // bumped whenever a workspace buffer is re-allocated
+  unsigned long long host_it = 0;         // micro-batches pushed through the host-buffer path so far (staging slot = host_it & 1)
 
   Tensor* find(const std::string& n) {
     auto it = w.find(n);
@@ -1056,8 +1057,11 @@ int sam2b_image_encode(sam2b_handle h, const float* img, int n, int normalised, 
 
 // Host-buffer encode.  `u8` = 0: img_host is fp32 [n][3][1024][1024]; `u8` = 1: img_host is uint8 [n][1024][1024][3] (raw frames),
 // uploaded as bytes (a quarter of the PCIe traffic) and converted on the device by preprocess_u8_hwc (/255, then mean/std).
+// async_mode: return without synchronising and without fencing the copy streams behind the caller's earlier work, so that
+// the uploads of this call overlap the compute of the previous one (sam2b_host_sync waits for everything).  The two staging
+// slots and their events live across calls (h->host_it), which is what orders slot re-use between calls.
 static int image_encode_host_impl(sam2b_handle h, const void* img_host_v, int u8, int n, int normalised, int add_no_mem_embed,
-                                  float* fpn0_host, float* fpn1_host, float* fpn2_host, void* stream) {
+                                  float* fpn0_host, float* fpn1_host, float* fpn2_host, void* stream, int async_mode = 0) {
   if (!h || !h->finalized) { set_error("sam2b_image_encode_host: engine not finalized"); return 1; }
   if (n <= 0 || !img_host_v || !fpn0_host || !fpn1_host || !fpn2_host) { set_error("sam2b_image_encode_host: bad arguments"); return 1; }
   ENTER_DEVICE(h->device);
@@ -1084,12 +1088,14 @@ static int image_encode_host_impl(sam2b_handle h, const void* img_host_v, int u8
   cudaStream_t cs = h->copy_stream, ds = h->copy_stream2;
   // ev[0..1]: input slot s uploaded; ev[2..3]: compute on slot s done; ev[4..5]: outputs of slot s downloaded;
   // ev[8..9], ev[10..11]: fpn0 / fpn1 of slot s complete (early, see image_encode_mb)
-  CUDA_OK(cudaEventRecord(h->ev[6], st));
-  CUDA_OK(cudaStreamWaitEvent(cs, h->ev[6], 0));
-  CUDA_OK(cudaStreamWaitEvent(ds, h->ev[6], 0));
-  int it = 0;
-  for (int i0 = 0; i0 < n; i0 += kMaxMicroBatch, ++it) {
-    const int s = it & 1;
+  if (!async_mode || h->host_it == 0) {
+    CUDA_OK(cudaEventRecord(h->ev[6], st));
+    CUDA_OK(cudaStreamWaitEvent(cs, h->ev[6], 0));
+    CUDA_OK(cudaStreamWaitEvent(ds, h->ev[6], 0));
+  }
+  for (int i0 = 0; i0 < n; i0 += kMaxMicroBatch) {
+    const unsigned long long it = h->host_it++;
+    const int s = (int)(it & 1);
     const int mb = (n - i0) < kMaxMicroBatch ? (n - i0) : kMaxMicroBatch;
     if (it >= 2) CUDA_OK(cudaStreamWaitEvent(cs, h->ev[2 + s], 0));       // slot's previous compute has consumed the input
     if (u8) CUDA_OK(cudaMemcpyAsync(raw[s], img_host_u8 + (size_t)i0 * in_sz, in_sz * mb, cudaMemcpyHostToDevice, cs));
@@ -1109,6 +1115,7 @@ static int image_encode_host_impl(sam2b_handle h, const void* img_host_v, int u8
     CUDA_OK(cudaMemcpyAsync(fpn2_host + (size_t)i0 * o2, f2[s], o2 * mb * 4, cudaMemcpyDeviceToHost, ds));
     CUDA_OK(cudaEventRecord(h->ev[4 + s], ds));
   }
+  if (async_mode) return 0;
   CUDA_OK(cudaStreamSynchronize(ds));
   CUDA_OK(cudaStreamSynchronize(cs));
   CUDA_OK(cudaStreamSynchronize(st));
@@ -1118,6 +1125,19 @@ static int image_encode_host_impl(sam2b_handle h, const void* img_host_v, int u8
 int sam2b_image_encode_host(sam2b_handle h, const float* img_host, int n, int normalised, int add_no_mem_embed,
                             float* fpn0_host, float* fpn1_host, float* fpn2_host, void* stream) {
   return image_encode_host_impl(h, img_host, 0, n, normalised, add_no_mem_embed, fpn0_host, fpn1_host, fpn2_host, stream);
+}
+
+int sam2b_image_encode_host_async(sam2b_handle h, const float* img_host, int n, int normalised, int add_no_mem_embed,
+                                  float* fpn0_host, float* fpn1_host, float* fpn2_host, void* stream) {
+  return image_encode_host_impl(h, img_host, 0, n, normalised, add_no_mem_embed, fpn0_host, fpn1_host, fpn2_host, stream, 1);
+}
+int sam2b_host_sync(sam2b_handle h, void* stream) {
+  if (!h) { set_error("sam2b_host_sync: null engine"); return 1; }
+  ENTER_DEVICE(h->device);
+  CUDA_OK(cudaStreamSynchronize(h->copy_stream2));
+  CUDA_OK(cudaStreamSynchronize(h->copy_stream));
+  CUDA_OK(cudaStreamSynchronize(reinterpret_cast<cudaStream_t>(stream)));
+  return 0;
 }
 
 int sam2b_image_encode_host_u8(sam2b_handle h, const void* hwc_u8_host, int n, int add_no_mem_embed,

@@ -138,19 +138,25 @@ class Engine:
                                                    _ptr(f0), _ptr(f1), _ptr(f2), self._stream()), "image_encode")
         return f0, f1, f2
 
-    def image_encode_host(self, img: torch.Tensor, normalised: bool, add_no_mem_embed: bool, out=None):
-        """Same through HOST tensors (pinned recommended): copies overlap compute inside the library."""
+    def image_encode_host(self, img: torch.Tensor, normalised: bool, add_no_mem_embed: bool, out=None, wait=True):
+        """Same through HOST tensors (pinned recommended): copies overlap compute inside the library.
+        wait=False (serving loops): return once everything is enqueued, so that the next call's uploads overlap this call's
+        compute; `img` and `out` must then stay alive and untouched until `host_sync()`."""
         assert not img.is_cuda and img.dtype == torch.float32 and img.is_contiguous()
         n = img.shape[0]
         if out is None:
             out = (torch.empty((n, 32, 256, 256), dtype=torch.float32).pin_memory(),
                    torch.empty((n, 64, 128, 128), dtype=torch.float32).pin_memory(),
                    torch.empty((n, 256, 64, 64), dtype=torch.float32).pin_memory())
+        fn = self.lib.sam2b_image_encode_host if wait else self.lib.sam2b_image_encode_host_async
         with self._lock:
-            _lib.check(self.lib.sam2b_image_encode_host(self._h, _ptr(img), n, int(normalised), int(add_no_mem_embed),
-                                                        _ptr(out[0]), _ptr(out[1]), _ptr(out[2]), self._stream()),
-                       "image_encode_host")
+            _lib.check(fn(self._h, _ptr(img), n, int(normalised), int(add_no_mem_embed),
+                          _ptr(out[0]), _ptr(out[1]), _ptr(out[2]), self._stream()), "image_encode_host")
         return out
+
+    def host_sync(self):
+        """Wait for every upload, kernel and download the host-buffer entry points have issued so far."""
+        _lib.check(self.lib.sam2b_host_sync(self._h, self._stream()), "host_sync")
 
     def image_encode_host_u8(self, frames: torch.Tensor, add_no_mem_embed: bool, out=None):
         """Raw HOST frames uint8 [n,1024,1024,3] (pinned recommended) -> the three HOST feature levels.  The frames are

@@ -59,3 +59,22 @@ def iou(a_bool, b_bool):
     a_bool, b_bool = np.asarray(a_bool, dtype=bool), np.asarray(b_bool, dtype=bool)
     u = (a_bool | b_bool).sum()
     return 1.0 if u == 0 else float((a_bool & b_bool).sum()) / float(u)
+
+
+def propagate_low_res_from_masks(model, frames, masks, max_track=None):
+    """Same with MASK prompts on frame 0 (`add_new_mask`, what the reference's tools/vos_inference.py feeds): `masks` =
+    {obj_id: bool array [H,W]}; returns ({frame: {obj_id: low-res logits}}, {obj_id: obj_ptr of frame 0})."""
+    with synthetic_video(frames):
+        st = model.init_state("synthetic")
+    for oid, m in masks.items():
+        model.add_new_mask(st, 0, oid, m)
+    out, ptrs = {}, {}
+    for fi, obj_ids, video_res in model.propagate_in_video(st, max_frame_num_to_track=max_track):
+        out[fi] = {}
+        for oid in obj_ids:
+            d = st["output_dict_per_obj"][st["obj_id_to_idx"][oid]]
+            rec = d["cond_frame_outputs"].get(fi) or d["non_cond_frame_outputs"][fi]
+            out[fi][oid] = rec["pred_masks"][0, 0].float().cpu().clone()
+            if fi == 0:
+                ptrs[oid] = rec["obj_ptr"][0].float().cpu().clone()
+    return out, ptrs

@@ -98,6 +98,27 @@ def test_host_buffer_entry_point_matches_device_path(engine):
         assert torch.equal(d.cpu(), h)
 
 
+def test_async_host_calls_overlap_without_changing_results(engine):
+    """sam2b_image_encode_host_async: three calls in flight over two sets of pinned buffers (an odd number of micro-batches
+    per call, so that consecutive calls start on different staging slots), one sam2b_host_sync at the end; every call must
+    return exactly what the device path returns, and a synchronous call afterwards still works."""
+    from oracle.synth import synth_image_norm
+    batches = [synth_image_norm(20, seed=21 + k) for k in range(3)]
+    want = []
+    for b in batches:
+        want.append([t.cpu() for t in engine.image_encode(b.cuda(), normalised=True, add_no_mem_embed=False)])
+    torch.cuda.synchronize()
+    pinned = [b.pin_memory() for b in batches]
+    outs = [engine.image_encode_host(pinned[k], True, False, None, wait=False) for k in range(3)]
+    engine.host_sync()
+    for k in range(3):
+        for w, h in zip(want[k], outs[k]):
+            assert torch.equal(w, h), f"async call {k} differs from the device path"
+    again = engine.image_encode_host(pinned[0], True, False)
+    for w, h in zip(want[0], again):
+        assert torch.equal(w, h)
+
+
 def test_fused_mlp_path_matches_the_two_gemm_path(monkeypatch):
     """mlp_fused.cu (fc1 -> GELU -> fc2 in one kernel for the stage-1 blocks, hidden layer in tensor memory; the default)
     against the fc1 / fc2 GEMM pair (SAM2B_FUSED_MLP=0) on the same engine: same arithmetic up to the order of the fp32 sums
