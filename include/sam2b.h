@@ -95,6 +95,16 @@ int sam2b_memory_attention_varlen(sam2b_handle h, const float* curr, const float
  * (the second reference output, the sine position encoding, is a constant: sam2b_position_encoding) */
 int sam2b_memory_encode(sam2b_handle h, const float* pix_feat, const float* masks, int n, float* out_x, void* stream);
 
+/* The same from the LOW-RESOLUTION mask logits the SAM heads produce: what SAM2Base._encode_new_memory does around the encoder
+ * (sam2_base_official.py:978-1026) is folded in.  low_res_masks dev [n,1,256,256]; the 1024^2 input of the down-sampler,
+ *   mask_for_mem = sigmoid(bilinear_x4(low)) * 20 - 10     (binarize = 1: (bilinear_x4(low) > 0) * 20 - 10, prompted frames),
+ * is evaluated inside the first convolution and never reaches memory (the reference writes the high-res mask, its sigmoid and
+ * the scaled copy: 4 x 4 MB per object and frame).  pix_batch_stride: 1048576, or 0 when all n objects share one frame's
+ * pix_feat [1,256,64,64].  object_score_logits dev [n] or NULL: objects with a score <= 0 get no_obj_embed_spatial added to
+ * their output (sam2_base_official.py:1019-1024). */
+int sam2b_memory_encode_low_res(sam2b_handle h, const float* pix_feat, int64_t pix_batch_stride, const float* low_res_masks,
+                                int binarize, const float* object_score_logits, int n, float* out_x, void* stream);
+
 /* ---- SAM heads: prompt encoder (points) + two-way mask decoder + object-pointer head ----
  * Replaces SAM2Base._forward_sam_heads (sam2/sam2/modeling/sam2_base_official.py:338-494), i.e. PromptEncoder._embed_points
  * (sam/prompt_encoder.py:124-150), MaskDecoder.forward / predict_masks (sam/mask_decoder.py:116-316, incl. the dynamic
@@ -108,19 +118,23 @@ int sam2b_memory_encode(sam2b_handle h, const float* pix_feat, const float* mask
  * point_coords dev [n,num_points,2] (x, y in the 1024 frame, before the +0.5 shift), point_labels dev int32 [n,num_points]
  *                  (-1 padding, 0/1 negative/positive click, 2/3 box corners); num_points = 0: no prompt (a tracked frame).
  *                  The padding point the reference appends is added internally; num_points <= 25.
+ * sparse_embeddings dev [n,num_sparse,256] or NULL: the sparse prompt embeddings themselves (MaskDecoder.forward's
+ *                  `sparse_prompt_embeddings`, e.g. from the reference's own PromptEncoder); when given they follow the 6 output
+ *                  tokens as they are (no padding point is added, num_sparse in [0,26]) and the point arguments are ignored
  * dense_embedding  dev [n,256,64,64] (the prompt encoder's mask_downscaling output) or NULL: no_mask_embed
  * multimask_output 1: the 3 multimask outputs and the best of them; 0: mask 0 unless it is unstable (dynamic fallback)
  * decoder_only     1: plain MaskDecoder.forward semantics (no NO_OBJ_SCORE fill: what SAM2ImagePredictor.predict uses)
  * outputs (any may be NULL), M = multimask_output ? 3 : 1:
  *   low_res_multimasks dev [n,M,256,256], high_res_multimasks dev [n,M,1024,1024], ious dev [n,M],
  *   low_res_masks dev [n,1,256,256] / high_res_masks dev [n,1,1024,1024] (the best mask), obj_ptr dev [n,256],
- *   object_score_logits dev [n,1]. */
+ *   object_score_logits dev [n,1], mask_tokens_out dev [n,4,256] (the four mask tokens after the transformer, from which
+ *   MaskDecoder.forward slices its `sam_tokens_out`). */
 int sam2b_sam_heads(sam2b_handle h, const float* backbone_features, int64_t feat_stride_n, int64_t feat_stride_c,
                     int64_t feat_stride_p, const float* feat_s0, int64_t s0_batch_stride, const float* feat_s1,
                     int64_t s1_batch_stride, const float* point_coords, const int32_t* point_labels, int num_points,
-                    const float* dense_embedding, int n, int multimask_output, int decoder_only, float* low_res_multimasks,
-                    float* high_res_multimasks, float* ious, float* low_res_masks, float* high_res_masks, float* obj_ptr,
-                    float* object_score_logits, void* stream);
+                    const float* sparse_embeddings, int num_sparse, const float* dense_embedding, int n, int multimask_output,
+                    int decoder_only, float* low_res_multimasks, float* high_res_multimasks, float* ious, float* low_res_masks,
+                    float* high_res_masks, float* obj_ptr, float* object_score_logits, float* mask_tokens_out, void* stream);
 
 /* ---- CUDA graphs over engine calls ----
  * The reference replays nothing: every frame re-enqueues its TensorRT contexts (tensorrt_executor.py:232-309).  Here the

@@ -26,8 +26,9 @@ SIGNATURES = {
     "sam2b_memory_attention": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _vp, _vp, _i, _i, _vp, _vp]),
     "sam2b_memory_attention_varlen": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _vp, _vp, _i, _i, C.POINTER(C.c_int32), C.POINTER(C.c_int32), _vp, _vp]),
     "sam2b_memory_encode": (_i, [_vp, _vp, _vp, _i, _vp, _vp]),
-    "sam2b_sam_heads": (_i, [_vp, _vp, _i64, _i64, _i64, _vp, _i64, _vp, _i64, _vp, _vp, _i, _vp, _i, _i, _i,
-                             _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
+    "sam2b_memory_encode_low_res": (_i, [_vp, _vp, _i64, _vp, _i, _vp, _i, _vp, _vp]),
+    "sam2b_sam_heads": (_i, [_vp, _vp, _i64, _i64, _i64, _vp, _i64, _vp, _i64, _vp, _vp, _i, _vp, _i, _vp, _i, _i, _i,
+                             _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "sam2b_stream_acquire": (_i, [_vp, _vp]),
     "sam2b_stream_release": (_i, [_vp, _vp]),
     "sam2b_workspace_generation": (C.c_ulonglong, [_vp]),

@@ -698,7 +698,10 @@ static int memory_attention_mb(sam2b_engine* e, const float* curr, const float* 
 // ------------------------------------------------------------------------------------------------------------
 // MemoryEncoder (boundary E4): MaskDownSampler -> + pix_feat_proj -> 2 x CXBlock -> out_proj, channels-last inside.
 // ------------------------------------------------------------------------------------------------------------
-static int memory_encode_mb(sam2b_engine* e, const float* pix_feat, const float* masks, int n, float* out_x, cudaStream_t st) {
+// low (optional, instead of masks): the low-resolution logits [n,256,256]; the 1024^2 mask_for_mem is then evaluated inside the
+// first down-sampler stage (binarize: the (mask > 0) form of prompted frames).  obj (optional): object_score_logits [n].
+static int memory_encode_mb(sam2b_engine* e, const float* pix_feat, const float* masks, int n, float* out_x, cudaStream_t st,
+                            const float* low = nullptr, int binarize = 0, const float* obj = nullptr, long pix_batch_stride = -1) {
   const long T = 4096L * n;
   float *D1, *D2, *D3, *D4, *MDS, *X;
   bf16 *COLS, *D3B, *D4N, *PIXT, *XN, *HID, *XB;
@@ -722,7 +725,8 @@ static int memory_encode_mb(sam2b_engine* e, const float* pix_feat, const float*
   int H = 1024;
   for (int j = 0; j < 2; ++j) {       // 1 -> 4 -> 16 channels: a few taps per output, fp32 FMA kernels (HBM bound)
     const std::string c = en + std::to_string(3 * j) + ".", l = en + std::to_string(3 * j + 1) + ".";
-    TRY(mask_ds_stage(j + 1, stage_in, stage_out[j], n, H, P(c + "weight"), P(c + "bias"), P(l + "weight"), P(l + "bias"), st));
+    if (j == 0 && low) TRY(mask_ds1_from_low(low, D1, n, binarize, P(c + "weight"), P(c + "bias"), P(l + "weight"), P(l + "bias"), st));
+    else TRY(mask_ds_stage(j + 1, stage_in, stage_out[j], n, H, P(c + "weight"), P(c + "bias"), P(l + "weight"), P(l + "bias"), st));
     stage_in = stage_out[j];
     H /= 2;
   }
@@ -745,7 +749,7 @@ static int memory_encode_mb(sam2b_engine* e, const float* pix_feat, const float*
   TRY(linear(COLS, T, 576, W16(e, "derived.memenc.ds4.weight"), P(en + "9.bias"), 256, ACT_NONE, nullptr, nullptr, D4, nullptr));
   TRY(layernorm_gelu_rows(D4, P(en + "10.weight"), P(en + "10.bias"), 1e-6f, D4N, T, 256, st));
   TRY(linear(D4N, T, 256, W16(e, en + "12.weight"), P(en + "12.bias"), 256, ACT_NONE, nullptr, nullptr, MDS, nullptr));
-  TRY(nchw_to_nhwc_bf16(pix_feat, PIXT, n, 256, 4096, st));
+  TRY(nchw_to_nhwc_bf16(pix_feat, PIXT, n, 256, 4096, st, pix_batch_stride));
   TRY(linear(PIXT, T, 256, W16(e, m + "pix_feat_proj.weight"), P(m + "pix_feat_proj.bias"), 256, ACT_NONE, nullptr, MDS, X, nullptr));
   for (int l = 0; l < 2; ++l) {
     const std::string f = m + "fuser.layers." + std::to_string(l) + ".";
@@ -764,6 +768,10 @@ static int memory_encode_mb(sam2b_engine* e, const float* pix_feat, const float*
     g.out_f32 = out_x; g.ldc = 4096; g.c_batch_stride = 64L * 4096;
     TRY(gemm_bf16(g, st));
   }
+  if (obj) {
+    if (!e->find("no_obj_embed_spatial")) { set_error("memory_encode: object scores given but the engine has no no_obj_embed_spatial tensor"); return 1; }
+    TRY(add_no_obj_embed(out_x, obj, W32(e, "no_obj_embed_spatial"), n, st));
+  }
   return 0;
 }
 
@@ -780,13 +788,14 @@ struct HeadsIO {
   const float* s0; long s0_bs;                   // conv_s0 level [.,32,256,256], batch stride (0: one image for all)
   const float* s1; long s1_bs;                   // conv_s1 level [.,64,128,128]
   const float* coords; const int* labels; int P; // device, [n,P,2] / [n,P]
+  const float* sparse; int S;                    // optional: the sparse prompt embeddings themselves [n,S,256] (then no points)
   const float* dense;                            // optional dense prompt embedding [n,256,64,64]
   int multimask, decoder_only;
-  float *low_multi, *high_multi, *ious, *low_best, *high_best, *obj_ptr, *obj_logits;
+  float *low_multi, *high_multi, *ious, *low_best, *high_best, *obj_ptr, *obj_logits, *mask_tokens;
 };
 
 static int sam_heads_mb(sam2b_engine* e, const HeadsIO& io, int n, cudaStream_t st) {
-  const int P = io.P > 0 ? io.P : 1, T = 6 + P + 1, nT = n * T;
+  const int P = io.P > 0 ? io.P : 1, T = io.sparse ? 6 + io.S : 6 + P + 1, nT = n * T;
   const long R = 4096L * n;
   float *KEYS, *KVQ, *XR, *TOK, *QPE, *TQ, *TK, *TV, *TA, *PART, *HID, *TPART, *H1, *H2, *IOU, *OBJ, *HYP, *PTR4, *MASKS, *IOUT, *OBJT, *PTRT;
   bf16 *KS, *OS;
@@ -804,7 +813,7 @@ static int sam_heads_mb(sam2b_engine* e, const HeadsIO& io, int n, cudaStream_t 
   TRY(ws_get_t(e, "sh_ta", (size_t)nT * 256, &TA));
   TRY(ws_get_t(e, "sh_part", (size_t)8 * nT * 256, &PART));
   TRY(ws_get_t(e, "sh_hid", (size_t)nT * 2048, &HID));
-  TRY(ws_get_t(e, "sh_tpart", (size_t)n * 8 * 16 * T * 18, &TPART));
+  TRY(ws_get_t(e, "sh_tpart", (size_t)n * 128 * T * 8 * 18, &TPART));      // 128 key tiles x T tokens x 8 heads x (max, sum, 16 outputs)
   TRY(ws_get_t(e, "sh_h1", (size_t)10 * n * 256, &H1));
   TRY(ws_get_t(e, "sh_h2", (size_t)10 * n * 256, &H2));
   TRY(ws_get_t(e, "sh_iou", (size_t)n * 4, &IOU));
@@ -824,7 +833,7 @@ static int sam_heads_mb(sam2b_engine* e, const HeadsIO& io, int n, cudaStream_t 
   // prompt encoder: no prompt at all = one point with label -1 (sam2_base_official.py:391-395) + the padding point
   const float* coords = io.coords;
   const int* labels = io.labels;
-  if (io.P <= 0) {
+  if (io.P <= 0 && !io.sparse) {
     CUDA_OK(cudaMemsetAsync(LABP, 0xFF, (size_t)n * 4 * sizeof(int), st));     // labels = -1; the coordinates are never read
     labels = LABP;
     coords = reinterpret_cast<const float*>(LABP);
@@ -832,8 +841,8 @@ static int sam_heads_mb(sam2b_engine* e, const HeadsIO& io, int n, cudaStream_t 
   const float* pt_emb[4] = {P32(pe + "point_embeddings.0.weight"), P32(pe + "point_embeddings.1.weight"),
                             P32(pe + "point_embeddings.2.weight"), P32(pe + "point_embeddings.3.weight")};
   TRY(heads_tokens(coords, labels, P, n, P32(pe + "pe_layer.positional_encoding_gaussian_matrix"), P32(pe + "not_a_point_embed.weight"),
-                   pt_emb, P32(md + "obj_score_token.weight"), P32(md + "iou_token.weight"), P32(md + "mask_tokens.weight"), TOK,
-                   QPE, st));
+                   pt_emb, P32(md + "obj_score_token.weight"), P32(md + "iou_token.weight"), P32(md + "mask_tokens.weight"),
+                   io.sparse, io.S, TOK, QPE, st));
   TRY(heads_prep_src(io.pix, io.sn, io.sc, io.sp, io.dense, P32(pe + "no_mask_embed.weight"), KEYS, KS, n, st));
 
   auto job = [&](const float* X, long ldx, const float* X2, const float* Wt, long ldw, const float* b, float* Y, long ldy, int rows,
@@ -908,6 +917,9 @@ static int sam_heads_mb(sam2b_engine* e, const HeadsIO& io, int n, cudaStream_t 
   TRY(image_gemm(KS, 768, "derived.heads.final.kv.weight", 256, nullptr, P32("derived.heads.final.kv.table"), 256, 4096, KVQ, 256));
   TRY(t2i_block(tr + "final_attn_token_to_image.", 256, tr + "norm_final_attn."));
 
+  if (io.mask_tokens)     // MaskDecoder.forward's third output comes from these: the four mask tokens after the transformer
+    CUDA_OK(cudaMemcpy2DAsync(io.mask_tokens, 4 * 256 * sizeof(float), TOK + 2 * 256, (size_t)T * 256 * sizeof(float),
+                              4 * 256 * sizeof(float), n, cudaMemcpyDeviceToDevice, st));
   // the small heads on the output tokens (mask_decoder.py:302-316, sam2_base_official.py:474-494): IoU (token 1), object score
   // (token 0), the four hyper-network MLPs and obj_ptr_proj on the four mask tokens (tokens 2..5); three launches of 10 jobs
   const std::string heads[10] = {md + "iou_prediction_head.", md + "pred_obj_score_head.", md + "output_hypernetworks_mlps.0.",
@@ -1201,14 +1213,15 @@ int sam2b_memory_encode(sam2b_handle h, const float* pix_feat, const float* mask
 int sam2b_sam_heads(sam2b_handle h, const float* backbone_features, int64_t feat_stride_n, int64_t feat_stride_c,
                     int64_t feat_stride_p, const float* feat_s0, int64_t s0_batch_stride, const float* feat_s1,
                     int64_t s1_batch_stride, const float* point_coords, const int32_t* point_labels, int num_points,
-                    const float* dense_embedding, int n, int multimask_output, int decoder_only, float* low_res_multimasks,
-                    float* high_res_multimasks, float* ious, float* low_res_masks, float* high_res_masks, float* obj_ptr,
-                    float* object_score_logits, void* stream) {
+                    const float* sparse_embeddings, int num_sparse, const float* dense_embedding, int n, int multimask_output,
+                    int decoder_only, float* low_res_multimasks, float* high_res_multimasks, float* ious, float* low_res_masks,
+                    float* high_res_masks, float* obj_ptr, float* object_score_logits, float* mask_tokens_out, void* stream) {
   if (!h || !h->finalized) { set_error("sam2b_sam_heads: engine not finalized"); return 1; }
   if (!h->has_heads) { set_error("sam2b_sam_heads: the engine was built without the sam_mask_decoder / sam_prompt_encoder tensors"); return 1; }
   if (!backbone_features || !feat_s0 || !feat_s1 || n <= 0) { set_error("sam2b_sam_heads: null/empty argument"); return 1; }
   if (num_points < 0 || num_points > 25) { set_error("sam2b_sam_heads: %d points per prompt (0..25)", num_points); return 1; }
-  if (num_points > 0 && (!point_coords || !point_labels)) { set_error("sam2b_sam_heads: num_points=%d but the point arrays are NULL", num_points); return 1; }
+  if (sparse_embeddings && (num_sparse < 0 || num_sparse > 26)) { set_error("sam2b_sam_heads: %d sparse embeddings per prompt (0..26)", num_sparse); return 1; }
+  if (!sparse_embeddings && num_points > 0 && (!point_coords || !point_labels)) { set_error("sam2b_sam_heads: num_points=%d but the point arrays are NULL", num_points); return 1; }
   if (high_res_multimasks && !low_res_multimasks) { set_error("sam2b_sam_heads: high_res_multimasks needs low_res_multimasks"); return 1; }
   ENTER_DEVICE(h->device);
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
@@ -1223,6 +1236,8 @@ int sam2b_sam_heads(sam2b_handle h, const float* backbone_features, int64_t feat
     io.coords = point_coords ? point_coords + (size_t)i0 * num_points * 2 : nullptr;
     io.labels = point_labels ? point_labels + (size_t)i0 * num_points : nullptr;
     io.P = num_points;
+    io.sparse = sparse_embeddings ? sparse_embeddings + (size_t)i0 * num_sparse * 256 : nullptr; io.S = num_sparse;
+    io.mask_tokens = mask_tokens_out ? mask_tokens_out + (size_t)i0 * 4 * 256 : nullptr;
     io.dense = dense_embedding ? dense_embedding + (size_t)i0 * 256 * 4096 : nullptr;
     io.multimask = multimask_output ? 1 : 0; io.decoder_only = decoder_only ? 1 : 0;
     io.low_multi = low_res_multimasks ? low_res_multimasks + (size_t)i0 * M * 65536 : nullptr;
@@ -1233,6 +1248,24 @@ int sam2b_sam_heads(sam2b_handle h, const float* backbone_features, int64_t feat
     io.obj_ptr = obj_ptr ? obj_ptr + (size_t)i0 * 256 : nullptr;
     io.obj_logits = object_score_logits ? object_score_logits + i0 : nullptr;
     TRY(sam_heads_mb(h, io, mb, st));
+  }
+  return 0;
+}
+
+int sam2b_memory_encode_low_res(sam2b_handle h, const float* pix_feat, int64_t pix_batch_stride, const float* low_res_masks,
+                                int binarize, const float* object_score_logits, int n, float* out_x, void* stream) {
+  if (!h || !h->finalized) { set_error("sam2b_memory_encode_low_res: engine not finalized"); return 1; }
+  if (!pix_feat || !low_res_masks || !out_x || n <= 0) { set_error("sam2b_memory_encode_low_res: null/empty argument"); return 1; }
+  if (pix_batch_stride != 0 && pix_batch_stride != 256 * 4096) { set_error("sam2b_memory_encode_low_res: pix_batch_stride must be 0 (one frame for all objects) or 1048576"); return 1; }
+  ENTER_DEVICE(h->device);
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  ENGINE_CALL(h, st);
+  const int kMaxMicroBatch = 16;
+  for (int i0 = 0; i0 < n; i0 += kMaxMicroBatch) {
+    const int mb = (n - i0) < kMaxMicroBatch ? (n - i0) : kMaxMicroBatch;
+    TRY(memory_encode_mb(h, pix_feat + (size_t)i0 * pix_batch_stride, nullptr, mb, out_x + (size_t)i0 * 64 * 4096, st,
+                         low_res_masks + (size_t)i0 * 65536, binarize, object_score_logits ? object_score_logits + i0 : nullptr,
+                         pix_batch_stride));
   }
   return 0;
 }

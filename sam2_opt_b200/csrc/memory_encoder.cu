@@ -104,6 +104,99 @@ __global__ void __launch_bounds__(256) mask_ds1_kernel(const float* __restrict__
   }
 }
 
+// stage 1 straight from the low-resolution mask logits [n][256][256]: the 1024^2 input of the down-sampler,
+//   mask_for_mem = sigmoid(bilinear_x4(low)) * 20 - 10        (binarize: (bilinear_x4(low) > 0) * 20 - 10)
+// (SAM2Base._encode_new_memory, sam2_base_official.py:1000-1013, on the high-res mask of _forward_sam_heads :447-452), is
+// evaluated per tap instead of being materialised: bilinear weights in the arithmetic of upsample_bilinear_mask (fp32, no
+// contraction), then the same conv3x3 s2 + LayerNorm2d + GELU as mask_ds1_kernel.
+__device__ __forceinline__ void ds_bilinear_coord(int dst, int in_size, int& i0, int& i1, float& l0, float& l1) {
+  float src = __fmaf_rn(0.25f, __fadd_rn((float)dst, 0.5f), -0.5f);
+  src = src < 0.f ? 0.f : src;
+  i0 = (int)src;
+  if (i0 > in_size - 1) i0 = in_size - 1;
+  i1 = i0 + (i0 < in_size - 1 ? 1 : 0);
+  l1 = __fsub_rn(src, (float)i0);
+  l1 = l1 < 0.f ? 0.f : (l1 > 1.f ? 1.f : l1);
+  l0 = __fsub_rn(1.f, l1);
+}
+__global__ void __launch_bounds__(256) mask_ds1_low_kernel(const float* __restrict__ low, float4* __restrict__ out, int n, int binarize,
+                                                           const float* __restrict__ w, const float* __restrict__ b,
+                                                           const float* __restrict__ ln_w, const float* __restrict__ ln_b) {
+  __shared__ float sw[36 + 12];
+  if (threadIdx.x < 36) sw[threadIdx.x] = w[threadIdx.x];
+  else if (threadIdx.x < 40) sw[threadIdx.x] = b[threadIdx.x - 36];
+  else if (threadIdx.x < 44) sw[threadIdx.x] = ln_w[threadIdx.x - 40];
+  else if (threadIdx.x < 48) sw[threadIdx.x] = ln_b[threadIdx.x - 44];
+  __syncthreads();
+  const int S = 1024, So = 512, L = 256;
+  const long total = (long)n * So * So;
+  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
+    const int ox = (int)(i % So);
+    const int oy = (int)((i / So) % So);
+    const float* src = low + (i / ((long)So * So)) * L * L;
+    int cx0[3], cx1[3];
+    float wx0[3], wx1[3];
+#pragma unroll
+    for (int kx = 0; kx < 3; ++kx) {
+      const int x = 2 * ox - 1 + kx;
+      ds_bilinear_coord(x < 0 ? 0 : (x >= S ? S - 1 : x), L, cx0[kx], cx1[kx], wx0[kx], wx1[kx]);
+    }
+    float o[4] = {sw[36], sw[37], sw[38], sw[39]};
+#pragma unroll
+    for (int ky = 0; ky < 3; ++ky) {
+      const int y = 2 * oy - 1 + ky;
+      if (y < 0 || y >= S) continue;
+      int y0, y1; float hl0, hl1;
+      ds_bilinear_coord(y, L, y0, y1, hl0, hl1);
+      const float* r0 = src + y0 * L;
+      const float* r1 = src + y1 * L;
+#pragma unroll
+      for (int kx = 0; kx < 3; ++kx) {
+        const int x = 2 * ox - 1 + kx;
+        if (x < 0 || x >= S) continue;
+        const float top = __fadd_rn(__fmul_rn(wx0[kx], __ldg(r0 + cx0[kx])), __fmul_rn(wx1[kx], __ldg(r0 + cx1[kx])));
+        const float bot = __fadd_rn(__fmul_rn(wx0[kx], __ldg(r1 + cx0[kx])), __fmul_rn(wx1[kx], __ldg(r1 + cx1[kx])));
+        const float hi = __fadd_rn(__fmul_rn(hl0, top), __fmul_rn(hl1, bot));
+        const float p = binarize ? (hi > 0.f ? 1.0f : 0.0f) : 1.0f / (1.0f + expf(-hi));
+        const float v = __fadd_rn(__fmul_rn(p, 20.0f), -10.0f);
+#pragma unroll
+        for (int c = 0; c < 4; ++c) o[c] = fmaf(v, sw[c * 9 + ky * 3 + kx], o[c]);
+      }
+    }
+    const float mean = 0.25f * ((o[0] + o[1]) + (o[2] + o[3]));
+    float q = 0.f;
+#pragma unroll
+    for (int c = 0; c < 4; ++c) q += (o[c] - mean) * (o[c] - mean);
+    const float rstd = rsqrtf(0.25f * q + 1e-6f);
+    ln_gelu_inplace<4>(o, sw + 40, sw + 44, 0, mean, rstd);
+    out[i] = make_float4(o[0], o[1], o[2], o[3]);
+  }
+}
+int mask_ds1_from_low(const float* low, float* out, int n, int binarize, const float* w, const float* b, const float* ln_w,
+                      const float* ln_b, cudaStream_t stream) {
+  const long pix = (long)n * 512 * 512;
+  ProfRange pr(stream, "mask_ds1_low", 2.0 * pix * 36, (double)pix * 16.0 + (double)n * 65536 * 4.0);
+  long blocks = (pix + 255) / 256; if (blocks > (long)num_sms() * 16) blocks = (long)num_sms() * 16;
+  mask_ds1_low_kernel<<<(unsigned)blocks, 256, 0, stream>>>(low, reinterpret_cast<float4*>(out), n, binarize, w, b, ln_w, ln_b);
+  SAM2B_CHECK_LAUNCH("mask_ds1_low");
+  return 0;
+}
+
+// out[b][c][p] += no_obj[c] for the objects whose score says "not there" (sam2_base_official.py:1019-1024)
+__global__ void add_no_obj_embed_kernel(float* __restrict__ x, const float* __restrict__ obj, const float* __restrict__ no_obj, long total) {
+  const long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= total) return;
+  const int b = (int)(i / (64 * 4096)), c = (int)((i / 4096) % 64);
+  if (!(obj[b] > 0.f)) x[i] += no_obj[c];
+}
+int add_no_obj_embed(float* x, const float* obj, const float* no_obj, int n, cudaStream_t stream) {
+  const long total = (long)n * 64 * 4096;
+  ProfRange pr(stream, "add_no_obj_embed", 0, (double)total * 8.0);
+  add_no_obj_embed_kernel<<<(unsigned)((total + 255) / 256), 256, 0, stream>>>(x, obj, no_obj, total);
+  SAM2B_CHECK_LAUNCH("add_no_obj_embed");
+  return 0;
+}
+
 // stage 2: 4 -> 16 channels, NHWC in, thread per output pixel
 __global__ void __launch_bounds__(128) mask_ds2_kernel(const float4* __restrict__ in, float4* __restrict__ out, int n, int H,
                                                        const float* __restrict__ w, const float* __restrict__ b,
@@ -237,19 +330,20 @@ int im2col3x3s2_nhwc_bf16(const bf16* in, bf16* cols, int n, int H, int C, cudaS
 }
 
 // ---- [n,C,HW] fp32 -> [n,HW,C] bf16 (32x32 smem tile transpose) ---------------------------------------------
-__global__ void __launch_bounds__(256) nchw_to_nhwc_bf16_kernel(const float* __restrict__ in, bf16* __restrict__ out, int C, int HW) {
+__global__ void __launch_bounds__(256) nchw_to_nhwc_bf16_kernel(const float* __restrict__ in, bf16* __restrict__ out, int C, int HW,
+                                                                long in_batch_stride) {
   __shared__ float tile[32][33];
   const int b = blockIdx.z;
   const int hw0 = blockIdx.x * 32, c0 = blockIdx.y * 32;
   const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;   // 32 x 8
-  for (int r = ty; r < 32; r += 8) tile[r][tx] = in[((long)b * C + c0 + r) * HW + hw0 + tx];
+  for (int r = ty; r < 32; r += 8) tile[r][tx] = in[b * in_batch_stride + (long)(c0 + r) * HW + hw0 + tx];
   __syncthreads();
   for (int r = ty; r < 32; r += 8) out[((long)b * HW + hw0 + r) * C + c0 + tx] = __float2bfloat16(tile[tx][r]);
 }
-int nchw_to_nhwc_bf16(const float* in, bf16* out, int n, int C, int HW, cudaStream_t stream) {
+int nchw_to_nhwc_bf16(const float* in, bf16* out, int n, int C, int HW, cudaStream_t stream, long in_batch_stride) {
   if (C % 32 || HW % 32) { set_error("nchw_to_nhwc_bf16: bad shape"); return 1; }
   ProfRange pr(stream, "nchw_to_nhwc_bf16", 0, (double)n * C * HW * 6.0);
-  nchw_to_nhwc_bf16_kernel<<<dim3(HW / 32, C / 32, n), 256, 0, stream>>>(in, out, C, HW);
+  nchw_to_nhwc_bf16_kernel<<<dim3(HW / 32, C / 32, n), 256, 0, stream>>>(in, out, C, HW, in_batch_stride < 0 ? (long)C * HW : in_batch_stride);
   SAM2B_CHECK_LAUNCH("nchw_to_nhwc_bf16");
   return 0;
 }

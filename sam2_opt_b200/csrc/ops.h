@@ -170,11 +170,18 @@ int layernorm_gelu_rows(const float* x, const float* gamma, const float* beta, f
 // w: conv weight in the reference layout [Cout,Cin,3,3]; b, ln_w, ln_b: [Cout]
 int mask_ds_stage(int stage, const float* in, float* out, int n, int H_in, const float* w, const float* b,
                   const float* ln_w, const float* ln_b, cudaStream_t stream);
+// stage 1 from the low-resolution logits [n,256,256]: the 1024^2 input sigmoid(bilinear_x4(low)) * 20 - 10 (or its binarised
+// form) is evaluated per tap, never materialised -> [n,512,512,4]
+int mask_ds1_from_low(const float* low, float* out, int n, int binarize, const float* w, const float* b, const float* ln_w,
+                      const float* ln_b, cudaStream_t stream);
+// x [n,64,4096] += no_obj_embed_spatial[c] where object_score_logits[b] <= 0
+int add_no_obj_embed(float* x, const float* obj, const float* no_obj, int n, cudaStream_t stream);
 // im2col for conv3x3 s2 p1 on NHWC fp32 [n,H,H,C] -> bf16 [n*(H/2)^2, 9*C], k = (ky*3+kx)*C + c
 int im2col3x3s2_nhwc(const float* in, bf16* cols, int n, int H, int C, cudaStream_t stream);
 int im2col3x3s2_nhwc_bf16(const bf16* in, bf16* cols, int n, int H, int C, cudaStream_t stream);
 // [n,C,HW] fp32 -> [n,HW,C] bf16
-int nchw_to_nhwc_bf16(const float* in, bf16* out, int n, int C, int HW, cudaStream_t stream);
+// in_batch_stride (elements): < 0 = C * HW (contiguous); 0 = one input image repeated for every output batch entry
+int nchw_to_nhwc_bf16(const float* in, bf16* out, int n, int C, int HW, cudaStream_t stream, long in_batch_stride = -1);
 // CXBlock front half: depthwise 7x7 (pad 3) + LayerNorm2d(eps 1e-6) on NHWC fp32 [n,H,H,256] -> bf16 [n*H*H,256].
 // dw_w: [49][256] (tap-major), dw_b/ln_w/ln_b: [256]
 int dwconv7_ln_nhwc(const float* x, bf16* y, int n, int H, const float* dw_w, const float* dw_b, const float* ln_w,
@@ -201,9 +208,9 @@ int heads_prep_src(const float* pix, long sn, long sc, long sp, const float* den
                    int n, cudaStream_t st);
 int ln256_split(const float* x, const float* g, const float* b, float eps, float* y, bf16* ys, long rows, cudaStream_t st);
 int heads_tokens(const float* coords, const int* labels, int P, int n, const float* gauss, const float* not_a_point,
-                 const float* const pt_emb[4], const float* obj_tok, const float* iou_tok, const float* mask_toks, float* tok,
-                 float* qpe, cudaStream_t st);
-// token -> image attention: kv rows of ld floats (k at column 0, v at column 128), q [n*T][128]; part: n*8*16*T*18 floats; out [n*T][128]
+                 const float* const pt_emb[4], const float* obj_tok, const float* iou_tok, const float* mask_toks,
+                 const float* sparse, int S, float* tok, float* qpe, cudaStream_t st);
+// token -> image attention: kv rows of ld floats (k at column 0, v at column 128), q [n*T][128]; part: n*128*T*8*18 floats; out [n*T][128]
 int t2i_attention(const float* kv, int ld, const float* q, int n, int T, float* part, float* out, cudaStream_t st);
 // image -> token attention: q = columns [q_col, q_col+128) of kvq; tk / tv [n*T][128]; os [n*4096][384] split operand
 int i2t_attention(const float* kvq, int ld, int q_col, const float* tk, const float* tv, int n, int T, bf16* os, cudaStream_t st);

@@ -110,8 +110,10 @@ __global__ void heads_tokens_kernel(const float* __restrict__ coords, const int*
                                     const float* __restrict__ pt_emb0, const float* __restrict__ pt_emb1,
                                     const float* __restrict__ pt_emb2, const float* __restrict__ pt_emb3,
                                     const float* __restrict__ obj_tok, const float* __restrict__ iou_tok,
-                                    const float* __restrict__ mask_toks /*[4][256]*/, float* __restrict__ tok, float* __restrict__ qpe) {
-  const int b = blockIdx.x, c = threadIdx.x, T = 6 + P + 1;
+                                    const float* __restrict__ mask_toks /*[4][256]*/, const float* __restrict__ sparse /*[n][S][256]*/,
+                                    int S, float* __restrict__ tok, float* __restrict__ qpe) {
+  // sparse != nullptr: the caller's own sparse prompt embeddings (MaskDecoder.forward's argument) follow the 6 output tokens
+  const int b = blockIdx.x, c = threadIdx.x, T = sparse ? 6 + S : 6 + P + 1;
   float* t0 = tok + (long)b * T * 256;
   float* q0 = qpe + (long)b * T * 256;
   for (int r = 0; r < T; ++r) {
@@ -119,6 +121,7 @@ __global__ void heads_tokens_kernel(const float* __restrict__ coords, const int*
     if (r == 0) v = obj_tok[c];
     else if (r == 1) v = iou_tok[c];
     else if (r < 6) v = mask_toks[(r - 2) * 256 + c];
+    else if (sparse) v = sparse[((long)b * S + (r - 6)) * 256 + c];
     else {
       const int i = r - 6;
       const int lab = (i < P) ? labels[b * P + i] : -1;
@@ -145,22 +148,23 @@ __global__ void heads_tokens_kernel(const float* __restrict__ coords, const int*
 // A job may be one K slice of a larger problem (split K: the partial sums are added by tok_sum_res_ln_kernel).
 // Tile: 16 rows x 64 columns per CTA, 128-wide K chunks through shared memory.
 // ---------------------------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) tok_linear_kernel(const __grid_constant__ LinJobs jobs) {
+__global__ void __launch_bounds__(128) tok_linear_kernel(const __grid_constant__ LinJobs jobs) {
   const LinJob& J = jobs.j[blockIdx.z];
   const int n0 = blockIdx.x * 64, r0 = blockIdx.y * 16;
   if (n0 >= J.N || r0 >= J.rows) return;
   // 128-wide K chunks; rows of 132 floats keep every float4 16-byte aligned and the LDS.128 of 8 consecutive rows on 32
-  // distinct banks.  The next chunk is fetched into registers while the current one is multiplied (these problems are tiny:
-  // what a launch costs is its chain of dependent memory round trips, not its arithmetic).
+  // distinct banks.  128 threads, each 2 rows x 4 columns (5.3 FMA per shared-memory load).  The next chunk is fetched into
+  // registers while the current one is multiplied (these problems are tiny: what a launch costs is its chain of dependent
+  // memory round trips, not its arithmetic).
   constexpr int KC = 128, LD = KC + 4;
   __shared__ __align__(16) float Xs[16 * LD];
   __shared__ __align__(16) float Ws[64 * LD];
   const int tid = threadIdx.x, tr = tid >> 4, tc = tid & 15;
-  float4 xr[2], wr[8];
+  float4 xr[4], wr[16];
   auto fetch = [&](int k0) {
 #pragma unroll
-    for (int i = 0; i < 2; ++i) {
-      const int idx = tid + 256 * i, r = idx >> 5, k4 = idx & 31;
+    for (int i = 0; i < 4; ++i) {
+      const int idx = tid + 128 * i, r = idx >> 5, k4 = idx & 31;
       float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
       if (r0 + r < J.rows) {
         v = *reinterpret_cast<const float4*>(J.X + (long)(r0 + r) * J.ldx + k0 + 4 * k4);
@@ -172,41 +176,48 @@ __global__ void __launch_bounds__(256) tok_linear_kernel(const __grid_constant__
       xr[i] = v;
     }
 #pragma unroll
-    for (int i = 0; i < 8; ++i) {
-      const int idx = tid + 256 * i, j = idx >> 5, k4 = idx & 31;
+    for (int i = 0; i < 16; ++i) {
+      const int idx = tid + 128 * i, j = idx >> 5, k4 = idx & 31;
       wr[i] = (n0 + j < J.N) ? *reinterpret_cast<const float4*>(J.W + (long)(n0 + j) * J.ldw + k0 + 4 * k4) : make_float4(0.f, 0.f, 0.f, 0.f);
     }
   };
-  float acc[4] = {0.f, 0.f, 0.f, 0.f};
+  float acc[2][4] = {{0.f, 0.f, 0.f, 0.f}, {0.f, 0.f, 0.f, 0.f}};
   fetch(0);
   for (int k0 = 0; k0 < J.K; k0 += KC) {
 #pragma unroll
-    for (int i = 0; i < 2; ++i) { const int idx = tid + 256 * i; *reinterpret_cast<float4*>(Xs + (idx >> 5) * LD + 4 * (idx & 31)) = xr[i]; }
+    for (int i = 0; i < 4; ++i) { const int idx = tid + 128 * i; *reinterpret_cast<float4*>(Xs + (idx >> 5) * LD + 4 * (idx & 31)) = xr[i]; }
 #pragma unroll
-    for (int i = 0; i < 8; ++i) { const int idx = tid + 256 * i; *reinterpret_cast<float4*>(Ws + (idx >> 5) * LD + 4 * (idx & 31)) = wr[i]; }
+    for (int i = 0; i < 16; ++i) { const int idx = tid + 128 * i; *reinterpret_cast<float4*>(Ws + (idx >> 5) * LD + 4 * (idx & 31)) = wr[i]; }
     __syncthreads();
     if (k0 + KC < J.K) fetch(k0 + KC);
-#pragma unroll 8
+#pragma unroll 4
     for (int k4 = 0; k4 < KC / 4; ++k4) {
-      const float4 x = *reinterpret_cast<const float4*>(Xs + tr * LD + 4 * k4);
+      const float4 x0 = *reinterpret_cast<const float4*>(Xs + tr * LD + 4 * k4);
+      const float4 x1 = *reinterpret_cast<const float4*>(Xs + (tr + 8) * LD + 4 * k4);
 #pragma unroll
       for (int jj = 0; jj < 4; ++jj) {
         const float4 w = *reinterpret_cast<const float4*>(Ws + (tc + 16 * jj) * LD + 4 * k4);
-        acc[jj] = fmaf(x.x, w.x, acc[jj]); acc[jj] = fmaf(x.y, w.y, acc[jj]);
-        acc[jj] = fmaf(x.z, w.z, acc[jj]); acc[jj] = fmaf(x.w, w.w, acc[jj]);
+        acc[0][jj] = fmaf(x0.x, w.x, acc[0][jj]); acc[0][jj] = fmaf(x0.y, w.y, acc[0][jj]);
+        acc[0][jj] = fmaf(x0.z, w.z, acc[0][jj]); acc[0][jj] = fmaf(x0.w, w.w, acc[0][jj]);
+        acc[1][jj] = fmaf(x1.x, w.x, acc[1][jj]); acc[1][jj] = fmaf(x1.y, w.y, acc[1][jj]);
+        acc[1][jj] = fmaf(x1.z, w.z, acc[1][jj]); acc[1][jj] = fmaf(x1.w, w.w, acc[1][jj]);
       }
     }
     __syncthreads();
   }
-  if (r0 + tr >= J.rows) return;
 #pragma unroll
-  for (int jj = 0; jj < 4; ++jj) {
-    const int j = n0 + tc + 16 * jj;
-    if (j >= J.N) continue;
-    float v = acc[jj] + (J.b ? J.b[j] : 0.f);
-    if (J.act == 1) v = fmaxf(v, 0.f);
-    else if (J.act == 2) v = 1.0f / (1.0f + expf(-v));
-    J.Y[(long)(r0 + tr) * J.ldy + j] = v;
+  for (int rr = 0; rr < 2; ++rr) {
+    const int r = r0 + tr + 8 * rr;
+    if (r >= J.rows) continue;
+#pragma unroll
+    for (int jj = 0; jj < 4; ++jj) {
+      const int j = n0 + tc + 16 * jj;
+      if (j >= J.N) continue;
+      float v = acc[rr][jj] + (J.b ? J.b[j] : 0.f);
+      if (J.act == 1) v = fmaxf(v, 0.f);
+      else if (J.act == 2) v = 1.0f / (1.0f + expf(-v));
+      J.Y[(long)r * J.ldy + j] = v;
+    }
   }
 }
 
@@ -298,73 +309,97 @@ __global__ void __launch_bounds__(256) tok_self_attn_kernel(const float* __restr
   }
 }
 
-// Token -> image cross-attention (8 heads of 16 over the 4096 image keys): one CTA per (256-key split, head, object), one key
-// per thread held in registers for all T queries.  kv: fp32 rows of `ld` floats with k at column 0 and v at column 128;
-// q [n*T][128].  part [n][8][16][T][18] = (max, sum, 16 un-normalised outputs) per split.
+// Token -> image cross-attention (8 heads of 16 over the 4096 image keys).  One CTA per (tile of 32 keys, object); one thread
+// per (token, head) pair runs its own soft-max over the tile (scores in registers, no cross-thread reduction at all) and
+// leaves (max, sum, 16 un-normalised outputs); t2i_combine_kernel merges the 128 tiles.  kv: fp32 rows of `ld` floats with k
+// at column 0 and v at column 128; q [n*T][128]; part [n][128][T][8][18].
+constexpr int kT2iKeys = 32, kT2iTiles = 4096 / kT2iKeys;
 __global__ void __launch_bounds__(256) t2i_partial_kernel(const float* __restrict__ kv, int ld, const float* __restrict__ q, int T,
                                                           float* __restrict__ part) {
-  __shared__ float qs[32][16];
-  __shared__ float red[8][32][18];
-  const int s = blockIdx.x, h = blockIdx.y, b = blockIdx.z, tid = threadIdx.x, w = tid >> 5, lane = tid & 31;
-  for (int i = tid; i < T * 16; i += 256) qs[i >> 4][i & 15] = q[((long)b * T + (i >> 4)) * 128 + h * 16 + (i & 15)] * 0.25f;
-  const float* row = kv + ((long)b * 4096 + s * 256 + tid) * ld + h * 16;
-  float kr[16], vr[16];
-#pragma unroll
-  for (int i = 0; i < 4; ++i) {
-    const float4 a = *reinterpret_cast<const float4*>(row + 4 * i), c = *reinterpret_cast<const float4*>(row + 128 + 4 * i);
-    kr[4 * i] = a.x; kr[4 * i + 1] = a.y; kr[4 * i + 2] = a.z; kr[4 * i + 3] = a.w;
-    vr[4 * i] = c.x; vr[4 * i + 1] = c.y; vr[4 * i + 2] = c.z; vr[4 * i + 3] = c.w;
+  // [key][head][17]: the 8 heads a warp reads at once fall on 8 different banks
+  __shared__ float ks[kT2iKeys * 8 * 17];
+  __shared__ float vs[kT2iKeys * 8 * 17];
+  const int tile = blockIdx.x, b = blockIdx.y, tid = threadIdx.x;
+  const float* base = kv + ((long)b * 4096 + tile * kT2iKeys) * ld;
+  for (int i = tid; i < kT2iKeys * 64; i += blockDim.x) {          // 64 float4 per key: 32 of k, 32 of v
+    const int j = i >> 6, c4 = i & 63;
+    const float4 a = *reinterpret_cast<const float4*>(base + (long)j * ld + 4 * c4);
+    float* dst = (c4 < 32 ? ks : vs) + (j * 8 + ((c4 & 31) >> 2)) * 17 + 4 * (c4 & 3);
+    dst[0] = a.x; dst[1] = a.y; dst[2] = a.z; dst[3] = a.w;
   }
-  __syncthreads();
-  for (int t = 0; t < T; ++t) {
-    float a = 0.f;
+  const int h = tid & 7, t = tid >> 3;
+  float qr[16];
+  if (t < T) {
 #pragma unroll
-    for (int d = 0; d < 16; ++d) a = fmaf(qs[t][d], kr[d], a);
-    const float m = warp_max(a);
-    const float p = expf(a - m);
-    const float l = warp_sum(p);
-    if (lane == 0) { red[w][t][0] = m; red[w][t][1] = l; }
-#pragma unroll
-    for (int d = 0; d < 16; ++d) {
-      const float o = warp_sum(p * vr[d]);
-      if (lane == 0) red[w][t][2 + d] = o;
+    for (int i = 0; i < 4; ++i) {
+      const float4 a = *reinterpret_cast<const float4*>(q + ((long)b * T + t) * 128 + h * 16 + 4 * i);
+      qr[4 * i] = a.x * 0.25f; qr[4 * i + 1] = a.y * 0.25f; qr[4 * i + 2] = a.z * 0.25f; qr[4 * i + 3] = a.w * 0.25f;
     }
   }
   __syncthreads();
-  float* dst = part + (((long)(b * 8 + h) * 16 + s) * T) * 18;
-  for (int i = tid; i < T * 16; i += 256) {
-    const int t = i >> 4, d = i & 15;
-    float M = -INFINITY;
+  if (t >= T) return;
+  float sc[kT2iKeys], m = -INFINITY;
 #pragma unroll
-    for (int ww = 0; ww < 8; ++ww) M = fmaxf(M, red[ww][t][0]);
-    float L = 0.f, O = 0.f;
+  for (int j = 0; j < kT2iKeys; ++j) {
+    const float* kk = ks + (j * 8 + h) * 17;
+    float a0 = 0.f, a1 = 0.f;
 #pragma unroll
-    for (int ww = 0; ww < 8; ++ww) {
-      const float e = expf(red[ww][t][0] - M);
-      L = fmaf(red[ww][t][1], e, L);
-      O = fmaf(red[ww][t][2 + d], e, O);
-    }
-    dst[t * 18 + 2 + d] = O;
-    if (d == 0) { dst[t * 18] = M; dst[t * 18 + 1] = L; }
+    for (int d = 0; d < 16; d += 2) { a0 = fmaf(qr[d], kk[d], a0); a1 = fmaf(qr[d + 1], kk[d + 1], a1); }
+    sc[j] = a0 + a1;
+    m = fmaxf(m, sc[j]);
   }
+  float l = 0.f, acc[16];
+#pragma unroll
+  for (int d = 0; d < 16; ++d) acc[d] = 0.f;
+#pragma unroll
+  for (int j = 0; j < kT2iKeys; ++j) {
+    const float* vv = vs + (j * 8 + h) * 17;
+    const float e = expf(sc[j] - m);
+    l += e;
+#pragma unroll
+    for (int d = 0; d < 16; ++d) acc[d] = fmaf(e, vv[d], acc[d]);
+  }
+  float* dst = part + ((((long)b * kT2iTiles + tile) * T + t) * 8 + h) * 18;
+  dst[0] = m; dst[1] = l;
+#pragma unroll
+  for (int d = 0; d < 16; ++d) dst[2 + d] = acc[d];
 }
 
-// merge the 16 key splits: out [n*T][128], column = head * 16 + d
-__global__ void t2i_combine_kernel(const float* __restrict__ part, int T, float* __restrict__ out, int total) {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= total) return;
-  const int d = i & 15, h = (i >> 4) & 7, bt = i >> 7, b = bt / T, t = bt % T;
-  const float* p = part + (((long)(b * 8 + h) * 16) * T + t) * 18;
-  const long ss = (long)T * 18;
-  float M = -INFINITY;
-  for (int s = 0; s < 16; ++s) M = fmaxf(M, p[s * ss]);
-  float L = 0.f, O = 0.f;
-  for (int s = 0; s < 16; ++s) {
-    const float e = expf(p[s * ss] - M);
-    L = fmaf(p[s * ss + 1], e, L);
-    O = fmaf(p[s * ss + 2 + d], e, O);
+// merge the key tiles: out [n*T][128], column = head * 16 + d.  One warp per (object, token, head): every lane folds 4 of the
+// 128 tiles, then the lanes merge their (max, sum, outputs) pairwise.
+__global__ void __launch_bounds__(256) t2i_combine_kernel(const float* __restrict__ part, int T, float* __restrict__ out, int total_warps) {
+  const int wid = blockIdx.x * 8 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+  if (wid >= total_warps) return;
+  const int h = wid & 7, bt = wid >> 3, b = bt / T, t = bt % T;
+  const float* p = part + ((((long)b * kT2iTiles) * T + t) * 8 + h) * 18;
+  const long ss = (long)T * 8 * 18;
+  float M = -INFINITY, L = 0.f, O[16];
+#pragma unroll
+  for (int d = 0; d < 16; ++d) O[d] = 0.f;
+#pragma unroll
+  for (int i = 0; i < kT2iTiles / 32; ++i) {
+    const float* q = p + (lane + 32 * i) * ss;
+    const float m = q[0], Mn = fmaxf(M, m), e0 = expf(M - Mn), e1 = expf(m - Mn);
+    L = L * e0 + q[1] * e1;
+#pragma unroll
+    for (int d = 0; d < 16; ++d) O[d] = O[d] * e0 + q[2 + d] * e1;
+    M = Mn;
   }
-  out[i] = O / L;
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    const float m = __shfl_xor_sync(0xffffffffu, M, o), l = __shfl_xor_sync(0xffffffffu, L, o);
+    const float Mn = fmaxf(M, m), e0 = expf(M - Mn), e1 = expf(m - Mn);
+    L = L * e0 + l * e1;
+#pragma unroll
+    for (int d = 0; d < 16; ++d) O[d] = O[d] * e0 + __shfl_xor_sync(0xffffffffu, O[d], o) * e1;
+    M = Mn;
+  }
+  if (lane < 16) {
+    float v = O[0];
+#pragma unroll
+    for (int d = 1; d < 16; ++d) v = (lane == d) ? O[d] : v;
+    out[(long)bt * 128 + h * 16 + lane] = v / L;
+  }
 }
 
 // Image -> token cross-attention: every pixel attends to the T tokens (8 heads of 16).  One thread per (pixel, head);
@@ -594,11 +629,11 @@ int ln256_split(const float* x, const float* g, const float* b, float eps, float
 }
 
 int heads_tokens(const float* coords, const int* labels, int P, int n, const float* gauss, const float* not_a_point,
-                 const float* const pt_emb[4], const float* obj_tok, const float* iou_tok, const float* mask_toks, float* tok,
-                 float* qpe, cudaStream_t st) {
+                 const float* const pt_emb[4], const float* obj_tok, const float* iou_tok, const float* mask_toks,
+                 const float* sparse, int S, float* tok, float* qpe, cudaStream_t st) {
   ProfRange pr(st, "heads_tokens", 0, 0);
   heads_tokens_kernel<<<n, 256, 0, st>>>(coords, labels, P, gauss, not_a_point, pt_emb[0], pt_emb[1], pt_emb[2], pt_emb[3], obj_tok,
-                                         iou_tok, mask_toks, tok, qpe);
+                                         iou_tok, mask_toks, sparse, S, tok, qpe);
   SAM2B_CHECK_LAUNCH("heads_tokens");
   return 0;
 }
@@ -618,7 +653,7 @@ int tok_linear(const LinJobs& jobs, int njobs, cudaStream_t st) {
     flops += 2.0 * j.rows * j.N * j.K;
   }
   ProfRange pr(st, "heads_tok_linear", flops, 0);
-  tok_linear_kernel<<<dim3((max_n + 63) / 64, (max_r + 15) / 16, njobs), 256, 0, st>>>(jobs);
+  tok_linear_kernel<<<dim3((max_n + 63) / 64, (max_r + 15) / 16, njobs), 128, 0, st>>>(jobs);
   SAM2B_CHECK_LAUNCH("tok_linear");
   return 0;
 }
@@ -641,12 +676,12 @@ int tok_self_attn(const float* q, const float* k, const float* v, int n, int T, 
 int t2i_attention(const float* kv, int ld, const float* q, int n, int T, float* part, float* out, cudaStream_t st) {
   {
     ProfRange pr(st, "heads_t2i_partial", 4.0 * n * T * 4096 * 128, (double)n * 4096 * 256 * 4);
-    t2i_partial_kernel<<<dim3(16, 8, n), 256, 0, st>>>(kv, ld, q, T, part);
+    t2i_partial_kernel<<<dim3(kT2iTiles, n), (8 * T + 31) / 32 * 32, 0, st>>>(kv, ld, q, T, part);
     SAM2B_CHECK_LAUNCH("t2i_partial");
   }
   ProfRange pr(st, "heads_t2i_combine", 0, 0);
-  const int total = n * T * 128;
-  t2i_combine_kernel<<<(total + 255) / 256, 256, 0, st>>>(part, T, out, total);
+  const int total_warps = n * T * 8;
+  t2i_combine_kernel<<<(total_warps + 7) / 8, 256, 0, st>>>(part, T, out, total_warps);
   SAM2B_CHECK_LAUNCH("t2i_combine");
   return 0;
 }

@@ -214,15 +214,35 @@ class Engine:
                        "memory_encode")
         return x, self.position_encoding(64, 64, n)
 
+    def memory_encode_low_res(self, pix_feat, low_res_masks, object_score_logits=None, binarize=False):
+        """E4 straight from the SAM heads' low-resolution logits [n,1,256,256] (ref: _encode_new_memory,
+        sam2_base_official.py:978-1026): sigmoid(bilinear x4) * 20 - 10 (binarize: the (mask > 0) form of prompted frames) is
+        evaluated inside the down-sampler's first convolution; with object_score_logits [n,1] the no-object embedding is added
+        too.  pix_feat [1 or n,256,64,64].  -> (maskmem_features fp32 [n,64,64,64], maskmem_pos_enc)"""
+        pix_feat, low = _f32c(pix_feat, "pix_feat"), _f32c(low_res_masks, "low_res_masks")
+        n = low.shape[0]
+        if tuple(low.shape[1:]) != (1, 256, 256) or pix_feat.shape[0] not in (1, n) or tuple(pix_feat.shape[1:]) != (256, 64, 64):
+            raise ValueError(f"memory_encode_low_res: pix_feat {tuple(pix_feat.shape)} / low_res_masks {tuple(low.shape)}")
+        obj = None if object_score_logits is None else _f32c(object_score_logits, "object_score_logits").reshape(n)
+        x = torch.empty((n, 64, 64, 64), device=self.device, dtype=torch.float32)
+        with self._lock:
+            _lib.check(self.lib.sam2b_memory_encode_low_res(self._h, _ptr(pix_feat), 0 if pix_feat.shape[0] == 1 and n > 1 else 256 * 4096,
+                                                            _ptr(low), int(bool(binarize)), _ptr(obj), n, _ptr(x), self._stream()),
+                       "memory_encode_low_res")
+        return x, self.position_encoding(64, 64, n)
+
     # -- SAM heads (SURVEY section 8 f-1) --------------------------------------------------------------------------
     def sam_heads(self, backbone_features, high_res_features, point_coords=None, point_labels=None, dense_embedding=None,
-                  multimask_output=False, decoder_only=False, high_res=True, high_res_multimasks=False):
+                  multimask_output=False, decoder_only=False, high_res=True, high_res_multimasks=False, sparse_embeddings=None,
+                  mask_tokens=False):
         """Prompt encoder (points) + mask decoder + object-pointer head for n prompts / objects in one library call
         (ref: sam2_base_official.py:338-494).  backbone_features [n,256,64,64] may be any view whose channel or pixel
         dimension is contiguous (the permuted E3 output, an expanded single image ...); high_res_features = [fpn0, fpn1]
         with batch 1 (shared) or n.  point_coords [n,P,2] / point_labels [n,P] or None (a tracked frame).
+        sparse_embeddings [n,S,256]: the sparse prompt embeddings themselves instead of points (no padding point is added).
         -> (low_res_multimasks [n,M,256,256], high_res_multimasks or None, ious [n,M], low_res_masks [n,1,256,256],
-            high_res_masks [n,1,1024,1024] or None, obj_ptr [n,256], object_score_logits [n,1])"""
+            high_res_masks [n,1,1024,1024] or None, obj_ptr [n,256], object_score_logits [n,1])
+           + mask tokens [n,4,256] as an eighth element with mask_tokens=True"""
         bf = backbone_features
         if not bf.is_cuda or bf.dtype != torch.float32:
             raise RuntimeError("sam_heads: expected a CUDA fp32 tensor (sam2_opt_b200 has no CPU path)")
@@ -247,6 +267,14 @@ class Engine:
             point_coords = _f32c(point_coords, "point_coords").reshape(n, -1, 2)
             P = point_coords.shape[1]
             point_labels = point_labels.to(torch.int32).contiguous().reshape(n, P)
+        S = 0
+        if sparse_embeddings is not None:
+            sparse_embeddings = _f32c(sparse_embeddings, "sparse_embeddings")
+            if sparse_embeddings.dim() != 3 or sparse_embeddings.shape[0] != n or sparse_embeddings.shape[2] != 256:
+                raise ValueError(f"sam_heads: sparse_embeddings {tuple(sparse_embeddings.shape)} != [{n},S,256]")
+            S, P = sparse_embeddings.shape[1], 0
+            if S == 0:          # an empty tensor has no usable address: the library still needs "given, with 0 rows"
+                sparse_embeddings = torch.zeros((n, 1, 256), device=self.device)
         if dense_embedding is not None:
             dense_embedding = _f32c(dense_embedding, "dense_embedding")
             if tuple(dense_embedding.shape) != (n, 256, 64, 64):
@@ -256,13 +284,15 @@ class Engine:
         low_multi, ious, low, ptr, obj = new(n, M, 256, 256), new(n, M), new(n, 1, 256, 256), new(n, 256), new(n, 1)
         high = new(n, 1, 1024, 1024) if high_res else None
         high_multi = new(n, M, 1024, 1024) if high_res_multimasks else None
+        toks = new(n, 4, 256) if mask_tokens else None
         with self._lock:
             _lib.check(self.lib.sam2b_sam_heads(
                 self._h, _ptr(bf), sn, sc, sx, _ptr(hr[0][0]), hr[0][1], _ptr(hr[1][0]), hr[1][1],
-                _ptr(point_coords if P else None), _ptr(point_labels if P else None), P, _ptr(dense_embedding), n,
-                int(bool(multimask_output)), int(bool(decoder_only)), _ptr(low_multi), _ptr(high_multi), _ptr(ious), _ptr(low),
-                _ptr(high), _ptr(ptr), _ptr(obj), self._stream()), "sam_heads")
-        return low_multi, high_multi, ious, low, high, ptr, obj
+                _ptr(point_coords if P else None), _ptr(point_labels if P else None), P, _ptr(sparse_embeddings), S,
+                _ptr(dense_embedding), n, int(bool(multimask_output)), int(bool(decoder_only)), _ptr(low_multi), _ptr(high_multi),
+                _ptr(ious), _ptr(low), _ptr(high), _ptr(ptr), _ptr(obj), _ptr(toks), self._stream()), "sam_heads")
+        out = (low_multi, high_multi, ious, low, high, ptr, obj)
+        return out + (toks,) if mask_tokens else out
 
     # -- CUDA graphs over engine calls -----------------------------------------------------------------------------
     def workspace_generation(self) -> int:

@@ -145,13 +145,16 @@ class SAM2ImagePredictor(_Base):
                 mask_t = mask_t[None]
         hr = [f[img_idx:img_idx + 1] for f in self._features["high_res_feats"]]
         emb = self._features["image_embed"][img_idx:img_idx + 1]
-        if self.native_heads and coords is not None:
+        if self.native_heads:
             # prompt encoder (points) + mask decoder inside libsam2b (sam2b_sam_heads, decoder-only semantics); a mask prompt
-            # enters as the dense embedding of the reference's mask_downscaling convolutions
-            nb = coords.shape[0]
+            # enters as the dense embedding of the reference's mask_downscaling convolutions; without any point the decoder sees
+            # no sparse token at all (prompt_encoder.py:197-211), which the library takes as an empty set of sparse embeddings
+            nb = 1 if coords is None else coords.shape[0]
             dense = None if mask_t is None else H.prompt_encoder(self.w, None, None, mask_t)[1].expand(nb, -1, -1, -1)
+            sparse = torch.empty((1, 0, H.D_MODEL), device=self.device) if coords is None else None
             low, _, iou, _, _, _, _ = self.engine.sam_heads(emb.expand(nb, -1, -1, -1), hr, coords, labels, dense,
-                                                            multimask_output=multimask_output, decoder_only=True, high_res=False)
+                                                            multimask_output=multimask_output, decoder_only=True, high_res=False,
+                                                            sparse_embeddings=sparse)
         else:
             sparse, dense = H.prompt_encoder(self.w, coords, labels, mask_t)
             batched = coords is not None and coords.shape[0] > 1
@@ -338,11 +341,8 @@ class _GraphedTrack:
         curr = self.f2.flatten(2).permute(2, 0, 1).expand(-1, n, -1)
         pix = vp.engine.memory_attention(curr, self.mem, self.pos2, self.pos, ptr_tok, ppos)
         pix = pix.permute(1, 2, 0).reshape(n, H.D_MODEL, 64, 64)
-        _, _, _, low, high, ptr, obj = vp.engine.sam_heads(pix, self.hr, multimask_output=True)
-        x, mp = vp.engine.memory_encode(self.f2.expand(n, -1, -1, -1), torch.sigmoid(high) * 20.0 - 10.0)
-        is_obj = (obj > 0).float()
-        x = x + (1 - is_obj[..., None, None]) * vp.w["no_obj_embed_spatial"][..., None, None].expand(*x.shape)
-        mf = x.to(torch.bfloat16)
+        _, _, _, low, _, ptr, obj = vp.engine.sam_heads(pix, self.hr, multimask_output=True, high_res=False)
+        mf, mp = vp._encode_memory_low(self.f2, low, obj, False)
         # the new frame replaces the oldest one in both rings (after everything that read them)
         self.mem.index_copy_(0, self.ctl[23:24], mf.float().flatten(2).permute(2, 0, 1)[None])
         self.ptrs.index_copy_(0, self.ctl[24:25], ptr[None])
@@ -478,6 +478,13 @@ class SAM2VideoPredictor(_Base):
         x, pos = self._ex["memory_encoder"].Inference([f2.expand(n, -1, -1, -1), m * 20.0 - 10.0], output_type="torch")
         is_obj = (obj_logits > 0).float()
         x = x + (1 - is_obj[..., None, None]) * self.w["no_obj_embed_spatial"][..., None, None].expand(*x.shape)
+        return x.to(torch.bfloat16), pos
+
+    def _encode_memory_low(self, f2, low, obj_logits, from_points):
+        """The same from the low-resolution logits (sam2b_memory_encode_low_res): the x4 bilinear up-sampling, the sigmoid /
+        binarisation, the * 20 - 10 scaling and the no-object embedding happen inside the library; the 1024^2 mask is never
+        written.  f2 [1,256,64,64] is shared by the n objects."""
+        x, pos = self.engine.memory_encode_low_res(f2, low, obj_logits, binarize=from_points)
         return x.to(torch.bfloat16), pos
 
     def _video_res(self, st, low):
@@ -622,9 +629,12 @@ class SAM2VideoPredictor(_Base):
                 continue
             f2 = self._features(st, t)[0]
             low = torch.cat([per_obj[o]["pred_masks"] for o in todo], 0)
-            high = F.interpolate(low, size=(1024, 1024), mode="bilinear", align_corners=False)
             obj = torch.cat([per_obj[o]["object_score_logits"] for o in todo], 0)
-            mf, mp = self._encode_memory(f2, high, obj, from_points=True)
+            if self.native_heads:
+                mf, mp = self._encode_memory_low(f2, low, obj, True)
+            else:
+                high = F.interpolate(low, size=(1024, 1024), mode="bilinear", align_corners=False)
+                mf, mp = self._encode_memory(f2, high, obj, from_points=True)
             for i, o in enumerate(todo):
                 per_obj[o]["maskmem_features"], per_obj[o]["maskmem_pos"] = mf[i:i + 1], mp[i:i + 1]
             st["cond_b"].pop(t, None)
@@ -634,8 +644,11 @@ class SAM2VideoPredictor(_Base):
             out = st["non_cond"].get(o, {}).get(t)
             if out is None or out["maskmem_features"] is not None:
                 continue
-            high = F.interpolate(out["pred_masks"], size=(1024, 1024), mode="bilinear", align_corners=False)
-            mf, mp = self._encode_memory(self._features(st, t)[0], high, out["object_score_logits"], from_points=True)
+            if self.native_heads:
+                mf, mp = self._encode_memory_low(self._features(st, t)[0], out["pred_masks"], out["object_score_logits"], True)
+            else:
+                high = F.interpolate(out["pred_masks"], size=(1024, 1024), mode="bilinear", align_corners=False)
+                mf, mp = self._encode_memory(self._features(st, t)[0], high, out["object_score_logits"], from_points=True)
             out["maskmem_features"], out["maskmem_pos"] = mf, mp
         st["pending_non_cond"].clear()
 
@@ -757,7 +770,7 @@ class SAM2VideoPredictor(_Base):
         pix = self._memory_conditioned(st, t, groups, f2, pos2)
         if self.native_heads:
             # ONE library call: ~50 launches of libsam2b's own kernels (split-bf16 tcgen05 GEMMs on the image side, fp32 token side)
-            _, _, _, low, high, ptr, obj = self.engine.sam_heads(pix, hr, multimask_output=True)
+            _, _, _, low, high, ptr, obj = self.engine.sam_heads(pix, hr, multimask_output=True, high_res=False)
         elif self.graph_heads:
             gk = (n, threading.get_ident())    # static buffers are per graph: one graph per host thread
             if gk not in self._heads_graphs:
@@ -766,7 +779,7 @@ class SAM2VideoPredictor(_Base):
         else:
             hr_n = [h.expand(n, -1, -1, -1) for h in hr]
             _, _, _, low, high, ptr, obj = H.forward_sam_heads(self.w, pix, high_res_features=hr_n, multimask_output=True, pe=self._dense_pe)
-        mf, mp = self._encode_memory(f2, high, obj, from_points=False)
+        mf, mp = self._encode_memory_low(f2, low, obj, False) if self.native_heads else self._encode_memory(f2, high, obj, from_points=False)
         low = self._fill_holes(low)            # after the memory is encoded from the unfilled masks, as in the reference
         results, o0 = {}, 0
         for _, _, g_objs in groups:

@@ -58,6 +58,36 @@ def _native_forward_sam_heads(model, engine):
     return forward
 
 
+def _native_mask_decoder_forward(model, engine):
+    """MaskDecoder.forward (ref: modeling/sam/mask_decoder.py:116-175) on the engine, for the callers that drive the decoder
+    themselves: SAM2ImagePredictor._predict (sam2_image_predictor.py:548-570) and, through it, SAM2AutomaticMaskGenerator with
+    its batches of 64 one-click prompts on one image.  `image_pe` is not read: every caller in the reference passes the prompt
+    encoder's own dense positional encoding, which the library carries folded into its projection tables."""
+    md = model.sam_mask_decoder
+    no_mask = model.sam_prompt_encoder.no_mask_embed.weight
+
+    def forward(image_embeddings, image_pe, sparse_prompt_embeddings, dense_prompt_embeddings, multimask_output, repeat_image,
+                high_res_features=None):
+        n = sparse_prompt_embeddings.shape[0]
+        if high_res_features is None or sparse_prompt_embeddings.shape[1] > 26 or (not repeat_image and image_embeddings.shape[0] != n):
+            return type(md).forward(md, image_embeddings, image_pe, sparse_prompt_embeddings, dense_prompt_embeddings,
+                                    multimask_output, repeat_image, high_res_features)
+        dev = image_embeddings.device
+        dense = dense_prompt_embeddings
+        if dense.data_ptr() == no_mask.data_ptr() and dense.stride(2) == 0 and dense.stride(3) == 0:
+            dense = None                                   # the expanded no_mask_embed: the library adds it itself
+        else:
+            dense = dense.expand(n, -1, -1, -1)
+        emb = image_embeddings.float().expand(n, -1, -1, -1)
+        low, _, iou, _, _, _, obj, toks = engine.sam_heads(emb, [f.float() for f in high_res_features], None, None, dense,
+                                                           multimask_output=multimask_output, decoder_only=True, high_res=False,
+                                                           sparse_embeddings=sparse_prompt_embeddings.float(), mask_tokens=True)
+        sam_tokens = toks[:, 1:] if (multimask_output and md.use_multimask_token_for_obj_ptr) else toks[:, 0:1]
+        return low.to(dev), iou.to(dev), sam_tokens.to(dev), obj.to(dev)
+
+    return forward
+
+
 def _heads_config_supported(model) -> bool:
     """The library implements the SAM2.1 head configuration (configs/sam2.1/sam2.1_hiera_*.yaml:98-117): high-resolution
     features, object scores from an MLP, fixed (hard) no-object pointer, the multimask token for the pointer, dynamic
@@ -88,6 +118,8 @@ def speedup(predictor, backend="b200", engine=None, engine_factory=None, warmup=
             model.memory_attention.set_runtime_backend(backend="torch")
             model.memory_encoder.set_runtime_backend(backend="torch")
             model.__dict__.pop("_forward_sam_heads", None)          # back to the class's own torch heads
+        if getattr(model, "sam_mask_decoder", None) is not None:
+            model.sam_mask_decoder.__dict__.pop("forward", None)
         return None
     if b not in B200_NAMES:
         raise Exception(f"unsupported runtime backend={backend}")
@@ -100,6 +132,8 @@ def speedup(predictor, backend="b200", engine=None, engine_factory=None, warmup=
         ex = B200Executor(engine, "set_image_e2e")
         predictor.backend_contexts.append(ex)
         predictor.set_image_e2e = lambda img, _ex=ex: tuple(o.to(img.device) for o in _ex.Inference([img], output_type="torch"))
+        if heads and hasattr(engine, "sam_heads") and _heads_config_supported(model):
+            model.sam_mask_decoder.forward = _native_mask_decoder_forward(model, engine)
         if warmup:
             ex.warmup([torch.randn(1, 3, 1024, 1024)])
         return engine
@@ -126,6 +160,7 @@ def speedup(predictor, backend="b200", engine=None, engine_factory=None, warmup=
     me.inference_memory = inference_memory
     if heads and hasattr(engine, "sam_heads") and _heads_config_supported(model):
         model._forward_sam_heads = _native_forward_sam_heads(model, engine)
+        model.sam_mask_decoder.forward = _native_mask_decoder_forward(model, engine)
     if warmup:
         ex_img.warmup([torch.randn(1, 3, 1024, 1024)])
         for L in (1, 7):

@@ -35,9 +35,8 @@ def run(n_obj, prof=False):
           f"{1 / steady:.2f} frames/s = {n_obj / steady:.1f} object-frames/s", flush=True)
 
 
-run(1)
-run(1)
-run(16)
+for _n in [int(x) for x in os.environ.get('VP_OBJS', '1,1,16').split(',')]:
+    run(_n)
 if "--prof" in sys.argv:
     from torch.profiler import profile, ProfilerActivity
     with profile(activities=[ProfilerActivity.CPU, ProfilerActivity.CUDA]) as p:

@@ -141,3 +141,29 @@ def test_matches_torch_heads_and_is_deterministic(engine, weights):
     finally:
         torch.backends.cuda.matmul.allow_tf32, torch.backends.cudnn.allow_tf32 = prev
     _check(a, (low.cpu(), None, ious.cpu(), low_best.cpu(), high_best.cpu(), ptr.cpu(), obj.cpu()), NAMES)
+
+
+def test_sparse_embeddings_given_and_mask_tokens_out(engine, weights):
+    """MaskDecoder.forward semantics: the caller's own sparse prompt embeddings (here the oracle prompt encoder's, box + point)
+    instead of points, and no sparse token at all with a mask prompt (SAM2ImagePredictor.predict with mask_input only)."""
+    from oracle import sam2_oracle as O
+    pix, s0, s1, g = _inputs(1, 6)
+    n = 3
+    coords = torch.rand(n, 3, 2, generator=g) * 1024
+    labels = torch.tensor([[2, 3, 1]] * n, dtype=torch.int32)
+    with torch.no_grad():
+        sparse, dense = O.prompt_encoder(weights, coords, labels, None)
+        masks, iou, sam_tok, obj = O.mask_decoder(weights, pix, sparse, dense, True, [s0, s1], repeat_image=True)
+    got = engine.sam_heads(pix.cuda().expand(n, -1, -1, -1), [s0.cuda(), s1.cuda()], sparse_embeddings=sparse.cuda(), multimask_output=True,
+                           decoder_only=True, high_res=False, mask_tokens=True)
+    assert rel_l2(got[0], masks) <= TOL and (got[2].cpu() - iou).abs().max().item() <= TOL
+    assert rel_l2(got[7][:, 1:], sam_tok) <= TOL and (got[6].cpu() - obj).abs().max().item() <= TOL
+    mask_in = 4.0 * torch.randn(1, 1, 256, 256, generator=g)
+    with torch.no_grad():
+        sparse0, dense0 = O.prompt_encoder(weights, None, None, mask_in)
+        masks0, iou0, tok0, obj0 = O.mask_decoder(weights, pix, sparse0, dense0, False, [s0, s1])
+    assert sparse0.shape[1] == 0
+    got0 = engine.sam_heads(pix.cuda(), [s0.cuda(), s1.cuda()], dense_embedding=dense0.contiguous().cuda(), sparse_embeddings=sparse0.cuda(),
+                            multimask_output=False, decoder_only=True, high_res=False, mask_tokens=True)
+    assert rel_l2(got0[0], masks0) <= TOL and (got0[2].cpu() - iou0).abs().max().item() <= TOL
+    assert rel_l2(got0[7][:, 0:1], tok0) <= TOL
