@@ -10,6 +10,7 @@
 // token side (<= 32 tokens per object) and every soft-max, LayerNorm and GELU is plain fp32.
 #include <math.h>
 
+#include "common.cuh"
 #include "ops.h"
 
 namespace sam2b {
@@ -183,6 +184,9 @@ __global__ void __launch_bounds__(128) tok_linear_kernel(const __grid_constant__
   };
   float acc[2][4] = {{0.f, 0.f, 0.f, 0.f}, {0.f, 0.f, 0.f, 0.f}};
   fetch(0);
+  float bias[4];                  // fetched with the first chunk: a load at the end would be one more exposed memory round trip
+#pragma unroll
+  for (int jj = 0; jj < 4; ++jj) bias[jj] = (J.b && n0 + tc + 16 * jj < J.N) ? J.b[n0 + tc + 16 * jj] : 0.f;
   for (int k0 = 0; k0 < J.K; k0 += KC) {
 #pragma unroll
     for (int i = 0; i < 4; ++i) { const int idx = tid + 128 * i; *reinterpret_cast<float4*>(Xs + (idx >> 5) * LD + 4 * (idx & 31)) = xr[i]; }
@@ -213,7 +217,7 @@ __global__ void __launch_bounds__(128) tok_linear_kernel(const __grid_constant__
     for (int jj = 0; jj < 4; ++jj) {
       const int j = n0 + tc + 16 * jj;
       if (j >= J.N) continue;
-      float v = acc[rr][jj] + (J.b ? J.b[j] : 0.f);
+      float v = acc[rr][jj] + bias[jj];
       if (J.act == 1) v = fmaxf(v, 0.f);
       else if (J.act == 2) v = 1.0f / (1.0f + expf(-v));
       J.Y[(long)r * J.ldy + j] = v;
@@ -465,7 +469,8 @@ __global__ void __launch_bounds__(256) i2t_attn_kernel(const float* __restrict__
 // Up-scaling tail (mask_decoder.py:283-300): u1 [n*4096][256 = (dy,dx,c)] is ConvTranspose2d(256 -> 64, k2 s2) of the
 // final keys (a GEMM); per 128x128 position: + feat_s1, LayerNorm2d(64), GELU, ConvTranspose2d(64 -> 32, k2 s2), + feat_s0, GELU,
 // then the 4 hyper-network dot products -> masks [n][4][256][256].  The 32-channel 256x256 map never exists.
-// One thread per (object, 128x128 position); w2 [64][4 = (ey,ex)][32] and the biases live in shared memory.
+// One CTA per 256 positions of the 128x128 grid: first a thread per position (up to the GELU), then a thread per (tap, 4
+// positions) for the second transposed convolution; w2 [64][4 = (ey,ex)][32] and the biases live in shared memory.
 // stab [n][2]: number of pixels of mask 0 above +delta / above -delta (mask_decoder.py:320-335), only if stab != nullptr.
 // ---------------------------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256) heads_upscale_kernel(const float* __restrict__ u1, const float* __restrict__ b1 /*[64]*/,
@@ -478,6 +483,7 @@ __global__ void __launch_bounds__(256) heads_upscale_kernel(const float* __restr
   float* w2s = smem;              // [64][4][32]
   float* hs = w2s + 64 * 128;     // [4][32]
   float* b2s = hs + 128;          // [32]
+  float* xs = b2s + 32;           // [64][256]: the 64-channel vector of each of the CTA's 256 positions after LayerNorm2d + GELU
   const int b = blockIdx.y, tid = threadIdx.x;
   for (int i = tid; i < 64 * 128; i += 256) w2s[i] = w2[i];
   if (tid < 128) hs[tid] = hyper[(long)b * 128 + tid];
@@ -505,33 +511,49 @@ __global__ void __launch_bounds__(256) heads_upscale_kernel(const float* __restr
 #pragma unroll
   for (int c = 0; c < 64; ++c) { x[c] -= mean; var = fmaf(x[c], x[c], var); }
   const float rstd = 1.0f / sqrtf(var * (1.0f / 64.0f) + 1e-6f);
+  // GELU: gelu_fast (common.cuh) = x * Phi(x) with Phi(-|x|) as 2^poly6, max |error| 2e-7 -- fp32-grade at a third of erff's cost
 #pragma unroll
-  for (int c = 0; c < 64; ++c) x[c] = gelu_exact(ln_g[c] * (x[c] * rstd) + ln_b[c]);
+  for (int c = 0; c < 64; ++c) xs[c * 256 + tid] = gelu_fast(ln_g[c] * (x[c] * rstd) + ln_b[c]);
+  __syncthreads();
+  // Second transposed convolution: every thread takes ONE of the four output taps q (uniform per warp) for FOUR positions, so
+  // that a weight read from shared memory (a broadcast LDS.128 costs four wavefronts) feeds 16 FMAs instead of 4: with one
+  // position per thread the kernel sat at the shared-memory pipe (ncu: 66 % l1tex, short-scoreboard stalls), 0.26 ms at 16 objects.
   int cnt_hi = 0, cnt_lo = 0;
-  for (int q = 0; q < 4; ++q) {
-    float acc[32];
+  const int q = tid >> 6, pg = tid & 63;
+  uint64_t acc2[4][16];
 #pragma unroll
-    for (int o = 0; o < 32; ++o) acc[o] = b2s[o];
+  for (int i = 0; i < 4; ++i)
 #pragma unroll
-    for (int c = 0; c < 64; ++c) {
-      const float4* wr = reinterpret_cast<const float4*>(w2s + (c * 4 + q) * 32);
+    for (int o = 0; o < 16; ++o) acc2[i][o] = f2_pack(b2s[2 * o], b2s[2 * o + 1]);
+#pragma unroll 4
+  for (int c = 0; c < 64; ++c) {
+    uint64_t xx[4];
 #pragma unroll
-      for (int o4 = 0; o4 < 8; ++o4) {
-        const float4 wv = wr[o4];
-        acc[4 * o4 + 0] = fmaf(x[c], wv.x, acc[4 * o4 + 0]);
-        acc[4 * o4 + 1] = fmaf(x[c], wv.y, acc[4 * o4 + 1]);
-        acc[4 * o4 + 2] = fmaf(x[c], wv.z, acc[4 * o4 + 2]);
-        acc[4 * o4 + 3] = fmaf(x[c], wv.w, acc[4 * o4 + 3]);
+    for (int i = 0; i < 4; ++i) { const float xc = xs[c * 256 + pg + 64 * i]; xx[i] = f2_pack(xc, xc); }
+    const ulonglong2* wr = reinterpret_cast<const ulonglong2*>(w2s + (c * 4 + q) * 32);
+#pragma unroll
+    for (int o4 = 0; o4 < 8; ++o4) {
+      const ulonglong2 wv = wr[o4];
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        acc2[i][2 * o4] = f2_fma(xx[i], wv.x, acc2[i][2 * o4]);
+        acc2[i][2 * o4 + 1] = f2_fma(xx[i], wv.y, acc2[i][2 * o4 + 1]);
       }
     }
-    const int y2 = 2 * y1 + (q >> 1), x2 = 2 * x1 + (q & 1);
+  }
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int p2 = blockIdx.x * 256 + pg + 64 * i, yy = p2 >> 7, xq = p2 & 127;
+    const int y2 = 2 * yy + (q >> 1), x2 = 2 * xq + (q & 1);
     const float* f0 = s0 + b * s0_bs + (long)y2 * 256 + x2;
     float m[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
-    for (int o = 0; o < 32; ++o) {
-      const float gv = gelu_exact(acc[o] + f0[(long)o * 65536]);
+    for (int o = 0; o < 16; ++o) {
+      float a0, a1;
+      f2_unpack(acc2[i][o], a0, a1);
+      const float g0 = gelu_fast(a0 + f0[(long)(2 * o) * 65536]), g1 = gelu_fast(a1 + f0[(long)(2 * o + 1) * 65536]);
 #pragma unroll
-      for (int k = 0; k < 4; ++k) m[k] = fmaf(hs[k * 32 + o], gv, m[k]);
+      for (int k = 0; k < 4; ++k) m[k] = fmaf(hs[k * 32 + 2 * o + 1], g1, fmaf(hs[k * 32 + 2 * o], g0, m[k]));
     }
 #pragma unroll
     for (int k = 0; k < 4; ++k) masks[(((long)b * 4 + k) * 256 + y2) * 256 + x2] = m[k];
@@ -697,7 +719,7 @@ int heads_upscale(const float* u1, const float* b1, const float* s1, long s1_bs,
                   const float* w2, const float* b2, const float* s0, long s0_bs, const float* hyper, float* masks, int* stab,
                   float delta, int n, cudaStream_t st) {
   static PerDeviceFlag attr;
-  const int smem = (64 * 128 + 128 + 32) * 4;
+  const int smem = (64 * 128 + 128 + 32 + 64 * 256) * 4;
   if (!attr.is_set()) {
     if (cudaFuncSetAttribute(heads_upscale_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem) != cudaSuccess) {
       set_error("heads_upscale: cannot set the shared-memory size");

@@ -363,13 +363,14 @@ class _GraphedTrack:
         else:
             if self.graph is None or self.gen != vp.engine.workspace_generation():
                 # (re-)capture: no kernel runs here; a workspace that another call re-allocated invalidates the old graph
-                side = torch.cuda.Stream(device=vp.device)
+                gen = vp.engine.workspace_generation()       # read BEFORE the capture: a re-allocation by another host thread
+                side = torch.cuda.Stream(device=vp.device)    # while this one captures must invalidate the new graph as well
                 side.wait_stream(torch.cuda.current_stream(vp.device))
                 self.graph = torch.cuda.CUDAGraph()
                 with torch.cuda.graph(self.graph, stream=side, capture_error_mode="thread_local"):
                     self.out = self._body()
                 torch.cuda.current_stream(vp.device).wait_stream(side)
-                self.gen = vp.engine.workspace_generation()
+                self.gen = gen
             vp.engine.replay(self.graph)
             out = self.out
         self.served += 1
