@@ -90,6 +90,15 @@ int sam2b_memory_attention_varlen(sam2b_handle h, const float* curr, const float
                                   const float* memory_pos_exclude, int P_max, int n, const int32_t* L_rows,
                                   const int32_t* P_rows, float* out, void* stream);
 
+/* The same with the per-object counts on the DEVICE: counts_dev is a device int32 array [2][n] = (frames L_b, pointer tokens
+ * P_b).  Nothing crosses from the host, so the call can sit inside a captured CUDA graph whose bank fills up from frame to frame
+ * (sam2_opt_b200.predictor._GraphedTrack).  The values are clamped to [1, L_max] / [0, P_max] (P_b rounded down to a multiple
+ * of 4) on the device, since the host cannot validate them. */
+int sam2b_memory_attention_varlen_dev(sam2b_handle h, const float* curr, const float* curr_pos, const float* memory,
+                                      const float* memory_pos, int L_max, const float* memory_exclude,
+                                      const float* memory_pos_exclude, int P_max, int n, const int32_t* counts_dev, float* out,
+                                      void* stream);
+
 /* ---- E4: MemoryEncoder ----
  * pix_feat dev [n,256,64,64], masks dev [n,1,1024,1024] (already sigmoid-scaled) -> out_x dev [n,64,64,64].
  * (the second reference output, the sine position encoding, is a constant: sam2b_position_encoding) */

@@ -25,6 +25,7 @@ SIGNATURES = {
     "sam2b_position_encoding": (_i, [_i, _i, _i, _vp, _vp]),
     "sam2b_memory_attention": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _vp, _vp, _i, _i, _vp, _vp]),
     "sam2b_memory_attention_varlen": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _vp, _vp, _i, _i, C.POINTER(C.c_int32), C.POINTER(C.c_int32), _vp, _vp]),
+    "sam2b_memory_attention_varlen_dev": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _vp, _vp, _i, _i, _vp, _vp, _vp]),
     "sam2b_memory_encode": (_i, [_vp, _vp, _vp, _i, _vp, _vp]),
     "sam2b_memory_encode_low_res": (_i, [_vp, _vp, _i64, _vp, _i, _vp, _i, _vp, _vp]),
     "sam2b_sam_heads": (_i, [_vp, _vp, _i64, _i64, _i64, _vp, _i64, _vp, _i64, _vp, _vp, _i, _vp, _i, _vp, _i, _i, _i,

@@ -583,7 +583,7 @@ static int image_encode_mb(sam2b_engine* e, const float* img, int n, int normali
 // different banks); nullptr = L and P for all.
 static int memory_attention_mb(sam2b_engine* e, const float* curr, const float* curr_pos, const float* memory,
                                const float* memory_pos, int L, const float* excl, const float* pos_excl, int P, int n,
-                               int n_total, const int* rows_host, float* out, cudaStream_t st) {
+                               int n_total, const int* rows_host, float* out, cudaStream_t st, const int* counts_dev = nullptr) {
   // curr/memory pointers address object 0 of this micro-batch inside tensors whose batch dimension is n_total
   const int T = 4096, C = 256;
   const long Lk = (long)L * 4096 + P;
@@ -603,6 +603,9 @@ static int memory_attention_mb(sam2b_engine* e, const float* curr, const float* 
     }
     // pageable source: staged by the runtime before the call returns, stream-ordered afterwards
     CUDA_OK(cudaMemcpyAsync(ROWS, r.data(), r.size() * sizeof(int), cudaMemcpyHostToDevice, st));
+  } else if (counts_dev) {      // the counts live on the device (a captured graph reads them from its control vector)
+    TRY(ws_get_t(e, "ma_rows", (size_t)3 * n, &ROWS));
+    TRY(memattn_rows_from_device(counts_dev, ROWS, n, L, P, st));
   }
   TRY(ws_get_t(e, "ma_x", (size_t)TT * C, &X));
   TRY(ws_get_t(e, "ma_out", (size_t)TT * C, &OUT));
@@ -1194,6 +1197,19 @@ int sam2b_memory_attention_varlen(sam2b_handle h, const float* curr, const float
   ENGINE_CALL(h, reinterpret_cast<cudaStream_t>(stream));
   return memory_attention_mb(h, curr, curr_pos, memory, memory_pos, L_max, memory_exclude, memory_pos_exclude, P_max, n, n, rows.data(),
                              out, reinterpret_cast<cudaStream_t>(stream));
+}
+
+int sam2b_memory_attention_varlen_dev(sam2b_handle h, const float* curr, const float* curr_pos, const float* memory,
+                                      const float* memory_pos, int L_max, const float* memory_exclude, const float* memory_pos_exclude,
+                                      int P_max, int n, const int32_t* counts_dev, float* out, void* stream) {
+  if (!h || !h->finalized) { set_error("sam2b_memory_attention_varlen_dev: engine not finalized"); return 1; }
+  if (!curr || !curr_pos || !memory || !memory_pos || !out || !counts_dev || n <= 0) { set_error("sam2b_memory_attention_varlen_dev: null/empty argument"); return 1; }
+  if (L_max < 1 || L_max > 16 || P_max < 0 || P_max > 64 || (P_max % 4)) { set_error("sam2b_memory_attention_varlen_dev: L_max=%d must be in [1,16], P_max=%d in [0,64] and a multiple of 4", L_max, P_max); return 1; }
+  if (P_max > 0 && (!memory_exclude || !memory_pos_exclude)) { set_error("sam2b_memory_attention_varlen_dev: P_max=%d but memory_exclude is NULL", P_max); return 1; }
+  ENTER_DEVICE(h->device);
+  ENGINE_CALL(h, reinterpret_cast<cudaStream_t>(stream));
+  return memory_attention_mb(h, curr, curr_pos, memory, memory_pos, L_max, memory_exclude, memory_pos_exclude, P_max, n, n, nullptr, out,
+                             reinterpret_cast<cudaStream_t>(stream), counts_dev);
 }
 
 int sam2b_memory_encode(sam2b_handle h, const float* pix_feat, const float* masks, int n, float* out_x, void* stream) {

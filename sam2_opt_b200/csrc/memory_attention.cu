@@ -20,6 +20,24 @@ __global__ void __launch_bounds__(256) memattn_prep_x_kernel(const float4* __res
     x[((long)b * T + t) * C4 + c] = make_float4(a.x + 0.1f * p.x, a.y + 0.1f * p.y, a.z + 0.1f * p.z, a.w + 0.1f * p.w);
   }
 }
+// rows [3][n] = (spatial keys, pointer tokens, keys in total) of every object from DEVICE counts [2][n] = (frames, pointer
+// tokens), clamped to the tensors' extents (the host cannot validate values it never sees)
+__global__ void memattn_rows_kernel(const int* __restrict__ counts, int* __restrict__ rows, int n, int L_max, int P_max) {
+  const int b = blockIdx.x * blockDim.x + threadIdx.x;
+  if (b >= n) return;
+  int L = counts[b], P = counts[n + b];
+  L = L < 1 ? 1 : (L > L_max ? L_max : L);
+  P = P < 0 ? 0 : (P > P_max ? P_max : P);
+  P &= ~3;
+  rows[b] = L * 4096; rows[n + b] = P; rows[2 * n + b] = L * 4096 + P;
+}
+int memattn_rows_from_device(const int* counts, int* rows, int n, int L_max, int P_max, cudaStream_t stream) {
+  ProfRange pr(stream, "memattn_rows", 0, 0);
+  memattn_rows_kernel<<<(n + 127) / 128, 128, 0, stream>>>(counts, rows, n, L_max, P_max);
+  SAM2B_CHECK_LAUNCH("memattn_rows");
+  return 0;
+}
+
 int memattn_prep_x(const float* curr, const float* curr_pos, float* x, int T, int n, int C, cudaStream_t stream) {
   const long total = (long)T * n * (C / 4);
   long blocks = (total + 255) / 256;

@@ -146,6 +146,8 @@ int mlp_fused(const bf16* xb, const float* stats_in, int parts_in, float eps, co
 
 namespace sam2b {
 // ---- memory attention helpers (memory_attention.cu) ----
+// rows [3][n] (spatial keys, pointer tokens, total) from device counts [2][n] (frames, pointer tokens), clamped to L_max / P_max
+int memattn_rows_from_device(const int* counts, int* rows, int n, int L_max, int P_max, cudaStream_t stream);
 // x[b][t][c] = curr[t][b][c] + 0.1 * curr_pos[t][b][c]      (seq-first [T,n,C] -> batch-major [n,T,C], fp32)
 int memattn_prep_x(const float* curr, const float* curr_pos, float* x, int T, int n, int C, cudaStream_t stream);
 // out[t][b][c] = x[b][t][c]

@@ -177,9 +177,10 @@ class Engine:
 
     # -- E3 --------------------------------------------------------------------------------------------------
     def memory_attention(self, curr, memory, curr_pos, memory_pos, memory_exclude=None, memory_pos_exclude=None,
-                         L_rows=None, P_rows=None):
+                         L_rows=None, P_rows=None, counts_dev=None):
         """E3.  L_rows / P_rows (optional sequences of n ints): objects whose banks differ share one call — the tensors are
-        padded to the largest bank and object b uses memory[:L_rows[b]] / memory_exclude[:P_rows[b]] only."""
+        padded to the largest bank and object b uses memory[:L_rows[b]] / memory_exclude[:P_rows[b]] only.
+        counts_dev: the same counts as a DEVICE int32 tensor [2,n] (frames, pointer tokens) — no host data, capturable."""
         curr, curr_pos = _f32c(curr, "curr"), _f32c(curr_pos, "curr_pos")
         memory, memory_pos = _f32c(memory, "memory"), _f32c(memory_pos, "memory_pos")
         L, n = memory.shape[0], curr.shape[1]
@@ -187,6 +188,15 @@ class Engine:
         if P:
             memory_exclude, memory_pos_exclude = _f32c(memory_exclude, "memory_exclude"), _f32c(memory_pos_exclude, "memory_pos_exclude")
         out = torch.empty_like(curr)
+        if counts_dev is not None:
+            if counts_dev.dtype != torch.int32 or not counts_dev.is_cuda or tuple(counts_dev.shape) != (2, n) or not counts_dev.is_contiguous():
+                raise ValueError(f"memory_attention: counts_dev must be a contiguous CUDA int32 tensor [2,{n}]")
+            with self._lock:
+                _lib.check(self.lib.sam2b_memory_attention_varlen_dev(
+                    self._h, _ptr(curr), _ptr(curr_pos), _ptr(memory), _ptr(memory_pos), L,
+                    _ptr(memory_exclude if P else None), _ptr(memory_pos_exclude if P else None), P, n, _ptr(counts_dev),
+                    _ptr(out), self._stream()), "memory_attention_varlen_dev")
+            return out
         if L_rows is not None or P_rows is not None:
             arr = lambda v: None if v is None else (C.c_int32 * n)(*[int(x) for x in v])
             if (L_rows is not None and len(L_rows) != n) or (P_rows is not None and len(P_rows) != n):

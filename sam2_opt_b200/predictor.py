@@ -273,17 +273,20 @@ class _BankRing:
 
 
 class _GraphedTrack:
-    """the steady-state tracked frame of one group of n objects as ONE CUDA graph.
+    """the tracked frame of one group of n objects as ONE CUDA graph.
 
-    Once the memory bank is full (one conditioning frame + the 6 most recent frames) and 16 object pointers exist, every
-    tracked frame runs the same ~150 kernels on the same shapes: memory_pos assembly, E3 (L = 7, P = 64), the SAM heads, E4
-    and the bank update.  At one object the GPU needs 1.2 ms for them while the host needs 1.9 ms to enqueue them
-    (tools/frame_timeline.py), so the sequence is captured once and replayed.  What differs from frame to frame is DATA on the
-    device: the bank lives in a ring `mem [7,4096,n,64]` (slot 0 the conditioning frame, frame t in slot 1 + t % 6), the object
-    pointers in `ptrs [16,n,256]` (slot 0 the conditioning frame, frame t in slot 1 + t % 15), and a small control vector
-    (one pinned H2D copy per frame) carries each slot's current age / temporal distance and the slots the new frame
-    overwrites.  Attention does not depend on the order of its keys as long as each keeps its own position term, so the
-    values equal `sam_heads.assemble_memory` up to fp32 summation order (ref: sam2_base_official.py:825-950)."""
+    Every tracked frame after a single conditioning frame runs the same ~150 kernels: memory_pos assembly, E3, the SAM heads,
+    E4 and the bank update.  At one object the GPU needs 1.2 ms for them while the host needs 1.9 ms to enqueue them (4.5 ms
+    while the bank is still filling and every frame has a new shape; tools/frame_timeline.py), so the sequence is captured once
+    and replayed.  What differs from frame to frame is DATA on the device: the bank lives in a ring `mem [7,4096,n,64]` (slot 0
+    the conditioning frame t_c, frame t in slot 1 + (t - t_c - 1) % 6), the object pointers in `ptrs [16,n,256]` (slot 0 the
+    conditioning frame, frame t in slot 1 + (t - t_c - 1) % 15), and a small control vector (one pinned H2D copy per frame)
+    carries each slot's current age / temporal distance, the slots the new frame overwrites and HOW MANY frames / pointers the
+    bank holds: E3 always runs at L = 7, P = 64 with the per-object counts read on the device
+    (sam2b_memory_attention_varlen_dev), so the frames right after the prompt (1 .. 6 bank frames, 1 .. 15 pointers: the
+    filled slots are a prefix of the rings) replay the same graph.  Attention does not depend on the order of its keys as long
+    as each keeps its own position term, so the values equal `sam_heads.assemble_memory` up to fp32 summation order
+    (ref: sam2_base_official.py:825-950)."""
 
     TABLE_ROWS = 2049          # projected temporal encodings of the pointer distances 0 .. 2048 (longer videos: a larger table)
 
@@ -296,8 +299,12 @@ class _GraphedTrack:
         self.pe = torch.empty((4096, 1, H.MEM_DIM), device=dev)           # sine encoding of the bank frames
         self.table = torch.zeros((self.TABLE_ROWS, H.MEM_DIM), device=dev)
         self.tpos = w["maskmem_tpos_enc"].reshape(H.NUM_MASKMEM, 1, 1, H.MEM_DIM)
-        self.ctl = torch.zeros(25, dtype=torch.int64, device=dev)          # ages[7] | distances[16] | mem slot | ptr slot
-        self.ctl_host = [torch.zeros(25, dtype=torch.int64).pin_memory() for _ in range(4)]
+        self.ctl = torch.zeros(27, dtype=torch.int64, device=dev)          # ages[7] | distances[16] | mem slot | ptr slot | L | P
+        # pinned staging ring for the control vector: slot i is rewritten only after the copy that last read it has completed
+        # (an event per slot; a caller that does not synchronise per frame lets the host run frames ahead of the device)
+        self.ctl_host = [torch.zeros(27, dtype=torch.int64).pin_memory() for _ in range(4)]
+        self.ctl_done = [None] * len(self.ctl_host)
+        self.counts = torch.zeros((2, n), dtype=torch.int32, device=dev)   # E3's per-object (frames, pointer tokens)
         self.f2 = torch.empty((1, 256, 64, 64), device=dev)
         self.hr = [torch.empty((1, 32, 256, 256), device=dev), torch.empty((1, 64, 128, 128), device=dev)]
         self.pos2 = vp.engine.position_encoding(256, 64, 1).flatten(2).permute(2, 0, 1).expand(-1, n, -1).contiguous()
@@ -311,10 +318,10 @@ class _GraphedTrack:
         self.mem[0].copy_(rows(cond_rec["maskmem_features"]))
         self.ptrs[0].copy_(cond_rec["obj_ptr"])
         self.pe.copy_(rows(cond_rec["maskmem_pos"][:1]))
-        for tt in range(t - 6, t):
-            self.mem[1 + tt % 6].copy_(rows(recs[tt]["maskmem_features"]))
-        for tt in range(t - 15, t):
-            self.ptrs[1 + tt % 15].copy_(recs[tt]["obj_ptr"])
+        for tt in range(max(t_cond + 1, t - 6), t):
+            self.mem[1 + (tt - t_cond - 1) % 6].copy_(rows(recs[tt]["maskmem_features"]))
+        for tt in range(max(t_cond + 1, t - 15), t):
+            self.ptrs[1 + (tt - t_cond - 1) % 15].copy_(recs[tt]["obj_ptr"])
         table = H._ptr_tpos_table(self.vp.w, num_frames, 16, self.vp._tpos_cache)  # [num_frames + 1, 64]
         if table.shape[0] > self.table.shape[0]:
             self.table = torch.zeros((table.shape[0], H.MEM_DIM), device=self.vp.device)
@@ -322,15 +329,15 @@ class _GraphedTrack:
         self.table[:table.shape[0]].copy_(table)
 
     def _control(self, t):
+        k0 = t - self.t_cond - 1                                           # tracked frames since the conditioning frame
         ages = [H.NUM_MASKMEM - 1]                                         # conditioning frame: t_pos 0
         for s in range(1, H.NUM_MASKMEM):
-            tt = t - 1 - ((t - 1 - (s - 1)) % 6)                           # the frame in slot s: tt = s - 1 (mod 6), t-6 <= tt < t
-            ages.append(t - tt - 1)                                        # t_pos = 7 - (t - tt) -> index 7 - t_pos - 1
+            # slot s holds frame tt = t - 1 - r, the latest one with (tt - t_c - 1) = s - 1 (mod 6); t_pos = 7 - (t - tt) -> index r
+            ages.append((k0 - s) % 6 if (s <= k0 or k0 >= 6) else 0)       # (unfilled slots: any valid index, never read)
         dists = [t - self.t_cond]
         for p in range(1, 16):
-            tt = t - 1 - ((t - 1 - (p - 1)) % 15)
-            dists.append(t - tt)
-        return ages + dists + [1 + t % 6, 1 + t % 15]
+            dists.append(1 + (k0 - p) % 15 if (p <= k0 or k0 >= 15) else 0)
+        return ages + dists + [1 + k0 % 6, 1 + k0 % 15, 1 + min(k0, 6), 4 * (1 + min(k0, 15))]
 
     def _body(self):
         vp, n = self.vp, self.n
@@ -339,7 +346,8 @@ class _GraphedTrack:
         ptr_tok = self.ptrs.reshape(16, n, 4, H.MEM_DIM).permute(0, 2, 1, 3).flatten(0, 1)                    # [64,n,64]
         ppos = self.table.index_select(0, self.ctl[7:23]).unsqueeze(1).expand(-1, n, H.MEM_DIM).repeat_interleave(4, dim=0)
         curr = self.f2.flatten(2).permute(2, 0, 1).expand(-1, n, -1)
-        pix = vp.engine.memory_attention(curr, self.mem, self.pos2, self.pos, ptr_tok, ppos)
+        self.counts.copy_(self.ctl[25:27, None].expand(2, n))              # int64 -> int32, one row of L and one of P
+        pix = vp.engine.memory_attention(curr, self.mem, self.pos2, self.pos, ptr_tok, ppos, counts_dev=self.counts)
         pix = pix.permute(1, 2, 0).reshape(n, H.D_MODEL, 64, 64)
         _, _, _, low, _, ptr, obj = vp.engine.sam_heads(pix, self.hr, multimask_output=True, high_res=False)
         mf, mp = vp._encode_memory_low(self.f2, low, obj, False)
@@ -351,9 +359,14 @@ class _GraphedTrack:
     def step(self, t, f2, hr):
         assert t == self.next_t
         vp = self.vp
-        h = self.ctl_host[t % len(self.ctl_host)]
+        i = t % len(self.ctl_host)
+        if self.ctl_done[i] is not None:
+            self.ctl_done[i].synchronize()
+        h = self.ctl_host[i]
         h.copy_(torch.tensor(self._control(t), dtype=torch.int64))
         self.ctl.copy_(h, non_blocking=True)
+        self.ctl_done[i] = torch.cuda.Event()
+        self.ctl_done[i].record(torch.cuda.current_stream(vp.device))
         self.f2.copy_(f2)
         self.hr[0].copy_(hr[0])
         self.hr[1].copy_(hr[1])
@@ -403,6 +416,7 @@ class SAM2VideoPredictor(_Base):
         self.add_all_frames_to_correct_as_cond = bool(add_all_frames_to_correct_as_cond)
         # graph_track: replay the steady-state tracked frame (full bank, 16 pointers) from one CUDA graph (see _GraphedTrack)
         self.graph_track = bool(graph_track)
+        self.graph_track_early_objects = 4     # up to this many objects the graph also serves the frames where the bank is filling
         self._heads_graphs = {}            # (object count, host thread) -> _GraphedHeads
         self._track_graphs = {}            # (object count, host thread) -> _GraphedTrack
         self._copy_stream = None           # host -> device copies of the next block of frames (see _upload)
@@ -800,12 +814,16 @@ class SAM2VideoPredictor(_Base):
         key = tuple(g_objs)
         if len(cond_keys) != 1 or cond_keys[0] >= t or st["num_frames"] < 17 or len(st["cond"]) != 1:
             return None
+        # while the bank is filling the graph still runs E3 at its full size (the counts only mask): worth it where the frame is
+        # bound by the host (few objects), not where the GPU is the limit and a 2-frame bank is 4x cheaper than a 7-frame one
+        if t - cond_keys[0] <= 15 and len(g_objs) > self.graph_track_early_objects:
+            return None
         gk = (len(key), threading.get_ident())          # static buffers and graph: one per object count and host thread
         tr = self._track_graphs.get(gk)
         owner = (id(st), key)
         if tr is None or tr.owner != owner or tr.next_t != t or st["gtrack"].get(key) is not tr:
-            recs = {tt: st["non_cond_b"].get(tt, {}).get(key) for tt in range(t - 15, t)}
-            if t - 15 <= cond_keys[0] or any(r is None for r in recs.values()):
+            recs = {tt: st["non_cond_b"].get(tt, {}).get(key) for tt in range(max(cond_keys[0] + 1, t - 15), t)}
+            if any(r is None for r in recs.values()):
                 return None
             if tr is None:
                 tr = self._track_graphs[gk] = _GraphedTrack(self, len(key))

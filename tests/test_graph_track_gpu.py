@@ -1,5 +1,6 @@
-"""GPU: the steady-state tracked frame replayed from one CUDA graph (predictor._GraphedTrack) against
-the same predictor enqueuing every call (graph_track=False).  The two differ only in the order of the memory-bank slots,
+"""GPU: the tracked frame replayed from one CUDA graph (predictor._GraphedTrack; with two objects the
+graph also serves the frames where the bank is still filling: E3 at full size with device-side counts) against the same
+predictor enqueuing every call (graph_track=False).  The two differ only in the order of the memory-bank slots,
 i.e. in fp32 summation order inside the attention: per-frame mask IoU >= 0.999, object pointers rel-L2 <= 1e-3.
 
 Also covered: a workspace re-allocation between replays (a larger problem arrives: the captured addresses go stale and the
@@ -54,7 +55,7 @@ def test_graph_replay_matches_enqueued_frames(weights):
     st_g = _run(vp, frames, clicks, poke)
     assert vp.engine.workspace_generation() > gen0
     trackers = list(st_g["gtrack"].values())
-    assert len(trackers) == 1 and trackers[0].served == T - 16, "the graph path did not run from frame 16 on"
+    assert len(trackers) == 1 and trackers[0].served == T - 1, "the graph path did not run from the first tracked frame on"
     vp_e = SAM2VideoPredictor(weights, graph_track=False)
     st_e = _run(vp_e, frames, clicks)
     worst, worst_ptr = 1.0, 0.0

@@ -157,3 +157,22 @@ def test_memory_attention_objects_with_different_banks_share_one_call(engine, we
         assert ((got[:, i] - alone).norm() / alone.norm()).item() < 5e-3
     with pytest.raises(RuntimeError, match="object 1 has L=9"):
         engine.memory_attention(curr.cuda(), mem.cuda(), curr_pos.cuda(), mpos.cuda(), ex.cuda(), pex.cuda(), L_rows=[7, 9, 1], P_rows=[64, 8, 0])
+
+
+def test_memory_attention_counts_on_the_device(engine):
+    """sam2b_memory_attention_varlen_dev: the per-object (frames, pointer tokens) counts as a DEVICE tensor (what a captured
+    graph reads from its control vector while the bank fills up) — every bank size a video passes through, all objects with
+    the same reduced count, against the plain call on the un-padded bank; NaN padding must never be read."""
+    from oracle.synth import synth_memattn_inputs
+    n, Lm, Pm = 2, 7, 64
+    curr, mem, curr_pos, mpos, ex, pex = [t.cuda() for t in synth_memattn_inputs(Lm, Pm, n, seed=31)]
+    for L, P in ((1, 4), (2, 8), (4, 16), (7, 28), (7, 64)):
+        want = engine.memory_attention(curr, mem[:L].contiguous(), curr_pos, mpos[:L].contiguous(), ex[:P].contiguous(), pex[:P].contiguous())
+        m2, p2, e2, q2 = mem.clone(), mpos.clone(), ex.clone(), pex.clone()
+        m2[L:], p2[L:], e2[P:], q2[P:] = float("nan"), float("nan"), float("nan"), float("nan")
+        counts = torch.tensor([[L] * n, [P] * n], dtype=torch.int32, device="cuda")
+        got = engine.memory_attention(curr, m2, curr_pos, p2, e2, q2, counts_dev=counts)
+        assert torch.isfinite(got).all()
+        r = ((got - want).norm() / want.norm()).item()
+        print(f"device counts (L={L}, P={P}): rel-L2 vs the un-padded call = {r:.2e}")
+        assert r < 5e-3
