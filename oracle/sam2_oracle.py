@@ -548,6 +548,23 @@ def forward_sam_heads(w: W, backbone_features: Tensor, point_inputs=None, mask_i
     return low, high, ious, low_best, high_best, ptr, obj_logits
 
 
+def use_mask_as_output(w: W, backbone_features: Tensor, high_res_features, mask_inputs: Tensor):
+    """A mask prompt turned straight into the frame's output (what `add_new_mask` / the VOS tool feed) — ref:
+    modeling/sam2_base_official.py:496-545 (_use_mask_as_output): +10 / -10 logits, antialiased x1/4 for the low-res copy, IoU
+    of one, the object pointer from the SAM heads run on `mask_downsample(mask)` as their mask prompt, and the MASK (not the
+    decoder) deciding whether the object is there.  Same 7 outputs as forward_sam_heads."""
+    m = mask_inputs.float()
+    high = m * 20.0 - 10.0
+    low = F.interpolate(high, size=(high.shape[-2] // 4, high.shape[-1] // 4), align_corners=False, mode="bilinear", antialias=True)
+    ious = torch.ones(m.shape[0], 1)
+    prompt = conv2d(m, w["mask_downsample.weight"], w["mask_downsample.bias"], stride=4)
+    ptr = forward_sam_heads(w, backbone_features, mask_inputs=prompt, high_res_features=high_res_features)[5]
+    lam = (m.flatten(1) > 0).any(dim=1, keepdim=True).float()
+    obj_logits = 20.0 * lam - 10.0
+    ptr = lam * ptr + (1 - lam) * w["no_obj_ptr"]
+    return low, high, ious, low, high, ptr, obj_logits
+
+
 # ---------------------------------------------------------------------------------------
 # Predictor-level glue (configs 1 and 3): image predict + single-direction video propagation
 # ---------------------------------------------------------------------------------------

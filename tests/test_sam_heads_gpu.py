@@ -167,3 +167,21 @@ def test_sparse_embeddings_given_and_mask_tokens_out(engine, weights):
                             multimask_output=False, decoder_only=True, high_res=False, mask_tokens=True)
     assert rel_l2(got0[0], masks0) <= TOL and (got0[2].cpu() - iou0).abs().max().item() <= TOL
     assert rel_l2(got0[7][:, 0:1], tok0) <= TOL
+
+
+def test_rejects_bad_arguments(engine):
+    """Errors are loud and name the problem (no silent fallback): too many points, mismatched shapes, host tensors."""
+    pix = torch.randn(1, 256, 64, 64, device="cuda")
+    hr = [torch.randn(1, 32, 256, 256, device="cuda"), torch.randn(1, 64, 128, 128, device="cuda")]
+    with pytest.raises(RuntimeError, match="points per prompt"):
+        engine.sam_heads(pix, hr, torch.rand(1, 26, 2, device="cuda") * 1024, torch.ones(1, 26, dtype=torch.int32, device="cuda"))
+    with pytest.raises(RuntimeError, match="sparse embeddings per prompt"):
+        engine.sam_heads(pix, hr, sparse_embeddings=torch.randn(1, 27, 256, device="cuda"))
+    with pytest.raises(ValueError, match="backbone_features"):
+        engine.sam_heads(pix[:, :128], hr)
+    with pytest.raises(ValueError, match="high-res feature"):
+        engine.sam_heads(pix, [hr[1], hr[0]])
+    with pytest.raises(RuntimeError, match="CUDA fp32"):
+        engine.sam_heads(pix.cpu(), hr)
+    with pytest.raises(ValueError, match="memory_encode_low_res"):
+        engine.memory_encode_low_res(pix, torch.randn(1, 1, 128, 128, device="cuda"))
