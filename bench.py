@@ -232,7 +232,7 @@ def grid_clicks(n_objects):
     return [[128 + 768.0 * (o % g) / max(1, g - 1), 128 + 768.0 * (o // g) / max(1, g - 1)] for o in range(n_objects)]
 
 
-def attention_roofline(rows):
+def attention_roofline(rows, nobj=1):
     """Roofline of the video path's dominant kernel, the cross-attention over the memory bank (flash_attn_hd256_v64_tcgen05_kernel),
     from the library's per-launch CUDA-event profile: full-bank launches only (7 frames x 4096 + 64 pointer tokens = 28 736 keys)."""
     peak, _, how = _peaks()
@@ -242,12 +242,21 @@ def attention_roofline(rows):
     s_ms, s_fl = sum(x[0] for x in self_), sum(x[1] for x in self_)
     tot = sum(r[1] for r in rows)
     issued = c_fl * 320.0 / 512.0      # the kernel issues 2 T Lk (256 + 64) flops; the reference's formulation needs 4 T Lk 256
-    return {"bound": "tensor", "kernel": "flash_attn_hd256_v64_tcgen05_kernel",
+    traffic, traffic_note = None, None
+    cap = os.path.join(ROOT, "profiles", "r2n_top_kernels_summary.json")
+    if nobj == 16 and os.path.exists(cap):      # the committed ncu --set full capture ran this kernel at 16 objects, 28 736 keys
+        with open(cap) as f:
+            v64 = [r for r in json.load(f) if "hd256_v64" in r["kernel"]]
+        if v64:
+            traffic = v64[-1]["dram_read_bytes"] + v64[-1]["dram_write_bytes"]
+            traffic_note = ("dram__bytes_read.sum + dram__bytes_write.sum of the warm launch at 16 objects x 28 736 keys (profiles/r2n_top_kernels_summary.json, "
+                            "tools/ncu_top_kernels.py); algorithmic bytes per launch: q 33.6 + k 235.4 + v 58.9 + out 8.4 = 336 MB")
+    return {"bound": "tensor", "kernel": "flash_attn_hd256_v64_tcgen05_kernel", "traffic_note": traffic_note,
             "achieved": issued / (c_ms * 1e-3) / 1e12 if c_ms else None, "peak": peak, "unit": "TFLOP/s",
             "frac": (issued / (c_ms * 1e-3) / 1e12 / peak) if c_ms else None,
             "achieved_algorithmic": c_fl / (c_ms * 1e-3) / 1e12 if c_ms else None,
             "launches": len(cross), "avg_launch_ms": c_ms / max(1, len(cross)),
-            "share_of_library_kernel_time": c_ms / tot if tot else None, "peak_source": how, "traffic": None,
+            "share_of_library_kernel_time": c_ms / tot if tot else None, "peak_source": how, "traffic": traffic,
             "self_attention": {"kernel": "flash_attn_hd256_tcgen05_kernel", "achieved": s_fl / (s_ms * 1e-3) / 1e12 if s_ms else None,
                                "launches": len(self_), "share_of_library_kernel_time": s_ms / tot if tot else None},
             "note": "achieved = flops the kernel issues, 2*4096*Lk*(256+64) per object and layer (v_proj is applied after P V on 64-wide "
@@ -430,7 +439,7 @@ def main():
         peak, hbm, how = _peaks()
         ach = g_fl / (g_ms * 1e-3) / 1e12
         traffic, traffic_note = None, None
-        tp = next((q for q in (os.path.join(ROOT, "profiles", n) for n in ("r2_traffic.json", "r2b_traffic.json")) if os.path.exists(q)), None)
+        tp = next((q for q in (os.path.join(ROOT, "profiles", n) for n in ("r2n_traffic.json", "r2_traffic.json", "r2b_traffic.json")) if os.path.exists(q)), None)
         if tp:
             tj = json.load(open(tp))
             traffic = tj["dram_bytes_per_launch_avg"]
@@ -518,7 +527,7 @@ def main():
                 E.profile_begin()
                 v0, lo0, hi0 = mine[0]
                 run_clip(vp, clips[v0][:22], clicks, lo0, hi0)
-                video16["roofline"] = attention_roofline(E.profile_end())
+                video16["roofline"] = attention_roofline(E.profile_end(), nobj)
                 vp.graph_track = True
             del clips
         vp.release()
