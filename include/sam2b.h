@@ -157,6 +157,12 @@ int sam2b_stream_acquire(sam2b_handle h, void* stream);
 int sam2b_stream_release(sam2b_handle h, void* stream);
 unsigned long long sam2b_workspace_generation(sam2b_handle h);
 
+/* The dense embedding of a mask prompt: PromptEncoder._embed_masks (sam2/sam2/modeling/sam/prompt_encoder.py:97-109,152-155),
+ * i.e. conv 2x2 s2 + LayerNorm2d + GELU twice and a 1x1 conv.  mask_prompt dev [n,1,256,256] (logits at the prompt encoder's
+ * mask_input_size) -> dense_embedding dev [n,256,64,64], the `dense_embedding` argument of sam2b_sam_heads.  Touches no
+ * workspace of the engine (no serialisation against other calls needed). */
+int sam2b_mask_downscale(sam2b_handle h, const float* mask_prompt, int n, float* dense_embedding, void* stream);
+
 /* ---- peer memory for the embedding gather (the only collective of the path) ----
  * The reference has no multi-GPU inference path (one process, one GPU: sam2/ytools/tensorrt/tensorrt_executor.py:26-29);
  * this is the B200-box replacement: one process per GPU, every rank owns a gather buffer that its peers map through CUDA

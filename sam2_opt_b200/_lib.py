@@ -30,6 +30,7 @@ SIGNATURES = {
     "sam2b_memory_encode_low_res": (_i, [_vp, _vp, _i64, _vp, _i, _vp, _i, _vp, _vp]),
     "sam2b_sam_heads": (_i, [_vp, _vp, _i64, _i64, _i64, _vp, _i64, _vp, _i64, _vp, _vp, _i, _vp, _i, _vp, _i, _i, _i,
                              _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
+    "sam2b_mask_downscale": (_i, [_vp, _vp, _i, _vp, _vp]),
     "sam2b_stream_acquire": (_i, [_vp, _vp]),
     "sam2b_stream_release": (_i, [_vp, _vp]),
     "sam2b_workspace_generation": (C.c_ulonglong, [_vp]),

@@ -336,6 +336,8 @@ static int finalize(sam2b_engine* e) {
         TRY(need(e, std::string(head) + "layers." + std::to_string(i) + ".bias", nullptr, false));
       }
     TRY(need(e, "no_obj_ptr", nullptr, false));
+    for (const char* nm : {"0.weight", "0.bias", "1.weight", "1.bias", "3.weight", "3.bias", "4.weight", "4.bias", "6.weight", "6.bias"})
+      TRY(need(e, pe + "mask_downscaling." + nm, nullptr, false));
     e->has_heads = true;
   }
   CUDA_OK(cudaStreamSynchronize(0));
@@ -1266,6 +1268,17 @@ int sam2b_sam_heads(sam2b_handle h, const float* backbone_features, int64_t feat
     TRY(sam_heads_mb(h, io, mb, st));
   }
   return 0;
+}
+
+int sam2b_mask_downscale(sam2b_handle h, const float* mask_prompt, int n, float* dense_embedding, void* stream) {
+  if (!h || !h->finalized || !h->has_heads) { set_error("sam2b_mask_downscale: engine not finalized or built without the SAM heads"); return 1; }
+  if (!mask_prompt || !dense_embedding || n <= 0) { set_error("sam2b_mask_downscale: null/empty argument"); return 1; }
+  ENTER_DEVICE(h->device);
+  const std::string d = "sam_prompt_encoder.mask_downscaling.";
+  const float* w[11] = {W32(h, d + "0.weight"), W32(h, d + "0.bias"), W32(h, d + "1.weight"), W32(h, d + "1.bias"),
+                        W32(h, d + "3.weight"), W32(h, d + "3.bias"), W32(h, d + "4.weight"), W32(h, d + "4.bias"),
+                        W32(h, d + "6.weight"), W32(h, d + "6.bias"), nullptr};
+  return mask_downscale(mask_prompt, w, dense_embedding, n, reinterpret_cast<cudaStream_t>(stream));
 }
 
 int sam2b_memory_encode_low_res(sam2b_handle h, const float* pix_feat, int64_t pix_batch_stride, const float* low_res_masks,

@@ -209,6 +209,9 @@ int tok_self_attn(const float* q, const float* k, const float* v, int n, int T, 
 int heads_prep_src(const float* pix, long sn, long sc, long sp, const float* dense, const float* nomask, float* keys, bf16* ks,
                    int n, cudaStream_t st);
 int ln256_split(const float* x, const float* g, const float* b, float eps, float* y, bf16* ys, long rows, cudaStream_t st);
+// PromptEncoder.mask_downscaling: mask [n,1,256,256] -> dense embedding [n,256,64,64]; w = {conv0 w, b, ln1 w, b, conv3 w, b, ln4 w, b,
+// conv6 w, b} in the reference's layouts
+int mask_downscale(const float* mask, const float* const w[11], float* out, int n, cudaStream_t st);
 int heads_tokens(const float* coords, const int* labels, int P, int n, const float* gauss, const float* not_a_point,
                  const float* const pt_emb[4], const float* obj_tok, const float* iou_tok, const float* mask_toks,
                  const float* sparse, int S, float* tok, float* qpe, cudaStream_t st);

@@ -144,6 +144,94 @@ __global__ void heads_tokens_kernel(const float* __restrict__ coords, const int*
 }
 
 // ---------------------------------------------------------------------------------------------------------------------
+// PromptEncoder.mask_downscaling (prompt_encoder.py:97-109,152-155): the dense embedding of a mask prompt [n,1,256,256] ->
+// conv 2x2 s2 (1 -> 4) + LayerNorm2d + GELU -> conv 2x2 s2 (4 -> 16) + LayerNorm2d + GELU -> conv 1x1 (16 -> 256) = [n,256,64,64].
+// One thread per output position: its 4 x 4 input patch, 4 x 4 and 16 intermediate values in registers; the 1x1 weights
+// [256][16] in shared memory.  fp32 throughout, exact (erf) GELU.
+// ---------------------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) mask_downscale_kernel(const float* __restrict__ mask, const float* __restrict__ w0,
+                                                             const float* __restrict__ b0, const float* __restrict__ g1,
+                                                             const float* __restrict__ be1, const float* __restrict__ w3,
+                                                             const float* __restrict__ b3, const float* __restrict__ g4,
+                                                             const float* __restrict__ be4, const float* __restrict__ w6,
+                                                             const float* __restrict__ b6, float* __restrict__ out) {
+  __shared__ float w6s[256 * 16];
+  __shared__ float w3s[16 * 16];     // [c2][c][dy][dx]
+  __shared__ float small[16 + 4 + 4 + 4 + 16 + 16 + 16];
+  float* w0s = small;                // [4][2][2]
+  float* b0s = w0s + 16; float* g1s = b0s + 4; float* be1s = g1s + 4;
+  float* b3s = be1s + 4; float* g4s = b3s + 16; float* be4s = g4s + 16;
+  const int tid = threadIdx.x, b = blockIdx.y;
+  for (int i = tid; i < 4096; i += 256) w6s[i] = w6[i];
+  w3s[tid] = w3[tid];
+  if (tid < 16) { w0s[tid] = w0[tid]; b3s[tid] = b3[tid]; g4s[tid] = g4[tid]; be4s[tid] = be4[tid]; }
+  if (tid < 4) { b0s[tid] = b0[tid]; g1s[tid] = g1[tid]; be1s[tid] = be1[tid]; }
+  __syncthreads();
+  const int pos = blockIdx.x * 256 + tid, y = pos >> 6, x = pos & 63;
+  const float* src = mask + (long)b * 65536 + (4 * y) * 256 + 4 * x;
+  float in[4][4];
+#pragma unroll
+  for (int r = 0; r < 4; ++r) {
+    const float4 v = *reinterpret_cast<const float4*>(src + r * 256);
+    in[r][0] = v.x; in[r][1] = v.y; in[r][2] = v.z; in[r][3] = v.w;
+  }
+  float a1[4][2][2];                 // [c][py][px] after LayerNorm2d + GELU
+#pragma unroll
+  for (int py = 0; py < 2; ++py)
+#pragma unroll
+    for (int px = 0; px < 2; ++px) {
+      float v[4], mean = 0.f;
+#pragma unroll
+      for (int c = 0; c < 4; ++c) {
+        float acc = b0s[c];
+#pragma unroll
+        for (int dy = 0; dy < 2; ++dy)
+#pragma unroll
+          for (int dx = 0; dx < 2; ++dx) acc = fmaf(w0s[c * 4 + dy * 2 + dx], in[2 * py + dy][2 * px + dx], acc);
+        v[c] = acc; mean += acc;
+      }
+      mean *= 0.25f;
+      float var = 0.f;
+#pragma unroll
+      for (int c = 0; c < 4; ++c) { v[c] -= mean; var = fmaf(v[c], v[c], var); }
+      const float rstd = 1.0f / sqrtf(var * 0.25f + 1e-6f);
+#pragma unroll
+      for (int c = 0; c < 4; ++c) a1[c][py][px] = gelu_exact(g1s[c] * (v[c] * rstd) + be1s[c]);
+    }
+  float a2[16], mean = 0.f;
+#pragma unroll
+  for (int c2 = 0; c2 < 16; ++c2) {
+    float acc = b3s[c2];
+#pragma unroll
+    for (int c = 0; c < 4; ++c)
+#pragma unroll
+      for (int dy = 0; dy < 2; ++dy)
+#pragma unroll
+        for (int dx = 0; dx < 2; ++dx) acc = fmaf(w3s[c2 * 16 + c * 4 + dy * 2 + dx], a1[c][dy][dx], acc);
+    a2[c2] = acc; mean += acc;
+  }
+  mean *= (1.0f / 16.0f);
+  float var = 0.f;
+#pragma unroll
+  for (int c2 = 0; c2 < 16; ++c2) { a2[c2] -= mean; var = fmaf(a2[c2], a2[c2], var); }
+  const float rstd = 1.0f / sqrtf(var * (1.0f / 16.0f) + 1e-6f);
+#pragma unroll
+  for (int c2 = 0; c2 < 16; ++c2) a2[c2] = gelu_exact(g4s[c2] * (a2[c2] * rstd) + be4s[c2]);
+  float* dst = out + (long)b * 256 * 4096 + pos;
+  for (int co = 0; co < 256; ++co) {
+    const float4* wr = reinterpret_cast<const float4*>(w6s + co * 16);
+    float acc = b6[co];
+#pragma unroll
+    for (int k4 = 0; k4 < 4; ++k4) {
+      const float4 wv = wr[k4];
+      acc = fmaf(wv.x, a2[4 * k4], acc); acc = fmaf(wv.y, a2[4 * k4 + 1], acc);
+      acc = fmaf(wv.z, a2[4 * k4 + 2], acc); acc = fmaf(wv.w, a2[4 * k4 + 3], acc);
+    }
+    dst[(long)co * 4096] = acc;
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
 // Small fp32 linear layers on the token side, several independent problems ("jobs") per launch:
 //   Y[r][j] = act( sum_k (X[r][k] + X2[r][k]) * W[j][k] + b[j] ),  r < rows, j < N, K % 128 == 0.
 // A job may be one K slice of a larger problem (split K: the partial sums are added by tok_sum_res_ln_kernel).
@@ -640,6 +728,13 @@ int heads_prep_src(const float* pix, long sn, long sc, long sp, const float* den
   ProfRange pr(st, "heads_prep_src", 0, (double)n * 4096 * 256 * (4 + 4 + 6));
   heads_prep_src_kernel<<<dim3(128, 8, n), dim3(32, 8), 0, st>>>(pix, sn, sc, sp, dense, nomask, keys, ks);
   SAM2B_CHECK_LAUNCH("heads_prep_src");
+  return 0;
+}
+
+int mask_downscale(const float* mask, const float* const w[11], float* out, int n, cudaStream_t st) {
+  ProfRange pr(st, "heads_mask_downscale", 2.0 * n * 4096 * (16 * 4 + 256 + 4096), (double)n * (65536 + 256 * 4096) * 4);
+  mask_downscale_kernel<<<dim3(16, n), 256, 0, st>>>(mask, w[0], w[1], w[2], w[3], w[4], w[5], w[6], w[7], w[8], w[9], out);
+  SAM2B_CHECK_LAUNCH("mask_downscale");
   return 0;
 }
 

@@ -224,6 +224,16 @@ class Engine:
                        "memory_encode")
         return x, self.position_encoding(64, 64, n)
 
+    def mask_downscale(self, mask_prompt):
+        """PromptEncoder._embed_masks (ref: sam/prompt_encoder.py:152-155): mask prompt logits [n,1,256,256] -> the dense
+        embedding [n,256,64,64] that `sam_heads(dense_embedding=...)` takes."""
+        m = _f32c(mask_prompt, "mask_prompt")
+        if m.dim() != 4 or tuple(m.shape[1:]) != (1, 256, 256):
+            raise ValueError(f"mask_downscale expects [n,1,256,256], got {tuple(m.shape)}")
+        out = torch.empty((m.shape[0], 256, 64, 64), device=self.device, dtype=torch.float32)
+        _lib.check(self.lib.sam2b_mask_downscale(self._h, _ptr(m), m.shape[0], _ptr(out), self._stream()), "mask_downscale")
+        return out
+
     def memory_encode_low_res(self, pix_feat, low_res_masks, object_score_logits=None, binarize=False):
         """E4 straight from the SAM heads' low-resolution logits [n,1,256,256] (ref: _encode_new_memory,
         sam2_base_official.py:978-1026): sigmoid(bilinear x4) * 20 - 10 (binarize: the (mask > 0) form of prompted frames) is

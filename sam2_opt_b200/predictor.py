@@ -150,7 +150,7 @@ class SAM2ImagePredictor(_Base):
             # enters as the dense embedding of the reference's mask_downscaling convolutions; without any point the decoder sees
             # no sparse token at all (prompt_encoder.py:197-211), which the library takes as an empty set of sparse embeddings
             nb = 1 if coords is None else coords.shape[0]
-            dense = None if mask_t is None else H.prompt_encoder(self.w, None, None, mask_t)[1].expand(nb, -1, -1, -1)
+            dense = None if mask_t is None else self.engine.mask_downscale(mask_t).expand(nb, -1, -1, -1)
             sparse = torch.empty((1, 0, H.D_MODEL), device=self.device) if coords is None else None
             low, _, iou, _, _, _, _ = self.engine.sam_heads(emb.expand(nb, -1, -1, -1), hr, coords, labels, dense,
                                                             multimask_output=multimask_output, decoder_only=True, high_res=False,
@@ -579,7 +579,7 @@ class SAM2VideoPredictor(_Base):
         low = F.interpolate(high, size=(256, 256), align_corners=False, mode="bilinear", antialias=True)
         prompt = F.conv2d(m, self.w["mask_downsample.weight"], self.w["mask_downsample.bias"], stride=4)     # [1,1,256,256]
         if self.native_heads:
-            dense = H.prompt_encoder(self.w, None, None, H.mask_prompt_256(prompt))[1]
+            dense = self.engine.mask_downscale(H.mask_prompt_256(prompt))
             ptr = self.engine.sam_heads(f2, hr, None, None, dense, multimask_output=False, high_res=False)[5]
         else:
             ptr = H.forward_sam_heads(self.w, f2, mask_inputs=prompt, high_res_features=hr, multimask_output=False, pe=self._dense_pe)[5]
@@ -616,7 +616,7 @@ class SAM2VideoPredictor(_Base):
         # ref: _use_multimask, sam2_base_official.py:1181-1189 (multimask_output_for_tracking, 0 <= points <= 1)
         multimask = pts.shape[0] <= 1
         if self.native_heads and pts.shape[0] > 0:
-            dense = None if prev_logits is None else H.prompt_encoder(self.w, None, None, H.mask_prompt_256(prev_logits))[1]
+            dense = None if prev_logits is None else self.engine.mask_downscale(H.mask_prompt_256(prev_logits))
             _, _, _, low, _, ptr, obj = self.engine.sam_heads(pix, hr, pts[None], lab[None], dense, multimask_output=multimask,
                                                               high_res=False)
         else:

@@ -33,8 +33,8 @@ def _make_engine(model, device, engine_factory):
 
 def _native_forward_sam_heads(model, engine):
     """SAM2Base._forward_sam_heads (ref: modeling/sam2_base_official.py:338-494) on the engine: same arguments, same 7 outputs.
-    The mask prompt keeps the reference's own down-scaling convolutions (sam/prompt_encoder.py:152-155) and enters the
-    library as the dense embedding; everything else is one sam2b_sam_heads call."""
+    The mask prompt's down-scaling convolutions (sam/prompt_encoder.py:152-155) are one library kernel (sam2b_mask_downscale) whose
+    result enters sam2b_sam_heads as the dense embedding; everything else is that one call."""
     import torch.nn.functional as F
 
     def forward(backbone_features, point_inputs=None, mask_inputs=None, high_res_features=None, multimask_output=False):
@@ -48,7 +48,7 @@ def _native_forward_sam_heads(model, engine):
             m = mask_inputs.float()
             if tuple(m.shape[-2:]) != size:
                 m = F.interpolate(m, size=size, align_corners=False, mode="bilinear", antialias=True)
-            dense = model.sam_prompt_encoder._embed_masks(m)
+            dense = engine.mask_downscale(m) if tuple(size) == (256, 256) else model.sam_prompt_encoder._embed_masks(m)
         dev = backbone_features.device
         low_multi, high_multi, ious, low, high, ptr, obj = engine.sam_heads(
             backbone_features.float(), [f.float() for f in high_res_features], coords, labels, dense,

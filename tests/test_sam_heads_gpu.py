@@ -185,3 +185,16 @@ def test_rejects_bad_arguments(engine):
         engine.sam_heads(pix.cpu(), hr)
     with pytest.raises(ValueError, match="memory_encode_low_res"):
         engine.memory_encode_low_res(pix, torch.randn(1, 1, 128, 128, device="cuda"))
+
+
+def test_mask_downscale_matches_the_prompt_encoder(engine, weights):
+    """sam2b_mask_downscale against the oracle's PromptEncoder mask branch (prompt_encoder.py:97-109,152-155), fp32."""
+    from oracle import sam2_oracle as O
+    g = torch.Generator().manual_seed(8)
+    m = 5.0 * torch.randn(3, 1, 256, 256, generator=g)
+    with torch.no_grad():
+        _, want = O.prompt_encoder(weights, None, None, m)
+    got = engine.mask_downscale(m.cuda())
+    r = rel_l2(got, want)
+    print(f"mask_downscale rel-L2 vs oracle = {r:.2e}")
+    assert got.shape == (3, 256, 64, 64) and r <= 1e-5
