@@ -201,6 +201,56 @@ def torch_gpu_baseline(dev, batch):
     return out
 
 
+def torch_gpu_video_baseline(dev, T):
+    """Config 3 on the same GPU through the UNMODIFIED reference `SAM2VideoPredictor` (its own per-object loop and memory-bank
+    assembly): (1) eager torch under bf16 autocast, the precision its own scripts use (sam2/sam2/benchmark.py:20-92); (2) the
+    same object after `predictor.speedup("b200")` — the drop-in a user of the reference gets before switching to this package's
+    batched predictor.  Host wall clock around the generator, every frame's masks read by the consumer."""
+    import numpy as np
+    import torch
+    from oracle import reference_loader as rl
+    from sam2_opt_b200.synth import synth_video
+    torch.set_grad_enabled(False)
+    if not rl.available():
+        return {"unavailable": "reference sources (oracle/_ref) not present"}
+    m, _ = _reference_model("video", dev)
+    import sam2.sam2_video_predictor_official as vpm
+    frames = synth_video(T, seed=1)
+    old_loader = vpm.load_video_frames
+    vpm.load_video_frames = lambda **k: (frames, 1024, 1024)
+
+    def run(n_frames):
+        st = m.init_state("synthetic")
+        m.add_new_points_or_box(st, 0, 1, points=np.array([[512, 512]], dtype=np.float32), labels=np.array([1], np.int32))
+        torch.cuda.synchronize(dev)
+        t0, n = time.perf_counter(), 0
+        for _, _, masks in m.propagate_in_video(st, max_frame_num_to_track=n_frames - 1):
+            (masks > 0).any().item()
+            n += 1
+        torch.cuda.synchronize(dev)
+        return n / (time.perf_counter() - t0)
+
+    out = {"kind": "reference", "api": "SAM2VideoPredictor.propagate_in_video (unmodified reference), 1 object, one click", "unit": "frames/s",
+           "frames_per_video": T}
+    try:
+        with torch.autocast("cuda", dtype=torch.bfloat16):
+            run(10)
+            out["bf16_autocast"] = run(T)
+        from sam2_opt_b200 import speedup as sp
+        sp.install(type(m))
+        m.speedup("b200")
+        run(20)
+        out["speedup_b200"] = run(T)
+        m.speedup("torch")
+    except Exception as ex:
+        out["unavailable"] = f"{type(ex).__name__}: {ex}"[:300]
+    finally:
+        vpm.load_video_frames = old_loader
+    del m
+    torch.cuda.empty_cache()
+    return out
+
+
 def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
@@ -548,6 +598,11 @@ def main():
             tgpu = torch_gpu_baseline(dev, B)
         except Exception as ex:      # a baseline must never take the headline line down with it
             tgpu = {"unavailable": f"{type(ex).__name__}: {ex}"[:300]}
+        if video is not None:
+            try:
+                video["torch_gpu_baseline"] = torch_gpu_video_baseline(dev, args.video_frames)
+            except Exception as ex:
+                video["torch_gpu_baseline"] = {"unavailable": f"{type(ex).__name__}: {ex}"[:300]}
 
     if rank == 0:
         print(json.dumps({
