@@ -98,7 +98,8 @@ def test_video_predictor_speedup_dropin(weights, golden):
         low = d["cond_frame_outputs" if fi == 0 else "non_cond_frame_outputs"][fi]["pred_masks"]
         np.testing.assert_allclose(low[0, 0, ::16, ::16].numpy(), golden["c3_low_res_slice"][fi], atol=2e-4)
     kinds = [c[0] for c in eng.calls]
-    assert kinds.count("image_encode") == T and kinds.count("memory_attention") == T - 1 and kinds.count("memory_encode") == T
+    # the frames are encoded in ONE block (speedup(encode_ahead=16) fills the reference's per-frame feature cache ahead)
+    assert kinds.count("image_encode") == 1 and kinds.count("memory_attention") == T - 1 and kinds.count("memory_encode") == T
     assert all(c[1:] == (True, False) for c in eng.calls if c[0] == "image_encode")   # E2: normalised in, no no_mem_embed
     assert [c[1:] for c in eng.calls if c[0] == "memory_attention"] == [(1, 4), (2, 8)]
     S.speedup(m, "torch")
