@@ -1,7 +1,8 @@
 """GPU: the tracked frame replayed from one CUDA graph (predictor._GraphedTrack; with two objects the
 graph also serves the frames where the bank is still filling: E3 at full size with device-side counts) against the same
 predictor enqueuing every call (graph_track=False).  The two differ only in the order of the memory-bank slots,
-i.e. in fp32 summation order inside the attention: per-frame mask IoU >= 0.999, object pointers rel-L2 <= 1e-3.
+i.e. in fp32 summation order inside the attention: per-frame mask IoU >= 0.998 (measured 0.9994; a real slot / age mix-up gave
+0.977), object pointers rel-L2 <= 1e-3 (measured 1e-4).
 
 Also covered: a workspace re-allocation between replays (a larger problem arrives: the captured addresses go stale and the
 graph must be captured again) and a correction click followed by a second propagation (the tracker starts over)."""
@@ -65,7 +66,7 @@ def test_graph_replay_matches_enqueued_frames(weights):
             worst = min(worst, _iou(a["pred_masks"], b["pred_masks"]))
             worst_ptr = max(worst_ptr, ((a["obj_ptr"] - b["obj_ptr"]).norm() / b["obj_ptr"].norm()).item())
     print(f"graph vs enqueued: worst mask IoU {worst:.5f}, worst pointer rel-L2 {worst_ptr:.2e}")
-    assert worst >= 0.999 and worst_ptr <= 1e-3
+    assert worst >= 0.998 and worst_ptr <= 1e-3
 
     # a correction click on a tracked frame, then a second propagation: both predictors must still agree
     for vp_, st_ in ((vp, st_g), (vp_e, st_e)):
@@ -74,6 +75,6 @@ def test_graph_replay_matches_enqueued_frames(weights):
         list(vp_.propagate_in_video(st_))
     worst = min(_iou(st_g["non_cond"][o][t]["pred_masks"], st_e["non_cond"][o][t]["pred_masks"]) for o in clicks for t in range(21, T))
     print(f"after a correction click: worst mask IoU {worst:.5f}")
-    assert worst >= 0.999
+    assert worst >= 0.998
     vp.release()
     vp_e.release()
