@@ -5,7 +5,9 @@
 586-736,843-945) over a plain ``state_dict`` with the reference's tensor names, so a user without the reference package
 installed (e.g. the GPU box) still has ``set_image`` / ``predict`` / ``init_state`` / ``add_new_points_or_box`` /
 ``propagate_in_video`` and the ``speedup()`` / ``release()`` switch.  The image encoder, memory attention and memory
-encoder run inside libsam2b.so; prompt encoder / mask decoder / memory-bank assembly are fp32 torch (``sam_heads.py``).
+encoder run inside libsam2b.so, and so do the prompt encoder / mask decoder / pointer head (``Engine.sam_heads``; the fp32 torch
+restatement in ``sam_heads.py`` remains as ``native_heads=False`` and as what the GPU tests compare against); the memory-bank
+assembly is device-resident rings plus, in steady state, one CUDA graph per tracked frame.
 
 Differences from the reference that are deliberate: all objects of a video are batched through the engine in one call
 per frame (the reference loops objects with batch 1, sam2_video_predictor_official.py:689-725), and frame embeddings are
