@@ -226,3 +226,41 @@ def test_gemm_layernorm_fold_sixteen_warps(code):
     ws = (ws - ws.mean(1, keepdim=True)).bfloat16()
     y = ops.gemm_ln_consumer(xb, ws, b + W @ beta, stats.contiguous(), 1e-6, act="gelu", block_n=2256)
     _close(y, torch.nn.functional.gelu(torch.nn.functional.layer_norm(x_ref, (C,), gamma, beta, 1e-6) @ W.t() + b), 1.5e-2)
+
+
+@pytest.mark.parametrize("kind,tol", [("outliers", 1.5e-2), ("mean5", 3e-2), ("mean50", 0.25)])
+def test_gemm_layernorm_fold_stress(kind, tol):
+    """Where the fold's rounding differs from LayerNorm-then-bf16: the rows reach the consumer GEMM un-centred, so a bf16
+    rounding step is relative to |x|, not to |x - mean|.  Outlier channels (a few channels at 100x the others, the 'massive
+    activations' of trained ViTs) cost nothing -- the error stays relative per element, as for LayerNorm output rounded to
+    bf16 -- while an offset common to all channels of a row grows the error as ~1.7e-3 (1 + |mean| / sigma) of the output
+    scale (same figure from a CPU model of the arithmetic; DESIGN.md section 2 'unpinned').  The statistics themselves
+    (sum, sum of squares in fp32) stay exact to 1e-4 in all three cases."""
+    from sam2_opt_b200 import ops
+    g = torch.Generator(device="cuda").manual_seed(len(kind))
+    M, C, Kp, N2 = 4096, 576, 256, 1152
+    a = torch.randn(M, Kp, device="cuda", generator=g).bfloat16()
+    wp = (torch.randn(C, Kp, device="cuda", generator=g) / Kp ** 0.5).bfloat16()
+    bp = torch.randn(C, device="cuda", generator=g)
+    res = torch.randn(M, C, device="cuda", generator=g) * 2
+    if kind == "outliers":
+        res[:, [5, 100, 400]] += torch.tensor([300.0, -250.0, 180.0], device="cuda")
+    else:
+        res += 2.2 * float(kind[4:])
+    x, xb, stats = ops.gemm_ln_producer(a, wp, bp, res)
+    x_ref = a.float() @ wp.float().t() + bp + res
+    s = stats.sum(1)
+    _close(s[:, 0], x_ref.sum(1), 1e-4)
+    _close(s[:, 1], (x_ref * x_ref).sum(1), 1e-4)
+    gamma = torch.rand(C, device="cuda", generator=g) + 0.5
+    beta = torch.randn(C, device="cuda", generator=g) * 0.3
+    W = torch.randn(N2, C, device="cuda", generator=g) / C ** 0.5
+    b = torch.randn(N2, device="cuda", generator=g)
+    ws = W * gamma[None, :]
+    ws = (ws - ws.mean(1, keepdim=True)).bfloat16()
+    y = ops.gemm_ln_consumer(xb, ws, b + W @ beta, stats.contiguous(), 1e-6, out_dtype=torch.float32)
+    y_ref = torch.nn.functional.layer_norm(x_ref, (C,), gamma, beta, 1e-6) @ W.t() + b
+    err = ((y - y_ref).abs().max() / y_ref.abs().max()).item()
+    ratio = (x_ref.mean(1).abs() / x_ref.std(1)).mean().item()
+    print(f"LayerNorm fold, {kind}: |mean|/sigma {ratio:.1f}, max err / scale {err:.3e}")
+    _close(y, y_ref, tol)
