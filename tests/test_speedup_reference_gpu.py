@@ -120,6 +120,38 @@ def test_reference_video_predictor_on_the_real_engine(weights):
     engine.release()
 
 
+def test_reference_vos_flow_mask_prompts_on_the_real_engine(weights):
+    """the flow of the reference's tools/vos_inference.py:175-205 (`init_state`, one `add_new_mask` per object
+    on the first frame, `propagate_in_video`) through the reference's SAM2VideoPredictor, torch path vs speedup("b200") on the
+    same device.  `_use_mask_as_output` (sam2_base_official.py:496-546) keeps the mask itself as the frame's output and calls the
+    rebound `_forward_sam_heads` with the down-sampled mask as prompt for the object pointer."""
+    import ref_gpu
+    from oracle.synth import synth_video
+    from sam2_opt_b200 import speedup as S
+    from sam2_opt_b200.engine import launch_count
+    torch.set_grad_enabled(False)
+    T = 9
+    frames = synth_video(T, seed=2)
+    yy, xx = np.mgrid[0:1024, 0:1024]
+    masks = {1: (xx - 420) ** 2 + (yy - 500) ** 2 < 170 ** 2, 2: (np.abs(xx - 760) < 90) & (np.abs(yy - 300) < 140)}
+    m = ref_gpu.build("video", weights)
+    S.install(type(m))
+    ref, ref_ptr = ref_gpu.propagate_low_res_from_masks(m, frames, masks)
+    l0 = launch_count()
+    m.speedup("b200")
+    got, got_ptr = ref_gpu.propagate_low_res_from_masks(m, frames, masks)
+    assert launch_count() - l0 > 1000 and sorted(got) == list(range(T))
+    for oid in masks:
+        assert torch.allclose(got[0][oid], ref[0][oid], atol=1e-4), "the prompted frame is the mask itself"
+        r = rel_l2(got_ptr[oid], ref_ptr[oid])
+        ious = [ref_gpu.iou((got[t][oid] > 0).numpy(), (ref[t][oid] > 0).numpy()) for t in range(1, T)]
+        print(f"reference VOS flow + b200 engine, object {oid}: frame-0 pointer rel-L2 {r:.3e}, propagated IoU min {min(ious):.4f}")
+        assert r <= 2e-2 and min(ious) >= 0.99
+    engine = m._sam2b_engine
+    m.speedup("torch")
+    engine.release()
+
+
 def test_reference_automatic_mask_generator_on_the_real_engine(weights):
     """SURVEY section 8 f-4 (other consumers of the same kernels): the reference's SAM2AutomaticMaskGenerator
     (automatic_mask_generator.py:170-294) owns a SAM2ImagePredictor, so `generator.predictor.speedup("b200")` is all it takes.
