@@ -125,6 +125,11 @@ def _heads_config_supported(model) -> bool:
     md = getattr(model, "sam_mask_decoder", None)
     if md is None:
         return False
+    # the fork's DAM4SAM track (SAM2_VERSION_TRACK=dam4sam, modeling/sam2_base_dam4sam.py:338-503) returns an eighth value from
+    # `_forward_sam_heads` (all candidate masks and IoUs as numpy, for its distractor memory) and overwrites the multimask
+    # outputs with the chosen mask: it keeps its own torch heads, E2 / E3 / E4 are rebound as usual
+    if "dam4sam" in (getattr(getattr(type(model), "_forward_sam_heads", None), "__module__", "") or ""):
+        return False
     want_model = dict(use_high_res_features_in_sam=True, pred_obj_scores=True, fixed_no_obj_ptr=True, soft_no_obj_ptr=False,
                       use_obj_ptrs_in_encoder=True)
     want_md = dict(use_multimask_token_for_obj_ptr=True, dynamic_multimask_via_stability=True, pred_obj_scores=True,

@@ -49,3 +49,30 @@ def test_assemble_memory_two_cond_frames_and_gap(w):
     got = H.assemble_memory(w, 12, cond, non_cond, 64, cache={})
     for a, b in zip(got, ref):
         torch.testing.assert_close(a.float(), b.float(), rtol=1e-5, atol=1e-6)
+
+
+def test_heads_hook_is_declined_for_other_head_configurations():
+    """speedup() rebinds `_forward_sam_heads` only for the SAM2.1 head configuration the library implements, and never for the
+    fork's DAM4SAM track, whose heads return an eighth value (ref: modeling/sam2_base_dam4sam.py:493-503)."""
+    import types
+    from sam2_opt_b200.speedup import _heads_config_supported
+    md = types.SimpleNamespace(use_multimask_token_for_obj_ptr=True, dynamic_multimask_via_stability=True, pred_obj_scores=True,
+                               use_high_res_features=True, dynamic_multimask_stability_delta=0.05, dynamic_multimask_stability_thresh=0.98)
+
+    def make(module):
+        fn = lambda self, *a, **k: None
+        fn.__module__ = module
+        cls = type("Model", (), {"_forward_sam_heads": fn})
+        m = cls()
+        m.sam_mask_decoder = md
+        for k, v in dict(use_high_res_features_in_sam=True, pred_obj_scores=True, fixed_no_obj_ptr=True, soft_no_obj_ptr=False,
+                         use_obj_ptrs_in_encoder=True, training=False).items():
+            setattr(m, k, v)
+        return m
+
+    assert _heads_config_supported(make("sam2.modeling.sam2_base_official"))
+    assert not _heads_config_supported(make("sam2.modeling.sam2_base_dam4sam"))
+    soft = make("sam2.modeling.sam2_base_official")
+    soft.soft_no_obj_ptr = True
+    assert not _heads_config_supported(soft)
+    assert not _heads_config_supported(types.SimpleNamespace())
