@@ -89,8 +89,25 @@ def derive_heads(w: Dict[str, torch.Tensor]) -> Dict[str, torch.Tensor]:
     return d
 
 
+def check_architecture(w: Dict[str, torch.Tensor]) -> None:
+    """The kernels are built for SAM2.1 Hiera-L (ref: configs/sam2.1/sam2.1_hiera_l.yaml: embed_dim 144, stages (2, 6, 36, 4),
+    window_spec (8, 4, 16, 8), 7x7 / 8x8 position-embedding background / window).  Any other trunk (Hiera-T / S / B+ have head
+    dims 96 / 56 and 14 x 14 windows that need padding) is refused here, by name, before anything is uploaded."""
+    t = "image_encoder.trunk."
+    pe = w.get(t + "patch_embed.proj.weight")
+    if pe is None:
+        raise ValueError("state_dict has no image_encoder.trunk.patch_embed.proj.weight: not a SAM2 model")
+    n_blocks = 1 + max((int(k[len(t) + 7:].split(".")[0]) for k in w if k.startswith(t + "blocks.")), default=-1)
+    win = tuple(w[t + "pos_embed_window"].shape[-2:]) if t + "pos_embed_window" in w else None
+    got = (int(pe.shape[0]), n_blocks, win)
+    if got != (144, 48, (8, 8)):
+        raise ValueError(f"sam2_opt_b200 implements the SAM2.1 Hiera-L trunk (embed_dim 144, 48 blocks, 8x8 window embedding); this "
+                         f"state_dict has embed_dim {got[0]}, {got[1]} blocks, window embedding {got[2]}: keep it on the torch path")
+
+
 def derive(w: Dict[str, torch.Tensor]) -> Dict[str, torch.Tensor]:
     """Derived constants for the engine (all fp32, same device as the weights)."""
+    check_architecture(w)
     d = {}
     dev = w["image_encoder.trunk.pos_embed"].device
     pw = w["image_encoder.trunk.patch_embed.proj.weight"].float().reshape(144, 147)

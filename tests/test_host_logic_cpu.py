@@ -76,3 +76,17 @@ def test_heads_hook_is_declined_for_other_head_configurations():
     soft.soft_no_obj_ptr = True
     assert not _heads_config_supported(soft)
     assert not _heads_config_supported(types.SimpleNamespace())
+
+
+def test_other_hiera_sizes_are_refused_by_name():
+    """weights.derive runs before anything reaches the device: a trunk that is not Hiera-L is refused with its dimensions in the
+    message (ref: configs/sam2.1/sam2.1_hiera_b+.yaml: embed_dim 112, stages (2, 3, 16, 3))."""
+    from sam2_opt_b200 import weights
+    w = O.make_weights(0)
+    weights.check_architecture(w)
+    small = {k: v for k, v in w.items() if not k.startswith("image_encoder.trunk.blocks.") or int(k.split(".")[3]) < 24}
+    small["image_encoder.trunk.patch_embed.proj.weight"] = torch.zeros(112, 3, 7, 7)
+    with pytest.raises(ValueError, match="embed_dim 112, 24 blocks"):
+        weights.derive(small)
+    with pytest.raises(ValueError, match="not a SAM2 model"):
+        weights.check_architecture({"foo": torch.zeros(1)})
