@@ -65,7 +65,14 @@ def encode_images_sharded(encode_fn, images: torch.Tensor, group=None):
     n = images.shape[0]
     counts = [split_range(n, world, r)[1] - split_range(n, world, r)[0] for r in range(world)]
     lo, hi = split_range(n, world, rank)
-    outs = encode_fn(images[lo:hi])
+    outs = encode_fn(images[lo:hi]) if hi > lo else None
+    if min(counts) == 0:
+        # fewer images than ranks: the engine refuses an empty batch (sam2b_image_encode: n <= 0), so a rank without images
+        # does not call it and contributes zero rows; it learns the levels' shapes from rank 0, which always has an image
+        meta = [[(tuple(o.shape[1:]), o.dtype) for o in outs] if rank == 0 else None]
+        dist.broadcast_object_list(meta, src=dist.get_global_rank(group, 0) if group is not None else 0, group=group)
+        if outs is None:
+            outs = tuple(torch.empty((0,) + shp, dtype=dt, device=images.device) for shp, dt in meta[0])
     return tuple(all_gather_batch(o, counts, group) for o in outs)
 
 

@@ -106,7 +106,11 @@ def _gather_worker(rank, world, port, q):
         g.close()
         # a global batch smaller than the world: the rank with an empty slice contributes zero rows
         images = torch.arange(3 * 4 * 4, dtype=torch.float32).reshape(1, 3, 4, 4)
-        outs = shard.encode_images_sharded(lambda x: (x * 2.0, x.flatten(1)), images)
+        def encode_nonempty(x):      # like the engine (sam2b_image_encode rejects n <= 0): never called on an empty slice
+            assert x.shape[0] > 0
+            return x * 2.0, x.flatten(1)
+
+        outs = shard.encode_images_sharded(encode_nonempty, images)
         ok = ok and torch.equal(outs[0], images * 2.0) and torch.equal(outs[1], images.flatten(1))
         q.put((rank, bool(ok)))
     finally:
